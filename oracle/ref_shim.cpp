@@ -1,0 +1,415 @@
+// TEST INFRASTRUCTURE ONLY -- never linked into the product library.
+//
+// C-ABI shim around the UNMODIFIED reference headers (mpetri/ans-large-alphabet,
+// /root/reference/include).  It is compiled by oracle/Makefile straight from the
+// sources where they lie (-I/root/reference/include) into oracle/_ref/libansref.so
+// and is used (a) to pin the C restatement in oracle/ans_oracle.c, (b) as the
+// per-block / whole-stream oracle of the -m gpu parity tests and (c) as the CPU
+// baseline ("kind": "reference") of bench.py.  No reference source is copied here:
+// this file only *calls* the reference.
+//
+// Include-order note: namespace `constants` used by every coder
+// lives in ans_byte.hpp, so that header comes first.
+#include <algorithm>
+#include <array>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <numeric>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "ans_byte.hpp"
+#include "ans_fold.hpp"
+#include "ans_int.hpp"
+#include "ans_msb.hpp"
+#include "ans_reorder_fold.hpp"
+#include "zipf_dist.hpp"
+
+enum { M_INT = 0, M_FOLD = 1, M_MSB = 2, M_RFOLD = 3 };
+
+#define FOLD_DISPATCH(f, EXPR)                                                                 \
+    switch (f) {                                                                               \
+    case 1: { constexpr uint32_t F = 1; EXPR; } break;                                         \
+    case 2: { constexpr uint32_t F = 2; EXPR; } break;                                         \
+    case 3: { constexpr uint32_t F = 3; EXPR; } break;                                         \
+    case 4: { constexpr uint32_t F = 4; EXPR; } break;                                         \
+    case 5: { constexpr uint32_t F = 5; EXPR; } break;                                         \
+    case 6: { constexpr uint32_t F = 6; EXPR; } break;                                         \
+    case 7: { constexpr uint32_t F = 7; EXPR; } break;                                         \
+    case 8: { constexpr uint32_t F = 8; EXPR; } break;                                         \
+    default: return -1;                                                                        \
+    }
+
+// ---------------------------------------------------------------------------
+// generic per-block drivers: the loops of ans_fold.hpp:250-278 / :291-310 applied to a
+// sub-range through the model's own members (SURVEY.md section 8(c) "per-block oracle").
+// ---------------------------------------------------------------------------
+template <class Enc>
+static size_t encode_range(Enc& m, const uint32_t* in, size_t n, uint8_t* dst)
+{
+    uint8_t* out = dst;
+    std::array<uint64_t, 4> st;
+    for (auto& s : st)
+        s = m.initial_state();
+    size_t cur = 0;
+    while ((n - cur) % 4 != 0) {
+        m.encode_symbol(st[0], in[n - cur - 1], out);
+        cur += 1;
+    }
+    while (cur != n) {
+        m.encode_symbol(st[0], in[n - cur - 1], out);
+        m.encode_symbol(st[1], in[n - cur - 2], out);
+        m.encode_symbol(st[2], in[n - cur - 3], out);
+        m.encode_symbol(st[3], in[n - cur - 4], out);
+        cur += 4;
+    }
+    for (auto& s : st)
+        m.flush_state(s, out);
+    return out - dst;
+}
+
+// fold / msb / rfold decoders share decode_sym(state, in); ans_int needs the entry type.
+template <class Dec, class Fn>
+static void decode_range(Dec& m, const uint8_t* src, size_t bytes, uint32_t* out, size_t n, Fn sym)
+{
+    const uint8_t* in = src + bytes;
+    std::array<uint64_t, 4> st;
+    st[3] = m.init_state(in);
+    st[2] = m.init_state(in);
+    st[1] = m.init_state(in);
+    st[0] = m.init_state(in);
+    size_t i = 0, fast = n - (n % 4);
+    while (i != fast) {
+        out[i] = sym(m, st[3], in);
+        out[i + 1] = sym(m, st[2], in);
+        out[i + 2] = sym(m, st[1], in);
+        out[i + 3] = sym(m, st[0], in);
+        i += 4;
+    }
+    while (i != n)
+        out[i++] = sym(m, st[0], in);
+}
+
+struct ref_model {
+    int method;
+    uint32_t f;
+    void* enc; // ans_*_encode*
+    void* dec; // ans_*_decode*
+};
+
+template <class T> static void del(void* p) { delete static_cast<T*>(p); }
+
+extern "C" {
+
+// ---- whole-stream reference coders (methods.hpp:484-567 call exactly these) ----------
+long ref_compress(int method, uint32_t f, uint8_t* dst, size_t cap, const uint32_t* src, size_t n)
+{
+    switch (method) {
+    case M_INT: return (long)ans_int_compress(dst, cap, src, n);
+    case M_MSB: return (long)ans_msb_compress(dst, cap, src, n);
+    case M_FOLD: FOLD_DISPATCH(f, return (long)ans_fold_compress<F>(dst, cap, src, n));
+    case M_RFOLD: FOLD_DISPATCH(f, return (long)ans_reorder_fold_compress<F>(dst, cap, src, n));
+    }
+    return -1;
+}
+
+int ref_decompress(int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src, size_t bytes)
+{
+    switch (method) {
+    case M_INT: ans_int_decompress(dst, n, src, bytes); return 0;
+    case M_MSB: ans_msb_decompress(dst, n, src, bytes); return 0;
+    case M_FOLD: FOLD_DISPATCH(f, ans_fold_decompress<F>(dst, n, src, bytes); return 0);
+    case M_RFOLD: FOLD_DISPATCH(f, ans_reorder_fold_decompress<F>(dst, n, src, bytes); return 0);
+    }
+    return -1;
+}
+
+// ---- model API (ans_util.hpp) ----------------------------------------------------------
+// out must hold largest_sym+1 entries.
+int ref_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_t largest_sym, int require_u16,
+    uint32_t H_approx, uint32_t* out)
+{
+    std::vector<uint64_t> F(freqs, freqs + nbins);
+    auto s = adjust_freqs(F, largest_sym, require_u16 != 0, H_approx);
+    std::copy(s.begin(), s.end(), out);
+    return (int)s.size();
+}
+
+// returns total prelude bytes (vbyte + log2 byte + interp words) written to out
+long ref_serialize_interp(const uint32_t* nfreqs, size_t count, uint64_t frame_size, uint8_t* out)
+{
+    std::vector<uint32_t> v(nfreqs, nfreqs + count);
+    uint8_t* p = out;
+    ans_serialize_interp(v, frame_size, p);
+    return p - out;
+}
+
+// out must hold max_sym+1 entries (call with out==NULL to get the count)
+long ref_load_interp(const uint8_t* in, uint32_t* out)
+{
+    auto v = ans_load_interp(in);
+    if (out)
+        std::copy(v.begin(), v.end(), out);
+    return (long)v.size();
+}
+
+long ref_interp_encode(uint32_t* dst, const uint32_t* in, size_t n, size_t u)
+{
+    return (long)interpolative_internal::encode(dst, in, n, u);
+}
+long ref_interp_decode(const uint32_t* src, uint32_t* out, size_t n, size_t u)
+{
+    return (long)interpolative_internal::decode(src, out, n, u);
+}
+
+// ---- mappings (known-answer material of src/test.cpp:49-71) ----------------------------
+int ref_fold_mapping(uint32_t f, uint32_t x, uint32_t* mapped)
+{
+    FOLD_DISPATCH(f, *mapped = ans_fold_mapping<F>(x); return 0);
+    return -1;
+}
+int ref_fold_undo(uint32_t f, uint32_t s, uint32_t* value, uint32_t* bytes)
+{
+    FOLD_DISPATCH(f, *value = ans_fold_undo_mapping<F>(s); *bytes = ans_fold_exception_bytes<F>(s); return 0);
+    return -1;
+}
+uint32_t ref_msb_mapping(uint32_t x) { return ans_msb_mapping(x); }
+void ref_msb_undo(uint32_t s, uint32_t* value, uint32_t* bytes)
+{
+    *value = ans_msb_undo_mapping(s);
+    *bytes = ans_msb_exception_bytes(s);
+}
+
+// ---- models + per-block oracle -----------------------------------------------------------
+ref_model* ref_model_create(int method, uint32_t f, const uint32_t* in, size_t n)
+{
+    auto* m = new ref_model { method, f, nullptr, nullptr };
+    switch (method) {
+    case M_INT: m->enc = new ans_int_encode(ans_int_encode::create(in, n)); return m;
+    case M_MSB: m->enc = new ans_msb_encode(ans_msb_encode::create(in, n)); return m;
+    case M_FOLD:
+        switch (f) {
+#define C(F) case F: m->enc = new ans_fold_encode<F>(ans_fold_encode<F>::create(in, n)); return m;
+            C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+        }
+        break;
+    case M_RFOLD:
+        switch (f) {
+#define C(F) case F: m->enc = new ans_reorder_fold_encode<F>(ans_reorder_fold_encode<F>::create(in, n)); return m;
+            C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+        }
+        break;
+    }
+    delete m;
+    return nullptr;
+}
+
+#define WITH_ENC(m, EXPR)                                                                      \
+    switch ((m)->method) {                                                                     \
+    case M_INT: { auto& e = *static_cast<ans_int_encode*>((m)->enc); EXPR; } break;            \
+    case M_MSB: { auto& e = *static_cast<ans_msb_encode*>((m)->enc); EXPR; } break;            \
+    case M_FOLD: FOLD_DISPATCH((m)->f, auto& e = *static_cast<ans_fold_encode<F>*>((m)->enc); EXPR); break; \
+    case M_RFOLD: FOLD_DISPATCH((m)->f, auto& e = *static_cast<ans_reorder_fold_encode<F>*>((m)->enc); EXPR); break; \
+    }
+
+long ref_model_info(ref_model* m, uint64_t* frame_size, uint32_t* nfreqs_out)
+{
+    WITH_ENC(m, *frame_size = e.frame_size; if (nfreqs_out) std::copy(e.nfreqs.begin(), e.nfreqs.end(), nfreqs_out);
+             return (long)e.nfreqs.size());
+    return -1;
+}
+
+long ref_model_serialize(ref_model* m, uint8_t* out)
+{
+    uint8_t* p = out;
+    WITH_ENC(m, e.serialize(p); return p - out);
+    return -1;
+}
+
+// rfold only: most_frequent list (empty when sigma < 2^(f+7)) and sigma
+long ref_model_rfold_info(ref_model* m, uint64_t* sigma, uint32_t* most_frequent_out)
+{
+    if (m->method != M_RFOLD)
+        return -1;
+    FOLD_DISPATCH(m->f, auto& e = *static_cast<ans_reorder_fold_encode<F>*>(m->enc); *sigma = e.sigma;
+                  if (most_frequent_out) std::copy(e.most_frequent.begin(), e.most_frequent.end(), most_frequent_out);
+                  return (long)e.most_frequent.size());
+    return -1;
+}
+
+long ref_encode_block(ref_model* m, const uint32_t* in, size_t n, uint8_t* dst)
+{
+    WITH_ENC(m, return (long)encode_range(e, in, n, dst));
+    return -1;
+}
+
+// decoder side: load() from a reference-format prelude
+ref_model* ref_model_load(int method, uint32_t f, const uint8_t* prelude)
+{
+    auto* m = new ref_model { method, f, nullptr, nullptr };
+    switch (method) {
+    case M_INT: m->dec = new ans_int_decode(ans_int_decode::load(prelude)); return m;
+    case M_MSB: m->dec = new ans_msb_decode(ans_msb_decode::load(prelude)); return m;
+    case M_FOLD:
+        switch (f) {
+#define C(F) case F: m->dec = new ans_fold_decode<F>(ans_fold_decode<F>::load(prelude)); return m;
+            C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+        }
+        break;
+    case M_RFOLD:
+        switch (f) {
+#define C(F) case F: m->dec = new ans_reorder_fold_decode<F>(ans_reorder_fold_decode<F>::load(prelude)); return m;
+            C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+        }
+        break;
+    }
+    delete m;
+    return nullptr;
+}
+
+int ref_decode_block(ref_model* m, const uint8_t* src, size_t bytes, uint32_t* out, size_t n)
+{
+    switch (m->method) {
+    case M_INT: {
+        auto& d = *static_cast<ans_int_decode*>(m->dec);
+        if (d.table_type == dec_table_type::SMALL)
+            decode_range(d, src, bytes, out, n, [](ans_int_decode& mm, uint64_t& s, const uint8_t*& in) {
+                return mm.decode_sym<dec_entry_int_small>(s, in);
+            });
+        else
+            decode_range(d, src, bytes, out, n, [](ans_int_decode& mm, uint64_t& s, const uint8_t*& in) {
+                return mm.decode_sym<dec_entry_int>(s, in);
+            });
+        return 0;
+    }
+    case M_MSB: {
+        auto& d = *static_cast<ans_msb_decode*>(m->dec);
+        decode_range(d, src, bytes, out, n,
+            [](ans_msb_decode& mm, uint64_t& s, const uint8_t*& in) { return mm.decode_sym(s, in); });
+        return 0;
+    }
+    case M_FOLD:
+        FOLD_DISPATCH(m->f, auto& d = *static_cast<ans_fold_decode<F>*>(m->dec);
+                      decode_range(d, src, bytes, out, n,
+                          [](ans_fold_decode<F>& mm, uint64_t& s, const uint8_t*& in) { return mm.decode_sym(s, in); });
+                      return 0);
+        break;
+    case M_RFOLD:
+        FOLD_DISPATCH(m->f, auto& d = *static_cast<ans_reorder_fold_decode<F>*>(m->dec);
+                      decode_range(d, src, bytes, out, n,
+                          [](ans_reorder_fold_decode<F>& mm, uint64_t& s, const uint8_t*& in) { return mm.decode_sym(s, in); });
+                      return 0);
+        break;
+    }
+    return -1;
+}
+
+void ref_model_free(ref_model* m)
+{
+    if (!m)
+        return;
+    if (m->enc) {
+        switch (m->method) {
+        case M_INT: del<ans_int_encode>(m->enc); break;
+        case M_MSB: del<ans_msb_encode>(m->enc); break;
+        case M_FOLD:
+            switch (m->f) {
+#define C(F) case F: del<ans_fold_encode<F>>(m->enc); break;
+                C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+            }
+            break;
+        case M_RFOLD:
+            switch (m->f) {
+#define C(F) case F: del<ans_reorder_fold_encode<F>>(m->enc); break;
+                C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+            }
+            break;
+        }
+    }
+    if (m->dec) {
+        switch (m->method) {
+        case M_INT: del<ans_int_decode>(m->dec); break;
+        case M_MSB: del<ans_msb_decode>(m->dec); break;
+        case M_FOLD:
+            switch (m->f) {
+#define C(F) case F: del<ans_fold_decode<F>>(m->dec); break;
+                C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+            }
+            break;
+        case M_RFOLD:
+            switch (m->f) {
+#define C(F) case F: del<ans_reorder_fold_decode<F>>(m->dec); break;
+                C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+            }
+            break;
+        }
+    }
+    delete m;
+}
+
+// ---- input generators of src/generate_inputs.cpp:70-117 (mt19937 + libstdc++ / zipf_dist.hpp)
+// kind: 0 = zipf(range, q) ; 1 = geometric(q) ; 2 = uniform [0, range) ; `sub` is subtracted
+// from every value (SURVEY.md C5 uses zipf(2^20, 1.2) - 1).
+int ref_generate(int kind, uint32_t seed, uint32_t range, double q, uint32_t sub, uint32_t* out, size_t n)
+{
+    std::mt19937 gen(seed);
+    if (kind == 0) {
+        zipf_distribution<uint32_t> d(range, q);
+        for (size_t i = 0; i < n; i++)
+            out[i] = d(gen) - sub;
+    } else if (kind == 1) {
+        std::geometric_distribution<uint32_t> d(q);
+        for (size_t i = 0; i < n; i++)
+            out[i] = d(gen) - sub;
+    } else if (kind == 2) {
+        std::uniform_int_distribution<uint32_t> d(0, range - 1);
+        for (size_t i = 0; i < n; i++)
+            out[i] = d(gen) - sub;
+    } else
+        return -1;
+    return 0;
+}
+
+// table_efficiency.cpp:77-101 style timing: min of `runs`, ns. Round trip is verified.
+int ref_time(int method, uint32_t f, const uint32_t* in, size_t n, int runs, double* enc_ns, double* dec_ns,
+    size_t* bytes)
+{
+    std::vector<uint8_t> out(n * 8 + 4096);
+    std::vector<uint32_t> rec(n + 16);
+    double be = 1e300, bd = 1e300;
+    long nb = 0;
+    for (int r = 0; r < runs; r++) {
+        auto t0 = std::chrono::high_resolution_clock::now();
+        nb = ref_compress(method, f, out.data(), out.size(), in, n);
+        auto t1 = std::chrono::high_resolution_clock::now();
+        if (nb < 0)
+            return -1;
+        be = std::min(be, (double)std::chrono::duration_cast<std::chrono::nanoseconds>(t1 - t0).count());
+    }
+    for (int r = 0; r < runs; r++) {
+        auto t0 = std::chrono::high_resolution_clock::now();
+        ref_decompress(method, f, rec.data(), n, out.data(), nb);
+        auto t1 = std::chrono::high_resolution_clock::now();
+        bd = std::min(bd, (double)std::chrono::duration_cast<std::chrono::nanoseconds>(t1 - t0).count());
+    }
+    if (std::memcmp(rec.data(), in, n * sizeof(uint32_t)) != 0)
+        return -2;
+    *enc_ns = be;
+    *dec_ns = bd;
+    *bytes = (size_t)nb;
+    return 0;
+}
+
+} // extern "C"
