@@ -1,0 +1,308 @@
+"""ctypes binding of include/b200ans.h (every exported symbol is declared here)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+METHOD_INT, METHOD_FOLD, METHOD_MSB, METHOD_RFOLD = 0, 1, 2, 3
+HEADER_BYTES = 64
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+u8p = C.POINTER(C.c_uint8)
+u32p = C.POINTER(C.c_uint32)
+u64p = C.POINTER(C.c_uint64)
+szp = C.POINTER(C.c_size_t)
+
+
+class B200AnsError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"b200ans error {code}: {msg}")
+        self.code = code
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("ms_histogram", C.c_float), ("ms_model", C.c_float), ("ms_encode", C.c_float),
+        ("ms_compact", C.c_float), ("ms_decode", C.c_float), ("ms_h2d", C.c_float), ("ms_d2h", C.c_float),
+        ("launches", C.c_uint64), ("frame_size", C.c_uint64), ("n_symbols_model", C.c_uint32),
+        ("n_blocks", C.c_uint32), ("prelude_bytes", C.c_uint64), ("payload_bytes", C.c_uint64),
+        ("total_bytes", C.c_uint64),
+    ]
+
+
+# name -> (restype, argtypes); this is the complete export list of include/b200ans.h
+SIGNATURES = {
+    "b200ans_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p]),
+    "b200ans_destroy": (None, [C.c_void_p]),
+    "b200ans_set_block_syms": (C.c_int, [C.c_void_p, C.c_uint32]),
+    "b200ans_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "b200ans_last_error": (C.c_char_p, [C.c_void_p]),
+    "b200ans_strerror": (C.c_char_p, [C.c_int]),
+    "b200ans_method_name": (C.c_char_p, [C.c_int, C.c_uint32, C.c_char_p, C.c_size_t]),
+    "b200ans_compress_bound": (C.c_size_t, [C.c_void_p, C.c_int, C.c_size_t]),
+    "b200ans_compress": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
+    "b200ans_decompress": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "b200ans_compress_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
+    "b200ans_decompress_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "b200ans_max_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200ans_histogram_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "b200ans_rfold_prepare": (C.c_int, [C.c_void_p, C.c_uint32, u64p, C.c_size_t]),
+    "b200ans_model_build": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u64p, C.c_size_t]),
+    "b200ans_model_prelude": (C.c_int, [C.c_void_p, u8p, C.c_size_t, szp]),
+    "b200ans_model_nfreqs": (C.c_int, [C.c_void_p, u32p, C.c_size_t, szp, u64p]),
+    "b200ans_model_load": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u8p, C.c_size_t, szp]),
+    "b200ans_encode_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
+    "b200ans_encode_blocks_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200ans_block_stride": (C.c_int, [C.c_void_p, C.c_int, szp]),
+    "b200ans_decode_blocks_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200ans_adjust_freqs": (C.c_int, [u64p, C.c_size_t, C.c_uint32, C.c_int, C.c_uint32, u32p]),
+    "b200ans_serialize_interp": (C.c_int, [u32p, C.c_size_t, C.c_uint64, u8p, C.c_size_t, szp]),
+    "b200ans_load_interp": (C.c_int, [u8p, u32p, C.c_size_t, szp, szp]),
+    "b200ans_interp_encode": (C.c_int, [u32p, u32p, C.c_size_t, C.c_size_t, szp]),
+    "b200ans_interp_decode": (C.c_int, [u32p, u32p, C.c_size_t, C.c_size_t, szp]),
+    "b200ans_fold_map": (C.c_uint32, [C.c_uint32, C.c_uint32, u32p]),
+    "b200ans_fold_unmap": (C.c_uint32, [C.c_uint32, C.c_uint32, u32p]),
+    "b200ans_msb_map": (C.c_uint32, [C.c_uint32, u32p]),
+    "b200ans_msb_unmap": (C.c_uint32, [C.c_uint32, u32p]),
+}
+
+
+def library_path():
+    return os.path.join(_HERE, "libb200ans.so")
+
+
+def build_library(force=False):
+    """nvcc -gencode arch=compute_100a,code=sm_100a ... -> libb200ans.so (in-tree)."""
+    if force and os.path.exists(library_path()):
+        os.remove(library_path())
+    subprocess.check_call(["make", "-C", _HERE, "libb200ans.so"])
+    return library_path()
+
+
+def load_library():
+    """Load the CUDA library.  There is deliberately no fallback: a missing library is an error."""
+    global _LIB
+    if _LIB is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise ImportError(
+                f"{path} is missing: build it with `make -C {_HERE}` (or __graft_entry__.build()); "
+                "b200ans has no CPU fallback")
+        lib = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError here = header/library mismatch
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = lib
+    return _LIB
+
+
+def method_name(method, fidelity=0):
+    buf = C.create_string_buffer(32)
+    return load_library().b200ans_method_name(method, fidelity, buf, 32).decode()
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t)
+
+
+class _HostApi:
+    """ans_util.hpp-shaped host functions (work without a GPU)."""
+
+    def __init__(self):
+        self.lib = load_library()
+
+    def adjust_freqs(self, freqs, largest_sym, require_u16, h_approx=1):
+        freqs = np.ascontiguousarray(freqs, dtype=np.uint64)
+        out = np.zeros(largest_sym + 1, dtype=np.uint32)
+        rc = self.lib.b200ans_adjust_freqs(_p(freqs, u64p), freqs.size, largest_sym, int(require_u16), h_approx, _p(out, u32p))
+        if rc:
+            raise B200AnsError(rc, "adjust_freqs")
+        return out
+
+    def serialize_interp(self, nfreqs, frame_size):
+        nfreqs = np.ascontiguousarray(nfreqs, dtype=np.uint32)
+        out = np.zeros(nfreqs.size * 8 + 64, dtype=np.uint8)
+        nb = C.c_size_t()
+        rc = self.lib.b200ans_serialize_interp(_p(nfreqs, u32p), nfreqs.size, frame_size, _p(out, u8p), out.size, C.byref(nb))
+        if rc:
+            raise B200AnsError(rc, "serialize_interp")
+        return out[: nb.value].copy()
+
+    def load_interp(self, blob):
+        buf = np.zeros(len(blob) + 16, dtype=np.uint8)
+        buf[: len(blob)] = blob
+        cnt, used = C.c_size_t(), C.c_size_t()
+        rc = self.lib.b200ans_load_interp(_p(buf, u8p), None, 0, C.byref(cnt), None)
+        if rc:
+            raise B200AnsError(rc, "load_interp")
+        out = np.zeros(cnt.value, dtype=np.uint32)
+        rc = self.lib.b200ans_load_interp(_p(buf, u8p), _p(out, u32p), out.size, C.byref(cnt), C.byref(used))
+        if rc:
+            raise B200AnsError(rc, "load_interp")
+        return out, used.value
+
+    def interp_encode(self, values, universe):
+        values = np.ascontiguousarray(values, dtype=np.uint32)
+        out = np.zeros(values.size * 2 + 16, dtype=np.uint32)
+        nb = C.c_size_t()
+        self.lib.b200ans_interp_encode(_p(out, u32p), _p(values, u32p), values.size, universe, C.byref(nb))
+        return out[: nb.value // 4].copy()
+
+    def interp_decode(self, words, n, universe):
+        buf = np.zeros(len(words) + 4, dtype=np.uint32)
+        buf[: len(words)] = words
+        out = np.zeros(n, dtype=np.uint32)
+        self.lib.b200ans_interp_decode(_p(buf, u32p), _p(out, u32p), n, universe, None)
+        return out
+
+    def fold_map(self, f, x):
+        k = C.c_uint32()
+        s = self.lib.b200ans_fold_map(f, int(x), C.byref(k))
+        return s, k.value
+
+    def fold_unmap(self, f, s):
+        k = C.c_uint32()
+        v = self.lib.b200ans_fold_unmap(f, int(s), C.byref(k))
+        return v, k.value
+
+    def msb_map(self, x):
+        k = C.c_uint32()
+        s = self.lib.b200ans_msb_map(int(x), C.byref(k))
+        return s, k.value
+
+    def msb_unmap(self, s):
+        k = C.c_uint32()
+        v = self.lib.b200ans_msb_unmap(int(s), C.byref(k))
+        return v, k.value
+
+
+def host_api():
+    return _HostApi()
+
+
+class Codec:
+    """One b200ans context (one GPU, one stream).  Pointers may be numpy arrays (host entry
+    points) or integers / torch tensors' data_ptr() (device entry points)."""
+
+    def __init__(self, device=0, block_syms=8192, stream=None):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.b200ans_create(C.byref(h), device, stream)
+        if rc:
+            raise B200AnsError(rc, self.lib.b200ans_strerror(rc).decode())
+        self.h = h
+        self.set_block_syms(block_syms)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b200ans_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc:
+            raise B200AnsError(rc, self.lib.b200ans_last_error(self.h).decode() or self.lib.b200ans_strerror(rc).decode())
+
+    def set_block_syms(self, bs):
+        self._check(self.lib.b200ans_set_block_syms(self.h, bs))
+        self.block_syms = bs
+
+    def stats(self):
+        s = Stats()
+        self._check(self.lib.b200ans_get_stats(self.h, C.byref(s)))
+        return s
+
+    def bound(self, method, n):
+        return self.lib.b200ans_compress_bound(self.h, method, n)
+
+    # ---- host buffers -------------------------------------------------------------------
+    def compress(self, method, f, data, out=None):
+        data = np.ascontiguousarray(data, dtype=np.uint32)
+        if out is None:
+            out = np.empty(self.bound(method, data.size), dtype=np.uint8)
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_compress(self.h, method, f, out.ctypes.data, out.size, data.ctypes.data, data.size, C.byref(nb)))
+        return out[: nb.value]
+
+    def decompress(self, method, f, blob, n, out=None):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        if out is None:
+            out = np.empty(n, dtype=np.uint32)
+        self._check(self.lib.b200ans_decompress(self.h, method, f, out.ctypes.data, n, blob.ctypes.data, blob.size))
+        return out
+
+    def compress_ptr(self, method, f, dst_ptr, cap, src_ptr, n):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_compress(self.h, method, f, dst_ptr, cap, src_ptr, n, C.byref(nb)))
+        return nb.value
+
+    def decompress_ptr(self, method, f, dst_ptr, n, src_ptr, nbytes):
+        self._check(self.lib.b200ans_decompress(self.h, method, f, dst_ptr, n, src_ptr, nbytes))
+
+    # ---- device buffers (raw pointers) ------------------------------------------------------
+    def compress_device(self, method, f, d_dst, cap, d_src, n):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_compress_device(self.h, method, f, d_dst, cap, d_src, n, C.byref(nb)))
+        return nb.value
+
+    def decompress_device(self, method, f, d_dst, n, d_src, nbytes):
+        self._check(self.lib.b200ans_decompress_device(self.h, method, f, d_dst, n, d_src, nbytes))
+
+    def max_device(self, d_src, n, d_max):
+        self._check(self.lib.b200ans_max_device(self.h, d_src, n, d_max))
+
+    def histogram_device(self, method, f, d_src, n, d_bins, nbins):
+        self._check(self.lib.b200ans_histogram_device(self.h, method, f, d_src, n, d_bins, nbins))
+
+    def rfold_prepare(self, f, raw_bins):
+        raw_bins = np.ascontiguousarray(raw_bins, dtype=np.uint64)
+        self._check(self.lib.b200ans_rfold_prepare(self.h, f, _p(raw_bins, u64p), raw_bins.size))
+
+    def model_build(self, method, f, bins):
+        bins = np.ascontiguousarray(bins, dtype=np.uint64)
+        self._check(self.lib.b200ans_model_build(self.h, method, f, _p(bins, u64p), bins.size))
+
+    def model_prelude(self):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_model_prelude(self.h, None, 0, C.byref(nb)))
+        out = np.zeros(nb.value, dtype=np.uint8)
+        self._check(self.lib.b200ans_model_prelude(self.h, _p(out, u8p), out.size, C.byref(nb)))
+        return out
+
+    def model_nfreqs(self):
+        cnt, fs = C.c_size_t(), C.c_uint64()
+        self._check(self.lib.b200ans_model_nfreqs(self.h, None, 0, C.byref(cnt), C.byref(fs)))
+        out = np.zeros(cnt.value, dtype=np.uint32)
+        self._check(self.lib.b200ans_model_nfreqs(self.h, _p(out, u32p), out.size, C.byref(cnt), C.byref(fs)))
+        return fs.value, out
+
+    def model_load(self, method, f, prelude):
+        prelude = np.ascontiguousarray(prelude, dtype=np.uint8)
+        used = C.c_size_t()
+        self._check(self.lib.b200ans_model_load(self.h, method, f, _p(prelude, u8p), prelude.size, C.byref(used)))
+        return used.value
+
+    def encode_device(self, d_dst, cap, d_src, n):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_encode_device(self.h, d_dst, cap, d_src, n, C.byref(nb)))
+        return nb.value
+
+    def block_stride(self, method):
+        s = C.c_size_t()
+        self._check(self.lib.b200ans_block_stride(self.h, method, C.byref(s)))
+        return s.value
+
+    def encode_blocks_device(self, d_src, n, d_scratch, stride, d_block_bytes):
+        self._check(self.lib.b200ans_encode_blocks_device(self.h, d_src, n, d_scratch, stride, d_block_bytes))
+
+    def decode_blocks_device(self, d_payload, d_offsets, d_block_bytes, n, d_dst):
+        self._check(self.lib.b200ans_decode_blocks_device(self.h, d_payload, d_offsets, d_block_bytes, n, d_dst))

@@ -1,0 +1,1247 @@
+// b200ans C-ABI implementation (include/b200ans.h): host orchestration around the sm_100a
+// kernels of kernels.cuh.  No CPU coding path exists here: the histogram, the encoder and the
+// decoder run on the GPU or the call fails.
+#include "../../include/b200ans.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../host/fold.hpp"
+#include "../host/model.hpp"
+#include "../host/prelude.hpp"
+#include "kernels.cuh"
+
+using namespace b200ans;
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes)
+    {
+        if (bytes <= cap)
+            return cudaSuccess;
+        if (p)
+            cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            want = bytes;
+            e = cudaMalloc(&p, want);
+        }
+        if (e == cudaSuccess)
+            cap = want;
+        return e;
+    }
+    void release()
+    {
+        if (p)
+            cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct Header {
+    uint32_t magic;
+    uint16_t version;
+    uint8_t method;
+    uint8_t fidelity;
+    uint64_t n_symbols;
+    uint32_t block_syms;
+    uint32_t n_blocks;
+    uint32_t prelude_bytes;
+    uint32_t flags;
+    uint64_t payload_bytes; // padded sum
+    uint8_t reserved[24];
+};
+static_assert(sizeof(Header) == B200ANS_HEADER_BYTES, "container header is 64 bytes");
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+} // namespace
+
+struct b200ans_ctx {
+    int device = 0;
+    int num_sms = 0;
+    size_t max_smem = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
+    std::string err;
+    b200ans_stats stats {};
+    cudaEvent_t ev[8] {};
+
+    // grow-only device buffers
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_s2s, dec_syms, io_in, io_out;
+    // `small` layout: [0] u32 max, [1] u32 error flag, [2..] pad; totals (2 x u64) at byte 16
+    uint32_t* d_max() { return small.as<uint32_t>(); }
+    uint32_t* d_err() { return small.as<uint32_t>() + 1; }
+    uint64_t* d_totals() { return reinterpret_cast<uint64_t*>(small.as<uint8_t>() + 16); }
+
+    // encoder model
+    bool have_enc = false;
+    int enc_method = -1;
+    uint32_t enc_f = 0;
+    std::vector<uint32_t> nfreqs;
+    uint64_t frame = 0;
+    uint32_t log2_frame = 0;
+    std::vector<uint8_t> prelude;
+    // rfold value reordering
+    bool have_mapping = false;
+    uint32_t map_f = 0;
+    uint32_t n_values = 0;
+    uint64_t rfold_sigma = 0;
+    std::vector<uint32_t> most_frequent;
+
+    // decoder model
+    bool have_dec = false;
+    int dec_method = -1;
+    uint32_t dec_f = 0;
+    uint32_t dec_log2_frame = 0;
+    uint32_t dec_n_syms = 0;
+    uint32_t dec_sym_bytes = 0;
+
+    int fail(int code, const std::string& what)
+    {
+        err = what;
+        return code;
+    }
+    int cuda_fail(cudaError_t e, const char* where)
+    {
+        err = std::string(where) + ": " + cudaGetErrorString(e);
+        cudaGetLastError();
+        return B200ANS_E_CUDA;
+    }
+};
+
+#define CU(ctx, call)                                                                                                  \
+    do {                                                                                                               \
+        cudaError_t e__ = (call);                                                                                      \
+        if (e__ != cudaSuccess)                                                                                        \
+            return (ctx)->cuda_fail(e__, #call);                                                                       \
+    } while (0)
+
+#define RET(call)                                                                                                      \
+    do {                                                                                                               \
+        int r__ = (call);                                                                                              \
+        if (r__ != B200ANS_OK)                                                                                         \
+            return r__;                                                                                                \
+    } while (0)
+
+namespace {
+
+bool valid_method(int method, uint32_t f)
+{
+    if (method == METHOD_INT || method == METHOD_MSB)
+        return true;
+    if (method == METHOD_FOLD || method == METHOD_RFOLD)
+        return f >= 1 && f <= 8;
+    return false;
+}
+
+size_t alphabet_bins(int method, uint32_t f, uint32_t max_value)
+{
+    switch (method) {
+    case METHOD_INT: return size_t(max_value) + 1;
+    case METHOD_MSB: return kMsbMaxSigma;
+    default: return size_t(1) << (f + 9);
+    }
+}
+
+// worst-case payload bytes of one block (+16 so 16-byte chunk stores never leave the slot)
+size_t block_stride(int method, size_t block_syms)
+{
+    const size_t per_sym = (method == METHOD_INT) ? 4 : 7;
+    return align_up(per_sym * block_syms + 32, 16) + 16;
+}
+
+float elapsed(cudaEvent_t a, cudaEvent_t b)
+{
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, a, b);
+    return ms;
+}
+
+double now_ms()
+{
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+} // namespace
+
+// ==========================================================================================
+// context
+// ==========================================================================================
+extern "C" int b200ans_create(b200ans_ctx** out, int device, void* stream)
+{
+    if (!out)
+        return B200ANS_E_ARG;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || device < 0 || device >= count) {
+        cudaGetLastError();
+        return B200ANS_E_CUDA; // no CPU fallback: without a GPU there is no coder
+    }
+    b200ans_ctx* c = new b200ans_ctx();
+    c->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) {
+        delete c;
+        return B200ANS_E_CUDA;
+    }
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    c->num_sms = prop.multiProcessorCount;
+    c->max_smem = prop.sharedMemPerBlockOptin;
+    if (stream) {
+        c->stream = static_cast<cudaStream_t>(stream);
+    } else {
+        if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+            delete c;
+            return B200ANS_E_CUDA;
+        }
+        c->own_stream = true;
+    }
+    for (auto& e : c->ev)
+        cudaEventCreate(&e);
+    if (c->small.reserve(256) != cudaSuccess) {
+        b200ans_destroy(c);
+        return B200ANS_E_CUDA;
+    }
+    *out = c;
+    return B200ANS_OK;
+}
+
+extern "C" void b200ans_destroy(b200ans_ctx* c)
+{
+    if (!c)
+        return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
+             &c->dec_slots, &c->dec_s2s, &c->dec_syms, &c->io_in, &c->io_out })
+        b->release();
+    for (auto& e : c->ev)
+        if (e)
+            cudaEventDestroy(e);
+    if (c->own_stream)
+        cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" int b200ans_set_block_syms(b200ans_ctx* c, uint32_t block_syms)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (block_syms != 0 && (block_syms % 128 != 0 || block_syms > (1u << 24)))
+        return c->fail(B200ANS_E_ARG, "block_syms must be 0 or a multiple of 128 up to 2^24");
+    c->block_syms = block_syms;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_get_stats(const b200ans_ctx* c, b200ans_stats* out)
+{
+    if (!c || !out)
+        return B200ANS_E_ARG;
+    *out = c->stats;
+    return B200ANS_OK;
+}
+
+extern "C" const char* b200ans_last_error(const b200ans_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+extern "C" const char* b200ans_strerror(int code)
+{
+    switch (code) {
+    case B200ANS_OK: return "ok";
+    case B200ANS_E_ARG: return "bad argument";
+    case B200ANS_E_CUDA: return "CUDA failure (or no CUDA device: this library has no CPU fallback)";
+    case B200ANS_E_CAPACITY: return "destination too small";
+    case B200ANS_E_DOMAIN: return "input outside the coder's valid domain";
+    case B200ANS_E_FORMAT: return "not a b200ans container";
+    case B200ANS_E_STATE: return "call sequence error";
+    }
+    return "unknown error";
+}
+
+// methods.hpp:485,500,530-533,550-553
+extern "C" const char* b200ans_method_name(int method, uint32_t fidelity, char* buf, size_t buflen)
+{
+    if (!buf || buflen == 0)
+        return "";
+    switch (method) {
+    case METHOD_INT: snprintf(buf, buflen, "ANS"); break;
+    case METHOD_MSB: snprintf(buf, buflen, "ANSmsb"); break;
+    case METHOD_FOLD: snprintf(buf, buflen, "ANSfold-%u", fidelity); break;
+    case METHOD_RFOLD: snprintf(buf, buflen, "ANSrfold-%u", fidelity); break;
+    default: snprintf(buf, buflen, "?"); break;
+    }
+    return buf;
+}
+
+extern "C" size_t b200ans_compress_bound(const b200ans_ctx* c, int method, size_t n)
+{
+    const uint32_t bs = c ? c->block_syms : B200ANS_DEFAULT_BLOCK_SYMS;
+    const size_t per_sym = (method == METHOD_INT) ? 4 : 7;
+    const size_t n_blocks = bs ? (n + bs - 1) / bs : 1;
+    // header + prelude (worst case ~ 5 bytes per distinct symbol, bounded by n and 2^30) + table + payloads
+    const size_t prelude = 4096 + 8 * std::min<size_t>(n, size_t(1) << 26) + (size_t(4) << 12);
+    return B200ANS_HEADER_BYTES + prelude + 4 * n_blocks + 16 + per_sym * n + n_blocks * 48 + 64;
+}
+
+// ==========================================================================================
+// host-only model API
+// ==========================================================================================
+extern "C" int b200ans_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_t largest_sym, int require_u16,
+    uint32_t H_approx, uint32_t* out)
+{
+    if (!freqs || !out || largest_sym >= nbins)
+        return B200ANS_E_ARG;
+    std::vector<uint64_t> F(freqs, freqs + nbins);
+    const std::vector<uint32_t> s = adjust_freqs(F, largest_sym, require_u16 != 0, H_approx);
+    std::copy(s.begin(), s.end(), out);
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_serialize_interp(const uint32_t* nfreqs, size_t count, uint64_t frame_size, uint8_t* dst,
+    size_t capacity, size_t* out_bytes)
+{
+    if (!nfreqs || !dst || !out_bytes || count == 0)
+        return B200ANS_E_ARG;
+    if (capacity < 8 * count + 16)
+        return B200ANS_E_CAPACITY;
+    std::vector<uint32_t> v(nfreqs, nfreqs + count);
+    uint8_t* p = dst;
+    ans_serialize_interp(v, size_t(frame_size), p);
+    *out_bytes = size_t(p - dst);
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_load_interp(const uint8_t* src, uint32_t* dst, size_t capacity, size_t* out_count, size_t* consumed)
+{
+    if (!src || !out_count)
+        return B200ANS_E_ARG;
+    const uint8_t* p = src;
+    const uint32_t max_sym = vbyte_decode_u32(p);
+    *out_count = size_t(max_sym) + 1;
+    if (!dst)
+        return B200ANS_OK;
+    if (capacity < *out_count)
+        return B200ANS_E_CAPACITY;
+    const std::vector<uint32_t> v = ans_load_interp(src, consumed);
+    std::copy(v.begin(), v.end(), dst);
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_interp_encode(uint32_t* dst, const uint32_t* in, size_t n, size_t universe, size_t* out_bytes)
+{
+    if (!dst || (!in && n) || !out_bytes)
+        return B200ANS_E_ARG;
+    *out_bytes = interp_encode(dst, in, n, universe);
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_interp_decode(const uint32_t* src, uint32_t* out, size_t n, size_t universe, size_t* words_read)
+{
+    if (!src || (!out && n))
+        return B200ANS_E_ARG;
+    const size_t w = interp_decode(src, out, n, universe);
+    if (words_read)
+        *words_read = w;
+    return B200ANS_OK;
+}
+
+extern "C" uint32_t b200ans_fold_map(uint32_t f, uint32_t x, uint32_t* nbytes)
+{
+    uint32_t k;
+    const uint32_t s = fold_map(x, f, k);
+    if (nbytes)
+        *nbytes = k;
+    return s;
+}
+extern "C" uint32_t b200ans_fold_unmap(uint32_t f, uint32_t sym, uint32_t* nbytes)
+{
+    uint32_t k;
+    const uint32_t v = fold_unmap(sym, f, k);
+    if (nbytes)
+        *nbytes = k;
+    return v;
+}
+extern "C" uint32_t b200ans_msb_map(uint32_t x, uint32_t* nbytes)
+{
+    uint32_t k;
+    const uint32_t s = msb_map(x, k);
+    if (nbytes)
+        *nbytes = k;
+    return s;
+}
+extern "C" uint32_t b200ans_msb_unmap(uint32_t sym, uint32_t* nbytes)
+{
+    uint32_t k;
+    const uint32_t v = msb_unmap(sym, k);
+    if (nbytes)
+        *nbytes = k;
+    return v;
+}
+
+// ==========================================================================================
+// K1 launches: maximum + histogram
+// ==========================================================================================
+namespace {
+
+template <int METHOD>
+int launch_histogram(b200ans_ctx* c, uint32_t f, const uint32_t* d_src, size_t n, uint64_t* d_bins, size_t nbins,
+    uint32_t* d_max)
+{
+    const bool smem = nbins <= kHistSmemBins;
+    const size_t smem_bytes = smem ? nbins * sizeof(uint32_t) : 0;
+    const size_t vec = (n >> 2) + 1;
+    int grid = int(std::min<size_t>((vec + kHistThreads - 1) / kHistThreads, size_t(c->num_sms) * 4));
+    grid = std::max(grid, 1);
+    const uint32_t* mapping = c->mapping.as<uint32_t>();
+    auto* bins = reinterpret_cast<unsigned long long*>(d_bins);
+    if (smem) {
+        auto k = histogram_kernel<METHOD, true>;
+        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kHistSmemBins * 4)));
+        k<<<grid, kHistThreads, smem_bytes, c->stream>>>(d_src, n, f, mapping, c->n_values, bins, uint32_t(nbins), d_max);
+    } else {
+        auto k = histogram_kernel<METHOD, false>;
+        k<<<grid, kHistThreads, 0, c->stream>>>(d_src, n, f, mapping, c->n_values, bins, uint32_t(nbins), d_max);
+    }
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
+int histogram_dispatch(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n, uint64_t* d_bins,
+    size_t nbins, uint32_t* d_max)
+{
+    if (nbins == 0 || nbins > (size_t(1) << 31))
+        return c->fail(B200ANS_E_ARG, "histogram: bad bin count");
+    switch (method) {
+    case METHOD_INT: return launch_histogram<METHOD_INT>(c, f, d_src, n, d_bins, nbins, d_max);
+    case METHOD_FOLD: return launch_histogram<METHOD_FOLD>(c, f, d_src, n, d_bins, nbins, d_max);
+    case METHOD_MSB: return launch_histogram<METHOD_MSB>(c, f, d_src, n, d_bins, nbins, d_max);
+    case METHOD_RFOLD:
+        if (!c->have_mapping || c->map_f != f)
+            return c->fail(B200ANS_E_STATE, "histogram(RFOLD) needs b200ans_rfold_prepare first");
+        return launch_histogram<METHOD_RFOLD>(c, f, d_src, n, d_bins, nbins, d_max);
+    }
+    return c->fail(B200ANS_E_ARG, "unknown method");
+}
+
+// maximum of the raw values: the histogram kernel in INT mode with a single dummy bin range of 0
+__global__ void __launch_bounds__(512) max_kernel(const uint32_t* __restrict__ in, uint64_t n, uint32_t* __restrict__ out)
+{
+    uint32_t m = 0;
+    const uint64_t n4 = n >> 2;
+    const uint4* in4 = reinterpret_cast<const uint4*>(in);
+    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const uint4 q = __ldg(in4 + i);
+        m = max(max(m, q.x), max(q.y, max(q.z, q.w)));
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 3) {
+        const uint64_t t = (n4 << 2) + threadIdx.x;
+        if (t < n)
+            m = max(m, in[t]);
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m)
+        atomicMax(out, m);
+}
+
+} // namespace
+
+extern "C" int b200ans_max_device(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t* d_max)
+{
+    if (!c || !d_src || !d_max || (reinterpret_cast<uintptr_t>(d_src) & 15))
+        return c ? c->fail(B200ANS_E_ARG, "max: null or unaligned pointer") : B200ANS_E_ARG;
+    CU(c, cudaSetDevice(c->device));
+    const size_t vec = (n >> 2) + 1;
+    const int grid = int(std::max<size_t>(1, std::min<size_t>((vec + 511) / 512, size_t(c->num_sms) * 4)));
+    max_kernel<<<grid, 512, 0, c->stream>>>(d_src, n, d_max);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_histogram_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n,
+    uint64_t* d_bins, size_t nbins)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_src || !d_bins || !valid_method(method, f) || (reinterpret_cast<uintptr_t>(d_src) & 15))
+        return c->fail(B200ANS_E_ARG, "histogram: bad argument (d_src must be 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    return histogram_dispatch(c, method, f, d_src, n, d_bins, nbins, c->d_max());
+}
+
+// ==========================================================================================
+// models
+// ==========================================================================================
+
+// ans_reorder_fold.hpp:75-106: order values by (-count, value), the first 2^(f+7) become
+// 0..2^(f+7)-1 and everything else moves up by 2^(f+7); identity if fewer distinct values.
+extern "C" int b200ans_rfold_prepare(b200ans_ctx* c, uint32_t f, const uint64_t* raw_bins, size_t nvalues)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!raw_bins || nvalues == 0 || f < 1 || f > 8 || nvalues > (size_t(1) << 31))
+        return c->fail(B200ANS_E_ARG, "rfold_prepare: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    const uint32_t thres = 1u << (f + 7);
+    std::vector<std::pair<uint64_t, uint32_t>> seen; // (count, value)
+    for (size_t v = 0; v < nvalues; v++)
+        if (raw_bins[v])
+            seen.emplace_back(raw_bins[v], uint32_t(v));
+    c->rfold_sigma = seen.size();
+    std::vector<uint32_t> mapping(nvalues);
+    c->most_frequent.clear();
+    if (seen.size() < thres) {
+        for (size_t v = 0; v < nvalues; v++)
+            mapping[v] = uint32_t(v);
+    } else {
+        auto hotter = [](const std::pair<uint64_t, uint32_t>& a, const std::pair<uint64_t, uint32_t>& b) {
+            return a.first != b.first ? a.first > b.first : a.second < b.second;
+        };
+        std::partial_sort(seen.begin(), seen.begin() + thres, seen.end(), hotter);
+        for (size_t v = 0; v < nvalues; v++)
+            mapping[v] = uint32_t(v) + thres;
+        c->most_frequent.resize(thres);
+        for (uint32_t i = 0; i < thres; i++) {
+            mapping[seen[i].second] = i;
+            c->most_frequent[i] = seen[i].second;
+        }
+    }
+    CU(c, c->mapping.reserve(nvalues * sizeof(uint32_t)));
+    CU(c, cudaMemcpyAsync(c->mapping.p, mapping.data(), nvalues * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->n_values = uint32_t(nvalues);
+    c->map_f = f;
+    c->have_mapping = true;
+    return B200ANS_OK;
+}
+
+// ans_X_encode::create after the counting loop (ans_fold.hpp:79-92) + serialize (ans_fold.hpp:96-99,
+// ans_reorder_fold.hpp:132-154) + the device encoder table.
+extern "C" int b200ans_model_build(b200ans_ctx* c, int method, uint32_t f, const uint64_t* bins, size_t nbins)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!bins || !valid_method(method, f) || nbins == 0)
+        return c->fail(B200ANS_E_ARG, "model_build: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    const double t0 = now_ms();
+    c->have_enc = false;
+    if (method == METHOD_RFOLD && (!c->have_mapping || c->map_f != f))
+        return c->fail(B200ANS_E_STATE, "model_build(RFOLD) needs b200ans_rfold_prepare first");
+    std::vector<uint64_t> freqs(bins, bins + nbins);
+    size_t sigma = 0;
+    uint32_t max_sym = 0;
+    for (size_t s = 0; s < nbins; s++)
+        if (freqs[s]) {
+            sigma++;
+            max_sym = uint32_t(s);
+        }
+    if (sigma == 0)
+        return c->fail(B200ANS_E_DOMAIN, "model_build: empty histogram");
+    if (method == METHOD_INT && sigma < 2)
+        return c->fail(B200ANS_E_DOMAIN,
+            "plain ANS needs at least two distinct symbols (the reference's adjust_freqs never terminates otherwise)");
+    c->nfreqs = adjust_freqs(freqs, max_sym, method != METHOD_INT);
+    uint64_t frame = 0;
+    for (uint32_t v : c->nfreqs)
+        frame += v;
+    if (!is_power_of_two(frame) || frame > (uint64_t(1) << 28))
+        return c->fail(B200ANS_E_DOMAIN, "model_build: normalisation produced an unusable frame size");
+    c->frame = frame;
+    c->log2_frame = uint32_t(63 - __builtin_clzll(frame));
+
+    // prelude
+    c->prelude.assign(c->nfreqs.size() * 8 + 64 + (method == METHOD_RFOLD ? 4 * c->most_frequent.size() + 8 : 0), 0);
+    uint8_t* p = c->prelude.data();
+    if (method == METHOD_RFOLD) {
+        const uint32_t flag = c->most_frequent.empty() ? 0u : 1u;
+        std::memcpy(p, &flag, 4);
+        p += 4;
+        if (flag) {
+            std::memcpy(p, c->most_frequent.data(), 4 * c->most_frequent.size());
+            p += 4 * c->most_frequent.size();
+        }
+    }
+    ans_serialize_interp(c->nfreqs, size_t(frame), p);
+    c->prelude.resize(size_t(p - c->prelude.data()));
+
+    // encoder table: {freq, base = exclusive prefix sum, reciprocal rounded towards zero}
+    std::vector<EncEntry> table(c->nfreqs.size());
+    uint64_t base = 0;
+    for (size_t s = 0; s < table.size(); s++) {
+        const uint32_t fr = c->nfreqs[s];
+        table[s].freq = fr;
+        table[s].base = uint32_t(base);
+        table[s].rcp = fr ? (1.0 / double(fr)) * (1.0 - 0x1p-50) : 0.0;
+        base += fr;
+    }
+    CU(c, c->enc_table.reserve(table.size() * sizeof(EncEntry)));
+    CU(c, cudaMemcpyAsync(c->enc_table.p, table.data(), table.size() * sizeof(EncEntry), cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->enc_method = method;
+    c->enc_f = f;
+    c->have_enc = true;
+    c->stats.frame_size = frame;
+    c->stats.n_symbols_model = uint32_t(c->nfreqs.size());
+    c->stats.prelude_bytes = c->prelude.size();
+    c->stats.ms_model = float(now_ms() - t0);
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_model_prelude(b200ans_ctx* c, uint8_t* dst, size_t capacity, size_t* out_bytes)
+{
+    if (!c || !out_bytes)
+        return B200ANS_E_ARG;
+    if (!c->have_enc)
+        return c->fail(B200ANS_E_STATE, "no encoder model");
+    *out_bytes = c->prelude.size();
+    if (!dst)
+        return B200ANS_OK;
+    if (capacity < c->prelude.size())
+        return c->fail(B200ANS_E_CAPACITY, "prelude buffer too small");
+    std::memcpy(dst, c->prelude.data(), c->prelude.size());
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_model_nfreqs(b200ans_ctx* c, uint32_t* dst, size_t capacity, size_t* out_count, uint64_t* frame_size)
+{
+    if (!c || !out_count)
+        return B200ANS_E_ARG;
+    if (!c->have_enc)
+        return c->fail(B200ANS_E_STATE, "no encoder model");
+    *out_count = c->nfreqs.size();
+    if (frame_size)
+        *frame_size = c->frame;
+    if (!dst)
+        return B200ANS_OK;
+    if (capacity < c->nfreqs.size())
+        return c->fail(B200ANS_E_CAPACITY, "nfreqs buffer too small");
+    std::copy(c->nfreqs.begin(), c->nfreqs.end(), dst);
+    return B200ANS_OK;
+}
+
+// ans_X_decode::load (ans_fold.hpp:179-207, ans_int.hpp:116-164, ans_msb.hpp:179-204,
+// ans_reorder_fold.hpp:235-279): prelude -> nfreqs -> slot tables, uploaded to the device.
+extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const uint8_t* prelude, size_t prelude_bytes,
+    size_t* consumed)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!prelude || !valid_method(method, f) || prelude_bytes < 3)
+        return c->fail(B200ANS_E_ARG, "model_load: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    const double t0 = now_ms();
+    c->have_dec = false;
+    // the interp reader may look one 32-bit word past the end: work on a padded copy
+    std::vector<uint8_t> buf(prelude_bytes + 16, 0);
+    std::memcpy(buf.data(), prelude, prelude_bytes);
+    const uint8_t* p = buf.data();
+    const uint32_t thres = 1u << (f + 7);
+    std::vector<uint32_t> most_frequent;
+    if (method == METHOD_RFOLD) {
+        uint32_t flag;
+        std::memcpy(&flag, p, 4);
+        p += 4;
+        most_frequent.resize(thres);
+        if (flag == 1) {
+            if (prelude_bytes < 4 + size_t(4) * thres + 3)
+                return c->fail(B200ANS_E_FORMAT, "model_load: truncated rfold prelude");
+            std::memcpy(most_frequent.data(), p, size_t(4) * thres);
+            p += size_t(4) * thres;
+        } else {
+            for (uint32_t i = 0; i < thres; i++)
+                most_frequent[i] = i;
+        }
+    }
+    {   // sanity-check the vbyte/log2 header before trusting it with allocations
+        const uint8_t* q = p;
+        const uint32_t max_sym = vbyte_decode_u32(q);
+        const uint32_t lg = *q;
+        if (lg > 28 || size_t(max_sym) + 1 > (size_t(1) << 28))
+            return c->fail(B200ANS_E_FORMAT, "model_load: implausible prelude header");
+        const size_t limit = method == METHOD_INT ? (size_t(1) << 28)
+                                                  : (method == METHOD_MSB ? size_t(kMsbMaxSigma) : (size_t(1) << (f + 9)));
+        if (size_t(max_sym) + 1 > limit)
+            return c->fail(B200ANS_E_FORMAT, "model_load: alphabet larger than the method allows");
+    }
+    size_t used = 0;
+    const std::vector<uint32_t> nfreqs = ans_load_interp(p, &used);
+    const size_t total_used = size_t(p - buf.data()) + used;
+    if (total_used > prelude_bytes + 4)
+        return c->fail(B200ANS_E_FORMAT, "model_load: prelude runs past its buffer");
+    if (consumed)
+        *consumed = std::min(total_used, prelude_bytes);
+    uint64_t frame = 0;
+    for (uint32_t v : nfreqs)
+        frame += v;
+    if (!is_power_of_two(frame) || frame > (uint64_t(1) << 28))
+        return c->fail(B200ANS_E_FORMAT, "model_load: frequencies do not sum to a power of two");
+    const uint32_t lg = uint32_t(63 - __builtin_clzll(frame));
+
+    if (method == METHOD_INT) {
+        const uint32_t sym_bytes = nfreqs.size() <= 65536 ? 2 : 4;
+        std::vector<SymEntry> syms(nfreqs.size());
+        std::vector<uint8_t> s2s(align_up(size_t(frame) * sym_bytes, 16), 0);
+        uint64_t base = 0;
+        for (size_t s = 0; s < nfreqs.size(); s++) {
+            syms[s].freq = nfreqs[s];
+            syms[s].base = uint32_t(base);
+            if (sym_bytes == 2) {
+                uint16_t* t = reinterpret_cast<uint16_t*>(s2s.data()) + base;
+                std::fill(t, t + nfreqs[s], uint16_t(s));
+            } else {
+                uint32_t* t = reinterpret_cast<uint32_t*>(s2s.data()) + base;
+                std::fill(t, t + nfreqs[s], uint32_t(s));
+            }
+            base += nfreqs[s];
+        }
+        CU(c, c->dec_s2s.reserve(s2s.size()));
+        CU(c, c->dec_syms.reserve(syms.size() * sizeof(SymEntry)));
+        CU(c, cudaMemcpyAsync(c->dec_s2s.p, s2s.data(), s2s.size(), cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(c->dec_syms.p, syms.data(), syms.size() * sizeof(SymEntry), cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        c->dec_sym_bytes = sym_bytes;
+    } else {
+        std::vector<DecEntry> slots(frame);
+        uint64_t base = 0;
+        for (size_t s = 0; s < nfreqs.size(); s++) {
+            const uint32_t fr = nfreqs[s];
+            if (fr > 65535)
+                return c->fail(B200ANS_E_FORMAT, "model_load: folded model with a frequency above 16 bits");
+            uint32_t k = 0, value;
+            if (method == METHOD_MSB)
+                value = msb_unmap(uint32_t(s), k);
+            else if (method == METHOD_RFOLD && s < thres)
+                value = most_frequent[s] + thres; // ans_reorder_fold.hpp:214-215
+            else
+                value = fold_unmap(uint32_t(s), f, k);
+            const uint32_t mapped = value + (k << 30);
+            for (uint32_t j = 0; j < fr; j++)
+                slots[base + j] = DecEntry { uint16_t(fr), uint16_t(j), mapped };
+            base += fr;
+        }
+        CU(c, c->dec_slots.reserve(slots.size() * sizeof(DecEntry)));
+        CU(c, cudaMemcpyAsync(c->dec_slots.p, slots.data(), slots.size() * sizeof(DecEntry), cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+    }
+    c->dec_method = method;
+    c->dec_f = f;
+    c->dec_log2_frame = lg;
+    c->dec_n_syms = uint32_t(nfreqs.size());
+    c->have_dec = true;
+    c->stats.frame_size = frame;
+    c->stats.n_symbols_model = uint32_t(nfreqs.size());
+    c->stats.ms_model = float(now_ms() - t0);
+    return B200ANS_OK;
+}
+
+// ==========================================================================================
+// K2 / K3 launches
+// ==========================================================================================
+namespace {
+
+template <class K> int persistent_grid(b200ans_ctx* c, K kernel, int threads, size_t smem, uint32_t n_tasks, int warps)
+{
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError();
+        per_sm = 1;
+    }
+    const uint32_t need = (n_tasks + uint32_t(warps) - 1) / uint32_t(warps);
+    return int(std::max<uint32_t>(1, std::min<uint32_t>(need, uint32_t(per_sm) * uint32_t(c->num_sms))));
+}
+
+template <int METHOD> int launch_encode_t(b200ans_ctx* c, const EncArgs& a)
+{
+    const size_t rows = size_t(kEncWarps) * 8 * kEncRowBytes;
+    const uint32_t n_tasks = (a.n_blocks + 7) / 8;
+    const bool smem_table = a.n_entries <= uint32_t(kEncMaxSmemEntries);
+    if (smem_table) {
+        auto k = encode_kernel<METHOD, true>;
+        const size_t smem = rows + size_t(a.n_entries) * sizeof(EncEntry);
+        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        const int grid = persistent_grid(c, k, kEncWarps * 32, smem, n_tasks, kEncWarps);
+        k<<<grid, kEncWarps * 32, smem, c->stream>>>(a);
+    } else {
+        auto k = encode_kernel<METHOD, false>;
+        const int grid = persistent_grid(c, k, kEncWarps * 32, rows, n_tasks, kEncWarps);
+        k<<<grid, kEncWarps * 32, rows, c->stream>>>(a);
+    }
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
+// encode d_src into scratch slots + block_bytes using the current encoder model
+int launch_encode(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t block_syms, uint32_t n_blocks,
+    uint8_t* d_scratch, size_t stride, uint32_t* d_block_bytes)
+{
+    EncArgs a {};
+    a.in = d_src;
+    a.n = n;
+    a.block_syms = block_syms;
+    a.n_blocks = n_blocks;
+    a.table = c->enc_table.as<EncEntry>();
+    a.n_entries = uint32_t(c->nfreqs.size());
+    a.log2_frame = c->log2_frame;
+    a.fidelity = c->enc_f;
+    a.mapping = c->mapping.as<uint32_t>();
+    a.n_values = c->n_values;
+    a.scratch = d_scratch;
+    a.stride = stride;
+    a.block_bytes = d_block_bytes;
+    a.error_flag = c->d_err();
+    CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
+    switch (c->enc_method) {
+    case METHOD_INT: return launch_encode_t<METHOD_INT>(c, a);
+    case METHOD_FOLD: return launch_encode_t<METHOD_FOLD>(c, a);
+    case METHOD_MSB: return launch_encode_t<METHOD_MSB>(c, a);
+    case METHOD_RFOLD: return launch_encode_t<METHOD_RFOLD>(c, a);
+    }
+    return c->fail(B200ANS_E_STATE, "encode: no model");
+}
+
+template <int METHOD, int TABLE> int launch_decode_tt(b200ans_ctx* c, const DecArgs& a, size_t table_bytes)
+{
+    auto k = decode_kernel<METHOD, TABLE>;
+    const size_t smem = table_bytes + size_t(kDecWarps) * 8 * kDecRowBytes;
+    CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    const uint32_t n_tasks = (a.n_blocks + 7) / 8;
+    const int grid = persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps);
+    k<<<grid, kDecWarps * 32, smem, c->stream>>>(a);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
+int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_offsets, const uint32_t* d_block_bytes,
+    size_t n, uint32_t block_syms, uint32_t n_blocks, uint32_t* d_dst)
+{
+    DecArgs a {};
+    a.payload = d_payload;
+    a.offsets = d_offsets;
+    a.block_bytes = d_block_bytes;
+    a.out = d_dst;
+    a.n = n;
+    a.block_syms = block_syms;
+    a.n_blocks = n_blocks;
+    a.log2_frame = c->dec_log2_frame;
+    a.fidelity = c->dec_f;
+    a.slots = c->dec_slots.as<DecEntry>();
+    a.slot_to_sym = c->dec_s2s.p;
+    a.syms = c->dec_syms.as<SymEntry>();
+    a.n_syms = c->dec_n_syms;
+    a.sym_bytes = c->dec_sym_bytes;
+    const size_t frame = size_t(1) << c->dec_log2_frame;
+    const size_t rows = size_t(kDecWarps) * 8 * kDecRowBytes;
+    const size_t budget = c->max_smem > rows + 1024 ? c->max_smem - rows - 1024 : 0;
+    if (c->dec_method == METHOD_INT) {
+        const size_t tb = align_up(align_up(frame * c->dec_sym_bytes, 16) + size_t(c->dec_n_syms) * sizeof(SymEntry), 16);
+        if (tb <= budget)
+            return launch_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
+        return launch_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);
+    }
+    const size_t tb = align_up(frame * sizeof(DecEntry), 16);
+    const bool smem = tb <= std::min<size_t>(budget, size_t(128) << 10);
+    switch (c->dec_method) {
+    case METHOD_FOLD:
+        return smem ? launch_decode_tt<METHOD_FOLD, DEC_FOLD_SMEM>(c, a, tb)
+                    : launch_decode_tt<METHOD_FOLD, DEC_FOLD_GLOBAL>(c, a, 0);
+    case METHOD_MSB:
+        return smem ? launch_decode_tt<METHOD_MSB, DEC_FOLD_SMEM>(c, a, tb)
+                    : launch_decode_tt<METHOD_MSB, DEC_FOLD_GLOBAL>(c, a, 0);
+    case METHOD_RFOLD:
+        return smem ? launch_decode_tt<METHOD_RFOLD, DEC_FOLD_SMEM>(c, a, tb)
+                    : launch_decode_tt<METHOD_RFOLD, DEC_FOLD_GLOBAL>(c, a, 0);
+    }
+    return c->fail(B200ANS_E_STATE, "decode: no model");
+}
+
+int check_error_flag(b200ans_ctx* c)
+{
+    uint32_t flag = 0;
+    CU(c, cudaMemcpyAsync(&flag, c->d_err(), 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (flag)
+        return c->fail(B200ANS_E_DOMAIN, "encode: input holds a symbol the model has no frequency for");
+    return B200ANS_OK;
+}
+
+} // namespace
+
+// ==========================================================================================
+// staged encode / decode
+// ==========================================================================================
+extern "C" int b200ans_block_stride(const b200ans_ctx* c, int method, size_t* stride)
+{
+    if (!c || !stride || c->block_syms == 0)
+        return B200ANS_E_ARG;
+    *stride = block_stride(method, c->block_syms);
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_encode_blocks_device(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint8_t* d_scratch,
+    size_t stride, uint32_t* d_block_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_src || !d_scratch || !d_block_bytes || n == 0 || (reinterpret_cast<uintptr_t>(d_src) & 15)
+        || (reinterpret_cast<uintptr_t>(d_scratch) & 15) || (stride & 15))
+        return c->fail(B200ANS_E_ARG, "encode_blocks: null / unaligned argument");
+    if (!c->have_enc)
+        return c->fail(B200ANS_E_STATE, "encode_blocks: build a model first");
+    if (c->block_syms == 0 && n >= (uint64_t(1) << 32))
+        return c->fail(B200ANS_E_ARG, "single-block mode is limited to 2^32-1 symbols");
+    CU(c, cudaSetDevice(c->device));
+    const uint32_t bs = c->block_syms ? c->block_syms : uint32_t(n);
+    const uint64_t nb = (n + bs - 1) / bs;
+    if (stride < block_stride(c->enc_method, bs))
+        return c->fail(B200ANS_E_CAPACITY, "encode_blocks: stride below the worst-case block size");
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    RET(launch_encode(c, d_src, n, bs, uint32_t(nb), d_scratch, stride, d_block_bytes));
+    CU(c, cudaEventRecord(c->ev[1], c->stream));
+    RET(check_error_flag(c));
+    c->stats.ms_encode = elapsed(c->ev[0], c->ev[1]);
+    c->stats.n_blocks = uint32_t(nb);
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_decode_blocks_device(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_offsets,
+    const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_payload || !d_offsets || !d_block_bytes || !d_dst || n == 0)
+        return c->fail(B200ANS_E_ARG, "decode_blocks: null argument");
+    if (!c->have_dec)
+        return c->fail(B200ANS_E_STATE, "decode_blocks: load a model first");
+    if (c->block_syms == 0 && n >= (uint64_t(1) << 32))
+        return c->fail(B200ANS_E_ARG, "single-block mode is limited to 2^32-1 symbols");
+    CU(c, cudaSetDevice(c->device));
+    const uint32_t bs = c->block_syms ? c->block_syms : uint32_t(n);
+    const uint64_t nb = (n + bs - 1) / bs;
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    RET(launch_decode(c, d_payload, d_offsets, d_block_bytes, n, bs, uint32_t(nb), d_dst));
+    CU(c, cudaEventRecord(c->ev[1], c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
+    c->stats.n_blocks = uint32_t(nb);
+    return B200ANS_OK;
+}
+
+// current model + d_src -> container (or reference wire format when block_syms == 0) at d_dst
+extern "C" int b200ans_encode_device(b200ans_ctx* c, uint8_t* d_dst, size_t cap, const uint32_t* d_src, size_t n,
+    size_t* out_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_dst || !d_src || !out_bytes || n == 0 || (reinterpret_cast<uintptr_t>(d_src) & 15)
+        || (reinterpret_cast<uintptr_t>(d_dst) & 15))
+        return c->fail(B200ANS_E_ARG, "encode: null / unaligned argument");
+    if (!c->have_enc)
+        return c->fail(B200ANS_E_STATE, "encode: build a model first");
+    if (c->block_syms == 0 && n >= (uint64_t(1) << 32))
+        return c->fail(B200ANS_E_ARG, "single-block mode is limited to 2^32-1 symbols");
+    CU(c, cudaSetDevice(c->device));
+    const bool raw = c->block_syms == 0;
+    const uint32_t bs = raw ? uint32_t(n) : c->block_syms;
+    const uint64_t nb64 = (n + bs - 1) / bs;
+    if (nb64 > 0xFFFFFFF0ull)
+        return c->fail(B200ANS_E_ARG, "too many blocks");
+    const uint32_t nb = uint32_t(nb64);
+    const size_t stride = block_stride(c->enc_method, bs);
+    CU(c, c->scratch.reserve(stride * nb));
+    CU(c, c->block_bytes.reserve(size_t(nb) * 4));
+    CU(c, c->offsets.reserve(size_t(nb) * 8));
+
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    RET(launch_encode(c, d_src, n, bs, nb, c->scratch.as<uint8_t>(), stride, c->block_bytes.as<uint32_t>()));
+    CU(c, cudaEventRecord(c->ev[1], c->stream));
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(c->block_bytes.as<uint32_t>(), nb, c->offsets.as<uint64_t>(), c->d_totals());
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    uint64_t totals[2] = { 0, 0 };
+    CU(c, cudaMemcpyAsync(totals, c->d_totals(), 16, cudaMemcpyDeviceToHost, c->stream));
+    RET(check_error_flag(c)); // synchronises
+
+    const size_t pre = c->prelude.size();
+    if (raw) {
+        // [prelude][payload], exactly ans_X_compress's output
+        if (cap < pre + totals[1])
+            return c->fail(B200ANS_E_CAPACITY, "encode: destination too small");
+        CU(c, cudaMemcpyAsync(d_dst, c->prelude.data(), pre, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(d_dst + pre, c->scratch.p, totals[1], cudaMemcpyDeviceToDevice, c->stream));
+        CU(c, cudaEventRecord(c->ev[2], c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        *out_bytes = pre + totals[1];
+        c->stats.payload_bytes = totals[1];
+    } else {
+        const size_t table_at = B200ANS_HEADER_BYTES + align_up(pre, 4);
+        const size_t payload_at = align_up(table_at + size_t(nb) * 4, 16);
+        const size_t total = payload_at + totals[0];
+        if (cap < total)
+            return c->fail(B200ANS_E_CAPACITY, "encode: destination too small");
+        std::vector<uint8_t> front(payload_at, 0);
+        Header h {};
+        h.magic = B200ANS_MAGIC;
+        h.version = 1;
+        h.method = uint8_t(c->enc_method);
+        h.fidelity = uint8_t(c->enc_f);
+        h.n_symbols = n;
+        h.block_syms = bs;
+        h.n_blocks = nb;
+        h.prelude_bytes = uint32_t(pre);
+        h.payload_bytes = totals[0];
+        std::memcpy(front.data(), &h, sizeof h);
+        std::memcpy(front.data() + B200ANS_HEADER_BYTES, c->prelude.data(), pre);
+        // the front (minus the size table, which the compaction kernel fills) goes first
+        CU(c, cudaMemcpyAsync(d_dst, front.data(), payload_at, cudaMemcpyHostToDevice, c->stream));
+        const int grid = int(std::max<uint32_t>(1, std::min<uint32_t>((nb + 7) / 8, uint32_t(c->num_sms) * 8)));
+        compact_kernel<<<grid, 256, 0, c->stream>>>(c->scratch.as<uint8_t>(), stride, c->block_bytes.as<uint32_t>(),
+            c->offsets.as<uint64_t>(), nb, d_dst + payload_at, reinterpret_cast<uint32_t*>(d_dst + table_at));
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+        CU(c, cudaEventRecord(c->ev[2], c->stream));
+        CU(c, cudaStreamSynchronize(c->stream)); // `front` must outlive the copy
+        *out_bytes = total;
+        c->stats.payload_bytes = totals[1];
+    }
+    c->stats.ms_encode = elapsed(c->ev[0], c->ev[1]);
+    c->stats.ms_compact = elapsed(c->ev[1], c->ev[2]);
+    c->stats.n_blocks = nb;
+    c->stats.total_bytes = *out_bytes;
+    return B200ANS_OK;
+}
+
+// ==========================================================================================
+// one-shot paths
+// ==========================================================================================
+namespace {
+
+int write_empty_container(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap, size_t* out_bytes)
+{
+    if (c->block_syms == 0) { // the reference cannot represent an empty input either
+        *out_bytes = 0;
+        return B200ANS_OK;
+    }
+    if (cap < B200ANS_HEADER_BYTES)
+        return c->fail(B200ANS_E_CAPACITY, "destination too small");
+    Header h {};
+    h.magic = B200ANS_MAGIC;
+    h.version = 1;
+    h.method = uint8_t(method);
+    h.fidelity = uint8_t(f);
+    h.block_syms = c->block_syms;
+    CU(c, cudaMemcpyAsync(d_dst, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    *out_bytes = B200ANS_HEADER_BYTES;
+    return B200ANS_OK;
+}
+
+// device histogram -> host bins
+int histogram_to_host(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n, size_t nbins,
+    std::vector<uint64_t>& host_bins)
+{
+    CU(c, c->bins.reserve(nbins * 8));
+    CU(c, cudaMemsetAsync(c->bins.p, 0, nbins * 8, c->stream));
+    RET(histogram_dispatch(c, method, f, d_src, n, c->bins.as<uint64_t>(), nbins, c->d_max()));
+    host_bins.resize(nbins);
+    CU(c, cudaMemcpyAsync(host_bins.data(), c->bins.p, nbins * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return B200ANS_OK;
+}
+
+} // namespace
+
+// ans_X_compress with device-resident buffers: histogram (K1) -> host normalise -> encode (K2)
+extern "C" int b200ans_compress_device(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap,
+    const uint32_t* d_src, size_t n, size_t* out_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_dst || !out_bytes || (!d_src && n) || !valid_method(method, f)
+        || (reinterpret_cast<uintptr_t>(d_src) & 15) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
+        return c->fail(B200ANS_E_ARG, "compress: bad argument (device buffers must be 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    c->stats.ms_histogram = c->stats.ms_encode = c->stats.ms_compact = c->stats.ms_model = 0.f;
+    if (n == 0)
+        return write_empty_container(c, method, f, d_dst, cap, out_bytes);
+
+    CU(c, cudaEventRecord(c->ev[3], c->stream));
+    CU(c, cudaMemsetAsync(c->d_max(), 0, 4, c->stream));
+    uint32_t max_value = 0;
+    std::vector<uint64_t> bins;
+    if (method == METHOD_INT || method == METHOD_RFOLD) {
+        // two passes like the reference (ans_int.hpp:42-49): the alphabet size comes first
+        RET(b200ans_max_device(c, d_src, n, c->d_max()));
+        CU(c, cudaMemcpyAsync(&max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        if (method == METHOD_RFOLD && uint64_t(max_value) + (1u << (f + 7)) >= (1u << 30))
+            return c->fail(B200ANS_E_DOMAIN, "ANSrfold needs value + 2^(f+7) < 2^30");
+        if (max_value >= (1u << 30))
+            return c->fail(B200ANS_E_DOMAIN, "plain ANS: alphabets beyond 2^30 are not supported");
+        RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins));
+        if (method == METHOD_RFOLD) {
+            RET(b200ans_rfold_prepare(c, f, bins.data(), bins.size()));
+            RET(histogram_to_host(c, METHOD_RFOLD, f, d_src, n, alphabet_bins(method, f, 0), bins));
+        }
+    } else {
+        RET(histogram_to_host(c, method, f, d_src, n, alphabet_bins(method, f, 0), bins));
+        CU(c, cudaMemcpyAsync(&max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        if (max_value >= (1u << 30)) // the decoder keeps the byte count in bits 30-31 (ans_fold.hpp:198-200)
+            return c->fail(B200ANS_E_DOMAIN, "folded coders need values < 2^30");
+    }
+    CU(c, cudaEventRecord(c->ev[4], c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    const float ms_hist = elapsed(c->ev[3], c->ev[4]);
+    RET(b200ans_model_build(c, method, f, bins.data(), bins.size()));
+    RET(b200ans_encode_device(c, d_dst, cap, d_src, n, out_bytes));
+    c->stats.ms_histogram = ms_hist;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_decompress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, size_t n,
+    const uint8_t* d_src, size_t src_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!d_dst && n) || !d_src || !valid_method(method, f) || (reinterpret_cast<uintptr_t>(d_src) & 15))
+        return c->fail(B200ANS_E_ARG, "decompress: bad argument (d_src must be 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    c->stats.ms_decode = c->stats.ms_model = 0.f;
+    if (c->block_syms == 0) {
+        // reference wire format: [prelude][payload]; n and src_bytes come from the caller (methods.hpp:541-546)
+        if (n == 0)
+            return B200ANS_OK;
+        const size_t head = std::min<size_t>(src_bytes, size_t(64) << 20);
+        std::vector<uint8_t> front(head);
+        CU(c, cudaMemcpyAsync(front.data(), d_src, head, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        size_t used = 0;
+        RET(b200ans_model_load(c, method, f, front.data(), head, &used));
+        if (src_bytes < used + 32)
+            return c->fail(B200ANS_E_FORMAT, "decompress: stream shorter than prelude + states");
+        CU(c, c->offsets.reserve(8));
+        CU(c, c->block_bytes.reserve(4));
+        const uint64_t off = used;
+        const uint32_t sz = uint32_t(src_bytes - used);
+        if (src_bytes - used > 0x7FFFFF00ull)
+            return c->fail(B200ANS_E_ARG, "single-block payloads are limited to 2 GiB");
+        CU(c, cudaMemcpyAsync(c->offsets.p, &off, 8, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(c->block_bytes.p, &sz, 4, cudaMemcpyHostToDevice, c->stream));
+        return b200ans_decode_blocks_device(c, d_src, c->offsets.as<uint64_t>(), c->block_bytes.as<uint32_t>(), n, d_dst);
+    }
+    if (src_bytes < B200ANS_HEADER_BYTES)
+        return c->fail(B200ANS_E_FORMAT, "decompress: shorter than a header");
+    Header h;
+    CU(c, cudaMemcpyAsync(&h, d_src, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (h.magic != B200ANS_MAGIC || h.version != 1)
+        return c->fail(B200ANS_E_FORMAT, "decompress: bad magic / version");
+    if (h.method != method || (h.fidelity != f && (method == METHOD_FOLD || method == METHOD_RFOLD)))
+        return c->fail(B200ANS_E_FORMAT, "decompress: container was written by another method");
+    if (h.n_symbols != n)
+        return c->fail(B200ANS_E_ARG, "decompress: symbol count does not match the container");
+    if (n == 0)
+        return B200ANS_OK;
+    if (h.block_syms == 0 || h.block_syms % 4 != 0 || h.n_blocks != (n + h.block_syms - 1) / h.block_syms)
+        return c->fail(B200ANS_E_FORMAT, "decompress: inconsistent block geometry");
+    const size_t table_at = B200ANS_HEADER_BYTES + align_up(h.prelude_bytes, 4);
+    const size_t payload_at = align_up(table_at + size_t(h.n_blocks) * 4, 16);
+    if (payload_at + h.payload_bytes > src_bytes)
+        return c->fail(B200ANS_E_FORMAT, "decompress: container truncated");
+    std::vector<uint8_t> prelude(h.prelude_bytes);
+    CU(c, cudaMemcpyAsync(prelude.data(), d_src + B200ANS_HEADER_BYTES, h.prelude_bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    RET(b200ans_model_load(c, method, f, prelude.data(), prelude.size(), nullptr));
+    CU(c, c->offsets.reserve(size_t(h.n_blocks) * 8));
+    const uint32_t* d_sizes = reinterpret_cast<const uint32_t*>(d_src + table_at);
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, h.n_blocks, c->offsets.as<uint64_t>(), c->d_totals());
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    uint64_t totals[2] = { 0, 0 };
+    CU(c, cudaMemcpyAsync(totals, c->d_totals(), 16, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (totals[0] != h.payload_bytes)
+        return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
+    const uint32_t saved = c->block_syms;
+    c->block_syms = h.block_syms;
+    const int rc = b200ans_decode_blocks_device(c, d_src + payload_at, c->offsets.as<uint64_t>(), d_sizes, n, d_dst);
+    c->block_syms = saved;
+    return rc;
+}
+
+// ---- host buffers: what methods.hpp's encode()/decode() hand over ----------------------------
+extern "C" int b200ans_compress(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, size_t cap, const uint32_t* src,
+    size_t n, size_t* out_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!dst || !out_bytes || (!src && n) || !valid_method(method, f))
+        return c->fail(B200ANS_E_ARG, "compress: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    const size_t bound = std::min(b200ans_compress_bound(c, method, n), std::max<size_t>(cap + 64, 4096));
+    CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
+    CU(c, c->io_out.reserve(bound));
+    CU(c, cudaEventRecord(c->ev[5], c->stream));
+    if (n)
+        CU(c, cudaMemcpyAsync(c->io_in.p, src, n * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaEventRecord(c->ev[6], c->stream));
+    size_t bytes = 0;
+    RET(b200ans_compress_device(c, method, f, c->io_out.as<uint8_t>(), std::min(bound, c->io_out.cap), c->io_in.as<uint32_t>(), n, &bytes));
+    if (bytes > cap)
+        return c->fail(B200ANS_E_CAPACITY, "compress: destination too small");
+    CU(c, cudaEventRecord(c->ev[7], c->stream));
+    if (bytes)
+        CU(c, cudaMemcpyAsync(dst, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaEventRecord(c->ev[3], c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->stats.ms_h2d = elapsed(c->ev[5], c->ev[6]);
+    c->stats.ms_d2h = elapsed(c->ev[7], c->ev[3]);
+    *out_bytes = bytes;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src,
+    size_t src_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!dst && n) || !src || !valid_method(method, f))
+        return c->fail(B200ANS_E_ARG, "decompress: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->io_out.reserve(src_bytes + 64));
+    CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
+    CU(c, cudaEventRecord(c->ev[5], c->stream));
+    CU(c, cudaMemcpyAsync(c->io_out.p, src, src_bytes, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaMemsetAsync(c->io_out.as<uint8_t>() + src_bytes, 0, 64, c->stream));
+    CU(c, cudaEventRecord(c->ev[6], c->stream));
+    RET(b200ans_decompress_device(c, method, f, c->io_in.as<uint32_t>(), n, c->io_out.as<uint8_t>(), src_bytes));
+    CU(c, cudaEventRecord(c->ev[7], c->stream));
+    if (n)
+        CU(c, cudaMemcpyAsync(dst, c->io_in.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaEventRecord(c->ev[3], c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->stats.ms_h2d = elapsed(c->ev[5], c->ev[6]);
+    c->stats.ms_d2h = elapsed(c->ev[7], c->ev[3]);
+    return B200ANS_OK;
+}

@@ -1,0 +1,637 @@
+// b200ans device code (sm_100a): histogram, block-parallel rANS encoder / decoder, size scan,
+// payload compaction.
+//
+// Parallel decomposition ("lane per chain"): the reference coder keeps four interleaved 64-bit
+// rANS states per stream (ans_fold.hpp:250-278).  Here the input is cut into independent
+// blocks; one *group* of 4 lanes owns one block -- lane g carries chain 3-g, i.e. the symbols
+// at block-relative index 4t+g -- and a warp runs 8 blocks side by side.  The four chains are
+// arithmetically independent; they meet only at the shared byte cursor, which a 4-lane
+// (segmented) scan of "bytes emitted this step" reproduces exactly, so each block's payload is
+// byte-identical to the reference coder run on that block.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../host/fold.hpp"
+
+namespace b200ans {
+
+// ------------------------------------------------------------------------------------------
+// Tables
+// ------------------------------------------------------------------------------------------
+
+// Encoder entry, one per (mapped) symbol.  Replaces enc_entry_fold/_int/_msb/_reorder_fold
+// {freq, base, sym_upper_bound} (ans_fold.hpp:30-34 ...): the upper bound is recomputed as
+// freq << 36, and `rcp` is a reciprocal rounded towards zero far enough that
+// trunc(double(state) * rcp) is floor(state / freq) or one less (fixed up exactly).
+struct __align__(16) EncEntry {
+    uint32_t freq;
+    uint32_t base;
+    double rcp;
+};
+
+// Decoder slot entry for the folded coders.  Same content as dec_entry_fold
+// (ans_fold.hpp:128-132): freq, offset-in-symbol, unfolded base value | nbytes << 30.
+struct __align__(8) DecEntry {
+    uint16_t freq;
+    uint16_t offset;
+    uint32_t mapped; // for rfold: most_frequent[s] + 2^(f+7) resp. unfolded value
+};
+
+// Plain ANS decodes through two small tables instead of the reference's 8/12-byte slot
+// entries (ans_int.hpp:100-110): slot -> symbol id, symbol id -> {freq, base}.  The table
+// *contents* are a pure function of nfreqs, so the layout is ours to choose; this one keeps a
+// 2^16-slot model inside one SM's shared memory.
+struct __align__(8) SymEntry {
+    uint32_t freq;
+    uint32_t base;
+};
+
+struct EncArgs {
+    const uint32_t* in;      // symbols
+    uint64_t n;              // number of symbols
+    uint32_t block_syms;     // symbols per block (multiple of 4), or n for single-block mode
+    uint32_t n_blocks;
+    const EncEntry* table;   // global copy of the encoder table
+    uint32_t n_entries;      // entries in table (alphabet bins for folded methods, max_sym+1 for INT)
+    uint32_t log2_frame;     // log2 M
+    uint32_t fidelity;
+    const uint32_t* mapping; // RFOLD: value -> reordered value (ans_reorder_fold.hpp:92-106)
+    uint32_t n_values;       // RFOLD: entries in mapping
+    uint8_t* scratch;        // block b's payload goes to scratch + b * stride
+    uint64_t stride;
+    uint32_t* block_bytes;   // out: payload bytes of block b
+    uint32_t* error_flag;    // set to non-zero if a symbol had no model entry
+};
+
+struct DecArgs {
+    const uint8_t* payload;      // base of the payload area
+    const uint64_t* offsets;     // byte offset of block b's payload from `payload`
+    const uint32_t* block_bytes; // payload bytes of block b
+    uint32_t* out;
+    uint64_t n;
+    uint32_t block_syms;
+    uint32_t n_blocks;
+    uint32_t log2_frame;
+    uint32_t fidelity;
+    const DecEntry* slots;     // folded methods: M entries
+    const void* slot_to_sym;   // INT: M entries, u16 or u32
+    const SymEntry* syms;      // INT: n_syms entries
+    uint32_t n_syms;
+    uint32_t sym_bytes;        // INT: 2 or 4
+};
+
+// ------------------------------------------------------------------------------------------
+// Small helpers
+// ------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+
+template <int METHOD> __device__ __forceinline__ uint32_t map_value(uint32_t v, uint32_t f, uint32_t& k)
+{
+    if (METHOD == METHOD_INT) {
+        k = 0;
+        return v;
+    } else if (METHOD == METHOD_MSB) {
+        return msb_map(v, k);
+    } else {
+        return fold_map(v, f, k);
+    }
+}
+
+// state -> (state / freq) * M + state % freq + base, exactly (ans_fold.hpp:111).
+// Precondition: state < freq * 2^36 (always true after the renormalisation check) so the
+// quotient is below 2^36 and the double product errs by less than 2^-13.
+__device__ __forceinline__ uint64_t ans_push(uint64_t x, uint32_t freq, uint32_t base, double rcp, uint32_t log2_frame)
+{
+    const double qd = __dmul_rz(__ull2double_rz(x), rcp);
+    uint64_t q = __double2ull_rz(qd);
+    uint32_t r = uint32_t(x) - uint32_t(q) * freq; // true remainder or remainder + freq; both < 2^32
+    if (r >= freq) {
+        r -= freq;
+        q += 1;
+    }
+    return (q << log2_frame) + uint64_t(r + base);
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: histogram (+ running maximum of the raw values)
+// ------------------------------------------------------------------------------------------
+// Replaces the counting loops of ans_fold.hpp:74-78, ans_msb.hpp:81-85, ans_int.hpp:42-49 and
+// ans_reorder_fold.hpp:75-84,110-115.  Folded alphabets (<= kHistSmemBins bins) are counted in
+// shared memory with warp-aggregated atomics: lanes holding the same bin elect one leader
+// (__match_any_sync) that adds the population count, so a skewed distribution does not
+// serialise on its hottest bin; each CTA then merges its non-zero bins into the global 64-bit
+// histogram.  Raw alphabets larger than that go straight to global 64-bit atomics.
+
+constexpr uint32_t kHistSmemBins = 16384;
+constexpr int kHistThreads = 512;
+
+template <int METHOD, bool SMEM>
+__global__ void __launch_bounds__(kHistThreads) histogram_kernel(const uint32_t* __restrict__ in, uint64_t n,
+    uint32_t fidelity, const uint32_t* __restrict__ mapping, uint32_t n_values,
+    unsigned long long* __restrict__ bins, uint32_t nbins, uint32_t* __restrict__ max_value)
+{
+    extern __shared__ uint32_t s_bins[];
+    if (SMEM) {
+        for (uint32_t i = threadIdx.x; i < nbins; i += blockDim.x)
+            s_bins[i] = 0;
+        __syncthreads();
+    }
+    uint32_t local_max = 0;
+    auto count = [&](uint32_t v, bool valid) {
+        uint32_t k;
+        uint32_t mv = v;
+        if (METHOD == METHOD_RFOLD)
+            mv = (valid && v < n_values) ? __ldg(mapping + v) : 0u;
+        const uint32_t bin = map_value<METHOD>(mv, fidelity, k);
+        if (SMEM) {
+            // warp-aggregated shared-memory atomic
+            const uint32_t active = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                const uint32_t peers = __match_any_sync(active, bin);
+                if ((peers & ((1u << lane_id()) - 1u)) == 0 && bin < nbins)
+                    atomicAdd(&s_bins[bin], uint32_t(__popc(peers)));
+            }
+        } else if (valid && bin < nbins) {
+            atomicAdd(&bins[bin], 1ull);
+        }
+        if (valid)
+            local_max = max(local_max, v);
+    };
+
+    // 128-bit loads over the 16-byte aligned body, scalar tail
+    const uint64_t n4 = n >> 2;
+    const uint4* in4 = reinterpret_cast<const uint4*>(in);
+    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+    // every lane of a warp runs the same number of iterations (match/ballot need convergence)
+    const uint64_t iters = (n4 + stride - 1) / stride;
+    uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    for (uint64_t it = 0; it < iters; it++, i += stride) {
+        const bool valid = i < n4;
+        uint4 q = make_uint4(0, 0, 0, 0);
+        if (valid)
+            q = __ldg(in4 + i);
+        count(q.x, valid);
+        count(q.y, valid);
+        count(q.z, valid);
+        count(q.w, valid);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 32) {
+        const uint64_t t = (n4 << 2) + threadIdx.x;
+        const bool valid = t < n;
+        count(valid ? in[t] : 0u, valid);
+    }
+    // maximum of the raw values
+    for (int o = 16; o > 0; o >>= 1)
+        local_max = max(local_max, __shfl_xor_sync(0xffffffffu, local_max, o));
+    if (lane_id() == 0 && local_max != 0)
+        atomicMax(max_value, local_max);
+    if (SMEM) {
+        __syncthreads();
+        for (uint32_t b = threadIdx.x; b < nbins; b += blockDim.x) {
+            const uint32_t c = s_bins[b];
+            if (c)
+                atomicAdd(&bins[b], (unsigned long long)c);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2: block encoder
+// ------------------------------------------------------------------------------------------
+// One warp = 8 blocks x 4 chains.  Per step every lane takes one symbol:
+//   fold it (k raw bytes), look up {freq, base, rcp}, decide renormalisation, and announce
+//   c = k + 4*renorm bytes.  A reverse 4-lane scan (chain 0 emits first, ans_fold.hpp:262-271)
+//   gives the lane its byte offset behind the block's cursor; it stores its raw bytes, then its
+//   32-bit word (ans_fold.hpp:102-110) into the block's shared-memory row, and updates its state.
+// Every kEncTile steps the rows are drained to global memory in aligned 16-byte chunks.
+
+constexpr int kEncWarps = 8;           // warps per CTA
+constexpr int kEncTile = 8;            // steps between drains
+constexpr int kEncRowBytes = 272;      // 15 carried + 28 * kEncTile + 32 (states) <= 271; 272 = 17 * 16 spreads banks
+constexpr int kEncMaxSmemEntries = 6144; // 96 KiB of EncEntry
+
+template <int METHOD, bool TABLE_SMEM>
+__global__ void __launch_bounds__(kEncWarps * 32) encode_kernel(const EncArgs a)
+{
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    EncEntry* s_table = reinterpret_cast<EncEntry*>(smem_raw);
+    uint8_t* s_rows = smem_raw + (TABLE_SMEM ? size_t(a.n_entries) * sizeof(EncEntry) : 0);
+
+    if (TABLE_SMEM) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.table);
+        uint4* dst = reinterpret_cast<uint4*>(s_table);
+        for (uint32_t i = threadIdx.x; i < a.n_entries; i += blockDim.x)
+            dst[i] = __ldg(src + i);
+        __syncthreads();
+    }
+
+    const uint32_t lane = lane_id();
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t grp = lane >> 2;
+    const uint32_t g = lane & 3u;           // position inside a 4-symbol step; chain = 3 - g
+    const uint32_t grp_base = lane & ~3u;
+    uint8_t* row = s_rows + (size_t(warp) * 8 + grp) * kEncRowBytes;
+    const EncEntry* table = TABLE_SMEM ? s_table : a.table;
+    const uint32_t log2_frame = a.log2_frame;
+    const uint32_t f = a.fidelity;
+    const uint64_t lower = uint64_t(kAnsK) << log2_frame; // L = K * M (ans_fold.hpp:91)
+
+    const uint32_t n_tasks = (a.n_blocks + 7u) >> 3;
+    for (uint32_t task = blockIdx.x * kEncWarps + warp; task < n_tasks; task += gridDim.x * kEncWarps) {
+        const uint32_t blk = task * 8 + grp;
+        const bool have_block = blk < a.n_blocks;
+        const uint64_t first = uint64_t(blk) * a.block_syms;
+        const uint32_t nb = have_block ? uint32_t(min(uint64_t(a.block_syms), a.n - first)) : 0u;
+        const uint32_t* src = a.in + first;
+        const uint32_t tail = nb & 3u;      // these go to chain 0 first (ans_fold.hpp:257-261)
+        const uint32_t quads = nb >> 2;
+        const uint32_t my_steps = quads + tail;
+        const uint32_t max_steps = __reduce_max_sync(0xffffffffu, my_steps);
+
+        uint64_t x = lower;    // initial_state() (ans_fold.hpp:113)
+        uint32_t fill = 0;     // bytes sitting in the row
+        uint64_t flushed = 0;  // bytes already drained to scratch
+        uint8_t* dst = a.scratch + uint64_t(blk) * a.stride;
+
+        // symbol for (step s, this lane) or "inactive"
+        auto fetch = [&](uint32_t s, uint32_t& v) -> bool {
+            bool active;
+            uint32_t idx;
+            if (s < tail) {
+                active = (g == 3u);
+                idx = nb - 1u - s;
+            } else {
+                active = s < my_steps;
+                idx = 4u * (quads - 1u - (s - tail)) + g;
+            }
+            v = 0;
+            if (active) {
+                v = __ldg(src + idx);
+                if (METHOD == METHOD_RFOLD) {
+                    if (v >= a.n_values) { // value the model has never seen
+                        *a.error_flag = 1u;
+                        v = 0;
+                    }
+                    v = __ldg(a.mapping + v);
+                }
+            }
+            return active;
+        };
+
+        uint32_t vnext[kEncTile];
+        uint32_t anext = 0;
+#pragma unroll
+        for (int i = 0; i < kEncTile; i++)
+            anext |= uint32_t(fetch(uint32_t(i), vnext[i])) << i;
+
+        for (uint32_t s0 = 0; s0 < max_steps; s0 += kEncTile) {
+            uint32_t vcur[kEncTile];
+            const uint32_t acur = anext;
+#pragma unroll
+            for (int i = 0; i < kEncTile; i++)
+                vcur[i] = vnext[i];
+            anext = 0;
+            if (s0 + kEncTile < max_steps) {
+#pragma unroll
+                for (int i = 0; i < kEncTile; i++)
+                    anext |= uint32_t(fetch(s0 + kEncTile + uint32_t(i), vnext[i])) << i;
+            }
+
+#pragma unroll
+            for (int i = 0; i < kEncTile; i++) {
+                const bool active = (acur >> i) & 1u;
+                const uint32_t v = vcur[i];
+                uint32_t k;
+                uint32_t sym = map_value<METHOD>(v, f, k);
+                if (sym >= a.n_entries) { // value outside the model: flag, stay in bounds
+                    if (active)
+                        *a.error_flag = 1u;
+                    sym = 0;
+                }
+                const EncEntry e = table[sym];
+                const bool renorm = active && (uint32_t(x >> 36) >= e.freq); // state >= freq * K * 2^32
+                const uint32_t c = active ? k + (renorm ? 4u : 0u) : 0u;
+                // reverse inclusive scan over the group: lanes with larger g emit first
+                uint32_t incl = c;
+                uint32_t t = __shfl_down_sync(0xffffffffu, incl, 1, 4);
+                if (g < 3u)
+                    incl += t;
+                t = __shfl_down_sync(0xffffffffu, incl, 2, 4);
+                if (g < 2u)
+                    incl += t;
+                const uint32_t total = __shfl_sync(0xffffffffu, incl, grp_base);
+                uint8_t* p = row + fill + (incl - c);
+                if (active) {
+                    if (k > 0u)
+                        p[0] = uint8_t(v);
+                    if (k > 1u)
+                        p[1] = uint8_t(v >> 8);
+                    if (k > 2u)
+                        p[2] = uint8_t(v >> 16);
+                    if (renorm) {
+                        const uint32_t w = uint32_t(x);
+                        p[k] = uint8_t(w);
+                        p[k + 1] = uint8_t(w >> 8);
+                        p[k + 2] = uint8_t(w >> 16);
+                        p[k + 3] = uint8_t(w >> 24);
+                        x >>= kRadixLog2;
+                    }
+                    if (e.freq == 0u)
+                        *a.error_flag = 1u;
+                    x = ans_push(x, e.freq, e.base, e.rcp, log2_frame);
+                }
+                fill += total;
+            }
+
+            // drain whole 16-byte chunks, carry the remainder to the front of the row
+            __syncwarp();
+            {
+                const uint32_t chunks = fill >> 4;
+                const uint4* rv = reinterpret_cast<const uint4*>(row);
+                uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
+                for (uint32_t ci = g; ci < chunks; ci += 4)
+                    gv[ci] = rv[ci];
+                uint4 carry = make_uint4(0, 0, 0, 0);
+                if (g == 0u && chunks != 0u)
+                    carry = rv[chunks];
+                __syncwarp();
+                if (g == 0u && chunks != 0u)
+                    *reinterpret_cast<uint4*>(row) = carry;
+                flushed += uint64_t(chunks) << 4;
+                fill &= 15u;
+            }
+            __syncwarp();
+        }
+
+        // flush_state x4 in chain order 0..3 (ans_fold.hpp:115-120, 275-278), then the rest of the row
+        if (have_block) {
+            const uint64_t fin = x - lower;
+            uint8_t* p = row + fill + 8u * (3u - g);
+#pragma unroll
+            for (int b = 0; b < 8; b++)
+                p[b] = uint8_t(fin >> (8 * b));
+        }
+        fill += have_block ? 32u : 0u;
+        // zero the padding up to the next 16-byte boundary so the container is deterministic
+        for (uint32_t z = fill + g; z < ((fill + 15u) & ~15u); z += 4)
+            row[z] = 0;
+        __syncwarp();
+        {
+            const uint32_t chunks = (fill + 15u) >> 4;
+            const uint4* rv = reinterpret_cast<const uint4*>(row);
+            uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
+            if (have_block)
+                for (uint32_t ci = g; ci < chunks; ci += 4)
+                    gv[ci] = rv[ci];
+            if (have_block && g == 0u)
+                a.block_bytes[blk] = uint32_t(flushed + fill);
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3: block decoder
+// ------------------------------------------------------------------------------------------
+// Mirror image: lane g of a group decodes the symbols at block index 4t+g with chain 3-g
+// (ans_fold.hpp:300-305).  Each step: slot lookup, state update, renormalisation test, forward
+// 4-lane scan of bytes consumed (renorm word first, then k raw bytes: ans_fold.hpp:221-226),
+// then an unaligned 8-byte window below the lane's position is assembled from the block's
+// staged bytes in shared memory.  Every kDecTile steps the stage is refilled with the next
+// 28*kDecTile (worst case) bytes below the cursor, in aligned 16-byte chunks.
+
+constexpr int kDecWarps = 8;
+constexpr int kDecTile = 8;
+constexpr int kDecPad = 16;        // bytes in front of the staged window (window under-read lands here)
+constexpr int kDecStageChunks = 18; // 16-byte chunks staged per refill: covers 28*8 + 12 + 4 + alignment
+constexpr int kDecRowBytes = kDecPad + kDecStageChunks * 16; // 304 = 19 * 16
+
+enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3 };
+
+template <int METHOD, int TABLE>
+__global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
+{
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    constexpr bool kInt = (METHOD == METHOD_INT);
+    constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM);
+    const uint32_t frame = 1u << a.log2_frame;
+    size_t table_bytes = 0;
+    if (kSmem) {
+        if (kInt)
+            table_bytes = ((size_t(frame) * a.sym_bytes + 15) & ~size_t(15)) + size_t(a.n_syms) * sizeof(SymEntry);
+        else
+            table_bytes = size_t(frame) * sizeof(DecEntry);
+        table_bytes = (table_bytes + 15) & ~size_t(15);
+    }
+    uint8_t* s_rows = smem_raw + table_bytes;
+    const DecEntry* slots = a.slots;
+    const void* s2s = a.slot_to_sym;
+    const SymEntry* syms = a.syms;
+    if (kSmem) {
+        // cooperative 16-byte copies of the tables
+        if (kInt) {
+            const size_t s2s_bytes = (size_t(frame) * a.sym_bytes + 15) & ~size_t(15);
+            const uint4* src = reinterpret_cast<const uint4*>(a.slot_to_sym);
+            uint4* dst = reinterpret_cast<uint4*>(smem_raw);
+            for (size_t i = threadIdx.x; i < s2s_bytes / 16; i += blockDim.x)
+                dst[i] = __ldg(src + i);
+            const uint2* src2 = reinterpret_cast<const uint2*>(a.syms);
+            uint2* dst2 = reinterpret_cast<uint2*>(smem_raw + s2s_bytes);
+            for (size_t i = threadIdx.x; i < a.n_syms; i += blockDim.x)
+                dst2[i] = __ldg(src2 + i);
+            s2s = smem_raw;
+            syms = reinterpret_cast<const SymEntry*>(smem_raw + s2s_bytes);
+        } else {
+            const uint2* src = reinterpret_cast<const uint2*>(a.slots);
+            uint2* dst = reinterpret_cast<uint2*>(smem_raw);
+            for (size_t i = threadIdx.x; i < frame; i += blockDim.x)
+                dst[i] = __ldg(src + i);
+            slots = reinterpret_cast<const DecEntry*>(smem_raw);
+        }
+        __syncthreads();
+    }
+
+    const uint32_t lane = lane_id();
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t grp = lane >> 2;
+    const uint32_t g = lane & 3u;
+    const uint32_t grp_last = lane | 3u;
+    uint8_t* row = s_rows + (size_t(warp) * 8 + grp) * kDecRowBytes;
+    const uint32_t log2_frame = a.log2_frame;
+    const uint32_t frame_mask = frame - 1u;
+    const uint64_t lower = uint64_t(kAnsK) << log2_frame;
+    const uint32_t rfold_bias = (METHOD == METHOD_RFOLD) ? (1u << (a.fidelity + 7)) : 0u; // ans_reorder_fold.hpp:301
+
+    const uint32_t n_tasks = (a.n_blocks + 7u) >> 3;
+    for (uint32_t task = blockIdx.x * kDecWarps + warp; task < n_tasks; task += gridDim.x * kDecWarps) {
+        const uint32_t blk = task * 8 + grp;
+        const bool have_block = blk < a.n_blocks;
+        const uint64_t first = uint64_t(blk) * a.block_syms;
+        const uint32_t nb = have_block ? uint32_t(min(uint64_t(a.block_syms), a.n - first)) : 0u;
+        const uint32_t tail = nb & 3u;
+        const uint32_t quads = nb >> 2;
+        const uint32_t my_steps = quads + tail;
+        const uint32_t max_steps = __reduce_max_sync(0xffffffffu, my_steps);
+        uint32_t* out = a.out + first;
+
+        // positions are relative to the 16-byte aligned address at or below the payload start
+        const uint8_t* pay = a.payload + (have_block ? a.offsets[blk] : 0);
+        const uint32_t delta = uint32_t(reinterpret_cast<uintptr_t>(pay) & 15u);
+        const uint8_t* pay_al = pay - delta;
+        const uint32_t size = have_block ? a.block_bytes[blk] : 32u;
+
+        // init_state x4: chain 3 is the last 8 bytes ... chain 0 the first of the 32 (ans_fold.hpp:291-295)
+        uint64_t x = lower;
+        if (have_block) {
+            const uint8_t* sp = pay + size - 32u + 8u * (3u - g);
+            uint64_t v = 0;
+#pragma unroll
+            for (int b = 0; b < 8; b++)
+                v |= uint64_t(sp[b]) << (8 * b);
+            x = v + lower;
+        }
+        int32_t cursor = int32_t(delta + size - 32u); // one past the next byte to consume
+
+        for (uint32_t s0 = 0; s0 < max_steps; s0 += kDecTile) {
+            // stage [lo, lo + 288) around the cursor
+            int32_t lo = cursor - (28 * kDecTile + 12);
+            lo = lo < 0 ? 0 : (lo & ~15);
+            __syncwarp();
+            if (have_block) {
+                const uint4* gsrc = reinterpret_cast<const uint4*>(pay_al + lo);
+                uint4* sdst = reinterpret_cast<uint4*>(row + kDecPad);
+                const int32_t need = (cursor + 4 - lo + 15) >> 4; // chunks that can be touched
+#pragma unroll
+                for (int ci = 0; ci < (kDecStageChunks + 3) / 4; ci++) {
+                    const int32_t c = ci * 4 + int32_t(g);
+                    if (c < need && c < kDecStageChunks)
+                        sdst[c] = __ldg(gsrc + c);
+                }
+            }
+            __syncwarp();
+            const uint8_t* stage = row + kDecPad - lo; // stage[pos] is payload byte `pos`
+
+#pragma unroll
+            for (int i = 0; i < kDecTile; i++) {
+                const uint32_t s = s0 + uint32_t(i);
+                // quads first, all four lanes; then the tail on chain 0 (lane g == 3)
+                const bool active = s < quads ? true : (s < my_steps && g == 3u);
+                const uint32_t idx = s < quads ? 4u * s + g : s + 3u * quads; // 4*quads + (s - quads)
+                const uint32_t slot = uint32_t(x) & frame_mask;
+                uint32_t freq, offset, mapped, k;
+                if (kInt) {
+                    const uint32_t sym = (a.sym_bytes == 2) ? uint32_t(reinterpret_cast<const uint16_t*>(s2s)[slot])
+                                                            : reinterpret_cast<const uint32_t*>(s2s)[slot];
+                    const SymEntry se = syms[sym];
+                    freq = se.freq;
+                    offset = slot - se.base;
+                    mapped = sym;
+                    k = 0;
+                } else {
+                    const DecEntry e = slots[slot];
+                    freq = e.freq;
+                    offset = e.offset;
+                    mapped = e.mapped & 0x3FFFFFFFu;
+                    k = e.mapped >> 30;
+                }
+                uint64_t nx = uint64_t(freq) * (x >> log2_frame) + offset;
+                const bool renorm = active && nx < lower;
+                const uint32_t c = active ? k + (renorm ? 4u : 0u) : 0u;
+                // forward inclusive scan: lane 0 of the group consumes first
+                uint32_t incl = c;
+                uint32_t t = __shfl_up_sync(0xffffffffu, incl, 1, 4);
+                if (g >= 1u)
+                    incl += t;
+                t = __shfl_up_sync(0xffffffffu, incl, 2, 4);
+                if (g >= 2u)
+                    incl += t;
+                const uint32_t total = __shfl_sync(0xffffffffu, incl, grp_last);
+                const int32_t end = cursor - int32_t(incl - c); // my bytes are [end - c, end)
+                // 8-byte window [end-8, end) from three aligned words
+                const int32_t wa = end - 8;
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(stage + (wa & ~3));
+                const uint32_t sh = (uint32_t(wa) & 3u) * 8u;
+                const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
+                const uint32_t win_lo = __funnelshift_r(w0, w1, sh);
+                const uint32_t win_hi = __funnelshift_r(w1, w2, sh);
+                if (renorm)
+                    nx = (nx << kRadixLog2) | uint64_t(win_hi);
+                const uint32_t exc_src = renorm ? win_lo : win_hi;
+                const uint32_t exc = __funnelshift_rc(exc_src, 0u, 32u - 8u * k); // top k bytes; 0 when k == 0
+                if (active) {
+                    x = nx;
+                    out[idx] = mapped + exc - rfold_bias;
+                }
+                cursor -= int32_t(total);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Size scan + payload compaction
+// ------------------------------------------------------------------------------------------
+
+// offsets[b] = sum_{b' < b} roundup16(bytes[b']); total[0] = sum of all; total[1] = unpadded sum
+__global__ void __launch_bounds__(1024) scan_block_sizes_kernel(const uint32_t* __restrict__ bytes, uint32_t n_blocks,
+    uint64_t* __restrict__ offsets, uint64_t* __restrict__ totals)
+{
+    __shared__ uint64_t s_part[1024];
+    __shared__ uint64_t s_raw[1024];
+    const uint32_t per = (n_blocks + blockDim.x - 1) / blockDim.x;
+    const uint32_t b0 = min(n_blocks, threadIdx.x * per);
+    const uint32_t b1 = min(n_blocks, b0 + per);
+    uint64_t sum = 0, raw = 0;
+    for (uint32_t b = b0; b < b1; b++) {
+        sum += (uint64_t(bytes[b]) + 15u) & ~uint64_t(15);
+        raw += bytes[b];
+    }
+    s_part[threadIdx.x] = sum;
+    s_raw[threadIdx.x] = raw;
+    __syncthreads();
+    // Hillis-Steele inclusive scan over 1024 partials
+    for (uint32_t d = 1; d < blockDim.x; d <<= 1) {
+        uint64_t v = 0, r = 0;
+        if (threadIdx.x >= d) {
+            v = s_part[threadIdx.x - d];
+            r = s_raw[threadIdx.x - d];
+        }
+        __syncthreads();
+        s_part[threadIdx.x] += v;
+        s_raw[threadIdx.x] += r;
+        __syncthreads();
+    }
+    uint64_t run = s_part[threadIdx.x] - sum;
+    for (uint32_t b = b0; b < b1; b++) {
+        offsets[b] = run;
+        run += (uint64_t(bytes[b]) + 15u) & ~uint64_t(15);
+    }
+    if (threadIdx.x == blockDim.x - 1) {
+        totals[0] = s_part[threadIdx.x];
+        totals[1] = s_raw[threadIdx.x];
+    }
+}
+
+// one warp per block: scratch + b*stride  ->  payload + offsets[b]; also fills the container's size table
+__global__ void __launch_bounds__(256) compact_kernel(const uint8_t* __restrict__ scratch, uint64_t stride,
+    const uint32_t* __restrict__ bytes, const uint64_t* __restrict__ offsets, uint32_t n_blocks,
+    uint8_t* __restrict__ payload, uint32_t* __restrict__ size_table)
+{
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    const uint32_t lane = lane_id();
+    for (uint32_t b = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); b < n_blocks; b += gridDim.x * warps_per_cta) {
+        const uint32_t sz = bytes[b];
+        const uint32_t chunks = (sz + 15u) >> 4;
+        const uint4* src = reinterpret_cast<const uint4*>(scratch + uint64_t(b) * stride);
+        uint4* dst = reinterpret_cast<uint4*>(payload + offsets[b]);
+        for (uint32_t c = lane; c < chunks; c += 32)
+            dst[c] = src[c];
+        if (lane == 0 && size_table)
+            size_table[b] = sz;
+    }
+}
+
+} // namespace b200ans

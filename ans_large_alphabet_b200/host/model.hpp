@@ -1,0 +1,145 @@
+// b200ans host-side model utilities: histogram -> normalised frequencies.
+//
+// Drop-in for the reference's ans_util.hpp model API (same free-function names, argument
+// meaning and results, bit for bit):
+//   adjust_freqs        <- /root/reference/include/ans_util.hpp:100-157
+//   scale_freqs         <- ans_util.hpp:77-95
+//   next_power_of_two   <- ans_util.hpp:65-72
+//   is_power_of_two     <- ans_util.hpp:74
+//   entropy             <- util.hpp:271-282
+//   cross_entropy       <- util.hpp:284-298
+// This step stays on the host: the histogram it consumes is
+// tiny for the folded coders and the accept/reject decision hangs on glibc's log2.
+//
+// "Bit for bit" includes the reference's quirks:
+//  * symbols are scaled rarest-first against a *running* ratio;
+//  * cross_entropy sums both distributions into a 32-bit signed accumulator;
+//  * the three multiply-adds below are fused, as GCC's default -ffp-contract=fast does to
+//    the reference on every FMA-capable x86-64 (its CMake build uses -march=native).
+#pragma once
+
+#include <algorithm>
+#include <cmath>
+#include <cstddef>
+#include <cstdint>
+#include <limits>
+#include <utility>
+#include <vector>
+
+namespace b200ans {
+
+inline bool is_power_of_two(uint64_t x) { return x != 0 && (x & (x - 1)) == 0; }
+
+// smallest power of two strictly greater than x's top bit, i.e. 2^(floor(log2 x) + 1); 1 for x = 0.
+// (callers only use it for non-powers of two, where this is "round up")
+inline uint64_t next_power_of_two(uint64_t x)
+{
+    if (x == 0)
+        return 1;
+    return uint64_t(2) << (63 - __builtin_clzll(x));
+}
+
+template <class X> inline double entropy(const std::vector<X>& freqs, size_t freqs_sum)
+{
+    const double total = double(freqs_sum);
+    double acc = 0.0;
+    for (const X& f : freqs) {
+        if (f == 0)
+            continue;
+        const double p = double(f) / total;
+        acc = std::fma(p, std::log2(p), acc);
+    }
+    return -acc;
+}
+
+namespace detail {
+    // std::accumulate(first, last, 0): the accumulator is an `int`
+    template <class V> inline double int_accumulated_sum(const V& v)
+    {
+        int32_t acc = 0;
+        for (const auto& e : v)
+            acc = int32_t(uint32_t(uint64_t(int64_t(acc)) + uint64_t(e)));
+        return double(acc);
+    }
+}
+
+template <class X, class Y> inline double cross_entropy(const std::vector<X>& P, const std::vector<Y>& Q)
+{
+    const double n = detail::int_accumulated_sum(P);
+    const double m = detail::int_accumulated_sum(Q);
+    double acc = 0.0;
+    for (size_t i = 0; i < P.size(); i++) {
+        if (P[i] == 0 || Q[i] == 0) // P is zero beyond Q's end, so Q[i] is never read out of range
+            continue;
+        const double p = double(P[i]) / n;
+        const double q = double(Q[i]) / m;
+        acc = std::fma(p, std::log2(q), acc);
+    }
+    return -acc;
+}
+
+// Fit F (symbols visited in `mapping` order, rarest first) into a frame of exactly M slots.
+// Returns true when the fit FAILED (slots left over or overdrawn), like the reference.
+inline bool scale_freqs(std::vector<uint32_t>& S, const std::vector<uint64_t>& F, std::vector<uint32_t>& mapping,
+    int64_t M, size_t sigma, size_t freq_sum)
+{
+    for (size_t rank = 0; rank < sigma; rank++) {
+        const uint32_t sym = mapping[rank];
+        const double ratio = double(M) / double(freq_sum);
+        uint32_t share = uint32_t(std::fma(ratio, double(F[sym]), 0.5));
+        if (share == 0)
+            share = 1;
+        S[sym] = share;
+        M -= share;
+        freq_sum -= F[sym];
+        if (M < 0)
+            break;
+    }
+    return M != 0;
+}
+
+// Smallest power-of-two frame whose cross entropy is within H_approx/1000 of the entropy
+// (or, with require_u16, the last frame before some normalised frequency reaches 65535).
+inline std::vector<uint32_t> adjust_freqs(
+    const std::vector<uint64_t>& freqs, uint32_t largest_sym, bool require_u16, uint32_t H_approx = 1)
+{
+    size_t sigma = 0, freq_sum = 0;
+    for (uint64_t f : freqs) {
+        freq_sum += f;
+        sigma += (f != 0);
+    }
+    size_t frame = is_power_of_two(sigma) ? sigma : size_t(next_power_of_two(sigma));
+
+    std::vector<std::pair<uint64_t, uint32_t>> by_freq;
+    by_freq.reserve(sigma);
+    for (size_t s = 0; s < freqs.size(); s++)
+        if (freqs[s] != 0)
+            by_freq.emplace_back(freqs[s], uint32_t(s));
+    std::sort(by_freq.begin(), by_freq.end());
+    std::vector<uint32_t> order(sigma);
+    for (size_t i = 0; i < sigma; i++)
+        order[i] = by_freq[i].second;
+
+    const double H = entropy(freqs, freq_sum);
+    const double limit = H * (1.0 + double(H_approx) / double(1000));
+    std::vector<uint32_t> cur(size_t(largest_sym) + 1, 0), last_good(size_t(largest_sym) + 1, 0);
+    for (;;) {
+        if (scale_freqs(cur, freqs, order, int64_t(frame), sigma, freq_sum)) {
+            frame *= 2;
+            continue;
+        }
+        const uint32_t top = *std::max_element(cur.begin(), cur.end());
+        const double XH = cross_entropy(freqs, cur);
+        if (require_u16 && top >= std::numeric_limits<uint16_t>::max()) {
+            cur = last_good;
+            break;
+        }
+        if (XH < limit)
+            break;
+        frame *= 2;
+        last_good = cur;
+    }
+    return cur;
+}
+
+} // namespace b200ans

@@ -1,0 +1,162 @@
+/* b200ans -- C ABI of the B200-native semi-static large-alphabet ANS coders.
+ *
+ * This is the drop-in boundary.  The reference
+ * (mpetri/ans-large-alphabet) is header-only C++ with no FFI layer; the entry points a
+ * binding would call are its L2 free functions, and each function below names the one it
+ * replaces (paths under /root/reference/include):
+ *
+ *   b200ans_compress / _decompress        ans_int_compress / ans_int_decompress    ans_int.hpp:197,257
+ *                                         ans_fold_compress<f> / _decompress<f>    ans_fold.hpp:238,283
+ *                                         ans_msb_compress / _decompress           ans_msb.hpp:235,294
+ *                                         ans_reorder_fold_compress<f> / _de..<f>  ans_reorder_fold.hpp:312,357
+ *                                         (what methods.hpp:484-567 ANSint/ANSmsb/ANSfold<f>/ANSrfold<f> call)
+ *   b200ans_histogram_device              the counting loops of ans_fold.hpp:74-78, ans_msb.hpp:81-85,
+ *                                         ans_int.hpp:42-49, ans_reorder_fold.hpp:75-84,110-115
+ *   b200ans_adjust_freqs                  adjust_freqs            ans_util.hpp:100-157
+ *   b200ans_serialize_interp              ans_serialize_interp    ans_util.hpp:46-63
+ *   b200ans_load_interp                   ans_load_interp         ans_util.hpp:25-42
+ *   b200ans_interp_encode / _decode       interpolative_internal::encode / decode   interp.hpp:100-118
+ *   b200ans_model_* / _encode_device /    ans_X_encode::create / serialize / encode_symbol / flush_state and
+ *   _decode_device                        ans_X_decode::load / init_state / decode_sym (ans_fold.hpp:68-125,177-235 ...)
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 (B200ANS_OK) or a
+ * negative error code; nothing throws or calls exit(); the library never frees caller memory.
+ * "d_" parameters are device pointers on the context's GPU, everything else is host memory.
+ * There is NO CPU fallback: without a usable CUDA device b200ans_create fails.
+ *
+ * Stream format.  block_syms > 0 (default 8192): a blocked container
+ *     [64-byte header][reference-format prelude][u32 bytes-per-block x n_blocks][pad to 16]
+ *     [block payloads, each 16-byte aligned]
+ * where every block payload is byte-identical to what the reference coder emits for that
+ * sub-range with the same (global) model: raw low bytes + renormalisation words in reverse
+ * input order, then the four 64-bit states (ans_fold.hpp:250-278).
+ * block_syms == 0: "reference wire format" -- prelude + one payload, no header; the output
+ * equals the reference's ans_X_compress() byte for byte (modulo the reference's own
+ * uninitialised prelude padding bits) and reference-produced streams decode. One block means
+ * four chains: correct, but slow on a GPU; it exists for interoperability and tests.
+ */
+#ifndef B200ANS_H
+#define B200ANS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ANS_OK 0
+#define B200ANS_E_ARG (-1)      /* bad argument (null pointer, unknown method, fidelity outside 1..8, alignment) */
+#define B200ANS_E_CUDA (-2)     /* a CUDA call failed; see b200ans_last_error */
+#define B200ANS_E_CAPACITY (-3) /* destination too small */
+#define B200ANS_E_DOMAIN (-4)   /* input outside the reference's valid domain */
+#define B200ANS_E_FORMAT (-5)   /* not a b200ans container / corrupt header */
+#define B200ANS_E_STATE (-6)    /* call sequence error (e.g. encode before a model exists) */
+
+#define B200ANS_METHOD_INT 0   /* "ANS"        plain large-alphabet ANS, ans_int.hpp          */
+#define B200ANS_METHOD_FOLD 1  /* "ANSfold-f"  ans_fold.hpp                                   */
+#define B200ANS_METHOD_MSB 2   /* "ANSmsb"     ans_msb.hpp                                    */
+#define B200ANS_METHOD_RFOLD 3 /* "ANSrfold-f" ans_reorder_fold.hpp                           */
+
+#define B200ANS_DEFAULT_BLOCK_SYMS 8192u
+#define B200ANS_HEADER_BYTES 64u
+#define B200ANS_MAGIC 0x4E413242u /* "B2AN" */
+
+typedef struct b200ans_ctx b200ans_ctx;
+
+/* Timings of the most recent call, measured with CUDA events on the context's stream. */
+typedef struct b200ans_stats {
+    float ms_histogram;   /* K1 (all histogram / max launches)                 */
+    float ms_model;       /* host: normalise + prelude + table build + upload  */
+    float ms_encode;      /* K2 block encoder                                  */
+    float ms_compact;     /* size scan + payload compaction                    */
+    float ms_decode;      /* K3 block decoder                                  */
+    float ms_h2d;         /* host->device copies inside the call               */
+    float ms_d2h;         /* device->host copies inside the call               */
+    uint64_t launches;    /* kernels launched by this context since creation   */
+    uint64_t frame_size;  /* M of the current model                            */
+    uint32_t n_symbols_model; /* max_sym + 1                                   */
+    uint32_t n_blocks;
+    uint64_t prelude_bytes;
+    uint64_t payload_bytes; /* sum of block payload bytes (unpadded)           */
+    uint64_t total_bytes;   /* whole container                                 */
+} b200ans_stats;
+
+/* ---- context ------------------------------------------------------------------------- */
+/* stream: a cudaStream_t (as void*) to run on, or NULL to let the context create its own. */
+int b200ans_create(b200ans_ctx** out, int device, void* stream);
+void b200ans_destroy(b200ans_ctx* ctx);
+int b200ans_set_block_syms(b200ans_ctx* ctx, uint32_t block_syms); /* 0 or a multiple of 128 */
+int b200ans_get_stats(const b200ans_ctx* ctx, b200ans_stats* out);
+const char* b200ans_last_error(const b200ans_ctx* ctx);
+const char* b200ans_strerror(int code);
+const char* b200ans_method_name(int method, uint32_t fidelity, char* buf, size_t buflen);
+/* upper bound on the container size for n symbols */
+size_t b200ans_compress_bound(const b200ans_ctx* ctx, int method, size_t n);
+
+/* ---- one-shot, host buffers (the methods.hpp encode/decode path) ------------------------ */
+int b200ans_compress(b200ans_ctx* ctx, int method, uint32_t fidelity, uint8_t* dst, size_t dst_capacity,
+    const uint32_t* src, size_t n, size_t* out_bytes);
+int b200ans_decompress(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* dst, size_t n,
+    const uint8_t* src, size_t src_bytes);
+
+/* ---- one-shot, device-resident buffers (d_src / d_dst 16-byte aligned) ------------------ */
+int b200ans_compress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint8_t* d_dst, size_t dst_capacity,
+    const uint32_t* d_src, size_t n, size_t* out_bytes);
+int b200ans_decompress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* d_dst, size_t n,
+    const uint8_t* d_src, size_t src_bytes);
+
+/* ---- staged path (multi-GPU: histogram -> all-reduce by the caller -> model -> encode) -- */
+/* max over d_src, atomically max-combined into *d_max (device u32, caller-initialised). */
+int b200ans_max_device(b200ans_ctx* ctx, const uint32_t* d_src, size_t n, uint32_t* d_max);
+/* adds the (mapped) symbol counts of d_src into d_bins[nbins] (device u64, caller-zeroed).
+ * nbins: INT -> max value + 1; FOLD / RFOLD -> 2^(f+9); MSB -> 1280.
+ * RFOLD uses the context's current value mapping (b200ans_rfold_prepare) -- call with
+ * method INT on the raw values first to obtain the full-alphabet histogram. */
+int b200ans_histogram_device(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint32_t* d_src, size_t n,
+    uint64_t* d_bins, size_t nbins);
+/* RFOLD only: from the full-alphabet histogram (host u64[nvalues]) pick the 2^(f+7) most
+ * frequent values, ties to the smaller value (ans_reorder_fold.hpp:79-106), and upload the
+ * value -> reordered-value table. */
+int b200ans_rfold_prepare(b200ans_ctx* ctx, uint32_t fidelity, const uint64_t* raw_bins, size_t nvalues);
+/* host histogram -> normalised model (adjust_freqs) + prelude + device encoder tables. */
+int b200ans_model_build(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint64_t* bins, size_t nbins);
+/* prelude of the current model; returns its size through out_bytes */
+int b200ans_model_prelude(b200ans_ctx* ctx, uint8_t* dst, size_t capacity, size_t* out_bytes);
+/* normalised frequencies of the current model (count = max_sym + 1) */
+int b200ans_model_nfreqs(b200ans_ctx* ctx, uint32_t* dst, size_t capacity, size_t* out_count, uint64_t* frame_size);
+/* decoder side: parse a reference-format prelude, build + upload the slot tables */
+int b200ans_model_load(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint8_t* prelude, size_t prelude_bytes,
+    size_t* consumed);
+/* encode d_src with the current model into a container at d_dst */
+int b200ans_encode_device(b200ans_ctx* ctx, uint8_t* d_dst, size_t dst_capacity, const uint32_t* d_src, size_t n,
+    size_t* out_bytes);
+/* per-block payload access for parity tests: encode, leaving payload b at d_scratch + b*stride */
+int b200ans_encode_blocks_device(b200ans_ctx* ctx, const uint32_t* d_src, size_t n, uint8_t* d_scratch,
+    size_t stride, uint32_t* d_block_bytes);
+int b200ans_block_stride(const b200ans_ctx* ctx, int method, size_t* stride);
+/* decode payload blocks that sit at d_payload + d_offsets[b] with sizes d_block_bytes[b] using
+ * the currently loaded decoder model */
+int b200ans_decode_blocks_device(b200ans_ctx* ctx, const uint8_t* d_payload, const uint64_t* d_offsets,
+    const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst);
+
+/* ---- host-only model API (ans_util.hpp / interp.hpp); usable without a GPU ------------- */
+/* out: largest_sym + 1 entries */
+int b200ans_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_t largest_sym, int require_u16,
+    uint32_t H_approx, uint32_t* out);
+int b200ans_serialize_interp(const uint32_t* nfreqs, size_t count, uint64_t frame_size, uint8_t* dst, size_t capacity,
+    size_t* out_bytes);
+/* dst may be NULL to query the count; consumed may be NULL */
+int b200ans_load_interp(const uint8_t* src, uint32_t* dst, size_t capacity, size_t* out_count, size_t* consumed);
+int b200ans_interp_encode(uint32_t* dst, const uint32_t* in, size_t n, size_t universe, size_t* out_bytes);
+int b200ans_interp_decode(const uint32_t* src, uint32_t* out, size_t n, size_t universe, size_t* words_read);
+/* mapping rules (ans_fold.hpp:38-65,150-175; ans_msb.hpp:41-73,156-176) */
+uint32_t b200ans_fold_map(uint32_t fidelity, uint32_t x, uint32_t* nbytes);
+uint32_t b200ans_fold_unmap(uint32_t fidelity, uint32_t sym, uint32_t* nbytes);
+uint32_t b200ans_msb_map(uint32_t x, uint32_t* nbytes);
+uint32_t b200ans_msb_unmap(uint32_t sym, uint32_t* nbytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ANS_H */
