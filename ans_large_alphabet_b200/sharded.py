@@ -1,0 +1,87 @@
+"""Multi-GPU semi-static coding: one process per GPU, the input split into per-rank block ranges.
+
+SURVEY.md section 8(e): blocks are independent given the model, so every rank encodes / decodes its
+own contiguous shard with no data-path collective.  The single semi-static model comes from ONE
+all-reduce (sum) of the symbol histogram -- plus an all-reduce (max) of the largest value for
+the methods whose alphabet is the raw value range -- after which every rank runs the same
+deterministic host normalisation on the same global histogram and therefore builds the same
+model without a broadcast.
+
+torch / torch.distributed are plumbing here (device buffers, the NCCL communicator); all coding
+work goes through the C-ABI of include/b200ans.h.
+"""
+import numpy as np
+
+from ._capi import METHOD_FOLD, METHOD_INT, METHOD_MSB, METHOD_RFOLD
+
+
+def shard_range(n, block_syms, rank, world):
+    """Contiguous block range of `rank`: blocks [rank*nb/world, (rank+1)*nb/world)  ->  symbol range."""
+    nb = (n + block_syms - 1) // block_syms
+    b0 = rank * nb // world
+    b1 = (rank + 1) * nb // world
+    return min(n, b0 * block_syms), min(n, b1 * block_syms)
+
+
+def alphabet_bins(method, f, max_value=0):
+    if method == METHOD_INT:
+        return int(max_value) + 1
+    if method == METHOD_MSB:
+        return 1280
+    return 1 << (f + 9)
+
+
+def _all_reduce(t, op, group):
+    import torch.distributed as dist
+
+    if group is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=op, group=group)
+
+
+def global_histogram(codec, method, f, d_src, n, group=None, sync=None):
+    """Device histogram of this rank's shard, all-reduced over `group`. Returns host uint64 bins.
+
+    d_src: torch uint32/int32 CUDA tensor (16-byte aligned). `sync` is called between library
+    calls and torch ops (the codec may run on its own stream)."""
+    import torch
+    import torch.distributed as dist
+
+    dev = d_src.device
+    sync = sync or (lambda: torch.cuda.synchronize(dev))
+    world = dist.get_world_size(group) if (group is not None and dist.is_initialized()) else 1
+
+    def hist(m, nbins):
+        bins = torch.zeros(nbins, dtype=torch.int64, device=dev)
+        sync()
+        codec.histogram_device(m, f, d_src.data_ptr(), n, bins.data_ptr(), nbins)
+        sync()
+        if world > 1:
+            _all_reduce(bins, dist.ReduceOp.SUM, group)
+        return bins.cpu().numpy().view(np.uint64)
+
+    if method in (METHOD_INT, METHOD_RFOLD):
+        mx = torch.zeros(1, dtype=torch.int32, device=dev)
+        sync()
+        codec.max_device(d_src.data_ptr(), n, mx.data_ptr())
+        sync()
+        if world > 1:
+            _all_reduce(mx, dist.ReduceOp.MAX, group)
+        max_value = int(mx.item())
+        raw = hist(METHOD_INT, max_value + 1)
+        if method == METHOD_INT:
+            return raw
+        codec.rfold_prepare(f, raw)  # identical on every rank: same global histogram, same tie-break
+        return hist(METHOD_RFOLD, alphabet_bins(method, f))
+    return hist(method, alphabet_bins(method, f))
+
+
+def compress_shard(codec, method, f, d_src, n, d_dst, group=None, sync=None):
+    """Semi-static encode of this rank's shard with the GLOBAL model. Returns container bytes."""
+    bins = global_histogram(codec, method, f, d_src, n, group, sync)
+    codec.model_build(method, f, bins)
+    return codec.encode_device(d_dst.data_ptr(), d_dst.numel() * d_dst.element_size(), d_src.data_ptr(), n)
+
+
+def decompress_shard(codec, method, f, d_blob, nbytes, d_out, n):
+    """Decode needs no communication: each shard's container carries the (global) prelude."""
+    codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nbytes)

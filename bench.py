@@ -1,0 +1,466 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the b200ans hot path (see DESIGN.md "Measurement").
+
+One "step" = one semi-static ENCODE pass (histogram K1 -> host normalise -> block encoder K2 ->
+size scan + compaction) followed by one DECODE pass (prelude -> tables -> block decoder K3) over
+one batch of synthetic uint32 symbols.  metric = GB/s of uint32 input, i.e. (4n + 4n) bytes per
+step / step time (the mean over the encode and the decode pass); the two passes are also
+reported separately.
+
+  value  : inputs resident in HBM when the timed region starts (device entry points)
+  e2e    : the same step through the host-buffer entry points b200ans_compress /
+           b200ans_decompress (what methods.hpp-shaped adaptors call) with pinned HOST buffers,
+           H2D / D2H copies inside the timed region
+  --impl reference : the reference's own single-threaded CPU coder (oracle/_ref/libansref.so,
+           the unmodified headers; falls back to the C port) on a bounded sample per step
+
+python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c1|c3|fold1|...] [--impl ours|reference]
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+M_INT, M_FOLD, M_MSB, M_RFOLD = 0, 1, 2, 3
+
+# BASELINE.json configs (SURVEY.md section 8 shorthand) + the north_star's 2^30 target sizes.
+WORKLOADS = {
+    # name: (method, fidelity, generator, n, description)
+    "c1": (M_FOLD, 1, ("zipf", 1 << 20, 1.0, 0), 10_000_000, "C1 ANSfold-1, 1e7-symbol Zipf(1.0, 2^20)"),
+    "c2": (M_INT, 0, ("geom", 0.01), 100_000_000, "C2 ANS (ans_int), 1e8-symbol geometric(p=0.01)"),
+    "c3": (M_FOLD, 2, ("zipf", 1 << 24, 1.0, 0), 1_000_000_000, "C3 ANSfold-2, 1e9-symbol Zipf(1.0, 2^24)"),
+    "c3r": (M_RFOLD, 2, ("zipf", 1 << 24, 1.0, 0), 1_000_000_000, "C3 ANSrfold-2, 1e9-symbol Zipf(1.0, 2^24)"),
+    "c5": (M_FOLD, 1, ("zipf", 1 << 20, 1.2, 1), 1 << 30, "C5-style ANSfold-1, 2^30-symbol Zipf(1.2, 2^20)-1 per GPU"),
+    "fold1": (M_FOLD, 1, ("zipf", 1 << 20, 1.0, 0), 1 << 30, "ANSfold-1, 2^30-symbol Zipf(1.0, 2^20)"),
+    "fold2": (M_FOLD, 2, ("zipf", 1 << 20, 1.0, 0), 1 << 30, "ANSfold-2, 2^30-symbol Zipf(1.0, 2^20)"),
+    "msb": (M_MSB, 0, ("zipf", 1 << 20, 1.0, 0), 1 << 30, "ANSmsb, 2^30-symbol Zipf(1.0, 2^20)"),
+    "ans30": (M_INT, 0, ("geom", 0.01), 1 << 30, "ANS (ans_int), 2^30-symbol geometric(p=0.01)"),
+}
+DEFAULT_WORKLOAD = "c2"  # the single-GPU configuration BASELINE.json's metric is quoted on (configs[1])
+METRIC = "encode+decode GB/s of uint32 input"
+UNIT = "GB/s"
+
+
+def method_label(method, f):
+    return {M_INT: "ANS", M_MSB: "ANSmsb", M_FOLD: f"ANSfold-{f}", M_RFOLD: f"ANSrfold-{f}"}[method]
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic inputs
+# ------------------------------------------------------------------------------------------------
+def generate_device(gen, n, device, seed):
+    """Synthetic symbols generated on the GPU (torch is plumbing here): same distributions as
+    generate_inputs.cpp:97-117, different random stream."""
+    import torch
+
+    g = torch.Generator(device=device)
+    g.manual_seed(1234 + seed)
+    out = torch.empty(n, dtype=torch.int32, device=device)
+    chunk = 1 << 26
+    if gen[0] == "geom":
+        p = gen[1]
+        inv = 1.0 / math.log1p(-p)
+        for lo in range(0, n, chunk):
+            m = min(chunk, n - lo)
+            u = torch.rand(m, device=device, generator=g, dtype=torch.float64)
+            out[lo : lo + m] = torch.floor(torch.log1p(-u) * inv).to(torch.int32)
+    elif gen[0] == "zipf":
+        _, alphabet, q, sub = gen
+        w = 1.0 / torch.arange(1, alphabet + 1, device=device, dtype=torch.float64) ** q
+        cdf = torch.cumsum(w, 0)
+        cdf /= cdf[-1].clone()
+        for lo in range(0, n, chunk):
+            m = min(chunk, n - lo)
+            u = torch.rand(m, device=device, generator=g, dtype=torch.float64)
+            r = torch.searchsorted(cdf, u).clamp_(max=alphabet - 1)
+            out[lo : lo + m] = (r + (1 - sub)).to(torch.int32)
+    else:
+        raise KeyError(gen)
+    return out
+
+
+def generate_host(gen, n, seed):
+    from _inputs import geometric, zipf
+
+    if gen[0] == "geom":
+        return geometric(n, gen[1], seed)
+    _, alphabet, q, sub = gen
+    return zipf(n, alphabet, q, seed, offset=1 - sub)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (B200_PROFILING.md "clocks DURING the timed region")
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        for ts, line in self.rows:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                clk, mx = float(parts[1]), float(parts[2])
+            except ValueError:
+                continue
+            smax = mx
+            if t0 - 0.05 <= ts <= t1 + 0.15:
+                sm.append(clk)
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+        if not sm:  # timed region shorter than the sampling period: take everything we saw
+            for ts, line in self.rows:
+                parts = [p.strip() for p in line.split(",")]
+                try:
+                    sm.append(float(parts[1]))
+                except Exception:
+                    pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the reference's own coder on this box's host cores (test infrastructure, the one
+# place besides tests/ and smoke() that executes anything under oracle/)
+# ------------------------------------------------------------------------------------------------
+def cpu_codec():
+    from _libs import have_reference, oracle, reference
+
+    if have_reference():
+        return reference(), "reference"
+    return oracle(), "port"
+
+
+def cpu_time_sample(method, f, sample, runs):
+    codec, kind = cpu_codec()
+    enc_ns, dec_ns, nbytes = codec.time(method, f, sample, runs)
+    gbs = 8.0 * sample.size / (enc_ns + dec_ns)  # (4n + 4n) bytes / (t_enc + t_dec); bytes/ns == GB/s
+    return {
+        "value": gbs, "unit": UNIT, "cores": 1, "kind": kind,
+        "sample": f"first {sample.size} symbols of the workload, whole-stream {method_label(method, f)}, min of {runs} runs",
+        "encode_gbs": 4.0 * sample.size / enc_ns, "decode_gbs": 4.0 * sample.size / dec_ns,
+        "encode_ns_per_symbol": enc_ns / sample.size, "decode_ns_per_symbol": dec_ns / sample.size,
+        "bits_per_symbol": 8.0 * nbytes / sample.size, "host_cores_total": os.cpu_count(),
+        "note": "the reference is single-threaded (no threading anywhere in its sources): 1 of %d cores" % (os.cpu_count() or 0),
+    }
+
+
+def run_reference_arm(args, wl):
+    """--impl reference: rank 0 only; each step = one encode + decode of a bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    method, f, gen, n, desc = wl
+    per_step = min(n, 20_000_000 if method != M_INT or gen[0] == "geom" else 5_000_000)
+    sample = generate_host(gen, per_step, seed=0)
+    codec, kind = cpu_codec()
+    for _ in range(args.warmup):
+        codec.time(method, f, sample[: per_step // 8], 1)
+    t0 = time.time()
+    enc = dec = 0.0
+    nbytes = 0
+    for _ in range(args.steps):
+        e, d, nbytes = codec.time(method, f, sample, 1)
+        enc += e
+        dec += d
+    wall = time.time() - t0
+    gbs = 8.0 * per_step * args.steps / (enc + dec)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gbs, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": (enc + dec) / args.steps / 1e6, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": desc, "method": method_label(method, f), "symbols_per_step": per_step,
+                   "note": "bounded sample of the workload per step; CPU throughput does not depend on n"},
+        "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": 1, "kind": kind,
+                         "sample": f"{per_step} symbols per step x {args.steps} steps, whole-stream encode + decode",
+                         "encode_gbs": 4.0 * per_step * args.steps / enc, "decode_gbs": 4.0 * per_step * args.steps / dec,
+                         "bits_per_symbol": 8.0 * nbytes / per_step, "host_cores_total": os.cpu_count()},
+        "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": wall,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args, wl):
+    import torch
+    import torch.distributed as dist
+
+    import ans_large_alphabet_b200 as P
+    from ans_large_alphabet_b200 import sharded
+
+    method, f, gen, n, desc = wl
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- b200ans has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+
+    if args.symbols:
+        n = args.symbols
+    stream = torch.cuda.Stream(device=dev)
+    codec = P.Codec(device=local, block_syms=args.block_syms, stream=stream.cuda_stream)
+    # weak scaling: every rank holds a full-size shard of the (N x larger) job
+    d_in = generate_device(gen, n, dev, seed=rank)
+    bound = codec.bound(method, n)
+    d_blob = torch.empty((bound + 15) // 16 * 16, dtype=torch.uint8, device=dev)
+    d_out = torch.empty(n, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize(dev)
+
+    def sync():
+        stream.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier(group)
+        torch.cuda.synchronize(dev)
+
+    kern = {"histogram": 0.0, "encode": 0.0, "compact": 0.0, "decode": 0.0, "model_host": 0.0}
+
+    def device_step(acc):
+        with torch.cuda.stream(stream):
+            if world == 1:
+                nb = codec.compress_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
+            else:
+                nb = sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
+            s = codec.stats()
+            enc_model = s.ms_model
+            codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nb)
+            s2 = codec.stats()
+        if acc is not None:
+            acc["histogram"] += s.ms_histogram
+            acc["encode"] += s.ms_encode
+            acc["compact"] += s.ms_compact
+            acc["decode"] += s2.ms_decode
+            acc["model_host"] += enc_model + s2.ms_model
+        return nb, s2
+
+    # ---- device-resident timing -------------------------------------------------------------
+    for _ in range(args.warmup):
+        device_step(None)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    launches0 = codec.stats().launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # separate encode / decode split, measured with events on the codec's stream
+    barrier()
+    t_wall0 = time.time()
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+    nb = 0
+    for _ in range(args.steps):
+        nb, st = device_step(kern)
+    with torch.cuda.stream(stream):
+        ev1.record(stream)
+    barrier()
+    t_wall1 = time.time()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = codec.stats().launches - launches0
+    clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
+    ok = bool(torch.equal(d_in, d_out))
+    st = codec.stats()
+    payload_bytes, total_bytes, n_blocks = st.payload_bytes, nb, st.n_blocks
+    frame, nsyms, prelude_bytes = st.frame_size, st.n_symbols_model, st.prelude_bytes
+
+    # encode-only / decode-only split (events around each pass)
+    enc_ms = dec_ms = 0.0
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    reps = max(1, min(args.steps, 5))
+    for _ in range(reps):
+        barrier()
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            if world == 1:
+                nb2 = codec.compress_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
+            else:
+                nb2 = sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
+            e1.record(stream)
+            codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nb2)
+            e2.record(stream)
+        stream.synchronize()
+        enc_ms += e0.elapsed_time(e1)
+        dec_ms += e1.elapsed_time(e2)
+    enc_ms /= reps
+    dec_ms /= reps
+
+    # ---- end to end: pinned host buffers through the host entry points ------------------------
+    h_in = torch.empty(n, dtype=torch.int32).pin_memory()
+    h_in.copy_(d_in)
+    h_blob = torch.empty(d_blob.numel(), dtype=torch.uint8).pin_memory()
+    h_out = torch.empty(n, dtype=torch.int32).pin_memory()
+    torch.cuda.synchronize(dev)
+
+    def e2e_step():
+        if world == 1:
+            nbh = codec.compress_ptr(method, f, h_blob.data_ptr(), h_blob.numel(), h_in.data_ptr(), n)
+            codec.decompress_ptr(method, f, h_out.data_ptr(), n, h_blob.data_ptr(), nbh)
+            return nbh
+        with torch.cuda.stream(stream):
+            d_in.copy_(h_in, non_blocking=True)
+            nbh = sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
+            h_blob[:nbh].copy_(d_blob[:nbh], non_blocking=True)
+            stream.synchronize()
+            d_blob[:nbh].copy_(h_blob[:nbh], non_blocking=True)
+            codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nbh)
+            h_out.copy_(d_out, non_blocking=True)
+            stream.synchronize()
+        return nbh
+
+    for _ in range(min(args.warmup, 2)):
+        e2e_step()
+    e2e_steps = max(1, min(args.steps, 5))
+    barrier()
+    tw0 = time.perf_counter()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        f0.record(stream)
+    for _ in range(e2e_steps):
+        nbh = e2e_step()
+    with torch.cuda.stream(stream):
+        f1.record(stream)
+    barrier()
+    e2e_ms = max(f0.elapsed_time(f1), (time.perf_counter() - tw0) * 1e3 * 0.0)  # device clock
+    e2e_ok = bool(torch.equal(h_in, h_out))
+
+    # ---- reduce over ranks: MAX time ----------------------------------------------------------
+    t = torch.tensor([ms_total, e2e_ms, enc_ms, dec_ms], dtype=torch.float64, device=dev)
+    okt = torch.tensor([int(ok and e2e_ok)], dtype=torch.int32, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN, group=group)
+    ms_total, e2e_ms, enc_ms, dec_ms = (float(x) for x in t.tolist())
+    all_ok = bool(okt.item())
+
+    if rank == 0:
+        ms_step = ms_total / args.steps
+        gb_step = 8.0 * n * world / 1e9
+        value = gb_step / (ms_step / 1e3)
+        c = payload_bytes / n
+        peak, peak_src = measured_peak()
+        per = {k: v / args.steps for k, v in kern.items()}
+        alg = {"histogram": 4.0 * n, "encode": (4.0 + c) * n, "compact": 2.0 * c * n, "decode": (4.0 + c) * n}
+        kernels = {}
+        for k in ("histogram", "encode", "compact", "decode"):
+            if per[k] > 0:
+                a = alg[k] / (per[k] * 1e6)
+                kernels[k] = {"ms": per[k], "algorithmic_bytes": alg[k], "achieved_gbs": a, "frac": a / peak}
+        dom = max(("encode", "decode", "histogram", "compact"), key=lambda k: per[k])
+        roofline = {"bound": "hbm", "kernel": dom + "_kernel", "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
+                    "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_symbol": alg[dom] / n, "ms_per_launch": per[dom]}
+        # CPU baseline on a bounded sample of the same workload (rank 0, N = 1 only)
+        cpu = None
+        bps_sample = None
+        if world == 1 and not args.no_cpu:
+            ns = min(n, args.cpu_sample)
+            sample = d_in[:ns].cpu().numpy().view(np.uint32)
+            cpu = cpu_time_sample(method, f, sample, runs=2)
+            sb = codec.compress(method, f, sample)
+            bps_sample = 8.0 * sb.size / ns
+            cpu["ours_bits_per_symbol_same_sample"] = bps_sample
+            cpu["size_overhead_vs_reference_pct"] = 100.0 * (bps_sample / cpu["bits_per_symbol"] - 1.0)
+        h2d = 4 * n + nbh
+        d2h = nbh + 4 * n
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": desc, "method": method_label(method, f), "symbols_per_gpu": n,
+                       "block_syms": args.block_syms, "n_blocks_per_gpu": n_blocks,
+                       "l2": "inputs (%.0f MB per GPU) larger than the 126 MB L2; no flush" % (4.0 * n / 1e6),
+                       "model": "semi-static, global histogram" + (" via NCCL all-reduce" if world > 1 else ""),
+                       "frame_size": frame, "model_symbols": nsyms},
+            "encode_gbs": 4.0 * n * world / (enc_ms * 1e6), "decode_gbs": 4.0 * n * world / (dec_ms * 1e6),
+            "encode_ms": enc_ms, "decode_ms": dec_ms,
+            "bits_per_symbol": 8.0 * total_bytes / n, "payload_bytes_per_symbol": c, "prelude_bytes": prelude_bytes,
+            "roundtrip_ok": all_ok,
+            "roofline": roofline, "kernels": kernels, "host_model_ms_per_step": per["model_host"],
+            "cpu_baseline": cpu,
+            "e2e": {"value": gb_step / (e2e_ms / e2e_steps / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+                    "api": "b200ans_compress + b200ans_decompress (host buffers, pinned)" if world == 1
+                    else "pinned H2D + staged device API + D2H per rank"},
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+        print(json.dumps(line))
+    codec.close()
+    if world > 1:
+        dist.destroy_process_group()
+    if not all_ok:
+        raise SystemExit("bench.py: round trip FAILED")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--symbols", type=int, default=0, help="override the workload's symbol count (per GPU)")
+    ap.add_argument("--block-syms", type=int, default=8192)
+    ap.add_argument("--cpu-sample", type=int, default=100_000_000)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()
