@@ -38,6 +38,26 @@ def _all_reduce(t, op, group):
         dist.all_reduce(t, op=op, group=group)
 
 
+def reduce_histogram(bins, group=None):
+    """ONE all-reduce (sum) of a rank-local histogram (torch int64 tensor, any device the group's
+    backend supports).  Returns the global histogram as host uint64.  Counts are < 2^63, so the
+    int64 transport is exact."""
+    import torch.distributed as dist
+
+    _all_reduce(bins, dist.ReduceOp.SUM, group)
+    return bins.cpu().numpy().view(np.uint64)
+
+
+def reduce_max(value, device, group=None):
+    """all-reduce (max) of the largest raw value (the alphabet size of ANS / ANSrfold pass 1)"""
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([int(value)], dtype=torch.int64, device=device)
+    _all_reduce(t, dist.ReduceOp.MAX, group)
+    return int(t.item())
+
+
 def global_histogram(codec, method, f, d_src, n, group=None, sync=None):
     """Device histogram of this rank's shard, all-reduced over `group`. Returns host uint64 bins.
 
@@ -55,18 +75,14 @@ def global_histogram(codec, method, f, d_src, n, group=None, sync=None):
         sync()
         codec.histogram_device(m, f, d_src.data_ptr(), n, bins.data_ptr(), nbins)
         sync()
-        if world > 1:
-            _all_reduce(bins, dist.ReduceOp.SUM, group)
-        return bins.cpu().numpy().view(np.uint64)
+        return reduce_histogram(bins, group if world > 1 else None)
 
     if method in (METHOD_INT, METHOD_RFOLD):
         mx = torch.zeros(1, dtype=torch.int32, device=dev)
         sync()
         codec.max_device(d_src.data_ptr(), n, mx.data_ptr())
         sync()
-        if world > 1:
-            _all_reduce(mx, dist.ReduceOp.MAX, group)
-        max_value = int(mx.item())
+        max_value = reduce_max(int(mx.item()), dev, group if world > 1 else None)
         raw = hist(METHOD_INT, max_value + 1)
         if method == METHOD_INT:
             return raw

@@ -1,0 +1,88 @@
+"""not gpu: the N > 1 host logic on CPU with world_size-2 gloo.  Each rank histograms its own
+block-aligned shard, ONE all-reduce gives the global histogram, every rank normalises it with the
+product's host adjust_freqs -> the same model everywhere (no broadcast), equal to the reference's
+single-process model (golden vector)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, HERE)
+    import torch
+    import torch.distributed as dist
+
+    import ans_large_alphabet_b200 as P
+    from ans_large_alphabet_b200 import sharded
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    host = P.host_api()
+    res = {}
+    for name in ("fold1_zipf20", "msb_zipf20", "int_geom"):
+        g = np.load(os.path.join(HERE, "golden", name + ".npz"))
+        method, f, data = int(g["method"]), int(g["fidelity"]), g["data"]
+        bs = 1024
+        lo, hi = sharded.shard_range(data.size, bs, rank, world)
+        mine = data[lo:hi]
+        if method == P.METHOD_INT:
+            mx = sharded.reduce_max(int(mine.max()) if mine.size else 0, "cpu", dist.group.WORLD)
+            local = np.bincount(mine, minlength=mx + 1).astype(np.int64)
+        else:
+            nb = sharded.alphabet_bins(method, f)
+            local = np.zeros(nb, dtype=np.int64)
+            uniq, cnt = np.unique(mine, return_counts=True)
+            for v, c in zip(uniq, cnt):
+                s = host.msb_map(v)[0] if method == P.METHOD_MSB else host.fold_map(f, v)[0]
+                local[s] += c
+        bins = sharded.reduce_histogram(torch.from_numpy(local), dist.group.WORLD)
+        largest = int(np.nonzero(bins)[0][-1])
+        nfreqs = host.adjust_freqs(bins, largest, method != P.METHOD_INT)
+        res[name + "_nfreqs"] = nfreqs
+        res[name + "_range"] = np.array([lo, hi])
+        res[name + "_total"] = np.array([int(bins.sum())])
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), **res)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_shard_ranges_partition_the_blocks():
+    from ans_large_alphabet_b200.sharded import shard_range
+
+    for n, bs, world in [(10_000_000, 8192, 8), (8192 * 5 + 3, 8192, 4), (100, 8192, 2), (1 << 30, 8192, 8), (70_001, 128, 3)]:
+        prev = 0
+        for r in range(world):
+            lo, hi = shard_range(n, bs, r, world)
+            assert lo == prev and lo % bs == 0 and (hi % bs == 0 or hi == n)
+            prev = hi
+        assert prev == n
+
+
+def test_two_rank_global_model_equals_reference(tmp_path):
+    import torch.multiprocessing as mp
+
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = np.load(tmp_path / "rank0.npz"), np.load(tmp_path / "rank1.npz")
+    for name in ("fold1_zipf20", "msb_zipf20", "int_geom"):
+        g = np.load(os.path.join(HERE, "golden", name + ".npz"))
+        assert np.array_equal(r0[name + "_nfreqs"], r1[name + "_nfreqs"]), "ranks disagree on the model"
+        assert np.array_equal(r0[name + "_nfreqs"], g["nfreqs"]), "global model differs from the reference's"
+        assert int(r0[name + "_total"][0]) == g["data"].size
+        assert r0[name + "_range"][1] == r1[name + "_range"][0] and r1[name + "_range"][1] == g["data"].size
