@@ -12,6 +12,9 @@ from ._capi import (  # noqa: F401
     METHOD_INT,
     METHOD_MSB,
     METHOD_RFOLD,
+    PATH_AUTO,
+    PATH_GROUP,
+    PATH_LPB,
     Stats,
     build_library,
     host_api,

@@ -6,6 +6,7 @@ import subprocess
 import numpy as np
 
 METHOD_INT, METHOD_FOLD, METHOD_MSB, METHOD_RFOLD = 0, 1, 2, 3
+PATH_AUTO, PATH_GROUP, PATH_LPB = 0, 1, 2
 HEADER_BYTES = 64
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -38,6 +39,7 @@ SIGNATURES = {
     "b200ans_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p]),
     "b200ans_destroy": (None, [C.c_void_p]),
     "b200ans_set_block_syms": (C.c_int, [C.c_void_p, C.c_uint32]),
+    "b200ans_set_kernel_path": (C.c_int, [C.c_void_p, C.c_int]),
     "b200ans_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "b200ans_last_error": (C.c_char_p, [C.c_void_p]),
     "b200ans_strerror": (C.c_char_p, [C.c_int]),
@@ -215,6 +217,10 @@ class Codec:
     def set_block_syms(self, bs):
         self._check(self.lib.b200ans_set_block_syms(self.h, bs))
         self.block_syms = bs
+
+    def set_kernel_path(self, path):
+        """0 = auto, 1 = group kernels (4 lanes per block), 2 = lane-per-block kernels"""
+        self._check(self.lib.b200ans_set_kernel_path(self.h, path))
 
     def stats(self):
         s = Stats()

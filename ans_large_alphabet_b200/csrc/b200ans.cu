@@ -5,6 +5,8 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cmath>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -14,6 +16,7 @@
 #include "../host/model.hpp"
 #include "../host/prelude.hpp"
 #include "kernels.cuh"
+#include "lpb_kernels.cuh"
 
 using namespace b200ans;
 
@@ -77,6 +80,8 @@ struct b200ans_ctx {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
+    int kernel_path = B200ANS_PATH_AUTO;
+    uint32_t max_nfreq = 0; // largest normalised frequency of the encoder model
     std::string err;
     b200ans_stats stats {};
     cudaEvent_t ev[8] {};
@@ -172,6 +177,15 @@ float elapsed(cudaEvent_t a, cudaEvent_t b)
     return ms;
 }
 
+// smallest double >= 1/f (kernels.cuh ans_push / lpb_kernels.cuh ans_push52 rely on the direction)
+double reciprocal_up(uint32_t f)
+{
+    double r = 1.0 / double(f);
+    if (std::fma(r, double(f), -1.0) < 0.0) // r * f < 1 exactly: one ulp up
+        r = std::nextafter(r, 2.0);
+    return r;
+}
+
 double now_ms()
 {
     using namespace std::chrono;
@@ -246,6 +260,16 @@ extern "C" int b200ans_set_block_syms(b200ans_ctx* c, uint32_t block_syms)
     if (block_syms != 0 && (block_syms % 128 != 0 || block_syms > (1u << 24)))
         return c->fail(B200ANS_E_ARG, "block_syms must be 0 or a multiple of 128 up to 2^24");
     c->block_syms = block_syms;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_set_kernel_path(b200ans_ctx* c, int path)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (path != B200ANS_PATH_AUTO && path != B200ANS_PATH_GROUP && path != B200ANS_PATH_LPB)
+        return c->fail(B200ANS_E_ARG, "unknown kernel path");
+    c->kernel_path = path;
     return B200ANS_OK;
 }
 
@@ -402,21 +426,36 @@ template <int METHOD>
 int launch_histogram(b200ans_ctx* c, uint32_t f, const uint32_t* d_src, size_t n, uint64_t* d_bins, size_t nbins,
     uint32_t* d_max)
 {
-    const bool smem = nbins <= kHistSmemBins;
-    const size_t smem_bytes = smem ? nbins * sizeof(uint32_t) : 0;
-    const size_t vec = (n >> 2) + 1;
-    int grid = int(std::min<size_t>((vec + kHistThreads - 1) / kHistThreads, size_t(c->num_sms) * 4));
-    grid = std::max(grid, 1);
-    const uint32_t* mapping = c->mapping.as<uint32_t>();
-    auto* bins = reinterpret_cast<unsigned long long*>(d_bins);
-    if (smem) {
-        auto k = histogram_kernel<METHOD, true>;
-        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kHistSmemBins * 4)));
-        k<<<grid, kHistThreads, smem_bytes, c->stream>>>(d_src, n, f, mapping, c->n_values, bins, uint32_t(nbins), d_max);
-    } else {
-        auto k = histogram_kernel<METHOD, false>;
-        k<<<grid, kHistThreads, 0, c->stream>>>(d_src, n, f, mapping, c->n_values, bins, uint32_t(nbins), d_max);
+    HistArgs a {};
+    a.in = d_src;
+    a.n = n;
+    a.fidelity = f;
+    a.mapping = c->mapping.as<uint32_t>();
+    a.n_values = c->n_values;
+    a.bins = reinterpret_cast<unsigned long long*>(d_bins);
+    a.nbins = uint32_t(nbins);
+    a.max_value = d_max;
+    // whole alphabet in shared memory when it fits, else only the hot head of the raw alphabet
+    a.smem_bins = nbins <= kHistSmemWords ? uint32_t(nbins) : kHistHeadBins;
+    uint32_t replicas = 8;
+    while (replicas > 1 && replicas * (a.smem_bins + 1) > kHistSmemWords)
+        replicas >>= 1;
+    a.replicas = replicas;
+    a.stride = (a.smem_bins & 31u) == 0 ? a.smem_bins + 1 : a.smem_bins | 1u; // one bank of skew per replica
+    if ((a.stride & 31u) == 0)
+        a.stride += 1;
+    const size_t smem_bytes = size_t(a.replicas) * a.stride * sizeof(uint32_t);
+    auto k = histogram_kernel<METHOD>;
+    CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kHistSmemWords * 4 + 1024)));
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kHistThreads, smem_bytes) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError();
+        per_sm = 1;
     }
+    const size_t vec = (n >> 2) + 1;
+    int grid = int(std::min<size_t>((vec + kHistThreads - 1) / kHistThreads, size_t(c->num_sms) * per_sm));
+    grid = std::max(grid, 1);
+    k<<<grid, kHistThreads, smem_bytes, c->stream>>>(a);
     c->stats.launches++;
     CU(c, cudaGetLastError());
     return B200ANS_OK;
@@ -583,15 +622,17 @@ extern "C" int b200ans_model_build(b200ans_ctx* c, int method, uint32_t f, const
     ans_serialize_interp(c->nfreqs, size_t(frame), p);
     c->prelude.resize(size_t(p - c->prelude.data()));
 
-    // encoder table: {freq, base = exclusive prefix sum, reciprocal rounded towards zero}
+    // encoder table: {freq, base = exclusive prefix sum, smallest double >= 1/freq}
     std::vector<EncEntry> table(c->nfreqs.size());
+    c->max_nfreq = 0;
     uint64_t base = 0;
     for (size_t s = 0; s < table.size(); s++) {
         const uint32_t fr = c->nfreqs[s];
         table[s].freq = fr;
         table[s].base = uint32_t(base);
-        table[s].rcp = fr ? (1.0 / double(fr)) * (1.0 - 0x1p-50) : 0.0;
+        table[s].rcp = fr ? reciprocal_up(fr) : 0.0;
         base += fr;
+        c->max_nfreq = std::max(c->max_nfreq, fr);
     }
     CU(c, c->enc_table.reserve(table.size() * sizeof(EncEntry)));
     CU(c, cudaMemcpyAsync(c->enc_table.p, table.data(), table.size() * sizeof(EncEntry), cudaMemcpyHostToDevice, c->stream));
@@ -790,6 +831,51 @@ template <int METHOD> int launch_encode_t(b200ans_ctx* c, const EncArgs& a)
     return B200ANS_OK;
 }
 
+// Lane-per-block kernels need 32 blocks per warp: worth it once that still fills the GPU.
+bool use_lpb(const b200ans_ctx* c, uint32_t n_blocks)
+{
+    if (c->kernel_path == B200ANS_PATH_GROUP)
+        return false;
+    if (c->kernel_path == B200ANS_PATH_LPB)
+        return true;
+    return n_blocks >= uint32_t(c->num_sms) * 32u * 8u; // >= 8 LPB warps per SM
+}
+
+template <int METHOD> int launch_lpb_encode_t(b200ans_ctx* c, const EncArgs& a)
+{
+    const size_t rows = size_t(kLpbEncWarps) * 32 * (kLpbInRow + kLpbOutRow);
+    const uint32_t n_tasks = (a.n_blocks + 31) / 32;
+    const bool smem_table = a.n_entries <= uint32_t(kLpbEncMaxSmemEntries);
+    if (smem_table) {
+        auto k = lpb_encode_kernel<METHOD, true>;
+        const size_t smem = rows + size_t(a.n_entries) * sizeof(EncEntry);
+        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        const int grid = persistent_grid(c, k, kLpbEncWarps * 32, smem, n_tasks, kLpbEncWarps);
+        k<<<grid, kLpbEncWarps * 32, smem, c->stream>>>(a);
+    } else {
+        auto k = lpb_encode_kernel<METHOD, false>;
+        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(rows)));
+        const int grid = persistent_grid(c, k, kLpbEncWarps * 32, rows, n_tasks, kLpbEncWarps);
+        k<<<grid, kLpbEncWarps * 32, rows, c->stream>>>(a);
+    }
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
+template <int METHOD, int TABLE> int launch_lpb_decode_tt(b200ans_ctx* c, const DecArgs& a, size_t table_bytes)
+{
+    auto k = lpb_decode_kernel<METHOD, TABLE>;
+    const size_t smem = table_bytes + size_t(kLpbDecWarps) * 32 * kLpbDecOutRow;
+    CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    const uint32_t n_tasks = (a.n_blocks + 31) / 32;
+    const int grid = persistent_grid(c, k, kLpbDecWarps * 32, smem, n_tasks, kLpbDecWarps);
+    k<<<grid, kLpbDecWarps * 32, smem, c->stream>>>(a);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
 // encode d_src into scratch slots + block_bytes using the current encoder model
 int launch_encode(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t block_syms, uint32_t n_blocks,
     uint8_t* d_scratch, size_t stride, uint32_t* d_block_bytes)
@@ -809,7 +895,16 @@ int launch_encode(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t bloc
     a.stride = stride;
     a.block_bytes = d_block_bytes;
     a.error_flag = c->d_err();
+    a.fast_div = c->max_nfreq < 65536u ? 1u : 0u;
     CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
+    if (use_lpb(c, n_blocks)) {
+        switch (c->enc_method) {
+        case METHOD_INT: return launch_lpb_encode_t<METHOD_INT>(c, a);
+        case METHOD_FOLD: return launch_lpb_encode_t<METHOD_FOLD>(c, a);
+        case METHOD_MSB: return launch_lpb_encode_t<METHOD_MSB>(c, a);
+        case METHOD_RFOLD: return launch_lpb_encode_t<METHOD_RFOLD>(c, a);
+        }
+    }
     switch (c->enc_method) {
     case METHOD_INT: return launch_encode_t<METHOD_INT>(c, a);
     case METHOD_FOLD: return launch_encode_t<METHOD_FOLD>(c, a);
@@ -851,6 +946,30 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     a.n_syms = c->dec_n_syms;
     a.sym_bytes = c->dec_sym_bytes;
     const size_t frame = size_t(1) << c->dec_log2_frame;
+    if (use_lpb(c, n_blocks)) {
+        const size_t lrows = size_t(kLpbDecWarps) * 32 * kLpbDecOutRow;
+        const size_t lbudget = c->max_smem > lrows + 1024 ? c->max_smem - lrows - 1024 : 0;
+        if (c->dec_method == METHOD_INT) {
+            const size_t tb = align_up(align_up(frame * c->dec_sym_bytes, 16) + size_t(c->dec_n_syms) * sizeof(SymEntry), 16);
+            if (tb <= lbudget)
+                return launch_lpb_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
+            return launch_lpb_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);
+        }
+        const size_t tb = align_up(frame * sizeof(DecEntry), 16);
+        const bool smem = tb <= std::min<size_t>(lbudget, size_t(128) << 10);
+        switch (c->dec_method) {
+        case METHOD_FOLD:
+            return smem ? launch_lpb_decode_tt<METHOD_FOLD, DEC_FOLD_SMEM>(c, a, tb)
+                        : launch_lpb_decode_tt<METHOD_FOLD, DEC_FOLD_GLOBAL>(c, a, 0);
+        case METHOD_MSB:
+            return smem ? launch_lpb_decode_tt<METHOD_MSB, DEC_FOLD_SMEM>(c, a, tb)
+                        : launch_lpb_decode_tt<METHOD_MSB, DEC_FOLD_GLOBAL>(c, a, 0);
+        case METHOD_RFOLD:
+            return smem ? launch_lpb_decode_tt<METHOD_RFOLD, DEC_FOLD_SMEM>(c, a, tb)
+                        : launch_lpb_decode_tt<METHOD_RFOLD, DEC_FOLD_GLOBAL>(c, a, 0);
+        }
+        return c->fail(B200ANS_E_STATE, "decode: no model");
+    }
     const size_t rows = size_t(kDecWarps) * 8 * kDecRowBytes;
     const size_t budget = c->max_smem > rows + 1024 ? c->max_smem - rows - 1024 : 0;
     if (c->dec_method == METHOD_INT) {

@@ -63,6 +63,7 @@ struct EncArgs {
     uint64_t stride;
     uint32_t* block_bytes;   // out: payload bytes of block b
     uint32_t* error_flag;    // set to non-zero if a symbol had no model entry
+    uint32_t fast_div;       // every frequency < 2^16: states stay below 2^52 (lpb_kernels.cuh ans_push52)
 };
 
 struct DecArgs {
@@ -119,82 +120,93 @@ __device__ __forceinline__ uint64_t ans_push(uint64_t x, uint32_t freq, uint32_t
 // K1: histogram (+ running maximum of the raw values)
 // ------------------------------------------------------------------------------------------
 // Replaces the counting loops of ans_fold.hpp:74-78, ans_msb.hpp:81-85, ans_int.hpp:42-49 and
-// ans_reorder_fold.hpp:75-84,110-115.  Folded alphabets (<= kHistSmemBins bins) are counted in
-// shared memory with warp-aggregated atomics: lanes holding the same bin elect one leader
-// (__match_any_sync) that adds the population count, so a skewed distribution does not
-// serialise on its hottest bin; each CTA then merges its non-zero bins into the global 64-bit
-// histogram.  Raw alphabets larger than that go straight to global 64-bit atomics.
+// ans_reorder_fold.hpp:75-84,110-115.
+//
+// Shared-memory counting with lane-striped replicas: a CTA keeps R copies of the (folded)
+// alphabet and lane l counts into copy l % R, each copy shifted by one bank.  Lanes of a warp
+// that hold the SAME symbol therefore aggregate over R different banks instead of serialising
+// on one address (a Zipf head symbol owns 2..12 lanes of every warp), and lanes with different
+// symbols conflict no more than random bank traffic does.  (A __match_any_sync leader election
+// was measured first: 54 issue cycles per warp-level count, 10 % of the HBM roofline.)
+// Each CTA then adds its non-zero bins, summed over the replicas, to the global 64-bit bins.
+//
+// HEAD > 0 (raw alphabets that do not fit): values below HEAD are counted in shared memory as
+// above (the hot head of a skewed distribution), the rest goes straight to global atomics.
 
-constexpr uint32_t kHistSmemBins = 16384;
 constexpr int kHistThreads = 512;
+constexpr uint32_t kHistSmemWords = 12288; // 48 KiB of counters per CTA
+constexpr uint32_t kHistHeadBins = 8192;   // privatised head of a large raw alphabet
 
-template <int METHOD, bool SMEM>
-__global__ void __launch_bounds__(kHistThreads) histogram_kernel(const uint32_t* __restrict__ in, uint64_t n,
-    uint32_t fidelity, const uint32_t* __restrict__ mapping, uint32_t n_values,
-    unsigned long long* __restrict__ bins, uint32_t nbins, uint32_t* __restrict__ max_value)
+struct HistArgs {
+    const uint32_t* in;
+    uint64_t n;
+    uint32_t fidelity;
+    const uint32_t* mapping; // RFOLD: value -> reordered value
+    uint32_t n_values;
+    unsigned long long* bins;
+    uint32_t nbins;
+    uint32_t smem_bins; // bins counted in shared memory (== nbins, or the head of a raw alphabet)
+    uint32_t replicas;  // power of two
+    uint32_t stride;    // words between replicas (odd multiple: +1 bank per replica)
+    uint32_t* max_value;
+};
+
+template <int METHOD>
+__global__ void __launch_bounds__(kHistThreads) histogram_kernel(const HistArgs a)
 {
     extern __shared__ uint32_t s_bins[];
-    if (SMEM) {
-        for (uint32_t i = threadIdx.x; i < nbins; i += blockDim.x)
-            s_bins[i] = 0;
-        __syncthreads();
-    }
+    const uint32_t total_words = a.replicas * a.stride;
+    for (uint32_t i = threadIdx.x; i < total_words; i += blockDim.x)
+        s_bins[i] = 0;
+    __syncthreads();
+    uint32_t* mine = s_bins + (lane_id() & (a.replicas - 1u)) * a.stride;
+    const uint32_t smem_bins = a.smem_bins, nbins = a.nbins, f = a.fidelity;
     uint32_t local_max = 0;
-    auto count = [&](uint32_t v, bool valid) {
+    auto count = [&](uint32_t v) {
         uint32_t k;
         uint32_t mv = v;
         if (METHOD == METHOD_RFOLD)
-            mv = (valid && v < n_values) ? __ldg(mapping + v) : 0u;
-        const uint32_t bin = map_value<METHOD>(mv, fidelity, k);
-        if (SMEM) {
-            // warp-aggregated shared-memory atomic
-            const uint32_t active = __ballot_sync(0xffffffffu, valid);
-            if (valid) {
-                const uint32_t peers = __match_any_sync(active, bin);
-                if ((peers & ((1u << lane_id()) - 1u)) == 0 && bin < nbins)
-                    atomicAdd(&s_bins[bin], uint32_t(__popc(peers)));
-            }
-        } else if (valid && bin < nbins) {
-            atomicAdd(&bins[bin], 1ull);
-        }
-        if (valid)
-            local_max = max(local_max, v);
+            mv = v < a.n_values ? __ldg(a.mapping + v) : 0u;
+        const uint32_t bin = map_value<METHOD>(mv, f, k);
+        if (bin < smem_bins)
+            atomicAdd(mine + bin, 1u);
+        else if (bin < nbins)
+            atomicAdd(a.bins + bin, 1ull);
+        local_max = max(local_max, v);
     };
 
-    // 128-bit loads over the 16-byte aligned body, scalar tail
-    const uint64_t n4 = n >> 2;
-    const uint4* in4 = reinterpret_cast<const uint4*>(in);
+    // 128-bit loads over the 16-byte aligned body, two in flight per thread; scalar tail
+    const uint64_t n4 = a.n >> 2;
+    const uint4* in4 = reinterpret_cast<const uint4*>(a.in);
     const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
-    // every lane of a warp runs the same number of iterations (match/ballot need convergence)
-    const uint64_t iters = (n4 + stride - 1) / stride;
     uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    for (uint64_t it = 0; it < iters; it++, i += stride) {
-        const bool valid = i < n4;
-        uint4 q = make_uint4(0, 0, 0, 0);
-        if (valid)
-            q = __ldg(in4 + i);
-        count(q.x, valid);
-        count(q.y, valid);
-        count(q.z, valid);
-        count(q.w, valid);
+    for (; i + stride < n4; i += 2 * stride) {
+        const uint4 q0 = __ldg(in4 + i);
+        const uint4 q1 = __ldg(in4 + i + stride);
+        count(q0.x), count(q0.y), count(q0.z), count(q0.w);
+        count(q1.x), count(q1.y), count(q1.z), count(q1.w);
     }
-    if (blockIdx.x == 0 && threadIdx.x < 32) {
+    if (i < n4) {
+        const uint4 q0 = __ldg(in4 + i);
+        count(q0.x), count(q0.y), count(q0.z), count(q0.w);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 3) {
         const uint64_t t = (n4 << 2) + threadIdx.x;
-        const bool valid = t < n;
-        count(valid ? in[t] : 0u, valid);
+        if (t < a.n)
+            count(a.in[t]);
     }
     // maximum of the raw values
     for (int o = 16; o > 0; o >>= 1)
         local_max = max(local_max, __shfl_xor_sync(0xffffffffu, local_max, o));
     if (lane_id() == 0 && local_max != 0)
-        atomicMax(max_value, local_max);
-    if (SMEM) {
-        __syncthreads();
-        for (uint32_t b = threadIdx.x; b < nbins; b += blockDim.x) {
-            const uint32_t c = s_bins[b];
-            if (c)
-                atomicAdd(&bins[b], (unsigned long long)c);
-        }
+        atomicMax(a.max_value, local_max);
+    __syncthreads();
+    for (uint32_t b = threadIdx.x; b < smem_bins; b += blockDim.x) {
+        uint32_t c = 0;
+        for (uint32_t r = 0; r < a.replicas; r++)
+            c += s_bins[r * a.stride + b];
+        if (c)
+            atomicAdd(a.bins + b, (unsigned long long)c);
     }
 }
 

@@ -1,0 +1,456 @@
+// b200ans device code (sm_100a): "lane per block" (LPB) encoder / decoder -- the large-input path.
+//
+// kernels.cuh runs one block on 4 lanes (lane per rANS chain) and pays for it with three
+// shuffles per symbol, byte-granular shared-memory stores and one 4-byte load per symbol.  When
+// the input has at least a few thousand blocks there is enough parallelism to give every lane
+// a whole block instead: the lane carries all four interleaved states of ans_fold.hpp:250-278 in
+// registers, the byte cursor is a plain register (no scan), the emitted bytes are packed into
+// 32-bit words in a register accumulator, and the four chains of a quad give the lane four
+// independent dependency chains to overlap.  A warp works on 32 consecutive blocks.
+//
+// Byte-identity with the reference coder run on each block is unchanged: the emission order inside
+// a block is exactly the serial order (tail symbols on state 0, then quads backwards with the
+// symbol at index 4t+g on state 3-g; per symbol raw low bytes first, then the 32-bit
+// renormalisation word: ans_fold.hpp:100-112,257-278).
+#pragma once
+
+#include "kernels.cuh"
+
+namespace b200ans {
+
+// ------------------------------------------------------------------------------------------
+// exact state update
+// ------------------------------------------------------------------------------------------
+// x -> (x / f) * M + x % f + base  (ans_fold.hpp:111) for x < 2^52 (true whenever every f < 2^16,
+// because x < f * 2^36 after the renormalisation test).  `rcp` is the smallest double >= 1/f.
+// x is exact as a double; fma_rz(x, rcp, 2^52) = 2^52 + floor(x * rcp) because the sum lies in
+// [2^52, 2^53) where doubles are the integers; and floor(x * rcp) = floor(x / f) because
+// x * (rcp - 1/f) < 2^52 * 2^-52 / f = 1/f while frac(x / f) <= 1 - 1/f.  No fix-up needed.
+__device__ __forceinline__ uint64_t ans_push52(uint32_t x_lo, uint32_t x_hi, uint32_t f, uint32_t base, double rcp,
+    uint32_t log2_frame)
+{
+    const double two52 = 4503599627370496.0;
+    const double xd = __hiloint2double(int(x_hi | 0x43300000u), int(x_lo)) - two52;
+    const double t = __fma_rz(xd, rcp, two52);
+    const uint32_t q_lo = uint32_t(__double2loint(t));
+    const uint32_t q_hi = uint32_t(__double2hiint(t)) & 0xFFFFFu;
+    const uint32_t r = x_lo - q_lo * f; // < f
+    const uint64_t q = (uint64_t(q_hi) << 32) | q_lo;
+    return (q << log2_frame) + uint64_t(r + base);
+}
+
+// ------------------------------------------------------------------------------------------
+// K2-LPB: encoder
+// ------------------------------------------------------------------------------------------
+constexpr int kLpbEncWarps = 8;
+constexpr int kLpbTileQuads = 4;                         // quads (of 4 symbols) per lane between drains
+constexpr int kLpbInRow = kLpbTileQuads * 16 + 16;        // 80 B: 5 x 16 (odd) -> conflict-free 128-bit row reads
+constexpr int kLpbOutRow = 176;                           // 12 carried + 28 * 16 symbols... see static_assert
+static_assert(12 + 28 * kLpbTileQuads + 36 + 4 <= kLpbOutRow && (kLpbOutRow / 16) % 2 == 1, "output row too small");
+constexpr int kLpbEncMaxSmemEntries = 6144;
+
+// Word-granular emitter: bytes are collected little-endian in `acc` (sh = 8 * pending bytes,
+// pending < 4) and complete 32-bit words go to the lane's row in shared memory.
+struct LpbEmitter {
+    uint32_t acc;
+    uint32_t sh;  // 0, 8, 16, 24
+    uint32_t wp;  // shared-memory byte address of the next word of the row
+    __device__ __forceinline__ void put_bytes(uint32_t v, uint32_t k) // k in 0..3 low bytes of v
+    {
+        const uint32_t vm = v & ((1u << (8u * k)) - 1u);
+        const uint32_t t = acc | (vm << sh);
+        const uint32_t hi = __funnelshift_l(vm, 0u, sh); // vm >> (32 - sh), 0 when sh == 0
+        const uint32_t nsh = sh + 8u * k;
+        const bool full = nsh >= 32u;
+        if (full) {
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(wp), "r"(t) : "memory");
+            wp += 4u;
+        }
+        acc = full ? hi : t;
+        sh = nsh & 31u;
+    }
+    __device__ __forceinline__ void put_word(uint32_t w, bool on)
+    {
+        const uint32_t t = acc | (w << sh);
+        if (on) {
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(wp), "r"(t) : "memory");
+            wp += 4u;
+            acc = __funnelshift_l(w, 0u, sh); // w >> (32 - sh), 0 when sh == 0
+        }
+    }
+};
+
+template <int METHOD, bool TABLE_SMEM>
+__global__ void __launch_bounds__(kLpbEncWarps * 32) lpb_encode_kernel(const EncArgs a)
+{
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    EncEntry* s_table = reinterpret_cast<EncEntry*>(smem_raw);
+    uint8_t* s_rows = smem_raw + (TABLE_SMEM ? size_t(a.n_entries) * sizeof(EncEntry) : 0);
+    if (TABLE_SMEM) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.table);
+        uint4* dst = reinterpret_cast<uint4*>(s_table);
+        for (uint32_t i = threadIdx.x; i < a.n_entries; i += blockDim.x)
+            dst[i] = __ldg(src + i);
+        __syncthreads();
+    }
+    const uint32_t lane = lane_id();
+    const uint32_t warp = threadIdx.x >> 5;
+    uint8_t* in_rows = s_rows + size_t(warp) * 32 * (kLpbInRow + kLpbOutRow);
+    uint8_t* out_rows = in_rows + 32 * kLpbInRow;
+    uint8_t* my_in = in_rows + lane * kLpbInRow;
+    uint8_t* my_out = out_rows + lane * kLpbOutRow;
+    const uint32_t my_out_s = uint32_t(__cvta_generic_to_shared(my_out));
+    const uint4* table4 = reinterpret_cast<const uint4*>(TABLE_SMEM ? s_table : a.table);
+    const uint32_t log2_frame = a.log2_frame;
+    const uint32_t f = a.fidelity;
+    const bool fast = a.fast_div != 0u; // every frequency < 2^16
+    const uint64_t lower = uint64_t(kAnsK) << log2_frame;
+    const uint32_t B = a.block_syms;
+
+    const uint32_t n_tasks = (a.n_blocks + 31u) >> 5;
+    for (uint32_t task = blockIdx.x * kLpbEncWarps + warp; task < n_tasks; task += gridDim.x * kLpbEncWarps) {
+        const uint32_t blk0 = task * 32u;
+        const uint32_t blk = blk0 + lane;
+        const bool have_block = blk < a.n_blocks;
+        const uint64_t first = uint64_t(blk) * B;
+        const uint32_t nb = have_block ? uint32_t(min(uint64_t(B), a.n - first)) : 0u;
+        const uint32_t tail = nb & 3u;
+        const uint32_t quads = nb >> 2;
+        const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
+        uint8_t* dst = a.scratch + uint64_t(blk) * a.stride;
+
+        uint64_t x0 = lower, x1 = lower, x2 = lower, x3 = lower; // initial_state() (ans_fold.hpp:113)
+        LpbEmitter em;
+        em.acc = 0;
+        em.sh = 0;
+        em.wp = my_out_s;
+        uint32_t flushed = 0;
+        uint32_t bad = 0;
+
+        auto encode_one = [&](uint32_t v, uint64_t& x, bool active) {
+            if (METHOD == METHOD_RFOLD) {
+                if (v >= a.n_values) { // value the model has never seen
+                    bad |= uint32_t(active);
+                    v = 0;
+                }
+                v = __ldg(a.mapping + v);
+            }
+            uint32_t k;
+            uint32_t sym = map_value<METHOD>(v, f, k);
+            if (sym >= a.n_entries) {
+                bad |= uint32_t(active);
+                sym = 0;
+            }
+            const uint4 raw = TABLE_SMEM ? table4[sym] : __ldg(table4 + sym);
+            const uint32_t fr = raw.x, base = raw.y;
+            const double rcp = __hiloint2double(int(raw.w), int(raw.z));
+            bad |= uint32_t(active && fr == 0u);
+            const uint32_t x_lo = uint32_t(x), x_hi = uint32_t(x >> 32);
+            const bool renorm = active && ((x_hi >> 4) >= fr); // state >= freq * K * 2^32 (ans_fold.hpp:105)
+            if (METHOD != METHOD_INT)
+                em.put_bytes(v, active ? k : 0u); // raw low bytes first (ans_fold.hpp:59-63)
+            em.put_word(x_lo, renorm);           // then the renormalisation word (ans_fold.hpp:106-109)
+            const uint32_t y_lo = renorm ? x_hi : x_lo;
+            const uint32_t y_hi = renorm ? 0u : x_hi;
+            uint64_t nx;
+            if (fast)
+                nx = ans_push52(y_lo, y_hi, fr, base, rcp, log2_frame);
+            else
+                nx = ans_push((uint64_t(y_hi) << 32) | y_lo, fr, base, rcp, log2_frame);
+            if (active)
+                x = nx;
+        };
+
+        // tail symbols (only the very last block of the input has any): state 0 (ans_fold.hpp:257-261)
+        if (__any_sync(0xffffffffu, tail != 0u)) {
+            for (uint32_t s = 0; s < 3u; s++) {
+                const bool active = s < tail;
+                const uint32_t v = active ? __ldg(a.in + first + (nb - 1u - s)) : 0u;
+                encode_one(v, x0, active);
+            }
+        }
+
+        for (uint32_t q0 = 0; q0 < max_quads; q0 += kLpbTileQuads) {
+            // ---- stage the next 16 symbols of each of the warp's 32 blocks (coalesced 64-byte pieces) ----
+            __syncwarp();
+#pragma unroll
+            for (int it = 0; it < 4; it++) {
+                const uint32_t row = uint32_t(it) * 8u + (lane >> 2);
+                const uint32_t chunk = lane & 3u;
+                const uint32_t rblk = blk0 + row;
+                if (rblk < a.n_blocks) {
+                    const uint64_t rfirst = uint64_t(rblk) * B;
+                    const uint32_t rnb = uint32_t(min(uint64_t(B), a.n - rfirst));
+                    const uint32_t rquads = rnb >> 2;
+                    // quad index (ascending in memory) held by this chunk
+                    const int64_t qi = int64_t(rquads) - int64_t(q0) - int64_t(kLpbTileQuads) + int64_t(chunk);
+                    if (qi >= 0) {
+                        const uint4 val = __ldg(reinterpret_cast<const uint4*>(a.in + rfirst) + qi);
+                        *reinterpret_cast<uint4*>(in_rows + row * kLpbInRow + chunk * 16u) = val;
+                    }
+                }
+            }
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < kLpbTileQuads; j++) {
+                const bool active = (q0 + uint32_t(j)) < quads;
+                const uint4 v4 = *reinterpret_cast<const uint4*>(my_in + (kLpbTileQuads - 1 - j) * 16);
+                // walking backwards: index 4t+3 (state 0) first ... index 4t (state 3) last (ans_fold.hpp:262-271)
+                encode_one(v4.w, x0, active);
+                encode_one(v4.z, x1, active);
+                encode_one(v4.y, x2, active);
+                encode_one(v4.x, x3, active);
+            }
+            // ---- drain whole 16-byte chunks of the lane's row, carry the rest to the front ----
+            {
+                const uint32_t fill = em.wp - my_out_s; // bytes in the row (multiple of 4)
+                const uint32_t chunks = fill >> 4;
+                const uint32_t max_chunks = __reduce_max_sync(0xffffffffu, chunks);
+                const uint4* rv = reinterpret_cast<const uint4*>(my_out);
+                uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
+                for (uint32_t ci = 0; ci < max_chunks; ci++)
+                    if (ci < chunks)
+                        gv[ci] = rv[ci];
+                if (chunks != 0u) {
+                    const uint4 carry = rv[chunks];
+                    *reinterpret_cast<uint4*>(my_out) = carry;
+                }
+                flushed += chunks << 4;
+                em.wp = my_out_s + (fill & 15u);
+            }
+        }
+
+        // flush_state x4 in chain order 0..3 (ans_fold.hpp:115-120, 275-278)
+        {
+            const uint64_t s0 = x0 - lower, s1 = x1 - lower, s2 = x2 - lower, s3 = x3 - lower;
+            em.put_word(uint32_t(s0), have_block), em.put_word(uint32_t(s0 >> 32), have_block);
+            em.put_word(uint32_t(s1), have_block), em.put_word(uint32_t(s1 >> 32), have_block);
+            em.put_word(uint32_t(s2), have_block), em.put_word(uint32_t(s2 >> 32), have_block);
+            em.put_word(uint32_t(s3), have_block), em.put_word(uint32_t(s3 >> 32), have_block);
+            uint32_t fill = em.wp - my_out_s;
+            const uint32_t total = flushed + fill + (em.sh >> 3);
+            // last partial word, then zero padding up to the next 16-byte boundary (deterministic container)
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(em.wp), "r"(em.acc) : "memory");
+            fill += 4u;
+            while (fill & 15u) {
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(my_out_s + fill), "r"(0u) : "memory");
+                fill += 4u;
+            }
+            const uint32_t chunks = (total - flushed + 15u) >> 4;
+            const uint32_t max_chunks = __reduce_max_sync(0xffffffffu, have_block ? chunks : 0u);
+            const uint4* rv = reinterpret_cast<const uint4*>(my_out);
+            uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
+            for (uint32_t ci = 0; ci < max_chunks; ci++)
+                if (have_block && ci < chunks)
+                    gv[ci] = rv[ci];
+            if (have_block)
+                a.block_bytes[blk] = total;
+        }
+        if (bad)
+            *a.error_flag = 1u;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3-LPB: decoder
+// ------------------------------------------------------------------------------------------
+// The lane walks its block's payload downwards from the four states.  The three aligned 32-bit
+// words that cover the 8 bytes below the cursor live in registers (t0 = word holding the byte
+// just below the cursor, t1, t2 = the two words below it); a symbol consumes at most 7 bytes,
+// i.e. moves the cursor across at most two word boundaries, so at most two predicated 4-byte
+// loads (L1-resident: every lane streams its own block) refill the window.  Decoded symbols are
+// staged per warp in shared memory and written out in coalesced 64-byte pieces.
+constexpr int kLpbDecWarps = 8;
+constexpr int kLpbDecOutRow = kLpbTileQuads * 16 + 16; // 80 B
+
+template <int METHOD, int TABLE>
+__global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const DecArgs a)
+{
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    constexpr bool kInt = (METHOD == METHOD_INT);
+    constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM);
+    const uint32_t frame = 1u << a.log2_frame;
+    size_t table_bytes = 0;
+    if (kSmem) {
+        if (kInt)
+            table_bytes = ((size_t(frame) * a.sym_bytes + 15) & ~size_t(15)) + size_t(a.n_syms) * sizeof(SymEntry);
+        else
+            table_bytes = size_t(frame) * sizeof(DecEntry);
+        table_bytes = (table_bytes + 15) & ~size_t(15);
+    }
+    uint8_t* s_rows = smem_raw + table_bytes;
+    const DecEntry* slots = a.slots;
+    const void* s2s = a.slot_to_sym;
+    const SymEntry* syms = a.syms;
+    if (kSmem) {
+        if (kInt) {
+            const size_t s2s_bytes = (size_t(frame) * a.sym_bytes + 15) & ~size_t(15);
+            const uint4* src = reinterpret_cast<const uint4*>(a.slot_to_sym);
+            uint4* dst = reinterpret_cast<uint4*>(smem_raw);
+            for (size_t i = threadIdx.x; i < s2s_bytes / 16; i += blockDim.x)
+                dst[i] = __ldg(src + i);
+            const uint2* src2 = reinterpret_cast<const uint2*>(a.syms);
+            uint2* dst2 = reinterpret_cast<uint2*>(smem_raw + s2s_bytes);
+            for (size_t i = threadIdx.x; i < a.n_syms; i += blockDim.x)
+                dst2[i] = __ldg(src2 + i);
+            s2s = smem_raw;
+            syms = reinterpret_cast<const SymEntry*>(smem_raw + s2s_bytes);
+        } else {
+            const uint2* src = reinterpret_cast<const uint2*>(a.slots);
+            uint2* dst = reinterpret_cast<uint2*>(smem_raw);
+            for (size_t i = threadIdx.x; i < frame; i += blockDim.x)
+                dst[i] = __ldg(src + i);
+            slots = reinterpret_cast<const DecEntry*>(smem_raw);
+        }
+        __syncthreads();
+    }
+
+    const uint32_t lane = lane_id();
+    const uint32_t warp = threadIdx.x >> 5;
+    uint8_t* out_rows = s_rows + size_t(warp) * 32 * kLpbDecOutRow;
+    uint8_t* my_out = out_rows + lane * kLpbDecOutRow;
+    const uint32_t log2_frame = a.log2_frame;
+    const uint32_t frame_mask = frame - 1u;
+    const uint64_t lower = uint64_t(kAnsK) << log2_frame;
+    const uint32_t rfold_bias = (METHOD == METHOD_RFOLD) ? (1u << (a.fidelity + 7)) : 0u; // ans_reorder_fold.hpp:301
+    const uint32_t B = a.block_syms;
+
+    const uint32_t n_tasks = (a.n_blocks + 31u) >> 5;
+    for (uint32_t task = blockIdx.x * kLpbDecWarps + warp; task < n_tasks; task += gridDim.x * kLpbDecWarps) {
+        const uint32_t blk0 = task * 32u;
+        const uint32_t blk = blk0 + lane;
+        const bool have_block = blk < a.n_blocks;
+        const uint64_t first = uint64_t(blk) * B;
+        const uint32_t nb = have_block ? uint32_t(min(uint64_t(B), a.n - first)) : 0u;
+        const uint32_t tail = nb & 3u;
+        const uint32_t quads = nb >> 2;
+        const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
+
+        // word-aligned view of the payload; `pos` counts bytes from words[0], one past the next byte to consume
+        const uint8_t* pay = a.payload + (have_block ? a.offsets[blk] : 0);
+        const uint32_t delta = uint32_t(reinterpret_cast<uintptr_t>(pay) & 3u);
+        const uint32_t* words = reinterpret_cast<const uint32_t*>(pay - delta);
+        const uint32_t size = have_block ? a.block_bytes[blk] : 32u;
+        auto word_at = [&](int32_t i) -> uint32_t { return (have_block && i >= 0) ? __ldg(words + i) : 0u; };
+
+        // init_state x4: state c sits at payload + size - 32 + 8c (ans_fold.hpp:291-295)
+        uint64_t x0, x1, x2, x3;
+        {
+            const uint32_t sp = delta + size - 32u;
+            const int32_t w = int32_t(sp >> 2);
+            const uint32_t sh = (sp & 3u) * 8u;
+            uint32_t t[9];
+#pragma unroll
+            for (int i = 0; i < 9; i++)
+                t[i] = (i < 8 || sh != 0u) ? word_at(w + i) : 0u;
+            uint32_t u[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                u[i] = __funnelshift_r(t[i], t[i + 1], sh);
+            x0 = ((uint64_t(u[1]) << 32) | u[0]) + lower;
+            x1 = ((uint64_t(u[3]) << 32) | u[2]) + lower;
+            x2 = ((uint64_t(u[5]) << 32) | u[4]) + lower;
+            x3 = ((uint64_t(u[7]) << 32) | u[6]) + lower;
+        }
+        uint32_t pos = delta + size - 32u;
+        int32_t wi = int32_t(pos + 3u) / 4 - 1; // index of the word that holds byte pos-1 (-1 when pos == 0)
+        uint32_t t0 = word_at(wi), t1 = word_at(wi - 1), t2 = word_at(wi - 2);
+
+        auto decode_one = [&](uint64_t& x, bool active) -> uint32_t {
+            const uint32_t slot = uint32_t(x) & frame_mask;
+            uint32_t freq, offset, mapped, k;
+            if (kInt) {
+                const uint32_t sym = (a.sym_bytes == 2) ? uint32_t(reinterpret_cast<const uint16_t*>(s2s)[slot])
+                                                        : reinterpret_cast<const uint32_t*>(s2s)[slot];
+                const SymEntry se = syms[sym];
+                freq = se.freq;
+                offset = slot - se.base;
+                mapped = sym;
+                k = 0;
+            } else {
+                const uint2 e = *reinterpret_cast<const uint2*>(slots + slot);
+                freq = e.x & 0xFFFFu;
+                offset = e.x >> 16;
+                mapped = e.y & 0x3FFFFFFFu;
+                k = e.y >> 30;
+            }
+            uint64_t nx = uint64_t(freq) * (x >> log2_frame) + offset;
+            const bool renorm = active && nx < lower;
+            // bytes [pos-8, pos): hi = the 4 bytes just below the cursor, lo = the 4 below those
+            const uint32_t sh = ((pos + 3u) & 3u) * 8u + 8u; // 8, 16, 24, 32
+            const uint32_t win_hi = __funnelshift_rc(t1, t0, sh);
+            const uint32_t win_lo = __funnelshift_rc(t2, t1, sh);
+            if (renorm) // renormalisation word first (ans_fold.hpp:221-224)
+                nx = (nx << kRadixLog2) | uint64_t(win_hi);
+            uint32_t value = mapped;
+            uint32_t c = renorm ? 4u : 0u;
+            if (!kInt) { // then k raw low bytes (ans_fold.hpp:135-147)
+                const uint32_t exc_src = renorm ? win_lo : win_hi;
+                value += __funnelshift_rc(exc_src, 0u, 32u - 8u * k);
+                c += k;
+            }
+            if (active) {
+                x = nx;
+                pos -= c;
+                // slide the word window: the cursor crossed 0, 1 or 2 word boundaries
+                const int32_t nwi = int32_t(pos + 3u) / 4 - 1;
+                if (nwi < wi) {
+                    t0 = t1;
+                    t1 = t2;
+                    t2 = word_at(wi - 3);
+                    wi -= 1;
+                }
+                if (!kInt && nwi < wi) {
+                    t0 = t1;
+                    t1 = t2;
+                    t2 = word_at(wi - 3);
+                    wi -= 1;
+                }
+            }
+            return value - rfold_bias;
+        };
+
+        for (uint32_t q0 = 0; q0 < max_quads; q0 += kLpbTileQuads) {
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < kLpbTileQuads; j++) {
+                const bool active = (q0 + uint32_t(j)) < quads;
+                uint4 o;
+                // index 4t+g is decoded by state 3-g (ans_fold.hpp:300-305)
+                o.x = decode_one(x3, active);
+                o.y = decode_one(x2, active);
+                o.z = decode_one(x1, active);
+                o.w = decode_one(x0, active);
+                *reinterpret_cast<uint4*>(my_out + j * 16) = o;
+            }
+            __syncwarp();
+            // coalesced write-out: 8 rows x 64 bytes per instruction
+#pragma unroll
+            for (int it = 0; it < 4; it++) {
+                const uint32_t row = uint32_t(it) * 8u + (lane >> 2);
+                const uint32_t chunk = lane & 3u;
+                const uint32_t rblk = blk0 + row;
+                if (rblk < a.n_blocks) {
+                    const uint64_t rfirst = uint64_t(rblk) * B;
+                    const uint32_t rnb = uint32_t(min(uint64_t(B), a.n - rfirst));
+                    const uint32_t qi = q0 + chunk;
+                    if (qi < (rnb >> 2)) {
+                        const uint4 val = *reinterpret_cast<const uint4*>(out_rows + row * kLpbDecOutRow + chunk * 16u);
+                        reinterpret_cast<uint4*>(a.out + rfirst)[qi] = val;
+                    }
+                }
+            }
+        }
+        // tail symbols on state 0 (ans_fold.hpp:306-310); only the last block of the input has any
+        if (__any_sync(0xffffffffu, tail != 0u)) {
+            for (uint32_t s = 0; s < 3u; s++) {
+                const bool active = s < tail;
+                const uint32_t v = decode_one(x0, active);
+                if (active)
+                    a.out[first + 4u * quads + s] = v;
+            }
+        }
+    }
+}
+
+} // namespace b200ans

@@ -58,6 +58,11 @@ extern "C" {
 #define B200ANS_METHOD_MSB 2   /* "ANSmsb"     ans_msb.hpp                                    */
 #define B200ANS_METHOD_RFOLD 3 /* "ANSrfold-f" ans_reorder_fold.hpp                           */
 
+/* kernel families (both produce identical bytes; AUTO picks by block count) */
+#define B200ANS_PATH_AUTO 0
+#define B200ANS_PATH_GROUP 1 /* 4 lanes per block, one lane per rANS chain: small / medium inputs */
+#define B200ANS_PATH_LPB 2   /* one lane per block, four chains per lane: large inputs          */
+
 #define B200ANS_DEFAULT_BLOCK_SYMS 8192u
 #define B200ANS_HEADER_BYTES 64u
 #define B200ANS_MAGIC 0x4E413242u /* "B2AN" */
@@ -87,6 +92,7 @@ typedef struct b200ans_stats {
 int b200ans_create(b200ans_ctx** out, int device, void* stream);
 void b200ans_destroy(b200ans_ctx* ctx);
 int b200ans_set_block_syms(b200ans_ctx* ctx, uint32_t block_syms); /* 0 or a multiple of 128 */
+int b200ans_set_kernel_path(b200ans_ctx* ctx, int path); /* B200ANS_PATH_* ; default AUTO */
 int b200ans_get_stats(const b200ans_ctx* ctx, b200ans_stats* out);
 const char* b200ans_last_error(const b200ans_ctx* ctx);
 const char* b200ans_strerror(int code);

@@ -13,6 +13,15 @@ from _libs import M_FOLD, M_INT, M_MSB, M_RFOLD, have_reference, oracle, referen
 
 pytestmark = pytest.mark.gpu
 
+PATHS = [pytest.param(1, id="group"), pytest.param(2, id="lpb")]  # B200ANS_PATH_GROUP / _LPB: identical bytes
+
+
+@pytest.fixture(autouse=True)
+def _auto_path(codec):
+    yield
+    codec.set_kernel_path(0)
+
+
 METHODS = [(M_FOLD, 1), (M_FOLD, 2), (M_MSB, 0), (M_INT, 0), (M_RFOLD, 1), (M_RFOLD, 2), (M_FOLD, 5), (M_FOLD, 8)]
 
 
@@ -50,11 +59,13 @@ def check_container(codec, method, f, data, blob, block_syms):
     return c
 
 
+@pytest.mark.parametrize("path", PATHS)
 @pytest.mark.parametrize("kind", ["zipf20", "geom", "wide", "u8", "zipf12s"])
 @pytest.mark.parametrize("method,f", METHODS)
-def test_blocks_byte_identical_and_roundtrip(codec, method, f, kind):
+def test_blocks_byte_identical_and_roundtrip(codec, method, f, kind, path):
     if not ok_for(method, f, kind):
         pytest.skip("outside the reference's valid domain")
+    codec.set_kernel_path(path)
     n = 200_003  # not a multiple of 4 nor of the block size
     data = _inputs.make(kind, n, seed=7)
     codec.set_block_syms(8192)
@@ -66,7 +77,9 @@ def test_blocks_byte_identical_and_roundtrip(codec, method, f, kind):
 
 @pytest.mark.parametrize("method,f", [(M_FOLD, 1), (M_INT, 0), (M_MSB, 0), (M_RFOLD, 2)])
 @pytest.mark.parametrize("block_syms", [128, 1024, 4096, 65536])
-def test_block_sizes(codec, method, f, block_syms):
+@pytest.mark.parametrize("path", PATHS)
+def test_block_sizes(codec, method, f, block_syms, path):
+    codec.set_kernel_path(path)
     data = _inputs.make("zipf16", 70_001, seed=3)
     codec.set_block_syms(block_syms)
     blob = codec.compress(method, f, data).copy()
@@ -77,7 +90,9 @@ def test_block_sizes(codec, method, f, block_syms):
 
 @pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 7, 8, 127, 128, 129, 8191, 8192, 8193, 8195, 16384 + 2])
 @pytest.mark.parametrize("method,f", [(M_FOLD, 1), (M_INT, 0), (M_MSB, 0)])
-def test_ragged_lengths(codec, method, f, n):
+@pytest.mark.parametrize("path", PATHS)
+def test_ragged_lengths(codec, method, f, n, path):
+    codec.set_kernel_path(path)
     base = _inputs.make("zipf16", 20_000, seed=11)
     data = base[:n].copy()
     if method == M_INT and np.unique(data).size < 2:
@@ -90,10 +105,12 @@ def test_ragged_lengths(codec, method, f, n):
 
 @pytest.mark.parametrize("kind", ["zipf20", "geom", "wide"])
 @pytest.mark.parametrize("method,f", METHODS)
-def test_reference_wire_format(codec, method, f, kind):
+@pytest.mark.parametrize("path", PATHS)
+def test_reference_wire_format(codec, method, f, kind, path):
     """block_syms = 0: output == ans_X_compress(), and reference streams decode."""
     if not ok_for(method, f, kind):
         pytest.skip("outside the reference's valid domain")
+    codec.set_kernel_path(path)
     n = 30_001
     data = _inputs.make(kind, n, seed=5)
     want = cpu().compress(method, f, data)
@@ -144,7 +161,9 @@ def test_domain_errors(codec):
 
 
 @pytest.mark.parametrize("method,f,kind", [(M_FOLD, 1, "zipf20"), (M_FOLD, 2, "zipf20"), (M_INT, 0, "geom"), (M_MSB, 0, "zipf20")])
-def test_large_roundtrip_properties(codec, method, f, kind):
+@pytest.mark.parametrize("path", PATHS)
+def test_large_roundtrip_properties(codec, method, f, kind, path):
+    codec.set_kernel_path(path)
     """2^25 symbols: round trip, size = sum of parts, bits/symbol within 1 % of the whole-stream CPU coder,
     and sampled blocks byte-identical."""
     n = 1 << 25
