@@ -87,7 +87,7 @@ struct b200ans_ctx {
     cudaEvent_t ev[8] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_s2s, dec_syms, io_in, io_out;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out;
     // `small` layout: [0] u32 max, [1] u32 error flag, [2..] pad; totals (2 x u64) at byte 16
     uint32_t* d_max() { return small.as<uint32_t>(); }
     uint32_t* d_err() { return small.as<uint32_t>() + 1; }
@@ -114,7 +114,8 @@ struct b200ans_ctx {
     uint32_t dec_f = 0;
     uint32_t dec_log2_frame = 0;
     uint32_t dec_n_syms = 0;
-    uint32_t dec_sym_bytes = 0;
+    uint32_t dec_n_present = 0;
+    uint32_t dec_cnt_bytes = 2;
 
     int fail(int code, const std::string& what)
     {
@@ -243,7 +244,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_s2s, &c->dec_syms, &c->io_in, &c->io_out })
+             &c->dec_slots, &c->dec_bits, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out })
         b->release();
     for (auto& e : c->ev)
         if (e)
@@ -738,28 +739,37 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
     const uint32_t lg = uint32_t(63 - __builtin_clzll(frame));
 
     if (method == METHOD_INT) {
-        const uint32_t sym_bytes = nfreqs.size() <= 65536 ? 2 : 4;
-        std::vector<SymEntry> syms(nfreqs.size());
-        std::vector<uint8_t> s2s(align_up(size_t(frame) * sym_bytes, 16), 0);
+        // rank/select index over the frame (kernels.cuh RankEntry)
+        const size_t words = (size_t(frame) + 31) / 32;
+        std::vector<uint32_t> bits(align_up(words, 4), 0);
+        std::vector<RankEntry> ent;
         uint64_t base = 0;
         for (size_t s = 0; s < nfreqs.size(); s++) {
-            syms[s].freq = nfreqs[s];
-            syms[s].base = uint32_t(base);
-            if (sym_bytes == 2) {
-                uint16_t* t = reinterpret_cast<uint16_t*>(s2s.data()) + base;
-                std::fill(t, t + nfreqs[s], uint16_t(s));
-            } else {
-                uint32_t* t = reinterpret_cast<uint32_t*>(s2s.data()) + base;
-                std::fill(t, t + nfreqs[s], uint32_t(s));
-            }
+            if (!nfreqs[s])
+                continue;
+            bits[base >> 5] |= 1u << (base & 31);
+            ent.push_back(RankEntry { uint32_t(base), nfreqs[s], uint32_t(s), 0u });
             base += nfreqs[s];
         }
-        CU(c, c->dec_s2s.reserve(s2s.size()));
-        CU(c, c->dec_syms.reserve(syms.size() * sizeof(SymEntry)));
-        CU(c, cudaMemcpyAsync(c->dec_s2s.p, s2s.data(), s2s.size(), cudaMemcpyHostToDevice, c->stream));
-        CU(c, cudaMemcpyAsync(c->dec_syms.p, syms.data(), syms.size() * sizeof(SymEntry), cudaMemcpyHostToDevice, c->stream));
+        const uint32_t cnt_bytes = ent.size() < 65536 ? 2 : 4;
+        std::vector<uint8_t> cnt(align_up(words * cnt_bytes, 16), 0);
+        uint32_t run = 0;
+        for (size_t w = 0; w < words; w++) {
+            if (cnt_bytes == 2)
+                reinterpret_cast<uint16_t*>(cnt.data())[w] = uint16_t(run);
+            else
+                reinterpret_cast<uint32_t*>(cnt.data())[w] = run;
+            run += uint32_t(__builtin_popcount(bits[w]));
+        }
+        CU(c, c->dec_bits.reserve(bits.size() * 4));
+        CU(c, c->dec_cnt.reserve(cnt.size()));
+        CU(c, c->dec_ent.reserve(ent.size() * sizeof(RankEntry)));
+        CU(c, cudaMemcpyAsync(c->dec_bits.p, bits.data(), bits.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(c->dec_cnt.p, cnt.data(), cnt.size(), cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(c->dec_ent.p, ent.data(), ent.size() * sizeof(RankEntry), cudaMemcpyHostToDevice, c->stream));
         CU(c, cudaStreamSynchronize(c->stream));
-        c->dec_sym_bytes = sym_bytes;
+        c->dec_cnt_bytes = cnt_bytes;
+        c->dec_n_present = uint32_t(ent.size());
     } else {
         std::vector<DecEntry> slots(frame);
         uint64_t base = 0;
@@ -866,7 +876,7 @@ template <int METHOD> int launch_lpb_encode_t(b200ans_ctx* c, const EncArgs& a)
 template <int METHOD, int TABLE> int launch_lpb_decode_tt(b200ans_ctx* c, const DecArgs& a, size_t table_bytes)
 {
     auto k = lpb_decode_kernel<METHOD, TABLE>;
-    const size_t smem = table_bytes + size_t(kLpbDecWarps) * 32 * kLpbDecOutRow;
+    const size_t smem = align_up(table_bytes, 16) + 128 + size_t(kLpbDecWarps) * 32 * (kLpbRing + kLpbDecOutRow);
     CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     const uint32_t n_tasks = (a.n_blocks + 31) / 32;
     const int grid = persistent_grid(c, k, kLpbDecWarps * 32, smem, n_tasks, kLpbDecWarps);
@@ -941,17 +951,18 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     a.log2_frame = c->dec_log2_frame;
     a.fidelity = c->dec_f;
     a.slots = c->dec_slots.as<DecEntry>();
-    a.slot_to_sym = c->dec_s2s.p;
-    a.syms = c->dec_syms.as<SymEntry>();
-    a.n_syms = c->dec_n_syms;
-    a.sym_bytes = c->dec_sym_bytes;
+    a.rank_bits = c->dec_bits.as<uint32_t>();
+    a.rank_cnt = c->dec_cnt.p;
+    a.rank_ent = c->dec_ent.as<RankEntry>();
+    a.n_present = c->dec_n_present;
+    a.cnt_bytes = c->dec_cnt_bytes;
     const size_t frame = size_t(1) << c->dec_log2_frame;
     if (use_lpb(c, n_blocks)) {
-        const size_t lrows = size_t(kLpbDecWarps) * 32 * kLpbDecOutRow;
+        const size_t lrows = size_t(kLpbDecWarps) * 32 * (kLpbRing + kLpbDecOutRow) + 128;
         const size_t lbudget = c->max_smem > lrows + 1024 ? c->max_smem - lrows - 1024 : 0;
         if (c->dec_method == METHOD_INT) {
-            const size_t tb = align_up(align_up(frame * c->dec_sym_bytes, 16) + size_t(c->dec_n_syms) * sizeof(SymEntry), 16);
-            if (tb <= lbudget)
+            const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_cnt_bytes);
+            if (tb <= std::min<size_t>(lbudget, size_t(100) << 10))
                 return launch_lpb_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
             return launch_lpb_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);
         }
@@ -973,8 +984,8 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     const size_t rows = size_t(kDecWarps) * 8 * kDecRowBytes;
     const size_t budget = c->max_smem > rows + 1024 ? c->max_smem - rows - 1024 : 0;
     if (c->dec_method == METHOD_INT) {
-        const size_t tb = align_up(align_up(frame * c->dec_sym_bytes, 16) + size_t(c->dec_n_syms) * sizeof(SymEntry), 16);
-        if (tb <= budget)
+        const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_cnt_bytes);
+        if (tb <= std::min<size_t>(budget, size_t(100) << 10))
             return launch_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
         return launch_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);
     }

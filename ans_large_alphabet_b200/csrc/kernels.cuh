@@ -39,13 +39,20 @@ struct __align__(8) DecEntry {
     uint32_t mapped; // for rfold: most_frequent[s] + 2^(f+7) resp. unfolded value
 };
 
-// Plain ANS decodes through two small tables instead of the reference's 8/12-byte slot
-// entries (ans_int.hpp:100-110): slot -> symbol id, symbol id -> {freq, base}.  The table
-// *contents* are a pure function of nfreqs, so the layout is ours to choose; this one keeps a
-// 2^16-slot model inside one SM's shared memory.
-struct __align__(8) SymEntry {
-    uint32_t freq;
+// Plain ANS (ans_int) replaces the reference's M-entry slot tables of 8 / 12 bytes per slot
+// (ans_int.hpp:100-110,129-161) by a rank/select index over the frame -- the table *contents*
+// are a pure function of nfreqs, so the layout is ours to choose:
+//   bits : M bits, bit s set iff slot s is the first slot of a symbol with freq > 0
+//   cnt  : per 32-slot word, the number of set bits in all earlier words (u16 or u32)
+//   ent  : per present symbol, in slot order: {base, freq, symbol id, 0}
+// slot -> rank = cnt[s >> 5] + popc(bits[s >> 5] & ((2 << (s & 31)) - 1)) - 1 -> ent[rank].
+// M / 8 + M / 16 + 16 * sigma bytes: a 2^17-slot model with 1 900 symbols takes 54 KiB and sits in
+// one SM's shared memory, where the reference layout (1 MiB) would live in L2.
+struct __align__(16) RankEntry {
     uint32_t base;
+    uint32_t freq;
+    uint32_t sym;
+    uint32_t pad;
 };
 
 struct EncArgs {
@@ -77,10 +84,102 @@ struct DecArgs {
     uint32_t log2_frame;
     uint32_t fidelity;
     const DecEntry* slots;     // folded methods: M entries
-    const void* slot_to_sym;   // INT: M entries, u16 or u32
-    const SymEntry* syms;      // INT: n_syms entries
-    uint32_t n_syms;
-    uint32_t sym_bytes;        // INT: 2 or 4
+    const uint32_t* rank_bits; // INT: M / 32 words
+    const void* rank_cnt;      // INT: M / 32 counters, u16 or u32
+    const RankEntry* rank_ent; // INT: n_present entries
+    uint32_t n_present;
+    uint32_t cnt_bytes;        // INT: 2 or 4
+};
+
+enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3 };
+
+// Decoder tables as the kernels see them: global pointers, or a copy in shared memory.
+template <int METHOD, int TABLE> struct DecTables {
+    static constexpr bool kInt = (METHOD == METHOD_INT);
+    static constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM);
+    const DecEntry* slots;
+    const uint32_t* bits;
+    const void* cnt;
+    const RankEntry* ent;
+    uint32_t cnt_bytes;
+
+    __host__ __device__ static size_t smem_bytes(uint32_t frame, uint32_t n_present, uint32_t cnt_bytes)
+    {
+        if (!kSmem)
+            return 0;
+        if (kInt) {
+            const size_t words = (size_t(frame) + 31) / 32;
+            return ((words * 4 + 15) & ~size_t(15)) + ((words * cnt_bytes + 15) & ~size_t(15)) + size_t(n_present) * sizeof(RankEntry);
+        }
+        return (size_t(frame) * sizeof(DecEntry) + 15) & ~size_t(15);
+    }
+
+    // cooperative copy into shared memory (all threads of the CTA); returns the bytes used
+    __device__ __forceinline__ size_t load(const DecArgs& a, uint8_t* smem)
+    {
+        slots = a.slots;
+        bits = a.rank_bits;
+        cnt = a.rank_cnt;
+        ent = a.rank_ent;
+        cnt_bytes = a.cnt_bytes;
+        if (!kSmem)
+            return 0;
+        const uint32_t frame = 1u << a.log2_frame;
+        if (kInt) {
+            const size_t words = (size_t(frame) + 31) / 32;
+            const size_t bits_bytes = (words * 4 + 15) & ~size_t(15);
+            const size_t cnt_b = (words * a.cnt_bytes + 15) & ~size_t(15);
+            const uint4* s0 = reinterpret_cast<const uint4*>(a.rank_bits);
+            uint4* d0 = reinterpret_cast<uint4*>(smem);
+            for (size_t i = threadIdx.x; i < bits_bytes / 16; i += blockDim.x)
+                d0[i] = __ldg(s0 + i);
+            const uint4* s1 = reinterpret_cast<const uint4*>(a.rank_cnt);
+            uint4* d1 = reinterpret_cast<uint4*>(smem + bits_bytes);
+            for (size_t i = threadIdx.x; i < cnt_b / 16; i += blockDim.x)
+                d1[i] = __ldg(s1 + i);
+            const uint4* s2 = reinterpret_cast<const uint4*>(a.rank_ent);
+            uint4* d2 = reinterpret_cast<uint4*>(smem + bits_bytes + cnt_b);
+            for (size_t i = threadIdx.x; i < a.n_present; i += blockDim.x)
+                d2[i] = __ldg(s2 + i);
+            bits = reinterpret_cast<const uint32_t*>(smem);
+            cnt = smem + bits_bytes;
+            ent = reinterpret_cast<const RankEntry*>(smem + bits_bytes + cnt_b);
+        } else {
+            const uint2* src = reinterpret_cast<const uint2*>(a.slots);
+            uint2* dst = reinterpret_cast<uint2*>(smem);
+            for (size_t i = threadIdx.x; i < frame; i += blockDim.x)
+                dst[i] = __ldg(src + i);
+            slots = reinterpret_cast<const DecEntry*>(smem);
+        }
+        __syncthreads();
+        return smem_bytes(frame, a.n_present, a.cnt_bytes);
+    }
+
+    // slot -> {freq, offset inside the symbol's slot range, unfolded base value / symbol id, raw byte count}
+    __device__ __forceinline__ void lookup(uint32_t slot, uint32_t& freq, uint32_t& offset, uint32_t& mapped, uint32_t& k) const
+    {
+        if (kInt) {
+            const uint32_t w = slot >> 5;
+            const uint32_t b = kSmem ? bits[w] : __ldg(bits + w);
+            uint32_t r;
+            if (cnt_bytes == 2)
+                r = kSmem ? uint32_t(reinterpret_cast<const uint16_t*>(cnt)[w]) : uint32_t(__ldg(reinterpret_cast<const uint16_t*>(cnt) + w));
+            else
+                r = kSmem ? reinterpret_cast<const uint32_t*>(cnt)[w] : __ldg(reinterpret_cast<const uint32_t*>(cnt) + w);
+            r += uint32_t(__popc(b & (0xFFFFFFFFu >> (31u - (slot & 31u))))) - 1u;
+            const uint4 e = kSmem ? *reinterpret_cast<const uint4*>(ent + r) : __ldg(reinterpret_cast<const uint4*>(ent + r));
+            freq = e.y;
+            offset = slot - e.x;
+            mapped = e.z;
+            k = 0;
+        } else {
+            const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(slots + slot) : __ldg(reinterpret_cast<const uint2*>(slots + slot));
+            freq = e.x & 0xFFFFu;
+            offset = e.x >> 16;
+            mapped = e.y & 0x3FFFFFFFu;
+            k = e.y >> 30;
+        }
+    }
 };
 
 // ------------------------------------------------------------------------------------------
@@ -421,50 +520,13 @@ constexpr int kDecPad = 16;        // bytes in front of the staged window (windo
 constexpr int kDecStageChunks = 18; // 16-byte chunks staged per refill: covers 28*8 + 12 + 4 + alignment
 constexpr int kDecRowBytes = kDecPad + kDecStageChunks * 16; // 304 = 19 * 16
 
-enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3 };
-
 template <int METHOD, int TABLE>
 __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    constexpr bool kInt = (METHOD == METHOD_INT);
-    constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM);
     const uint32_t frame = 1u << a.log2_frame;
-    size_t table_bytes = 0;
-    if (kSmem) {
-        if (kInt)
-            table_bytes = ((size_t(frame) * a.sym_bytes + 15) & ~size_t(15)) + size_t(a.n_syms) * sizeof(SymEntry);
-        else
-            table_bytes = size_t(frame) * sizeof(DecEntry);
-        table_bytes = (table_bytes + 15) & ~size_t(15);
-    }
-    uint8_t* s_rows = smem_raw + table_bytes;
-    const DecEntry* slots = a.slots;
-    const void* s2s = a.slot_to_sym;
-    const SymEntry* syms = a.syms;
-    if (kSmem) {
-        // cooperative 16-byte copies of the tables
-        if (kInt) {
-            const size_t s2s_bytes = (size_t(frame) * a.sym_bytes + 15) & ~size_t(15);
-            const uint4* src = reinterpret_cast<const uint4*>(a.slot_to_sym);
-            uint4* dst = reinterpret_cast<uint4*>(smem_raw);
-            for (size_t i = threadIdx.x; i < s2s_bytes / 16; i += blockDim.x)
-                dst[i] = __ldg(src + i);
-            const uint2* src2 = reinterpret_cast<const uint2*>(a.syms);
-            uint2* dst2 = reinterpret_cast<uint2*>(smem_raw + s2s_bytes);
-            for (size_t i = threadIdx.x; i < a.n_syms; i += blockDim.x)
-                dst2[i] = __ldg(src2 + i);
-            s2s = smem_raw;
-            syms = reinterpret_cast<const SymEntry*>(smem_raw + s2s_bytes);
-        } else {
-            const uint2* src = reinterpret_cast<const uint2*>(a.slots);
-            uint2* dst = reinterpret_cast<uint2*>(smem_raw);
-            for (size_t i = threadIdx.x; i < frame; i += blockDim.x)
-                dst[i] = __ldg(src + i);
-            slots = reinterpret_cast<const DecEntry*>(smem_raw);
-        }
-        __syncthreads();
-    }
+    DecTables<METHOD, TABLE> tables;
+    uint8_t* s_rows = smem_raw + tables.load(a, smem_raw);
 
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
@@ -534,21 +596,7 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
                 const uint32_t idx = s < quads ? 4u * s + g : s + 3u * quads; // 4*quads + (s - quads)
                 const uint32_t slot = uint32_t(x) & frame_mask;
                 uint32_t freq, offset, mapped, k;
-                if (kInt) {
-                    const uint32_t sym = (a.sym_bytes == 2) ? uint32_t(reinterpret_cast<const uint16_t*>(s2s)[slot])
-                                                            : reinterpret_cast<const uint32_t*>(s2s)[slot];
-                    const SymEntry se = syms[sym];
-                    freq = se.freq;
-                    offset = slot - se.base;
-                    mapped = sym;
-                    k = 0;
-                } else {
-                    const DecEntry e = slots[slot];
-                    freq = e.freq;
-                    offset = e.offset;
-                    mapped = e.mapped & 0x3FFFFFFFu;
-                    k = e.mapped >> 30;
-                }
+                tables.lookup(slot, freq, offset, mapped, k);
                 uint64_t nx = uint64_t(freq) * (x >> log2_frame) + offset;
                 const bool renorm = active && nx < lower;
                 const uint32_t c = active ? k + (renorm ? 4u : 0u) : 0u;

@@ -254,60 +254,50 @@ __global__ void __launch_bounds__(kLpbEncWarps * 32) lpb_encode_kernel(const Enc
 // ------------------------------------------------------------------------------------------
 // K3-LPB: decoder
 // ------------------------------------------------------------------------------------------
-// The lane walks its block's payload downwards from the four states.  The three aligned 32-bit
-// words that cover the 8 bytes below the cursor live in registers (t0 = word holding the byte
-// just below the cursor, t1, t2 = the two words below it); a symbol consumes at most 7 bytes,
-// i.e. moves the cursor across at most two word boundaries, so at most two predicated 4-byte
-// loads (L1-resident: every lane streams its own block) refill the window.  Decoded symbols are
-// staged per warp in shared memory and written out in coalesced 64-byte pieces.
+// The lane walks its block's payload downwards from the four states.  The compressed bytes are
+// staged in a lane-private 128-byte ring in shared memory, filled by asynchronous 16-byte copies
+// (cp.async / LDGSTS) that run kLpbPrefetch bytes ahead of the cursor: one quad (<= 28 bytes)
+// ahead is always complete, so the decode loop never waits on HBM.  Per symbol the 8 bytes
+// below the cursor are assembled from three aligned ring words; the four chains of a quad are
+// independent up to the cursor (a plain register add), which gives the lane four table lookups
+// to overlap.  Decoded symbols are staged per warp and written out in coalesced 64-byte pieces.
 constexpr int kLpbDecWarps = 8;
 constexpr int kLpbDecOutRow = kLpbTileQuads * 16 + 16; // 80 B
+constexpr int kLpbRing = 128;                           // bytes of ring per lane (power of two, 128-aligned rows)
+constexpr int kLpbPrefetch = 80;                        // bytes below the cursor kept in flight: >= 2 * 28 + 15
+static_assert(kLpbPrefetch + 15 + 16 <= kLpbRing, "ring too small for the prefetch distance");
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ uint32_t lds32(uint32_t smem_addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_addr) : "memory");
+    return v;
+}
 
 template <int METHOD, int TABLE>
 __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const DecArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     constexpr bool kInt = (METHOD == METHOD_INT);
-    constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM);
     const uint32_t frame = 1u << a.log2_frame;
-    size_t table_bytes = 0;
-    if (kSmem) {
-        if (kInt)
-            table_bytes = ((size_t(frame) * a.sym_bytes + 15) & ~size_t(15)) + size_t(a.n_syms) * sizeof(SymEntry);
-        else
-            table_bytes = size_t(frame) * sizeof(DecEntry);
-        table_bytes = (table_bytes + 15) & ~size_t(15);
-    }
+    DecTables<METHOD, TABLE> tables;
+    const size_t table_bytes = tables.load(a, smem_raw);
+    // rings must be 128-byte aligned (ring | offset addressing); the host adds 128 bytes of slack
     uint8_t* s_rows = smem_raw + table_bytes;
-    const DecEntry* slots = a.slots;
-    const void* s2s = a.slot_to_sym;
-    const SymEntry* syms = a.syms;
-    if (kSmem) {
-        if (kInt) {
-            const size_t s2s_bytes = (size_t(frame) * a.sym_bytes + 15) & ~size_t(15);
-            const uint4* src = reinterpret_cast<const uint4*>(a.slot_to_sym);
-            uint4* dst = reinterpret_cast<uint4*>(smem_raw);
-            for (size_t i = threadIdx.x; i < s2s_bytes / 16; i += blockDim.x)
-                dst[i] = __ldg(src + i);
-            const uint2* src2 = reinterpret_cast<const uint2*>(a.syms);
-            uint2* dst2 = reinterpret_cast<uint2*>(smem_raw + s2s_bytes);
-            for (size_t i = threadIdx.x; i < a.n_syms; i += blockDim.x)
-                dst2[i] = __ldg(src2 + i);
-            s2s = smem_raw;
-            syms = reinterpret_cast<const SymEntry*>(smem_raw + s2s_bytes);
-        } else {
-            const uint2* src = reinterpret_cast<const uint2*>(a.slots);
-            uint2* dst = reinterpret_cast<uint2*>(smem_raw);
-            for (size_t i = threadIdx.x; i < frame; i += blockDim.x)
-                dst[i] = __ldg(src + i);
-            slots = reinterpret_cast<const DecEntry*>(smem_raw);
-        }
-        __syncthreads();
-    }
+    s_rows += (128u - (uint32_t(__cvta_generic_to_shared(s_rows)) & 127u)) & 127u;
 
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
-    uint8_t* out_rows = s_rows + size_t(warp) * 32 * kLpbDecOutRow;
+    // per warp: 32 rings of 128 B (128-aligned), then 32 output rows
+    uint8_t* warp_base = s_rows + size_t(warp) * 32 * (kLpbRing + kLpbDecOutRow);
+    const uint32_t ring = uint32_t(__cvta_generic_to_shared(warp_base)) + lane * kLpbRing;
+    uint8_t* out_rows = warp_base + 32 * kLpbRing;
     uint8_t* my_out = out_rows + lane * kLpbDecOutRow;
     const uint32_t log2_frame = a.log2_frame;
     const uint32_t frame_mask = frame - 1u;
@@ -326,86 +316,74 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
         const uint32_t quads = nb >> 2;
         const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
 
-        // word-aligned view of the payload; `pos` counts bytes from words[0], one past the next byte to consume
+        // 16-byte aligned view of the payload; `pos` counts bytes from pay16, one past the next byte to consume
         const uint8_t* pay = a.payload + (have_block ? a.offsets[blk] : 0);
-        const uint32_t delta = uint32_t(reinterpret_cast<uintptr_t>(pay) & 3u);
-        const uint32_t* words = reinterpret_cast<const uint32_t*>(pay - delta);
+        const uint32_t delta = uint32_t(reinterpret_cast<uintptr_t>(pay) & 15u);
+        const uint8_t* pay16 = pay - delta;
         const uint32_t size = have_block ? a.block_bytes[blk] : 32u;
-        auto word_at = [&](int32_t i) -> uint32_t { return (have_block && i >= 0) ? __ldg(words + i) : 0u; };
+        int32_t pos = int32_t(delta + size - 32u);
 
         // init_state x4: state c sits at payload + size - 32 + 8c (ans_fold.hpp:291-295)
-        uint64_t x0, x1, x2, x3;
-        {
-            const uint32_t sp = delta + size - 32u;
-            const int32_t w = int32_t(sp >> 2);
-            const uint32_t sh = (sp & 3u) * 8u;
+        uint64_t x0 = lower, x1 = lower, x2 = lower, x3 = lower;
+        if (have_block) {
+            const uint32_t* words = reinterpret_cast<const uint32_t*>(pay16);
+            const int32_t w = pos >> 2;
+            const uint32_t sh = (uint32_t(pos) & 3u) * 8u;
             uint32_t t[9];
 #pragma unroll
             for (int i = 0; i < 9; i++)
-                t[i] = (i < 8 || sh != 0u) ? word_at(w + i) : 0u;
+                t[i] = (i < 8 || sh != 0u) ? __ldg(words + w + i) : 0u;
             uint32_t u[8];
 #pragma unroll
             for (int i = 0; i < 8; i++)
                 u[i] = __funnelshift_r(t[i], t[i + 1], sh);
-            x0 = ((uint64_t(u[1]) << 32) | u[0]) + lower;
-            x1 = ((uint64_t(u[3]) << 32) | u[2]) + lower;
-            x2 = ((uint64_t(u[5]) << 32) | u[4]) + lower;
-            x3 = ((uint64_t(u[7]) << 32) | u[6]) + lower;
+            x0 += (uint64_t(u[1]) << 32) | u[0];
+            x1 += (uint64_t(u[3]) << 32) | u[2];
+            x2 += (uint64_t(u[5]) << 32) | u[4];
+            x3 += (uint64_t(u[7]) << 32) | u[6];
         }
-        uint32_t pos = delta + size - 32u;
-        int32_t wi = int32_t(pos + 3u) / 4 - 1; // index of the word that holds byte pos-1 (-1 when pos == 0)
-        uint32_t t0 = word_at(wi), t1 = word_at(wi - 1), t2 = word_at(wi - 2);
+
+        // ring fill: everything from the chunk that holds byte pos-1 down to pos - kLpbPrefetch
+        int32_t fetched_lo = (pos + 15) & ~15; // chunks [fetched_lo, top) are in the ring
+        auto prefetch = [&](int max_chunks) {
+            const int32_t want = max(pos - kLpbPrefetch, 0) & ~15;
+#pragma unroll
+            for (int i = 0; i < max_chunks; i++) {
+                if (have_block && fetched_lo > want) {
+                    fetched_lo -= 16;
+                    cp_async16(ring + (uint32_t(fetched_lo) & uint32_t(kLpbRing - 1)), pay16 + fetched_lo);
+                }
+            }
+            cp_async_commit();
+        };
+        prefetch((kLpbPrefetch + 15 + 15) / 16 + 1);
 
         auto decode_one = [&](uint64_t& x, bool active) -> uint32_t {
             const uint32_t slot = uint32_t(x) & frame_mask;
             uint32_t freq, offset, mapped, k;
-            if (kInt) {
-                const uint32_t sym = (a.sym_bytes == 2) ? uint32_t(reinterpret_cast<const uint16_t*>(s2s)[slot])
-                                                        : reinterpret_cast<const uint32_t*>(s2s)[slot];
-                const SymEntry se = syms[sym];
-                freq = se.freq;
-                offset = slot - se.base;
-                mapped = sym;
-                k = 0;
-            } else {
-                const uint2 e = *reinterpret_cast<const uint2*>(slots + slot);
-                freq = e.x & 0xFFFFu;
-                offset = e.x >> 16;
-                mapped = e.y & 0x3FFFFFFFu;
-                k = e.y >> 30;
-            }
+            tables.lookup(slot, freq, offset, mapped, k);
             uint64_t nx = uint64_t(freq) * (x >> log2_frame) + offset;
             const bool renorm = active && nx < lower;
-            // bytes [pos-8, pos): hi = the 4 bytes just below the cursor, lo = the 4 below those
-            const uint32_t sh = ((pos + 3u) & 3u) * 8u + 8u; // 8, 16, 24, 32
-            const uint32_t win_hi = __funnelshift_rc(t1, t0, sh);
-            const uint32_t win_lo = __funnelshift_rc(t2, t1, sh);
+            // bytes [pos-8, pos) from the three aligned ring words that cover them
+            const uint32_t p1 = uint32_t(pos - 1);
+            const uint32_t w0 = lds32(ring | (p1 & uint32_t(kLpbRing - 4)));
+            const uint32_t w1 = lds32(ring | ((p1 - 4u) & uint32_t(kLpbRing - 4)));
+            const uint32_t sh = (p1 & 3u) * 8u + 8u; // 8, 16, 24, 32
+            const uint32_t win_hi = __funnelshift_rc(w1, w0, sh); // the 4 bytes just below the cursor
             if (renorm) // renormalisation word first (ans_fold.hpp:221-224)
                 nx = (nx << kRadixLog2) | uint64_t(win_hi);
             uint32_t value = mapped;
             uint32_t c = renorm ? 4u : 0u;
             if (!kInt) { // then k raw low bytes (ans_fold.hpp:135-147)
+                const uint32_t w2 = lds32(ring | ((p1 - 8u) & uint32_t(kLpbRing - 4)));
+                const uint32_t win_lo = __funnelshift_rc(w2, w1, sh);
                 const uint32_t exc_src = renorm ? win_lo : win_hi;
                 value += __funnelshift_rc(exc_src, 0u, 32u - 8u * k);
                 c += k;
             }
             if (active) {
                 x = nx;
-                pos -= c;
-                // slide the word window: the cursor crossed 0, 1 or 2 word boundaries
-                const int32_t nwi = int32_t(pos + 3u) / 4 - 1;
-                if (nwi < wi) {
-                    t0 = t1;
-                    t1 = t2;
-                    t2 = word_at(wi - 3);
-                    wi -= 1;
-                }
-                if (!kInt && nwi < wi) {
-                    t0 = t1;
-                    t1 = t2;
-                    t2 = word_at(wi - 3);
-                    wi -= 1;
-                }
+                pos -= int32_t(c);
             }
             return value - rfold_bias;
         };
@@ -415,6 +393,9 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
 #pragma unroll
             for (int j = 0; j < kLpbTileQuads; j++) {
                 const bool active = (q0 + uint32_t(j)) < quads;
+                // keep the ring kLpbPrefetch bytes ahead; everything this quad can touch was committed a quad ago
+                prefetch(3);
+                cp_async_wait<1>();
                 uint4 o;
                 // index 4t+g is decoded by state 3-g (ans_fold.hpp:300-305)
                 o.x = decode_one(x3, active);
@@ -443,6 +424,8 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
         }
         // tail symbols on state 0 (ans_fold.hpp:306-310); only the last block of the input has any
         if (__any_sync(0xffffffffu, tail != 0u)) {
+            prefetch(3);
+            cp_async_wait<0>();
             for (uint32_t s = 0; s < 3u; s++) {
                 const bool active = s < tail;
                 const uint32_t v = decode_one(x0, active);
@@ -450,6 +433,7 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
                     a.out[first + 4u * quads + s] = v;
             }
         }
+        cp_async_wait<0>();
     }
 }
 
