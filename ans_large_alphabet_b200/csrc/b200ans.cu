@@ -77,6 +77,7 @@ struct b200ans_ctx {
     int device = 0;
     int num_sms = 0;
     size_t max_smem = 0;
+    size_t max_smem_sm = 0; // shared memory per SM
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
@@ -218,6 +219,7 @@ extern "C" int b200ans_create(b200ans_ctx** out, int device, void* stream)
     cudaGetDeviceProperties(&prop, device);
     c->num_sms = prop.multiProcessorCount;
     c->max_smem = prop.sharedMemPerBlockOptin;
+    c->max_smem_sm = prop.sharedMemPerMultiprocessor;
     if (stream) {
         c->stream = static_cast<cudaStream_t>(stream);
     } else {
@@ -851,39 +853,40 @@ bool use_lpb(const b200ans_ctx* c, uint32_t n_blocks)
     return n_blocks >= uint32_t(c->num_sms) * 32u * 8u; // >= 8 LPB warps per SM
 }
 
+// Lane-per-block launch shape: ONE CTA per SM.  A task (32 blocks) runs for the whole kernel, so
+// the tasks are spread in balanced waves: waves = ceil(tasks / (SMs * max warps)), and every CTA
+// gets ceil(tasks / (SMs * waves)) warps -- 2^30 symbols are 4096 tasks = one wave of 28 warps per SM.
+template <class K> int launch_lpb(b200ans_ctx* c, K k, size_t table_bytes, size_t warp_bytes, uint32_t n_blocks, const void* args)
+{
+    const size_t room = c->max_smem > table_bytes + 1024 ? c->max_smem - table_bytes - 1024 : 0;
+    const uint32_t max_warps = uint32_t(std::max<size_t>(1, std::min<size_t>(kLpbMaxWarps, room / warp_bytes)));
+    const uint32_t n_tasks = (n_blocks + 31) / 32;
+    const uint32_t sms = uint32_t(c->num_sms);
+    const uint32_t waves = (n_tasks + sms * max_warps - 1) / (sms * max_warps);
+    const uint32_t warps = std::max<uint32_t>(1, std::min<uint32_t>(max_warps, (n_tasks + sms * waves - 1) / (sms * waves)));
+    const uint32_t grid = std::min<uint32_t>(sms, (n_tasks + warps - 1) / warps);
+    const size_t smem = table_bytes + 128 + size_t(warps) * warp_bytes;
+    CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    void* params[] = { const_cast<void*>(args) };
+    CU(c, cudaLaunchKernel(reinterpret_cast<const void*>(k), dim3(grid), dim3(warps * 32), params, smem, c->stream));
+    c->stats.launches++;
+    return B200ANS_OK;
+}
+
 template <int METHOD> int launch_lpb_encode_t(b200ans_ctx* c, const EncArgs& a)
 {
-    const size_t rows = size_t(kLpbEncWarps) * 32 * (kLpbInRow + kLpbOutRow);
-    const uint32_t n_tasks = (a.n_blocks + 31) / 32;
     const bool smem_table = a.n_entries <= uint32_t(kLpbEncMaxSmemEntries);
-    if (smem_table) {
-        auto k = lpb_encode_kernel<METHOD, true>;
-        const size_t smem = rows + size_t(a.n_entries) * sizeof(EncEntry);
-        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-        const int grid = persistent_grid(c, k, kLpbEncWarps * 32, smem, n_tasks, kLpbEncWarps);
-        k<<<grid, kLpbEncWarps * 32, smem, c->stream>>>(a);
-    } else {
-        auto k = lpb_encode_kernel<METHOD, false>;
-        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(rows)));
-        const int grid = persistent_grid(c, k, kLpbEncWarps * 32, rows, n_tasks, kLpbEncWarps);
-        k<<<grid, kLpbEncWarps * 32, rows, c->stream>>>(a);
-    }
-    c->stats.launches++;
-    CU(c, cudaGetLastError());
-    return B200ANS_OK;
+    const size_t tb = smem_table ? size_t(a.n_entries) * sizeof(EncEntry) : 0;
+    if (smem_table)
+        return a.fast_div ? launch_lpb(c, lpb_encode_kernel<METHOD, true, true>, tb, kLpbEncWarpBytes, a.n_blocks, &a)
+                          : launch_lpb(c, lpb_encode_kernel<METHOD, true, false>, tb, kLpbEncWarpBytes, a.n_blocks, &a);
+    return a.fast_div ? launch_lpb(c, lpb_encode_kernel<METHOD, false, true>, tb, kLpbEncWarpBytes, a.n_blocks, &a)
+                      : launch_lpb(c, lpb_encode_kernel<METHOD, false, false>, tb, kLpbEncWarpBytes, a.n_blocks, &a);
 }
 
 template <int METHOD, int TABLE> int launch_lpb_decode_tt(b200ans_ctx* c, const DecArgs& a, size_t table_bytes)
 {
-    auto k = lpb_decode_kernel<METHOD, TABLE>;
-    const size_t smem = align_up(table_bytes, 16) + 128 + size_t(kLpbDecWarps) * 32 * (kLpbRing + kLpbDecOutRow);
-    CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    const uint32_t n_tasks = (a.n_blocks + 31) / 32;
-    const int grid = persistent_grid(c, k, kLpbDecWarps * 32, smem, n_tasks, kLpbDecWarps);
-    k<<<grid, kLpbDecWarps * 32, smem, c->stream>>>(a);
-    c->stats.launches++;
-    CU(c, cudaGetLastError());
-    return B200ANS_OK;
+    return launch_lpb(c, lpb_decode_kernel<METHOD, TABLE>, align_up(table_bytes, 16), kLpbDecWarpBytes, a.n_blocks, &a);
 }
 
 // encode d_src into scratch slots + block_bytes using the current encoder model
@@ -958,8 +961,7 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     a.cnt_bytes = c->dec_cnt_bytes;
     const size_t frame = size_t(1) << c->dec_log2_frame;
     if (use_lpb(c, n_blocks)) {
-        const size_t lrows = size_t(kLpbDecWarps) * 32 * (kLpbRing + kLpbDecOutRow) + 128;
-        const size_t lbudget = c->max_smem > lrows + 1024 ? c->max_smem - lrows - 1024 : 0;
+        const size_t lbudget = c->max_smem > size_t(16) * kLpbDecWarpBytes + 4096 ? c->max_smem - size_t(16) * kLpbDecWarpBytes - 4096 : 0;
         if (c->dec_method == METHOD_INT) {
             const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_cnt_bytes);
             if (tb <= std::min<size_t>(lbudget, size_t(100) << 10))

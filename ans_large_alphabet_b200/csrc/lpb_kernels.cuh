@@ -40,21 +40,40 @@ __device__ __forceinline__ uint64_t ans_push52(uint32_t x_lo, uint32_t x_hi, uin
 }
 
 // ------------------------------------------------------------------------------------------
+// asynchronous 16-byte global -> shared copies (LDGSTS)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem_ptr, const void* gptr)
+{
+    const uint32_t s = uint32_t(__cvta_generic_to_shared(smem_ptr));
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int kLpbMaxWarps = 28;   // warps per CTA; one CTA per SM (the host picks the count: one balanced wave of tasks)
+constexpr int kLpbTileQuads = 4;   // quads (of 4 symbols) per lane and output tile of the decoder
+constexpr int kLpbInQuads = 2;     // quads per lane and input tile of the encoder
+
+// ------------------------------------------------------------------------------------------
 // K2-LPB: encoder
 // ------------------------------------------------------------------------------------------
-constexpr int kLpbEncWarps = 8;
-constexpr int kLpbTileQuads = 4;                         // quads (of 4 symbols) per lane between drains
-constexpr int kLpbInRow = kLpbTileQuads * 16 + 16;        // 80 B: 5 x 16 (odd) -> conflict-free 128-bit row reads
-constexpr int kLpbOutRow = 176;                           // 12 carried + 28 * 16 symbols... see static_assert
-static_assert(12 + 28 * kLpbTileQuads + 36 + 4 <= kLpbOutRow && (kLpbOutRow / 16) % 2 == 1, "output row too small");
-constexpr int kLpbEncMaxSmemEntries = 6144;
+// Per warp: two input buffers of 32 rows x 32 B (the next tile is in flight while the current one
+// is coded) and 32 output rows.  A quad is coded in four phases so that the lane's four chains
+// overlap: (1) fold + table lookups of the 4 symbols, (2) the 4 renormalisation tests, (3) the
+// serial emission into the word accumulator, (4) the 4 exact state updates.
+constexpr int kLpbInRow = kLpbInQuads * 16 + 16;   // 48 B: 3 x 16 (odd) -> conflict-free 128-bit row reads
+constexpr int kLpbDrainQuads = kLpbInQuads;        // the output row is drained after every input tile
+constexpr int kLpbOutRow = 112;                    // 12 carried + 28 * 2 quads + 32 states + 4 partial <= 104
+static_assert(12 + 28 * kLpbDrainQuads + 36 <= kLpbOutRow && (kLpbOutRow / 16) % 2 == 1, "output row too small");
+constexpr int kLpbEncWarpBytes = 32 * (2 * kLpbInRow + kLpbOutRow);
+constexpr int kLpbEncMaxSmemEntries = 4096;
 
 // Word-granular emitter: bytes are collected little-endian in `acc` (sh = 8 * pending bytes,
 // pending < 4) and complete 32-bit words go to the lane's row in shared memory.
 struct LpbEmitter {
     uint32_t acc;
-    uint32_t sh;  // 0, 8, 16, 24
-    uint32_t wp;  // shared-memory byte address of the next word of the row
+    uint32_t sh;   // 0, 8, 16, 24
+    uint32_t* wp;  // next word of the row
     __device__ __forceinline__ void put_bytes(uint32_t v, uint32_t k) // k in 0..3 low bytes of v
     {
         const uint32_t vm = v & ((1u << (8u * k)) - 1u);
@@ -62,10 +81,8 @@ struct LpbEmitter {
         const uint32_t hi = __funnelshift_l(vm, 0u, sh); // vm >> (32 - sh), 0 when sh == 0
         const uint32_t nsh = sh + 8u * k;
         const bool full = nsh >= 32u;
-        if (full) {
-            asm volatile("st.shared.u32 [%0], %1;" ::"r"(wp), "r"(t) : "memory");
-            wp += 4u;
-        }
+        if (full)
+            *wp++ = t;
         acc = full ? hi : t;
         sh = nsh & 31u;
     }
@@ -73,15 +90,14 @@ struct LpbEmitter {
     {
         const uint32_t t = acc | (w << sh);
         if (on) {
-            asm volatile("st.shared.u32 [%0], %1;" ::"r"(wp), "r"(t) : "memory");
-            wp += 4u;
+            *wp++ = t;
             acc = __funnelshift_l(w, 0u, sh); // w >> (32 - sh), 0 when sh == 0
         }
     }
 };
 
-template <int METHOD, bool TABLE_SMEM>
-__global__ void __launch_bounds__(kLpbEncWarps * 32) lpb_encode_kernel(const EncArgs a)
+template <int METHOD, bool TABLE_SMEM, bool FAST>
+__global__ void __launch_bounds__(kLpbMaxWarps * 32, 1) lpb_encode_kernel(const EncArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     EncEntry* s_table = reinterpret_cast<EncEntry*>(smem_raw);
@@ -95,20 +111,18 @@ __global__ void __launch_bounds__(kLpbEncWarps * 32) lpb_encode_kernel(const Enc
     }
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
-    uint8_t* in_rows = s_rows + size_t(warp) * 32 * (kLpbInRow + kLpbOutRow);
-    uint8_t* out_rows = in_rows + 32 * kLpbInRow;
-    uint8_t* my_in = in_rows + lane * kLpbInRow;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    uint8_t* in_rows = s_rows + size_t(warp) * kLpbEncWarpBytes; // 2 buffers of 32 rows
+    uint8_t* out_rows = in_rows + 2 * 32 * kLpbInRow;
     uint8_t* my_out = out_rows + lane * kLpbOutRow;
-    const uint32_t my_out_s = uint32_t(__cvta_generic_to_shared(my_out));
     const uint4* table4 = reinterpret_cast<const uint4*>(TABLE_SMEM ? s_table : a.table);
     const uint32_t log2_frame = a.log2_frame;
     const uint32_t f = a.fidelity;
-    const bool fast = a.fast_div != 0u; // every frequency < 2^16
     const uint64_t lower = uint64_t(kAnsK) << log2_frame;
     const uint32_t B = a.block_syms;
 
     const uint32_t n_tasks = (a.n_blocks + 31u) >> 5;
-    for (uint32_t task = blockIdx.x * kLpbEncWarps + warp; task < n_tasks; task += gridDim.x * kLpbEncWarps) {
+    for (uint32_t task = blockIdx.x * warps_per_cta + warp; task < n_tasks; task += gridDim.x * warps_per_cta) {
         const uint32_t blk0 = task * 32u;
         const uint32_t blk = blk0 + lane;
         const bool have_block = blk < a.n_blocks;
@@ -119,15 +133,16 @@ __global__ void __launch_bounds__(kLpbEncWarps * 32) lpb_encode_kernel(const Enc
         const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
         uint8_t* dst = a.scratch + uint64_t(blk) * a.stride;
 
-        uint64_t x0 = lower, x1 = lower, x2 = lower, x3 = lower; // initial_state() (ans_fold.hpp:113)
+        uint64_t xs[4] = { lower, lower, lower, lower }; // initial_state() (ans_fold.hpp:113)
         LpbEmitter em;
         em.acc = 0;
         em.sh = 0;
-        em.wp = my_out_s;
+        em.wp = reinterpret_cast<uint32_t*>(my_out);
         uint32_t flushed = 0;
         uint32_t bad = 0;
 
-        auto encode_one = [&](uint32_t v, uint64_t& x, bool active) {
+        // symbol -> {k raw bytes, freq, base, reciprocal}
+        auto model = [&](uint32_t& v, bool active, uint32_t& k, uint32_t& fr, uint32_t& base, double& rcp) {
             if (METHOD == METHOD_RFOLD) {
                 if (v >= a.n_values) { // value the model has never seen
                     bad |= uint32_t(active);
@@ -135,112 +150,145 @@ __global__ void __launch_bounds__(kLpbEncWarps * 32) lpb_encode_kernel(const Enc
                 }
                 v = __ldg(a.mapping + v);
             }
-            uint32_t k;
             uint32_t sym = map_value<METHOD>(v, f, k);
             if (sym >= a.n_entries) {
                 bad |= uint32_t(active);
                 sym = 0;
             }
             const uint4 raw = TABLE_SMEM ? table4[sym] : __ldg(table4 + sym);
-            const uint32_t fr = raw.x, base = raw.y;
-            const double rcp = __hiloint2double(int(raw.w), int(raw.z));
+            fr = raw.x;
+            base = raw.y;
+            rcp = __hiloint2double(int(raw.w), int(raw.z));
             bad |= uint32_t(active && fr == 0u);
+        };
+        auto push = [&](uint64_t x, bool renorm, uint32_t fr, uint32_t base, double rcp) -> uint64_t {
             const uint32_t x_lo = uint32_t(x), x_hi = uint32_t(x >> 32);
-            const bool renorm = active && ((x_hi >> 4) >= fr); // state >= freq * K * 2^32 (ans_fold.hpp:105)
-            if (METHOD != METHOD_INT)
-                em.put_bytes(v, active ? k : 0u); // raw low bytes first (ans_fold.hpp:59-63)
-            em.put_word(x_lo, renorm);           // then the renormalisation word (ans_fold.hpp:106-109)
             const uint32_t y_lo = renorm ? x_hi : x_lo;
             const uint32_t y_hi = renorm ? 0u : x_hi;
-            uint64_t nx;
-            if (fast)
-                nx = ans_push52(y_lo, y_hi, fr, base, rcp, log2_frame);
-            else
-                nx = ans_push((uint64_t(y_hi) << 32) | y_lo, fr, base, rcp, log2_frame);
-            if (active)
-                x = nx;
+            if (FAST)
+                return ans_push52(y_lo, y_hi, fr, base, rcp, log2_frame);
+            return ans_push((uint64_t(y_hi) << 32) | y_lo, fr, base, rcp, log2_frame);
+        };
+        auto drain = [&](uint32_t max_chunks_hint) {
+            const uint32_t fill = uint32_t(reinterpret_cast<uint8_t*>(em.wp) - my_out); // multiple of 4
+            const uint32_t chunks = fill >> 4;
+            const uint4* rv = reinterpret_cast<const uint4*>(my_out);
+            uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
+#pragma unroll
+            for (uint32_t ci = 0; ci < 5u; ci++)
+                if (ci < max_chunks_hint && ci < chunks)
+                    gv[ci] = rv[ci];
+            if (chunks != 0u) {
+                const uint4 carry = rv[chunks];
+                *reinterpret_cast<uint4*>(my_out) = carry;
+            }
+            flushed += chunks << 4;
+            em.wp = reinterpret_cast<uint32_t*>(my_out + (fill & 15u));
         };
 
         // tail symbols (only the very last block of the input has any): state 0 (ans_fold.hpp:257-261)
         if (__any_sync(0xffffffffu, tail != 0u)) {
             for (uint32_t s = 0; s < 3u; s++) {
                 const bool active = s < tail;
-                const uint32_t v = active ? __ldg(a.in + first + (nb - 1u - s)) : 0u;
-                encode_one(v, x0, active);
+                uint32_t v = active ? __ldg(a.in + first + (nb - 1u - s)) : 0u;
+                uint32_t k, fr, base;
+                double rcp;
+                model(v, active, k, fr, base, rcp);
+                const bool renorm = active && ((uint32_t(xs[0] >> 32) >> 4) >= fr);
+                if (METHOD != METHOD_INT)
+                    em.put_bytes(v, active ? k : 0u);
+                em.put_word(uint32_t(xs[0]), renorm);
+                const uint64_t nx = push(xs[0], renorm, fr, base, rcp);
+                if (active)
+                    xs[0] = nx;
             }
+            drain(2);
         }
 
-        for (uint32_t q0 = 0; q0 < max_quads; q0 += kLpbTileQuads) {
-            // ---- stage the next 16 symbols of each of the warp's 32 blocks (coalesced 64-byte pieces) ----
-            __syncwarp();
+        // stage the 8 symbols per block of tile q0 into buffer `buf`: coalesced 32-byte pieces, asynchronous
+        auto stage = [&](uint32_t q0, uint32_t buf) {
+            if (q0 < max_quads) {
 #pragma unroll
-            for (int it = 0; it < 4; it++) {
-                const uint32_t row = uint32_t(it) * 8u + (lane >> 2);
-                const uint32_t chunk = lane & 3u;
-                const uint32_t rblk = blk0 + row;
-                if (rblk < a.n_blocks) {
-                    const uint64_t rfirst = uint64_t(rblk) * B;
-                    const uint32_t rnb = uint32_t(min(uint64_t(B), a.n - rfirst));
-                    const uint32_t rquads = rnb >> 2;
-                    // quad index (ascending in memory) held by this chunk
-                    const int64_t qi = int64_t(rquads) - int64_t(q0) - int64_t(kLpbTileQuads) + int64_t(chunk);
-                    if (qi >= 0) {
-                        const uint4 val = __ldg(reinterpret_cast<const uint4*>(a.in + rfirst) + qi);
-                        *reinterpret_cast<uint4*>(in_rows + row * kLpbInRow + chunk * 16u) = val;
+                for (int it = 0; it < 2; it++) {
+                    const uint32_t row = uint32_t(it) * 16u + (lane >> 1);
+                    const uint32_t chunk = lane & 1u;
+                    const uint32_t rblk = blk0 + row;
+                    if (rblk < a.n_blocks) {
+                        const uint64_t rfirst = uint64_t(rblk) * B;
+                        const uint32_t rnb = uint32_t(min(uint64_t(B), a.n - rfirst));
+                        // quad index (ascending in memory) held by this chunk
+                        const int32_t qi = int32_t(rnb >> 2) - int32_t(q0) - kLpbInQuads + int32_t(chunk);
+                        if (qi >= 0)
+                            cp_async16(in_rows + (buf * 32u + row) * kLpbInRow + chunk * 16u,
+                                reinterpret_cast<const uint4*>(a.in + rfirst) + qi);
                     }
                 }
             }
-            __syncwarp();
+            cp_async_commit();
+        };
+
+        stage(0, 0);
+        uint32_t buf = 0;
+        for (uint32_t q0 = 0; q0 < max_quads; q0 += kLpbInQuads, buf ^= 1u) {
+            stage(q0 + kLpbInQuads, buf ^ 1u);
+            cp_async_wait<1>(); // this tile has landed (for the copies this lane issued) ...
+            __syncwarp();       // ... and for everybody else's
+            const uint8_t* my_in = in_rows + (buf * 32u + lane) * kLpbInRow;
 #pragma unroll
-            for (int j = 0; j < kLpbTileQuads; j++) {
+            for (int j = 0; j < kLpbInQuads; j++) {
                 const bool active = (q0 + uint32_t(j)) < quads;
-                const uint4 v4 = *reinterpret_cast<const uint4*>(my_in + (kLpbTileQuads - 1 - j) * 16);
+                const uint4 v4 = *reinterpret_cast<const uint4*>(my_in + (kLpbInQuads - 1 - j) * 16);
                 // walking backwards: index 4t+3 (state 0) first ... index 4t (state 3) last (ans_fold.hpp:262-271)
-                encode_one(v4.w, x0, active);
-                encode_one(v4.z, x1, active);
-                encode_one(v4.y, x2, active);
-                encode_one(v4.x, x3, active);
-            }
-            // ---- drain whole 16-byte chunks of the lane's row, carry the rest to the front ----
-            {
-                const uint32_t fill = em.wp - my_out_s; // bytes in the row (multiple of 4)
-                const uint32_t chunks = fill >> 4;
-                const uint32_t max_chunks = __reduce_max_sync(0xffffffffu, chunks);
-                const uint4* rv = reinterpret_cast<const uint4*>(my_out);
-                uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
-                for (uint32_t ci = 0; ci < max_chunks; ci++)
-                    if (ci < chunks)
-                        gv[ci] = rv[ci];
-                if (chunks != 0u) {
-                    const uint4 carry = rv[chunks];
-                    *reinterpret_cast<uint4*>(my_out) = carry;
+                uint32_t v[4] = { v4.w, v4.z, v4.y, v4.x };
+                uint32_t k[4], fr[4], base[4];
+                double rcp[4];
+                bool rn[4];
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    model(v[c], active, k[c], fr[c], base[c], rcp[c]);
+#pragma unroll
+                for (int c = 0; c < 4; c++) // state >= freq * K * 2^32 (ans_fold.hpp:105)
+                    rn[c] = active && ((uint32_t(xs[c] >> 32) >> 4) >= fr[c]);
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    if (METHOD != METHOD_INT)
+                        em.put_bytes(v[c], active ? k[c] : 0u); // raw low bytes first (ans_fold.hpp:59-63)
+                    em.put_word(uint32_t(xs[c]), rn[c]);        // then the renormalisation word (ans_fold.hpp:106-109)
                 }
-                flushed += chunks << 4;
-                em.wp = my_out_s + (fill & 15u);
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const uint64_t nx = push(xs[c], rn[c], fr[c], base[c], rcp[c]);
+                    if (active)
+                        xs[c] = nx;
+                }
             }
+            drain(5);
+            __syncwarp(); // every lane is done with this buffer before the next stage overwrites it
         }
+        cp_async_wait<0>();
 
         // flush_state x4 in chain order 0..3 (ans_fold.hpp:115-120, 275-278)
         {
-            const uint64_t s0 = x0 - lower, s1 = x1 - lower, s2 = x2 - lower, s3 = x3 - lower;
-            em.put_word(uint32_t(s0), have_block), em.put_word(uint32_t(s0 >> 32), have_block);
-            em.put_word(uint32_t(s1), have_block), em.put_word(uint32_t(s1 >> 32), have_block);
-            em.put_word(uint32_t(s2), have_block), em.put_word(uint32_t(s2 >> 32), have_block);
-            em.put_word(uint32_t(s3), have_block), em.put_word(uint32_t(s3 >> 32), have_block);
-            uint32_t fill = em.wp - my_out_s;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const uint64_t st = xs[c] - lower;
+                em.put_word(uint32_t(st), have_block);
+                em.put_word(uint32_t(st >> 32), have_block);
+            }
+            uint32_t fill = uint32_t(reinterpret_cast<uint8_t*>(em.wp) - my_out);
             const uint32_t total = flushed + fill + (em.sh >> 3);
             // last partial word, then zero padding up to the next 16-byte boundary (deterministic container)
-            asm volatile("st.shared.u32 [%0], %1;" ::"r"(em.wp), "r"(em.acc) : "memory");
+            *em.wp = em.acc;
             fill += 4u;
             while (fill & 15u) {
-                asm volatile("st.shared.u32 [%0], %1;" ::"r"(my_out_s + fill), "r"(0u) : "memory");
+                *reinterpret_cast<uint32_t*>(my_out + fill) = 0u;
                 fill += 4u;
             }
             const uint32_t chunks = (total - flushed + 15u) >> 4;
-            const uint32_t max_chunks = __reduce_max_sync(0xffffffffu, have_block ? chunks : 0u);
             const uint4* rv = reinterpret_cast<const uint4*>(my_out);
             uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
-            for (uint32_t ci = 0; ci < max_chunks; ci++)
+#pragma unroll
+            for (uint32_t ci = 0; ci < uint32_t(kLpbOutRow / 16); ci++)
                 if (have_block && ci < chunks)
                     gv[ci] = rv[ci];
             if (have_block)
@@ -256,47 +304,36 @@ __global__ void __launch_bounds__(kLpbEncWarps * 32) lpb_encode_kernel(const Enc
 // ------------------------------------------------------------------------------------------
 // The lane walks its block's payload downwards from the four states.  The compressed bytes are
 // staged in a lane-private 128-byte ring in shared memory, filled by asynchronous 16-byte copies
-// (cp.async / LDGSTS) that run kLpbPrefetch bytes ahead of the cursor: one quad (<= 28 bytes)
-// ahead is always complete, so the decode loop never waits on HBM.  Per symbol the 8 bytes
-// below the cursor are assembled from three aligned ring words; the four chains of a quad are
-// independent up to the cursor (a plain register add), which gives the lane four table lookups
-// to overlap.  Decoded symbols are staged per warp and written out in coalesced 64-byte pieces.
-constexpr int kLpbDecWarps = 8;
+// (cp.async / LDGSTS) that run kLpbPrefetch bytes ahead of the cursor: what a quad (<= 28 bytes)
+// can touch was committed one quad earlier, so the decode loop does not wait on HBM.  A quad is
+// decoded in three phases so that the lane's four chains overlap: (1) the 4 slot lookups and
+// state updates, which tell how many bytes each symbol consumes, (2) the 4 cursor positions
+// (register adds), (3) per symbol the 8 bytes below its cursor, assembled from three aligned ring
+// words.  Decoded symbols are staged per warp and written out in coalesced 64-byte pieces.
 constexpr int kLpbDecOutRow = kLpbTileQuads * 16 + 16; // 80 B
 constexpr int kLpbRing = 128;                           // bytes of ring per lane (power of two, 128-aligned rows)
 constexpr int kLpbPrefetch = 80;                        // bytes below the cursor kept in flight: >= 2 * 28 + 15
 static_assert(kLpbPrefetch + 15 + 16 <= kLpbRing, "ring too small for the prefetch distance");
-
-__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ uint32_t lds32(uint32_t smem_addr)
-{
-    uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_addr) : "memory");
-    return v;
-}
+constexpr int kLpbDecWarpBytes = 32 * (kLpbRing + kLpbDecOutRow);
 
 template <int METHOD, int TABLE>
-__global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const DecArgs a)
+__global__ void __launch_bounds__(kLpbMaxWarps * 32, 1) lpb_decode_kernel(const DecArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     constexpr bool kInt = (METHOD == METHOD_INT);
     const uint32_t frame = 1u << a.log2_frame;
     DecTables<METHOD, TABLE> tables;
     const size_t table_bytes = tables.load(a, smem_raw);
-    // rings must be 128-byte aligned (ring | offset addressing); the host adds 128 bytes of slack
+    // rings must be 128-byte aligned (ring + (offset & 127) addressing); the host adds 128 bytes of slack
     uint8_t* s_rows = smem_raw + table_bytes;
     s_rows += (128u - (uint32_t(__cvta_generic_to_shared(s_rows)) & 127u)) & 127u;
 
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
-    // per warp: 32 rings of 128 B (128-aligned), then 32 output rows
-    uint8_t* warp_base = s_rows + size_t(warp) * 32 * (kLpbRing + kLpbDecOutRow);
-    const uint32_t ring = uint32_t(__cvta_generic_to_shared(warp_base)) + lane * kLpbRing;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    // per warp: 32 rings of 128 B, then 32 output rows
+    uint8_t* warp_base = s_rows + size_t(warp) * kLpbDecWarpBytes;
+    uint8_t* ring = warp_base + lane * kLpbRing;
     uint8_t* out_rows = warp_base + 32 * kLpbRing;
     uint8_t* my_out = out_rows + lane * kLpbDecOutRow;
     const uint32_t log2_frame = a.log2_frame;
@@ -306,7 +343,7 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
     const uint32_t B = a.block_syms;
 
     const uint32_t n_tasks = (a.n_blocks + 31u) >> 5;
-    for (uint32_t task = blockIdx.x * kLpbDecWarps + warp; task < n_tasks; task += gridDim.x * kLpbDecWarps) {
+    for (uint32_t task = blockIdx.x * warps_per_cta + warp; task < n_tasks; task += gridDim.x * warps_per_cta) {
         const uint32_t blk0 = task * 32u;
         const uint32_t blk = blk0 + lane;
         const bool have_block = blk < a.n_blocks;
@@ -324,7 +361,7 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
         int32_t pos = int32_t(delta + size - 32u);
 
         // init_state x4: state c sits at payload + size - 32 + 8c (ans_fold.hpp:291-295)
-        uint64_t x0 = lower, x1 = lower, x2 = lower, x3 = lower;
+        uint64_t xs[4] = { lower, lower, lower, lower };
         if (have_block) {
             const uint32_t* words = reinterpret_cast<const uint32_t*>(pay16);
             const int32_t w = pos >> 2;
@@ -333,14 +370,12 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
 #pragma unroll
             for (int i = 0; i < 9; i++)
                 t[i] = (i < 8 || sh != 0u) ? __ldg(words + w + i) : 0u;
-            uint32_t u[8];
 #pragma unroll
-            for (int i = 0; i < 8; i++)
-                u[i] = __funnelshift_r(t[i], t[i + 1], sh);
-            x0 += (uint64_t(u[1]) << 32) | u[0];
-            x1 += (uint64_t(u[3]) << 32) | u[2];
-            x2 += (uint64_t(u[5]) << 32) | u[4];
-            x3 += (uint64_t(u[7]) << 32) | u[6];
+            for (int c = 0; c < 4; c++) {
+                const uint32_t lo = __funnelshift_r(t[2 * c], t[2 * c + 1], sh);
+                const uint32_t hi = __funnelshift_r(t[2 * c + 1], t[2 * c + 2], sh);
+                xs[c] += (uint64_t(hi) << 32) | lo;
+            }
         }
 
         // ring fill: everything from the chunk that holds byte pos-1 down to pos - kLpbPrefetch
@@ -358,35 +393,37 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
         };
         prefetch((kLpbPrefetch + 15 + 15) / 16 + 1);
 
-        auto decode_one = [&](uint64_t& x, bool active) -> uint32_t {
-            const uint32_t slot = uint32_t(x) & frame_mask;
-            uint32_t freq, offset, mapped, k;
-            tables.lookup(slot, freq, offset, mapped, k);
-            uint64_t nx = uint64_t(freq) * (x >> log2_frame) + offset;
-            const bool renorm = active && nx < lower;
-            // bytes [pos-8, pos) from the three aligned ring words that cover them
-            const uint32_t p1 = uint32_t(pos - 1);
-            const uint32_t w0 = lds32(ring | (p1 & uint32_t(kLpbRing - 4)));
-            const uint32_t w1 = lds32(ring | ((p1 - 4u) & uint32_t(kLpbRing - 4)));
-            const uint32_t sh = (p1 & 3u) * 8u + 8u; // 8, 16, 24, 32
-            const uint32_t win_hi = __funnelshift_rc(w1, w0, sh); // the 4 bytes just below the cursor
-            if (renorm) // renormalisation word first (ans_fold.hpp:221-224)
+        // Word window: t0 = the aligned ring word that holds byte pos-1, t1 and t2 the two words below it.
+        auto ring_word = [&](int32_t word_index) -> uint32_t {
+            return *reinterpret_cast<const uint32_t*>(ring + ((uint32_t(word_index) << 2) & uint32_t(kLpbRing - 4)));
+        };
+        // phase 1 of a symbol: slot lookup + state update; returns the bytes it consumes
+        auto advance = [&](uint64_t x, bool active, uint64_t& nx, bool& renorm, uint32_t& mapped, uint32_t& k) -> uint32_t {
+            uint32_t freq, offset;
+            tables.lookup(uint32_t(x) & frame_mask, freq, offset, mapped, k);
+            nx = uint64_t(freq) * (x >> log2_frame) + offset;
+            renorm = active && nx < lower;
+            return active ? k + (renorm ? 4u : 0u) : 0u;
+        };
+        // phase 3: renormalisation word first (ans_fold.hpp:221-224), then k raw low bytes (ans_fold.hpp:135-147),
+        // both taken from the 8 bytes below cursor p, which the three cached words t0 t1 t2 cover
+        auto finish = [&](int32_t p, uint32_t t0, uint32_t t1, uint32_t t2, uint64_t& nx, bool renorm, uint32_t mapped,
+                          uint32_t k) -> uint32_t {
+            const uint32_t sh = (uint32_t(p - 1) & 3u) * 8u + 8u; // 8, 16, 24, 32
+            const uint32_t win_hi = __funnelshift_rc(t1, t0, sh); // the 4 bytes just below the cursor
+            if (renorm)
                 nx = (nx << kRadixLog2) | uint64_t(win_hi);
             uint32_t value = mapped;
-            uint32_t c = renorm ? 4u : 0u;
-            if (!kInt) { // then k raw low bytes (ans_fold.hpp:135-147)
-                const uint32_t w2 = lds32(ring | ((p1 - 8u) & uint32_t(kLpbRing - 4)));
-                const uint32_t win_lo = __funnelshift_rc(w2, w1, sh);
+            if (!kInt) {
+                const uint32_t win_lo = __funnelshift_rc(t2, t1, sh); // the 4 bytes below those
                 const uint32_t exc_src = renorm ? win_lo : win_hi;
                 value += __funnelshift_rc(exc_src, 0u, 32u - 8u * k);
-                c += k;
-            }
-            if (active) {
-                x = nx;
-                pos -= int32_t(c);
             }
             return value - rfold_bias;
         };
+        cp_async_wait<0>();
+        int32_t wi = (pos - 1) >> 2; // word index of byte pos-1 (pos >= 1: at least the states' first byte is below... )
+        uint32_t t0 = ring_word(wi), t1 = ring_word(wi - 1), t2 = ring_word(wi - 2);
 
         for (uint32_t q0 = 0; q0 < max_quads; q0 += kLpbTileQuads) {
             __syncwarp();
@@ -396,13 +433,48 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
                 // keep the ring kLpbPrefetch bytes ahead; everything this quad can touch was committed a quad ago
                 prefetch(3);
                 cp_async_wait<1>();
-                uint4 o;
-                // index 4t+g is decoded by state 3-g (ans_fold.hpp:300-305)
-                o.x = decode_one(x3, active);
-                o.y = decode_one(x2, active);
-                o.z = decode_one(x1, active);
-                o.w = decode_one(x0, active);
-                *reinterpret_cast<uint4*>(my_out + j * 16) = o;
+                uint64_t nx[4];
+                bool rn[4];
+                uint32_t mp[4], k[4], c[4], val[4];
+                int32_t p[5], w[5];
+                // index 4t+g is decoded by state 3-g (ans_fold.hpp:300-305): g = 0 reads the stream first
+#pragma unroll
+                for (int g = 0; g < 4; g++)
+                    c[g] = advance(xs[3 - g], active, nx[g], rn[g], mp[g], k[g]);
+                p[0] = pos;
+                w[0] = wi;
+#pragma unroll
+                for (int g = 0; g < 4; g++) {
+                    p[g + 1] = p[g] - int32_t(c[g]);
+                    w[g + 1] = (p[g + 1] - 1) >> 2;
+                }
+                // every word the four windows will need beyond the cached three: a symbol moves the
+                // cursor across at most two word boundaries (7 bytes), so two predicated loads each
+                uint32_t ra[4], rb[4];
+#pragma unroll
+                for (int g = 0; g < 4; g++) {
+                    ra[g] = (w[g + 1] < w[g]) ? ring_word(w[g] - 3) : 0u;
+                    rb[g] = (!kInt && w[g + 1] < w[g] - 1) ? ring_word(w[g] - 4) : 0u;
+                }
+#pragma unroll
+                for (int g = 0; g < 4; g++) {
+                    val[g] = finish(p[g], t0, t1, t2, nx[g], rn[g], mp[g], k[g]);
+                    if (active)
+                        xs[3 - g] = nx[g];
+                    if (w[g + 1] < w[g]) {
+                        t0 = t1;
+                        t1 = t2;
+                        t2 = ra[g];
+                    }
+                    if (!kInt && w[g + 1] < w[g] - 1) {
+                        t0 = t1;
+                        t1 = t2;
+                        t2 = rb[g];
+                    }
+                }
+                pos = p[4];
+                wi = w[4];
+                *reinterpret_cast<uint4*>(my_out + j * 16) = make_uint4(val[0], val[1], val[2], val[3]);
             }
             __syncwarp();
             // coalesced write-out: 8 rows x 64 bytes per instruction
@@ -428,9 +500,17 @@ __global__ void __launch_bounds__(kLpbDecWarps * 32) lpb_decode_kernel(const Dec
             cp_async_wait<0>();
             for (uint32_t s = 0; s < 3u; s++) {
                 const bool active = s < tail;
-                const uint32_t v = decode_one(x0, active);
-                if (active)
+                uint64_t nx;
+                bool rn;
+                uint32_t mp, k;
+                const uint32_t c = advance(xs[0], active, nx, rn, mp, k);
+                t0 = ring_word((pos - 1) >> 2), t1 = ring_word(((pos - 1) >> 2) - 1), t2 = ring_word(((pos - 1) >> 2) - 2);
+                const uint32_t v = finish(pos, t0, t1, t2, nx, rn, mp, k);
+                pos -= int32_t(c);
+                if (active) {
+                    xs[0] = nx;
                     a.out[first + 4u * quads + s] = v;
+                }
             }
         }
         cp_async_wait<0>();

@@ -63,9 +63,13 @@ for (kid, name) in kernels:
     wave = collections.Counter()
     stalls = collections.Counter()
     tot = 0
+    seen = set()
     for r in src[hdr_i + 1:]:
         if len(r) < len(h) or not r[col["Instructions Executed"]].isdigit():
             continue
+        if r[col["Address"]] in seen:  # the page repeats the SASS rows once per view
+            continue
+        seen.add(r[col["Address"]])
         sass = r[col["Source"]].strip()
         toks = sass.split()
         op = toks[1] if toks and toks[0].startswith("@") and len(toks) > 1 else (toks[0] if toks else "?")
