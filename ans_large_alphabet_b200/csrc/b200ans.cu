@@ -17,6 +17,7 @@
 #include "../host/prelude.hpp"
 #include "kernels.cuh"
 #include "lpb_kernels.cuh"
+#include "lpb3_kernels.cuh"
 
 using namespace b200ans;
 
@@ -844,13 +845,15 @@ template <int METHOD> int launch_encode_t(b200ans_ctx* c, const EncArgs& a)
 }
 
 // Lane-per-block kernels need 32 blocks per warp: worth it once that still fills the GPU.
-bool use_lpb(const b200ans_ctx* c, uint32_t n_blocks)
+bool use_lpb(const b200ans_ctx* c, uint32_t n_blocks, bool encode)
 {
     if (c->kernel_path == B200ANS_PATH_GROUP)
         return false;
     if (c->kernel_path == B200ANS_PATH_LPB)
         return true;
-    return n_blocks >= uint32_t(c->num_sms) * 32u * 8u; // >= 8 LPB warps per SM
+    // The L3 encoder beats the 4-lanes-per-block encoder from one full warp of blocks upwards (measured: 1e7 and
+    // 1e8 symbols, 0.44 ms against 0.67 / 0.69 ms); the decoder needs >= 8 LPB warps per SM to win.
+    return encode ? n_blocks >= 32u : n_blocks >= uint32_t(c->num_sms) * 32u * 8u;
 }
 
 // Lane-per-block launch shape: ONE CTA per SM.  A task (32 blocks) runs for the whole kernel, so
@@ -889,6 +892,126 @@ template <int METHOD, int TABLE> int launch_lpb_decode_tt(b200ans_ctx* c, const 
     return launch_lpb(c, lpb_decode_kernel<METHOD, TABLE>, align_up(table_bytes, 16), kLpbDecWarpBytes, a.n_blocks, &a);
 }
 
+// ---- L3 encoder (lpb3_kernels.cuh): TMA input tiles + replicated shared-memory table ---------
+typedef CUresult (*tensor_map_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+tensor_map_encode_fn tensor_map_encoder()
+{
+    static tensor_map_encode_fn fn = []() -> tensor_map_encode_fn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return reinterpret_cast<tensor_map_encode_fn>(p);
+    }();
+    return fn;
+}
+
+int env_int(const char* name, int dflt)
+{
+    const char* v = std::getenv(name);
+    return v && *v ? std::atoi(v) : dflt;
+}
+
+// largest input value whose (folded) symbol is below n_entries; the mappings are monotone
+uint32_t max_value_below(int method, uint32_t f, uint32_t n_entries)
+{
+    uint64_t lo = 0, hi = 0xFFFFFFFFull; // invariant: map(lo) < n_entries
+    uint32_t k;
+    auto sym = [&](uint32_t v) { return method == METHOD_MSB ? msb_map(v, k) : fold_map(v, f, k); };
+    if (sym(0xFFFFFFFFu) < n_entries)
+        return 0xFFFFFFFFu;
+    while (lo + 1 < hi) {
+        const uint64_t mid = (lo + hi) / 2;
+        if (sym(uint32_t(mid)) < n_entries)
+            lo = mid;
+        else
+            hi = mid;
+    }
+    return uint32_t(lo);
+}
+
+// returns B200ANS_OK after a launch, 1 when this input / model is not for the L3 kernel
+template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, const EncArgs& a)
+{
+    constexpr int TQ = CFG::TQ;
+    if (!a.fast_div || a.block_syms % 128u != 0u || a.n / a.block_syms == 0 || env_int("B200ANS_NO_L3", 0))
+        return 1;
+    tensor_map_encode_fn encode = tensor_map_encoder();
+    if (!encode)
+        return 1;
+    const uint32_t alphabet = METHOD == METHOD_INT ? a.n_entries + 1u : uint32_t(alphabet_bins(METHOD, a.fidelity, 0));
+    const uint32_t alloc = METHOD == METHOD_INT ? a.n_entries + 1u : a.n_entries;
+    const uint32_t n_tasks = (a.n_blocks + 31) / 32;
+    const uint32_t sms = uint32_t(c->num_sms);
+    // replicas: as many as leave room for one balanced wave of warps (or 16 warps, whichever is less)
+    const uint32_t want_warps = std::min<uint32_t>(CFG::MAXW, std::max<uint32_t>(1, (n_tasks + sms - 1) / sms));
+    int rep = -1;
+    uint32_t max_warps = 0;
+    const int rep_hi = std::min(3, env_int("B200ANS_L3_REP", 3));
+    for (int r = rep_hi; r >= 0; r--) {
+        const size_t table_bytes = align_up((size_t(alloc) << r) * 16, 1024);
+        // every address the mapping can produce must stay inside the CTA's shared-memory window
+        if ((size_t(alphabet) << r) * 16 + 64 > c->max_smem || table_bytes + 2048 > c->max_smem)
+            continue;
+        const uint32_t fit = uint32_t(std::min<size_t>(CFG::MAXW, (c->max_smem - table_bytes - 1024) / L3Geom<CFG>::kWarpBytes));
+        if (fit >= std::min<uint32_t>(want_warps, 16u) || r == 0) {
+            rep = r;
+            max_warps = fit;
+            break;
+        }
+    }
+    if (rep < 0 || max_warps == 0)
+        return 1;
+    max_warps = std::min<uint32_t>(max_warps, uint32_t(std::max(1, env_int("B200ANS_L3_WARPS", CFG::MAXW))));
+    const uint32_t waves = (n_tasks + sms * max_warps - 1) / (sms * max_warps);
+    const uint32_t warps = std::max<uint32_t>(1, std::min<uint32_t>(max_warps, (n_tasks + sms * waves - 1) / (sms * waves)));
+    const uint32_t grid = std::min<uint32_t>(sms, (n_tasks + warps - 1) / warps);
+
+    Enc3Args g {};
+    g.rep_log2 = uint32_t(rep);
+    g.table_alloc = alloc;
+    g.n_full_blocks = uint32_t(a.n / a.block_syms);
+    g.max_value = METHOD == METHOD_INT ? 0xFFFFFFFFu : max_value_below(METHOD, a.fidelity, a.n_entries);
+
+    CUtensorMap tmap;
+    const cuuint64_t dims[2] = { a.block_syms, g.n_full_blocks };
+    const cuuint64_t strides[1] = { cuuint64_t(a.block_syms) * 4 };
+    const cuuint32_t box[2] = { 4 * TQ, 32 };
+    const cuuint32_t estr[2] = { 1, 1 };
+    const int promo = env_int("B200ANS_L3_PROMO", 3);
+    const CUresult rc = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint32_t*>(a.in), dims, strides, box, estr,
+        CU_TENSOR_MAP_INTERLEAVE_NONE,
+        TQ == 2 ? CU_TENSOR_MAP_SWIZZLE_32B : TQ == 4 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+        promo == 3 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : promo == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_NONE,
+        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS)
+        return 1;
+
+    // the full window: symbols beyond the model read (and flag) whatever lies behind the table
+    const size_t smem = c->max_smem;
+    auto k = lpb3_encode_kernel<METHOD, 0, CFG>;
+    auto k1 = lpb3_encode_kernel<METHOD, 1, CFG>;
+    const bool f1 = METHOD == METHOD_FOLD && a.fidelity == 1;
+    CU(c, cudaFuncSetAttribute(f1 ? k1 : k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    if (f1)
+        k1<<<grid, warps * 32, smem, c->stream>>>(a, g, tmap);
+    else
+        k<<<grid, warps * 32, smem, c->stream>>>(a, g, tmap);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
+template <int METHOD> int launch_lpb3_encode_t(b200ans_ctx* c, const EncArgs& a)
+{
+    return launch_lpb3_encode_cfg<METHOD, L3Cfg>(c, a);
+}
+
 // encode d_src into scratch slots + block_bytes using the current encoder model
 int launch_encode(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t block_syms, uint32_t n_blocks,
     uint8_t* d_scratch, size_t stride, uint32_t* d_block_bytes)
@@ -910,7 +1033,16 @@ int launch_encode(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t bloc
     a.error_flag = c->d_err();
     a.fast_div = c->max_nfreq < 65536u ? 1u : 0u;
     CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
-    if (use_lpb(c, n_blocks)) {
+    if (use_lpb(c, n_blocks, true)) {
+        int rc3 = 1;
+        switch (c->enc_method) {
+        case METHOD_INT: rc3 = launch_lpb3_encode_t<METHOD_INT>(c, a); break;
+        case METHOD_FOLD: rc3 = launch_lpb3_encode_t<METHOD_FOLD>(c, a); break;
+        case METHOD_MSB: rc3 = launch_lpb3_encode_t<METHOD_MSB>(c, a); break;
+        default: break;
+        }
+        if (rc3 <= 0)
+            return rc3;
         switch (c->enc_method) {
         case METHOD_INT: return launch_lpb_encode_t<METHOD_INT>(c, a);
         case METHOD_FOLD: return launch_lpb_encode_t<METHOD_FOLD>(c, a);
@@ -960,7 +1092,7 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     a.n_present = c->dec_n_present;
     a.cnt_bytes = c->dec_cnt_bytes;
     const size_t frame = size_t(1) << c->dec_log2_frame;
-    if (use_lpb(c, n_blocks)) {
+    if (use_lpb(c, n_blocks, false)) {
         const size_t lbudget = c->max_smem > size_t(16) * kLpbDecWarpBytes + 4096 ? c->max_smem - size_t(16) * kLpbDecWarpBytes - 4096 : 0;
         if (c->dec_method == METHOD_INT) {
             const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_cnt_bytes);

@@ -1,0 +1,482 @@
+// b200ans device code (sm_100a): lane-per-block encoder, third generation ("L3").
+//
+// ncu on the second-generation kernel (lpb_kernels.cuh) showed it bound by two things at once:
+// the integer ALU pipe (46 ALU instructions per symbol at one warp instruction per 2 cycles and
+// scheduler) and the shared-memory data pipe (21 wavefronts per 32 symbols).  This kernel keeps
+// the decomposition -- one lane owns one block and carries the four interleaved rANS states of
+// ans_fold.hpp:250-278 in registers, a warp works on 32 consecutive blocks -- and attacks both:
+//
+//  * input tiles (32 blocks x 8 symbols) arrive by TMA (cp.async.bulk.tensor.2d, 32-byte
+//    swizzle, mbarrier completion): one instruction per warp and tile instead of 32 LDGSTS
+//    lanes whose sectors each cost a shared-memory wavefront;
+//  * the {freq, base, reciprocal} table is REPLICATED R times in shared memory, replica r
+//    interleaved so that it only occupies the 16-byte bank group r: the 8 lanes of a quarter
+//    warp read 8 different bank groups, so a random 128-bit lookup costs 4 wavefronts, not ~10;
+//  * the state update runs on the FP64 and FMA pipes (exact reciprocal divide by DFMA, the
+//    multiply by the frame size M as IMAD/IMAD.HI), the byte packer is a one-hot multiplier
+//    (acc += piece * 2^fill as IMAD/IMAD.HI, the fill advances by a rotate), validity is a
+//    sticky NaN accumulated by an FFMA -- what is left on the ALU pipe is ~16 instructions
+//    per symbol.
+//
+// Byte-identity with the reference coder run on each block is unchanged: the emission order
+// inside a block is exactly the serial order (ans_fold.hpp:100-112,257-278).
+#pragma once
+
+#include <cuda.h>
+
+#include "lpb_kernels.cuh"
+
+namespace b200ans {
+
+// Launch shapes.  TQ = quads per lane and input tile (rows of 16 * TQ bytes), STAGES = input tiles in
+// flight per warp, DQ = quads between drains of the lane's output row, MAXW = warps per CTA (one CTA per SM).
+// Measured on B200 (tools/micro/gather_bw.cu): the TMA gather of 32 rows x 64 B runs at 5.8 TB/s with 14
+// warps per SM but drops to 3.9 TB/s with 28 (more streams in flight than the memory system likes), so the
+// default shape is few, well-fed warps with registers to spare.
+struct L3Cfg {
+    static constexpr int TQ = 4, STAGES = 2, DQ = 2, MAXW = 16;
+};
+// output row: 12 carried bytes + 28 per quad + slack for the final partial word; an odd number of 16-byte chunks
+template <class CFG> struct L3Geom {
+    static constexpr int kTileBytes = 32 * CFG::TQ * 16;
+    static constexpr int kOutRow = CFG::DQ == 1 ? 48 : 112;
+    static constexpr int kWarpBytes = CFG::STAGES * kTileBytes + 32 * kOutRow + 8 * CFG::STAGES;
+    static_assert(12 + 28 * CFG::DQ + 4 <= kOutRow && (kOutRow / 16) % 2 == 1, "output row too small");
+    static_assert(CFG::TQ % CFG::DQ == 0 && (CFG::TQ == 2 || CFG::TQ == 4 || CFG::TQ == 8), "tile shape");
+};
+
+struct Enc3Args {
+    uint32_t rep_log2;      // log2 of the number of table replicas (0..3)
+    uint32_t table_alloc;   // entries per replica: covers every symbol the mapping can produce
+    uint32_t n_full_blocks; // rows of the tensor map (blocks that hold block_syms symbols)
+    uint32_t max_value;     // FOLD / MSB: largest input value whose symbol is < n_entries
+};
+
+// ---- mbarrier / TMA (PTX ISA 8.x, sm_90+) ---------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "L3_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra L3_DONE;\n"
+        "bra L3_WAIT;\n"
+        "L3_DONE:\n"
+        "}\n" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+// box (16 symbols x 32 blocks) at (column x, row y) of the [n_full_blocks][block_syms] view of the input
+__device__ __forceinline__ void tma_load_tile(uint32_t dst, const CUtensorMap* map, int32_t x, int32_t y, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+                 "l"(reinterpret_cast<uint64_t>(map)), "r"(x), "r"(y), "r"(bar)
+                 : "memory");
+}
+
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0u;
+}
+
+__device__ __forceinline__ uint32_t bfind_u32(uint32_t x)
+{
+    uint32_t r;
+    asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(x));
+    return r;
+}
+__device__ __forceinline__ uint32_t mad_lo(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t mad_hi(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t r;
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+
+// Word-granular byte packer.  `acc` holds the pending bytes (little-endian, fewer than 4),
+// `am` = 2^(8 * pending bytes) as a one-hot multiplier: appending a piece is acc + piece * am
+// (low half: the word to store, high half: what spills into the next word), the fill advances
+// by rotating `am`, and a completed word shows as the rotate wrapping around.
+struct L3Packer {
+    uint32_t acc;
+    uint32_t am;
+    uint32_t wp; // shared-memory address of the next word of the lane's row
+    __device__ __forceinline__ void put_bits(uint32_t piece, uint32_t nbits) // nbits in {0, 8, 16, 24}, piece < 2^nbits
+    {
+        const uint32_t t = mad_lo(piece, am, acc);
+        const uint32_t hi = mad_hi(piece, am, 0u);
+        const uint32_t am2 = __funnelshift_l(am, am, nbits);
+        const bool full = am2 < am;
+        if (full) {
+            sts32(wp, t);
+            wp += 4u;
+        }
+        acc = full ? hi : t;
+        am = am2;
+    }
+    __device__ __forceinline__ void put_word(uint32_t w, bool on)
+    {
+        const uint32_t t = mad_lo(w, am, acc);
+        const uint32_t hi = mad_hi(w, am, 0u);
+        if (on) {
+            sts32(wp, t);
+            wp += 4u;
+            acc = hi;
+        }
+    }
+    __device__ __forceinline__ uint32_t pending_bytes() const { return bfind_u32(am) >> 3; }
+};
+
+// value -> shared-memory address of its table entry (replica chosen by `lane_tb`) and 8 * (raw low bytes)
+template <int METHOD, int FID>
+__device__ __forceinline__ uint32_t l3_entry_addr(uint32_t v, uint32_t lane_tb, uint32_t ent_stride, uint32_t k8_stride, uint32_t f,
+    uint32_t n_entries, uint32_t& k8)
+{
+    if (METHOD == METHOD_INT) {
+        k8 = 0;
+        return mad_lo(min(v, n_entries), ent_stride, lane_tb); // entry n_entries is the "no such symbol" sentinel
+    }
+    uint32_t fl;
+    if (METHOD == METHOD_MSB) {
+        // k = (x > 2^8) + (x > 2^16) + (x > 2^24)  (ans_msb.hpp:41-73)  ==  highest bit of (x - 1) / 8
+        fl = bfind_u32((max(v, 1u) - 1u) | 1u);
+    } else if (FID == 1) {
+        fl = bfind_u32(v | 1u); // thres = 2^8: k = highest bit / 8  (ans_fold.hpp:38-50)
+    } else {
+        fl = bfind_u32(v | (1u << (f - 1u))) - (f - 1u); // thres = 2^(f+7)
+    }
+    k8 = fl & 0x18u;
+    const uint32_t xs = v >> k8;
+    // symbol = xs + k * step  ->  address = xs * stride + k8 * (step * stride / 8) + replica base
+    return mad_lo(xs, ent_stride, mad_lo(k8, k8_stride, lane_tb));
+}
+
+template <int METHOD, int FID, class CFG>
+__global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const EncArgs a, const Enc3Args g, const __grid_constant__ CUtensorMap tmap)
+{
+    constexpr int TQ = CFG::TQ, STAGES = CFG::STAGES, DQ = CFG::DQ;
+    constexpr int kTileBytes = L3Geom<CFG>::kTileBytes;
+    constexpr int kOutRow = L3Geom<CFG>::kOutRow;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // layout: [table: table_alloc << rep_log2 entries][input tiles: warps x STAGES, 1 KiB aligned][output rows][mbarriers]
+    // (the table comes first: a symbol beyond the model then reads -- and flags -- whatever follows, inside the window)
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    const uint32_t lane = lane_id();
+    const uint32_t warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0); // warp-uniform for the compiler too
+    const uint32_t s_base = smem_u32(smem_raw);
+    const uint32_t s_table = s_base;
+    const uint32_t table_bytes = (g.table_alloc << g.rep_log2) * 16u;
+    const uint32_t s_tiles = s_base + ((table_bytes + 1023u) & ~1023u);
+    const uint32_t s_rows = s_tiles + warps_per_cta * uint32_t(STAGES * kTileBytes);
+    const uint32_t s_bars = s_rows + warps_per_cta * 32u * kOutRow;
+
+    // ---- replicated table: entry e of replica r at ((e << rep_log2) + r) * 16 ---------------
+    {
+        const uint32_t total = g.table_alloc << g.rep_log2;
+        const uint4* src = reinterpret_cast<const uint4*>(a.table);
+        for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) {
+            const uint32_t e = i >> g.rep_log2;
+            uint4 raw = make_uint4(0u, 0u, 0u, 0x7FF80000u); // NaN reciprocal marks "no such symbol"
+            if (e < a.n_entries) {
+                const uint4 t = __ldg(src + e);
+                if (t.x != 0u)
+                    raw = make_uint4(0u - t.x, t.y, t.z, t.w); // {-freq, base, reciprocal}
+            }
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(s_table + i * 16u), "r"(raw.x), "r"(raw.y), "r"(raw.z), "r"(raw.w) : "memory");
+        }
+    }
+    const uint32_t bar0 = s_bars + warp * uint32_t(8 * STAGES);
+    if (lane == 0) {
+#pragma unroll
+        for (int st = 0; st < STAGES; st++)
+            mbar_init(bar0 + 8u * st, 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    const uint32_t log2_frame = a.log2_frame;
+    const uint32_t frame = 1u << log2_frame;
+    const uint32_t f = a.fidelity;
+    const uint32_t lower_hi = (log2_frame + 4u >= 32u) ? (1u << (log2_frame + 4u - 32u)) : 0u; // L = 16 M (ans_fold.hpp:91)
+    const uint32_t lower_lo = (log2_frame + 4u >= 32u) ? 0u : (1u << (log2_frame + 4u));
+    const uint32_t neg_bias = 0u - (0x43300000u << log2_frame); // cancels the double's exponent bits in q_hi * M
+    const uint32_t ent_stride = 16u << g.rep_log2;
+    const uint32_t step = (METHOD == METHOD_MSB) ? 256u : (255u << (f - 1u));
+    const uint32_t k8_stride = (METHOD == METHOD_INT) ? 0u : (step * ent_stride) >> 3;
+    const uint32_t lane_tb = s_table + ((lane & ((1u << g.rep_log2) - 1u)) << 4);
+    const uint32_t B = a.block_syms;
+    const uint32_t my_tiles = s_tiles + warp * uint32_t(STAGES * kTileBytes);
+    const uint32_t my_row_in = lane * (16u * TQ);                 // row offset inside a tile
+    // 32 / 64 / 128-byte swizzle: the 16-byte chunk index is XORed with address bits 7.. (Swizzle<log2 TQ, 4, 3>)
+    const uint32_t swz = ((lane >> (TQ == 2 ? 2 : TQ == 4 ? 1 : 0)) & uint32_t(TQ - 1)) << 4;
+    const uint32_t my_out = s_rows + (warp * 32u + lane) * kOutRow;
+    const double two52 = 4503599627370496.0;
+    uint32_t phases = 0; // bit st: parity of the phase the next wait on stage st's mbarrier is for
+
+    const uint32_t n_tasks = (a.n_blocks + 31u) >> 5;
+    for (uint32_t task = blockIdx.x * warps_per_cta + warp; task < n_tasks; task += gridDim.x * warps_per_cta) {
+        const uint32_t blk0 = task * 32u;
+        const uint32_t blk = blk0 + lane;
+        const bool have_block = blk < a.n_blocks;
+        uint8_t* dst = a.scratch + uint64_t(blk) * a.stride;
+        // full task: every block of it that exists holds B symbols (B is a multiple of 8)
+        const bool task_full = min(blk0 + 32u, a.n_blocks) <= g.n_full_blocks;
+
+        uint32_t xlo[4], xhi[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) { // initial_state() (ans_fold.hpp:113)
+            xlo[c] = lower_lo;
+            xhi[c] = lower_hi;
+        }
+        L3Packer pk;
+        pk.acc = 0u;
+        pk.am = 1u;
+        pk.wp = my_out;
+        uint32_t flushed = 0;
+        float badf = 0.f;
+        uint32_t vmax = 0u;
+
+        auto drain = [&]() {
+            const uint32_t fill = pk.wp - my_out; // multiple of 4
+            const uint32_t chunks = fill >> 4;    // <= 2 (DQ == 1) or <= 4 (DQ == 2)
+            uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
+            if (DQ == 1) {
+                if (chunks != 0u) {
+                    const uint4 c0 = lds128(my_out);
+                    const uint4 c1 = lds128(my_out + 16u);
+                    const uint4 c2 = lds128(my_out + 32u);
+                    if (have_block) {
+                        gv[0] = c0;
+                        if (chunks > 1u)
+                            gv[1] = c1;
+                    }
+                    const uint4 carry = chunks > 1u ? c2 : c1;
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(my_out), "r"(carry.x), "r"(carry.y), "r"(carry.z), "r"(carry.w) : "memory");
+                }
+            } else {
+#pragma unroll
+                for (uint32_t ci = 0; ci < 4u; ci++)
+                    if (ci < chunks && have_block)
+                        gv[ci] = lds128(my_out + ci * 16u);
+                if (chunks != 0u) {
+                    const uint4 carry = lds128(my_out + chunks * 16u);
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(my_out), "r"(carry.x), "r"(carry.y), "r"(carry.z), "r"(carry.w) : "memory");
+                }
+            }
+            flushed += chunks << 4;
+            pk.wp = my_out + (fill & 15u);
+        };
+
+        // one quad: index 4t+3 (state 0) first ... index 4t (state 3) last (ans_fold.hpp:262-271)
+        auto code_quad = [&](const uint4 v4, bool active) {
+            uint32_t v[4] = { v4.w, v4.z, v4.y, v4.x };
+            uint32_t k8[4], nfr[4], base[4], fr16[4];
+            double rcp[4];
+            bool rn[4];
+            if (METHOD != METHOD_INT)
+                vmax = max(vmax, max(max(v[0], v[1]), max(v[2], v[3])));
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const uint32_t addr = l3_entry_addr<METHOD, FID>(v[c], lane_tb, ent_stride, k8_stride, f, a.n_entries, k8[c]);
+                const uint4 e = lds128(addr);
+                nfr[c] = e.x;
+                base[c] = e.y;
+                rcp[c] = __hiloint2double(int(e.w), int(e.z));
+                if (active)
+                    badf = fmaf(__uint_as_float(e.w), 0.f, badf); // NaN (no such symbol) sticks
+                fr16[c] = nfr[c] * 0xFFFFFFF0u;               // freq * 16
+            }
+#pragma unroll
+            for (int c = 0; c < 4; c++) // state >= freq * K * 2^32 (ans_fold.hpp:105)
+                rn[c] = active && (xhi[c] >= fr16[c]);
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                if (METHOD != METHOD_INT) { // raw low bytes first (ans_fold.hpp:59-63)
+                    uint32_t mask;
+                    asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(mask) : "r"(active ? k8[c] : 0u));
+                    pk.put_bits(v[c] & mask, active ? k8[c] : 0u);
+                }
+                pk.put_word(xlo[c], rn[c]); // then the renormalisation word (ans_fold.hpp:106-109)
+            }
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                // x -> (x / f) * M + x % f + base (ans_fold.hpp:111); x < 2^52 after the renormalisation
+                const uint32_t y_lo = rn[c] ? xhi[c] : xlo[c];
+                const uint32_t y_hi = rn[c] ? 0x43300000u : (xhi[c] | 0x43300000u);
+                const double xd = __hiloint2double(int(y_hi), int(y_lo)) - two52;
+                const double t = __fma_rz(xd, rcp[c], two52); // 2^52 + floor(x / f), see ans_push52
+                const uint32_t q_lo = uint32_t(__double2loint(t));
+                const uint32_t q_hr = uint32_t(__double2hiint(t)); // 0x43300000 + (q >> 32)
+                const uint32_t r = mad_lo(q_lo, nfr[c], y_lo);     // x - q * f  (< f)
+                const uint32_t nlo = mad_lo(q_lo, frame, r + base[c]); // r + base < M: no carry into the shifted quotient
+                const uint32_t nhi = mad_lo(q_hr, frame, mad_hi(q_lo, frame, neg_bias));
+                if (active) {
+                    xlo[c] = nlo;
+                    xhi[c] = nhi;
+                }
+            }
+        };
+
+        if (task_full) {
+            // tiles of 4 TQ symbols per block, walking backwards, STAGES - 1 tiles ahead of the coder
+            const uint32_t tiles = B / (4u * TQ);
+            auto issue = [&](uint32_t t, uint32_t st) { // tile t -> stage st
+                if (elect_one()) {
+                    mbar_expect_tx(bar0 + st * 8u, kTileBytes);
+                    tma_load_tile(my_tiles + st * kTileBytes, &tmap, int32_t(B - 4u * TQ * (t + 1u)), int32_t(blk0), bar0 + st * 8u);
+                }
+            };
+#pragma unroll
+            for (int st = 0; st < STAGES - 1; st++)
+                if (uint32_t(st) < tiles)
+                    issue(uint32_t(st), uint32_t(st));
+            uint32_t st = 0;              // stage of tile t
+            uint32_t st_next = STAGES - 1; // stage of tile t + STAGES - 1
+            for (uint32_t t = 0; t < tiles; t++) {
+                __syncwarp(); // every lane has finished reading the stage that is refilled now
+                if (t + uint32_t(STAGES - 1) < tiles)
+                    issue(t + uint32_t(STAGES - 1), st_next);
+                mbar_wait(bar0 + st * 8u, (phases >> st) & 1u);
+                phases ^= 1u << st;
+                const uint32_t row = my_tiles + st * kTileBytes + my_row_in;
+#pragma unroll
+                for (int j = TQ - 1; j >= 0; j -= 2) { // the last symbols of the tile are coded first
+                    const uint4 qa = lds128(row + (uint32_t(j * 16) ^ swz));
+                    const uint4 qb = lds128(row + (uint32_t((j - 1) * 16) ^ swz));
+                    code_quad(qa, true);
+                    if (DQ == 1)
+                        drain();
+                    code_quad(qb, true);
+                    drain();
+                }
+                st = st + 1u == uint32_t(STAGES) ? 0u : st + 1u;
+                st_next = st_next + 1u == uint32_t(STAGES) ? 0u : st_next + 1u;
+            }
+        } else {
+            // the one task that holds the partial last block: predicated, loads straight from global memory
+            const uint64_t first = uint64_t(blk) * B;
+            const uint32_t nb = have_block ? uint32_t(min(uint64_t(B), a.n - first)) : 0u;
+            const uint32_t tail = nb & 3u;
+            const uint32_t quads = nb >> 2;
+            const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
+            if (__any_sync(0xffffffffu, tail != 0u)) { // tail symbols on state 0 (ans_fold.hpp:257-261)
+                for (uint32_t s = 0; s < 3u; s++) {
+                    const bool active = s < tail;
+                    const uint32_t v = active ? __ldg(a.in + first + (nb - 1u - s)) : 0u;
+                    // run the symbol as a "quad" whose other three members are inactive: rotate it into slot 0
+                    uint32_t k8;
+                    const uint32_t addr = l3_entry_addr<METHOD, FID>(v, lane_tb, ent_stride, k8_stride, f, a.n_entries, k8);
+                    const uint4 e = lds128(addr);
+                    if (active) {
+                        badf = fmaf(__uint_as_float(e.w), 0.f, badf);
+                        vmax = max(vmax, v);
+                    }
+                    const uint32_t fr16 = e.x * 0xFFFFFFF0u;
+                    const bool rn = active && (xhi[0] >= fr16);
+                    if (METHOD != METHOD_INT) {
+                        const uint32_t kk = active ? k8 : 0u;
+                        pk.put_bits(v & ((1u << kk) - 1u), kk);
+                    }
+                    pk.put_word(xlo[0], rn);
+                    const uint32_t y_lo = rn ? xhi[0] : xlo[0];
+                    const uint32_t y_hi = rn ? 0x43300000u : (xhi[0] | 0x43300000u);
+                    const double xd = __hiloint2double(int(y_hi), int(y_lo)) - two52;
+                    const double t = __fma_rz(xd, __hiloint2double(int(e.w), int(e.z)), two52);
+                    const uint32_t q_lo = uint32_t(__double2loint(t));
+                    const uint32_t q_hr = uint32_t(__double2hiint(t));
+                    const uint32_t r = mad_lo(q_lo, e.x, y_lo);
+                    if (active) {
+                        xlo[0] = mad_lo(q_lo, frame, r + e.y);
+                        xhi[0] = mad_lo(q_hr, frame, mad_hi(q_lo, frame, neg_bias));
+                    }
+                }
+                drain();
+            }
+            const uint4* in4 = reinterpret_cast<const uint4*>(a.in + first);
+            const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+            // two quads of read-ahead in registers (consecutive quads share L1 lines)
+            uint4 nxt0 = quads > 0u ? __ldg(in4 + (quads - 1u)) : zero4;
+            uint4 nxt1 = quads > 1u ? __ldg(in4 + (quads - 2u)) : zero4;
+            for (uint32_t q = 0; q < max_quads; q += 2u) {
+                const uint4 qa = nxt0, qb = nxt1;
+                nxt0 = (q + 2u < quads) ? __ldg(in4 + (quads - 3u - q)) : zero4;
+                nxt1 = (q + 3u < quads) ? __ldg(in4 + (quads - 4u - q)) : zero4;
+                code_quad(qa, q < quads);
+                if (DQ == 1)
+                    drain();
+                code_quad(qb, q + 1u < quads);
+                drain();
+            }
+        }
+
+        // flush_state x4 in chain order 0..3 (ans_fold.hpp:115-120, 275-278)
+        {
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                // state - L as 64 bits
+                const uint32_t lo = xlo[c] - lower_lo;
+                const uint32_t hi = xhi[c] - lower_hi - (xlo[c] < lower_lo ? 1u : 0u);
+                pk.put_word(lo, true);
+                pk.put_word(hi, true);
+                if (c == 1 && DQ == 1)
+                    drain();
+            }
+            uint32_t fill = pk.wp - my_out; // <= 28
+            const uint32_t total = flushed + fill + pk.pending_bytes();
+            // last partial word, then zero padding up to the next 16-byte boundary (deterministic container)
+            sts32(pk.wp, pk.acc);
+            fill += 4u;
+            while (fill & 15u) {
+                sts32(my_out + fill, 0u);
+                fill += 4u;
+            }
+            const uint32_t chunks = (total - flushed + 15u) >> 4;
+            uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
+#pragma unroll
+            for (uint32_t ci = 0; ci < (DQ == 1 ? 2u : 4u); ci++)
+                if (have_block && ci < chunks)
+                    gv[ci] = lds128(my_out + ci * 16u);
+            if (have_block)
+                a.block_bytes[blk] = total;
+        }
+        bool bad = badf != badf;
+        if (METHOD != METHOD_INT)
+            bad = bad || vmax > g.max_value;
+        if (bad && have_block)
+            *a.error_flag = 1u;
+        __syncwarp();
+    }
+}
+
+} // namespace b200ans
