@@ -166,11 +166,11 @@ size_t alphabet_bins(int method, uint32_t f, uint32_t max_value)
     }
 }
 
-// worst-case payload bytes of one block (+16 so 16-byte chunk stores never leave the slot)
+// worst-case payload bytes of one block (+32 so whole-sector stores never leave the slot); slots are 32-byte aligned
 size_t block_stride(int method, size_t block_syms)
 {
     const size_t per_sym = (method == METHOD_INT) ? 4 : 7;
-    return align_up(per_sym * block_syms + 32, 16) + 16;
+    return align_up(per_sym * block_syms + 32, 32) + 32;
 }
 
 float elapsed(cudaEvent_t a, cudaEvent_t b)
@@ -812,6 +812,12 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
 // ==========================================================================================
 namespace {
 
+int env_int(const char* name, int dflt)
+{
+    const char* v = std::getenv(name);
+    return v && *v ? std::atoi(v) : dflt;
+}
+
 template <class K> int persistent_grid(b200ans_ctx* c, K kernel, int threads, size_t smem, uint32_t n_tasks, int warps)
 {
     int per_sm = 0;
@@ -859,10 +865,11 @@ bool use_lpb(const b200ans_ctx* c, uint32_t n_blocks, bool encode)
 // Lane-per-block launch shape: ONE CTA per SM.  A task (32 blocks) runs for the whole kernel, so
 // the tasks are spread in balanced waves: waves = ceil(tasks / (SMs * max warps)), and every CTA
 // gets ceil(tasks / (SMs * waves)) warps -- 2^30 symbols are 4096 tasks = one wave of 28 warps per SM.
-template <class K> int launch_lpb(b200ans_ctx* c, K k, size_t table_bytes, size_t warp_bytes, uint32_t n_blocks, const void* args)
+template <class K>
+int launch_lpb(b200ans_ctx* c, K k, size_t table_bytes, size_t warp_bytes, uint32_t n_blocks, const void* args, int warp_cap = kLpbMaxWarps)
 {
     const size_t room = c->max_smem > table_bytes + 1024 ? c->max_smem - table_bytes - 1024 : 0;
-    const uint32_t max_warps = uint32_t(std::max<size_t>(1, std::min<size_t>(kLpbMaxWarps, room / warp_bytes)));
+    const uint32_t max_warps = uint32_t(std::max<size_t>(1, std::min<size_t>(size_t(warp_cap), room / warp_bytes)));
     const uint32_t n_tasks = (n_blocks + 31) / 32;
     const uint32_t sms = uint32_t(c->num_sms);
     const uint32_t waves = (n_tasks + sms * max_warps - 1) / (sms * max_warps);
@@ -889,6 +896,17 @@ template <int METHOD> int launch_lpb_encode_t(b200ans_ctx* c, const EncArgs& a)
 
 template <int METHOD, int TABLE> int launch_lpb_decode_tt(b200ans_ctx* c, const DecArgs& a, size_t table_bytes)
 {
+    // L3 decoder (lpb3_kernels.cuh) needs 16-byte aligned output; QI = 2 stores whole 32-byte sectors
+    const uintptr_t out_addr = reinterpret_cast<uintptr_t>(a.out);
+    if ((out_addr & 15) == 0 && a.block_syms % 8u == 0u && !env_int("B200ANS_NO_L3", 0)) {
+        const size_t tb = align_up(table_bytes, 16);
+        const int shape = env_int("B200ANS_L3_DEC", 0);
+        if ((out_addr & 31) == 0 && shape == 0)
+            return launch_lpb(c, lpb3_decode_kernel<METHOD, TABLE, 2, 16>, tb + 256, L3DecGeom<2>::kWarpBytes, a.n_blocks, &a, 16);
+        if ((out_addr & 31) == 0 && shape == 2)
+            return launch_lpb(c, lpb3_decode_kernel<METHOD, TABLE, 2, 28>, tb + 256, L3DecGeom<2>::kWarpBytes, a.n_blocks, &a, 28);
+        return launch_lpb(c, lpb3_decode_kernel<METHOD, TABLE, 1, 28>, tb + 128, L3DecGeom<1>::kWarpBytes, a.n_blocks, &a, 28);
+    }
     return launch_lpb(c, lpb_decode_kernel<METHOD, TABLE>, align_up(table_bytes, 16), kLpbDecWarpBytes, a.n_blocks, &a);
 }
 
@@ -909,12 +927,6 @@ tensor_map_encode_fn tensor_map_encoder()
         return reinterpret_cast<tensor_map_encode_fn>(p);
     }();
     return fn;
-}
-
-int env_int(const char* name, int dflt)
-{
-    const char* v = std::getenv(name);
-    return v && *v ? std::atoi(v) : dflt;
 }
 
 // largest input value whose (folded) symbol is below n_entries; the mappings are monotone
@@ -1168,8 +1180,8 @@ extern "C" int b200ans_encode_blocks_device(b200ans_ctx* c, const uint32_t* d_sr
     if (!c)
         return B200ANS_E_ARG;
     if (!d_src || !d_scratch || !d_block_bytes || n == 0 || (reinterpret_cast<uintptr_t>(d_src) & 15)
-        || (reinterpret_cast<uintptr_t>(d_scratch) & 15) || (stride & 15))
-        return c->fail(B200ANS_E_ARG, "encode_blocks: null / unaligned argument");
+        || (reinterpret_cast<uintptr_t>(d_scratch) & 31) || (stride & 31))
+        return c->fail(B200ANS_E_ARG, "encode_blocks: null / unaligned argument (scratch and stride: 32 bytes)");
     if (!c->have_enc)
         return c->fail(B200ANS_E_STATE, "encode_blocks: build a model first");
     if (c->block_syms == 0 && n >= (uint64_t(1) << 32))

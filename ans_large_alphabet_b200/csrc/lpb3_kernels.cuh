@@ -24,6 +24,8 @@
 
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "lpb_kernels.cuh"
 
 namespace b200ans {
@@ -39,9 +41,9 @@ struct L3Cfg {
 // output row: 12 carried bytes + 28 per quad + slack for the final partial word; an odd number of 16-byte chunks
 template <class CFG> struct L3Geom {
     static constexpr int kTileBytes = 32 * CFG::TQ * 16;
-    static constexpr int kOutRow = CFG::DQ == 1 ? 48 : 112;
+    static constexpr int kOutRow = 112; // 28 carried bytes + 56 of two quads (+ the final partial word), 7 chunks
     static constexpr int kWarpBytes = CFG::STAGES * kTileBytes + 32 * kOutRow + 8 * CFG::STAGES;
-    static_assert(12 + 28 * CFG::DQ + 4 <= kOutRow && (kOutRow / 16) % 2 == 1, "output row too small");
+    static_assert(CFG::DQ == 2 && 28 + 28 * CFG::DQ + 4 <= kOutRow && (kOutRow / 16) % 2 == 1, "output row too small");
     static_assert(CFG::TQ % CFG::DQ == 0 && (CFG::TQ == 2 || CFG::TQ == 4 || CFG::TQ == 8), "tile shape");
 };
 
@@ -267,35 +269,35 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
         float badf = 0.f;
         uint32_t vmax = 0u;
 
+        // Whole 32-byte sectors go to global memory (a 16-byte store is a partial-sector write, which the
+        // memory system handles at less than half the speed); what is left (< 32 bytes) moves to the row's front.
         auto drain = [&]() {
             const uint32_t fill = pk.wp - my_out; // multiple of 4
-            const uint32_t chunks = fill >> 4;    // <= 2 (DQ == 1) or <= 4 (DQ == 2)
-            uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
-            if (DQ == 1) {
-                if (chunks != 0u) {
-                    const uint4 c0 = lds128(my_out);
-                    const uint4 c1 = lds128(my_out + 16u);
-                    const uint4 c2 = lds128(my_out + 32u);
-                    if (have_block) {
-                        gv[0] = c0;
-                        if (chunks > 1u)
-                            gv[1] = c1;
-                    }
-                    const uint4 carry = chunks > 1u ? c2 : c1;
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(my_out), "r"(carry.x), "r"(carry.y), "r"(carry.z), "r"(carry.w) : "memory");
+            const uint32_t sectors = fill >> 5;   // <= 2: at most 28 carried + 56 new bytes
+            uint8_t* gp = dst + flushed;
+            if (sectors != 0u) {
+                const uint4 c0 = lds128(my_out), c1 = lds128(my_out + 16u);
+                const uint4 c2 = lds128(my_out + 32u), c3 = lds128(my_out + 48u);
+                uint4 c4 = c2, c5 = c3;
+                if (sectors > 1u) {
+                    c4 = lds128(my_out + 64u);
+                    c5 = lds128(my_out + 80u);
                 }
-            } else {
-#pragma unroll
-                for (uint32_t ci = 0; ci < 4u; ci++)
-                    if (ci < chunks && have_block)
-                        gv[ci] = lds128(my_out + ci * 16u);
-                if (chunks != 0u) {
-                    const uint4 carry = lds128(my_out + chunks * 16u);
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(my_out), "r"(carry.x), "r"(carry.y), "r"(carry.z), "r"(carry.w) : "memory");
+                if (have_block) {
+                    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(gp), "r"(c0.x), "r"(c0.y), "r"(c0.z), "r"(c0.w), "r"(c1.x),
+                                 "r"(c1.y), "r"(c1.z), "r"(c1.w)
+                                 : "memory");
+                    if (sectors > 1u)
+                        asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(gp + 32), "r"(c2.x), "r"(c2.y), "r"(c2.z), "r"(c2.w),
+                                     "r"(c3.x), "r"(c3.y), "r"(c3.z), "r"(c3.w)
+                                     : "memory");
                 }
+                const uint4 k0 = c4, k1 = c5;
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(my_out), "r"(k0.x), "r"(k0.y), "r"(k0.z), "r"(k0.w) : "memory");
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(my_out + 16u), "r"(k1.x), "r"(k1.y), "r"(k1.z), "r"(k1.w) : "memory");
             }
-            flushed += chunks << 4;
-            pk.wp = my_out + (fill & 15u);
+            flushed += sectors << 5;
+            pk.wp = my_out + (fill & 31u);
         };
 
         // one quad: index 4t+3 (state 0) first ... index 4t (state 3) last (ans_fold.hpp:262-271)
@@ -375,8 +377,6 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                     const uint4 qa = lds128(row + (uint32_t(j * 16) ^ swz));
                     const uint4 qb = lds128(row + (uint32_t((j - 1) * 16) ^ swz));
                     code_quad(qa, true);
-                    if (DQ == 1)
-                        drain();
                     code_quad(qb, true);
                     drain();
                 }
@@ -433,8 +433,6 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                 nxt0 = (q + 2u < quads) ? __ldg(in4 + (quads - 3u - q)) : zero4;
                 nxt1 = (q + 3u < quads) ? __ldg(in4 + (quads - 4u - q)) : zero4;
                 code_quad(qa, q < quads);
-                if (DQ == 1)
-                    drain();
                 code_quad(qb, q + 1u < quads);
                 drain();
             }
@@ -449,10 +447,8 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                 const uint32_t hi = xhi[c] - lower_hi - (xlo[c] < lower_lo ? 1u : 0u);
                 pk.put_word(lo, true);
                 pk.put_word(hi, true);
-                if (c == 1 && DQ == 1)
-                    drain();
             }
-            uint32_t fill = pk.wp - my_out; // <= 28
+            uint32_t fill = pk.wp - my_out; // <= 28 + 32
             const uint32_t total = flushed + fill + pk.pending_bytes();
             // last partial word, then zero padding up to the next 16-byte boundary (deterministic container)
             sts32(pk.wp, pk.acc);
@@ -464,7 +460,7 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
             const uint32_t chunks = (total - flushed + 15u) >> 4;
             uint4* gv = reinterpret_cast<uint4*>(dst + flushed);
 #pragma unroll
-            for (uint32_t ci = 0; ci < (DQ == 1 ? 2u : 4u); ci++)
+            for (uint32_t ci = 0; ci < 4u; ci++)
                 if (have_block && ci < chunks)
                     gv[ci] = lds128(my_out + ci * 16u);
             if (have_block)
@@ -476,6 +472,246 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
         if (bad && have_block)
             *a.error_flag = 1u;
         __syncwarp();
+    }
+}
+
+} // namespace b200ans
+
+namespace b200ans {
+
+// ==========================================================================================
+// L3 decoder
+// ==========================================================================================
+// Same decomposition as the encoder (lane = block, the four states of ans_fold.hpp:283-311 in
+// registers).  What changed against lpb_kernels.cuh's decoder (47 ALU instructions per symbol):
+//
+//  * the payload is read as a stream of aligned 32-bit words going down, through a left-aligned
+//    bit accumulator (`acc` holds the unread low bytes of the current word at its top): the
+//    renormalisation word is acc | next >> fill, the k raw bytes are the top 8k bits -- no
+//    per-symbol window of three words, no byte positions;
+//  * the lane-private cp.async ring is refilled once per loop iteration by a warp-uniform loop
+//    (usually one trip) instead of three predicated copies per quad;
+//  * decoded quads go straight from registers to global memory as 16-byte (QI == 1) or 32-byte
+//    (QI == 2: one full sector, STG.256) stores -- no staging rows, no __syncwarp in the loop.
+template <int QI> struct L3DecGeom {
+    static constexpr int kRing = QI == 1 ? 128 : 256;      // bytes of ring per lane (power of two)
+    static constexpr int kDist = 56 * QI + 4;               // bytes below the cursor resident after a refill:
+                                                            // this iteration's 28 QI, the next one's, word alignment
+    static constexpr int kWarpBytes = 32 * kRing;
+    static_assert(kDist + 15 + 16 <= kRing, "ring too small for the prefetch distance");
+};
+
+__device__ __forceinline__ void cp_async16_s(uint32_t saddr, const void* gptr)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(gptr) : "memory");
+}
+
+struct L3Reader {
+    uint32_t acc;  // unread low bits of the current word (right-aligned, everything above is zero)
+    uint32_t fill; // how many: 0, 8, 16, 24
+    uint32_t mask; // 2^fill - 1
+    int32_t rp;    // byte offset (from the 16-byte aligned payload base) of the next word to read
+    uint32_t ring; // shared-memory address of the lane's ring (aligned to its size)
+    template <int RING> __device__ __forceinline__ uint32_t next_addr() const { return (uint32_t(rp) & uint32_t(RING - 1)) | ring; }
+    // the next 32 bits of the stream (ans_fold.hpp:221-224), consumed when `on`
+    template <int RING> __device__ __forceinline__ uint32_t get_word(bool on)
+    {
+        uint32_t t = 0u;
+        if (on) {
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t) : "r"(next_addr<RING>()));
+            rp -= 4;
+        }
+        const uint32_t w = __funnelshift_r(t, acc, fill); // acc's `fill` bits on top of the new word's upper part
+        if (on)
+            acc = t & mask;
+        return w;
+    }
+    // the next nbits (0, 8, 16 or 24) of the stream as an integer (ans_fold.hpp:135-147)
+    template <int RING> __device__ __forceinline__ uint32_t get_bits(uint32_t nbits)
+    {
+        const int32_t s = int32_t(fill) - int32_t(nbits);
+        const bool more = s < 0; // the bits run into the next word
+        uint32_t lo = acc;
+        const uint32_t hi = more ? acc : 0u;
+        if (more) {
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lo) : "r"(next_addr<RING>()));
+            rp -= 4;
+        }
+        const uint32_t v = __funnelshift_r(lo, hi, uint32_t(s)); // more: (acc : word) >> (s + 32); else acc >> s
+        fill = uint32_t(s) & 31u;
+        asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(mask) : "r"(fill));
+        acc = lo & mask;
+        return v;
+    }
+};
+
+template <int METHOD, int TABLE, int QI, int MAXW>
+__global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs a)
+{
+    constexpr int RING = L3DecGeom<QI>::kRing;
+    constexpr int DIST = L3DecGeom<QI>::kDist;
+    constexpr bool kInt = (METHOD == METHOD_INT);
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const uint32_t frame = 1u << a.log2_frame;
+    DecTables<METHOD, TABLE> tables;
+    const size_t table_bytes = tables.load(a, smem_raw);
+    uint8_t* s_rings = smem_raw + table_bytes;
+    s_rings += (uint32_t(RING) - (smem_u32(s_rings) & uint32_t(RING - 1))) & uint32_t(RING - 1); // the host adds RING bytes of slack
+
+    const uint32_t lane = lane_id();
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    const uint32_t log2_frame = a.log2_frame;
+    const uint32_t frame_mask = frame - 1u;
+    const uint32_t lower_shift = log2_frame + 4u; // L = 16 M (ans_fold.hpp:91); at most 32
+    const uint32_t lower_lo = lower_shift >= 32u ? 0u : (1u << lower_shift);
+    const uint32_t lower_hi = lower_shift >= 32u ? 1u : 0u;
+    const uint32_t rfold_bias = (METHOD == METHOD_RFOLD) ? (1u << (a.fidelity + 7)) : 0u; // ans_reorder_fold.hpp:301
+    const uint32_t B = a.block_syms;
+
+    L3Reader rd;
+    rd.ring = smem_u32(s_rings) + (warp * 32u + lane) * uint32_t(RING);
+
+    const uint32_t n_tasks = (a.n_blocks + 31u) >> 5;
+    for (uint32_t task = blockIdx.x * warps_per_cta + warp; task < n_tasks; task += gridDim.x * warps_per_cta) {
+        const uint32_t blk = task * 32u + lane;
+        const bool have_block = blk < a.n_blocks;
+        const uint64_t first = uint64_t(blk) * B;
+        const uint32_t nb = have_block ? uint32_t(min(uint64_t(B), a.n - first)) : 0u;
+        const uint32_t tail = nb & 3u;
+        const uint32_t quads = nb >> 2;
+        const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
+        const bool uniform = __all_sync(0xffffffffu, have_block && quads == max_quads);
+
+        // 16-byte aligned view of the payload; positions count bytes from pay16
+        const uint8_t* pay = a.payload + (have_block ? a.offsets[blk] : 0);
+        const uint32_t delta = uint32_t(reinterpret_cast<uintptr_t>(pay) & 15u);
+        const uint8_t* pay16 = pay - delta;
+        const uint32_t size = have_block ? a.block_bytes[blk] : 32u;
+        const int32_t p0 = int32_t(delta + size - 32u); // one past the last payload byte below the four states
+
+        // init_state x4: state c sits at payload + size - 32 + 8c (ans_fold.hpp:291-295)
+        uint32_t xlo[4] = { lower_lo, lower_lo, lower_lo, lower_lo }, xhi[4] = { lower_hi, lower_hi, lower_hi, lower_hi };
+        rd.acc = 0u;
+        rd.fill = (uint32_t(p0) & 3u) * 8u;
+        rd.mask = (1u << rd.fill) - 1u;
+        rd.rp = (p0 & ~3) - 4;
+        if (have_block) {
+            const uint32_t* words = reinterpret_cast<const uint32_t*>(pay16);
+            const int32_t w = p0 >> 2;
+            const uint32_t sh = rd.fill;
+            uint32_t t[9];
+#pragma unroll
+            for (int i = 0; i < 9; i++)
+                t[i] = (i < 8 || sh != 0u) ? __ldg(words + w + i) : 0u;
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const uint32_t lo = __funnelshift_r(t[2 * c], t[2 * c + 1], sh);
+                const uint32_t hi = __funnelshift_r(t[2 * c + 1], t[2 * c + 2], sh);
+                const uint32_t slo = xlo[c] + lo;
+                xhi[c] = xhi[c] + hi + (slo < lo ? 1u : 0u);
+                xlo[c] = slo;
+            }
+            // the word that holds byte p0 - 1 .. : its low (p0 & 3) bytes are still unread
+            rd.acc = t[0] & rd.mask;
+        }
+
+        // ring: chunks [fetched_lo, ...) are resident (or in flight); refill down to `DIST` bytes below the cursor
+        int32_t fetched_lo = (rd.rp + 4 + 15) & ~15;
+        auto refill = [&]() {
+            const int32_t want = max(rd.rp + 4 - DIST, 0) & ~15;
+            while (__any_sync(0xffffffffu, have_block && fetched_lo > want)) {
+                if (have_block && fetched_lo > want) {
+                    fetched_lo -= 16;
+                    cp_async16_s(rd.ring + (uint32_t(fetched_lo) & uint32_t(RING - 1)), pay16 + fetched_lo);
+                }
+            }
+            cp_async_commit();
+        };
+        refill();
+
+        // one symbol per chain: slot lookup + state update (ans_fold.hpp:216-220); returns the renormalisation flag
+        uint32_t nlo[4], nhi[4], mp[4], k8[4];
+        bool rn[4];
+        auto advance = [&](int g, bool active) {
+            const int c = 3 - g; // index 4t+g is decoded by state 3-g (ans_fold.hpp:300-305)
+            uint32_t freq, offset, k;
+            tables.lookup(xlo[c] & frame_mask, freq, offset, mp[g], k);
+            k8[g] = active ? k * 8u : 0u;
+            const uint32_t q_lo = __funnelshift_r(xlo[c], xhi[c], log2_frame);
+            const uint32_t q_hi = xhi[c] >> log2_frame;
+            const uint64_t p = uint64_t(freq) * q_lo + offset;
+            nlo[g] = uint32_t(p);
+            nhi[g] = uint32_t(p >> 32) + freq * q_hi;
+            // state < L = 2^(log2 M + 4)
+            rn[g] = active && (lower_shift >= 32u ? nhi[g] == 0u : (nhi[g] == 0u && nlo[g] < lower_lo));
+        };
+        auto finish = [&](int g, bool active) -> uint32_t {
+            const int c = 3 - g;
+            const uint32_t w = rd.get_word<RING>(rn[g]); // renormalisation word first (ans_fold.hpp:221-224)
+            if (rn[g]) {
+                nhi[g] = nlo[g];
+                nlo[g] = w;
+            }
+            uint32_t value = mp[g];
+            if (!kInt)
+                value += rd.get_bits<RING>(k8[g]); // then k raw low bytes (ans_fold.hpp:135-147)
+            if (active) {
+                xlo[c] = nlo[g];
+                xhi[c] = nhi[g];
+            }
+            return value - rfold_bias;
+        };
+
+        uint32_t* out = a.out + first;
+        auto run = [&](auto full_tag) {
+            constexpr bool FULL = decltype(full_tag)::value; // every lane has a block and all blocks have max_quads quads
+            for (uint32_t q0 = 0; q0 < max_quads; q0 += QI) {
+                refill();
+                cp_async_wait<1>(); // everything this iteration can touch was committed an iteration ago
+                uint32_t val[4 * QI];
+#pragma unroll
+                for (int j = 0; j < QI; j++) {
+                    const bool active = FULL || (q0 + uint32_t(j)) < quads;
+#pragma unroll
+                    for (int g = 0; g < 4; g++)
+                        advance(g, active);
+#pragma unroll
+                    for (int g = 0; g < 4; g++)
+                        val[4 * j + g] = finish(g, active);
+                }
+                if (QI == 2) {
+                    if (FULL || q0 + 1u < quads) {
+                        asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(out + 4u * q0), "r"(val[0]), "r"(val[1]), "r"(val[2]),
+                                     "r"(val[3]), "r"(val[4 * (QI - 1)]), "r"(val[4 * (QI - 1) + 1]), "r"(val[4 * (QI - 1) + 2]),
+                                     "r"(val[4 * (QI - 1) + 3])
+                                     : "memory");
+                    } else if (q0 < quads) {
+                        reinterpret_cast<uint4*>(out)[q0] = make_uint4(val[0], val[1], val[2], val[3]);
+                    }
+                } else {
+                    if (FULL || q0 < quads)
+                        reinterpret_cast<uint4*>(out)[q0] = make_uint4(val[0], val[1], val[2], val[3]);
+                }
+            }
+        };
+        if (uniform && (max_quads % QI) == 0u)
+            run(std::true_type {});
+        else
+            run(std::false_type {});
+        // tail symbols on state 0 (ans_fold.hpp:306-310); only the last block of the input has any
+        if (__any_sync(0xffffffffu, tail != 0u)) {
+            refill();
+            cp_async_wait<0>();
+            for (uint32_t s = 0; s < 3u; s++) {
+                const bool active = s < tail;
+                advance(3, active); // g = 3 <-> state 0
+                const uint32_t v = finish(3, active);
+                if (active)
+                    out[4u * quads + s] = v;
+            }
+        }
+        cp_async_wait<0>();
     }
 }
 
