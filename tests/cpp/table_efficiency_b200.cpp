@@ -1,0 +1,101 @@
+// A driver in the shape of the reference's src/table_efficiency.cpp (run<t_compressor>, :64-121): best-of-N timing of
+// T::encode / T::decode over synthetic inputs, REQUIRE_EQUAL-style verification -- instantiated with the b200ans
+// adaptor structs instead of the reference's.  Shows that the adaptors are drop-ins for the `run<>` templates and is
+// run by tests/test_cpp_adaptors.py on the GPU box.  Inputs follow src/generate_inputs.cpp:70-117 (mt19937 seed 0).
+//
+// build: g++ -std=c++17 -O2 -I include tests/cpp/table_efficiency_b200.cpp -L ans_large_alphabet_b200 -lb200ans
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <iostream>
+#include <limits>
+#include <random>
+
+#include "b200ans_methods.hpp"
+
+const int NUM_RUNS = 3;
+
+static double compute_ips(size_t n, size_t ns) { return double(n) / (double(ns) / 1e9) / 1e6; } // million ints / s
+
+template <class t_compressor> bool run(const std::vector<std::vector<uint32_t>>& inputs)
+{
+    bool ok = true;
+    for (const auto& input : inputs) {
+        std::vector<uint8_t> encoded_data(input.size() * 8 + 4096);
+        std::vector<uint8_t> tmp_buf(16);
+        size_t encoded_bytes = 0;
+        size_t enc_ns = std::numeric_limits<size_t>::max();
+        for (int i = 0; i < NUM_RUNS; i++) {
+            auto t0 = std::chrono::high_resolution_clock::now();
+            encoded_bytes = t_compressor::encode(input.data(), input.size(), encoded_data.data(), encoded_data.size(), tmp_buf.data());
+            auto t1 = std::chrono::high_resolution_clock::now();
+            enc_ns = std::min(size_t((t1 - t0).count()), enc_ns);
+        }
+        encoded_data.resize(encoded_bytes);
+        std::vector<uint32_t> recover(input.size());
+        size_t dec_ns = std::numeric_limits<size_t>::max();
+        for (int i = 0; i < NUM_RUNS; i++) {
+            auto t0 = std::chrono::high_resolution_clock::now();
+            t_compressor::decode(encoded_data.data(), encoded_data.size(), recover.data(), recover.size(), tmp_buf.data());
+            auto t1 = std::chrono::high_resolution_clock::now();
+            dec_ns = std::min(size_t((t1 - t0).count()), dec_ns);
+        }
+        const bool same = std::memcmp(input.data(), recover.data(), input.size() * 4) == 0; // REQUIRE_EQUAL (cutil.hpp:30-50)
+        ok = ok && same;
+        std::printf("%-12s n=%9zu  bytes=%10zu  bpi=%7.4f  enc=%9.2f Mint/s  dec=%9.2f Mint/s  %s\n", t_compressor::name().c_str(),
+            input.size(), encoded_bytes, 8.0 * encoded_bytes / input.size(), compute_ips(input.size(), enc_ns),
+            compute_ips(input.size(), dec_ns), same ? "OK" : "MISMATCH");
+    }
+    return ok;
+}
+
+int main(int argc, char** argv)
+{
+    const size_t n = argc > 1 ? std::strtoull(argv[1], nullptr, 10) : 2000003;
+    std::vector<std::vector<uint32_t>> inputs;
+    {
+        std::mt19937 gen(0);
+        std::geometric_distribution<uint32_t> d(0.01); // generate_inputs.cpp:97-98
+        std::vector<uint32_t> v(n);
+        for (auto& x : v)
+            x = d(gen);
+        inputs.push_back(std::move(v));
+    }
+    {
+        std::mt19937 gen(0);
+        std::uniform_int_distribution<uint32_t> d(0, (1u << 20) - 1); // generate_inputs.cpp:88-95 (uniform 20 bit)
+        std::vector<uint32_t> v(n);
+        for (auto& x : v)
+            x = d(gen) >> (gen() % 12); // skewed towards small values so that folding has something to do
+        inputs.push_back(std::move(v));
+    }
+    bool ok = true;
+    ok = run<ANSint_b200>(inputs) && ok;
+    ok = run<ANSmsb_b200>(inputs) && ok;
+    ok = run<ANSfold_b200<1>>(inputs) && ok;
+    ok = run<ANSfold_b200<2>>(inputs) && ok;
+    ok = run<ANSrfold_b200<1>>({ inputs[1] }) && ok; // rfold needs sigma >= 2^(f+7)
+
+    // the ans_util.hpp model API: histogram -> adjust_freqs -> serialize -> load
+    std::vector<uint64_t> freqs(300, 0);
+    for (uint32_t x : inputs[0])
+        freqs[std::min<uint32_t>(x, 299)]++;
+    uint32_t largest = 0;
+    for (uint32_t s = 0; s < freqs.size(); s++)
+        if (freqs[s])
+            largest = s;
+    std::vector<uint32_t> nfreqs = b200::adjust_freqs(freqs, largest, true);
+    uint64_t frame = 0;
+    for (uint32_t f : nfreqs)
+        frame += f;
+    std::vector<uint8_t> prelude(nfreqs.size() * 8 + 128);
+    uint8_t* p = prelude.data();
+    const size_t interp_bytes = b200::ans_serialize_interp(nfreqs, frame, p);
+    const std::vector<uint32_t> back = b200::ans_load_interp(prelude.data());
+    const bool model_ok = b200::is_power_of_two(frame) && back == nfreqs && interp_bytes > 0 && size_t(p - prelude.data()) > interp_bytes;
+    std::printf("model API: sigma=%zu frame=%llu prelude=%zu bytes (interp %zu)  %s\n", nfreqs.size(), (unsigned long long)frame,
+        size_t(p - prelude.data()), interp_bytes, model_ok ? "OK" : "MISMATCH");
+    ok = ok && model_ok;
+    std::printf(ok ? "ALL OK\n" : "FAILED\n");
+    return ok ? 0 : 1;
+}
