@@ -117,7 +117,7 @@ struct b200ans_ctx {
     uint32_t dec_log2_frame = 0;
     uint32_t dec_n_syms = 0;
     uint32_t dec_n_present = 0;
-    uint32_t dec_cnt_bytes = 2;
+    uint32_t dec_dense = 0;
 
     int fail(int code, const std::string& what)
     {
@@ -742,37 +742,35 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
     const uint32_t lg = uint32_t(63 - __builtin_clzll(frame));
 
     if (method == METHOD_INT) {
-        // rank/select index over the frame (kernels.cuh RankEntry)
+        // rank/select index over the frame (kernels.cuh RankRec / RankEntry)
         const size_t words = (size_t(frame) + 31) / 32;
-        std::vector<uint32_t> bits(align_up(words, 4), 0);
+        std::vector<RankRec> rec(align_up(words, 2), RankRec { 0u, 0u });
         std::vector<RankEntry> ent;
+        std::vector<uint32_t> ids;
         uint64_t base = 0;
         for (size_t s = 0; s < nfreqs.size(); s++) {
             if (!nfreqs[s])
                 continue;
-            bits[base >> 5] |= 1u << (base & 31);
-            ent.push_back(RankEntry { uint32_t(base), nfreqs[s], uint32_t(s), 0u });
+            rec[base >> 5].bits |= 1u << (base & 31);
+            ent.push_back(RankEntry { uint32_t(base), nfreqs[s] });
+            ids.push_back(uint32_t(s));
             base += nfreqs[s];
         }
-        const uint32_t cnt_bytes = ent.size() < 65536 ? 2 : 4;
-        std::vector<uint8_t> cnt(align_up(words * cnt_bytes, 16), 0);
         uint32_t run = 0;
         for (size_t w = 0; w < words; w++) {
-            if (cnt_bytes == 2)
-                reinterpret_cast<uint16_t*>(cnt.data())[w] = uint16_t(run);
-            else
-                reinterpret_cast<uint32_t*>(cnt.data())[w] = run;
-            run += uint32_t(__builtin_popcount(bits[w]));
+            rec[w].cnt = run;
+            run += uint32_t(__builtin_popcount(rec[w].bits));
         }
-        CU(c, c->dec_bits.reserve(bits.size() * 4));
-        CU(c, c->dec_cnt.reserve(cnt.size()));
+        ent.resize(align_up(ent.size(), 2), RankEntry { 0u, 0u });
+        CU(c, c->dec_bits.reserve(rec.size() * sizeof(RankRec)));
+        CU(c, c->dec_cnt.reserve(std::max<size_t>(ids.size() * 4, 16)));
         CU(c, c->dec_ent.reserve(ent.size() * sizeof(RankEntry)));
-        CU(c, cudaMemcpyAsync(c->dec_bits.p, bits.data(), bits.size() * 4, cudaMemcpyHostToDevice, c->stream));
-        CU(c, cudaMemcpyAsync(c->dec_cnt.p, cnt.data(), cnt.size(), cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(c->dec_bits.p, rec.data(), rec.size() * sizeof(RankRec), cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(c->dec_cnt.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, c->stream));
         CU(c, cudaMemcpyAsync(c->dec_ent.p, ent.data(), ent.size() * sizeof(RankEntry), cudaMemcpyHostToDevice, c->stream));
         CU(c, cudaStreamSynchronize(c->stream));
-        c->dec_cnt_bytes = cnt_bytes;
-        c->dec_n_present = uint32_t(ent.size());
+        c->dec_n_present = uint32_t(ids.size());
+        c->dec_dense = ids.size() == nfreqs.size() ? 1u : 0u;
     } else {
         std::vector<DecEntry> slots(frame);
         uint64_t base = 0;
@@ -1098,16 +1096,16 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     a.log2_frame = c->dec_log2_frame;
     a.fidelity = c->dec_f;
     a.slots = c->dec_slots.as<DecEntry>();
-    a.rank_bits = c->dec_bits.as<uint32_t>();
-    a.rank_cnt = c->dec_cnt.p;
+    a.rank_rec = c->dec_bits.as<RankRec>();
+    a.rank_sym = c->dec_cnt.as<uint32_t>();
     a.rank_ent = c->dec_ent.as<RankEntry>();
     a.n_present = c->dec_n_present;
-    a.cnt_bytes = c->dec_cnt_bytes;
+    a.dense = c->dec_dense;
     const size_t frame = size_t(1) << c->dec_log2_frame;
     if (use_lpb(c, n_blocks, false)) {
         const size_t lbudget = c->max_smem > size_t(16) * kLpbDecWarpBytes + 4096 ? c->max_smem - size_t(16) * kLpbDecWarpBytes - 4096 : 0;
         if (c->dec_method == METHOD_INT) {
-            const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_cnt_bytes);
+            const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_dense);
             if (tb <= std::min<size_t>(lbudget, size_t(100) << 10))
                 return launch_lpb_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
             return launch_lpb_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);
@@ -1130,7 +1128,7 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     const size_t rows = size_t(kDecWarps) * 8 * kDecRowBytes;
     const size_t budget = c->max_smem > rows + 1024 ? c->max_smem - rows - 1024 : 0;
     if (c->dec_method == METHOD_INT) {
-        const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_cnt_bytes);
+        const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_dense);
         if (tb <= std::min<size_t>(budget, size_t(100) << 10))
             return launch_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
         return launch_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);

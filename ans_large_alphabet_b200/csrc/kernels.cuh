@@ -42,17 +42,20 @@ struct __align__(8) DecEntry {
 // Plain ANS (ans_int) replaces the reference's M-entry slot tables of 8 / 12 bytes per slot
 // (ans_int.hpp:100-110,129-161) by a rank/select index over the frame -- the table *contents*
 // are a pure function of nfreqs, so the layout is ours to choose:
-//   bits : M bits, bit s set iff slot s is the first slot of a symbol with freq > 0
-//   cnt  : per 32-slot word, the number of set bits in all earlier words (u16 or u32)
-//   ent  : per present symbol, in slot order: {base, freq, symbol id, 0}
-// slot -> rank = cnt[s >> 5] + popc(bits[s >> 5] & ((2 << (s & 31)) - 1)) - 1 -> ent[rank].
-// M / 8 + M / 16 + 16 * sigma bytes: a 2^17-slot model with 1 900 symbols takes 54 KiB and sits in
+//   rec : per 32 slots {bits, cnt}: bit s set iff slot s is the first slot of a symbol with freq > 0,
+//         cnt = number of set bits in all earlier words
+//   ent : per present symbol, in slot order: {base, freq}
+//   sym : per present symbol its id -- only needed when some id below max_sym is absent
+// slot -> rank = cnt + popc(bits & ((2 << (s & 31)) - 1)) - 1 -> ent[rank]: two dependent 8-byte loads.
+// M / 4 + 8 * sigma bytes: a 2^17-slot model with 1 900 symbols takes 47 KiB and sits in
 // one SM's shared memory, where the reference layout (1 MiB) would live in L2.
-struct __align__(16) RankEntry {
+struct __align__(8) RankRec {
+    uint32_t bits;
+    uint32_t cnt;
+};
+struct __align__(8) RankEntry {
     uint32_t base;
     uint32_t freq;
-    uint32_t sym;
-    uint32_t pad;
 };
 
 struct EncArgs {
@@ -84,11 +87,11 @@ struct DecArgs {
     uint32_t log2_frame;
     uint32_t fidelity;
     const DecEntry* slots;     // folded methods: M entries
-    const uint32_t* rank_bits; // INT: M / 32 words
-    const void* rank_cnt;      // INT: M / 32 counters, u16 or u32
+    const RankRec* rank_rec;   // INT: M / 32 records
+    const uint32_t* rank_sym;  // INT: n_present symbol ids (unused when dense)
     const RankEntry* rank_ent; // INT: n_present entries
     uint32_t n_present;
-    uint32_t cnt_bytes;        // INT: 2 or 4
+    uint32_t dense;            // INT: every id 0..max_sym is present, so the rank is the symbol
 };
 
 enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3 };
@@ -98,18 +101,19 @@ template <int METHOD, int TABLE> struct DecTables {
     static constexpr bool kInt = (METHOD == METHOD_INT);
     static constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM);
     const DecEntry* slots;
-    const uint32_t* bits;
-    const void* cnt;
+    const RankRec* rec;
+    const uint32_t* sym;
     const RankEntry* ent;
-    uint32_t cnt_bytes;
+    uint32_t dense;
 
-    __host__ __device__ static size_t smem_bytes(uint32_t frame, uint32_t n_present, uint32_t cnt_bytes)
+    __host__ __device__ static size_t smem_bytes(uint32_t frame, uint32_t n_present, uint32_t dense)
     {
         if (!kSmem)
             return 0;
         if (kInt) {
             const size_t words = (size_t(frame) + 31) / 32;
-            return ((words * 4 + 15) & ~size_t(15)) + ((words * cnt_bytes + 15) & ~size_t(15)) + size_t(n_present) * sizeof(RankEntry);
+            return ((words * 8 + 15) & ~size_t(15)) + ((size_t(n_present) * 8 + 15) & ~size_t(15))
+                + (dense ? 0 : ((size_t(n_present) * 4 + 15) & ~size_t(15)));
         }
         return (size_t(frame) * sizeof(DecEntry) + 15) & ~size_t(15);
     }
@@ -118,32 +122,33 @@ template <int METHOD, int TABLE> struct DecTables {
     __device__ __forceinline__ size_t load(const DecArgs& a, uint8_t* smem)
     {
         slots = a.slots;
-        bits = a.rank_bits;
-        cnt = a.rank_cnt;
+        rec = a.rank_rec;
+        sym = a.rank_sym;
         ent = a.rank_ent;
-        cnt_bytes = a.cnt_bytes;
+        dense = a.dense;
         if (!kSmem)
             return 0;
         const uint32_t frame = 1u << a.log2_frame;
         if (kInt) {
             const size_t words = (size_t(frame) + 31) / 32;
-            const size_t bits_bytes = (words * 4 + 15) & ~size_t(15);
-            const size_t cnt_b = (words * a.cnt_bytes + 15) & ~size_t(15);
-            const uint4* s0 = reinterpret_cast<const uint4*>(a.rank_bits);
-            uint4* d0 = reinterpret_cast<uint4*>(smem);
-            for (size_t i = threadIdx.x; i < bits_bytes / 16; i += blockDim.x)
+            const size_t rec_b = (words * 8 + 15) & ~size_t(15);
+            const size_t ent_b = (size_t(a.n_present) * 8 + 15) & ~size_t(15);
+            const uint2* s0 = reinterpret_cast<const uint2*>(a.rank_rec);
+            uint2* d0 = reinterpret_cast<uint2*>(smem);
+            for (size_t i = threadIdx.x; i < words; i += blockDim.x)
                 d0[i] = __ldg(s0 + i);
-            const uint4* s1 = reinterpret_cast<const uint4*>(a.rank_cnt);
-            uint4* d1 = reinterpret_cast<uint4*>(smem + bits_bytes);
-            for (size_t i = threadIdx.x; i < cnt_b / 16; i += blockDim.x)
-                d1[i] = __ldg(s1 + i);
-            const uint4* s2 = reinterpret_cast<const uint4*>(a.rank_ent);
-            uint4* d2 = reinterpret_cast<uint4*>(smem + bits_bytes + cnt_b);
+            const uint2* s1 = reinterpret_cast<const uint2*>(a.rank_ent);
+            uint2* d1 = reinterpret_cast<uint2*>(smem + rec_b);
             for (size_t i = threadIdx.x; i < a.n_present; i += blockDim.x)
-                d2[i] = __ldg(s2 + i);
-            bits = reinterpret_cast<const uint32_t*>(smem);
-            cnt = smem + bits_bytes;
-            ent = reinterpret_cast<const RankEntry*>(smem + bits_bytes + cnt_b);
+                d1[i] = __ldg(s1 + i);
+            rec = reinterpret_cast<const RankRec*>(smem);
+            ent = reinterpret_cast<const RankEntry*>(smem + rec_b);
+            if (!a.dense) {
+                uint32_t* d2 = reinterpret_cast<uint32_t*>(smem + rec_b + ent_b);
+                for (size_t i = threadIdx.x; i < a.n_present; i += blockDim.x)
+                    d2[i] = __ldg(a.rank_sym + i);
+                sym = d2;
+            }
         } else {
             const uint2* src = reinterpret_cast<const uint2*>(a.slots);
             uint2* dst = reinterpret_cast<uint2*>(smem);
@@ -152,7 +157,21 @@ template <int METHOD, int TABLE> struct DecTables {
             slots = reinterpret_cast<const DecEntry*>(smem);
         }
         __syncthreads();
-        return smem_bytes(frame, a.n_present, a.cnt_bytes);
+        return smem_bytes(frame, a.n_present, a.dense);
+    }
+
+    // as lookup(), but the folded coders get the packed word (unfolded base value | k << 30) back
+    __device__ __forceinline__ void lookup_raw(uint32_t slot, uint32_t& freq, uint32_t& offset, uint32_t& raw, uint32_t& k) const
+    {
+        if (kInt) {
+            lookup(slot, freq, offset, raw, k);
+        } else {
+            const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(slots + slot) : __ldg(reinterpret_cast<const uint2*>(slots + slot));
+            freq = e.x & 0xFFFFu;
+            offset = e.x >> 16;
+            raw = e.y;
+            k = e.y >> 30;
+        }
     }
 
     // slot -> {freq, offset inside the symbol's slot range, unfolded base value / symbol id, raw byte count}
@@ -160,17 +179,14 @@ template <int METHOD, int TABLE> struct DecTables {
     {
         if (kInt) {
             const uint32_t w = slot >> 5;
-            const uint32_t b = kSmem ? bits[w] : __ldg(bits + w);
-            uint32_t r;
-            if (cnt_bytes == 2)
-                r = kSmem ? uint32_t(reinterpret_cast<const uint16_t*>(cnt)[w]) : uint32_t(__ldg(reinterpret_cast<const uint16_t*>(cnt) + w));
-            else
-                r = kSmem ? reinterpret_cast<const uint32_t*>(cnt)[w] : __ldg(reinterpret_cast<const uint32_t*>(cnt) + w);
-            r += uint32_t(__popc(b & (0xFFFFFFFFu >> (31u - (slot & 31u))))) - 1u;
-            const uint4 e = kSmem ? *reinterpret_cast<const uint4*>(ent + r) : __ldg(reinterpret_cast<const uint4*>(ent + r));
+            const uint2 rc = kSmem ? *reinterpret_cast<const uint2*>(rec + w) : __ldg(reinterpret_cast<const uint2*>(rec + w));
+            const uint32_t r = rc.y + uint32_t(__popc(rc.x & (0xFFFFFFFFu >> (31u - (slot & 31u))))) - 1u;
+            const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(ent + r) : __ldg(reinterpret_cast<const uint2*>(ent + r));
             freq = e.y;
             offset = slot - e.x;
-            mapped = e.z;
+            mapped = r;
+            if (!dense)
+                mapped = kSmem ? sym[r] : __ldg(sym + r);
             k = 0;
         } else {
             const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(slots + slot) : __ldg(reinterpret_cast<const uint2*>(slots + slot));

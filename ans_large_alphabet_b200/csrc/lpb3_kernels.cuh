@@ -136,24 +136,22 @@ struct L3Packer {
     __device__ __forceinline__ void put_bits(uint32_t piece, uint32_t nbits) // nbits in {0, 8, 16, 24}, piece < 2^nbits
     {
         const uint32_t t = mad_lo(piece, am, acc);
-        const uint32_t hi = mad_hi(piece, am, 0u);
         const uint32_t am2 = __funnelshift_l(am, am, nbits);
         const bool full = am2 < am;
+        acc = t;
         if (full) {
             sts32(wp, t);
             wp += 4u;
+            acc = mad_hi(piece, am, 0u); // what spilled over the word
         }
-        acc = full ? hi : t;
         am = am2;
     }
     __device__ __forceinline__ void put_word(uint32_t w, bool on)
     {
-        const uint32_t t = mad_lo(w, am, acc);
-        const uint32_t hi = mad_hi(w, am, 0u);
         if (on) {
-            sts32(wp, t);
+            sts32(wp, mad_lo(w, am, acc));
             wp += 4u;
-            acc = hi;
+            acc = mad_hi(w, am, 0u);
         }
     }
     __device__ __forceinline__ uint32_t pending_bytes() const { return bfind_u32(am) >> 3; }
@@ -341,8 +339,13 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                 const uint32_t q_lo = uint32_t(__double2loint(t));
                 const uint32_t q_hr = uint32_t(__double2hiint(t)); // 0x43300000 + (q >> 32)
                 const uint32_t r = mad_lo(q_lo, nfr[c], y_lo);     // x - q * f  (< f)
-                const uint32_t nlo = mad_lo(q_lo, frame, r + base[c]); // r + base < M: no carry into the shifted quotient
-                const uint32_t nhi = mad_lo(q_hr, frame, mad_hi(q_lo, frame, neg_bias));
+                // q * M + (r + base) as one 64-bit multiply-add; the addend's high word cancels the exponent bits
+                // that q_hr * M leaves behind (zero for log2 M >= 12)
+                uint64_t addend, prod;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(addend) : "r"(r + base[c]), "r"(neg_bias));
+                asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(prod) : "r"(q_lo), "r"(frame), "l"(addend));
+                const uint32_t nlo = uint32_t(prod);
+                const uint32_t nhi = mad_lo(q_hr, frame, uint32_t(prod >> 32));
                 if (active) {
                     xlo[c] = nlo;
                     xhi[c] = nhi;
@@ -513,31 +516,29 @@ struct L3Reader {
     int32_t rp;    // byte offset (from the 16-byte aligned payload base) of the next word to read
     uint32_t ring; // shared-memory address of the lane's ring (aligned to its size)
     template <int RING> __device__ __forceinline__ uint32_t next_addr() const { return (uint32_t(rp) & uint32_t(RING - 1)) | ring; }
-    // the next 32 bits of the stream (ans_fold.hpp:221-224), consumed when `on`
-    template <int RING> __device__ __forceinline__ uint32_t get_word(bool on)
+    // renormalisation (ans_fold.hpp:221-224): state = state << 32 | the next 32 bits of the stream
+    template <int RING> __device__ __forceinline__ void renorm(bool on, uint32_t& lo, uint32_t& hi)
     {
-        uint32_t t = 0u;
         if (on) {
+            uint32_t t;
             asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t) : "r"(next_addr<RING>()));
             rp -= 4;
-        }
-        const uint32_t w = __funnelshift_r(t, acc, fill); // acc's `fill` bits on top of the new word's upper part
-        if (on)
+            hi = lo;
+            lo = __funnelshift_r(t, acc, fill); // acc's `fill` bits on top of the new word's upper part
             acc = t & mask;
-        return w;
+        }
     }
-    // the next nbits (0, 8, 16 or 24) of the stream as an integer (ans_fold.hpp:135-147)
-    template <int RING> __device__ __forceinline__ uint32_t get_bits(uint32_t nbits)
+    // the next k bytes (0..3) of the stream as an integer (ans_fold.hpp:135-147)
+    template <int RING> __device__ __forceinline__ uint32_t get_bytes(uint32_t k)
     {
-        const int32_t s = int32_t(fill) - int32_t(nbits);
-        const bool more = s < 0; // the bits run into the next word
+        const int32_t s = int32_t(mad_lo(k, 0xFFFFFFF8u, fill)); // fill - 8 k
+        uint32_t v = __funnelshift_r(acc, 0u, uint32_t(s));       // acc >> s when the bits are all in acc
         uint32_t lo = acc;
-        const uint32_t hi = more ? acc : 0u;
-        if (more) {
+        if (s < 0) { // they run into the next word: (acc : word) >> (s + 32)
             asm volatile("ld.shared.u32 %0, [%1];" : "=r"(lo) : "r"(next_addr<RING>()));
             rp -= 4;
+            v = __funnelshift_r(lo, acc, uint32_t(s));
         }
-        const uint32_t v = __funnelshift_r(lo, hi, uint32_t(s)); // more: (acc : word) >> (s + 32); else acc >> s
         fill = uint32_t(s) & 31u;
         asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(mask) : "r"(fill));
         acc = lo & mask;
@@ -631,13 +632,13 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
         refill();
 
         // one symbol per chain: slot lookup + state update (ans_fold.hpp:216-220); returns the renormalisation flag
-        uint32_t nlo[4], nhi[4], mp[4], k8[4];
+        uint32_t nlo[4], nhi[4], raw[4], kk[4];
         bool rn[4];
         auto advance = [&](int g, bool active) {
             const int c = 3 - g; // index 4t+g is decoded by state 3-g (ans_fold.hpp:300-305)
             uint32_t freq, offset, k;
-            tables.lookup(xlo[c] & frame_mask, freq, offset, mp[g], k);
-            k8[g] = active ? k * 8u : 0u;
+            tables.lookup_raw(xlo[c] & frame_mask, freq, offset, raw[g], k);
+            kk[g] = active ? k : 0u;
             const uint32_t q_lo = __funnelshift_r(xlo[c], xhi[c], log2_frame);
             const uint32_t q_hi = xhi[c] >> log2_frame;
             const uint64_t p = uint64_t(freq) * q_lo + offset;
@@ -648,14 +649,10 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
         };
         auto finish = [&](int g, bool active) -> uint32_t {
             const int c = 3 - g;
-            const uint32_t w = rd.get_word<RING>(rn[g]); // renormalisation word first (ans_fold.hpp:221-224)
-            if (rn[g]) {
-                nhi[g] = nlo[g];
-                nlo[g] = w;
-            }
-            uint32_t value = mp[g];
-            if (!kInt)
-                value += rd.get_bits<RING>(k8[g]); // then k raw low bytes (ans_fold.hpp:135-147)
+            rd.renorm<RING>(rn[g], nlo[g], nhi[g]); // renormalisation word first (ans_fold.hpp:221-224)
+            uint32_t value = raw[g];
+            if (!kInt) // then k raw low bytes (ans_fold.hpp:135-147); raw = unfolded base | k << 30
+                value = mad_lo(kk[g], 0xC0000000u, value + rd.get_bytes<RING>(kk[g]));
             if (active) {
                 xlo[c] = nlo[g];
                 xhi[c] = nhi[g];
