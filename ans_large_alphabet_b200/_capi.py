@@ -40,6 +40,7 @@ SIGNATURES = {
     "b200ans_destroy": (None, [C.c_void_p]),
     "b200ans_set_block_syms": (C.c_int, [C.c_void_p, C.c_uint32]),
     "b200ans_set_kernel_path": (C.c_int, [C.c_void_p, C.c_int]),
+    "b200ans_set_h_approx": (C.c_int, [C.c_void_p, C.c_uint32]),
     "b200ans_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "b200ans_last_error": (C.c_char_p, [C.c_void_p]),
     "b200ans_strerror": (C.c_char_p, [C.c_int]),
@@ -217,6 +218,10 @@ class Codec:
     def set_block_syms(self, bs):
         self._check(self.lib.b200ans_set_block_syms(self.h, bs))
         self.block_syms = bs
+
+    def set_h_approx(self, h):
+        """adjust_freqs' H_approx: 1 = ANS / ANSmsb / ANSfold, other values = ANSsint<H> / ANSsmsb<H>"""
+        self._check(self.lib.b200ans_set_h_approx(self.h, h))
 
     def set_kernel_path(self, path):
         """0 = auto, 1 = group kernels (4 lanes per block), 2 = lane-per-block kernels"""

@@ -83,6 +83,7 @@ struct b200ans_ctx {
     bool own_stream = false;
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
     int kernel_path = B200ANS_PATH_AUTO;
+    uint32_t h_approx = 1; // adjust_freqs' H_approx (ANSsint<H> / ANSsmsb<H>)
     uint32_t max_nfreq = 0; // largest normalised frequency of the encoder model
     std::string err;
     b200ans_stats stats {};
@@ -274,6 +275,16 @@ extern "C" int b200ans_set_kernel_path(b200ans_ctx* c, int path)
     if (path != B200ANS_PATH_AUTO && path != B200ANS_PATH_GROUP && path != B200ANS_PATH_LPB)
         return c->fail(B200ANS_E_ARG, "unknown kernel path");
     c->kernel_path = path;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_set_h_approx(b200ans_ctx* c, uint32_t h_approx)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (h_approx == 0 || h_approx > 1000)
+        return c->fail(B200ANS_E_ARG, "H_approx must be in 1..1000");
+    c->h_approx = h_approx;
     return B200ANS_OK;
 }
 
@@ -602,7 +613,7 @@ extern "C" int b200ans_model_build(b200ans_ctx* c, int method, uint32_t f, const
     if (method == METHOD_INT && sigma < 2)
         return c->fail(B200ANS_E_DOMAIN,
             "plain ANS needs at least two distinct symbols (the reference's adjust_freqs never terminates otherwise)");
-    c->nfreqs = adjust_freqs(freqs, max_sym, method != METHOD_INT);
+    c->nfreqs = adjust_freqs(freqs, max_sym, method != METHOD_INT, c->h_approx);
     uint64_t frame = 0;
     for (uint32_t v : c->nfreqs)
         frame += v;
@@ -856,8 +867,9 @@ bool use_lpb(const b200ans_ctx* c, uint32_t n_blocks, bool encode)
     if (c->kernel_path == B200ANS_PATH_LPB)
         return true;
     // The L3 encoder beats the 4-lanes-per-block encoder from one full warp of blocks upwards (measured: 1e7 and
-    // 1e8 symbols, 0.44 ms against 0.67 / 0.69 ms); the decoder needs >= 8 LPB warps per SM to win.
-    return encode ? n_blocks >= 32u : n_blocks >= uint32_t(c->num_sms) * 32u * 8u;
+    // 1e8 symbols, 0.44 ms against 0.67 / 0.69 ms); the L3 decoder from ~3.5 warps of blocks per SM (1e8 symbols:
+    // 24 414 blocks 0.39 ms against 0.54 ms, 12 207 blocks 0.78 ms against 0.74 ms).
+    return encode ? n_blocks >= 32u : n_blocks >= uint32_t(c->num_sms) * 112u;
 }
 
 // Lane-per-block launch shape: ONE CTA per SM.  A task (32 blocks) runs for the whole kernel, so

@@ -691,7 +691,8 @@ __global__ void __launch_bounds__(1024) scan_block_sizes_kernel(const uint32_t* 
     }
 }
 
-// one warp per block: scratch + b*stride  ->  payload + offsets[b]; also fills the container's size table
+// one warp per block: scratch + b*stride  ->  payload + offsets[b]; also fills the container's size table.
+// Four 16-byte chunks per lane in flight (a block is ~0.9 chunks per lane and pass otherwise: latency-bound).
 __global__ void __launch_bounds__(256) compact_kernel(const uint8_t* __restrict__ scratch, uint64_t stride,
     const uint32_t* __restrict__ bytes, const uint64_t* __restrict__ offsets, uint32_t n_blocks,
     uint8_t* __restrict__ payload, uint32_t* __restrict__ size_table)
@@ -703,8 +704,16 @@ __global__ void __launch_bounds__(256) compact_kernel(const uint8_t* __restrict_
         const uint32_t chunks = (sz + 15u) >> 4;
         const uint4* src = reinterpret_cast<const uint4*>(scratch + uint64_t(b) * stride);
         uint4* dst = reinterpret_cast<uint4*>(payload + offsets[b]);
-        for (uint32_t c = lane; c < chunks; c += 32)
-            dst[c] = src[c];
+        uint32_t c = lane;
+        for (; c + 96u < chunks; c += 128u) {
+            const uint4 v0 = __ldcs(src + c), v1 = __ldcs(src + c + 32u), v2 = __ldcs(src + c + 64u), v3 = __ldcs(src + c + 96u);
+            dst[c] = v0;
+            dst[c + 32u] = v1;
+            dst[c + 64u] = v2;
+            dst[c + 96u] = v3;
+        }
+        for (; c < chunks; c += 32u)
+            dst[c] = __ldcs(src + c);
         if (lane == 0 && size_table)
             size_table[b] = sz;
     }

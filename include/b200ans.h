@@ -93,6 +93,9 @@ int b200ans_create(b200ans_ctx** out, int device, void* stream);
 void b200ans_destroy(b200ans_ctx* ctx);
 int b200ans_set_block_syms(b200ans_ctx* ctx, uint32_t block_syms); /* 0 or a multiple of 128 */
 int b200ans_set_kernel_path(b200ans_ctx* ctx, int path); /* B200ANS_PATH_* ; default AUTO */
+/* H_approx of adjust_freqs (ans_util.hpp:100-101; ANSsint<H> / ANSsmsb<H>, methods.hpp:584-620): the frame stops
+ * growing once the cross entropy is within H/1000 of the entropy. Default 1 (ANS / ANSmsb / ANSfold / ANSrfold). */
+int b200ans_set_h_approx(b200ans_ctx* ctx, uint32_t h_approx);
 int b200ans_get_stats(const b200ans_ctx* ctx, b200ans_stats* out);
 const char* b200ans_last_error(const b200ans_ctx* ctx);
 const char* b200ans_strerror(int code);

@@ -9,6 +9,8 @@
 //   struct ANSmsb            methods.hpp:499-512            struct ANSmsb_b200            name() == "ANSmsb"
 //   template ANSfold<f>      methods.hpp:529-547            template ANSfold_b200<f>      "ANSfold-f"
 //   template ANSrfold<f>     methods.hpp:549-567            template ANSrfold_b200<f>     "ANSrfold-f"
+//   template ANSsint<H>      methods.hpp:584-601            template ANSsint_b200<H>      "ANSsint-H"
+//   template ANSsmsb<H>      methods.hpp:603-620            template ANSsmsb_b200<H>      "ANSsmsb-H"
 //   ans_int_compress / _decompress      ans_int.hpp:197,257             b200::ans_int_compress / _decompress
 //   ans_fold_compress<f> / _decompress  ans_fold.hpp:238,283            b200::ans_fold_compress<f> / ...
 //   ans_msb_compress / _decompress      ans_msb.hpp:235,294             b200::ans_msb_compress / ...
@@ -125,6 +127,30 @@ void ans_reorder_fold_decompress(uint32_t* dst, size_t to_decode, const uint8_t*
     decompress(B200ANS_METHOD_RFOLD, fidelity, dst, to_decode, cSrc, cSrcSize);
 }
 
+// ANSsint<H> / ANSsmsb<H> (ans_sint.hpp:197, ans_smsb.hpp:235): the same coders with adjust_freqs' H_approx = H
+template <uint32_t H_approx> size_t ans_sint_compress(uint8_t* dst, size_t dstCapacity, const uint32_t* src, size_t srcSize)
+{
+    b200ans_set_h_approx(context(), H_approx);
+    const size_t bytes = compress(B200ANS_METHOD_INT, 0, dst, dstCapacity, src, srcSize);
+    b200ans_set_h_approx(context(), 1);
+    return bytes;
+}
+inline void ans_sint_decompress(uint32_t* dst, size_t to_decode, const uint8_t* cSrc, size_t cSrcSize)
+{
+    decompress(B200ANS_METHOD_INT, 0, dst, to_decode, cSrc, cSrcSize);
+}
+template <uint32_t H_approx> size_t ans_smsb_compress(uint8_t* dst, size_t dstCapacity, const uint32_t* src, size_t srcSize)
+{
+    b200ans_set_h_approx(context(), H_approx);
+    const size_t bytes = compress(B200ANS_METHOD_MSB, 0, dst, dstCapacity, src, srcSize);
+    b200ans_set_h_approx(context(), 1);
+    return bytes;
+}
+inline void ans_smsb_decompress(uint32_t* dst, size_t to_decode, const uint8_t* cSrc, size_t cSrcSize)
+{
+    decompress(B200ANS_METHOD_MSB, 0, dst, to_decode, cSrc, cSrcSize);
+}
+
 // ---- the ans_util.hpp model API (host only; no GPU needed) -------------------------------------------------------
 inline uint64_t next_power_of_two(uint64_t x)
 {
@@ -205,6 +231,34 @@ struct ANSmsb_b200 {
     {
         (void)buf;
         b200::ans_msb_decompress(out_ptr, out_size_u32, in_ptr, in_size_u8);
+    }
+};
+
+template <uint32_t H_approx> struct ANSsint_b200 { // methods.hpp:584-601
+    static std::string name() { return std::string("ANSsint-") + std::to_string(H_approx); }
+    static size_t encode(const uint32_t* in_ptr, size_t in_size_u32, uint8_t* out_ptr, size_t out_size_u8, uint8_t* buf = NULL)
+    {
+        (void)buf;
+        return b200::ans_sint_compress<H_approx>(out_ptr, out_size_u8, in_ptr, in_size_u32);
+    }
+    static void decode(const uint8_t* in_ptr, size_t in_size_u8, uint32_t* out_ptr, size_t out_size_u32, uint8_t* buf = NULL)
+    {
+        (void)buf;
+        b200::ans_sint_decompress(out_ptr, out_size_u32, in_ptr, in_size_u8);
+    }
+};
+
+template <uint32_t H_approx> struct ANSsmsb_b200 { // methods.hpp:603-620
+    static std::string name() { return std::string("ANSsmsb-") + std::to_string(H_approx); }
+    static size_t encode(const uint32_t* in_ptr, size_t in_size_u32, uint8_t* out_ptr, size_t out_size_u8, uint8_t* buf = NULL)
+    {
+        (void)buf;
+        return b200::ans_smsb_compress<H_approx>(out_ptr, out_size_u8, in_ptr, in_size_u32);
+    }
+    static void decode(const uint8_t* in_ptr, size_t in_size_u8, uint32_t* out_ptr, size_t out_size_u32, uint8_t* buf = NULL)
+    {
+        (void)buf;
+        b200::ans_smsb_decompress(out_ptr, out_size_u32, in_ptr, in_size_u8);
     }
 };
 

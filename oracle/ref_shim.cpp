@@ -27,6 +27,8 @@
 #include "ans_int.hpp"
 #include "ans_msb.hpp"
 #include "ans_reorder_fold.hpp"
+#include "ans_sint.hpp"
+#include "ans_smsb.hpp"
 #include "zipf_dist.hpp"
 
 enum { M_INT = 0, M_FOLD = 1, M_MSB = 2, M_RFOLD = 3 };
@@ -115,6 +117,39 @@ long ref_compress(int method, uint32_t f, uint8_t* dst, size_t cap, const uint32
     case M_RFOLD: FOLD_DISPATCH(f, return (long)ans_reorder_fold_compress<F>(dst, cap, src, n));
     }
     return -1;
+}
+
+// ANSsint<H> / ANSsmsb<H> (methods.hpp:584-620): the entropy-approximation variants of benchmark.cpp:156-172
+#define H_DISPATCH(h, EXPR)                                                                    \
+    switch (h) {                                                                               \
+    case 1: { constexpr uint32_t H = 1; EXPR; } break;                                         \
+    case 5: { constexpr uint32_t H = 5; EXPR; } break;                                         \
+    case 10: { constexpr uint32_t H = 10; EXPR; } break;                                       \
+    case 20: { constexpr uint32_t H = 20; EXPR; } break;                                       \
+    case 40: { constexpr uint32_t H = 40; EXPR; } break;                                       \
+    case 80: { constexpr uint32_t H = 80; EXPR; } break;                                       \
+    case 160: { constexpr uint32_t H = 160; EXPR; } break;                                     \
+    case 320: { constexpr uint32_t H = 320; EXPR; } break;                                     \
+    default: return -1;                                                                        \
+    }
+long ref_compress_h(int method, uint32_t h, uint8_t* dst, size_t cap, const uint32_t* src, size_t n)
+{
+    if (method == M_INT) {
+        H_DISPATCH(h, return (long)ans_sint_compress<H>(dst, cap, src, n));
+    } else if (method == M_MSB) {
+        H_DISPATCH(h, return (long)ans_smsb_compress<H>(dst, cap, src, n));
+    }
+    return -1;
+}
+int ref_decompress_h(int method, uint32_t* dst, size_t n, const uint8_t* src, size_t bytes)
+{
+    if (method == M_INT)
+        ans_sint_decompress(dst, n, src, bytes);
+    else if (method == M_MSB)
+        ans_smsb_decompress(dst, n, src, bytes);
+    else
+        return -1;
+    return 0;
 }
 
 int ref_decompress(int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src, size_t bytes)

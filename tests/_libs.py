@@ -69,8 +69,30 @@ class _CpuCodec:
         g("time").argtypes = [C.c_int, C.c_uint32, u32p, C.c_size_t, C.c_int,
                               C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_size_t)]
 
+        if prefix == "ref_" and hasattr(L, "ref_compress_h"):  # ANSsint<H> / ANSsmsb<H>: reference shim only
+            L.ref_compress_h.restype = C.c_long
+            L.ref_compress_h.argtypes = [C.c_int, C.c_uint32, u8p, C.c_size_t, u32p, C.c_size_t]
+            L.ref_decompress_h.restype = C.c_int
+            L.ref_decompress_h.argtypes = [C.c_int, u32p, C.c_size_t, u8p, C.c_size_t]
+
     def _f(self, name):
         return getattr(self.lib, self.p + name)
+
+    def compress_h(self, method, h_approx, data):
+        """ans_sint_compress<H> / ans_smsb_compress<H> of the unmodified reference"""
+        data = np.ascontiguousarray(data, dtype=np.uint32)
+        out = np.zeros(data.size * 8 + (1 << 16) + (8 << 20) * (method == M_INT), dtype=np.uint8)
+        nb = self.lib.ref_compress_h(method, h_approx, ptr(out, u8p), out.size, ptr(data, u32p), data.size)
+        assert nb >= 0
+        return out[:nb].copy()
+
+    def decompress_h(self, method, blob, n):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        buf = np.zeros(blob.size + 16, dtype=np.uint8)
+        buf[: blob.size] = blob
+        out = np.zeros(n + 8, dtype=np.uint32)
+        assert self.lib.ref_decompress_h(method, ptr(out, u32p), n, ptr(buf, u8p), blob.size) == 0
+        return out[:n].copy()
 
     # ---- whole stream -----------------------------------------------------------------
     def compress(self, method, f, data):

@@ -74,6 +74,8 @@ int main(int argc, char** argv)
     ok = run<ANSmsb_b200>(inputs) && ok;
     ok = run<ANSfold_b200<1>>(inputs) && ok;
     ok = run<ANSfold_b200<2>>(inputs) && ok;
+    ok = run<ANSsint_b200<20>>({ inputs[0] }) && ok;  // benchmark.cpp:165-172
+    ok = run<ANSsmsb_b200<80>>(inputs) && ok;         // benchmark.cpp:156-163
     ok = run<ANSrfold_b200<1>>({ inputs[1] }) && ok; // rfold needs sigma >= 2^(f+7)
 
     // the ans_util.hpp model API: histogram -> adjust_freqs -> serialize -> load

@@ -128,6 +128,41 @@ def test_reference_wire_format(codec, method, f, kind, path):
         codec.set_block_syms(8192)
 
 
+@pytest.mark.parametrize("h_approx", [5, 40, 320])
+@pytest.mark.parametrize("method", [M_INT, M_MSB])
+def test_h_approx_variants(codec, method, h_approx):
+    """ANSsint<H> / ANSsmsb<H> (methods.hpp:584-620): same coders, adjust_freqs stops at H/1000 above the entropy."""
+    if not have_reference():
+        pytest.skip("needs the reference shim (ans_sint.hpp / ans_smsb.hpp)")
+    ref = reference()
+    if not hasattr(ref.lib, "ref_compress_h"):
+        pytest.skip("reference shim was built without the H_approx entry points")
+    n = 60_001
+    data = _inputs.make("zipf20" if method == M_MSB else "geom", n, seed=11)
+    want = ref.compress_h(method, h_approx, data)
+    plain = ref.compress(method, 0, data)
+    codec.set_h_approx(h_approx)
+    try:
+        codec.set_block_syms(0)
+        got = codec.compress(method, 0, data).copy()
+        assert got.size == want.size
+        pre = codec.model_prelude().size
+        assert _container.prelude_equal(got[:pre], want[:pre])
+        assert np.array_equal(got[pre:], want[pre:]), "payload differs from ans_sint/smsb_compress<H>"
+        assert np.array_equal(ref.decompress_h(method, got, n), data), "reference cannot decode our stream"
+        assert np.array_equal(codec.decompress(method, 0, want, n), data), "cannot decode the reference's stream"
+        if h_approx >= 40:
+            assert got.size != plain.size or not np.array_equal(got, plain), "H_approx had no effect"
+        codec.set_block_syms(8192)
+        blob = codec.compress(method, 0, data).copy()
+        assert np.array_equal(codec.decompress(method, 0, blob, n), data)
+    finally:
+        codec.set_h_approx(1)
+        codec.set_block_syms(8192)
+    with pytest.raises(Exception):
+        codec.set_h_approx(0)
+
+
 def test_empty_input(codec):
     codec.set_block_syms(8192)
     blob = codec.compress(M_FOLD, 1, np.zeros(0, np.uint32)).copy()
