@@ -34,6 +34,14 @@ class Stats(C.Structure):
     ]
 
 
+class Container(C.Structure):
+    _fields_ = [
+        ("method", C.c_int), ("fidelity", C.c_uint32), ("n_symbols", C.c_uint64), ("block_syms", C.c_uint32),
+        ("n_blocks", C.c_uint32), ("prelude_bytes", C.c_uint64), ("payload_bytes", C.c_uint64),
+        ("total_bytes", C.c_uint64),
+    ]
+
+
 # name -> (restype, argtypes); this is the complete export list of include/b200ans.h
 SIGNATURES = {
     "b200ans_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_void_p]),
@@ -41,6 +49,7 @@ SIGNATURES = {
     "b200ans_set_block_syms": (C.c_int, [C.c_void_p, C.c_uint32]),
     "b200ans_set_kernel_path": (C.c_int, [C.c_void_p, C.c_int]),
     "b200ans_set_h_approx": (C.c_int, [C.c_void_p, C.c_uint32]),
+    "b200ans_container_info": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(Container)]),
     "b200ans_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "b200ans_last_error": (C.c_char_p, [C.c_void_p]),
     "b200ans_strerror": (C.c_char_p, [C.c_int]),
@@ -161,6 +170,15 @@ class _HostApi:
         out = np.zeros(n, dtype=np.uint32)
         self.lib.b200ans_interp_decode(_p(buf, u32p), _p(out, u32p), n, universe, None)
         return out
+
+    def container_info(self, blob):
+        """header of a b200ans container as a dict (host only)"""
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        info = Container()
+        rc = self.lib.b200ans_container_info(_p(blob, C.c_void_p), blob.size, C.byref(info))
+        if rc:
+            raise B200AnsError(rc, "not a b200ans container")
+        return {k: getattr(info, k) for k, _ in Container._fields_}
 
     def fold_map(self, f, x):
         k = C.c_uint32()

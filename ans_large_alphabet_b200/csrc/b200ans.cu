@@ -81,6 +81,7 @@ struct b200ans_ctx {
     size_t max_smem_sm = 0; // shared memory per SM
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    std::vector<uint8_t> front; // container front of the encode in flight (must outlive its H2D copy)
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
     int kernel_path = B200ANS_PATH_AUTO;
     uint32_t h_approx = 1; // adjust_freqs' H_approx (ANSsint<H> / ANSsmsb<H>)
@@ -95,6 +96,15 @@ struct b200ans_ctx {
     uint32_t* d_max() { return small.as<uint32_t>(); }
     uint32_t* d_err() { return small.as<uint32_t>() + 1; }
     uint64_t* d_totals() { return reinterpret_cast<uint64_t*>(small.as<uint8_t>() + 16); }
+    // pinned host mirror: kPinnedBins bytes of histogram bins, then the 32 bytes of `small`; lets the small
+    // device->host reads of one step share a single synchronisation
+    static constexpr size_t kPinnedBins = size_t(64) << 10;
+    uint8_t* pinned = nullptr;
+    struct SmallHost {
+        uint32_t max_value, error_flag, pad[2];
+        uint64_t totals[2];
+    };
+    SmallHost* h_small() { return reinterpret_cast<SmallHost*>(pinned + kPinnedBins); }
 
     // encoder model
     bool have_enc = false;
@@ -233,7 +243,9 @@ extern "C" int b200ans_create(b200ans_ctx** out, int device, void* stream)
     }
     for (auto& e : c->ev)
         cudaEventCreate(&e);
-    if (c->small.reserve(256) != cudaSuccess) {
+    if (cudaHostAlloc(reinterpret_cast<void**>(&c->pinned), b200ans_ctx::kPinnedBins + 64, cudaHostAllocDefault) != cudaSuccess)
+        c->pinned = nullptr;
+    if (!c->pinned || c->small.reserve(256) != cudaSuccess) {
         b200ans_destroy(c);
         return B200ANS_E_CUDA;
     }
@@ -253,6 +265,8 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     for (auto& e : c->ev)
         if (e)
             cudaEventDestroy(e);
+    if (c->pinned)
+        cudaFreeHost(c->pinned);
     if (c->own_stream)
         cudaStreamDestroy(c->stream);
     delete c;
@@ -275,6 +289,29 @@ extern "C" int b200ans_set_kernel_path(b200ans_ctx* c, int path)
     if (path != B200ANS_PATH_AUTO && path != B200ANS_PATH_GROUP && path != B200ANS_PATH_LPB)
         return c->fail(B200ANS_E_ARG, "unknown kernel path");
     c->kernel_path = path;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_container_info(const uint8_t* src, size_t src_bytes, b200ans_container* out)
+{
+    if (!src || !out)
+        return B200ANS_E_ARG;
+    if (src_bytes < B200ANS_HEADER_BYTES)
+        return B200ANS_E_FORMAT;
+    Header h;
+    std::memcpy(&h, src, sizeof h);
+    if (h.magic != B200ANS_MAGIC || h.version != 1 || h.method > METHOD_RFOLD)
+        return B200ANS_E_FORMAT;
+    out->method = h.method;
+    out->fidelity = h.fidelity;
+    out->n_symbols = h.n_symbols;
+    out->block_syms = h.block_syms;
+    out->n_blocks = h.n_blocks;
+    out->prelude_bytes = h.prelude_bytes;
+    out->payload_bytes = h.payload_bytes;
+    out->total_bytes = h.n_symbols == 0
+        ? B200ANS_HEADER_BYTES
+        : align_up(B200ANS_HEADER_BYTES + align_up(h.prelude_bytes, 4) + size_t(h.n_blocks) * 4, 16) + h.payload_bytes;
     return B200ANS_OK;
 }
 
@@ -650,8 +687,8 @@ extern "C" int b200ans_model_build(b200ans_ctx* c, int method, uint32_t f, const
         c->max_nfreq = std::max(c->max_nfreq, fr);
     }
     CU(c, c->enc_table.reserve(table.size() * sizeof(EncEntry)));
+    // pageable source: cudaMemcpyAsync returns once the buffer is staged, so `table` may go out of scope
     CU(c, cudaMemcpyAsync(c->enc_table.p, table.data(), table.size() * sizeof(EncEntry), cudaMemcpyHostToDevice, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
     c->enc_method = method;
     c->enc_f = f;
     c->have_enc = true;
@@ -779,7 +816,7 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
         CU(c, cudaMemcpyAsync(c->dec_bits.p, rec.data(), rec.size() * sizeof(RankRec), cudaMemcpyHostToDevice, c->stream));
         CU(c, cudaMemcpyAsync(c->dec_cnt.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, c->stream));
         CU(c, cudaMemcpyAsync(c->dec_ent.p, ent.data(), ent.size() * sizeof(RankEntry), cudaMemcpyHostToDevice, c->stream));
-        CU(c, cudaStreamSynchronize(c->stream));
+        // (pageable sources are staged before cudaMemcpyAsync returns: no synchronisation needed for the locals)
         c->dec_n_present = uint32_t(ids.size());
         c->dec_dense = ids.size() == nfreqs.size() ? 1u : 0u;
     } else {
@@ -803,7 +840,6 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
         }
         CU(c, c->dec_slots.reserve(slots.size() * sizeof(DecEntry)));
         CU(c, cudaMemcpyAsync(c->dec_slots.p, slots.data(), slots.size() * sizeof(DecEntry), cudaMemcpyHostToDevice, c->stream));
-        CU(c, cudaStreamSynchronize(c->stream));
     }
     c->dec_method = method;
     c->dec_f = f;
@@ -1161,6 +1197,14 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     return c->fail(B200ANS_E_STATE, "decode: no model");
 }
 
+// one asynchronous read of the device control block (maximum, error flag, scan totals) + one synchronisation
+int read_small(b200ans_ctx* c)
+{
+    CU(c, cudaMemcpyAsync(c->h_small(), c->small.p, sizeof(b200ans_ctx::SmallHost), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return B200ANS_OK;
+}
+
 int check_error_flag(b200ans_ctx* c)
 {
     uint32_t flag = 0;
@@ -1258,34 +1302,17 @@ extern "C" int b200ans_encode_device(b200ans_ctx* c, uint8_t* d_dst, size_t cap,
     CU(c, c->block_bytes.reserve(size_t(nb) * 4));
     CU(c, c->offsets.reserve(size_t(nb) * 8));
 
-    CU(c, cudaEventRecord(c->ev[0], c->stream));
-    RET(launch_encode(c, d_src, n, bs, nb, c->scratch.as<uint8_t>(), stride, c->block_bytes.as<uint32_t>()));
-    CU(c, cudaEventRecord(c->ev[1], c->stream));
-    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(c->block_bytes.as<uint32_t>(), nb, c->offsets.as<uint64_t>(), c->d_totals());
-    c->stats.launches++;
-    CU(c, cudaGetLastError());
-    uint64_t totals[2] = { 0, 0 };
-    CU(c, cudaMemcpyAsync(totals, c->d_totals(), 16, cudaMemcpyDeviceToHost, c->stream));
-    RET(check_error_flag(c)); // synchronises
-
     const size_t pre = c->prelude.size();
-    if (raw) {
-        // [prelude][payload], exactly ans_X_compress's output
-        if (cap < pre + totals[1])
+    const size_t table_at = B200ANS_HEADER_BYTES + align_up(pre, 4);
+    const size_t payload_at = align_up(table_at + size_t(nb) * 4, 16);
+    uint64_t* d_header_total = nullptr;
+    if (!raw) {
+        // The front (header, prelude; the size table is the compaction kernel's) is known before any kernel runs,
+        // except the payload total, which the size scan patches in on the device.  Everything after this copy is
+        // stream-ordered kernels and one final synchronisation.
+        if (cap < payload_at)
             return c->fail(B200ANS_E_CAPACITY, "encode: destination too small");
-        CU(c, cudaMemcpyAsync(d_dst, c->prelude.data(), pre, cudaMemcpyHostToDevice, c->stream));
-        CU(c, cudaMemcpyAsync(d_dst + pre, c->scratch.p, totals[1], cudaMemcpyDeviceToDevice, c->stream));
-        CU(c, cudaEventRecord(c->ev[2], c->stream));
-        CU(c, cudaStreamSynchronize(c->stream));
-        *out_bytes = pre + totals[1];
-        c->stats.payload_bytes = totals[1];
-    } else {
-        const size_t table_at = B200ANS_HEADER_BYTES + align_up(pre, 4);
-        const size_t payload_at = align_up(table_at + size_t(nb) * 4, 16);
-        const size_t total = payload_at + totals[0];
-        if (cap < total)
-            return c->fail(B200ANS_E_CAPACITY, "encode: destination too small");
-        std::vector<uint8_t> front(payload_at, 0);
+        c->front.assign(payload_at, 0);
         Header h {};
         h.magic = B200ANS_MAGIC;
         h.version = 1;
@@ -1295,18 +1322,48 @@ extern "C" int b200ans_encode_device(b200ans_ctx* c, uint8_t* d_dst, size_t cap,
         h.block_syms = bs;
         h.n_blocks = nb;
         h.prelude_bytes = uint32_t(pre);
-        h.payload_bytes = totals[0];
-        std::memcpy(front.data(), &h, sizeof h);
-        std::memcpy(front.data() + B200ANS_HEADER_BYTES, c->prelude.data(), pre);
-        // the front (minus the size table, which the compaction kernel fills) goes first
-        CU(c, cudaMemcpyAsync(d_dst, front.data(), payload_at, cudaMemcpyHostToDevice, c->stream));
+        std::memcpy(c->front.data(), &h, sizeof h);
+        std::memcpy(c->front.data() + B200ANS_HEADER_BYTES, c->prelude.data(), pre);
+        CU(c, cudaMemcpyAsync(d_dst, c->front.data(), payload_at, cudaMemcpyHostToDevice, c->stream));
+        d_header_total = reinterpret_cast<uint64_t*>(d_dst + offsetof(Header, payload_bytes));
+    }
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    RET(launch_encode(c, d_src, n, bs, nb, c->scratch.as<uint8_t>(), stride, c->block_bytes.as<uint32_t>()));
+    CU(c, cudaEventRecord(c->ev[1], c->stream));
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(c->block_bytes.as<uint32_t>(), nb, c->offsets.as<uint64_t>(), c->d_totals(),
+        d_header_total);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    uint64_t totals[2] = { 0, 0 };
+    if (raw) {
+        // [prelude][payload], exactly ans_X_compress's output
+        CU(c, cudaMemcpyAsync(totals, c->d_totals(), 16, cudaMemcpyDeviceToHost, c->stream));
+        RET(check_error_flag(c)); // synchronises
+        if (cap < pre + totals[1])
+            return c->fail(B200ANS_E_CAPACITY, "encode: destination too small");
+        CU(c, cudaMemcpyAsync(d_dst, c->prelude.data(), pre, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(d_dst + pre, c->scratch.p, totals[1], cudaMemcpyDeviceToDevice, c->stream));
+        CU(c, cudaEventRecord(c->ev[2], c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        *out_bytes = pre + totals[1];
+        c->stats.payload_bytes = totals[1];
+    } else {
+        // compaction is launched without waiting for the total: it skips blocks that would not fit
         const int grid = int(std::max<uint32_t>(1, std::min<uint32_t>((nb + 7) / 8, uint32_t(c->num_sms) * 8)));
         compact_kernel<<<grid, 256, 0, c->stream>>>(c->scratch.as<uint8_t>(), stride, c->block_bytes.as<uint32_t>(),
-            c->offsets.as<uint64_t>(), nb, d_dst + payload_at, reinterpret_cast<uint32_t*>(d_dst + table_at));
+            c->offsets.as<uint64_t>(), nb, d_dst + payload_at, reinterpret_cast<uint32_t*>(d_dst + table_at),
+            uint64_t(cap - payload_at));
         c->stats.launches++;
         CU(c, cudaGetLastError());
         CU(c, cudaEventRecord(c->ev[2], c->stream));
-        CU(c, cudaStreamSynchronize(c->stream)); // `front` must outlive the copy
+        RET(read_small(c)); // the step's only synchronisation after the model upload
+        if (c->h_small()->error_flag)
+            return c->fail(B200ANS_E_DOMAIN, "encode: input holds a symbol the model has no frequency for");
+        totals[0] = c->h_small()->totals[0];
+        totals[1] = c->h_small()->totals[1];
+        const size_t total = payload_at + totals[0];
+        if (cap < total)
+            return c->fail(B200ANS_E_CAPACITY, "encode: destination too small");
         *out_bytes = total;
         c->stats.payload_bytes = totals[1];
     }
@@ -1344,13 +1401,24 @@ int write_empty_container(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst
 
 // device histogram -> host bins
 int histogram_to_host(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n, size_t nbins,
-    std::vector<uint64_t>& host_bins)
+    std::vector<uint64_t>& host_bins, uint32_t* max_value = nullptr)
 {
     CU(c, c->bins.reserve(nbins * 8));
     CU(c, cudaMemsetAsync(c->bins.p, 0, nbins * 8, c->stream));
     RET(histogram_dispatch(c, method, f, d_src, n, c->bins.as<uint64_t>(), nbins, c->d_max()));
     host_bins.resize(nbins);
+    if (nbins * 8 <= b200ans_ctx::kPinnedBins) {
+        // bins and the running maximum through pinned memory: both copies are asynchronous, one synchronisation
+        CU(c, cudaMemcpyAsync(c->pinned, c->bins.p, nbins * 8, cudaMemcpyDeviceToHost, c->stream));
+        RET(read_small(c));
+        std::memcpy(host_bins.data(), c->pinned, nbins * 8);
+        if (max_value)
+            *max_value = c->h_small()->max_value;
+        return B200ANS_OK;
+    }
     CU(c, cudaMemcpyAsync(host_bins.data(), c->bins.p, nbins * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (max_value)
+        CU(c, cudaMemcpyAsync(max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     return B200ANS_OK;
 }
@@ -1375,29 +1443,34 @@ extern "C" int b200ans_compress_device(b200ans_ctx* c, int method, uint32_t f, u
     CU(c, cudaMemsetAsync(c->d_max(), 0, 4, c->stream));
     uint32_t max_value = 0;
     std::vector<uint64_t> bins;
-    if (method == METHOD_INT || method == METHOD_RFOLD) {
-        // two passes like the reference (ans_int.hpp:42-49): the alphabet size comes first
+    if (method == METHOD_INT) {
+        // The reference takes the maximum first, then counts (ans_int.hpp:42-49).  K1 keeps the running maximum
+        // while it counts, so alphabets that fit four shared-memory replicas need one pass: count into kOptBins
+        // bins (larger values are dropped by the kernel's bounds check) and look at the maximum afterwards.
+        constexpr size_t kOptBins = kHistSmemWords / 4 - 1;
+        RET(histogram_to_host(c, METHOD_INT, f, d_src, n, kOptBins, bins, &max_value));
+        if (max_value >= (1u << 30))
+            return c->fail(B200ANS_E_DOMAIN, "plain ANS: alphabets beyond 2^30 are not supported");
+        if (max_value >= kOptBins)
+            RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins));
+        else
+            bins.resize(size_t(max_value) + 1);
+    } else if (method == METHOD_RFOLD) {
         RET(b200ans_max_device(c, d_src, n, c->d_max()));
         CU(c, cudaMemcpyAsync(&max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
         CU(c, cudaStreamSynchronize(c->stream));
-        if (method == METHOD_RFOLD && uint64_t(max_value) + (1u << (f + 7)) >= (1u << 30))
+        if (uint64_t(max_value) + (1u << (f + 7)) >= (1u << 30))
             return c->fail(B200ANS_E_DOMAIN, "ANSrfold needs value + 2^(f+7) < 2^30");
-        if (max_value >= (1u << 30))
-            return c->fail(B200ANS_E_DOMAIN, "plain ANS: alphabets beyond 2^30 are not supported");
         RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins));
-        if (method == METHOD_RFOLD) {
-            RET(b200ans_rfold_prepare(c, f, bins.data(), bins.size()));
-            RET(histogram_to_host(c, METHOD_RFOLD, f, d_src, n, alphabet_bins(method, f, 0), bins));
-        }
+        RET(b200ans_rfold_prepare(c, f, bins.data(), bins.size()));
+        RET(histogram_to_host(c, METHOD_RFOLD, f, d_src, n, alphabet_bins(method, f, 0), bins));
     } else {
-        RET(histogram_to_host(c, method, f, d_src, n, alphabet_bins(method, f, 0), bins));
-        CU(c, cudaMemcpyAsync(&max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
-        CU(c, cudaStreamSynchronize(c->stream));
+        RET(histogram_to_host(c, method, f, d_src, n, alphabet_bins(method, f, 0), bins, &max_value));
         if (max_value >= (1u << 30)) // the decoder keeps the byte count in bits 30-31 (ans_fold.hpp:198-200)
             return c->fail(B200ANS_E_DOMAIN, "folded coders need values < 2^30");
     }
     CU(c, cudaEventRecord(c->ev[4], c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+    CU(c, cudaEventSynchronize(c->ev[4]));
     const float ms_hist = elapsed(c->ev[3], c->ev[4]);
     RET(b200ans_model_build(c, method, f, bins.data(), bins.size()));
     RET(b200ans_encode_device(c, d_dst, cap, d_src, n, out_bytes));
@@ -1438,9 +1511,13 @@ extern "C" int b200ans_decompress_device(b200ans_ctx* c, int method, uint32_t f,
     }
     if (src_bytes < B200ANS_HEADER_BYTES)
         return c->fail(B200ANS_E_FORMAT, "decompress: shorter than a header");
-    Header h;
-    CU(c, cudaMemcpyAsync(&h, d_src, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    // header and (normally) the whole prelude in one copy
+    const size_t head = std::min<size_t>(src_bytes, B200ANS_HEADER_BYTES + 4032);
+    c->front.resize(std::max(c->front.size(), head));
+    CU(c, cudaMemcpyAsync(c->front.data(), d_src, head, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
+    Header h;
+    std::memcpy(&h, c->front.data(), sizeof h);
     if (h.magic != B200ANS_MAGIC || h.version != 1)
         return c->fail(B200ANS_E_FORMAT, "decompress: bad magic / version");
     if (h.method != method || (h.fidelity != f && (method == METHOD_FOLD || method == METHOD_RFOLD)))
@@ -1456,18 +1533,21 @@ extern "C" int b200ans_decompress_device(b200ans_ctx* c, int method, uint32_t f,
     if (payload_at + h.payload_bytes > src_bytes)
         return c->fail(B200ANS_E_FORMAT, "decompress: container truncated");
     std::vector<uint8_t> prelude(h.prelude_bytes);
-    CU(c, cudaMemcpyAsync(prelude.data(), d_src + B200ANS_HEADER_BYTES, h.prelude_bytes, cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+    const size_t have = std::min<size_t>(h.prelude_bytes, head - B200ANS_HEADER_BYTES);
+    std::memcpy(prelude.data(), c->front.data() + B200ANS_HEADER_BYTES, have);
+    if (have < h.prelude_bytes) {
+        CU(c, cudaMemcpyAsync(prelude.data() + have, d_src + B200ANS_HEADER_BYTES + have, h.prelude_bytes - have,
+            cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+    }
     RET(b200ans_model_load(c, method, f, prelude.data(), prelude.size(), nullptr));
     CU(c, c->offsets.reserve(size_t(h.n_blocks) * 8));
     const uint32_t* d_sizes = reinterpret_cast<const uint32_t*>(d_src + table_at);
-    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, h.n_blocks, c->offsets.as<uint64_t>(), c->d_totals());
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, h.n_blocks, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
     c->stats.launches++;
     CU(c, cudaGetLastError());
-    uint64_t totals[2] = { 0, 0 };
-    CU(c, cudaMemcpyAsync(totals, c->d_totals(), 16, cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
-    if (totals[0] != h.payload_bytes)
+    RET(read_small(c));
+    if (c->h_small()->totals[0] != h.payload_bytes)
         return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
     const uint32_t saved = c->block_syms;
     c->block_syms = h.block_syms;

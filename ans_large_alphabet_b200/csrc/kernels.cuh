@@ -653,7 +653,7 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
 
 // offsets[b] = sum_{b' < b} roundup16(bytes[b']); total[0] = sum of all; total[1] = unpadded sum
 __global__ void __launch_bounds__(1024) scan_block_sizes_kernel(const uint32_t* __restrict__ bytes, uint32_t n_blocks,
-    uint64_t* __restrict__ offsets, uint64_t* __restrict__ totals)
+    uint64_t* __restrict__ offsets, uint64_t* __restrict__ totals, uint64_t* __restrict__ header_total)
 {
     __shared__ uint64_t s_part[1024];
     __shared__ uint64_t s_raw[1024];
@@ -688,6 +688,8 @@ __global__ void __launch_bounds__(1024) scan_block_sizes_kernel(const uint32_t* 
     if (threadIdx.x == blockDim.x - 1) {
         totals[0] = s_part[threadIdx.x];
         totals[1] = s_raw[threadIdx.x];
+        if (header_total) // the container header's payload_bytes field
+            *header_total = s_part[threadIdx.x];
     }
 }
 
@@ -695,15 +697,18 @@ __global__ void __launch_bounds__(1024) scan_block_sizes_kernel(const uint32_t* 
 // Four 16-byte chunks per lane in flight (a block is ~0.9 chunks per lane and pass otherwise: latency-bound).
 __global__ void __launch_bounds__(256) compact_kernel(const uint8_t* __restrict__ scratch, uint64_t stride,
     const uint32_t* __restrict__ bytes, const uint64_t* __restrict__ offsets, uint32_t n_blocks,
-    uint8_t* __restrict__ payload, uint32_t* __restrict__ size_table)
+    uint8_t* __restrict__ payload, uint32_t* __restrict__ size_table, uint64_t payload_capacity)
 {
     const uint32_t warps_per_cta = blockDim.x >> 5;
     const uint32_t lane = lane_id();
     for (uint32_t b = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); b < n_blocks; b += gridDim.x * warps_per_cta) {
         const uint32_t sz = bytes[b];
         const uint32_t chunks = (sz + 15u) >> 4;
+        const uint64_t at = offsets[b];
+        if (at + (uint64_t(chunks) << 4) > payload_capacity)
+            continue; // destination too small: the host reports it from the scan's total
         const uint4* src = reinterpret_cast<const uint4*>(scratch + uint64_t(b) * stride);
-        uint4* dst = reinterpret_cast<uint4*>(payload + offsets[b]);
+        uint4* dst = reinterpret_cast<uint4*>(payload + at);
         uint32_t c = lane;
         for (; c + 96u < chunks; c += 128u) {
             const uint4 v0 = __ldcs(src + c), v1 = __ldcs(src + c + 32u), v2 = __ldcs(src + c + 64u), v3 = __ldcs(src + c + 96u);

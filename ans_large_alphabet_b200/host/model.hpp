@@ -78,6 +78,44 @@ template <class X, class Y> inline double cross_entropy(const std::vector<X>& P,
     return -acc;
 }
 
+namespace detail {
+    // cross_entropy(P, Q) for normalised frequencies Q: log2(double(Q[i]) / m) is the same call with the same
+    // argument for every symbol that got the same share, so it is evaluated once per distinct small Q[i]
+    // (same bits, fewer libm calls: the tail of a large alphabet shares a handful of values).
+    inline double cross_entropy_shared_log(const std::vector<uint64_t>& P, const std::vector<uint32_t>& Q)
+    {
+        constexpr uint32_t kMemo = 4096;
+        static thread_local double memo[kMemo];
+        static thread_local uint32_t stamp[kMemo];
+        static thread_local uint32_t epoch = 0;
+        if (++epoch == 0) {
+            std::fill(stamp, stamp + kMemo, 0u);
+            epoch = 1;
+        }
+        const double n = int_accumulated_sum(P);
+        const double m = int_accumulated_sum(Q);
+        double acc = 0.0;
+        for (size_t i = 0; i < P.size(); i++) {
+            if (P[i] == 0 || Q[i] == 0)
+                continue;
+            const double p = double(P[i]) / n;
+            const uint32_t share = Q[i];
+            double lg;
+            if (share < kMemo) {
+                if (stamp[share] != epoch) {
+                    memo[share] = std::log2(double(share) / m);
+                    stamp[share] = epoch;
+                }
+                lg = memo[share];
+            } else {
+                lg = std::log2(double(share) / m);
+            }
+            acc = std::fma(p, lg, acc);
+        }
+        return -acc;
+    }
+}
+
 // Fit F (symbols visited in `mapping` order, rarest first) into a frame of exactly M slots.
 // Returns true when the fit FAILED (slots left over or overdrawn), like the reference.
 inline bool scale_freqs(std::vector<uint32_t>& S, const std::vector<uint64_t>& F, std::vector<uint32_t>& mapping,
@@ -96,6 +134,42 @@ inline bool scale_freqs(std::vector<uint32_t>& S, const std::vector<uint64_t>& F
             break;
     }
     return M != 0;
+}
+
+namespace detail {
+    // scale_freqs for the frames M0, 2·M0, ... 2^(K-1)·M0 in one sweep (K independent dependency chains).
+    // failed[j] and S[j] are what scale_freqs(S, F, mapping, M0 << j, ...) gives on a zeroed S; entries a failed fit
+    // leaves behind are never looked at.
+    template <int K>
+    inline void scale_freqs_batch(std::vector<uint32_t> (&S)[K], bool (&failed)[K], const std::vector<uint64_t>& F,
+        const std::vector<uint32_t>& mapping, int64_t M0, size_t sigma, size_t freq_sum)
+    {
+        int64_t M[K];
+        bool live[K];
+        for (int j = 0; j < K; j++) {
+            M[j] = M0 << j;
+            live[j] = true;
+        }
+        for (size_t rank = 0; rank < sigma; rank++) {
+            const uint32_t sym = mapping[rank];
+            const double f = double(F[sym]);
+            const double rest = double(freq_sum);
+            for (int j = 0; j < K; j++) {
+                if (!live[j])
+                    continue;
+                const double ratio = double(M[j]) / rest;
+                uint32_t share = uint32_t(std::fma(ratio, f, 0.5));
+                if (share == 0)
+                    share = 1;
+                S[j][sym] = share;
+                M[j] -= share;
+                live[j] = M[j] >= 0;
+            }
+            freq_sum -= F[sym];
+        }
+        for (int j = 0; j < K; j++)
+            failed[j] = M[j] != 0;
+    }
 }
 
 // Smallest power-of-two frame whose cross entropy is within H_approx/1000 of the entropy
@@ -122,24 +196,31 @@ inline std::vector<uint32_t> adjust_freqs(
 
     const double H = entropy(freqs, freq_sum);
     const double limit = H * (1.0 + double(H_approx) / double(1000));
-    std::vector<uint32_t> cur(size_t(largest_sym) + 1, 0), last_good(size_t(largest_sym) + 1, 0);
+    // The reference tries frame, 2·frame, 4·frame, ... one after the other.  Each fit is a serial chain
+    // (divide -> round -> subtract per symbol) that does not depend on the other frames, so kBatch consecutive
+    // frames are fitted in one interleaved sweep and then examined in the reference's order.
+    constexpr int kBatch = 4;
+    std::vector<uint32_t> cand[kBatch];
+    for (auto& v : cand)
+        v.assign(size_t(largest_sym) + 1, 0);
+    std::vector<uint32_t> last_good(size_t(largest_sym) + 1, 0);
     for (;;) {
-        if (scale_freqs(cur, freqs, order, int64_t(frame), sigma, freq_sum)) {
-            frame *= 2;
-            continue;
+        bool failed[kBatch];
+        detail::scale_freqs_batch<kBatch>(cand, failed, freqs, order, int64_t(frame), sigma, freq_sum);
+        for (int j = 0; j < kBatch; j++) {
+            if (failed[j])
+                continue;
+            std::vector<uint32_t>& cur = cand[j];
+            const uint32_t top = *std::max_element(cur.begin(), cur.end());
+            const double XH = detail::cross_entropy_shared_log(freqs, cur);
+            if (require_u16 && top >= std::numeric_limits<uint16_t>::max())
+                return last_good;
+            if (XH < limit)
+                return std::move(cur);
+            last_good = cur;
         }
-        const uint32_t top = *std::max_element(cur.begin(), cur.end());
-        const double XH = cross_entropy(freqs, cur);
-        if (require_u16 && top >= std::numeric_limits<uint16_t>::max()) {
-            cur = last_good;
-            break;
-        }
-        if (XH < limit)
-            break;
-        frame *= 2;
-        last_good = cur;
+        frame <<= kBatch;
     }
-    return cur;
 }
 
 } // namespace b200ans

@@ -87,6 +87,18 @@ typedef struct b200ans_stats {
     uint64_t total_bytes;   /* whole container                                 */
 } b200ans_stats;
 
+/* What a container says about itself (the reference stores neither n nor the byte count, methods.hpp:541-546). */
+typedef struct b200ans_container {
+    int method;            /* B200ANS_METHOD_*                                   */
+    uint32_t fidelity;
+    uint64_t n_symbols;
+    uint32_t block_syms;
+    uint32_t n_blocks;
+    uint64_t prelude_bytes;
+    uint64_t payload_bytes; /* padded sum of the block payloads                  */
+    uint64_t total_bytes;   /* header + prelude + size table + payloads          */
+} b200ans_container;
+
 /* ---- context ------------------------------------------------------------------------- */
 /* stream: a cudaStream_t (as void*) to run on, or NULL to let the context create its own. */
 int b200ans_create(b200ans_ctx** out, int device, void* stream);
@@ -101,6 +113,8 @@ const char* b200ans_last_error(const b200ans_ctx* ctx);
 const char* b200ans_strerror(int code);
 const char* b200ans_method_name(int method, uint32_t fidelity, char* buf, size_t buflen);
 /* upper bound on the container size for n symbols */
+/* Host-only: parse the 64-byte header at `src` (host memory). B200ANS_E_FORMAT if it is not a b200ans container. */
+int b200ans_container_info(const uint8_t* src, size_t src_bytes, b200ans_container* out);
 size_t b200ans_compress_bound(const b200ans_ctx* ctx, int method, size_t n);
 
 /* ---- one-shot, host buffers (the methods.hpp encode/decode path) ------------------------ */
