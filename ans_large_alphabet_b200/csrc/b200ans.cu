@@ -497,7 +497,8 @@ int launch_histogram(b200ans_ctx* c, uint32_t f, const uint32_t* d_src, size_t n
     if ((a.stride & 31u) == 0)
         a.stride += 1;
     const size_t smem_bytes = size_t(a.replicas) * a.stride * sizeof(uint32_t);
-    auto k = histogram_kernel<METHOD>;
+    const bool all_smem = a.smem_bins == a.nbins;
+    auto k = all_smem ? histogram_kernel<METHOD, true> : histogram_kernel<METHOD, false>;
     CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kHistSmemWords * 4 + 1024)));
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kHistThreads, smem_bytes) != cudaSuccess || per_sm < 1) {

@@ -266,7 +266,15 @@ struct HistArgs {
     uint32_t* max_value;
 };
 
-template <int METHOD>
+__device__ __forceinline__ void red_shared_inc(uint32_t addr)
+{
+    asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(addr) : "memory");
+}
+
+// ALL_SMEM: every bin has a shared-memory counter (all folded alphabets up to fidelity 4, small raw alphabets).
+// Then counting is branch-free: bin address straight from the bit position of the value (as in lpb3_kernels.cuh
+// l3_entry_addr), one `red.shared` on a 32-bit shared address.
+template <int METHOD, bool ALL_SMEM>
 __global__ void __launch_bounds__(kHistThreads) histogram_kernel(const HistArgs a)
 {
     extern __shared__ uint32_t s_bins[];
@@ -275,18 +283,38 @@ __global__ void __launch_bounds__(kHistThreads) histogram_kernel(const HistArgs 
         s_bins[i] = 0;
     __syncthreads();
     uint32_t* mine = s_bins + (lane_id() & (a.replicas - 1u)) * a.stride;
+    const uint32_t mine_s = uint32_t(__cvta_generic_to_shared(mine));
     const uint32_t smem_bins = a.smem_bins, nbins = a.nbins, f = a.fidelity;
+    const uint32_t step = METHOD == METHOD_MSB ? 256u : (255u << (f - 1u)); // symbols per extra raw byte
+    const uint32_t fbit = METHOD == METHOD_MSB ? 1u : (1u << (f - 1u));
     uint32_t local_max = 0;
     auto count = [&](uint32_t v) {
-        uint32_t k;
         uint32_t mv = v;
         if (METHOD == METHOD_RFOLD)
             mv = v < a.n_values ? __ldg(a.mapping + v) : 0u;
-        const uint32_t bin = map_value<METHOD>(mv, f, k);
-        if (bin < smem_bins)
-            atomicAdd(mine + bin, 1u);
-        else if (bin < nbins)
-            atomicAdd(a.bins + bin, 1ull);
+        if (ALL_SMEM) {
+            if (METHOD == METHOD_INT) {
+                if (mv < nbins)
+                    red_shared_inc(mine_s + (mv << 2));
+            } else {
+                // k = raw low bytes = (highest bit above the threshold) / 8, at most 3: the bin is always in range
+                uint32_t fl;
+                if (METHOD == METHOD_MSB)
+                    fl = 31u - __clz((max(mv, 1u) - 1u) | 1u);
+                else
+                    fl = 31u - __clz(mv | fbit) - (f - 1u);
+                const uint32_t k8 = fl & 0x18u;
+                // 4 * (xs + k * step) = (8 * xs + k8 * step) / 2
+                red_shared_inc(mine_s + ((((mv >> k8) << 3) + k8 * step) >> 1));
+            }
+        } else {
+            uint32_t k;
+            const uint32_t bin = map_value<METHOD>(mv, f, k);
+            if (bin < smem_bins)
+                atomicAdd(mine + bin, 1u);
+            else if (bin < nbins)
+                atomicAdd(a.bins + bin, 1ull);
+        }
         local_max = max(local_max, v);
     };
 
