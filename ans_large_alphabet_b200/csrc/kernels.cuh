@@ -679,45 +679,62 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
 // Size scan + payload compaction
 // ------------------------------------------------------------------------------------------
 
-// offsets[b] = sum_{b' < b} roundup16(bytes[b']); total[0] = sum of all; total[1] = unpadded sum
+// offsets[b] = sum_{b' < b} roundup16(bytes[b']); total[0] = sum of all; total[1] = unpadded sum.
+// One CTA, three phases: every warp sums a contiguous run of 32-element rows (coalesced), the 32 warp totals are
+// scanned, then every warp scans its rows again with a running carry and writes the offsets (coalesced).
 __global__ void __launch_bounds__(1024) scan_block_sizes_kernel(const uint32_t* __restrict__ bytes, uint32_t n_blocks,
     uint64_t* __restrict__ offsets, uint64_t* __restrict__ totals, uint64_t* __restrict__ header_total)
 {
-    __shared__ uint64_t s_part[1024];
-    __shared__ uint64_t s_raw[1024];
-    const uint32_t per = (n_blocks + blockDim.x - 1) / blockDim.x;
-    const uint32_t b0 = min(n_blocks, threadIdx.x * per);
-    const uint32_t b1 = min(n_blocks, b0 + per);
-    uint64_t sum = 0, raw = 0;
-    for (uint32_t b = b0; b < b1; b++) {
-        sum += (uint64_t(bytes[b]) + 15u) & ~uint64_t(15);
-        raw += bytes[b];
+    __shared__ uint64_t s_pad[32];
+    __shared__ uint64_t s_raw[32];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t rows = (n_blocks + 31u) >> 5;
+    const uint32_t rows_per_warp = (rows + 31u) >> 5;
+    const uint32_t r0 = min(rows, warp * rows_per_warp), r1 = min(rows, r0 + rows_per_warp);
+    uint64_t pad = 0, raw = 0;
+#pragma unroll 4
+    for (uint32_t r = r0; r < r1; r++) {
+        const uint32_t b = (r << 5) + lane;
+        const uint32_t v = b < n_blocks ? __ldg(bytes + b) : 0u;
+        pad += (uint64_t(v) + 15u) & ~uint64_t(15);
+        raw += v;
     }
-    s_part[threadIdx.x] = sum;
-    s_raw[threadIdx.x] = raw;
+    for (int o = 16; o > 0; o >>= 1) {
+        pad += __shfl_xor_sync(0xffffffffu, pad, o);
+        raw += __shfl_xor_sync(0xffffffffu, raw, o);
+    }
+    if (lane == 0) {
+        s_pad[warp] = pad;
+        s_raw[warp] = raw;
+    }
     __syncthreads();
-    // Hillis-Steele inclusive scan over 1024 partials
-    for (uint32_t d = 1; d < blockDim.x; d <<= 1) {
-        uint64_t v = 0, r = 0;
-        if (threadIdx.x >= d) {
-            v = s_part[threadIdx.x - d];
-            r = s_raw[threadIdx.x - d];
-        }
-        __syncthreads();
-        s_part[threadIdx.x] += v;
-        s_raw[threadIdx.x] += r;
-        __syncthreads();
+    const uint64_t wp = s_pad[lane], wr = s_raw[lane];
+    uint64_t carry = lane < warp ? wp : 0, all_pad = wp, all_raw = wr;
+    for (int o = 16; o > 0; o >>= 1) {
+        carry += __shfl_xor_sync(0xffffffffu, carry, o);
+        all_pad += __shfl_xor_sync(0xffffffffu, all_pad, o);
+        all_raw += __shfl_xor_sync(0xffffffffu, all_raw, o);
     }
-    uint64_t run = s_part[threadIdx.x] - sum;
-    for (uint32_t b = b0; b < b1; b++) {
-        offsets[b] = run;
-        run += (uint64_t(bytes[b]) + 15u) & ~uint64_t(15);
-    }
-    if (threadIdx.x == blockDim.x - 1) {
-        totals[0] = s_part[threadIdx.x];
-        totals[1] = s_raw[threadIdx.x];
+    if (threadIdx.x == 0) {
+        totals[0] = all_pad;
+        totals[1] = all_raw;
         if (header_total) // the container header's payload_bytes field
-            *header_total = s_part[threadIdx.x];
+            *header_total = all_pad;
+    }
+#pragma unroll 4
+    for (uint32_t r = r0; r < r1; r++) {
+        const uint32_t b = (r << 5) + lane;
+        const uint32_t v = b < n_blocks ? __ldg(bytes + b) : 0u;
+        const uint64_t p = (uint64_t(v) + 15u) & ~uint64_t(15);
+        uint64_t incl = p;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint64_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= uint32_t(o))
+                incl += t;
+        }
+        if (b < n_blocks)
+            offsets[b] = carry + incl - p;
+        carry += __shfl_sync(0xffffffffu, incl, 31);
     }
 }
 
