@@ -184,22 +184,38 @@ inline std::vector<uint32_t> adjust_freqs(
     }
     size_t frame = is_power_of_two(sigma) ? sigma : size_t(next_power_of_two(sigma));
 
-    std::vector<std::pair<uint64_t, uint32_t>> by_freq;
-    by_freq.reserve(sigma);
-    for (size_t s = 0; s < freqs.size(); s++)
-        if (freqs[s] != 0)
-            by_freq.emplace_back(freqs[s], uint32_t(s));
-    std::sort(by_freq.begin(), by_freq.end());
+    // symbols by (frequency, symbol) ascending -- std::sort of pairs in the reference; the order is total, so any
+    // sort gives the same sequence.  Packed 64-bit keys when they fit (faster compares), pairs otherwise.
     std::vector<uint32_t> order(sigma);
-    for (size_t i = 0; i < sigma; i++)
-        order[i] = by_freq[i].second;
+    uint64_t top_freq = 0;
+    for (uint64_t f : freqs)
+        top_freq = std::max(top_freq, f);
+    if (top_freq < (uint64_t(1) << 40) && freqs.size() <= (size_t(1) << 24)) {
+        std::vector<uint64_t> keys;
+        keys.reserve(sigma);
+        for (size_t s = 0; s < freqs.size(); s++)
+            if (freqs[s] != 0)
+                keys.push_back((freqs[s] << 24) | uint64_t(s));
+        std::sort(keys.begin(), keys.end());
+        for (size_t i = 0; i < sigma; i++)
+            order[i] = uint32_t(keys[i] & 0xFFFFFFu);
+    } else {
+        std::vector<std::pair<uint64_t, uint32_t>> by_freq;
+        by_freq.reserve(sigma);
+        for (size_t s = 0; s < freqs.size(); s++)
+            if (freqs[s] != 0)
+                by_freq.emplace_back(freqs[s], uint32_t(s));
+        std::sort(by_freq.begin(), by_freq.end());
+        for (size_t i = 0; i < sigma; i++)
+            order[i] = by_freq[i].second;
+    }
 
     const double H = entropy(freqs, freq_sum);
     const double limit = H * (1.0 + double(H_approx) / double(1000));
     // The reference tries frame, 2·frame, 4·frame, ... one after the other.  Each fit is a serial chain
     // (divide -> round -> subtract per symbol) that does not depend on the other frames, so kBatch consecutive
     // frames are fitted in one interleaved sweep and then examined in the reference's order.
-    constexpr int kBatch = 4;
+    constexpr int kBatch = 8;
     std::vector<uint32_t> cand[kBatch];
     for (auto& v : cand)
         v.assign(size_t(largest_sym) + 1, 0);
