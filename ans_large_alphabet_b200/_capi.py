@@ -49,6 +49,11 @@ SIGNATURES = {
     "b200ans_set_block_syms": (C.c_int, [C.c_void_p, C.c_uint32]),
     "b200ans_set_kernel_path": (C.c_int, [C.c_void_p, C.c_int]),
     "b200ans_set_h_approx": (C.c_int, [C.c_void_p, C.c_uint32]),
+    "b200ans_pa_compress_bound": (C.c_size_t, [C.c_void_p, C.c_int, C.c_uint32, C.c_size_t]),
+    "b200ans_pa_compress": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
+    "b200ans_pa_decompress": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "b200ans_pa_compress_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
+    "b200ans_pa_decompress_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "b200ans_container_info": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(Container)]),
     "b200ans_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "b200ans_last_error": (C.c_char_p, [C.c_void_p]),
@@ -268,6 +273,32 @@ class Codec:
             out = np.empty(n, dtype=np.uint32)
         self._check(self.lib.b200ans_decompress(self.h, method, f, out.ctypes.data, n, blob.ctypes.data, blob.size))
         return out
+
+    # ---- pseudo-adaptive mode: one model per `model_syms` symbols (pseudo_adaptive.cpp) ----
+    def pa_bound(self, method, model_syms, n):
+        return self.lib.b200ans_pa_compress_bound(self.h, method, model_syms, n)
+
+    def pa_compress(self, method, f, model_syms, data):
+        data = np.ascontiguousarray(data, dtype=np.uint32)
+        out = np.empty(self.pa_bound(method, model_syms, data.size), dtype=np.uint8)
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_pa_compress(self.h, method, f, model_syms, out.ctypes.data, out.size, data.ctypes.data,
+                                                 data.size, C.byref(nb)))
+        return out[: nb.value]
+
+    def pa_decompress(self, method, f, blob, n):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        out = np.empty(n, dtype=np.uint32)
+        self._check(self.lib.b200ans_pa_decompress(self.h, method, f, out.ctypes.data, n, blob.ctypes.data, blob.size))
+        return out
+
+    def pa_compress_device(self, method, f, model_syms, d_dst, cap, d_src, n):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_pa_compress_device(self.h, method, f, model_syms, d_dst, cap, d_src, n, C.byref(nb)))
+        return nb.value
+
+    def pa_decompress_device(self, method, f, d_dst, n, d_src, nbytes):
+        self._check(self.lib.b200ans_pa_decompress_device(self.h, method, f, d_dst, n, d_src, nbytes))
 
     def compress_ptr(self, method, f, dst_ptr, cap, src_ptr, n):
         nb = C.c_size_t()

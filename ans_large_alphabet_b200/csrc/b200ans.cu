@@ -69,6 +69,7 @@ struct Header {
     uint8_t reserved[24];
 };
 static_assert(sizeof(Header) == B200ANS_HEADER_BYTES, "container header is 64 bytes");
+constexpr uint32_t kFlagPseudoAdaptive = 1u; // Header::flags bit 0: one model per block (pseudo-adaptive container)
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -91,7 +92,9 @@ struct b200ans_ctx {
     cudaEvent_t ev[8] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs;
+    uint8_t* pa_pinned = nullptr; // pseudo-adaptive mode: counts / frequencies of all models (pinned, grows on demand)
+    size_t pa_pinned_cap = 0;
     // `small` layout: [0] u32 max, [1] u32 error flag, [2..] pad; totals (2 x u64) at byte 16
     uint32_t* d_max() { return small.as<uint32_t>(); }
     uint32_t* d_err() { return small.as<uint32_t>() + 1; }
@@ -260,13 +263,15 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_bits, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out })
+             &c->dec_slots, &c->dec_bits, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs })
         b->release();
     for (auto& e : c->ev)
         if (e)
             cudaEventDestroy(e);
     if (c->pinned)
         cudaFreeHost(c->pinned);
+    if (c->pa_pinned)
+        cudaFreeHost(c->pa_pinned);
     if (c->own_stream)
         cudaStreamDestroy(c->stream);
     delete c;
@@ -1521,6 +1526,8 @@ extern "C" int b200ans_decompress_device(b200ans_ctx* c, int method, uint32_t f,
     std::memcpy(&h, c->front.data(), sizeof h);
     if (h.magic != B200ANS_MAGIC || h.version != 1)
         return c->fail(B200ANS_E_FORMAT, "decompress: bad magic / version");
+    if (h.flags & kFlagPseudoAdaptive)
+        return c->fail(B200ANS_E_FORMAT, "decompress: pseudo-adaptive container (use b200ans_pa_decompress)");
     if (h.method != method || (h.fidelity != f && (method == METHOD_FOLD || method == METHOD_RFOLD)))
         return c->fail(B200ANS_E_FORMAT, "decompress: container was written by another method");
     if (h.n_symbols != n)
@@ -1610,5 +1617,459 @@ extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32
     CU(c, cudaStreamSynchronize(c->stream));
     c->stats.ms_h2d = elapsed(c->ev[5], c->ev[6]);
     c->stats.ms_d2h = elapsed(c->ev[7], c->ev[3]);
+    return B200ANS_OK;
+}
+
+// ==========================================================================================
+// pseudo-adaptive mode: one semi-static model per block of `model_syms` symbols
+// (src/pseudo_adaptive.cpp:64-177 -- every block goes through T::encode on its own; no shared histogram)
+// ==========================================================================================
+// Container: [64-byte header, flags bit 0 set, block_syms = model_syms, n_blocks = models]
+//            [u32 prelude bytes of model m][u32 payload bytes of model m][pad to 16]
+//            [preludes, each 16-byte aligned][payloads, each 16-byte aligned]
+// prelude(m) followed by payload(m) is exactly what the reference's ans_X_compress() writes for block m.
+// Device: K1 per block (pa_histogram_kernel) -> host: normalise + prelude for all blocks on all host cores ->
+// device: encoder tables from the frequencies (pa_enc_tables_kernel), one reference-format stream per block
+// (encode_kernel<.., PA>), size scan + compaction.  Decode mirrors it (pa_dec_tables_kernel, decode_kernel<.., PA>).
+#include <atomic>
+#include <thread>
+
+namespace {
+
+template <class F> void parallel_for(size_t n, F&& fn)
+{
+    const unsigned hw = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+    const size_t threads = std::min<size_t>(hw, std::max<size_t>(1, n / 8));
+    if (threads <= 1) {
+        for (size_t i = 0; i < n; i++)
+            fn(i);
+        return;
+    }
+    std::atomic<size_t> next { 0 };
+    auto work = [&]() {
+        for (;;) {
+            const size_t i0 = next.fetch_add(16);
+            if (i0 >= n)
+                return;
+            for (size_t i = i0; i < std::min(n, i0 + 16); i++)
+                fn(i);
+        }
+    };
+    std::vector<std::thread> pool;
+    for (size_t t = 1; t < threads; t++)
+        pool.emplace_back(work);
+    work();
+    for (auto& t : pool)
+        t.join();
+}
+
+int pa_check(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms)
+{
+    if (!(method == METHOD_MSB || (method == METHOD_FOLD && f >= 1 && f <= 2)))
+        return c->fail(B200ANS_E_ARG, "pseudo-adaptive mode: ANSfold-1, ANSfold-2 and ANSmsb (alphabets up to 2048 bins)");
+    if (model_syms < 1024 || model_syms % 128 != 0 || model_syms > (1u << 24))
+        return c->fail(B200ANS_E_ARG, "pseudo-adaptive mode: symbols per model must be a multiple of 128 in [1024, 2^24]");
+    return B200ANS_OK;
+}
+
+// pinned staging that grows on demand
+int pa_pinned(b200ans_ctx* c, size_t bytes)
+{
+    if (bytes <= c->pa_pinned_cap)
+        return B200ANS_OK;
+    if (c->pa_pinned)
+        cudaFreeHost(c->pa_pinned);
+    c->pa_pinned = nullptr;
+    c->pa_pinned_cap = 0;
+    CU(c, cudaHostAlloc(reinterpret_cast<void**>(&c->pa_pinned), bytes + bytes / 8, cudaHostAllocDefault));
+    c->pa_pinned_cap = bytes + bytes / 8;
+    return B200ANS_OK;
+}
+
+} // namespace
+
+extern "C" size_t b200ans_pa_compress_bound(const b200ans_ctx* c, int method, uint32_t model_syms, size_t n)
+{
+    (void)c;
+    if (model_syms == 0)
+        return 0;
+    const size_t models = (n + model_syms - 1) / model_syms;
+    // per model: prelude (<= 8 bytes per bin + header), sizes, padding; per symbol at most 7 bytes + states
+    const size_t per_model = size_t(2048) * 8 + 128 + 8 + 32 + 64;
+    return B200ANS_HEADER_BYTES + models * per_model + n * (method == METHOD_INT ? 4 : 7) + 64;
+}
+
+extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms, uint8_t* d_dst,
+    size_t cap, const uint32_t* d_src, size_t n, size_t* out_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_dst || !out_bytes || (!d_src && n) || (reinterpret_cast<uintptr_t>(d_src) & 15) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
+        return c->fail(B200ANS_E_ARG, "pa_compress: bad argument (device buffers must be 16-byte aligned)");
+    RET(pa_check(c, method, f, model_syms));
+    CU(c, cudaSetDevice(c->device));
+    c->stats.ms_histogram = c->stats.ms_encode = c->stats.ms_compact = c->stats.ms_model = 0.f;
+    const uint64_t nm64 = (n + model_syms - 1) / model_syms;
+    if (nm64 > (uint64_t(1) << 24))
+        return c->fail(B200ANS_E_ARG, "pa_compress: more than 2^24 models");
+    const uint32_t nm = uint32_t(nm64);
+    Header h {};
+    h.magic = B200ANS_MAGIC;
+    h.version = 1;
+    h.method = uint8_t(method);
+    h.fidelity = uint8_t(f);
+    h.n_symbols = n;
+    h.block_syms = model_syms;
+    h.n_blocks = nm;
+    h.flags = kFlagPseudoAdaptive;
+    if (n == 0) {
+        if (cap < B200ANS_HEADER_BYTES)
+            return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
+        CU(c, cudaMemcpyAsync(d_dst, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        *out_bytes = B200ANS_HEADER_BYTES;
+        return B200ANS_OK;
+    }
+    const uint32_t nbins = uint32_t(alphabet_bins(method, f, 0));
+
+    // K1 per model block
+    CU(c, cudaEventRecord(c->ev[3], c->stream));
+    CU(c, c->bins.reserve(size_t(nm) * nbins * 4));
+    CU(c, cudaMemsetAsync(c->d_max(), 0, 4, c->stream));
+    {
+        const int grid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
+        const size_t smem = size_t(4) * (nbins | 1u) * 4;
+        if (method == METHOD_MSB)
+            pa_histogram_kernel<METHOD_MSB><<<grid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
+        else
+            pa_histogram_kernel<METHOD_FOLD><<<grid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    }
+    CU(c, cudaEventRecord(c->ev[4], c->stream));
+    const size_t bins_bytes = size_t(nm) * nbins * 4;
+    RET(pa_pinned(c, bins_bytes + nm));
+    CU(c, cudaMemcpyAsync(c->pa_pinned, c->bins.p, bins_bytes, cudaMemcpyDeviceToHost, c->stream));
+    RET(read_small(c));
+    c->stats.ms_histogram = elapsed(c->ev[3], c->ev[4]);
+    if (c->h_small()->max_value >= (1u << 30))
+        return c->fail(B200ANS_E_DOMAIN, "folded coders need values < 2^30");
+
+    // host: normalise + prelude per model, all cores; the frequencies go back in place of the counts
+    const double t0 = now_ms();
+    uint32_t* counts = reinterpret_cast<uint32_t*>(c->pa_pinned);
+    uint8_t* lg = c->pa_pinned + bins_bytes;
+    std::vector<std::vector<uint8_t>> preludes(nm);
+    std::atomic<int> bad { 0 };
+    const uint32_t h_approx = c->h_approx;
+    parallel_for(nm, [&](size_t m) {
+        uint32_t* row = counts + m * nbins;
+        std::vector<uint64_t> freqs(nbins);
+        uint32_t max_sym = 0;
+        for (uint32_t b = 0; b < nbins; b++) {
+            freqs[b] = row[b];
+            if (row[b])
+                max_sym = b;
+        }
+        freqs.resize(size_t(max_sym) + 1);
+        std::vector<uint32_t> nf = adjust_freqs(freqs, max_sym, true, h_approx);
+        uint64_t frame = 0;
+        for (uint32_t v : nf)
+            frame += v;
+        if (!is_power_of_two(frame) || frame > (uint64_t(1) << 20)) {
+            bad = 1;
+            return;
+        }
+        lg[m] = uint8_t(63 - __builtin_clzll(frame));
+        std::vector<uint8_t>& pre = preludes[m];
+        pre.assign(nf.size() * 8 + 64, 0);
+        uint8_t* p = pre.data();
+        ans_serialize_interp(nf, size_t(frame), p);
+        pre.resize(size_t(p - pre.data()));
+        std::fill(row, row + nbins, 0u);
+        std::copy(nf.begin(), nf.end(), row);
+    });
+    if (bad)
+        return c->fail(B200ANS_E_DOMAIN, "pa_compress: normalisation produced an unusable frame size");
+    c->stats.ms_model = float(now_ms() - t0);
+
+    // front: header, size arrays, preludes
+    size_t pre_region = 0;
+    for (const auto& p : preludes)
+        pre_region += align_up(p.size(), 16);
+    const size_t sizes_at = B200ANS_HEADER_BYTES;
+    const size_t pre_at = align_up(sizes_at + size_t(nm) * 8, 16);
+    const size_t payload_at = pre_at + pre_region;
+    if (cap < payload_at)
+        return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
+    if (pre_region > 0xFFFFFFF0ull)
+        return c->fail(B200ANS_E_ARG, "pa_compress: preludes exceed 4 GiB");
+    h.prelude_bytes = uint32_t(pre_region);
+    c->front.assign(payload_at, 0);
+    std::memcpy(c->front.data(), &h, sizeof h);
+    {
+        uint32_t* pre_sizes = reinterpret_cast<uint32_t*>(c->front.data() + sizes_at);
+        size_t at = pre_at;
+        for (uint32_t m = 0; m < nm; m++) {
+            pre_sizes[m] = uint32_t(preludes[m].size());
+            std::memcpy(c->front.data() + at, preludes[m].data(), preludes[m].size());
+            at += align_up(preludes[m].size(), 16);
+        }
+    }
+    CU(c, cudaMemcpyAsync(d_dst, c->front.data(), payload_at, cudaMemcpyHostToDevice, c->stream));
+
+    // device: frequencies -> encoder tables -> one stream per model block
+    CU(c, c->pa_nfreqs.reserve(bins_bytes + nm));
+    CU(c, cudaMemcpyAsync(c->pa_nfreqs.p, c->pa_pinned, bins_bytes + nm, cudaMemcpyHostToDevice, c->stream));
+    CU(c, c->enc_table.reserve(size_t(nm) * nbins * sizeof(EncEntry)));
+    c->have_enc = false; // the single-model encoder table is gone
+    const int tgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
+    pa_enc_tables_kernel<<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, c->enc_table.as<EncEntry>());
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+
+    const size_t stride = block_stride(method, model_syms);
+    CU(c, c->scratch.reserve(stride * nm));
+    CU(c, c->block_bytes.reserve(size_t(nm) * 4));
+    CU(c, c->offsets.reserve(size_t(nm) * 8));
+    EncArgs a {};
+    a.in = d_src;
+    a.n = n;
+    a.block_syms = model_syms;
+    a.n_blocks = nm;
+    a.table = c->enc_table.as<EncEntry>();
+    a.n_entries = nbins;
+    a.fidelity = f;
+    a.scratch = c->scratch.as<uint8_t>();
+    a.stride = stride;
+    a.block_bytes = c->block_bytes.as<uint32_t>();
+    a.error_flag = c->d_err();
+    a.pa_log2 = c->pa_nfreqs.as<uint8_t>() + bins_bytes;
+    a.pa_table_stride = nbins;
+    CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    {
+        const size_t rows = size_t(kEncWarps) * 8 * kEncRowBytes;
+        const uint32_t n_tasks = (nm + 7) / 8;
+        if (method == METHOD_MSB) {
+            auto k = encode_kernel<METHOD_MSB, false, true>;
+            k<<<persistent_grid(c, k, kEncWarps * 32, rows, n_tasks, kEncWarps), kEncWarps * 32, rows, c->stream>>>(a);
+        } else {
+            auto k = encode_kernel<METHOD_FOLD, false, true>;
+            k<<<persistent_grid(c, k, kEncWarps * 32, rows, n_tasks, kEncWarps), kEncWarps * 32, rows, c->stream>>>(a);
+        }
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    }
+    CU(c, cudaEventRecord(c->ev[1], c->stream));
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(c->block_bytes.as<uint32_t>(), nm, c->offsets.as<uint64_t>(), c->d_totals(),
+        reinterpret_cast<uint64_t*>(d_dst + offsetof(Header, payload_bytes)));
+    const int cgrid = int(std::max<uint32_t>(1, std::min<uint32_t>((nm + 7) / 8, uint32_t(c->num_sms) * 8)));
+    compact_kernel<<<cgrid, 256, 0, c->stream>>>(c->scratch.as<uint8_t>(), stride, c->block_bytes.as<uint32_t>(), c->offsets.as<uint64_t>(),
+        nm, d_dst + payload_at, reinterpret_cast<uint32_t*>(d_dst + sizes_at + size_t(nm) * 4), uint64_t(cap - payload_at));
+    c->stats.launches += 2;
+    CU(c, cudaGetLastError());
+    CU(c, cudaEventRecord(c->ev[2], c->stream));
+    RET(read_small(c));
+    if (c->h_small()->error_flag)
+        return c->fail(B200ANS_E_DOMAIN, "pa_compress: a symbol had no frequency in its block's model");
+    const size_t total = payload_at + c->h_small()->totals[0];
+    if (cap < total)
+        return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
+    *out_bytes = total;
+    c->stats.ms_encode = elapsed(c->ev[0], c->ev[1]);
+    c->stats.ms_compact = elapsed(c->ev[1], c->ev[2]);
+    c->stats.n_blocks = nm;
+    c->stats.prelude_bytes = pre_region;
+    c->stats.payload_bytes = c->h_small()->totals[1];
+    c->stats.total_bytes = total;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, size_t n,
+    const uint8_t* d_src, size_t src_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!d_dst && n) || !d_src || (reinterpret_cast<uintptr_t>(d_src) & 15))
+        return c->fail(B200ANS_E_ARG, "pa_decompress: bad argument (d_src must be 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    c->stats.ms_decode = c->stats.ms_model = 0.f;
+    if (src_bytes < B200ANS_HEADER_BYTES)
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: shorter than a header");
+    Header h;
+    CU(c, cudaMemcpyAsync(&h, d_src, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (h.magic != B200ANS_MAGIC || h.version != 1 || !(h.flags & kFlagPseudoAdaptive))
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: not a pseudo-adaptive b200ans container");
+    if (h.method != method || h.fidelity != f)
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: container was written by another method");
+    if (h.n_symbols != n)
+        return c->fail(B200ANS_E_ARG, "pa_decompress: symbol count does not match the container");
+    if (n == 0)
+        return B200ANS_OK;
+    RET(pa_check(c, method, f, h.block_syms));
+    const uint32_t nm = h.n_blocks;
+    if (nm != (n + h.block_syms - 1) / h.block_syms)
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: inconsistent block geometry");
+    const uint32_t nbins = uint32_t(alphabet_bins(method, f, 0));
+    const size_t sizes_at = B200ANS_HEADER_BYTES;
+    const size_t pre_at = align_up(sizes_at + size_t(nm) * 8, 16);
+    const size_t payload_at = pre_at + h.prelude_bytes;
+    if (payload_at + h.payload_bytes > src_bytes)
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: container truncated");
+
+    // host: prelude sizes + preludes -> frequencies of every model
+    const size_t bins_bytes = size_t(nm) * nbins * 4;
+    RET(pa_pinned(c, std::max(bins_bytes + nm, payload_at + 64)));
+    std::vector<uint8_t> front(payload_at + 16, 0);
+    CU(c, cudaMemcpyAsync(front.data(), d_src, payload_at, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    const double t0 = now_ms();
+    const uint32_t* pre_sizes = reinterpret_cast<const uint32_t*>(front.data() + sizes_at);
+    std::vector<size_t> pre_off(nm);
+    {
+        size_t at = pre_at;
+        for (uint32_t m = 0; m < nm; m++) {
+            pre_off[m] = at;
+            if (pre_sizes[m] < 3 || pre_sizes[m] > payload_at - at)
+                return c->fail(B200ANS_E_FORMAT, "pa_decompress: prelude size table does not fit the container");
+            at += align_up(pre_sizes[m], 16);
+        }
+        if (at != payload_at)
+            return c->fail(B200ANS_E_FORMAT, "pa_decompress: prelude sizes do not add up");
+    }
+    uint32_t* rows = reinterpret_cast<uint32_t*>(c->pa_pinned);
+    uint8_t* lg = c->pa_pinned + bins_bytes;
+    std::atomic<int> bad { 0 };
+    parallel_for(nm, [&](size_t m) {
+        std::vector<uint8_t> buf(size_t(pre_sizes[m]) + 16, 0); // the interp reader may look one word past the end
+        std::memcpy(buf.data(), front.data() + pre_off[m], pre_sizes[m]);
+        const uint8_t* q = buf.data();
+        const uint32_t max_sym = vbyte_decode_u32(q);
+        if (size_t(max_sym) + 1 > nbins || *q > 20) {
+            bad = 1;
+            return;
+        }
+        size_t used = 0;
+        const std::vector<uint32_t> nf = ans_load_interp(buf.data(), &used);
+        uint64_t frame = 0;
+        for (uint32_t v : nf)
+            frame += v;
+        if (used > size_t(pre_sizes[m]) + 4 || nf.size() > nbins || !is_power_of_two(frame) || frame > (uint64_t(1) << 20)
+            || *std::max_element(nf.begin(), nf.end()) > 65535u) {
+            bad = 1;
+            return;
+        }
+        uint32_t* row = rows + m * nbins;
+        std::fill(row, row + nbins, 0u);
+        std::copy(nf.begin(), nf.end(), row);
+        lg[m] = uint8_t(63 - __builtin_clzll(frame));
+    });
+    if (bad)
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: a block's prelude is not a valid model");
+    uint32_t max_lg = 0;
+    for (uint32_t m = 0; m < nm; m++)
+        max_lg = std::max<uint32_t>(max_lg, lg[m]);
+    const uint64_t slot_stride = uint64_t(1) << max_lg;
+    if (slot_stride * nm * sizeof(DecEntry) > (uint64_t(48) << 30))
+        return c->fail(B200ANS_E_ARG, "pa_decompress: slot tables of all models exceed 48 GiB; decode in pieces");
+    c->stats.ms_model = float(now_ms() - t0);
+
+    CU(c, c->pa_nfreqs.reserve(bins_bytes + nm));
+    CU(c, cudaMemcpyAsync(c->pa_nfreqs.p, c->pa_pinned, bins_bytes + nm, cudaMemcpyHostToDevice, c->stream));
+    CU(c, c->dec_slots.reserve(slot_stride * nm * sizeof(DecEntry)));
+    c->have_dec = false;
+    const uint8_t* d_lg = c->pa_nfreqs.as<uint8_t>() + bins_bytes;
+    const int tgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
+    if (method == METHOD_MSB)
+        pa_dec_tables_kernel<METHOD_MSB><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
+    else
+        pa_dec_tables_kernel<METHOD_FOLD><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+
+    CU(c, c->offsets.reserve(size_t(nm) * 8));
+    const uint32_t* d_sizes = reinterpret_cast<const uint32_t*>(d_src + sizes_at + size_t(nm) * 4);
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, nm, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    RET(read_small(c));
+    if (c->h_small()->totals[0] != h.payload_bytes)
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: block size table does not add up");
+
+    DecArgs a {};
+    a.payload = d_src + payload_at;
+    a.offsets = c->offsets.as<uint64_t>();
+    a.block_bytes = d_sizes;
+    a.out = d_dst;
+    a.n = n;
+    a.block_syms = h.block_syms;
+    a.n_blocks = nm;
+    a.fidelity = f;
+    a.slots = c->dec_slots.as<DecEntry>();
+    a.pa_log2 = d_lg;
+    a.pa_slot_stride = slot_stride;
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    {
+        const size_t smem = size_t(kDecWarps) * 8 * kDecRowBytes;
+        const uint32_t n_tasks = (nm + 7) / 8;
+        if (method == METHOD_MSB) {
+            auto k = decode_kernel<METHOD_MSB, DEC_FOLD_GLOBAL, true>;
+            k<<<persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps), kDecWarps * 32, smem, c->stream>>>(a);
+        } else {
+            auto k = decode_kernel<METHOD_FOLD, DEC_FOLD_GLOBAL, true>;
+            k<<<persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps), kDecWarps * 32, smem, c->stream>>>(a);
+        }
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    }
+    CU(c, cudaEventRecord(c->ev[1], c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
+    c->stats.n_blocks = nm;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_pa_compress(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms, uint8_t* dst, size_t cap,
+    const uint32_t* src, size_t n, size_t* out_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!dst || !out_bytes || (!src && n) || model_syms == 0)
+        return c->fail(B200ANS_E_ARG, "pa_compress: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    const size_t bound = std::min(b200ans_pa_compress_bound(c, method, model_syms, n), std::max<size_t>(cap + 64, 4096));
+    CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
+    CU(c, c->io_out.reserve(bound));
+    if (n)
+        CU(c, cudaMemcpyAsync(c->io_in.p, src, n * 4, cudaMemcpyHostToDevice, c->stream));
+    size_t bytes = 0;
+    RET(b200ans_pa_compress_device(c, method, f, model_syms, c->io_out.as<uint8_t>(), std::min(bound, c->io_out.cap),
+        c->io_in.as<uint32_t>(), n, &bytes));
+    if (bytes > cap)
+        return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
+    CU(c, cudaMemcpyAsync(dst, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    *out_bytes = bytes;
+    return B200ANS_OK;
+}
+
+extern "C" int b200ans_pa_decompress(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src,
+    size_t src_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!dst && n) || !src)
+        return c->fail(B200ANS_E_ARG, "pa_decompress: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->io_out.reserve(src_bytes + 64));
+    CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
+    CU(c, cudaMemcpyAsync(c->io_out.p, src, src_bytes, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaMemsetAsync(c->io_out.as<uint8_t>() + src_bytes, 0, 64, c->stream));
+    RET(b200ans_pa_decompress_device(c, method, f, c->io_in.as<uint32_t>(), n, c->io_out.as<uint8_t>(), src_bytes));
+    if (n)
+        CU(c, cudaMemcpyAsync(dst, c->io_in.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
     return B200ANS_OK;
 }

@@ -74,6 +74,9 @@ struct EncArgs {
     uint32_t* block_bytes;   // out: payload bytes of block b
     uint32_t* error_flag;    // set to non-zero if a symbol had no model entry
     uint32_t fast_div;       // every frequency < 2^16: states stay below 2^52 (lpb_kernels.cuh ans_push52)
+    // pseudo-adaptive mode: block b has its own model -- table + b * pa_table_stride, log2 M = pa_log2[b]
+    const uint8_t* pa_log2;
+    uint64_t pa_table_stride; // entries
 };
 
 struct DecArgs {
@@ -92,6 +95,9 @@ struct DecArgs {
     const RankEntry* rank_ent; // INT: n_present entries
     uint32_t n_present;
     uint32_t dense;            // INT: every id 0..max_sym is present, so the rank is the symbol
+    // pseudo-adaptive mode: block b decodes with slots + b * pa_slot_stride and log2 M = pa_log2[b]
+    const uint8_t* pa_log2;
+    uint64_t pa_slot_stride; // entries
 };
 
 enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3 };
@@ -368,9 +374,10 @@ constexpr int kEncTile = 8;            // steps between drains
 constexpr int kEncRowBytes = 272;      // 15 carried + 28 * kEncTile + 32 (states) <= 271; 272 = 17 * 16 spreads banks
 constexpr int kEncMaxSmemEntries = 6144; // 96 KiB of EncEntry
 
-template <int METHOD, bool TABLE_SMEM>
+template <int METHOD, bool TABLE_SMEM, bool PA = false>
 __global__ void __launch_bounds__(kEncWarps * 32) encode_kernel(const EncArgs a)
 {
+    static_assert(!(PA && TABLE_SMEM), "per-block models live in global memory");
     extern __shared__ __align__(16) uint8_t smem_raw[];
     EncEntry* s_table = reinterpret_cast<EncEntry*>(smem_raw);
     uint8_t* s_rows = smem_raw + (TABLE_SMEM ? size_t(a.n_entries) * sizeof(EncEntry) : 0);
@@ -389,15 +396,22 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_kernel(const EncArgs a)
     const uint32_t g = lane & 3u;           // position inside a 4-symbol step; chain = 3 - g
     const uint32_t grp_base = lane & ~3u;
     uint8_t* row = s_rows + (size_t(warp) * 8 + grp) * kEncRowBytes;
-    const EncEntry* table = TABLE_SMEM ? s_table : a.table;
-    const uint32_t log2_frame = a.log2_frame;
+    const EncEntry* table0 = TABLE_SMEM ? s_table : a.table;
     const uint32_t f = a.fidelity;
-    const uint64_t lower = uint64_t(kAnsK) << log2_frame; // L = K * M (ans_fold.hpp:91)
 
     const uint32_t n_tasks = (a.n_blocks + 7u) >> 3;
     for (uint32_t task = blockIdx.x * kEncWarps + warp; task < n_tasks; task += gridDim.x * kEncWarps) {
         const uint32_t blk = task * 8 + grp;
         const bool have_block = blk < a.n_blocks;
+        // the model: one for all blocks, or (pseudo-adaptive) the block's own
+        const EncEntry* table = table0;
+        uint32_t log2_frame = a.log2_frame;
+        if (PA) {
+            const uint32_t m = min(blk, a.n_blocks - 1u);
+            table = a.table + uint64_t(m) * a.pa_table_stride;
+            log2_frame = a.pa_log2[m];
+        }
+        const uint64_t lower = uint64_t(kAnsK) << log2_frame; // L = K * M (ans_fold.hpp:91)
         const uint64_t first = uint64_t(blk) * a.block_syms;
         const uint32_t nb = have_block ? uint32_t(min(uint64_t(a.block_syms), a.n - first)) : 0u;
         const uint32_t* src = a.in + first;
@@ -564,11 +578,11 @@ constexpr int kDecPad = 16;        // bytes in front of the staged window (windo
 constexpr int kDecStageChunks = 18; // 16-byte chunks staged per refill: covers 28*8 + 12 + 4 + alignment
 constexpr int kDecRowBytes = kDecPad + kDecStageChunks * 16; // 304 = 19 * 16
 
-template <int METHOD, int TABLE>
+template <int METHOD, int TABLE, bool PA = false>
 __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
 {
+    static_assert(!PA || TABLE == DEC_FOLD_GLOBAL, "per-block models: folded slot tables in global memory");
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    const uint32_t frame = 1u << a.log2_frame;
     DecTables<METHOD, TABLE> tables;
     uint8_t* s_rows = smem_raw + tables.load(a, smem_raw);
 
@@ -578,15 +592,20 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
     const uint32_t g = lane & 3u;
     const uint32_t grp_last = lane | 3u;
     uint8_t* row = s_rows + (size_t(warp) * 8 + grp) * kDecRowBytes;
-    const uint32_t log2_frame = a.log2_frame;
-    const uint32_t frame_mask = frame - 1u;
-    const uint64_t lower = uint64_t(kAnsK) << log2_frame;
     const uint32_t rfold_bias = (METHOD == METHOD_RFOLD) ? (1u << (a.fidelity + 7)) : 0u; // ans_reorder_fold.hpp:301
 
     const uint32_t n_tasks = (a.n_blocks + 7u) >> 3;
     for (uint32_t task = blockIdx.x * kDecWarps + warp; task < n_tasks; task += gridDim.x * kDecWarps) {
         const uint32_t blk = task * 8 + grp;
         const bool have_block = blk < a.n_blocks;
+        uint32_t log2_frame = a.log2_frame;
+        if (PA) {
+            const uint32_t m = min(blk, a.n_blocks - 1u);
+            tables.slots = a.slots + uint64_t(m) * a.pa_slot_stride;
+            log2_frame = a.pa_log2[m];
+        }
+        const uint32_t frame_mask = (1u << log2_frame) - 1u;
+        const uint64_t lower = uint64_t(kAnsK) << log2_frame;
         const uint64_t first = uint64_t(blk) * a.block_syms;
         const uint32_t nb = have_block ? uint32_t(min(uint64_t(a.block_syms), a.n - first)) : 0u;
         const uint32_t tail = nb & 3u;
@@ -768,5 +787,166 @@ __global__ void __launch_bounds__(256) compact_kernel(const uint8_t* __restrict_
             size_table[b] = sz;
     }
 }
+
+// ------------------------------------------------------------------------------------------
+// Pseudo-adaptive mode (src/pseudo_adaptive.cpp:64-177): one model per block, no shared histogram
+// ------------------------------------------------------------------------------------------
+
+// shared-memory byte offset of a value's bin (folded / msb alphabets), as in histogram_kernel<.., true>
+template <int METHOD> __device__ __forceinline__ uint32_t pa_bin_offset(uint32_t v, uint32_t f)
+{
+    const uint32_t step = METHOD == METHOD_MSB ? 256u : (255u << (f - 1u));
+    uint32_t fl;
+    if (METHOD == METHOD_MSB)
+        fl = 31u - __clz((max(v, 1u) - 1u) | 1u);
+    else
+        fl = 31u - __clz(v | (1u << (f - 1u))) - (f - 1u);
+    const uint32_t k8 = fl & 0x18u;
+    return (((v >> k8) << 3) + k8 * step) >> 1;
+}
+
+// One CTA per model block: the block's histogram over the folded alphabet (u32 bins, plain stores -- every bin of
+// every model is written, no memset needed) and the running maximum of the raw values (domain check).
+constexpr int kPaThreads = 256;
+template <int METHOD>
+__global__ void __launch_bounds__(kPaThreads) pa_histogram_kernel(const uint32_t* __restrict__ in, uint64_t n, uint32_t model_syms,
+    uint32_t n_models, uint32_t fidelity, uint32_t nbins, uint32_t* __restrict__ bins, uint32_t* __restrict__ max_value)
+{
+    extern __shared__ uint32_t s_bins[];
+    constexpr uint32_t R = 4; // lane-striped replicas, one bank of skew each
+    const uint32_t stride = nbins | 1u;
+    const uint32_t mine_s = uint32_t(__cvta_generic_to_shared(s_bins + (lane_id() & (R - 1u)) * stride));
+    uint32_t local_max = 0;
+    for (uint32_t m = blockIdx.x; m < n_models; m += gridDim.x) {
+        for (uint32_t i = threadIdx.x; i < R * stride; i += blockDim.x)
+            s_bins[i] = 0;
+        __syncthreads();
+        const uint64_t first = uint64_t(m) * model_syms;
+        const uint32_t len = uint32_t(min(uint64_t(model_syms), n - first));
+        const uint4* in4 = reinterpret_cast<const uint4*>(in + first); // model_syms is a multiple of 128: aligned
+        for (uint32_t i = threadIdx.x; i < (len >> 2); i += blockDim.x) {
+            const uint4 q = __ldg(in4 + i);
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.x, fidelity));
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.y, fidelity));
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.z, fidelity));
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.w, fidelity));
+            local_max = max(local_max, max(max(q.x, q.y), max(q.z, q.w)));
+        }
+        if (threadIdx.x < (len & 3u)) {
+            const uint32_t v = in[first + (len & ~3u) + threadIdx.x];
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(v, fidelity));
+            local_max = max(local_max, v);
+        }
+        __syncthreads();
+        for (uint32_t b = threadIdx.x; b < nbins; b += blockDim.x)
+            bins[uint64_t(m) * nbins + b] = s_bins[b] + s_bins[stride + b] + s_bins[2 * stride + b] + s_bins[3 * stride + b];
+        __syncthreads();
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        local_max = max(local_max, __shfl_xor_sync(0xffffffffu, local_max, o));
+    if (lane_id() == 0 && local_max != 0)
+        atomicMax(max_value, local_max);
+}
+
+// exclusive prefix sum of a model's nfreqs into shared memory (nbins <= 2048); returns nothing, s_base[nbins] = M
+__device__ __forceinline__ void pa_prefix(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t* s_base, uint32_t* s_warp)
+{
+    // each thread owns 8 consecutive bins (256 threads x 8 = 2048)
+    const uint32_t b0 = threadIdx.x * 8u;
+    uint32_t v[8], sum = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        v[j] = b0 + j < nbins ? __ldg(nfreqs + b0 + j) : 0u;
+        sum += v[j];
+    }
+    uint32_t incl = sum;
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane_id() >= uint32_t(o))
+            incl += t;
+    }
+    if (lane_id() == 31)
+        s_warp[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    uint32_t carry = 0;
+    for (uint32_t w = 0; w < (threadIdx.x >> 5); w++)
+        carry += s_warp[w];
+    uint32_t run = carry + incl - sum;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        if (b0 + j <= nbins)
+            s_base[b0 + j] = run;
+        run += v[j];
+    }
+    if (threadIdx.x == blockDim.x - 1 && b0 + 8 <= nbins)
+        s_base[nbins] = run;
+    __syncthreads();
+}
+
+// smallest double >= 1/f (b200ans.cu reciprocal_up, same IEEE operations)
+__device__ __forceinline__ double pa_reciprocal_up(uint32_t f)
+{
+    double r = 1.0 / double(f);
+    if (fma(r, double(f), -1.0) < 0.0)
+        r = __longlong_as_double(__double_as_longlong(r) + 1);
+    return r;
+}
+
+// encoder tables of all models from their normalised frequencies (ans_fold.hpp:84-91): one CTA per model
+__global__ void __launch_bounds__(kPaThreads) pa_enc_tables_kernel(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t n_models,
+    EncEntry* __restrict__ tables)
+{
+    __shared__ uint32_t s_base[2048 + 8];
+    __shared__ uint32_t s_warp[kPaThreads / 32];
+    for (uint32_t m = blockIdx.x; m < n_models; m += gridDim.x) {
+        const uint32_t* nf = nfreqs + uint64_t(m) * nbins;
+        pa_prefix(nf, nbins, s_base, s_warp);
+        for (uint32_t b = threadIdx.x; b < nbins; b += blockDim.x) {
+            const uint32_t fr = __ldg(nf + b);
+            EncEntry e;
+            e.freq = fr;
+            e.base = s_base[b];
+            e.rcp = fr ? pa_reciprocal_up(fr) : 0.0;
+            tables[uint64_t(m) * nbins + b] = e;
+        }
+        __syncthreads();
+    }
+}
+
+// decoder slot tables of all models (ans_fold.hpp:179-207, ans_msb.hpp:179-204): one CTA per model, one thread per
+// slot, the slot's symbol by binary search over the prefix sums
+template <int METHOD>
+__global__ void __launch_bounds__(kPaThreads) pa_dec_tables_kernel(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t n_models,
+    uint32_t fidelity, const uint8_t* __restrict__ log2_frame, DecEntry* __restrict__ slots, uint64_t slot_stride)
+{
+    __shared__ uint32_t s_base[2048 + 8];
+    __shared__ uint32_t s_warp[kPaThreads / 32];
+    for (uint32_t m = blockIdx.x; m < n_models; m += gridDim.x) {
+        const uint32_t* nf = nfreqs + uint64_t(m) * nbins;
+        pa_prefix(nf, nbins, s_base, s_warp);
+        const uint32_t frame = 1u << log2_frame[m];
+        DecEntry* out = slots + uint64_t(m) * slot_stride;
+        for (uint32_t slot = threadIdx.x; slot < frame; slot += blockDim.x) {
+            // largest s with base[s] <= slot (symbols of frequency 0 share a base with their successor: take the last)
+            uint32_t lo = 0, hi = nbins; // base[lo] <= slot < base[hi] = M
+            while (hi - lo > 1u) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (s_base[mid] <= slot)
+                    lo = mid;
+                else
+                    hi = mid;
+            }
+            const uint32_t fr = s_base[lo + 1] - s_base[lo];
+            uint32_t k = 0, value;
+            if (METHOD == METHOD_MSB)
+                value = msb_unmap(lo, k);
+            else
+                value = fold_unmap(lo, fidelity, k);
+            out[slot] = DecEntry { uint16_t(fr), uint16_t(slot - s_base[lo]), value + (k << 30) };
+        }
+        __syncthreads();
+    }
+}
+
 
 } // namespace b200ans

@@ -163,6 +163,24 @@ int b200ans_block_stride(const b200ans_ctx* ctx, int method, size_t* stride);
 int b200ans_decode_blocks_device(b200ans_ctx* ctx, const uint8_t* d_payload, const uint64_t* d_offsets,
     const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst);
 
+/* ---- pseudo-adaptive mode (src/pseudo_adaptive.cpp:64-177) ------------------------------ */
+/* Every `model_syms` consecutive symbols (a multiple of 128 in [1024, 2^24]) are coded with their own semi-static
+ * model -- own histogram, own adjust_freqs, own prelude -- as the reference's driver does by calling T::encode block by
+ * block; nothing is shared between blocks, so shards need no collective. Methods: ANSfold-1, ANSfold-2, ANSmsb.
+ * Container: header (flags bit 0), u32 prelude bytes and u32 payload bytes per block, the preludes, the payloads;
+ * prelude(b) followed by payload(b) is byte for byte what ans_X_compress() writes for block b (ans_fold.hpp:238-281).
+ * The reference driver's dense-rank alphabet remap (pseudo_adaptive.cpp:83-105) is not applied: values are coded as
+ * they are (the folded coders do not need a dense alphabet). */
+size_t b200ans_pa_compress_bound(const b200ans_ctx* ctx, int method, uint32_t model_syms, size_t n);
+int b200ans_pa_compress(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t model_syms, uint8_t* dst,
+                        size_t dst_capacity, const uint32_t* src, size_t n, size_t* out_bytes);
+int b200ans_pa_decompress(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* dst, size_t n, const uint8_t* src,
+                          size_t src_bytes);
+int b200ans_pa_compress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t model_syms, uint8_t* d_dst,
+                               size_t dst_capacity, const uint32_t* d_src, size_t n, size_t* out_bytes);
+int b200ans_pa_decompress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* d_dst, size_t n,
+                                 const uint8_t* d_src, size_t src_bytes);
+
 /* ---- host-only model API (ans_util.hpp / interp.hpp); usable without a GPU ------------- */
 /* out: largest_sym + 1 entries */
 int b200ans_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_t largest_sym, int require_u16,
