@@ -93,6 +93,7 @@ struct b200ans_ctx {
 
     // grow-only device buffers
     DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs;
+    uint32_t pa_undecided = 0;    // models of the last pa_compress the device normaliser handed to the host
     uint8_t* pa_pinned = nullptr; // pseudo-adaptive mode: counts / frequencies of all models (pinned, grows on demand)
     size_t pa_pinned_cap = 0;
     // `small` layout: [0] u32 max, [1] u32 error flag, [2..] pad; totals (2 x u64) at byte 16
@@ -1748,50 +1749,86 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     }
     CU(c, cudaEventRecord(c->ev[4], c->stream));
     const size_t bins_bytes = size_t(nm) * nbins * 4;
-    RET(pa_pinned(c, bins_bytes + nm));
-    CU(c, cudaMemcpyAsync(c->pa_pinned, c->bins.p, bins_bytes, cudaMemcpyDeviceToHost, c->stream));
+    // device normalisation (pa_normalise_kernel): counts -> frequencies, log2 M and a status byte per model
+    CU(c, c->pa_nfreqs.reserve(bins_bytes + 2 * size_t(nm)));
+    uint8_t* d_lg = c->pa_nfreqs.as<uint8_t>() + bins_bytes;
+    uint8_t* d_status = d_lg + nm;
+    {
+        uint32_t n_keys = 1;
+        while (n_keys < nbins)
+            n_keys <<= 1;
+        const size_t smem = size_t(n_keys) * 8 + size_t(nbins) * 4;
+        const int grid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 16));
+        // B200ANS_PA_MARGIN (testing): a huge margin sends every model to the host's adjust_freqs
+        const char* mv = std::getenv("B200ANS_PA_MARGIN");
+        const double margin = mv && *mv ? std::atof(mv) : kPaMargin;
+        pa_normalise_kernel<<<grid, kPaNormThreads, smem, c->stream>>>(c->bins.as<uint32_t>(), nbins, nm, c->h_approx, margin,
+            c->pa_nfreqs.as<uint32_t>(), d_lg, d_status);
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    }
+    CU(c, cudaEventRecord(c->ev[5], c->stream));
+    RET(pa_pinned(c, bins_bytes + 2 * size_t(nm)));
+    CU(c, cudaMemcpyAsync(c->pa_pinned, c->pa_nfreqs.p, bins_bytes + 2 * size_t(nm), cudaMemcpyDeviceToHost, c->stream));
     RET(read_small(c));
     c->stats.ms_histogram = elapsed(c->ev[3], c->ev[4]);
+    const float ms_normalise = elapsed(c->ev[4], c->ev[5]);
     if (c->h_small()->max_value >= (1u << 30))
         return c->fail(B200ANS_E_DOMAIN, "folded coders need values < 2^30");
 
-    // host: normalise + prelude per model, all cores; the frequencies go back in place of the counts
+    // host: the models the device left undecided (decision margin below kPaMargin) go through adjust_freqs here;
+    // then the prelude of every model, on all cores
     const double t0 = now_ms();
-    uint32_t* counts = reinterpret_cast<uint32_t*>(c->pa_pinned);
+    uint32_t* rows = reinterpret_cast<uint32_t*>(c->pa_pinned);
     uint8_t* lg = c->pa_pinned + bins_bytes;
-    std::vector<std::vector<uint8_t>> preludes(nm);
-    std::atomic<int> bad { 0 };
-    const uint32_t h_approx = c->h_approx;
-    parallel_for(nm, [&](size_t m) {
-        uint32_t* row = counts + m * nbins;
-        std::vector<uint64_t> freqs(nbins);
+    const uint8_t* status = lg + nm;
+    uint32_t undecided = 0;
+    for (uint32_t m = 0; m < nm; m++) {
+        if (status[m] == 1)
+            return c->fail(B200ANS_E_DOMAIN, "pa_compress: normalisation produced an unusable frame size");
+        if (status[m] != 2)
+            continue;
+        undecided++;
+        std::vector<uint32_t> cnt(nbins);
+        CU(c, cudaMemcpy(cnt.data(), c->bins.as<uint32_t>() + size_t(m) * nbins, size_t(nbins) * 4, cudaMemcpyDeviceToHost));
+        std::vector<uint64_t> freqs(cnt.begin(), cnt.end());
         uint32_t max_sym = 0;
-        for (uint32_t b = 0; b < nbins; b++) {
-            freqs[b] = row[b];
-            if (row[b])
+        for (uint32_t b = 0; b < nbins; b++)
+            if (cnt[b])
                 max_sym = b;
-        }
         freqs.resize(size_t(max_sym) + 1);
-        std::vector<uint32_t> nf = adjust_freqs(freqs, max_sym, true, h_approx);
+        const std::vector<uint32_t> nf = adjust_freqs(freqs, max_sym, true, c->h_approx);
         uint64_t frame = 0;
         for (uint32_t v : nf)
             frame += v;
-        if (!is_power_of_two(frame) || frame > (uint64_t(1) << 20)) {
-            bad = 1;
-            return;
-        }
+        if (!is_power_of_two(frame) || frame > (uint64_t(1) << 20))
+            return c->fail(B200ANS_E_DOMAIN, "pa_compress: normalisation produced an unusable frame size");
+        uint32_t* row = rows + size_t(m) * nbins;
+        std::fill(row, row + nbins, 0u);
+        std::copy(nf.begin(), nf.end(), row);
         lg[m] = uint8_t(63 - __builtin_clzll(frame));
+        CU(c, cudaMemcpyAsync(c->pa_nfreqs.as<uint32_t>() + size_t(m) * nbins, row, size_t(nbins) * 4, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(d_lg + m, lg + m, 1, cudaMemcpyHostToDevice, c->stream));
+    }
+    c->pa_undecided = undecided;
+    std::vector<std::vector<uint8_t>> preludes(nm);
+    parallel_for(nm, [&](size_t m) {
+        const uint32_t* row = rows + m * nbins;
+        uint32_t max_sym = 0;
+        for (uint32_t b = 0; b < nbins; b++)
+            if (row[b])
+                max_sym = b;
+        std::vector<uint32_t> nf(row, row + max_sym + 1);
         std::vector<uint8_t>& pre = preludes[m];
         pre.assign(nf.size() * 8 + 64, 0);
         uint8_t* p = pre.data();
-        ans_serialize_interp(nf, size_t(frame), p);
+        ans_serialize_interp(nf, size_t(1) << lg[m], p);
         pre.resize(size_t(p - pre.data()));
-        std::fill(row, row + nbins, 0u);
-        std::copy(nf.begin(), nf.end(), row);
     });
-    if (bad)
-        return c->fail(B200ANS_E_DOMAIN, "pa_compress: normalisation produced an unusable frame size");
-    c->stats.ms_model = float(now_ms() - t0);
+    c->stats.ms_model = float(now_ms() - t0) + ms_normalise;
+    if (std::getenv("B200ANS_PA_TRACE"))
+        std::fprintf(stderr, "pa_compress: %u models, device normalise %.3f ms, host preludes %.3f ms, %u undecided\n", nm, ms_normalise,
+            now_ms() - t0, undecided);
 
     // front: header, size arrays, preludes
     size_t pre_region = 0;
@@ -1819,8 +1856,6 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     CU(c, cudaMemcpyAsync(d_dst, c->front.data(), payload_at, cudaMemcpyHostToDevice, c->stream));
 
     // device: frequencies -> encoder tables -> one stream per model block
-    CU(c, c->pa_nfreqs.reserve(bins_bytes + nm));
-    CU(c, cudaMemcpyAsync(c->pa_nfreqs.p, c->pa_pinned, bins_bytes + nm, cudaMemcpyHostToDevice, c->stream));
     CU(c, c->enc_table.reserve(size_t(nm) * nbins * sizeof(EncEntry)));
     c->have_enc = false; // the single-model encoder table is gone
     const int tgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
@@ -1844,7 +1879,7 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     a.stride = stride;
     a.block_bytes = c->block_bytes.as<uint32_t>();
     a.error_flag = c->d_err();
-    a.pa_log2 = c->pa_nfreqs.as<uint8_t>() + bins_bytes;
+    a.pa_log2 = d_lg;
     a.pa_table_stride = nbins;
     CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
     CU(c, cudaEventRecord(c->ev[0], c->stream));

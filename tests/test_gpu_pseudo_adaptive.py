@@ -90,3 +90,19 @@ def test_edges_and_errors(codec):
     with pytest.raises(P.B200AnsError):
         codec.pa_compress(M_FOLD, 1, 8192, np.array([1, 2, 1 << 30, 4] * 600, dtype=np.uint32))
     assert np.array_equal(codec.pa_decompress(M_MSB, 0, blob, data.size), data)
+
+
+def test_host_fallback_of_the_normaliser_gives_the_same_bytes(codec, monkeypatch):
+    """pa_normalise_kernel hands models with a decision margin below 1e-9 to the host's adjust_freqs; forcing
+    every model down that road must not change a byte"""
+    import ans_large_alphabet_b200 as P
+
+    data = _inputs.make("zipf20", 150_001, seed=3)
+    want = codec.pa_compress(M_FOLD, 1, 2048, data).copy()
+    monkeypatch.setenv("B200ANS_PA_MARGIN", "1e30")
+    other = P.Codec(device=0)
+    try:
+        got = other.pa_compress(M_FOLD, 1, 2048, data).copy()
+    finally:
+        other.close()
+    assert np.array_equal(got, want)
