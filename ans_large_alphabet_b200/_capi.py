@@ -292,6 +292,14 @@ class Codec:
         self._check(self.lib.b200ans_pa_decompress(self.h, method, f, out.ctypes.data, n, blob.ctypes.data, blob.size))
         return out
 
+    def pa_compress_ptr(self, method, f, model_syms, dst_ptr, cap, src_ptr, n):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_pa_compress(self.h, method, f, model_syms, dst_ptr, cap, src_ptr, n, C.byref(nb)))
+        return nb.value
+
+    def pa_decompress_ptr(self, method, f, dst_ptr, n, src_ptr, nbytes):
+        self._check(self.lib.b200ans_pa_decompress(self.h, method, f, dst_ptr, n, src_ptr, nbytes))
+
     def pa_compress_device(self, method, f, model_syms, d_dst, cap, d_src, n):
         nb = C.c_size_t()
         self._check(self.lib.b200ans_pa_compress_device(self.h, method, f, model_syms, d_dst, cap, d_src, n, C.byref(nb)))

@@ -45,7 +45,10 @@ WORKLOADS = {
     "fold2": (M_FOLD, 2, ("zipf", 1 << 20, 1.0, 0), 1 << 30, "ANSfold-2, 2^30-symbol Zipf(1.0, 2^20)"),
     "msb": (M_MSB, 0, ("zipf", 1 << 20, 1.0, 0), 1 << 30, "ANSmsb, 2^30-symbol Zipf(1.0, 2^20)"),
     "ans30": (M_INT, 0, ("geom", 0.01), 1 << 30, "ANS (ans_int), 2^30-symbol geometric(p=0.01)"),
+    "c4": (M_FOLD, 1, ("zipf", 1 << 20, 1.0, 0), 1 << 27, "C4 pseudo-adaptive ANSfold-1 (one model per 8192 symbols), 2^27-symbol Zipf(1.0, 2^20) per GPU"),
 }
+# pseudo-adaptive workloads: symbols per model (every block has its own histogram / model / prelude; no collective)
+PA_MODEL_SYMS = {"c4": 8192}
 DEFAULT_WORKLOAD = "c2"  # the single-GPU configuration BASELINE.json's metric is quoted on (configs[1])
 # Symbols per block (a container parameter).  8192 is the library default; the 1e8-symbol C2 input has only 12 207 such
 # blocks x 4 rANS chains = 48 828 independent chains for 148 SMs, so it runs with 4096 (twice the chains; the size
@@ -177,13 +180,15 @@ def cpu_codec():
     return oracle(), "port"
 
 
-def cpu_time_sample(method, f, sample, runs):
+def cpu_time_sample(method, f, sample, runs, block=0):
     codec, kind = cpu_codec()
-    enc_ns, dec_ns, nbytes = codec.time(method, f, sample, runs)
+    enc_ns, dec_ns, nbytes = codec.time(method, f, sample, runs, block)
     gbs = 8.0 * sample.size / (enc_ns + dec_ns)  # (4n + 4n) bytes / (t_enc + t_dec); bytes/ns == GB/s
     return {
         "value": gbs, "unit": UNIT, "cores": 1, "kind": kind,
-        "sample": f"first {sample.size} symbols of the workload, whole-stream {method_label(method, f)}, min of {runs} runs",
+        "sample": f"first {sample.size} symbols of the workload, "
+                  + (f"{method_label(method, f)} block by block ({block} symbols each)" if block else f"whole-stream {method_label(method, f)}")
+                  + f", min of {runs} runs",
         "encode_gbs": 4.0 * sample.size / enc_ns, "decode_gbs": 4.0 * sample.size / dec_ns,
         "encode_ns_per_symbol": enc_ns / sample.size, "decode_ns_per_symbol": dec_ns / sample.size,
         "bits_per_symbol": 8.0 * nbytes / sample.size, "host_cores_total": os.cpu_count(),
@@ -200,13 +205,14 @@ def run_reference_arm(args, wl):
     per_step = min(n, 20_000_000 if method != M_INT or gen[0] == "geom" else 5_000_000)
     sample = generate_host(gen, per_step, seed=0)
     codec, kind = cpu_codec()
+    block = PA_MODEL_SYMS.get(args.workload, 0)
     for _ in range(args.warmup):
-        codec.time(method, f, sample[: per_step // 8], 1)
+        codec.time(method, f, sample[: per_step // 8], 1, block)
     t0 = time.time()
     enc = dec = 0.0
     nbytes = 0
     for _ in range(args.steps):
-        e, d, nbytes = codec.time(method, f, sample, 1)
+        e, d, nbytes = codec.time(method, f, sample, 1, block)
         enc += e
         dec += d
     wall = time.time() - t0
@@ -306,7 +312,7 @@ def run_ours(args, wl):
     codec = P.Codec(device=local, block_syms=args.block_syms, stream=stream.cuda_stream)
     # weak scaling: every rank holds a full-size shard of the (N x larger) job
     d_in = generate_device(gen, n, dev, seed=rank)
-    bound = codec.bound(method, n)
+    bound = codec.pa_bound(method, PA_MODEL_SYMS[args.workload], n) if args.workload in PA_MODEL_SYMS else codec.bound(method, n)
     d_blob = torch.empty((bound + 15) // 16 * 16, dtype=torch.uint8, device=dev)
     d_out = torch.empty(n, dtype=torch.int32, device=dev)
     torch.cuda.synchronize(dev)
@@ -320,16 +326,27 @@ def run_ours(args, wl):
         torch.cuda.synchronize(dev)
 
     kern = {"histogram": 0.0, "encode": 0.0, "compact": 0.0, "decode": 0.0, "model_host": 0.0}
+    pa = PA_MODEL_SYMS.get(args.workload, 0)
+
+    def enc_dev():
+        if pa:  # per-block models: nothing is shared between ranks
+            return codec.pa_compress_device(method, f, pa, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
+        if world == 1:
+            return codec.compress_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
+        return sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
+
+    def dec_dev(nbytes):
+        if pa:
+            codec.pa_decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nbytes)
+        else:
+            codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nbytes)
 
     def device_step(acc):
         with torch.cuda.stream(stream):
-            if world == 1:
-                nb = codec.compress_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
-            else:
-                nb = sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
+            nb = enc_dev()
             s = codec.stats()
             enc_model = s.ms_model
-            codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nb)
+            dec_dev(nb)
             s2 = codec.stats()
         if acc is not None:
             acc["histogram"] += s.ms_histogram
@@ -376,12 +393,9 @@ def run_ours(args, wl):
         barrier()
         with torch.cuda.stream(stream):
             e0.record(stream)
-            if world == 1:
-                nb2 = codec.compress_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
-            else:
-                nb2 = sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
+            nb2 = enc_dev()
             e1.record(stream)
-            codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nb2)
+            dec_dev(nb2)
             e2.record(stream)
         stream.synchronize()
         enc_ms += e0.elapsed_time(e1)
@@ -397,6 +411,10 @@ def run_ours(args, wl):
     torch.cuda.synchronize(dev)
 
     def e2e_step():
+        if pa:
+            nbh = codec.pa_compress_ptr(method, f, pa, h_blob.data_ptr(), h_blob.numel(), h_in.data_ptr(), n)
+            codec.pa_decompress_ptr(method, f, h_out.data_ptr(), n, h_blob.data_ptr(), nbh)
+            return nbh
         if world == 1:
             nbh = codec.compress_ptr(method, f, h_blob.data_ptr(), h_blob.numel(), h_in.data_ptr(), n)
             codec.decompress_ptr(method, f, h_out.data_ptr(), n, h_blob.data_ptr(), nbh)
@@ -460,8 +478,8 @@ def run_ours(args, wl):
         if world == 1 and not args.no_cpu:
             ns = min(n, args.cpu_sample)
             sample = d_in[:ns].cpu().numpy().view(np.uint32)
-            cpu = cpu_time_sample(method, f, sample, runs=2)
-            sb = codec.compress(method, f, sample)
+            cpu = cpu_time_sample(method, f, sample, runs=2, block=pa)
+            sb = codec.pa_compress(method, f, pa, sample) if pa else codec.compress(method, f, sample)
             bps_sample = 8.0 * sb.size / ns
             cpu["ours_bits_per_symbol_same_sample"] = bps_sample
             cpu["size_overhead_vs_reference_pct"] = 100.0 * (bps_sample / cpu["bits_per_symbol"] - 1.0)
@@ -472,9 +490,10 @@ def run_ours(args, wl):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
             "config": {"workload": desc, "method": method_label(method, f), "symbols_per_gpu": n,
-                       "block_syms": args.block_syms, "n_blocks_per_gpu": n_blocks,
+                       "block_syms": pa or args.block_syms, "n_blocks_per_gpu": n_blocks,
                        "l2": "inputs (%.0f MB per GPU) larger than the 126 MB L2; no flush" % (4.0 * n / 1e6),
-                       "model": "semi-static, global histogram" + (" via NCCL all-reduce" if world > 1 else ""),
+                       "model": ("pseudo-adaptive: one model per block, normalised on the device, no collective" if pa else
+                                 "semi-static, global histogram" + (" via NCCL all-reduce" if world > 1 else "")),
                        "frame_size": frame, "model_symbols": nsyms},
             "encode_gbs": 4.0 * n * world / (enc_ms * 1e6), "decode_gbs": 4.0 * n * world / (dec_ms * 1e6),
             "encode_ms": enc_ms, "decode_ms": dec_ms,
@@ -484,7 +503,8 @@ def run_ours(args, wl):
             "cpu_baseline": cpu,
             "e2e": {"value": gb_step / (e2e_ms / e2e_steps / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
-                    "api": "b200ans_compress + b200ans_decompress (host buffers, pinned)" if world == 1
+                    "api": "b200ans_pa_compress + b200ans_pa_decompress (host buffers, pinned)" if pa
+                    else "b200ans_compress + b200ans_decompress (host buffers, pinned)" if world == 1
                     else "pinned H2D + staged device API + D2H per rank"},
             "gpu_launches": int(launches), "clocks": clocks,
         }

@@ -164,9 +164,25 @@ class _CpuCodec:
         assert h
         return _Model(self, h)
 
-    def time(self, method, f, data, runs=1):
+    def time(self, method, f, data, runs=1, block=0):
+        """(encode ns, decode ns, bytes); block > 0: every `block` symbols compressed on their own (pseudo_adaptive.cpp)"""
         data = np.ascontiguousarray(data, dtype=np.uint32)
         e, d, b = C.c_double(), C.c_double(), C.c_size_t()
+        if block:
+            if hasattr(self.lib, self.p + "time_blocks"):
+                fn = self._f("time_blocks")
+                fn.restype = C.c_int
+                fn.argtypes = [C.c_int, C.c_uint32, u32p, C.c_size_t, C.c_size_t, C.c_int,
+                               C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_size_t)]
+                rc = fn(method, f, ptr(data, u32p), data.size, block, runs, C.byref(e), C.byref(d), C.byref(b))
+                assert rc == 0, rc
+                return e.value, d.value, b.value
+            te = td = 0.0
+            tb = 0
+            for i in range(0, data.size, block):
+                ei, di, bi = self.time(method, f, data[i : i + block], runs)
+                te, td, tb = te + ei, td + di, tb + bi
+            return te, td, tb
         rc = self._f("time")(method, f, ptr(data, u32p), data.size, runs, C.byref(e), C.byref(d), C.byref(b))
         assert rc == 0, rc
         return e.value, d.value, b.value
