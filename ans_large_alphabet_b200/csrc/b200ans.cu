@@ -92,7 +92,7 @@ struct b200ans_ctx {
     cudaEvent_t ev[8] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre;
     uint32_t pa_undecided = 0;    // models of the last pa_compress the device normaliser handed to the host
     uint8_t* pa_pinned = nullptr; // pseudo-adaptive mode: counts / frequencies of all models (pinned, grows on demand)
     size_t pa_pinned_cap = 0;
@@ -105,9 +105,12 @@ struct b200ans_ctx {
     static constexpr size_t kPinnedBins = size_t(64) << 10;
     uint8_t* pinned = nullptr;
     struct SmallHost {
-        uint32_t max_value, error_flag, pad[2];
+        uint32_t max_value, error_flag, max_log2, pad;
         uint64_t totals[2];
+        uint64_t totals_b[2]; // a second scan in flight (pseudo-adaptive: preludes and payloads)
     };
+    uint32_t* d_max_log2() { return small.as<uint32_t>() + 2; }
+    uint64_t* d_totals_b() { return reinterpret_cast<uint64_t*>(small.as<uint8_t>() + 32); }
     SmallHost* h_small() { return reinterpret_cast<SmallHost*>(pinned + kPinnedBins); }
 
     // encoder model
@@ -264,7 +267,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_bits, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs })
+             &c->dec_slots, &c->dec_bits, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre })
         b->release();
     for (auto& e : c->ev)
         if (e)
@@ -1629,40 +1632,12 @@ extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32
 //            [u32 prelude bytes of model m][u32 payload bytes of model m][pad to 16]
 //            [preludes, each 16-byte aligned][payloads, each 16-byte aligned]
 // prelude(m) followed by payload(m) is exactly what the reference's ans_X_compress() writes for block m.
-// Device: K1 per block (pa_histogram_kernel) -> host: normalise + prelude for all blocks on all host cores ->
-// device: encoder tables from the frequencies (pa_enc_tables_kernel), one reference-format stream per block
-// (encode_kernel<.., PA>), size scan + compaction.  Decode mirrors it (pa_dec_tables_kernel, decode_kernel<.., PA>).
-#include <atomic>
-#include <thread>
-
+// Everything per block runs on the device: K1 (pa_histogram_kernel) -> adjust_freqs restated (pa_normalise_kernel; the
+// rare model whose accept/reject margin is within 1e-9 is redone by the host's adjust_freqs) -> prelude
+// (pa_prelude_encode_kernel) -> encoder tables (pa_enc_tables_kernel) -> one reference-format stream per block
+// (encode_kernel<.., PA>) -> size scans + compaction of preludes and payloads.  Decode mirrors it
+// (pa_prelude_decode_kernel, pa_dec_tables_kernel, decode_kernel<.., PA>).  The host only lays the container out.
 namespace {
-
-template <class F> void parallel_for(size_t n, F&& fn)
-{
-    const unsigned hw = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
-    const size_t threads = std::min<size_t>(hw, std::max<size_t>(1, n / 8));
-    if (threads <= 1) {
-        for (size_t i = 0; i < n; i++)
-            fn(i);
-        return;
-    }
-    std::atomic<size_t> next { 0 };
-    auto work = [&]() {
-        for (;;) {
-            const size_t i0 = next.fetch_add(16);
-            if (i0 >= n)
-                return;
-            for (size_t i = i0; i < std::min(n, i0 + 16); i++)
-                fn(i);
-        }
-    };
-    std::vector<std::thread> pool;
-    for (size_t t = 1; t < threads; t++)
-        pool.emplace_back(work);
-    work();
-    for (auto& t : pool)
-        t.join();
-}
 
 int pa_check(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms)
 {
@@ -1732,23 +1707,28 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
         return B200ANS_OK;
     }
     const uint32_t nbins = uint32_t(alphabet_bins(method, f, 0));
+    const size_t bins_bytes = size_t(nm) * nbins * 4;
+    const size_t sizes_at = B200ANS_HEADER_BYTES;
+    const size_t pre_at = align_up(sizes_at + size_t(nm) * 8, 16);
+    if (cap < pre_at)
+        return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
+    const int mgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
 
     // K1 per model block
     CU(c, cudaEventRecord(c->ev[3], c->stream));
-    CU(c, c->bins.reserve(size_t(nm) * nbins * 4));
-    CU(c, cudaMemsetAsync(c->d_max(), 0, 4, c->stream));
+    CU(c, c->bins.reserve(bins_bytes));
+    CU(c, cudaMemsetAsync(c->small.p, 0, 64, c->stream));
     {
-        const int grid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
         const size_t smem = size_t(4) * (nbins | 1u) * 4;
         if (method == METHOD_MSB)
-            pa_histogram_kernel<METHOD_MSB><<<grid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
+            pa_histogram_kernel<METHOD_MSB><<<mgrid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
         else
-            pa_histogram_kernel<METHOD_FOLD><<<grid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
+            pa_histogram_kernel<METHOD_FOLD><<<mgrid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
         c->stats.launches++;
         CU(c, cudaGetLastError());
     }
     CU(c, cudaEventRecord(c->ev[4], c->stream));
-    const size_t bins_bytes = size_t(nm) * nbins * 4;
+
     // device normalisation (pa_normalise_kernel): counts -> frequencies, log2 M and a status byte per model
     CU(c, c->pa_nfreqs.reserve(bins_bytes + 2 * size_t(nm)));
     uint8_t* d_lg = c->pa_nfreqs.as<uint8_t>() + bins_bytes;
@@ -1768,20 +1748,17 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
         CU(c, cudaGetLastError());
     }
     CU(c, cudaEventRecord(c->ev[5], c->stream));
-    RET(pa_pinned(c, bins_bytes + 2 * size_t(nm)));
-    CU(c, cudaMemcpyAsync(c->pa_pinned, c->pa_nfreqs.p, bins_bytes + 2 * size_t(nm), cudaMemcpyDeviceToHost, c->stream));
+    RET(pa_pinned(c, size_t(nm) + 64));
+    CU(c, cudaMemcpyAsync(c->pa_pinned, d_status, nm, cudaMemcpyDeviceToHost, c->stream));
     RET(read_small(c));
     c->stats.ms_histogram = elapsed(c->ev[3], c->ev[4]);
     const float ms_normalise = elapsed(c->ev[4], c->ev[5]);
     if (c->h_small()->max_value >= (1u << 30))
         return c->fail(B200ANS_E_DOMAIN, "folded coders need values < 2^30");
 
-    // host: the models the device left undecided (decision margin below kPaMargin) go through adjust_freqs here;
-    // then the prelude of every model, on all cores
+    // host: only the models the device left undecided (decision margin below kPaMargin) go through adjust_freqs here
     const double t0 = now_ms();
-    uint32_t* rows = reinterpret_cast<uint32_t*>(c->pa_pinned);
-    uint8_t* lg = c->pa_pinned + bins_bytes;
-    const uint8_t* status = lg + nm;
+    const uint8_t* status = c->pa_pinned;
     uint32_t undecided = 0;
     for (uint32_t m = 0; m < nm; m++) {
         if (status[m] == 1)
@@ -1790,7 +1767,8 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
             continue;
         undecided++;
         std::vector<uint32_t> cnt(nbins);
-        CU(c, cudaMemcpy(cnt.data(), c->bins.as<uint32_t>() + size_t(m) * nbins, size_t(nbins) * 4, cudaMemcpyDeviceToHost));
+        CU(c, cudaMemcpyAsync(cnt.data(), c->bins.as<uint32_t>() + size_t(m) * nbins, size_t(nbins) * 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
         std::vector<uint64_t> freqs(cnt.begin(), cnt.end());
         uint32_t max_sym = 0;
         for (uint32_t b = 0; b < nbins; b++)
@@ -1803,66 +1781,38 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
             frame += v;
         if (!is_power_of_two(frame) || frame > (uint64_t(1) << 20))
             return c->fail(B200ANS_E_DOMAIN, "pa_compress: normalisation produced an unusable frame size");
-        uint32_t* row = rows + size_t(m) * nbins;
-        std::fill(row, row + nbins, 0u);
-        std::copy(nf.begin(), nf.end(), row);
-        lg[m] = uint8_t(63 - __builtin_clzll(frame));
-        CU(c, cudaMemcpyAsync(c->pa_nfreqs.as<uint32_t>() + size_t(m) * nbins, row, size_t(nbins) * 4, cudaMemcpyHostToDevice, c->stream));
-        CU(c, cudaMemcpyAsync(d_lg + m, lg + m, 1, cudaMemcpyHostToDevice, c->stream));
+        std::fill(cnt.begin(), cnt.end(), 0u);
+        std::copy(nf.begin(), nf.end(), cnt.begin());
+        const uint8_t lgm = uint8_t(63 - __builtin_clzll(frame));
+        CU(c, cudaMemcpyAsync(c->pa_nfreqs.as<uint32_t>() + size_t(m) * nbins, cnt.data(), size_t(nbins) * 4, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaMemcpyAsync(d_lg + m, &lgm, 1, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
     }
     c->pa_undecided = undecided;
-    std::vector<std::vector<uint8_t>> preludes(nm);
-    parallel_for(nm, [&](size_t m) {
-        const uint32_t* row = rows + m * nbins;
-        uint32_t max_sym = 0;
-        for (uint32_t b = 0; b < nbins; b++)
-            if (row[b])
-                max_sym = b;
-        std::vector<uint32_t> nf(row, row + max_sym + 1);
-        std::vector<uint8_t>& pre = preludes[m];
-        pre.assign(nf.size() * 8 + 64, 0);
-        uint8_t* p = pre.data();
-        ans_serialize_interp(nf, size_t(1) << lg[m], p);
-        pre.resize(size_t(p - pre.data()));
-    });
-    c->stats.ms_model = float(now_ms() - t0) + ms_normalise;
-    if (std::getenv("B200ANS_PA_TRACE"))
-        std::fprintf(stderr, "pa_compress: %u models, device normalise %.3f ms, host preludes %.3f ms, %u undecided\n", nm, ms_normalise,
-            now_ms() - t0, undecided);
+    const float ms_host = float(now_ms() - t0);
 
-    // front: header, size arrays, preludes
-    size_t pre_region = 0;
-    for (const auto& p : preludes)
-        pre_region += align_up(p.size(), 16);
-    const size_t sizes_at = B200ANS_HEADER_BYTES;
-    const size_t pre_at = align_up(sizes_at + size_t(nm) * 8, 16);
-    const size_t payload_at = pre_at + pre_region;
-    if (cap < payload_at)
-        return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
-    if (pre_region > 0xFFFFFFF0ull)
-        return c->fail(B200ANS_E_ARG, "pa_compress: preludes exceed 4 GiB");
-    h.prelude_bytes = uint32_t(pre_region);
-    c->front.assign(payload_at, 0);
-    std::memcpy(c->front.data(), &h, sizeof h);
-    {
-        uint32_t* pre_sizes = reinterpret_cast<uint32_t*>(c->front.data() + sizes_at);
-        size_t at = pre_at;
-        for (uint32_t m = 0; m < nm; m++) {
-            pre_sizes[m] = uint32_t(preludes[m].size());
-            std::memcpy(c->front.data() + at, preludes[m].data(), preludes[m].size());
-            at += align_up(preludes[m].size(), 16);
-        }
-    }
-    CU(c, cudaMemcpyAsync(d_dst, c->front.data(), payload_at, cudaMemcpyHostToDevice, c->stream));
+    // preludes on the device (the counts are no longer needed: their buffer is the coder's scratch), then their
+    // sizes are scanned; the total comes back while the encoder runs
+    CU(c, cudaEventRecord(c->ev[6], c->stream));
+    const uint32_t pre_stride = uint32_t(align_up(size_t(nbins) * 4 + 64, 16));
+    CU(c, c->pa_pre.reserve(size_t(nm) * pre_stride + size_t(nm) * 12));
+    uint8_t* d_pre = c->pa_pre.as<uint8_t>();
+    uint64_t* d_pre_off = reinterpret_cast<uint64_t*>(d_pre + size_t(nm) * pre_stride);
+    uint32_t* d_pre_bytes = reinterpret_cast<uint32_t*>(d_pre_off + nm);
+    pa_prelude_encode_kernel<<<(nm + kPaPreThreads - 1) / kPaPreThreads, kPaPreThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm,
+        d_lg, c->bins.as<uint32_t>(), d_pre, pre_stride, d_pre_bytes);
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
+    c->stats.launches += 2;
+    CU(c, cudaGetLastError());
+    CU(c, cudaMemcpyAsync(c->h_small(), c->small.p, sizeof(b200ans_ctx::SmallHost), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaEventRecord(c->ev[7], c->stream));
 
-    // device: frequencies -> encoder tables -> one stream per model block
+    // frequencies -> encoder tables -> one reference-format stream per model block
     CU(c, c->enc_table.reserve(size_t(nm) * nbins * sizeof(EncEntry)));
     c->have_enc = false; // the single-model encoder table is gone
-    const int tgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
-    pa_enc_tables_kernel<<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, c->enc_table.as<EncEntry>());
+    pa_enc_tables_kernel<<<mgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, c->enc_table.as<EncEntry>());
     c->stats.launches++;
     CU(c, cudaGetLastError());
-
     const size_t stride = block_stride(method, model_syms);
     CU(c, c->scratch.reserve(stride * nm));
     CU(c, c->block_bytes.reserve(size_t(nm) * 4));
@@ -1881,7 +1831,6 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     a.error_flag = c->d_err();
     a.pa_log2 = d_lg;
     a.pa_table_stride = nbins;
-    CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
     CU(c, cudaEventRecord(c->ev[0], c->stream));
     {
         const size_t rows = size_t(kEncWarps) * 8 * kEncRowBytes;
@@ -1897,12 +1846,26 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
         CU(c, cudaGetLastError());
     }
     CU(c, cudaEventRecord(c->ev[1], c->stream));
+
+    // the prelude total is on the host by now (the encoder is still running): lay the container out
+    CU(c, cudaEventSynchronize(c->ev[7]));
+    const size_t pre_region = c->h_small()->totals_b[0];
+    const size_t payload_at = pre_at + pre_region;
+    if (pre_region > 0xFFFFFFF0ull)
+        return c->fail(B200ANS_E_ARG, "pa_compress: preludes exceed 4 GiB");
+    if (cap < payload_at)
+        return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
+    h.prelude_bytes = uint32_t(pre_region);
+    std::memcpy(c->pinned, &h, sizeof h); // pinned: the copy below is asynchronous
+    CU(c, cudaMemcpyAsync(d_dst, c->pinned, sizeof h, cudaMemcpyHostToDevice, c->stream));
+    const int cgrid = int(std::max<uint32_t>(1, std::min<uint32_t>((nm + 7) / 8, uint32_t(c->num_sms) * 8)));
+    compact_kernel<<<cgrid, 256, 0, c->stream>>>(d_pre, pre_stride, d_pre_bytes, d_pre_off, nm, d_dst + pre_at,
+        reinterpret_cast<uint32_t*>(d_dst + sizes_at), uint64_t(pre_region));
     scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(c->block_bytes.as<uint32_t>(), nm, c->offsets.as<uint64_t>(), c->d_totals(),
         reinterpret_cast<uint64_t*>(d_dst + offsetof(Header, payload_bytes)));
-    const int cgrid = int(std::max<uint32_t>(1, std::min<uint32_t>((nm + 7) / 8, uint32_t(c->num_sms) * 8)));
     compact_kernel<<<cgrid, 256, 0, c->stream>>>(c->scratch.as<uint8_t>(), stride, c->block_bytes.as<uint32_t>(), c->offsets.as<uint64_t>(),
         nm, d_dst + payload_at, reinterpret_cast<uint32_t*>(d_dst + sizes_at + size_t(nm) * 4), uint64_t(cap - payload_at));
-    c->stats.launches += 2;
+    c->stats.launches += 3;
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(c->ev[2], c->stream));
     RET(read_small(c));
@@ -1912,12 +1875,16 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     if (cap < total)
         return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
     *out_bytes = total;
+    c->stats.ms_model = ms_normalise + ms_host + elapsed(c->ev[6], c->ev[7]);
     c->stats.ms_encode = elapsed(c->ev[0], c->ev[1]);
     c->stats.ms_compact = elapsed(c->ev[1], c->ev[2]);
     c->stats.n_blocks = nm;
     c->stats.prelude_bytes = pre_region;
     c->stats.payload_bytes = c->h_small()->totals[1];
     c->stats.total_bytes = total;
+    if (std::getenv("B200ANS_PA_TRACE"))
+        std::fprintf(stderr, "pa_compress: %u models, normalise %.3f ms, host %.3f ms (%u undecided), preludes %.3f ms\n", nm, ms_normalise,
+            ms_host, undecided, elapsed(c->ev[6], c->ev[7]));
     return B200ANS_OK;
 }
 
@@ -1948,74 +1915,45 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
     if (nm != (n + h.block_syms - 1) / h.block_syms)
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: inconsistent block geometry");
     const uint32_t nbins = uint32_t(alphabet_bins(method, f, 0));
+    const size_t bins_bytes = size_t(nm) * nbins * 4;
     const size_t sizes_at = B200ANS_HEADER_BYTES;
     const size_t pre_at = align_up(sizes_at + size_t(nm) * 8, 16);
     const size_t payload_at = pre_at + h.prelude_bytes;
-    if (payload_at + h.payload_bytes > src_bytes)
+    if (payload_at + h.payload_bytes > src_bytes || payload_at < pre_at)
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: container truncated");
 
-    // host: prelude sizes + preludes -> frequencies of every model
-    const size_t bins_bytes = size_t(nm) * nbins * 4;
-    RET(pa_pinned(c, std::max(bins_bytes + nm, payload_at + 64)));
-    std::vector<uint8_t> front(payload_at + 16, 0);
-    CU(c, cudaMemcpyAsync(front.data(), d_src, payload_at, cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
-    const double t0 = now_ms();
-    const uint32_t* pre_sizes = reinterpret_cast<const uint32_t*>(front.data() + sizes_at);
-    std::vector<size_t> pre_off(nm);
-    {
-        size_t at = pre_at;
-        for (uint32_t m = 0; m < nm; m++) {
-            pre_off[m] = at;
-            if (pre_sizes[m] < 3 || pre_sizes[m] > payload_at - at)
-                return c->fail(B200ANS_E_FORMAT, "pa_decompress: prelude size table does not fit the container");
-            at += align_up(pre_sizes[m], 16);
-        }
-        if (at != payload_at)
-            return c->fail(B200ANS_E_FORMAT, "pa_decompress: prelude sizes do not add up");
-    }
-    uint32_t* rows = reinterpret_cast<uint32_t*>(c->pa_pinned);
-    uint8_t* lg = c->pa_pinned + bins_bytes;
-    std::atomic<int> bad { 0 };
-    parallel_for(nm, [&](size_t m) {
-        std::vector<uint8_t> buf(size_t(pre_sizes[m]) + 16, 0); // the interp reader may look one word past the end
-        std::memcpy(buf.data(), front.data() + pre_off[m], pre_sizes[m]);
-        const uint8_t* q = buf.data();
-        const uint32_t max_sym = vbyte_decode_u32(q);
-        if (size_t(max_sym) + 1 > nbins || *q > 20) {
-            bad = 1;
-            return;
-        }
-        size_t used = 0;
-        const std::vector<uint32_t> nf = ans_load_interp(buf.data(), &used);
-        uint64_t frame = 0;
-        for (uint32_t v : nf)
-            frame += v;
-        if (used > size_t(pre_sizes[m]) + 4 || nf.size() > nbins || !is_power_of_two(frame) || frame > (uint64_t(1) << 20)
-            || *std::max_element(nf.begin(), nf.end()) > 65535u) {
-            bad = 1;
-            return;
-        }
-        uint32_t* row = rows + m * nbins;
-        std::fill(row, row + nbins, 0u);
-        std::copy(nf.begin(), nf.end(), row);
-        lg[m] = uint8_t(63 - __builtin_clzll(frame));
-    });
-    if (bad)
+    // device: size scans, preludes -> frequencies (pa_prelude_decode_kernel), one synchronisation for the verdicts
+    CU(c, cudaEventRecord(c->ev[3], c->stream));
+    const uint32_t* d_pre_bytes = reinterpret_cast<const uint32_t*>(d_src + sizes_at);
+    const uint32_t* d_pay_bytes = d_pre_bytes + nm;
+    CU(c, c->pa_pre.reserve(size_t(nm) * 8));
+    CU(c, c->offsets.reserve(size_t(nm) * 8));
+    CU(c, c->bins.reserve(bins_bytes));
+    CU(c, c->pa_nfreqs.reserve(bins_bytes + 2 * size_t(nm)));
+    uint8_t* d_lg = c->pa_nfreqs.as<uint8_t>() + bins_bytes;
+    uint64_t* d_pre_off = c->pa_pre.as<uint64_t>();
+    CU(c, cudaMemsetAsync(c->small.p, 0, 64, c->stream));
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_pay_bytes, nm, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
+    pa_prelude_decode_kernel<<<(nm + kPaPreThreads - 1) / kPaPreThreads, kPaPreThreads, 0, c->stream>>>(d_src + pre_at, d_pre_off, d_pre_bytes,
+        uint64_t(h.prelude_bytes), nbins, nm, c->bins.as<uint32_t>(), c->pa_nfreqs.as<uint32_t>(), d_lg, c->d_err(), c->d_max_log2());
+    c->stats.launches += 3;
+    CU(c, cudaGetLastError());
+    CU(c, cudaEventRecord(c->ev[4], c->stream));
+    RET(read_small(c));
+    if (c->h_small()->totals_b[0] != h.prelude_bytes)
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: prelude size table does not add up");
+    if (c->h_small()->totals[0] != h.payload_bytes)
+        return c->fail(B200ANS_E_FORMAT, "pa_decompress: block size table does not add up");
+    if (c->h_small()->error_flag)
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: a block's prelude is not a valid model");
-    uint32_t max_lg = 0;
-    for (uint32_t m = 0; m < nm; m++)
-        max_lg = std::max<uint32_t>(max_lg, lg[m]);
-    const uint64_t slot_stride = uint64_t(1) << max_lg;
+    const uint64_t slot_stride = uint64_t(1) << c->h_small()->max_log2;
     if (slot_stride * nm * sizeof(DecEntry) > (uint64_t(48) << 30))
         return c->fail(B200ANS_E_ARG, "pa_decompress: slot tables of all models exceed 48 GiB; decode in pieces");
-    c->stats.ms_model = float(now_ms() - t0);
+    c->stats.ms_model = elapsed(c->ev[3], c->ev[4]);
 
-    CU(c, c->pa_nfreqs.reserve(bins_bytes + nm));
-    CU(c, cudaMemcpyAsync(c->pa_nfreqs.p, c->pa_pinned, bins_bytes + nm, cudaMemcpyHostToDevice, c->stream));
     CU(c, c->dec_slots.reserve(slot_stride * nm * sizeof(DecEntry)));
     c->have_dec = false;
-    const uint8_t* d_lg = c->pa_nfreqs.as<uint8_t>() + bins_bytes;
     const int tgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
     if (method == METHOD_MSB)
         pa_dec_tables_kernel<METHOD_MSB><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
@@ -2024,19 +1962,10 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
     c->stats.launches++;
     CU(c, cudaGetLastError());
 
-    CU(c, c->offsets.reserve(size_t(nm) * 8));
-    const uint32_t* d_sizes = reinterpret_cast<const uint32_t*>(d_src + sizes_at + size_t(nm) * 4);
-    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, nm, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
-    c->stats.launches++;
-    CU(c, cudaGetLastError());
-    RET(read_small(c));
-    if (c->h_small()->totals[0] != h.payload_bytes)
-        return c->fail(B200ANS_E_FORMAT, "pa_decompress: block size table does not add up");
-
     DecArgs a {};
     a.payload = d_src + payload_at;
     a.offsets = c->offsets.as<uint64_t>();
-    a.block_bytes = d_sizes;
+    a.block_bytes = d_pay_bytes;
     a.out = d_dst;
     a.n = n;
     a.block_syms = h.block_syms;

@@ -1140,4 +1140,245 @@ __global__ void __launch_bounds__(kPaNormThreads) pa_normalise_kernel(const uint
 }
 
 
+// ------------------------------------------------------------------------------------------
+// Preludes on the device (pseudo-adaptive mode): one thread per model writes / reads the reference-format prelude
+//   vbyte(max_sym) . u8(log2 M) . binary interpolative code of the prefix sums of (nfreq + 1)
+// (ans_util.hpp:25-63, interp.hpp:28-118, bits.hpp:146-218; same bits as host/prelude.hpp).  The recursion of the
+// interpolative code is data-independent in shape, so it runs on an explicit stack of at most 12 frames.
+// ------------------------------------------------------------------------------------------
+struct PaBitWriter {
+    uint8_t* out;
+    uint64_t acc = 0;
+    uint32_t fill = 0;
+    __device__ __forceinline__ void spill()
+    {
+        const uint32_t w = uint32_t(acc);
+        out[0] = uint8_t(w), out[1] = uint8_t(w >> 8), out[2] = uint8_t(w >> 16), out[3] = uint8_t(w >> 24);
+        out += 4;
+        acc >>= 32;
+        fill -= 32;
+    }
+    __device__ __forceinline__ void put(uint32_t value, uint32_t width)
+    {
+        if (width == 0)
+            return;
+        acc |= uint64_t(value & (0xFFFFFFFFu >> (32u - width))) << fill;
+        fill += width;
+        if (fill >= 32)
+            spill();
+    }
+    __device__ __forceinline__ void finish()
+    {
+        if (fill != 0) {
+            fill = 32;
+            spill();
+        }
+    }
+};
+
+struct PaBitReader {
+    const uint8_t* in;
+    uint32_t pos = 0;   // byte position of the next word
+    uint32_t limit = 0; // bytes that exist (reads beyond return zero)
+    uint64_t acc = 0;
+    uint32_t fill = 0;
+    __device__ __forceinline__ uint32_t byte(uint32_t i) const { return i < limit ? in[i] : 0u; }
+    __device__ __forceinline__ uint32_t get(uint32_t width)
+    {
+        if (width == 0)
+            return 0;
+        if (fill < width) {
+            const uint32_t w = byte(pos) | (byte(pos + 1) << 8) | (byte(pos + 2) << 16) | (byte(pos + 3) << 24);
+            pos += 4;
+            acc |= uint64_t(w) << fill;
+            fill += 32;
+        }
+        const uint32_t v = uint32_t(acc) & (0xFFFFFFFFu >> (32u - width));
+        acc >>= width;
+        fill -= width;
+        return v;
+    }
+};
+
+// centred minimal binary code for val in [1, u], u < 2^31 (host/prelude.hpp put_centered / get_centered)
+__device__ __forceinline__ void pa_put_centered(PaBitWriter& w, uint32_t val, uint32_t u)
+{
+    if (u == 1)
+        return;
+    const uint32_t b = 32u - __clz(u - 1u);
+    const uint32_t span = 1u << b;
+    const uint32_t longs = 2u * u - span;
+    val += u - (longs >> 1);
+    if (val > u)
+        val -= u;
+    const uint32_t shorts = span - u;
+    if (val <= shorts) {
+        w.put(val - 1u, b - 1u);
+    } else {
+        val += shorts;
+        w.put((val - 1u) >> 1, b - 1u);
+        w.put((val - 1u) & 1u, 1u);
+    }
+}
+
+__device__ __forceinline__ uint32_t pa_get_centered(PaBitReader& r, uint32_t u)
+{
+    if (u == 1)
+        return 1;
+    const uint32_t b = 32u - __clz(u - 1u);
+    const uint32_t span = 1u << b;
+    const uint32_t longs = 2u * u - span;
+    const uint32_t shorts = span - u;
+    uint32_t val = r.get(b - 1u) + 1u;
+    if (val > shorts)
+        val = 2u * val + r.get(1u) - shorts - 1u;
+    val += longs >> 1;
+    if (val > u)
+        val -= u;
+    return val;
+}
+
+constexpr int kPaPreThreads = 64;
+
+// nfreqs[model][nbins], log2_frame[model]  ->  prelude bytes at pre + model * pre_stride, pre_bytes[model].
+// `climb` is scratch of the same shape as nfreqs (the prefix sums the code is built on).
+__global__ void __launch_bounds__(kPaPreThreads) pa_prelude_encode_kernel(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t n_models,
+    const uint8_t* __restrict__ log2_frame, uint32_t* __restrict__ climb, uint8_t* __restrict__ pre, uint32_t pre_stride,
+    uint32_t* __restrict__ pre_bytes)
+{
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n_models)
+        return;
+    const uint32_t* nf = nfreqs + uint64_t(m) * nbins;
+    uint32_t* v = climb + uint64_t(m) * nbins;
+    uint32_t max_sym = 0, run = 0;
+    for (uint32_t s = 0; s < nbins; s++) {
+        const uint32_t f = nf[s];
+        run += f + (s ? 1u : 0u);
+        v[s] = run;
+        if (f)
+            max_sym = s;
+    }
+    const uint32_t n = max_sym + 1u;
+    const uint32_t frame = 1u << log2_frame[m];
+    uint8_t* out = pre + uint64_t(m) * pre_stride;
+    uint8_t* p = out;
+    for (uint32_t x = max_sym;; x >>= 7) { // vbyte (vbyte.hpp:57-75)
+        if (x >= 0x80u) {
+            *p++ = uint8_t(x | 0x80u);
+        } else {
+            *p++ = uint8_t(x);
+            break;
+        }
+    }
+    *p++ = log2_frame[m];
+    PaBitWriter w;
+    w.out = p;
+    // interp_put(v, n, low = 1, high = u + 1), u = frame + n + 1
+    uint32_t st_off[12], st_n[12], st_low[12], st_high[12];
+    int sp = 0;
+    uint32_t off = 0, cnt = n, low = 1u, high = frame + n + 2u;
+    for (;;) {
+        if (cnt == 0) {
+            if (sp == 0)
+                break;
+            sp--;
+            off = st_off[sp], cnt = st_n[sp], low = st_low[sp], high = st_high[sp];
+            continue;
+        }
+        const uint32_t h = (cnt + 1u) >> 1, left = h - 1u, right = cnt - h;
+        const uint32_t mid = v[off + h - 1u] + 1u;
+        pa_put_centered(w, mid - low - left + 1u, high - right - low - left + 1u);
+        // right half later, left half now
+        st_off[sp] = off + h, st_n[sp] = right, st_low[sp] = mid + 1u, st_high[sp] = high;
+        sp++;
+        cnt = left;
+        high = mid - 1u;
+    }
+    w.finish();
+    const uint32_t bytes = uint32_t(w.out - out);
+    pre_bytes[m] = bytes;
+    for (uint32_t z = bytes; z < ((bytes + 15u) & ~15u); z++) // the compaction copies whole 16-byte chunks: keep them deterministic
+        out[z] = 0;
+}
+
+// prelude bytes of model m at src + offsets[m] (pre_bytes[m] of them)  ->  nfreqs[model][nbins], log2_frame[model];
+// anything that is not a valid model of at most nbins symbols sets *error (and leaves a harmless one-symbol model).
+__global__ void __launch_bounds__(kPaPreThreads) pa_prelude_decode_kernel(const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets,
+    const uint32_t* __restrict__ pre_bytes, uint64_t region_bytes, uint32_t nbins, uint32_t n_models, uint32_t* __restrict__ climb,
+    uint32_t* __restrict__ nfreqs, uint8_t* __restrict__ log2_frame, uint32_t* __restrict__ error, uint32_t* __restrict__ max_log2)
+{
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= n_models)
+        return;
+    PaBitReader r;
+    const bool inside = offsets[m] + pre_bytes[m] <= region_bytes; // the size table is untrusted
+    r.in = src + (inside ? offsets[m] : 0);
+    r.limit = inside ? pre_bytes[m] : 0u;
+    uint32_t* v = climb + uint64_t(m) * nbins;
+    uint32_t* nf = nfreqs + uint64_t(m) * nbins;
+    uint32_t max_sym = 0, pos = 0;
+    for (uint32_t shift = 0; shift < 35u; shift += 7) {
+        const uint32_t c = r.byte(pos++);
+        max_sym += (c & 0x7Fu) << shift;
+        if (c < 0x80u)
+            break;
+    }
+    const uint32_t lg = r.byte(pos++);
+    bool bad = max_sym >= nbins || lg > 20u || pos > r.limit;
+    const uint32_t n = bad ? 1u : max_sym + 1u;
+    const uint32_t frame = 1u << (bad ? 0u : lg);
+    r.pos = pos;
+    uint32_t st_off[12], st_n[12], st_low[12], st_high[12];
+    int sp = 0;
+    uint32_t off = 0, cnt = n, low = 1u, high = frame + n + 2u;
+    for (;;) {
+        if (cnt == 0) {
+            if (sp == 0)
+                break;
+            sp--;
+            off = st_off[sp], cnt = st_n[sp], low = st_low[sp], high = st_high[sp];
+            continue;
+        }
+        const uint32_t h = (cnt + 1u) >> 1, left = h - 1u, right = cnt - h;
+        const uint32_t u = high - right - low - left + 1u;
+        if (u == 0u || u > (1u << 23)) { // not a sequence this coder wrote
+            bad = true;
+            break;
+        }
+        const uint32_t mid = low + left - 1u + pa_get_centered(r, u);
+        v[off + h - 1u] = mid - 1u;
+        st_off[sp] = off + h, st_n[sp] = right, st_low[sp] = mid + 1u, st_high[sp] = high;
+        sp++;
+        cnt = left;
+        high = mid - 1u;
+    }
+    if (r.pos > ((r.limit + 3u) & ~3u) + 4u)
+        bad = true;
+    uint64_t sum = 0;
+    uint32_t below = 0;
+    for (uint32_t s = 0; s < nbins; s++) {
+        uint32_t f = 0;
+        if (!bad && s < n) {
+            const uint32_t here = v[s];
+            f = s ? here - below - 1u : here;
+            below = here;
+            if (f > 65535u)
+                bad = true;
+        }
+        nf[s] = f;
+        sum += f;
+    }
+    if (bad || sum != frame) {
+        atomicExch(error, 1u);
+        for (uint32_t s = 0; s < nbins; s++)
+            nf[s] = s == 0 ? 1u : 0u;
+        log2_frame[m] = 0;
+    } else {
+        log2_frame[m] = uint8_t(lg);
+        atomicMax(max_log2, lg);
+    }
+}
+
+
 } // namespace b200ans
