@@ -92,7 +92,7 @@ struct b200ans_ctx {
     cudaEvent_t ev[8] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre, pa_keys;
     uint32_t pa_undecided = 0;    // models of the last pa_compress the device normaliser handed to the host
     uint8_t* pa_pinned = nullptr; // pseudo-adaptive mode: counts / frequencies of all models (pinned, grows on demand)
     size_t pa_pinned_cap = 0;
@@ -267,7 +267,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_bits, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre })
+             &c->dec_slots, &c->dec_bits, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys })
         b->release();
     for (auto& e : c->ev)
         if (e)
@@ -1632,7 +1632,7 @@ extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32
 //            [u32 prelude bytes of model m][u32 payload bytes of model m][pad to 16]
 //            [preludes, each 16-byte aligned][payloads, each 16-byte aligned]
 // prelude(m) followed by payload(m) is exactly what the reference's ans_X_compress() writes for block m.
-// Everything per block runs on the device: K1 (pa_histogram_kernel) -> adjust_freqs restated (pa_normalise_kernel; the
+// Everything per block runs on the device: K1 (pa_histogram_kernel) -> adjust_freqs restated (pa_sort_kernel + pa_fit_kernel; the
 // rare model whose accept/reject margin is within 1e-9 is redone by the host's adjust_freqs) -> prelude
 // (pa_prelude_encode_kernel) -> encoder tables (pa_enc_tables_kernel) -> one reference-format stream per block
 // (encode_kernel<.., PA>) -> size scans + compaction of preludes and payloads.  Decode mirrors it
@@ -1729,7 +1729,7 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     }
     CU(c, cudaEventRecord(c->ev[4], c->stream));
 
-    // device normalisation (pa_normalise_kernel): counts -> frequencies, log2 M and a status byte per model
+    // device normalisation (pa_sort_kernel + pa_fit_kernel): counts -> frequencies, log2 M and a status byte per model
     CU(c, c->pa_nfreqs.reserve(bins_bytes + 2 * size_t(nm)));
     uint8_t* d_lg = c->pa_nfreqs.as<uint8_t>() + bins_bytes;
     uint8_t* d_status = d_lg + nm;
@@ -1737,14 +1737,21 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
         uint32_t n_keys = 1;
         while (n_keys < nbins)
             n_keys <<= 1;
-        const size_t smem = size_t(n_keys) * 8 + size_t(nbins) * 4;
+        const size_t smem = size_t(n_keys) * 8;
         const int grid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 16));
         // B200ANS_PA_MARGIN (testing): a huge margin sends every model to the host's adjust_freqs
         const char* mv = std::getenv("B200ANS_PA_MARGIN");
         const double margin = mv && *mv ? std::atof(mv) : kPaMargin;
-        pa_normalise_kernel<<<grid, kPaNormThreads, smem, c->stream>>>(c->bins.as<uint32_t>(), nbins, nm, c->h_approx, margin,
-            c->pa_nfreqs.as<uint32_t>(), d_lg, d_status);
-        c->stats.launches++;
+        const size_t keys_bytes = size_t(nm) * n_keys * 8;
+        CU(c, c->pa_keys.reserve(keys_bytes + size_t(nm) * sizeof(PaMeta)));
+        uint64_t* d_keys = c->pa_keys.as<uint64_t>();
+        PaMeta* d_meta = reinterpret_cast<PaMeta*>(c->pa_keys.as<uint8_t>() + keys_bytes);
+        pa_sort_kernel<<<grid, kPaNormThreads, smem, c->stream>>>(c->bins.as<uint32_t>(), nbins, nm, c->h_approx, d_keys, d_meta,
+            c->pa_nfreqs.as<uint32_t>());
+        const uint32_t fit_threads = nm * 8u;
+        pa_fit_kernel<<<(fit_threads + kPaFitThreads - 1) / kPaFitThreads, kPaFitThreads, 0, c->stream>>>(d_keys, n_keys, d_meta, nbins, nm,
+            margin, c->pa_nfreqs.as<uint32_t>(), d_lg, d_status);
+        c->stats.launches += 2;
         CU(c, cudaGetLastError());
     }
     CU(c, cudaEventRecord(c->ev[5], c->stream));

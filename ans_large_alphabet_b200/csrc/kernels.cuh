@@ -949,40 +949,55 @@ __global__ void __launch_bounds__(kPaThreads) pa_dec_tables_kernel(const uint32_
 }
 
 
-// Device restatement of adjust_freqs (ans_util.hpp:100-157) for the per-block models: one CTA per model.
-//   1. symbols sorted by (count, symbol) ascending -- bitonic sort of 64-bit keys in shared memory;
-//   2. thread j < 8 fits frame M0 << (8r + j): the reference's serial chain ratio = M / rest (IEEE divide),
-//      share = (uint32)fma(ratio, count, 0.5), M -= share, rest -= count -- the same IEEE operations in the same
-//      order as the host code, so shares, the "fit failed" flag and the largest share are bit-identical -- and
-//      accumulates the cross entropy of its fit on the way;
-//   3. thread 0 walks the eight results in the reference's order (skip failed fits; stop at the 16-bit guard with
-//      the last good fit; stop when XH < H * (1 + H_approx / 1000); else remember the fit as last good);
-//   4. the chosen frame is fitted once more, this time storing the shares.
+// Device restatement of adjust_freqs (ans_util.hpp:100-157) for the per-block models, in two kernels.
+//   pa_sort_kernel, one CTA per model: symbols sorted by (count, symbol) ascending -- bitonic sort of 64-bit keys in
+//      shared memory -- written to global memory with the model's entropy limit H * (1 + H_approx / 1000).
+//   pa_fit_kernel, one thread per (model, frame): thread j of a model's 8-lane group fits frame M0 << (8r + j) with
+//      the reference's serial chain ratio = M / rest (IEEE divide), share = (uint32)fma(ratio, count, 0.5),
+//      M -= share, rest -= count -- the same IEEE operations in the same order as the host code, so shares, the
+//      "fit failed" flag and the largest share are bit-identical -- and accumulates the cross entropy of its fit on
+//      the way.  The group then walks its eight results in the reference's order (skip failed fits; stop at the
+//      16-bit guard with the last good fit; stop when XH < limit; else remember the fit as last good) and the
+//      chosen frame is fitted once more, this time storing the shares.  All models are in flight at once, which is
+//      what hides the latency of the serial chains.
 // Entropy and cross entropy are sums of p * log2(q): the device's log2 and summation order differ from glibc's in
-// the last bits, so a model whose decision margin |XH - limit| is below kPaMargin (a million times the worst-case
-// difference) is not decided here: status 2 sends it to the host's adjust_freqs.  Everything else is exact.
+// the last bits, so a model whose decision margin |XH - limit| is below kPaMargin (a thousand times the worst-case
+// difference and more) is not decided here: status 2 sends it to the host's adjust_freqs.  Everything else is exact.
 constexpr int kPaNormThreads = 64;
+constexpr int kPaFitThreads = 128;
 constexpr double kPaMargin = 1e-9;
 
-__device__ __forceinline__ void pa_fit(const uint64_t* keys, uint32_t first, uint32_t n_keys, int64_t M, uint64_t rest, double m_inv_unused,
-    double total, bool store, uint32_t* shares, bool& failed, uint32_t& top, double& xh)
+struct PaMeta {
+    double limit;       // H * (1 + H_approx / 1000)
+    double inv_total;   // 1 / symbols in the block (cross entropy only; the fits divide exactly)
+    uint64_t total;     // symbols in the block
+    uint32_t first;     // index of the first non-zero key
+    uint32_t frame0_lg; // log2 of the first frame tried: sigma rounded up to a power of two
+    uint32_t sigma;
+    uint32_t pad;
+};
+
+// STORE: write the shares to `shares` (the winning fit); otherwise accumulate the cross entropy
+template <bool STORE>
+__device__ __forceinline__ void pa_fit(const uint64_t* __restrict__ keys, uint32_t first, uint32_t n_keys, uint32_t lgM, uint64_t rest,
+    double inv_total, uint32_t* __restrict__ shares, bool& failed, uint32_t& top, double& xh)
 {
-    (void)m_inv_unused;
-    const double m = double(M);
+    int64_t M = int64_t(1) << lgM;
+    const double lgm = double(lgM);
     double acc = 0.0;
     uint32_t mx = 0;
     for (uint32_t r = first; r < n_keys; r++) {
-        const uint64_t key = keys[r];
+        const uint64_t key = __ldg(keys + r);
         const uint32_t sym = uint32_t(key) & 0xFFFFu;
         const uint64_t cnt = key >> 16;
         const double ratio = double(M) / double(rest);
         uint32_t share = uint32_t(fma(ratio, double(cnt), 0.5));
         if (share == 0)
             share = 1;
-        if (store)
+        if (STORE)
             shares[sym] = share;
         else
-            acc = fma(double(cnt) / total, log2(double(share) / m), acc);
+            acc = fma(double(cnt) * inv_total, log2(double(share)) - lgm, acc);
         mx = max(mx, share);
         M -= int64_t(share);
         rest -= cnt;
@@ -994,24 +1009,21 @@ __device__ __forceinline__ void pa_fit(const uint64_t* keys, uint32_t first, uin
     xh = -acc;
 }
 
-// status: 0 = decided here, 1 = unusable (the reference would return an empty model), 2 = undecided (host decides)
-__global__ void __launch_bounds__(kPaNormThreads) pa_normalise_kernel(const uint32_t* __restrict__ counts, uint32_t nbins, uint32_t n_models,
-    uint32_t h_approx, double margin, uint32_t* __restrict__ nfreqs, uint8_t* __restrict__ log2_frame, uint8_t* __restrict__ status)
+__global__ void __launch_bounds__(kPaNormThreads) pa_sort_kernel(const uint32_t* __restrict__ counts, uint32_t nbins, uint32_t n_models,
+    uint32_t h_approx, uint64_t* __restrict__ gkeys, PaMeta* __restrict__ meta, uint32_t* __restrict__ nfreqs)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     uint32_t n_keys = 1;
     while (n_keys < nbins)
         n_keys <<= 1;
     uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);
-    uint32_t* shares = reinterpret_cast<uint32_t*>(keys + n_keys);
     __shared__ double s_h[kPaNormThreads];
     __shared__ uint32_t s_cnt[kPaNormThreads];
     __shared__ uint64_t s_sum[kPaNormThreads];
-    __shared__ int s_choice[2]; // chosen frame exponent (relative to M0), or -1; status
 
     for (uint32_t model = blockIdx.x; model < n_models; model += gridDim.x) {
         const uint32_t* row = counts + uint64_t(model) * nbins;
-        // keys + sigma + total
+        uint32_t* out = nfreqs + uint64_t(model) * nbins;
         uint32_t sigma = 0;
         uint64_t total = 0;
         for (uint32_t b = threadIdx.x; b < n_keys; b += blockDim.x) {
@@ -1019,6 +1031,8 @@ __global__ void __launch_bounds__(kPaNormThreads) pa_normalise_kernel(const uint
             keys[b] = (uint64_t(cnt) << 16) | (cnt ? b : 0u);
             sigma += cnt != 0u;
             total += cnt;
+            if (b < nbins)
+                out[b] = 0; // the winning fit only writes the symbols that occur
         }
         s_cnt[threadIdx.x] = sigma;
         s_sum[threadIdx.x] = total;
@@ -1047,95 +1061,96 @@ __global__ void __launch_bounds__(kPaNormThreads) pa_normalise_kernel(const uint
         __syncthreads();
         const uint32_t first = n_keys - sigma;
         const double totald = double(total);
-        // entropy: fixed-shape reduction
-        {
-            double acc = 0.0;
-            for (uint32_t r = first + threadIdx.x; r < n_keys; r += blockDim.x) {
-                const double p = double(keys[r] >> 16) / totald;
+        uint64_t* gk = gkeys + uint64_t(model) * n_keys;
+        double acc = 0.0; // entropy: fixed-shape reduction
+        for (uint32_t r = threadIdx.x; r < n_keys; r += blockDim.x) {
+            const uint64_t key = keys[r];
+            gk[r] = key;
+            if (r >= first) {
+                const double p = double(key >> 16) / totald;
                 acc = fma(p, log2(p), acc);
             }
-            s_h[threadIdx.x] = acc;
         }
+        s_h[threadIdx.x] = acc;
         __syncthreads();
-        double H = 0.0;
-        for (int t = 0; t < kPaNormThreads; t++)
-            H += s_h[t];
-        H = -H;
-        const double limit = H * (1.0 + double(h_approx) / 1000.0);
-        uint64_t frame0 = sigma;
-        if (sigma & (sigma - 1u)) {
-            frame0 = 1;
-            while (frame0 <= sigma)
-                frame0 <<= 1; // next_power_of_two: 2^(floor(log2 sigma) + 1)
-        }
         if (threadIdx.x == 0) {
-            s_choice[0] = -1;
-            s_choice[1] = sigma == 0 ? 1 : -1;
-        }
-        __syncthreads();
-        int last_good = -1;
-        for (int round = 0; round < 4 && s_choice[1] < 0; round++) {
-            bool failed = true;
-            uint32_t top = 0;
-            double xh = 0.0;
-            if (threadIdx.x < 8)
-                pa_fit(keys, first, n_keys, int64_t(frame0 << (8 * round + threadIdx.x)), total, 0.0, totald, false, nullptr, failed, top, xh);
-            // gather to thread 0 through shared memory
-            __syncthreads();
-            if (threadIdx.x < 8) {
-                s_h[threadIdx.x] = xh;
-                s_cnt[threadIdx.x] = failed ? 0xFFFFFFFFu : top;
-            }
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                for (int j = 0; j < 8 && s_choice[1] < 0; j++) {
-                    if (s_cnt[j] == 0xFFFFFFFFu)
-                        continue;
-                    if (s_cnt[j] >= 65535u) { // the 16-bit guard: back to the last good fit (possibly none)
-                        s_choice[0] = last_good;
-                        s_choice[1] = last_good < 0 ? 1 : 0;
-                        break;
-                    }
-                    const double d = s_h[j] - limit;
-                    if (fabs(d) <= margin) {
-                        s_choice[1] = 2;
-                        break;
-                    }
-                    if (d < 0.0) {
-                        s_choice[0] = 8 * round + j;
-                        s_choice[1] = 0;
-                        break;
-                    }
-                    last_good = 8 * round + j;
-                }
-            }
-            __syncthreads();
-        }
-        const int st = s_choice[1] < 0 ? 2 : s_choice[1]; // no decision in 32 doublings: let the host look at it
-        uint32_t* out = nfreqs + uint64_t(model) * nbins;
-        if (st == 0) {
-            for (uint32_t b = threadIdx.x; b < nbins; b += blockDim.x)
-                shares[b] = 0;
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                bool failed;
-                uint32_t top;
-                double xh;
-                pa_fit(keys, first, n_keys, int64_t(frame0 << s_choice[0]), total, 0.0, totald, true, shares, failed, top, xh);
-            }
-            __syncthreads();
-            for (uint32_t b = threadIdx.x; b < nbins; b += blockDim.x)
-                out[b] = shares[b];
-        }
-        if (threadIdx.x == 0) {
-            status[model] = uint8_t(st);
-            uint64_t fr = st == 0 ? (frame0 << s_choice[0]) : 1;
-            uint32_t lg = 0;
-            while ((uint64_t(1) << lg) < fr)
+            double H = 0.0;
+            for (int t = 0; t < kPaNormThreads; t++)
+                H += s_h[t];
+            H = -H;
+            uint32_t lg = 0; // sigma if it is a power of two, else next_power_of_two: 2^(floor(log2 sigma) + 1)
+            while ((1u << lg) < sigma)
                 lg++;
-            log2_frame[model] = uint8_t(lg);
+            PaMeta mt;
+            mt.limit = H * (1.0 + double(h_approx) / 1000.0);
+            mt.inv_total = 1.0 / totald;
+            mt.total = total;
+            mt.first = first;
+            mt.frame0_lg = lg;
+            mt.sigma = sigma;
+            mt.pad = 0;
+            meta[model] = mt;
         }
         __syncthreads();
+    }
+}
+
+// status: 0 = decided here, 1 = unusable (the reference would return an empty model), 2 = undecided (host decides)
+__global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* __restrict__ gkeys, uint32_t n_keys, const PaMeta* __restrict__ meta,
+    uint32_t nbins, uint32_t n_models, double margin, uint32_t* __restrict__ nfreqs, uint8_t* __restrict__ log2_frame,
+    uint8_t* __restrict__ status)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t j = t & 7u;
+    const bool live = (t >> 3) < n_models;
+    const uint32_t model = live ? (t >> 3) : n_models - 1u; // spare lanes shadow the last model: shuffles stay full-warp
+    const PaMeta mt = meta[model];
+    const uint64_t* keys = gkeys + uint64_t(model) * n_keys;
+    int st = mt.sigma == 0 ? 1 : -1, choice = -1, last_good = -1;
+    for (int round = 0; round < 4; round++) {
+        if (!__any_sync(0xffffffffu, st < 0))
+            break;
+        bool failed = true;
+        uint32_t top = 0;
+        double xh = 0.0;
+        if (st < 0)
+            pa_fit<false>(keys, mt.first, n_keys, mt.frame0_lg + 8u * round + j, mt.total, mt.inv_total, nullptr, failed, top, xh);
+        const uint32_t code = failed ? 0xFFFFFFFFu : top;
+#pragma unroll
+        for (int jj = 0; jj < 8; jj++) { // every lane of the group walks the eight results in the reference's order
+            const uint32_t cj = __shfl_sync(0xffffffffu, code, jj, 8);
+            const double xj = __shfl_sync(0xffffffffu, xh, jj, 8);
+            if (st >= 0 || cj == 0xFFFFFFFFu)
+                continue;
+            if (cj >= 65535u) { // the 16-bit guard: back to the last good fit (possibly none)
+                choice = last_good;
+                st = last_good < 0 ? 1 : 0;
+                continue;
+            }
+            const double d = xj - mt.limit;
+            if (fabs(d) <= margin) {
+                st = 2;
+            } else if (d < 0.0) {
+                choice = 8 * round + jj;
+                st = 0;
+            } else {
+                last_good = 8 * round + jj;
+            }
+        }
+    }
+    if (st < 0)
+        st = 2; // no decision in 32 doublings: let the host look at it
+    if (live && j == 0u) {
+        uint32_t lg = 0;
+        if (st == 0) {
+            lg = mt.frame0_lg + uint32_t(choice);
+            bool failed;
+            uint32_t top;
+            double xh;
+            pa_fit<true>(keys, mt.first, n_keys, lg, mt.total, mt.inv_total, nfreqs + uint64_t(model) * nbins, failed, top, xh);
+        }
+        status[model] = uint8_t(st);
+        log2_frame[model] = uint8_t(lg);
     }
 }
 

@@ -93,7 +93,7 @@ def test_edges_and_errors(codec):
 
 
 def test_host_fallback_of_the_normaliser_gives_the_same_bytes(codec, monkeypatch):
-    """pa_normalise_kernel hands models with a decision margin below 1e-9 to the host's adjust_freqs; forcing
+    """pa_fit_kernel hands models with a decision margin below 1e-9 to the host's adjust_freqs; forcing
     every model down that road must not change a byte"""
     import ans_large_alphabet_b200 as P
 
