@@ -5,16 +5,21 @@ tag=${1:-r01c}
 out=gpurun_out/$tag; mkdir -p $out
 K='histogram_kernel|lpb3_encode_kernel|compact_kernel|lpb3_decode_kernel'
 timeout 600 python bench.py > $out/bench_c2.json 2> $out/bench_c2.err; echo "bench c2 exit $?"
-for wl in fold1 fold2 ans30; do
+for wl in fold1 fold2 ans30 c4; do
   timeout 600 python bench.py --workload $wl --no-targets > $out/bench_$wl.json 2> $out/bench_$wl.err; echo "bench $wl exit $?"
 done
 timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > $out/bench_ref_c2.json 2> $out/bench_ref_c2.err; echo "bench ref exit $?"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/bench_c2_launches.csv \
   python bench.py --steps 2 --warmup 1 --no-targets > $out/ncu_launches.log 2>&1; echo "launch list exit $?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/bench_c4_launches.csv \
+  python bench.py --workload c4 --steps 2 --warmup 1 --no-targets --no-cpu > $out/ncu_launches_c4.log 2>&1; echo "launch list c4 exit $?"
+python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 2>&1; echo "smoke exit $?"; tail -4 $out/smoke.log
 for wl in fold1 ans30; do
   timeout 1500 ncu --set full --clock-control none --import-source on -k regex:"$K" -s 12 -c 4 -o $out/full_$wl \
     python tools/kbench.py --workloads $wl --paths 0 --reps 1 > $out/ncu_full_$wl.log 2>&1; echo "ncu full $wl exit $?"
 done
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"$K" -s 12 -c 4 -o $out/full_c2 \
   python tools/kbench.py --workloads c2 --paths 0 --reps 1 --block-syms 4096 > $out/ncu_full_c2.log 2>&1; echo "ncu full c2 exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:^(pa_.*|encode_kernel|decode_kernel)$' -s 9 -c 9 -o $out/full_c4 \
+  python tools/pabench.py --model-syms 8192 --reps 1 > $out/ncu_full_c4.log 2>&1; echo "ncu full c4 exit $?"
 ls -la $out

@@ -77,7 +77,7 @@ for (kid, name) in kernels:
         n = int(r[col["Instructions Executed"]] or 0)
         ops[op] += n
         tot += n
-        w = int(r[col["L1 Wavefronts Shared"]] or 0)
+        w = int(r[col["L1 Wavefronts Shared"]] or 0) if "L1 Wavefronts Shared" in col else 0  # absent: no smem access
         if w:
             wave[op] += w
             wave[op + " (ideal)"] += int(r[col["L1 Wavefronts Shared Ideal"]] or 0)
