@@ -18,6 +18,7 @@
 #include "kernels.cuh"
 #include "lpb_kernels.cuh"
 #include "lpb3_kernels.cuh"
+#include "pa_kernels.cuh"
 
 using namespace b200ans;
 
@@ -105,11 +106,12 @@ struct b200ans_ctx {
     static constexpr size_t kPinnedBins = size_t(64) << 10;
     uint8_t* pinned = nullptr;
     struct SmallHost {
-        uint32_t max_value, error_flag, max_log2, pad;
+        uint32_t max_value, error_flag, max_log2, max_symbol;
         uint64_t totals[2];
         uint64_t totals_b[2]; // a second scan in flight (pseudo-adaptive: preludes and payloads)
     };
     uint32_t* d_max_log2() { return small.as<uint32_t>() + 2; }
+    uint32_t* d_max_symbol() { return small.as<uint32_t>() + 3; }
     uint64_t* d_totals_b() { return reinterpret_cast<uint64_t*>(small.as<uint8_t>() + 32); }
     SmallHost* h_small() { return reinterpret_cast<SmallHost*>(pinned + kPinnedBins); }
 
@@ -1648,6 +1650,33 @@ int pa_check(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms)
     return B200ANS_OK;
 }
 
+// Launch shape of the shared-memory-table coders (pa_kernels.cuh): one CTA per SM, as many warps (8 models each) as
+// fit next to `fixed` bytes, spread in balanced waves: tasks / (SMs * waves) warps per CTA, rounded up.
+struct PaLaunch {
+    uint32_t max_warps, warps, grid;
+    size_t smem;
+};
+
+PaLaunch pa_launch_shape(const b200ans_ctx* c, size_t fixed, size_t warp_bytes, uint32_t n_tasks)
+{
+    PaLaunch p {};
+    const size_t room = c->max_smem > fixed + 1024 ? c->max_smem - fixed - 1024 : 0;
+    p.max_warps = uint32_t(std::min<size_t>(size_t(kPaCodeMaxWarps), room / warp_bytes));
+    const int cap = env_int("B200ANS_PA_WARPS", 0);
+    if (cap > 0)
+        p.max_warps = std::min<uint32_t>(p.max_warps, uint32_t(cap));
+    if (p.max_warps == 0)
+        return p;
+    const uint32_t sms = uint32_t(c->num_sms);
+    const uint32_t waves = (n_tasks + sms * p.max_warps - 1) / (sms * p.max_warps);
+    p.warps = std::max<uint32_t>(1, std::min<uint32_t>(p.max_warps, (n_tasks + sms * waves - 1) / (sms * waves)));
+    if (n_tasks >= 2u * sms)
+        p.warps = std::max<uint32_t>(p.warps, std::min<uint32_t>(p.max_warps, 2u));
+    p.grid = std::max<uint32_t>(1, std::min<uint32_t>(sms, (n_tasks + p.warps - 1) / p.warps));
+    p.smem = fixed + size_t(p.warps) * warp_bytes;
+    return p;
+}
+
 // pinned staging that grows on demand
 int pa_pinned(b200ans_ctx* c, size_t bytes)
 {
@@ -1750,7 +1779,7 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
             c->pa_nfreqs.as<uint32_t>());
         const uint32_t fit_threads = nm * 8u;
         pa_fit_kernel<<<(fit_threads + kPaFitThreads - 1) / kPaFitThreads, kPaFitThreads, 0, c->stream>>>(d_keys, n_keys, d_meta, nbins, nm,
-            margin, c->pa_nfreqs.as<uint32_t>(), d_lg, d_status);
+            margin, c->pa_nfreqs.as<uint32_t>(), d_lg, d_status, c->d_max_log2());
         c->stats.launches += 2;
         CU(c, cudaGetLastError());
     }
@@ -1767,6 +1796,7 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     const double t0 = now_ms();
     const uint8_t* status = c->pa_pinned;
     uint32_t undecided = 0;
+    uint32_t max_lg = c->h_small()->max_log2;
     for (uint32_t m = 0; m < nm; m++) {
         if (status[m] == 1)
             return c->fail(B200ANS_E_DOMAIN, "pa_compress: normalisation produced an unusable frame size");
@@ -1791,6 +1821,7 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
         std::fill(cnt.begin(), cnt.end(), 0u);
         std::copy(nf.begin(), nf.end(), cnt.begin());
         const uint8_t lgm = uint8_t(63 - __builtin_clzll(frame));
+        max_lg = std::max<uint32_t>(max_lg, lgm);
         CU(c, cudaMemcpyAsync(c->pa_nfreqs.as<uint32_t>() + size_t(m) * nbins, cnt.data(), size_t(nbins) * 4, cudaMemcpyHostToDevice, c->stream));
         CU(c, cudaMemcpyAsync(d_lg + m, &lgm, 1, cudaMemcpyHostToDevice, c->stream));
         CU(c, cudaStreamSynchronize(c->stream));
@@ -1814,22 +1845,19 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     CU(c, cudaMemcpyAsync(c->h_small(), c->small.p, sizeof(b200ans_ctx::SmallHost), cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaEventRecord(c->ev[7], c->stream));
 
-    // frequencies -> encoder tables -> one reference-format stream per model block
-    CU(c, c->enc_table.reserve(size_t(nm) * nbins * sizeof(EncEntry)));
-    c->have_enc = false; // the single-model encoder table is gone
-    pa_enc_tables_kernel<<<mgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, c->enc_table.as<EncEntry>());
-    c->stats.launches++;
-    CU(c, cudaGetLastError());
+    // frequencies -> one reference-format stream per model block.  Tables: built per block in shared memory by the
+    // coder itself (pa_kernels.cuh) when every frame is at most 2^16, else one 16-byte entry per symbol and model in
+    // global memory (pa_enc_tables_kernel + encode_kernel<.., PA>, the first generation; B200ANS_PATH_GROUP forces it)
     const size_t stride = block_stride(method, model_syms);
     CU(c, c->scratch.reserve(stride * nm));
     CU(c, c->block_bytes.reserve(size_t(nm) * 4));
     CU(c, c->offsets.reserve(size_t(nm) * 8));
+    c->have_enc = false; // the single-model encoder table is gone
     EncArgs a {};
     a.in = d_src;
     a.n = n;
     a.block_syms = model_syms;
     a.n_blocks = nm;
-    a.table = c->enc_table.as<EncEntry>();
     a.n_entries = nbins;
     a.fidelity = f;
     a.scratch = c->scratch.as<uint8_t>();
@@ -1838,10 +1866,32 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     a.error_flag = c->d_err();
     a.pa_log2 = d_lg;
     a.pa_table_stride = nbins;
-    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    a.pa_nfreqs = c->pa_nfreqs.as<uint32_t>();
+    a.pa_nbins = nbins;
     {
+        uint32_t kk;
+        const uint32_t top_sym = method == METHOD_MSB ? msb_map(c->h_small()->max_value, kk) : fold_map(c->h_small()->max_value, f, kk);
+        a.pa_syms = std::min<uint32_t>(nbins, (top_sym + 1u + 15u) & ~15u);
+    }
+    const uint32_t n_tasks = (nm + 7) / 8;
+    PaLaunch pl = pa_launch_shape(c, size_t(kPaRcpN) * 8, size_t(8) * pa_enc_group_bytes(a.pa_syms), n_tasks);
+    const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && max_lg <= 16u && pl.warps >= 2u;
+    if (!smem_tables) {
+        CU(c, c->enc_table.reserve(size_t(nm) * nbins * sizeof(EncEntry)));
+        a.table = c->enc_table.as<EncEntry>();
+        pa_enc_tables_kernel<<<mgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, c->enc_table.as<EncEntry>());
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    }
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    if (smem_tables) {
+        auto k = method == METHOD_MSB ? pa_smem_encode_kernel<METHOD_MSB> : pa_smem_encode_kernel<METHOD_FOLD>;
+        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
+        k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    } else {
         const size_t rows = size_t(kEncWarps) * 8 * kEncRowBytes;
-        const uint32_t n_tasks = (nm + 7) / 8;
         if (method == METHOD_MSB) {
             auto k = encode_kernel<METHOD_MSB, false, true>;
             k<<<persistent_grid(c, k, kEncWarps * 32, rows, n_tasks, kEncWarps), kEncWarps * 32, rows, c->stream>>>(a);
@@ -1943,7 +1993,7 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
     scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
     scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_pay_bytes, nm, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
     pa_prelude_decode_kernel<<<(nm + kPaPreThreads - 1) / kPaPreThreads, kPaPreThreads, 0, c->stream>>>(d_src + pre_at, d_pre_off, d_pre_bytes,
-        uint64_t(h.prelude_bytes), nbins, nm, c->bins.as<uint32_t>(), c->pa_nfreqs.as<uint32_t>(), d_lg, c->d_err(), c->d_max_log2());
+        uint64_t(h.prelude_bytes), nbins, nm, c->bins.as<uint32_t>(), c->pa_nfreqs.as<uint32_t>(), d_lg, c->d_err(), c->d_max_log2(), c->d_max_symbol());
     c->stats.launches += 3;
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(c->ev[4], c->stream));
@@ -1954,20 +2004,8 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: block size table does not add up");
     if (c->h_small()->error_flag)
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: a block's prelude is not a valid model");
-    const uint64_t slot_stride = uint64_t(1) << c->h_small()->max_log2;
-    if (slot_stride * nm * sizeof(DecEntry) > (uint64_t(48) << 30))
-        return c->fail(B200ANS_E_ARG, "pa_decompress: slot tables of all models exceed 48 GiB; decode in pieces");
     c->stats.ms_model = elapsed(c->ev[3], c->ev[4]);
-
-    CU(c, c->dec_slots.reserve(slot_stride * nm * sizeof(DecEntry)));
     c->have_dec = false;
-    const int tgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
-    if (method == METHOD_MSB)
-        pa_dec_tables_kernel<METHOD_MSB><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
-    else
-        pa_dec_tables_kernel<METHOD_FOLD><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
-    c->stats.launches++;
-    CU(c, cudaGetLastError());
 
     DecArgs a {};
     a.payload = d_src + payload_at;
@@ -1978,13 +2016,47 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
     a.block_syms = h.block_syms;
     a.n_blocks = nm;
     a.fidelity = f;
-    a.slots = c->dec_slots.as<DecEntry>();
     a.pa_log2 = d_lg;
-    a.pa_slot_stride = slot_stride;
-    CU(c, cudaEventRecord(c->ev[0], c->stream));
-    {
+    a.pa_nfreqs = c->pa_nfreqs.as<uint32_t>();
+    a.pa_nbins = nbins;
+    const uint32_t n_tasks = (nm + 7) / 8;
+    // Tables: prefix sums + bucket index per block in shared memory, built by the decoder (pa_kernels.cuh), when every
+    // frame is at most 2^16; else M-entry slot tables in global memory (pa_dec_tables_kernel + decode_kernel<.., PA>).
+    // Bucket index: the finest (2^10 .. 2^8 entries) that still lets one round of tasks be resident.
+    a.pa_syms = std::min<uint32_t>(nbins, (c->h_small()->max_symbol + 1u + 15u) & ~15u);
+    PaLaunch pl {};
+    const int blog_env = env_int("B200ANS_PA_BLOG", 0);
+    const uint32_t want_warps = std::min<uint32_t>(uint32_t(kPaCodeMaxWarps), (n_tasks + uint32_t(c->num_sms) - 1) / uint32_t(c->num_sms));
+    for (uint32_t blog = blog_env ? uint32_t(blog_env) : 10u; blog >= 8u; blog--) {
+        pl = pa_launch_shape(c, 0, size_t(8) * pa_dec_group_bytes(a.pa_syms, blog), n_tasks);
+        a.pa_bucket_log2 = blog;
+        if (pl.max_warps >= want_warps || blog_env)
+            break;
+    }
+    const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && c->h_small()->max_log2 <= 16u && pl.warps >= 2u;
+    if (smem_tables) {
+        CU(c, cudaEventRecord(c->ev[0], c->stream));
+        auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
+        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
+        k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    } else {
+        const uint64_t slot_stride = uint64_t(1) << c->h_small()->max_log2;
+        if (slot_stride * nm * sizeof(DecEntry) > (uint64_t(48) << 30))
+            return c->fail(B200ANS_E_ARG, "pa_decompress: slot tables of all models exceed 48 GiB; decode in pieces");
+        CU(c, c->dec_slots.reserve(slot_stride * nm * sizeof(DecEntry)));
+        const int tgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
+        if (method == METHOD_MSB)
+            pa_dec_tables_kernel<METHOD_MSB><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
+        else
+            pa_dec_tables_kernel<METHOD_FOLD><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+        a.slots = c->dec_slots.as<DecEntry>();
+        a.pa_slot_stride = slot_stride;
+        CU(c, cudaEventRecord(c->ev[0], c->stream));
         const size_t smem = size_t(kDecWarps) * 8 * kDecRowBytes;
-        const uint32_t n_tasks = (nm + 7) / 8;
         if (method == METHOD_MSB) {
             auto k = decode_kernel<METHOD_MSB, DEC_FOLD_GLOBAL, true>;
             k<<<persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps), kDecWarps * 32, smem, c->stream>>>(a);

@@ -77,6 +77,10 @@ struct EncArgs {
     // pseudo-adaptive mode: block b has its own model -- table + b * pa_table_stride, log2 M = pa_log2[b]
     const uint8_t* pa_log2;
     uint64_t pa_table_stride; // entries
+    // pa_kernels.cuh (tables built in shared memory): normalised frequencies of model b at pa_nfreqs + b * pa_nbins
+    const uint32_t* pa_nfreqs;
+    uint32_t pa_nbins;
+    uint32_t pa_syms;         // table entries per model: beyond the largest symbol of the input, multiple of 16
 };
 
 struct DecArgs {
@@ -98,6 +102,11 @@ struct DecArgs {
     // pseudo-adaptive mode: block b decodes with slots + b * pa_slot_stride and log2 M = pa_log2[b]
     const uint8_t* pa_log2;
     uint64_t pa_slot_stride; // entries
+    // pa_kernels.cuh (no slot tables): normalised frequencies of model b at pa_nfreqs + b * pa_nbins
+    const uint32_t* pa_nfreqs;
+    uint32_t pa_nbins;
+    uint32_t pa_syms;         // table entries per model: beyond the largest symbol of every model, multiple of 16
+    uint32_t pa_bucket_log2;  // the bucket index has 2^pa_bucket_log2 entries per model
 };
 
 enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3 };
@@ -1098,7 +1107,7 @@ __global__ void __launch_bounds__(kPaNormThreads) pa_sort_kernel(const uint32_t*
 // status: 0 = decided here, 1 = unusable (the reference would return an empty model), 2 = undecided (host decides)
 __global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* __restrict__ gkeys, uint32_t n_keys, const PaMeta* __restrict__ meta,
     uint32_t nbins, uint32_t n_models, double margin, uint32_t* __restrict__ nfreqs, uint8_t* __restrict__ log2_frame,
-    uint8_t* __restrict__ status)
+    uint8_t* __restrict__ status, uint32_t* __restrict__ max_log2)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t j = t & 7u;
@@ -1151,6 +1160,7 @@ __global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* _
         }
         status[model] = uint8_t(st);
         log2_frame[model] = uint8_t(lg);
+        atomicMax(max_log2, lg); // the coder picks its table layout by the largest frame
     }
 }
 
@@ -1321,7 +1331,8 @@ __global__ void __launch_bounds__(kPaPreThreads) pa_prelude_encode_kernel(const 
 // anything that is not a valid model of at most nbins symbols sets *error (and leaves a harmless one-symbol model).
 __global__ void __launch_bounds__(kPaPreThreads) pa_prelude_decode_kernel(const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets,
     const uint32_t* __restrict__ pre_bytes, uint64_t region_bytes, uint32_t nbins, uint32_t n_models, uint32_t* __restrict__ climb,
-    uint32_t* __restrict__ nfreqs, uint8_t* __restrict__ log2_frame, uint32_t* __restrict__ error, uint32_t* __restrict__ max_log2)
+    uint32_t* __restrict__ nfreqs, uint8_t* __restrict__ log2_frame, uint32_t* __restrict__ error, uint32_t* __restrict__ max_log2,
+    uint32_t* __restrict__ max_symbol)
 {
     const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= n_models)
@@ -1392,6 +1403,7 @@ __global__ void __launch_bounds__(kPaPreThreads) pa_prelude_decode_kernel(const 
     } else {
         log2_frame[m] = uint8_t(lg);
         atomicMax(max_log2, lg);
+        atomicMax(max_symbol, max_sym); // the decoder sizes its per-model tables by the largest symbol
     }
 }
 

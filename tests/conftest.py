@@ -59,9 +59,18 @@ def host():
 
 
 @pytest.fixture(scope="session")
-def codec():
+def _session_codec():
     import ans_large_alphabet_b200 as P
 
     c = P.Codec(device=0)
     yield c
     c.close()
+
+
+@pytest.fixture
+def codec(_session_codec):
+    """one context per session; every test starts from the default kernel path and block size"""
+    _session_codec.set_kernel_path(0)
+    _session_codec.set_block_syms(8192)
+    yield _session_codec
+    _session_codec.set_kernel_path(0)

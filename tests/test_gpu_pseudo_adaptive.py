@@ -38,7 +38,9 @@ def split(blob, n, model_syms):
 
 @pytest.mark.parametrize("method,f", [(M_FOLD, 1), (M_FOLD, 2), (M_MSB, 0)])
 @pytest.mark.parametrize("model_syms,n", [(1024, 20_000), (8192, 100_003), (65536, 300_001), (8192, 8192 * 3)])
-def test_blocks_equal_reference(codec, method, f, model_syms, n):
+@pytest.mark.parametrize("path", [0, 1])  # 0: tables built in shared memory (pa_kernels.cuh); 1: tables in global memory
+def test_blocks_equal_reference(codec, method, f, model_syms, n, path):
+    codec.set_kernel_path(path)
     data = _inputs.make("zipf20", n, seed=7)
     blob = codec.pa_compress(method, f, model_syms, data).copy()
     blocks = split(blob, n, model_syms)
@@ -56,6 +58,46 @@ def test_blocks_equal_reference(codec, method, f, model_syms, n):
         total += want.size
     assert np.array_equal(codec.pa_decompress(method, f, blob, n), data)
     assert blob.size >= total and blob.size <= total + 64 + len(blocks) * (8 + 30) + 16
+
+
+@pytest.mark.parametrize("method,f", [(M_FOLD, 1), (M_FOLD, 2), (M_MSB, 0)])
+def test_skewed_and_wide_blocks_both_table_layouts(codec, method, f):
+    """blocks with one dominant symbol (frequencies beyond the per-CTA reciprocal table), blocks that use the whole
+    value range (every alphabet bin in play) and near-uniform blocks (large frames): both kernel generations must
+    write the same bytes, and sampled blocks must equal the reference's"""
+    rng = np.random.default_rng(11)
+    S = 4096
+    parts = []
+    for b in range(48):
+        kind = b % 4
+        if kind == 0:  # 97 % one value
+            x = rng.integers(0, 1 << 12, size=S, dtype=np.uint32)
+            x[rng.random(S) < 0.97] = 5
+        elif kind == 1:  # whole range below 2^30
+            x = (2.0 ** rng.uniform(0, 30, size=S)).astype(np.uint32)
+            x[0] = (1 << 30) - 1
+        elif kind == 2:  # uniform over 2^9 values
+            x = rng.integers(0, 1 << 9, size=S, dtype=np.uint32)
+        else:
+            x = _inputs.make("zipf20", S, seed=100 + b)
+        parts.append(x.astype(np.uint32))
+    data = np.concatenate(parts + [parts[1][:777]])
+    codec.set_kernel_path(0)
+    blob = codec.pa_compress(method, f, S, data).copy()
+    back = codec.pa_decompress(method, f, blob, data.size)
+    assert np.array_equal(back, data)
+    codec.set_kernel_path(1)
+    blob1 = codec.pa_compress(method, f, S, data).copy()
+    assert np.array_equal(blob1, blob), "shared-memory-table and global-table encoders differ"
+    assert np.array_equal(codec.pa_decompress(method, f, blob, data.size), data)
+    codec.set_kernel_path(0)
+    ref = cpu()
+    blocks = split(blob, data.size, S)
+    for m in list(range(0, 8)) + [len(blocks) - 1]:
+        chunk = data[m * S : (m + 1) * S]
+        want = ref.compress(method, f, chunk)
+        pre, pay = blocks[m]
+        assert _container.prelude_equal(pre, want[: pre.size]) and np.array_equal(pay, want[pre.size :]), m
 
 
 def test_large_round_trip_and_gain(codec):
