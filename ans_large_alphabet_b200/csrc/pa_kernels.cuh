@@ -101,6 +101,25 @@ __device__ __forceinline__ void pa_build_cum(const uint32_t* __restrict__ nf_mod
     }
 }
 
+// Inclusive scan and total of c = k + 4 * r (k = 0..3 raw bytes, r = renormalisation) over the 4 lanes of a group,
+// from three ballots instead of three dependent shuffles: the group's nibbles are spread to one bit per unit of
+// weight (k bit 0 once, k bit 1 twice, r four times), masked with the lanes that count, and counted.
+// `mine` = that 28-bit spread of {lanes of my group at or before me in emission order} (a per-lane constant).
+__device__ __forceinline__ uint32_t pa_scan_mask(uint32_t g, bool forward)
+{
+    const uint32_t lanes = forward ? (0xFu >> (3u - g)) : ((0xFu << g) & 0xFu); // forward: g' <= g; reverse: g' >= g
+    return lanes * 0x1111111u;
+}
+__device__ __forceinline__ void pa_group_scan(uint32_t k, bool r, uint32_t gshift, uint32_t mine, uint32_t& incl, uint32_t& total)
+{
+    const uint32_t b0 = __ballot_sync(0xffffffffu, (k & 1u) != 0u);
+    const uint32_t b1 = __ballot_sync(0xffffffffu, (k & 2u) != 0u);
+    const uint32_t br = __ballot_sync(0xffffffffu, r);
+    const uint32_t v = ((b0 >> gshift) & 0xFu) + ((b1 >> gshift) & 0xFu) * 0x110u + ((br >> gshift) & 0xFu) * 0x1111000u;
+    incl = uint32_t(__popc(v & mine));
+    total = uint32_t(__popc(v));
+}
+
 template <int METHOD> __device__ __forceinline__ uint32_t pa_unmap(uint32_t s, uint32_t f, uint32_t& k)
 {
     if (METHOD == METHOD_MSB)
@@ -135,6 +154,7 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_encode_kernel(co
     uint16_t* cum = reinterpret_cast<uint16_t*>(gmem);
     uint8_t* row = gmem + pa_cum_bytes(syms);
     const uint32_t f = a.fidelity;
+    const uint32_t scan_mine = pa_scan_mask(g, false);
 
     const uint32_t n_tasks = (a.n_blocks + 7u) >> 3;
     for (uint32_t task = blockIdx.x * warps + warp; task < n_tasks; task += gridDim.x * warps) {
@@ -158,6 +178,7 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_encode_kernel(co
         const uint32_t max_steps = __reduce_max_sync(0xffffffffu, my_steps);
 
         uint64_t x = lower;   // initial_state() (ans_fold.hpp:113)
+        bool bad = false;     // a symbol without a frequency in this block's model
         uint32_t fill = 0;    // bytes sitting in the row
         uint64_t flushed = 0; // bytes already drained to scratch
         uint8_t* dst = a.scratch + uint64_t(blk) * a.stride;
@@ -195,31 +216,38 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_encode_kernel(co
                     anext |= uint32_t(fetch(s0 + kEncTile + uint32_t(i), vnext[i])) << i;
             }
 
+            // Table entries one step ahead: the loads of step i + 1 are issued before the row stores of step i (which
+            // the compiler must assume alias them), so their latency overlaps the scan and the state update.
+            uint32_t k_n, freq_n, base_n;
+            double rcp_n;
+            auto lookup = [&](uint32_t v, bool active) {
+                uint32_t sym = map_value<METHOD>(v, f, k_n);
+                const bool outside = sym >= syms; // value beyond every model of this input: flag, stay in bounds
+                sym = outside ? 0u : sym;
+                base_n = cum[sym];
+                freq_n = (uint32_t(cum[sym + 1u]) - base_n) & 0xFFFFu;
+                rcp_n = freq_n < uint32_t(kPaRcpN) ? s_rcp[freq_n] : pa_rcp_up(freq_n);
+                bad |= active && (outside || freq_n == 0u);
+                k_n = active ? k_n : 0u;
+            };
+            lookup(vcur[0], acur & 1u);
 #pragma unroll
             for (int i = 0; i < kEncTile; i++) {
                 const bool active = (acur >> i) & 1u;
                 const uint32_t v = vcur[i];
-                uint32_t k;
-                uint32_t sym = map_value<METHOD>(v, f, k);
-                if (sym >= syms) { // value outside every model of this input: flag, stay in bounds
-                    if (active)
-                        *a.error_flag = 1u;
-                    sym = 0;
-                }
-                const uint32_t base = cum[sym];
-                const uint32_t freq = (uint32_t(cum[sym + 1u]) - base) & 0xFFFFu;
-                const double rcp = freq < uint32_t(kPaRcpN) ? s_rcp[freq] : pa_rcp_up(freq);
+                const uint32_t k = k_n, freq = freq_n, base = base_n;
+                const double rcp = rcp_n;
+                if (i + 1 < kEncTile)
+                    lookup(vcur[i + 1], (acur >> (i + 1)) & 1u);
                 const bool renorm = active && (uint32_t(x >> 36) >= freq); // state >= freq * K * 2^32
-                const uint32_t c = active ? k + (renorm ? 4u : 0u) : 0u;
+                const uint32_t c = k + (renorm ? 4u : 0u);
                 // reverse inclusive scan over the group: lanes with larger g emit first
-                uint32_t incl = c;
-                uint32_t t = __shfl_down_sync(0xffffffffu, incl, 1, 4);
-                if (g < 3u)
-                    incl += t;
-                t = __shfl_down_sync(0xffffffffu, incl, 2, 4);
-                if (g < 2u)
-                    incl += t;
-                const uint32_t total = __shfl_sync(0xffffffffu, incl, grp_base);
+                uint32_t incl, total;
+                pa_group_scan(k, renorm, grp_base, scan_mine, incl, total);
+                const uint32_t w = uint32_t(x);
+                if (renorm)
+                    x >>= kRadixLog2;
+                const uint64_t xn = ans_push(x, freq, base, rcp, log2_frame);
                 uint8_t* p = row + fill + (incl - c);
                 if (active) {
                     if (k > 0u)
@@ -229,16 +257,12 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_encode_kernel(co
                     if (k > 2u)
                         p[2] = uint8_t(v >> 16);
                     if (renorm) {
-                        const uint32_t w = uint32_t(x);
                         p[k] = uint8_t(w);
                         p[k + 1] = uint8_t(w >> 8);
                         p[k + 2] = uint8_t(w >> 16);
                         p[k + 3] = uint8_t(w >> 24);
-                        x >>= kRadixLog2;
                     }
-                    if (freq == 0u)
-                        *a.error_flag = 1u;
-                    x = ans_push(x, freq, base, rcp, log2_frame);
+                    x = xn;
                 }
                 fill += total;
             }
@@ -285,6 +309,8 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_encode_kernel(co
             if (have_block && g == 0u)
                 a.block_bytes[blk] = uint32_t(flushed + fill);
         }
+        if (bad)
+            *a.error_flag = 1u;
         __syncwarp();
     }
 }
@@ -301,7 +327,8 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_decode_kernel(co
     const uint32_t warps = blockDim.x >> 5;
     const uint32_t grp = lane >> 2;
     const uint32_t g = lane & 3u;
-    const uint32_t grp_last = lane | 3u;
+    const uint32_t grp_base = lane & ~3u;
+    const uint32_t scan_mine = pa_scan_mask(g, true);
     const uint32_t syms = a.pa_syms; // multiple of 16, beyond the largest symbol of every model
     const uint32_t blog = a.pa_bucket_log2;
     uint8_t* gmem = smem_raw + size_t(warp * 8u + grp) * pa_dec_group_bytes(syms, blog);
@@ -395,16 +422,11 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_decode_kernel(co
                 const uint32_t mapped = pa_unmap<METHOD>(slo, f, k);
                 uint64_t nx = uint64_t(freq) * (x >> log2_frame) + offset;
                 const bool renorm = active && nx < lower;
-                const uint32_t c = active ? k + (renorm ? 4u : 0u) : 0u;
+                k = active ? k : 0u;
+                const uint32_t c = k + (renorm ? 4u : 0u);
                 // forward inclusive scan: lane 0 of the group consumes first
-                uint32_t incl = c;
-                uint32_t t = __shfl_up_sync(0xffffffffu, incl, 1, 4);
-                if (g >= 1u)
-                    incl += t;
-                t = __shfl_up_sync(0xffffffffu, incl, 2, 4);
-                if (g >= 2u)
-                    incl += t;
-                const uint32_t total = __shfl_sync(0xffffffffu, incl, grp_last);
+                uint32_t incl, total;
+                pa_group_scan(k, renorm, grp_base, scan_mine, incl, total);
                 const int32_t end = cursor - int32_t(incl - c); // my bytes are [end - c, end)
                 // 8-byte window [end-8, end) from three aligned words
                 const int32_t wa = end - 8;
