@@ -91,6 +91,10 @@ struct b200ans_ctx {
     std::string err;
     b200ans_stats stats {};
     cudaEvent_t ev[8] {};
+    // host-buffer decode pipeline: a copy-in and a copy-out stream next to `stream`, one event pair per chunk
+    static constexpr int kPipeChunks = 8;
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
 
     // grow-only device buffers
     DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre, pa_keys;
@@ -274,6 +278,16 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     for (auto& e : c->ev)
         if (e)
             cudaEventDestroy(e);
+    for (auto& e : c->ev_in)
+        if (e)
+            cudaEventDestroy(e);
+    for (auto& e : c->ev_dec)
+        if (e)
+            cudaEventDestroy(e);
+    if (c->copy_in)
+        cudaStreamDestroy(c->copy_in);
+    if (c->copy_out)
+        cudaStreamDestroy(c->copy_out);
     if (c->pinned)
         cudaFreeHost(c->pinned);
     if (c->pa_pinned)
@@ -1601,6 +1615,124 @@ extern "C" int b200ans_compress(b200ans_ctx* c, int method, uint32_t f, uint8_t*
     return B200ANS_OK;
 }
 
+namespace {
+
+// Host-buffer decode of a blocked container as a three-stage pipeline over up to kPipeChunks runs of blocks:
+//   copy_in : container front (header, prelude, size table), then the payload run by run            (H2D engine)
+//   stream  : model tables, size scan, then one decoder launch per run as its bytes arrive          (SMs)
+//   copy_out: the decoded symbols of a run, as soon as its launch is done                           (D2H engine)
+// PCIe is full duplex, so the (4 n)-byte copy out overlaps the copy in and the decoding instead of following them.
+// Header, prelude and block sizes are read from the caller's buffer on the host: no device round trip before
+// the first launch.  Blocks are independent given the model, so a run needs only its own payload bytes.
+int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src, size_t src_bytes)
+{
+    if (src_bytes < B200ANS_HEADER_BYTES)
+        return c->fail(B200ANS_E_FORMAT, "decompress: shorter than a header");
+    Header h;
+    std::memcpy(&h, src, sizeof h);
+    if (h.magic != B200ANS_MAGIC || h.version != 1)
+        return c->fail(B200ANS_E_FORMAT, "decompress: bad magic / version");
+    if (h.flags & kFlagPseudoAdaptive)
+        return c->fail(B200ANS_E_FORMAT, "decompress: pseudo-adaptive container (use b200ans_pa_decompress)");
+    if (h.method != method || (h.fidelity != f && (method == METHOD_FOLD || method == METHOD_RFOLD)))
+        return c->fail(B200ANS_E_FORMAT, "decompress: container was written by another method");
+    if (h.n_symbols != n)
+        return c->fail(B200ANS_E_ARG, "decompress: symbol count does not match the container");
+    if (n == 0)
+        return B200ANS_OK;
+    if (h.block_syms == 0 || h.block_syms % 4 != 0 || h.n_blocks != (n + h.block_syms - 1) / h.block_syms)
+        return c->fail(B200ANS_E_FORMAT, "decompress: inconsistent block geometry");
+    const size_t table_at = B200ANS_HEADER_BYTES + align_up(h.prelude_bytes, 4);
+    const size_t payload_at = align_up(table_at + size_t(h.n_blocks) * 4, 16);
+    if (payload_at < table_at || payload_at + h.payload_bytes > src_bytes || payload_at + h.payload_bytes < payload_at)
+        return c->fail(B200ANS_E_FORMAT, "decompress: container truncated");
+    const uint32_t nb = h.n_blocks;
+
+    // runs of blocks with about equal payload; the size table must add up to the header's total
+    const int want = int(std::max<uint64_t>(1, std::min<uint64_t>(b200ans_ctx::kPipeChunks, h.payload_bytes / (uint64_t(4) << 20))));
+    uint32_t run_end[b200ans_ctx::kPipeChunks];
+    uint64_t run_bytes_end[b200ans_ctx::kPipeChunks];
+    int runs = 0;
+    {
+        const uint8_t* tp = src + table_at;
+        uint64_t total = 0;
+        const uint64_t per = (h.payload_bytes + uint64_t(want) - 1) / uint64_t(want);
+        for (uint32_t b = 0; b < nb; b++) {
+            uint32_t v;
+            std::memcpy(&v, tp + size_t(b) * 4, 4);
+            if (v < 32u)
+                return c->fail(B200ANS_E_FORMAT, "decompress: a block is shorter than its four states");
+            total += (uint64_t(v) + 15u) & ~uint64_t(15);
+            if (total > h.payload_bytes)
+                return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
+            if ((total >= per * uint64_t(runs + 1) && runs < want - 1) || b == nb - 1) {
+                run_end[runs] = b + 1;
+                run_bytes_end[runs] = total;
+                runs++;
+            }
+        }
+        if (total != h.payload_bytes)
+            return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
+    }
+
+    if (!c->copy_in) {
+        CU(c, cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking));
+        CU(c, cudaStreamCreateWithFlags(&c->copy_out, cudaStreamNonBlocking));
+        for (auto& e : c->ev_in)
+            CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (auto& e : c->ev_dec)
+            CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    CU(c, c->io_out.reserve(src_bytes + 64));
+    CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
+    CU(c, c->offsets.reserve(size_t(nb) * 8));
+    uint8_t* d_src = c->io_out.as<uint8_t>();
+    uint32_t* d_dst = c->io_in.as<uint32_t>();
+
+    // everything queued on `stream` so far (e.g. the caller's work on a borrowed stream) comes first
+    CU(c, cudaEventRecord(c->ev[5], c->stream));
+    CU(c, cudaStreamWaitEvent(c->copy_in, c->ev[5], 0));
+    CU(c, cudaStreamWaitEvent(c->copy_out, c->ev[5], 0));
+    CU(c, cudaMemcpyAsync(d_src, src, payload_at, cudaMemcpyHostToDevice, c->copy_in));
+    CU(c, cudaMemsetAsync(d_src + src_bytes, 0, 64, c->copy_in));
+    CU(c, cudaEventRecord(c->ev_in[b200ans_ctx::kPipeChunks], c->copy_in));
+    for (int r = 0; r < runs; r++) {
+        const uint64_t lo = r ? run_bytes_end[r - 1] : 0;
+        CU(c, cudaMemcpyAsync(d_src + payload_at + lo, src + payload_at + lo, size_t(run_bytes_end[r] - lo), cudaMemcpyHostToDevice, c->copy_in));
+        CU(c, cudaEventRecord(c->ev_in[r], c->copy_in));
+    }
+
+    // the model: prelude -> tables (host), uploaded on `stream` while the payload is on its way
+    RET(b200ans_model_load(c, method, f, src + B200ANS_HEADER_BYTES, h.prelude_bytes, nullptr));
+    CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[b200ans_ctx::kPipeChunks], 0));
+    const uint32_t* d_sizes = reinterpret_cast<const uint32_t*>(d_src + table_at);
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, nb, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    for (int r = 0; r < runs; r++) {
+        const uint32_t b0 = r ? run_end[r - 1] : 0, b1 = run_end[r];
+        const uint64_t s0 = uint64_t(b0) * h.block_syms, s1 = std::min<uint64_t>(n, uint64_t(b1) * h.block_syms);
+        CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
+        RET(launch_decode(c, d_src + payload_at, c->offsets.as<uint64_t>() + b0, d_sizes + b0, size_t(s1 - s0), h.block_syms, b1 - b0, d_dst + s0));
+        CU(c, cudaEventRecord(c->ev_dec[r], c->stream));
+        CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_dec[r], 0));
+        CU(c, cudaMemcpyAsync(dst + s0, d_dst + s0, size_t(s1 - s0) * 4, cudaMemcpyDeviceToHost, c->copy_out));
+    }
+    CU(c, cudaEventRecord(c->ev[1], c->stream));
+    CU(c, cudaEventRecord(c->ev[6], c->copy_out));
+    CU(c, cudaStreamWaitEvent(c->stream, c->ev[6], 0)); // the call's work ends on `stream`, as every other entry point's
+    CU(c, cudaEventRecord(c->ev[7], c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
+    c->stats.ms_h2d = 0.f; // overlapped: the stages are not separable
+    c->stats.ms_d2h = elapsed(c->ev[1], c->ev[7]);
+    c->stats.n_blocks = nb;
+    return B200ANS_OK;
+}
+
+} // namespace
+
 extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src,
     size_t src_bytes)
 {
@@ -1609,6 +1741,10 @@ extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32
     if ((!dst && n) || !src || !valid_method(method, f))
         return c->fail(B200ANS_E_ARG, "decompress: bad argument");
     CU(c, cudaSetDevice(c->device));
+    if (c->block_syms != 0 && !env_int("B200ANS_NO_PIPELINE", 0)) {
+        c->stats.ms_decode = c->stats.ms_model = 0.f;
+        return decompress_pipelined(c, method, f, dst, n, src, src_bytes);
+    }
     CU(c, c->io_out.reserve(src_bytes + 64));
     CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
     CU(c, cudaEventRecord(c->ev[5], c->stream));
