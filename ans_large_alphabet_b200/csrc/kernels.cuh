@@ -231,6 +231,25 @@ template <int METHOD> __device__ __forceinline__ uint32_t map_value(uint32_t v, 
     }
 }
 
+// Inclusive scan and total of c = k + 4 * r (k = 0..3 raw bytes, r = renormalisation) over the 4 lanes of a group,
+// from three ballots instead of three dependent shuffles: the group's nibbles are spread to one bit per unit of
+// weight (k bit 0 once, k bit 1 twice, r four times), masked with the lanes that count, and counted.
+// `mine` = that 28-bit spread of {lanes of my group at or before me in emission order} (a per-lane constant).
+__device__ __forceinline__ uint32_t group_scan_mask(uint32_t g, bool forward)
+{
+    const uint32_t lanes = forward ? (0xFu >> (3u - g)) : ((0xFu << g) & 0xFu); // forward: g' <= g; reverse: g' >= g
+    return lanes * 0x1111111u;
+}
+__device__ __forceinline__ void group_scan(uint32_t k, bool r, uint32_t gshift, uint32_t mine, uint32_t& incl, uint32_t& total)
+{
+    const uint32_t b0 = __ballot_sync(0xffffffffu, (k & 1u) != 0u);
+    const uint32_t b1 = __ballot_sync(0xffffffffu, (k & 2u) != 0u);
+    const uint32_t br = __ballot_sync(0xffffffffu, r);
+    const uint32_t v = ((b0 >> gshift) & 0xFu) + ((b1 >> gshift) & 0xFu) * 0x110u + ((br >> gshift) & 0xFu) * 0x1111000u;
+    incl = uint32_t(__popc(v & mine));
+    total = uint32_t(__popc(v));
+}
+
 // state -> (state / freq) * M + state % freq + base, exactly (ans_fold.hpp:111).
 // Precondition: state < freq * 2^36 (always true after the renormalisation check) so the
 // quotient is below 2^36 and the double product errs by less than 2^-13.
@@ -404,6 +423,7 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_kernel(const EncArgs a)
     const uint32_t grp = lane >> 2;
     const uint32_t g = lane & 3u;           // position inside a 4-symbol step; chain = 3 - g
     const uint32_t grp_base = lane & ~3u;
+    const uint32_t scan_mine = group_scan_mask(g, false);
     uint8_t* row = s_rows + (size_t(warp) * 8 + grp) * kEncRowBytes;
     const EncEntry* table0 = TABLE_SMEM ? s_table : a.table;
     const uint32_t f = a.fidelity;
@@ -493,14 +513,8 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_kernel(const EncArgs a)
                 const bool renorm = active && (uint32_t(x >> 36) >= e.freq); // state >= freq * K * 2^32
                 const uint32_t c = active ? k + (renorm ? 4u : 0u) : 0u;
                 // reverse inclusive scan over the group: lanes with larger g emit first
-                uint32_t incl = c;
-                uint32_t t = __shfl_down_sync(0xffffffffu, incl, 1, 4);
-                if (g < 3u)
-                    incl += t;
-                t = __shfl_down_sync(0xffffffffu, incl, 2, 4);
-                if (g < 2u)
-                    incl += t;
-                const uint32_t total = __shfl_sync(0xffffffffu, incl, grp_base);
+                uint32_t incl, total;
+                group_scan(active ? k : 0u, renorm, grp_base, scan_mine, incl, total);
                 uint8_t* p = row + fill + (incl - c);
                 if (active) {
                     if (k > 0u)
@@ -599,7 +613,8 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t grp = lane >> 2;
     const uint32_t g = lane & 3u;
-    const uint32_t grp_last = lane | 3u;
+    const uint32_t grp_base = lane & ~3u;
+    const uint32_t scan_mine = group_scan_mask(g, true);
     uint8_t* row = s_rows + (size_t(warp) * 8 + grp) * kDecRowBytes;
     const uint32_t rfold_bias = (METHOD == METHOD_RFOLD) ? (1u << (a.fidelity + 7)) : 0u; // ans_reorder_fold.hpp:301
 
@@ -673,14 +688,8 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
                 const bool renorm = active && nx < lower;
                 const uint32_t c = active ? k + (renorm ? 4u : 0u) : 0u;
                 // forward inclusive scan: lane 0 of the group consumes first
-                uint32_t incl = c;
-                uint32_t t = __shfl_up_sync(0xffffffffu, incl, 1, 4);
-                if (g >= 1u)
-                    incl += t;
-                t = __shfl_up_sync(0xffffffffu, incl, 2, 4);
-                if (g >= 2u)
-                    incl += t;
-                const uint32_t total = __shfl_sync(0xffffffffu, incl, grp_last);
+                uint32_t incl, total;
+                group_scan(active ? k : 0u, renorm, grp_base, scan_mine, incl, total);
                 const int32_t end = cursor - int32_t(incl - c); // my bytes are [end - c, end)
                 // 8-byte window [end-8, end) from three aligned words
                 const int32_t wa = end - 8;

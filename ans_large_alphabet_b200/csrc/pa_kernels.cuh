@@ -101,25 +101,6 @@ __device__ __forceinline__ void pa_build_cum(const uint32_t* __restrict__ nf_mod
     }
 }
 
-// Inclusive scan and total of c = k + 4 * r (k = 0..3 raw bytes, r = renormalisation) over the 4 lanes of a group,
-// from three ballots instead of three dependent shuffles: the group's nibbles are spread to one bit per unit of
-// weight (k bit 0 once, k bit 1 twice, r four times), masked with the lanes that count, and counted.
-// `mine` = that 28-bit spread of {lanes of my group at or before me in emission order} (a per-lane constant).
-__device__ __forceinline__ uint32_t pa_scan_mask(uint32_t g, bool forward)
-{
-    const uint32_t lanes = forward ? (0xFu >> (3u - g)) : ((0xFu << g) & 0xFu); // forward: g' <= g; reverse: g' >= g
-    return lanes * 0x1111111u;
-}
-__device__ __forceinline__ void pa_group_scan(uint32_t k, bool r, uint32_t gshift, uint32_t mine, uint32_t& incl, uint32_t& total)
-{
-    const uint32_t b0 = __ballot_sync(0xffffffffu, (k & 1u) != 0u);
-    const uint32_t b1 = __ballot_sync(0xffffffffu, (k & 2u) != 0u);
-    const uint32_t br = __ballot_sync(0xffffffffu, r);
-    const uint32_t v = ((b0 >> gshift) & 0xFu) + ((b1 >> gshift) & 0xFu) * 0x110u + ((br >> gshift) & 0xFu) * 0x1111000u;
-    incl = uint32_t(__popc(v & mine));
-    total = uint32_t(__popc(v));
-}
-
 template <int METHOD> __device__ __forceinline__ uint32_t pa_unmap(uint32_t s, uint32_t f, uint32_t& k)
 {
     if (METHOD == METHOD_MSB)
@@ -154,7 +135,7 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_encode_kernel(co
     uint16_t* cum = reinterpret_cast<uint16_t*>(gmem);
     uint8_t* row = gmem + pa_cum_bytes(syms);
     const uint32_t f = a.fidelity;
-    const uint32_t scan_mine = pa_scan_mask(g, false);
+    const uint32_t scan_mine = group_scan_mask(g, false);
 
     const uint32_t n_tasks = (a.n_blocks + 7u) >> 3;
     for (uint32_t task = blockIdx.x * warps + warp; task < n_tasks; task += gridDim.x * warps) {
@@ -243,7 +224,7 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_encode_kernel(co
                 const uint32_t c = k + (renorm ? 4u : 0u);
                 // reverse inclusive scan over the group: lanes with larger g emit first
                 uint32_t incl, total;
-                pa_group_scan(k, renorm, grp_base, scan_mine, incl, total);
+                group_scan(k, renorm, grp_base, scan_mine, incl, total);
                 const uint32_t w = uint32_t(x);
                 if (renorm)
                     x >>= kRadixLog2;
@@ -328,7 +309,7 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_decode_kernel(co
     const uint32_t grp = lane >> 2;
     const uint32_t g = lane & 3u;
     const uint32_t grp_base = lane & ~3u;
-    const uint32_t scan_mine = pa_scan_mask(g, true);
+    const uint32_t scan_mine = group_scan_mask(g, true);
     const uint32_t syms = a.pa_syms; // multiple of 16, beyond the largest symbol of every model
     const uint32_t blog = a.pa_bucket_log2;
     uint8_t* gmem = smem_raw + size_t(warp * 8u + grp) * pa_dec_group_bytes(syms, blog);
@@ -426,7 +407,7 @@ __global__ void __launch_bounds__(kPaCodeMaxWarps * 32) pa_smem_decode_kernel(co
                 const uint32_t c = k + (renorm ? 4u : 0u);
                 // forward inclusive scan: lane 0 of the group consumes first
                 uint32_t incl, total;
-                pa_group_scan(k, renorm, grp_base, scan_mine, incl, total);
+                group_scan(k, renorm, grp_base, scan_mine, incl, total);
                 const int32_t end = cursor - int32_t(incl - c); // my bytes are [end - c, end)
                 // 8-byte window [end-8, end) from three aligned words
                 const int32_t wa = end - 8;
