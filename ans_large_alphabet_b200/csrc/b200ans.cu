@@ -86,6 +86,7 @@ struct b200ans_ctx {
     std::vector<uint8_t> front; // container front of the encode in flight (must outlive its H2D copy)
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
     int kernel_path = B200ANS_PATH_AUTO;
+    bool dec_words_aligned = false; // the decode in flight reads container blocks: payloads start 16-byte aligned
     uint32_t h_approx = 1; // adjust_freqs' H_approx (ANSsint<H> / ANSsmsb<H>)
     uint32_t max_nfreq = 0; // largest normalised frequency of the encoder model
     std::string err;
@@ -1156,6 +1157,19 @@ template <int METHOD, int TABLE> int launch_decode_tt(b200ans_ctx* c, const DecA
     return B200ANS_OK;
 }
 
+template <int TABLE> int launch_int_decode_t(b200ans_ctx* c, const DecArgs& a, size_t table_bytes)
+{
+    auto k = int_decode_kernel<TABLE>;
+    const size_t smem = table_bytes + size_t(kDecWarps) * 8 * kDecRowBytes;
+    CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    const uint32_t n_tasks = (a.n_blocks + 7) / 8;
+    const int grid = persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps);
+    k<<<grid, kDecWarps * 32, smem, c->stream>>>(a);
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
 int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_offsets, const uint32_t* d_block_bytes,
     size_t n, uint32_t block_syms, uint32_t n_blocks, uint32_t* d_dst)
 {
@@ -1203,9 +1217,10 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     const size_t budget = c->max_smem > rows + 1024 ? c->max_smem - rows - 1024 : 0;
     if (c->dec_method == METHOD_INT) {
         const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_dense);
+        const bool words = c->dec_words_aligned && (reinterpret_cast<uintptr_t>(d_payload) & 3) == 0 && !env_int("B200ANS_NO_INTDEC", 0);
         if (tb <= std::min<size_t>(budget, size_t(100) << 10))
-            return launch_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
-        return launch_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);
+            return words ? launch_int_decode_t<DEC_INT_SMEM>(c, a, tb) : launch_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
+        return words ? launch_int_decode_t<DEC_INT_GLOBAL>(c, a, 0) : launch_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);
     }
     const size_t tb = align_up(frame * sizeof(DecEntry), 16);
     const bool smem = tb <= std::min<size_t>(budget, size_t(128) << 10);
@@ -1579,7 +1594,9 @@ extern "C" int b200ans_decompress_device(b200ans_ctx* c, int method, uint32_t f,
         return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
     const uint32_t saved = c->block_syms;
     c->block_syms = h.block_syms;
+    c->dec_words_aligned = true; // container blocks start 16-byte aligned (offsets come from our own scan)
     const int rc = b200ans_decode_blocks_device(c, d_src + payload_at, c->offsets.as<uint64_t>(), d_sizes, n, d_dst);
+    c->dec_words_aligned = false;
     c->block_syms = saved;
     return rc;
 }
@@ -1714,7 +1731,10 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
         const uint32_t b0 = r ? run_end[r - 1] : 0, b1 = run_end[r];
         const uint64_t s0 = uint64_t(b0) * h.block_syms, s1 = std::min<uint64_t>(n, uint64_t(b1) * h.block_syms);
         CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
-        RET(launch_decode(c, d_src + payload_at, c->offsets.as<uint64_t>() + b0, d_sizes + b0, size_t(s1 - s0), h.block_syms, b1 - b0, d_dst + s0));
+        c->dec_words_aligned = true;
+        const int rc = launch_decode(c, d_src + payload_at, c->offsets.as<uint64_t>() + b0, d_sizes + b0, size_t(s1 - s0), h.block_syms, b1 - b0, d_dst + s0);
+        c->dec_words_aligned = false;
+        RET(rc);
         CU(c, cudaEventRecord(c->ev_dec[r], c->stream));
         CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_dec[r], 0));
         CU(c, cudaMemcpyAsync(dst + s0, d_dst + s0, size_t(s1 - s0) * 4, cudaMemcpyDeviceToHost, c->copy_out));

@@ -713,6 +713,110 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
 }
 
 // ------------------------------------------------------------------------------------------
+// K3 for plain ANS (ans_int.hpp:257-306), word-aligned payloads: the same 4-lanes-per-block decomposition as
+// decode_kernel, stripped to what a stream without raw bytes needs.  A block's payload is then a sequence of aligned
+// 32-bit renormalisation words (every container block starts 16-byte aligned), so a step is: rank/select lookup,
+// state update, ONE ballot for the group's renormalisation flags (the lane's word is the popc(flags below me)-th
+// below the cursor), one aligned word from the staged window.  About half the instructions of the generic kernel
+// (no 3-word window + funnel shifts, no raw-byte counts); with 4x the warps of the lane-per-block decoder it is the
+// faster one while the input has fewer than ~112 blocks per SM (C2: 24 415 blocks of 4096 symbols).
+// ------------------------------------------------------------------------------------------
+constexpr int kIntDecTile = 16; // steps per staged window: 16 steps x 4 lanes x 4 bytes = 256 bytes + alignment
+// (Measured and dropped: a 128-word ring per block refilled one tile ahead with cp.async -- the extra 26 KB per CTA
+// cost a resident CTA per SM and the per-lane 16-byte copies more than the hidden latency gave back: C2 0.41 -> 0.43 ms.)
+
+template <int TABLE>
+__global__ void __launch_bounds__(kDecWarps * 32) int_decode_kernel(const DecArgs a)
+{
+    static_assert(kDecPad + (kIntDecTile + 1) * 16 <= kDecRowBytes, "staged window does not fit the row");
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    DecTables<METHOD_INT, TABLE> tables;
+    uint8_t* s_rows = smem_raw + tables.load(a, smem_raw);
+
+    const uint32_t lane = lane_id();
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t grp = lane >> 2;
+    const uint32_t g = lane & 3u;
+    const uint32_t grp_base = lane & ~3u;
+    const uint32_t below = (1u << g) - 1u; // lanes of my group that consume before me (ans_int.hpp:273-289 order)
+    uint8_t* row = s_rows + (size_t(warp) * 8 + grp) * kDecRowBytes;
+    const uint32_t log2_frame = a.log2_frame;
+    const uint32_t frame_mask = (1u << log2_frame) - 1u;
+    const uint64_t lower = uint64_t(kAnsK) << log2_frame;
+
+    const uint32_t n_tasks = (a.n_blocks + 7u) >> 3;
+    for (uint32_t task = blockIdx.x * kDecWarps + warp; task < n_tasks; task += gridDim.x * kDecWarps) {
+        const uint32_t blk = task * 8 + grp;
+        const bool have_block = blk < a.n_blocks;
+        const uint64_t first = uint64_t(blk) * a.block_syms;
+        const uint32_t nb = have_block ? uint32_t(min(uint64_t(a.block_syms), a.n - first)) : 0u;
+        const uint32_t tail = nb & 3u;
+        const uint32_t quads = nb >> 2;
+        const uint32_t my_steps = quads + tail;
+        const uint32_t max_steps = __reduce_max_sync(0xffffffffu, my_steps);
+        uint32_t* out = a.out + first;
+
+        // word positions are relative to the 16-byte aligned address at or below the payload start
+        const uint8_t* pay = a.payload + (have_block ? a.offsets[blk] : 0);
+        const uint32_t delta = uint32_t(reinterpret_cast<uintptr_t>(pay) & 15u);
+        const uint4* pay_al = reinterpret_cast<const uint4*>(pay - delta);
+        const uint32_t size = have_block ? a.block_bytes[blk] : 32u;
+
+        // init_state x4: chain 3 is the last 8 bytes ... chain 0 the first of the 32 (ans_int.hpp:262-270)
+        uint64_t x = lower;
+        if (have_block) {
+            const uint32_t* sp = reinterpret_cast<const uint32_t*>(pay + size - 32u + 8u * (3u - g));
+            x = (uint64_t(__ldg(sp)) | (uint64_t(__ldg(sp + 1)) << 32)) + lower;
+        }
+        int32_t wcur = int32_t((delta + size - 32u) >> 2); // one past the next word to consume
+
+        for (uint32_t s0 = 0; s0 < max_steps; s0 += kIntDecTile) {
+            // stage the words [lo, wcur): at most 4 * kIntDecTile are consumed before the next refill
+            int32_t lo = wcur - 4 * kIntDecTile;
+            lo = lo < 0 ? 0 : (lo & ~3);
+            __syncwarp();
+            if (have_block) {
+                const uint4* gsrc = pay_al + (lo >> 2);
+                uint4* sdst = reinterpret_cast<uint4*>(row + kDecPad);
+                const int32_t need = (wcur - lo + 3) >> 2; // chunks that can be touched: <= kIntDecTile + 1
+#pragma unroll
+                for (int ci = 0; ci < (kIntDecTile + 1 + 3) / 4; ci++) {
+                    const int32_t c = ci * 4 + int32_t(g);
+                    if (c < need)
+                        sdst[c] = __ldg(gsrc + c);
+                }
+            }
+            __syncwarp();
+            const uint32_t* stage = reinterpret_cast<const uint32_t*>(row + kDecPad) - lo; // stage[w] is payload word w
+
+#pragma unroll
+            for (int i = 0; i < kIntDecTile; i++) {
+                const uint32_t s = s0 + uint32_t(i);
+                // quads first, all four lanes; then the tail on chain 0 (lane g == 3)
+                const bool active = s < quads ? true : (s < my_steps && g == 3u);
+                const uint32_t idx = s < quads ? 4u * s + g : s + 3u * quads;
+                const uint32_t slot = uint32_t(x) & frame_mask;
+                uint32_t freq, offset, sym, k;
+                tables.lookup(slot, freq, offset, sym, k);
+                uint64_t nx = uint64_t(freq) * (x >> log2_frame) + offset;
+                const bool renorm = active && nx < lower;
+                const uint32_t flags = (__ballot_sync(0xffffffffu, renorm) >> grp_base) & 0xFu;
+                // my word is the popc(flags below me)-th below the cursor (unread when I do not renormalise: the row
+                // has kDecPad bytes in front, so the address stays inside it)
+                const uint32_t w = stage[wcur - 1 - int32_t(__popc(flags & below))];
+                if (renorm)
+                    nx = (nx << kRadixLog2) | uint64_t(w);
+                if (active) {
+                    x = nx;
+                    out[idx] = sym;
+                }
+                wcur -= int32_t(__popc(flags));
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // Size scan + payload compaction
 // ------------------------------------------------------------------------------------------
 
