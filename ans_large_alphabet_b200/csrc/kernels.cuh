@@ -1146,11 +1146,15 @@ __global__ void __launch_bounds__(kPaNormThreads) pa_sort_kernel(const uint32_t*
     for (uint32_t model = blockIdx.x; model < n_models; model += gridDim.x) {
         const uint32_t* row = counts + uint64_t(model) * nbins;
         uint32_t* out = nfreqs + uint64_t(model) * nbins;
+        // Only the symbols that occur are sorted: thread t compacts the non-zero bins of its contiguous run to the
+        // back of a power-of-two window of n_sort >= sigma keys (zeros in front), 2.4x less bitonic work for a
+        // 500-symbol block in a 1024-bin alphabet.  Keys (count << 16 | symbol) are unique: the order is the same.
+        const uint32_t per = n_keys / blockDim.x; // n_keys is a multiple of the CTA size (1024 or 2048 over 64)
+        const uint32_t b0 = threadIdx.x * per;
         uint32_t sigma = 0;
         uint64_t total = 0;
-        for (uint32_t b = threadIdx.x; b < n_keys; b += blockDim.x) {
+        for (uint32_t b = b0; b < b0 + per; b++) {
             const uint32_t cnt = b < nbins ? __ldg(row + b) : 0u;
-            keys[b] = (uint64_t(cnt) << 16) | (cnt ? b : 0u);
             sigma += cnt != 0u;
             total += cnt;
             if (b < nbins)
@@ -1159,17 +1163,33 @@ __global__ void __launch_bounds__(kPaNormThreads) pa_sort_kernel(const uint32_t*
         s_cnt[threadIdx.x] = sigma;
         s_sum[threadIdx.x] = total;
         __syncthreads();
+        uint32_t before = 0;
         sigma = 0;
         total = 0;
         for (int t = 0; t < kPaNormThreads; t++) {
+            before += t < int(threadIdx.x) ? s_cnt[t] : 0u;
             sigma += s_cnt[t];
             total += s_sum[t];
         }
+        uint32_t n_sort = 2;
+        while (n_sort < sigma)
+            n_sort <<= 1;
+        const uint32_t pad = n_sort - sigma;
+        for (uint32_t r = threadIdx.x; r < pad; r += blockDim.x)
+            keys[r] = 0;
+        {
+            uint32_t at = pad + before;
+            for (uint32_t b = b0; b < b0 + per; b++) {
+                const uint32_t cnt = b < nbins ? __ldg(row + b) : 0u;
+                if (cnt)
+                    keys[at++] = (uint64_t(cnt) << 16) | b;
+            }
+        }
         // bitonic sort, ascending
-        for (uint32_t k = 2; k <= n_keys; k <<= 1)
+        for (uint32_t k = 2; k <= n_sort; k <<= 1)
             for (uint32_t j = k >> 1; j > 0; j >>= 1) {
                 __syncthreads();
-                for (uint32_t t = threadIdx.x; t < (n_keys >> 1); t += blockDim.x) {
+                for (uint32_t t = threadIdx.x; t < (n_sort >> 1); t += blockDim.x) {
                     const uint32_t i = ((t & ~(j - 1u)) << 1) | (t & (j - 1u)); // index with bit j clear
                     const uint32_t l = i | j;
                     const uint64_t a = keys[i], b = keys[l];
@@ -1183,12 +1203,12 @@ __global__ void __launch_bounds__(kPaNormThreads) pa_sort_kernel(const uint32_t*
         __syncthreads();
         const uint32_t first = n_keys - sigma;
         const double totald = double(total);
-        uint64_t* gk = gkeys + uint64_t(model) * n_keys;
+        uint64_t* gk = gkeys + uint64_t(model) * n_keys + (n_keys - n_sort); // the fits read [first, n_keys) only
         double acc = 0.0; // entropy: fixed-shape reduction
-        for (uint32_t r = threadIdx.x; r < n_keys; r += blockDim.x) {
+        for (uint32_t r = threadIdx.x; r < n_sort; r += blockDim.x) {
             const uint64_t key = keys[r];
             gk[r] = key;
-            if (r >= first) {
+            if (r >= pad) {
                 const double p = double(key >> 16) / totald;
                 acc = fma(p, log2(p), acc);
             }
