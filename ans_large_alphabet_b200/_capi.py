@@ -66,6 +66,7 @@ SIGNATURES = {
     "b200ans_decompress_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "b200ans_max_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_histogram_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "b200ans_histogram_max_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_rfold_prepare": (C.c_int, [C.c_void_p, C.c_uint32, u64p, C.c_size_t]),
     "b200ans_model_build": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u64p, C.c_size_t]),
     "b200ans_model_prelude": (C.c_int, [C.c_void_p, u8p, C.c_size_t, szp]),
@@ -330,6 +331,9 @@ class Codec:
 
     def histogram_device(self, method, f, d_src, n, d_bins, nbins):
         self._check(self.lib.b200ans_histogram_device(self.h, method, f, d_src, n, d_bins, nbins))
+
+    def histogram_max_device(self, method, f, d_src, n, d_bins, nbins, d_max):
+        self._check(self.lib.b200ans_histogram_max_device(self.h, method, f, d_src, n, d_bins, nbins, d_max))
 
     def rfold_prepare(self, f, raw_bins):
         raw_bins = np.ascontiguousarray(raw_bins, dtype=np.uint64)

@@ -605,6 +605,21 @@ extern "C" int b200ans_histogram_device(b200ans_ctx* c, int method, uint32_t f, 
     return histogram_dispatch(c, method, f, d_src, n, d_bins, nbins, c->d_max());
 }
 
+// As b200ans_histogram_device, and the largest raw value of the input goes to *d_max (device, zeroed here).  Values
+// whose bin is beyond nbins are not counted, so a caller that guesses the alphabet (plain ANS: ans_int.hpp:42-49
+// takes the maximum first) counts optimistically in ONE pass and looks at the maximum afterwards.
+extern "C" int b200ans_histogram_max_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n,
+    uint64_t* d_bins, size_t nbins, uint32_t* d_max)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_src || !d_bins || !d_max || !valid_method(method, f) || (reinterpret_cast<uintptr_t>(d_src) & 15))
+        return c->fail(B200ANS_E_ARG, "histogram: bad argument (d_src must be 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemsetAsync(d_max, 0, 4, c->stream));
+    return histogram_dispatch(c, method, f, d_src, n, d_bins, nbins, d_max);
+}
+
 // ==========================================================================================
 // models
 // ==========================================================================================

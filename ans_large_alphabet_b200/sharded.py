@@ -15,6 +15,9 @@ import numpy as np
 from ._capi import METHOD_FOLD, METHOD_INT, METHOD_MSB, METHOD_RFOLD
 
 
+OPT_BINS = 3071  # plain ANS: bins counted optimistically in one pass (four shared-memory replicas; b200ans.cu kOptBins)
+
+
 def shard_range(n, block_syms, rank, world):
     """Contiguous block range of `rank`: blocks [rank*nb/world, (rank+1)*nb/world)  ->  symbol range."""
     nb = (n + block_syms - 1) // block_syms
@@ -48,6 +51,14 @@ def reduce_histogram(bins, group=None):
     return bins.cpu().numpy().view(np.uint64)
 
 
+def reduce_bins_and_max(buf, opt_bins, group=None):
+    """ONE all-reduce for counts AND the largest value: `buf` holds this rank's optimistic counts in [0, opt_bins) and
+    its own maximum in slot opt_bins + rank (zeros in the other ranks' slots), so the sum is an all-gather of the
+    maxima behind the global counts.  Returns (global counts as host uint64, global maximum)."""
+    host = reduce_histogram(buf, group)
+    return host[:opt_bins], int(host[opt_bins:].max())
+
+
 def reduce_max(value, device, group=None):
     """all-reduce (max) of the largest raw value (the alphabet size of ANS / ANSrfold pass 1)"""
     import torch
@@ -77,15 +88,29 @@ def global_histogram(codec, method, f, d_src, n, group=None, sync=None):
         sync()
         return reduce_histogram(bins, group if world > 1 else None)
 
-    if method in (METHOD_INT, METHOD_RFOLD):
+    if method == METHOD_INT:
+        # The reference takes the maximum first, then counts (ans_int.hpp:42-49).  One pass and ONE all-reduce instead:
+        # count optimistically into OPT_BINS bins while the kernel keeps the running maximum, and ship every rank's
+        # maximum in its own slot behind the bins (sum of one-hot slots = all-gather).  Only an alphabet beyond
+        # OPT_BINS needs the second pass.
+        rank = dist.get_rank(group) if world > 1 else 0
+        buf = torch.zeros(OPT_BINS + world, dtype=torch.int64, device=dev)
+        sync()
+        # the kernel's 32-bit maximum lands in the low half of this rank's (zeroed, little-endian) int64 slot
+        codec.histogram_max_device(METHOD_INT, f, d_src.data_ptr(), n, buf.data_ptr(), OPT_BINS,
+                                   buf.data_ptr() + 8 * (OPT_BINS + rank))
+        sync()
+        counts, max_value = reduce_bins_and_max(buf, OPT_BINS, group if world > 1 else None)
+        if max_value < OPT_BINS:
+            return counts[: max_value + 1].copy()
+        return hist(METHOD_INT, max_value + 1)
+    if method == METHOD_RFOLD:
         mx = torch.zeros(1, dtype=torch.int32, device=dev)
         sync()
         codec.max_device(d_src.data_ptr(), n, mx.data_ptr())
         sync()
-        max_value = reduce_max(int(mx.item()), dev, group if world > 1 else None)
+        max_value = reduce_max(int(mx.item()) & 0xFFFFFFFF, dev, group if world > 1 else None)
         raw = hist(METHOD_INT, max_value + 1)
-        if method == METHOD_INT:
-            return raw
         codec.rfold_prepare(f, raw)  # identical on every rank: same global histogram, same tie-break
         return hist(METHOD_RFOLD, alphabet_bins(method, f))
     return hist(method, alphabet_bins(method, f))

@@ -230,7 +230,7 @@ def run_reference_arm(args, wl):
         "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": wall,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -318,7 +318,9 @@ def run_ours(args, wl):
     torch.cuda.synchronize(dev)
 
     def sync():
-        stream.synchronize()
+        # the codec runs on `stream` and so do the torch ops around it (every step is inside torch.cuda.stream(stream)):
+        # stream order is all the ordering the sharded path needs
+        pass
 
     def barrier():
         if world > 1:
@@ -424,10 +426,8 @@ def run_ours(args, wl):
             nbh = sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
             h_blob[:nbh].copy_(d_blob[:nbh], non_blocking=True)
             stream.synchronize()
-            d_blob[:nbh].copy_(h_blob[:nbh], non_blocking=True)
-            codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nbh)
-            h_out.copy_(d_out, non_blocking=True)
-            stream.synchronize()
+            # decoding needs no collective: the same host-buffer call as at N = 1 (copy-in / decode / copy-out pipeline)
+            codec.decompress_ptr(method, f, h_out.data_ptr(), n, h_blob.data_ptr(), nbh)
         return nbh
 
     for _ in range(min(args.warmup, 2)):
@@ -512,7 +512,7 @@ def run_ours(args, wl):
             del d_in, d_blob, d_out, h_in, h_blob, h_out
             torch.cuda.empty_cache()
             line["north_star_2p30"] = north_star_summary(P, dev, stream, peak)
-        print(json.dumps(line))
+        emit(line)
     codec.close()
     if world > 1:
         dist.destroy_process_group()
@@ -520,7 +520,26 @@ def run_ours(args, wl):
         raise SystemExit("bench.py: round trip FAILED")
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """the ONE JSON line of the contract, on the process's real stdout"""
+    text = json.dumps(line) + "\n"
+    if _REAL_STDOUT is None:
+        sys.stdout.write(text)
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, text.encode())
+
+
 def main():
+    # Libraries write to fd 1 behind Python's back (NCCL prints its version banner there at the first collective):
+    # everything but the JSON line goes to stderr.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

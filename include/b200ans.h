@@ -138,6 +138,10 @@ int b200ans_max_device(b200ans_ctx* ctx, const uint32_t* d_src, size_t n, uint32
  * method INT on the raw values first to obtain the full-alphabet histogram. */
 int b200ans_histogram_device(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint32_t* d_src, size_t n,
     uint64_t* d_bins, size_t nbins);
+/* the same, plus the largest raw value of the input to *d_max (device); values whose bin is beyond nbins are not
+ * counted, so plain ANS (ans_int.hpp:42-49: maximum first, then counts) can count optimistically in one pass */
+int b200ans_histogram_max_device(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint32_t* d_src, size_t n,
+    uint64_t* d_bins, size_t nbins, uint32_t* d_max);
 /* RFOLD only: from the full-alphabet histogram (host u64[nvalues]) pick the 2^(f+7) most
  * frequent values, ties to the smaller value (ans_reorder_fold.hpp:79-106), and upload the
  * value -> reordered-value table. */

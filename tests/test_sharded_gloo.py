@@ -44,6 +44,15 @@ def _worker(rank, world, port, out_dir):
         if method == P.METHOD_INT:
             mx = sharded.reduce_max(int(mine.max()) if mine.size else 0, "cpu", dist.group.WORLD)
             local = np.bincount(mine, minlength=mx + 1).astype(np.int64)
+            # the one-pass variant the GPU path uses: optimistic counts + one-hot maxima in ONE all-reduce
+            K = sharded.OPT_BINS
+            buf = np.zeros(K + world, dtype=np.int64)
+            inside = mine[mine < K]
+            buf[:K] = np.bincount(inside, minlength=K)[:K]
+            buf[K + rank] = int(mine.max()) if mine.size else 0
+            counts, gmax = sharded.reduce_bins_and_max(torch.from_numpy(buf), K, dist.group.WORLD)
+            assert gmax == mx, (gmax, mx)
+            res[name + "_onepass"] = counts[: gmax + 1].copy() if gmax < K else np.zeros(0, np.uint64)
         else:
             nb = sharded.alphabet_bins(method, f)
             local = np.zeros(nb, dtype=np.int64)
@@ -86,3 +95,7 @@ def test_two_rank_global_model_equals_reference(tmp_path):
         assert np.array_equal(r0[name + "_nfreqs"], g["nfreqs"]), "global model differs from the reference's"
         assert int(r0[name + "_total"][0]) == g["data"].size
         assert r0[name + "_range"][1] == r1[name + "_range"][0] and r1[name + "_range"][1] == g["data"].size
+    # plain ANS, one pass + one all-reduce: the same global counts on both ranks, equal to a histogram of the whole input
+    g = np.load(os.path.join(HERE, "golden", "int_geom.npz"))
+    want = np.bincount(g["data"]).astype(np.uint64)
+    assert np.array_equal(r0["int_geom_onepass"], want) and np.array_equal(r1["int_geom_onepass"], want)
