@@ -86,6 +86,7 @@ struct b200ans_ctx {
     std::vector<uint8_t> front; // container front of the encode in flight (must outlive its H2D copy)
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
     int kernel_path = B200ANS_PATH_AUTO;
+    bool dec_fold_rank = false;     // folded decoder model with a rank/select index next to its (large) slot table
     bool dec_words_aligned = false; // the decode in flight reads container blocks: payloads start 16-byte aligned
     uint32_t h_approx = 1; // adjust_freqs' H_approx (ANSsint<H> / ANSsmsb<H>)
     uint32_t max_nfreq = 0; // largest normalised frequency of the encoder model
@@ -831,8 +832,9 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
         return c->fail(B200ANS_E_FORMAT, "model_load: frequencies do not sum to a power of two");
     const uint32_t lg = uint32_t(63 - __builtin_clzll(frame));
 
-    if (method == METHOD_INT) {
-        // rank/select index over the frame (kernels.cuh RankRec / RankEntry)
+    // rank/select index over the frame (kernels.cuh RankRec / RankEntry); `word(s)` is what the kernels get back for
+    // present symbol s: its id (plain ANS) or the slot table's packed word (folded coders with a large frame)
+    auto upload_rank = [&](auto&& word) -> int {
         const size_t words = (size_t(frame) + 31) / 32;
         std::vector<RankRec> rec(align_up(words, 2), RankRec { 0u, 0u });
         std::vector<RankEntry> ent;
@@ -843,7 +845,7 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
                 continue;
             rec[base >> 5].bits |= 1u << (base & 31);
             ent.push_back(RankEntry { uint32_t(base), nfreqs[s] });
-            ids.push_back(uint32_t(s));
+            ids.push_back(word(uint32_t(s)));
             base += nfreqs[s];
         }
         uint32_t run = 0;
@@ -860,28 +862,43 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
         CU(c, cudaMemcpyAsync(c->dec_ent.p, ent.data(), ent.size() * sizeof(RankEntry), cudaMemcpyHostToDevice, c->stream));
         // (pageable sources are staged before cudaMemcpyAsync returns: no synchronisation needed for the locals)
         c->dec_n_present = uint32_t(ids.size());
-        c->dec_dense = ids.size() == nfreqs.size() ? 1u : 0u;
+        return B200ANS_OK;
+    };
+    c->dec_fold_rank = false;
+    if (method == METHOD_INT) {
+        RET(upload_rank([](uint32_t s) { return s; }));
+        c->dec_dense = c->dec_n_present == nfreqs.size() ? 1u : 0u;
     } else {
+        auto packed = [&](uint32_t s) { // the slot table's word for symbol s: unfolded base value | raw bytes << 30
+            uint32_t k = 0, value;
+            if (method == METHOD_MSB)
+                value = msb_unmap(s, k);
+            else if (method == METHOD_RFOLD && s < thres)
+                value = most_frequent[s] + thres; // ans_reorder_fold.hpp:214-215
+            else
+                value = fold_unmap(s, f, k);
+            return value + (k << 30);
+        };
         std::vector<DecEntry> slots(frame);
         uint64_t base = 0;
         for (size_t s = 0; s < nfreqs.size(); s++) {
             const uint32_t fr = nfreqs[s];
             if (fr > 65535)
                 return c->fail(B200ANS_E_FORMAT, "model_load: folded model with a frequency above 16 bits");
-            uint32_t k = 0, value;
-            if (method == METHOD_MSB)
-                value = msb_unmap(uint32_t(s), k);
-            else if (method == METHOD_RFOLD && s < thres)
-                value = most_frequent[s] + thres; // ans_reorder_fold.hpp:214-215
-            else
-                value = fold_unmap(uint32_t(s), f, k);
-            const uint32_t mapped = value + (k << 30);
+            const uint32_t mapped = packed(uint32_t(s));
             for (uint32_t j = 0; j < fr; j++)
                 slots[base + j] = DecEntry { uint16_t(fr), uint16_t(j), mapped };
             base += fr;
         }
         CU(c, c->dec_slots.reserve(slots.size() * sizeof(DecEntry)));
         CU(c, cudaMemcpyAsync(c->dec_slots.p, slots.data(), slots.size() * sizeof(DecEntry), cudaMemcpyHostToDevice, c->stream));
+        // A frame beyond 2^14 slots (the 8-byte slot table no longer fits next to the decoder's rings in shared memory;
+        // M = 2^18 once the input reaches 2^32 symbols) also gets the rank/select index, which does: M / 4 + 12 sigma bytes.
+        if (frame * sizeof(DecEntry) > (size_t(128) << 10) && frame <= (uint64_t(1) << 21)) {
+            RET(upload_rank(packed));
+            c->dec_dense = 0;
+            c->dec_fold_rank = true;
+        }
     }
     c->dec_method = method;
     c->dec_f = f;
@@ -1215,6 +1232,16 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
         }
         const size_t tb = align_up(frame * sizeof(DecEntry), 16);
         const bool smem = tb <= std::min<size_t>(lbudget, size_t(128) << 10);
+        if (!smem && c->dec_fold_rank && !env_int("B200ANS_NO_FOLD_RANK", 0)) {
+            const size_t rb = DecTables<METHOD_FOLD, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, 0);
+            if (rb <= std::min<size_t>(lbudget, size_t(100) << 10)) {
+                switch (c->dec_method) {
+                case METHOD_FOLD: return launch_lpb_decode_tt<METHOD_FOLD, DEC_INT_SMEM>(c, a, rb);
+                case METHOD_MSB: return launch_lpb_decode_tt<METHOD_MSB, DEC_INT_SMEM>(c, a, rb);
+                case METHOD_RFOLD: return launch_lpb_decode_tt<METHOD_RFOLD, DEC_INT_SMEM>(c, a, rb);
+                }
+            }
+        }
         switch (c->dec_method) {
         case METHOD_FOLD:
             return smem ? launch_lpb_decode_tt<METHOD_FOLD, DEC_FOLD_SMEM>(c, a, tb)
@@ -1239,6 +1266,16 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     }
     const size_t tb = align_up(frame * sizeof(DecEntry), 16);
     const bool smem = tb <= std::min<size_t>(budget, size_t(128) << 10);
+    if (!smem && c->dec_fold_rank && !env_int("B200ANS_NO_FOLD_RANK", 0)) {
+        const size_t rb = DecTables<METHOD_FOLD, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, 0);
+        if (rb <= std::min<size_t>(budget, size_t(100) << 10)) {
+            switch (c->dec_method) {
+            case METHOD_FOLD: return launch_decode_tt<METHOD_FOLD, DEC_INT_SMEM>(c, a, rb);
+            case METHOD_MSB: return launch_decode_tt<METHOD_MSB, DEC_INT_SMEM>(c, a, rb);
+            case METHOD_RFOLD: return launch_decode_tt<METHOD_RFOLD, DEC_INT_SMEM>(c, a, rb);
+            }
+        }
+    }
     switch (c->dec_method) {
     case METHOD_FOLD:
         return smem ? launch_decode_tt<METHOD_FOLD, DEC_FOLD_SMEM>(c, a, tb)

@@ -112,8 +112,12 @@ struct DecArgs {
 enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3 };
 
 // Decoder tables as the kernels see them: global pointers, or a copy in shared memory.
+// The rank/select layouts (DEC_INT_*) also serve the FOLDED coders when their frame is too large for an M-entry slot
+// table in shared memory (M = 2^18 for a 2^32-symbol input: adjust_freqs keeps doubling until the largest frequency
+// nears 16 bits): `sym` then holds, per present symbol, the slot table's packed word (unfolded base value | k << 30).
 template <int METHOD, int TABLE> struct DecTables {
-    static constexpr bool kInt = (METHOD == METHOD_INT);
+    static constexpr bool kInt = (TABLE == DEC_INT_SMEM || TABLE == DEC_INT_GLOBAL); // rank/select lookup
+    static constexpr bool kPacked = kInt && METHOD != METHOD_INT;                    // sym[] = value | k << 30
     static constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM);
     const DecEntry* slots;
     const RankRec* rec;
@@ -158,7 +162,7 @@ template <int METHOD, int TABLE> struct DecTables {
                 d1[i] = __ldg(s1 + i);
             rec = reinterpret_cast<const RankRec*>(smem);
             ent = reinterpret_cast<const RankEntry*>(smem + rec_b);
-            if (!a.dense) {
+            if (kPacked || !a.dense) {
                 uint32_t* d2 = reinterpret_cast<uint32_t*>(smem + rec_b + ent_b);
                 for (size_t i = threadIdx.x; i < a.n_present; i += blockDim.x)
                     d2[i] = __ldg(a.rank_sym + i);
@@ -180,6 +184,8 @@ template <int METHOD, int TABLE> struct DecTables {
     {
         if (kInt) {
             lookup(slot, freq, offset, raw, k);
+            if (kPacked)
+                raw |= k << 30;
         } else {
             const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(slots + slot) : __ldg(reinterpret_cast<const uint2*>(slots + slot));
             freq = e.x & 0xFFFFu;
@@ -200,9 +206,13 @@ template <int METHOD, int TABLE> struct DecTables {
             freq = e.y;
             offset = slot - e.x;
             mapped = r;
-            if (!dense)
+            if (kPacked || !dense)
                 mapped = kSmem ? sym[r] : __ldg(sym + r);
             k = 0;
+            if (kPacked) {
+                k = mapped >> 30;
+                mapped &= 0x3FFFFFFFu;
+            }
         } else {
             const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(slots + slot) : __ldg(reinterpret_cast<const uint2*>(slots + slot));
             freq = e.x & 0xFFFFu;

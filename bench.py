@@ -472,6 +472,16 @@ def run_ours(args, wl):
         roofline = {"bound": "hbm", "kernel": dom + "_kernel", "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
                     "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
                     "algorithmic_bytes_per_symbol": alg[dom] / n, "ms_per_launch": per[dom]}
+        # DRAM bytes of that kernel from the committed `ncu --set full` capture of this workload (tools/ncu_traffic.py)
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+                tr = json.load(fh).get(args.workload, {}).get(dom)
+            if tr and not args.symbols:
+                roofline["traffic"] = tr["dram_bytes_per_launch"]
+                roofline["traffic_source"] = f"ncu dram__bytes_read.sum + dram__bytes_write.sum, {tr['kernel']}, profiles/ ({tr['source']})"
+                roofline["traffic_over_algorithmic"] = tr["dram_bytes_per_launch"] / alg[dom]
+        except (OSError, ValueError, KeyError):
+            pass
         # CPU baseline on a bounded sample of the same workload (rank 0, N = 1 only)
         cpu = None
         bps_sample = None

@@ -216,3 +216,40 @@ def test_large_roundtrip_properties(codec, method, f, kind, path):
         assert np.array_equal(c["blocks"][b], want)
     whole = cpu().compress(method, f, data).size
     assert blob.size <= whole * 1.01, (blob.size, whole)
+
+
+@pytest.mark.parametrize("method,f", [(M_FOLD, 1), (M_FOLD, 2), (M_MSB, 0)])
+def test_folded_decoder_with_a_large_frame(codec, monkeypatch, method, f):
+    """A rank of a multi-GPU job codes its shard with the GLOBAL model; once the job reaches 2^32 symbols adjust_freqs
+    keeps doubling the frame until a frequency nears 16 bits (M = 2^17 .. 2^19), and the 8-byte slot table no longer
+    fits in shared memory.  The decoder then runs on the rank/select index: same symbols as with the slot table in
+    global memory, on both kernel families, and the model must be the reference's for that histogram."""
+    import torch
+
+    import ans_large_alphabet_b200 as P
+
+    host = P.host_api()
+    n = 300_007
+    data = _inputs.make("zipf20", n, seed=9)
+    nbins = 1280 if method == M_MSB else 1 << (f + 9)
+    bins = np.zeros(nbins, dtype=np.uint64)
+    vals, cnts = np.unique(data, return_counts=True)
+    for v, c in zip(vals, cnts):
+        s = host.msb_map(int(v))[0] if method == M_MSB else host.fold_map(f, int(v))[0]
+        bins[s] += np.uint64(c)
+    bins *= np.uint64(1 << 15)  # the same shape, 9.8e9 symbols in total
+    largest = int(np.nonzero(bins)[0][-1])
+    want_nf = cpu().adjust_freqs(bins[: largest + 1], largest, True)
+    codec.model_build(method, f, bins[: largest + 1])
+    frame, nf = codec.model_nfreqs()
+    assert np.array_equal(nf, want_nf) and frame == int(want_nf.sum()) and frame >= 1 << 15, frame
+    d_in = torch.from_numpy(data.view(np.int32)).cuda()
+    d_blob = torch.empty((codec.bound(method, n) + 15) // 16 * 16, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    nb = codec.encode_device(d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
+    blob = d_blob[:nb].cpu().numpy()
+    for path in (1, 2):
+        codec.set_kernel_path(path)
+        for no_rank in ("0", "1"):
+            monkeypatch.setenv("B200ANS_NO_FOLD_RANK", no_rank)
+            assert np.array_equal(codec.decompress(method, f, blob, n), data), (path, no_rank)
