@@ -86,6 +86,7 @@ struct b200ans_ctx {
     std::vector<uint8_t> front; // container front of the encode in flight (must outlive its H2D copy)
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
     int kernel_path = B200ANS_PATH_AUTO;
+    bool dec_have_pure = false;     // dec_bits_pure holds the rank records with whole-group answers (DEC_INT_SMEM_PURE)
     bool dec_fold_rank = false;     // folded decoder model with a rank/select index next to its (large) slot table
     bool dec_words_aligned = false; // the decode in flight reads container blocks: payloads start 16-byte aligned
     uint32_t h_approx = 1; // adjust_freqs' H_approx (ANSsint<H> / ANSsmsb<H>)
@@ -99,7 +100,7 @@ struct b200ans_ctx {
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre, pa_keys;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre, pa_keys;
     uint32_t pa_undecided = 0;    // models of the last pa_compress the device normaliser handed to the host
     uint8_t* pa_pinned = nullptr; // pseudo-adaptive mode: counts / frequencies of all models (pinned, grows on demand)
     size_t pa_pinned_cap = 0;
@@ -275,7 +276,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_bits, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys })
+             &c->dec_slots, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys })
         b->release();
     for (auto& e : c->ev)
         if (e)
@@ -862,6 +863,21 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
         CU(c, cudaMemcpyAsync(c->dec_ent.p, ent.data(), ent.size() * sizeof(RankEntry), cudaMemcpyHostToDevice, c->stream));
         // (pageable sources are staged before cudaMemcpyAsync returns: no synchronisation needed for the locals)
         c->dec_n_present = uint32_t(ids.size());
+        // the same records with whole-group answers (kernels.cuh DEC_INT_SMEM_PURE)
+        c->dec_have_pure = false;
+        if (frame <= (uint64_t(1) << 19) && ids.size() < (size_t(1) << 23) && frame * 8 / 32 <= (size_t(100) << 10)) {
+            std::vector<RankRec> pure(rec);
+            for (size_t w = 0; w < words; w++) {
+                if (rec[w].bits & ~1u)
+                    continue; // a symbol starts inside the group
+                const uint32_t r = rec[w].cnt + (rec[w].bits & 1u) - 1u; // the symbol that holds slot 32 w
+                pure[w].bits = ent[r].base | ((r & 0xFFFu) << 20);
+                pure[w].cnt = kRankPureFlag | ((r >> 12) << 20) | ent[r].freq;
+            }
+            CU(c, c->dec_bits_pure.reserve(pure.size() * sizeof(RankRec)));
+            CU(c, cudaMemcpyAsync(c->dec_bits_pure.p, pure.data(), pure.size() * sizeof(RankRec), cudaMemcpyHostToDevice, c->stream));
+            c->dec_have_pure = true;
+        }
         return B200ANS_OK;
     };
     c->dec_fold_rank = false;
@@ -1013,6 +1029,25 @@ template <int METHOD, int TABLE> int launch_lpb_decode_tt(b200ans_ctx* c, const 
         return launch_lpb(c, lpb3_decode_kernel<METHOD, TABLE, 1, 28>, tb + 128, L3DecGeom<1>::kWarpBytes, a.n_blocks, &a, 28);
     }
     return launch_lpb(c, lpb_decode_kernel<METHOD, TABLE>, align_up(table_bytes, 16), kLpbDecWarpBytes, a.n_blocks, &a);
+}
+
+// rank/select records with whole-group answers: worth it where the decoder is bound by shared-memory wavefronts, i.e.
+// from about two rounds of tasks per SM upwards (below that the kernel waits on latency and the extra selects cost)
+template <int METHOD> int launch_lpb3_decode_pure(b200ans_ctx* c, DecArgs a, size_t table_bytes)
+{
+    a.rank_rec = c->dec_bits_pure.as<RankRec>();
+    const size_t tb = align_up(table_bytes, 16);
+    return launch_lpb(c, lpb3_decode_kernel<METHOD, DEC_INT_SMEM_PURE, 2, 16>, tb + 256, L3DecGeom<2>::kWarpBytes, a.n_blocks, &a, 16);
+}
+
+bool use_pure_records(const b200ans_ctx* c, const DecArgs& a)
+{
+    const int mode = env_int("B200ANS_PURE", -1); // 0 / 1 force, default by size
+    if (!c->dec_have_pure || mode == 0 || env_int("B200ANS_NO_L3", 0) || env_int("B200ANS_L3_DEC", 0))
+        return false;
+    if ((reinterpret_cast<uintptr_t>(a.out) & 31) != 0 || a.block_syms % 8u != 0u)
+        return false;
+    return mode == 1 || a.n_blocks >= uint32_t(c->num_sms) * 448u;
 }
 
 // ---- L3 encoder (lpb3_kernels.cuh): TMA input tiles + replicated shared-memory table ---------
@@ -1227,7 +1262,7 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
         if (c->dec_method == METHOD_INT) {
             const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_dense);
             if (tb <= std::min<size_t>(lbudget, size_t(100) << 10))
-                return launch_lpb_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
+                return use_pure_records(c, a) ? launch_lpb3_decode_pure<METHOD_INT>(c, a, tb) : launch_lpb_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
             return launch_lpb_decode_tt<METHOD_INT, DEC_INT_GLOBAL>(c, a, 0);
         }
         const size_t tb = align_up(frame * sizeof(DecEntry), 16);
@@ -1235,6 +1270,8 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
         if (!smem && c->dec_fold_rank && !env_int("B200ANS_NO_FOLD_RANK", 0)) {
             const size_t rb = DecTables<METHOD_FOLD, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, 0);
             if (rb <= std::min<size_t>(lbudget, size_t(100) << 10)) {
+                if (c->dec_method == METHOD_FOLD && use_pure_records(c, a))
+                    return launch_lpb3_decode_pure<METHOD_FOLD>(c, a, rb);
                 switch (c->dec_method) {
                 case METHOD_FOLD: return launch_lpb_decode_tt<METHOD_FOLD, DEC_INT_SMEM>(c, a, rb);
                 case METHOD_MSB: return launch_lpb_decode_tt<METHOD_MSB, DEC_INT_SMEM>(c, a, rb);

@@ -109,16 +109,24 @@ struct DecArgs {
     uint32_t pa_bucket_log2;  // the bucket index has 2^pa_bucket_log2 entries per model
 };
 
-enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3 };
+enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3, DEC_INT_SMEM_PURE = 4 };
+
+// DEC_INT_SMEM_PURE: the same index, but a 32-slot group that lies inside ONE symbol (no symbol starts at its slots
+// 1..31) carries that symbol's answer in its own record -- x = base | rank<11:0> << 20, y = 1 << 31 | rank<22:12> << 20 |
+// freq -- so only the lanes whose slot falls into a mixed group take the second lookup (geometric(0.01) at M = 2^17:
+// 11 % of them).  The decoder of a large input is bound by shared-memory wavefronts, and a lookup by 3 lanes costs one
+// where a lookup by 32 costs six.  Needs M <= 2^19 and fewer than 2^23 symbols (the host checks).
+constexpr uint32_t kRankPureFlag = 0x80000000u;
 
 // Decoder tables as the kernels see them: global pointers, or a copy in shared memory.
 // The rank/select layouts (DEC_INT_*) also serve the FOLDED coders when their frame is too large for an M-entry slot
 // table in shared memory (M = 2^18 for a 2^32-symbol input: adjust_freqs keeps doubling until the largest frequency
 // nears 16 bits): `sym` then holds, per present symbol, the slot table's packed word (unfolded base value | k << 30).
 template <int METHOD, int TABLE> struct DecTables {
-    static constexpr bool kInt = (TABLE == DEC_INT_SMEM || TABLE == DEC_INT_GLOBAL); // rank/select lookup
-    static constexpr bool kPacked = kInt && METHOD != METHOD_INT;                    // sym[] = value | k << 30
-    static constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM);
+    static constexpr bool kPure = (TABLE == DEC_INT_SMEM_PURE);
+    static constexpr bool kInt = (TABLE == DEC_INT_SMEM || TABLE == DEC_INT_GLOBAL || kPure); // rank/select lookup
+    static constexpr bool kPacked = kInt && METHOD != METHOD_INT;                             // sym[] = value | k << 30
+    static constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM || kPure);
     const DecEntry* slots;
     const RankRec* rec;
     const uint32_t* sym;
@@ -201,8 +209,18 @@ template <int METHOD, int TABLE> struct DecTables {
         if (kInt) {
             const uint32_t w = slot >> 5;
             const uint2 rc = kSmem ? *reinterpret_cast<const uint2*>(rec + w) : __ldg(reinterpret_cast<const uint2*>(rec + w));
-            const uint32_t r = rc.y + uint32_t(__popc(rc.x & (0xFFFFFFFFu >> (31u - (slot & 31u))))) - 1u;
-            const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(ent + r) : __ldg(reinterpret_cast<const uint2*>(ent + r));
+            uint32_t r = rc.y + uint32_t(__popc(rc.x & (0xFFFFFFFFu >> (31u - (slot & 31u))))) - 1u;
+            uint2 e;
+            if (kPure) {
+                const bool pure = int32_t(rc.y) < 0;
+                if (pure)
+                    r = (rc.x >> 20) | ((rc.y >> 8) & 0x7FF000u);
+                e = make_uint2(rc.x & 0xFFFFFu, rc.y & 0xFFFFFu);
+                if (!pure)
+                    e = *reinterpret_cast<const uint2*>(ent + r);
+            } else {
+                e = kSmem ? *reinterpret_cast<const uint2*>(ent + r) : __ldg(reinterpret_cast<const uint2*>(ent + r));
+            }
             freq = e.y;
             offset = slot - e.x;
             mapped = r;

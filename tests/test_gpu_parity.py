@@ -252,4 +252,26 @@ def test_folded_decoder_with_a_large_frame(codec, monkeypatch, method, f):
         codec.set_kernel_path(path)
         for no_rank in ("0", "1"):
             monkeypatch.setenv("B200ANS_NO_FOLD_RANK", no_rank)
-            assert np.array_equal(codec.decompress(method, f, blob, n), data), (path, no_rank)
+            for pure in ("0", "1"):  # rank records with whole-group answers (ANSfold only; others ignore the switch)
+                monkeypatch.setenv("B200ANS_PURE", pure)
+                assert np.array_equal(codec.decompress(method, f, blob, n), data), (path, no_rank, pure)
+
+
+@pytest.mark.parametrize("kind", ["geom", "gaps", "skewed"])
+def test_plain_ans_rank_records_with_whole_group_answers(codec, monkeypatch, kind):
+    """DEC_INT_SMEM_PURE (large inputs take it by themselves): groups of 32 frame slots inside one symbol answer from
+    their own record.  Dense and sparse alphabets, a dominant symbol, ragged last block; same symbols as without."""
+    rng = np.random.default_rng(3)
+    n = 1_000_003
+    if kind == "geom":
+        data = _inputs.make("geom", n, seed=4)
+    elif kind == "gaps":
+        data = (_inputs.make("geom", n, seed=5) * 3 + 1).astype(np.uint32)  # two of three ids never occur
+    else:
+        data = rng.integers(0, 3000, size=n, dtype=np.uint32)
+        data[rng.random(n) < 0.9] = 17
+    codec.set_kernel_path(2)
+    blob = codec.compress(M_INT, 0, data).copy()
+    for pure in ("0", "1"):
+        monkeypatch.setenv("B200ANS_PURE", pure)
+        assert np.array_equal(codec.decompress(M_INT, 0, blob, n), data), pure
