@@ -1327,6 +1327,21 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     return c->fail(B200ANS_E_STATE, "decode: no model");
 }
 
+// the two side streams (copy-in / copy-out of the host-buffer decode pipeline; the first also runs the pseudo-adaptive
+// prelude coder next to the encoder) and their events, created on first use
+int ensure_side_streams(b200ans_ctx* c)
+{
+    if (c->copy_in)
+        return B200ANS_OK;
+    CU(c, cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking));
+    CU(c, cudaStreamCreateWithFlags(&c->copy_out, cudaStreamNonBlocking));
+    for (auto& e : c->ev_in)
+        CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : c->ev_dec)
+        CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    return B200ANS_OK;
+}
+
 // one asynchronous read of the device control block (maximum, error flag, scan totals) + one synchronisation
 int read_small(b200ans_ctx* c)
 {
@@ -1781,14 +1796,7 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
             return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
     }
 
-    if (!c->copy_in) {
-        CU(c, cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking));
-        CU(c, cudaStreamCreateWithFlags(&c->copy_out, cudaStreamNonBlocking));
-        for (auto& e : c->ev_in)
-            CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        for (auto& e : c->ev_dec)
-            CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    }
+    RET(ensure_side_streams(c));
     CU(c, c->io_out.reserve(src_bytes + 64));
     CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
     CU(c, c->offsets.reserve(size_t(nb) * 8));
@@ -2074,21 +2082,25 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     c->pa_undecided = undecided;
     const float ms_host = float(now_ms() - t0);
 
-    // preludes on the device (the counts are no longer needed: their buffer is the coder's scratch), then their
-    // sizes are scanned; the total comes back while the encoder runs
+    // Preludes on the device (the counts are no longer needed: their buffer is the coder's scratch), then their sizes
+    // are scanned.  The prelude coder is one thread per model (a serial bit stream each: 3.5 warps per SM for 16 384
+    // models) and needs only the frequencies, as the encoder does: it runs NEXT TO the encoder on a side stream, and
+    // its total comes back while the encoder runs.
+    RET(ensure_side_streams(c));
     CU(c, cudaEventRecord(c->ev[6], c->stream));
+    CU(c, cudaStreamWaitEvent(c->copy_in, c->ev[6], 0));
     const uint32_t pre_stride = uint32_t(align_up(size_t(nbins) * 4 + 64, 16));
     CU(c, c->pa_pre.reserve(size_t(nm) * pre_stride + size_t(nm) * 12));
     uint8_t* d_pre = c->pa_pre.as<uint8_t>();
     uint64_t* d_pre_off = reinterpret_cast<uint64_t*>(d_pre + size_t(nm) * pre_stride);
     uint32_t* d_pre_bytes = reinterpret_cast<uint32_t*>(d_pre_off + nm);
-    pa_prelude_encode_kernel<<<(nm + kPaPreThreads - 1) / kPaPreThreads, kPaPreThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm,
+    pa_prelude_encode_kernel<<<(nm + kPaPreThreads - 1) / kPaPreThreads, kPaPreThreads, 0, c->copy_in>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm,
         d_lg, c->bins.as<uint32_t>(), d_pre, pre_stride, d_pre_bytes);
-    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
+    scan_block_sizes_kernel<<<1, 1024, 0, c->copy_in>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
     c->stats.launches += 2;
     CU(c, cudaGetLastError());
-    CU(c, cudaMemcpyAsync(c->h_small(), c->small.p, sizeof(b200ans_ctx::SmallHost), cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaEventRecord(c->ev[7], c->stream));
+    CU(c, cudaMemcpyAsync(c->h_small(), c->small.p, sizeof(b200ans_ctx::SmallHost), cudaMemcpyDeviceToHost, c->copy_in));
+    CU(c, cudaEventRecord(c->ev[7], c->copy_in));
 
     // frequencies -> one reference-format stream per model block.  Tables: built per block in shared memory by the
     // coder itself (pa_kernels.cuh) when every frame is at most 2^16, else one 16-byte entry per symbol and model in
@@ -2151,6 +2163,7 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
 
     // the prelude total is on the host by now (the encoder is still running): lay the container out
     CU(c, cudaEventSynchronize(c->ev[7]));
+    CU(c, cudaStreamWaitEvent(c->stream, c->ev[7], 0)); // the compaction below reads what the side stream wrote
     const size_t pre_region = c->h_small()->totals_b[0];
     const size_t payload_at = pre_at + pre_region;
     if (pre_region > 0xFFFFFFF0ull)
