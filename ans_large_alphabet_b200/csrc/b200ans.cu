@@ -87,7 +87,7 @@ struct b200ans_ctx {
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
     int kernel_path = B200ANS_PATH_AUTO;
     bool dec_have_pure = false;     // dec_bits_pure holds the rank records with whole-group answers (DEC_INT_SMEM_PURE)
-    bool dec_fold_rank = false;     // folded decoder model with a rank/select index next to its (large) slot table
+    bool dec_fold_rank = false;     // folded decoder model with a large frame: rank/select index, no slot table
     bool dec_words_aligned = false; // the decode in flight reads container blocks: payloads start 16-byte aligned
     uint32_t h_approx = 1; // adjust_freqs' H_approx (ANSsint<H> / ANSsmsb<H>)
     uint32_t max_nfreq = 0; // largest normalised frequency of the encoder model
@@ -865,7 +865,7 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
         c->dec_n_present = uint32_t(ids.size());
         // the same records with whole-group answers (kernels.cuh DEC_INT_SMEM_PURE)
         c->dec_have_pure = false;
-        if (frame <= (uint64_t(1) << 19) && ids.size() < (size_t(1) << 23) && frame * 8 / 32 <= (size_t(100) << 10)) {
+        if (frame <= (uint64_t(1) << 19) && ids.size() < (size_t(1) << 23)) {
             std::vector<RankRec> pure(rec);
             for (size_t w = 0; w < words; w++) {
                 if (rec[w].bits & ~1u)
@@ -895,25 +895,28 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
                 value = fold_unmap(s, f, k);
             return value + (k << 30);
         };
-        std::vector<DecEntry> slots(frame);
-        uint64_t base = 0;
-        for (size_t s = 0; s < nfreqs.size(); s++) {
-            const uint32_t fr = nfreqs[s];
+        for (uint32_t fr : nfreqs)
             if (fr > 65535)
                 return c->fail(B200ANS_E_FORMAT, "model_load: folded model with a frequency above 16 bits");
-            const uint32_t mapped = packed(uint32_t(s));
-            for (uint32_t j = 0; j < fr; j++)
-                slots[base + j] = DecEntry { uint16_t(fr), uint16_t(j), mapped };
-            base += fr;
-        }
-        CU(c, c->dec_slots.reserve(slots.size() * sizeof(DecEntry)));
-        CU(c, cudaMemcpyAsync(c->dec_slots.p, slots.data(), slots.size() * sizeof(DecEntry), cudaMemcpyHostToDevice, c->stream));
-        // A frame beyond 2^14 slots (the 8-byte slot table no longer fits next to the decoder's rings in shared memory;
-        // M = 2^18 once the input reaches 2^32 symbols) also gets the rank/select index, which does: M / 4 + 12 sigma bytes.
-        if (frame * sizeof(DecEntry) > (size_t(128) << 10) && frame <= (uint64_t(1) << 21)) {
+        if (frame * sizeof(DecEntry) > (size_t(128) << 10)) {
+            // A frame beyond 2^14 slots: the 8-byte slot table no longer fits next to the decoder's rings in shared
+            // memory (M = 2^18 .. 2^19 once the job reaches 2^32 symbols: 2 .. 4 MB to build here, upload and gather
+            // from L2 per symbol).  Such models get the rank/select index instead: M / 4 + 12 sigma bytes.
             RET(upload_rank(packed));
             c->dec_dense = 0;
             c->dec_fold_rank = true;
+        } else {
+            std::vector<DecEntry> slots(frame);
+            uint64_t base = 0;
+            for (size_t s = 0; s < nfreqs.size(); s++) {
+                const uint32_t fr = nfreqs[s];
+                const uint32_t mapped = packed(uint32_t(s));
+                for (uint32_t j = 0; j < fr; j++)
+                    slots[base + j] = DecEntry { uint16_t(fr), uint16_t(j), mapped };
+                base += fr;
+            }
+            CU(c, c->dec_slots.reserve(slots.size() * sizeof(DecEntry)));
+            CU(c, cudaMemcpyAsync(c->dec_slots.p, slots.data(), slots.size() * sizeof(DecEntry), cudaMemcpyHostToDevice, c->stream));
         }
     }
     c->dec_method = method;
@@ -1267,9 +1270,10 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
         }
         const size_t tb = align_up(frame * sizeof(DecEntry), 16);
         const bool smem = tb <= std::min<size_t>(lbudget, size_t(128) << 10);
-        if (!smem && c->dec_fold_rank && !env_int("B200ANS_NO_FOLD_RANK", 0)) {
+        if (c->dec_fold_rank) { // large frame: rank/select index in shared memory (fewer warps if need be), else in L2
             const size_t rb = DecTables<METHOD_FOLD, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, 0);
-            if (rb <= std::min<size_t>(lbudget, size_t(100) << 10)) {
+            const size_t room = c->max_smem > size_t(4) * L3DecGeom<2>::kWarpBytes + 4096 ? c->max_smem - size_t(4) * L3DecGeom<2>::kWarpBytes - 4096 : 0;
+            if (rb <= room && !env_int("B200ANS_RANK_GLOBAL", 0)) {
                 if (c->dec_method == METHOD_FOLD && use_pure_records(c, a))
                     return launch_lpb3_decode_pure<METHOD_FOLD>(c, a, rb);
                 switch (c->dec_method) {
@@ -1277,6 +1281,11 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
                 case METHOD_MSB: return launch_lpb_decode_tt<METHOD_MSB, DEC_INT_SMEM>(c, a, rb);
                 case METHOD_RFOLD: return launch_lpb_decode_tt<METHOD_RFOLD, DEC_INT_SMEM>(c, a, rb);
                 }
+            }
+            switch (c->dec_method) {
+            case METHOD_FOLD: return launch_lpb_decode_tt<METHOD_FOLD, DEC_INT_GLOBAL>(c, a, 0);
+            case METHOD_MSB: return launch_lpb_decode_tt<METHOD_MSB, DEC_INT_GLOBAL>(c, a, 0);
+            case METHOD_RFOLD: return launch_lpb_decode_tt<METHOD_RFOLD, DEC_INT_GLOBAL>(c, a, 0);
             }
         }
         switch (c->dec_method) {
@@ -1303,14 +1312,19 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     }
     const size_t tb = align_up(frame * sizeof(DecEntry), 16);
     const bool smem = tb <= std::min<size_t>(budget, size_t(128) << 10);
-    if (!smem && c->dec_fold_rank && !env_int("B200ANS_NO_FOLD_RANK", 0)) {
+    if (c->dec_fold_rank) {
         const size_t rb = DecTables<METHOD_FOLD, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, 0);
-        if (rb <= std::min<size_t>(budget, size_t(100) << 10)) {
+        if (rb <= budget && !env_int("B200ANS_RANK_GLOBAL", 0)) {
             switch (c->dec_method) {
             case METHOD_FOLD: return launch_decode_tt<METHOD_FOLD, DEC_INT_SMEM>(c, a, rb);
             case METHOD_MSB: return launch_decode_tt<METHOD_MSB, DEC_INT_SMEM>(c, a, rb);
             case METHOD_RFOLD: return launch_decode_tt<METHOD_RFOLD, DEC_INT_SMEM>(c, a, rb);
             }
+        }
+        switch (c->dec_method) {
+        case METHOD_FOLD: return launch_decode_tt<METHOD_FOLD, DEC_INT_GLOBAL>(c, a, 0);
+        case METHOD_MSB: return launch_decode_tt<METHOD_MSB, DEC_INT_GLOBAL>(c, a, 0);
+        case METHOD_RFOLD: return launch_decode_tt<METHOD_RFOLD, DEC_INT_GLOBAL>(c, a, 0);
         }
     }
     switch (c->dec_method) {

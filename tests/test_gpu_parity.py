@@ -222,8 +222,8 @@ def test_large_roundtrip_properties(codec, method, f, kind, path):
 def test_folded_decoder_with_a_large_frame(codec, monkeypatch, method, f):
     """A rank of a multi-GPU job codes its shard with the GLOBAL model; once the job reaches 2^32 symbols adjust_freqs
     keeps doubling the frame until a frequency nears 16 bits (M = 2^17 .. 2^19), and the 8-byte slot table no longer
-    fits in shared memory.  The decoder then runs on the rank/select index: same symbols as with the slot table in
-    global memory, on both kernel families, and the model must be the reference's for that histogram."""
+    fits in shared memory.  The decoder then runs on the rank/select index (no slot table is built at all), from shared
+    or from global memory, on both kernel families; the model must be the reference's for that histogram."""
     import torch
 
     import ans_large_alphabet_b200 as P
@@ -250,8 +250,8 @@ def test_folded_decoder_with_a_large_frame(codec, monkeypatch, method, f):
     blob = d_blob[:nb].cpu().numpy()
     for path in (1, 2):
         codec.set_kernel_path(path)
-        for no_rank in ("0", "1"):
-            monkeypatch.setenv("B200ANS_NO_FOLD_RANK", no_rank)
+        for no_rank in ("0", "1"):  # the index in shared memory / in global memory (frames whose index does not fit)
+            monkeypatch.setenv("B200ANS_RANK_GLOBAL", no_rank)
             for pure in ("0", "1"):  # rank records with whole-group answers (ANSfold only; others ignore the switch)
                 monkeypatch.setenv("B200ANS_PURE", pure)
                 assert np.array_equal(codec.decompress(method, f, blob, n), data), (path, no_rank, pure)
