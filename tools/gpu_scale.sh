@@ -2,7 +2,7 @@
 # N-GPU bench lines (weak scaling): usage gpu_scale.sh N tag
 N=${1:-8}; tag=${2:-scale}; out=gpurun_out/$tag; mkdir -p $out
 port=29600
-for wl in c2 fold1 c4 c5; do
+for wl in ${WLS:-c2 fold1 c4 c5}; do
   port=$((port+1))
   extra="--no-targets --no-cpu"; [ $wl = c2 ] && extra="--no-targets"
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $port bench.py --gpus $N --steps 10 --warmup 3 --workload $wl $extra > $out/bench_${wl}_n$N.json 2> $out/bench_${wl}_n$N.err; echo "$wl N=$N exit $?"
