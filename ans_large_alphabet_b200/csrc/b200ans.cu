@@ -87,6 +87,10 @@ struct b200ans_ctx {
     uint32_t block_syms = B200ANS_DEFAULT_BLOCK_SYMS;
     int kernel_path = B200ANS_PATH_AUTO;
     bool dec_have_pure = false;     // dec_bits_pure holds the rank records with whole-group answers (DEC_INT_SMEM_PURE)
+    bool dec_pure_possible = false; // ... or can be built from the host copies below (frame <= 2^19)
+    std::vector<RankRec> h_rank_rec;
+    std::vector<RankEntry> h_rank_ent;
+    size_t h_rank_words = 0;
     bool dec_fold_rank = false;     // folded decoder model with a large frame: rank/select index, no slot table
     bool dec_words_aligned = false; // the decode in flight reads container blocks: payloads start 16-byte aligned
     uint32_t h_approx = 1; // adjust_freqs' H_approx (ANSsint<H> / ANSsmsb<H>)
@@ -863,20 +867,13 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
         CU(c, cudaMemcpyAsync(c->dec_ent.p, ent.data(), ent.size() * sizeof(RankEntry), cudaMemcpyHostToDevice, c->stream));
         // (pageable sources are staged before cudaMemcpyAsync returns: no synchronisation needed for the locals)
         c->dec_n_present = uint32_t(ids.size());
-        // the same records with whole-group answers (kernels.cuh DEC_INT_SMEM_PURE)
+        // the same records with whole-group answers (kernels.cuh DEC_INT_SMEM_PURE) are built when a launch wants them
         c->dec_have_pure = false;
-        if (frame <= (uint64_t(1) << 19) && ids.size() < (size_t(1) << 23)) {
-            std::vector<RankRec> pure(rec);
-            for (size_t w = 0; w < words; w++) {
-                if (rec[w].bits & ~1u)
-                    continue; // a symbol starts inside the group
-                const uint32_t r = rec[w].cnt + (rec[w].bits & 1u) - 1u; // the symbol that holds slot 32 w
-                pure[w].bits = ent[r].base | ((r & 0xFFFu) << 20);
-                pure[w].cnt = kRankPureFlag | ((r >> 12) << 20) | ent[r].freq;
-            }
-            CU(c, c->dec_bits_pure.reserve(pure.size() * sizeof(RankRec)));
-            CU(c, cudaMemcpyAsync(c->dec_bits_pure.p, pure.data(), pure.size() * sizeof(RankRec), cudaMemcpyHostToDevice, c->stream));
-            c->dec_have_pure = true;
+        c->dec_pure_possible = frame <= (uint64_t(1) << 19) && ids.size() < (size_t(1) << 23);
+        if (c->dec_pure_possible) {
+            c->h_rank_rec.swap(rec);
+            c->h_rank_ent.swap(ent);
+            c->h_rank_words = words;
         }
         return B200ANS_OK;
     };
@@ -1038,6 +1035,20 @@ template <int METHOD, int TABLE> int launch_lpb_decode_tt(b200ans_ctx* c, const 
 // from about two rounds of tasks per SM upwards (below that the kernel waits on latency and the extra selects cost)
 template <int METHOD> int launch_lpb3_decode_pure(b200ans_ctx* c, DecArgs a, size_t table_bytes)
 {
+    if (!c->dec_have_pure) { // first large decode with this model: rewrite the records of groups inside one symbol
+        std::vector<RankRec>& pure = c->h_rank_rec;
+        const std::vector<RankEntry>& ent = c->h_rank_ent;
+        for (size_t w = 0; w < c->h_rank_words; w++) {
+            if (pure[w].bits & ~1u)
+                continue; // a symbol starts inside the group
+            const uint32_t r = pure[w].cnt + (pure[w].bits & 1u) - 1u; // the symbol that holds slot 32 w
+            pure[w].bits = ent[r].base | ((r & 0xFFFu) << 20);
+            pure[w].cnt = kRankPureFlag | ((r >> 12) << 20) | ent[r].freq;
+        }
+        CU(c, c->dec_bits_pure.reserve(pure.size() * sizeof(RankRec)));
+        CU(c, cudaMemcpyAsync(c->dec_bits_pure.p, pure.data(), pure.size() * sizeof(RankRec), cudaMemcpyHostToDevice, c->stream));
+        c->dec_have_pure = true;
+    }
     a.rank_rec = c->dec_bits_pure.as<RankRec>();
     const size_t tb = align_up(table_bytes, 16);
     return launch_lpb(c, lpb3_decode_kernel<METHOD, DEC_INT_SMEM_PURE, 2, 16>, tb + 256, L3DecGeom<2>::kWarpBytes, a.n_blocks, &a, 16);
@@ -1046,7 +1057,7 @@ template <int METHOD> int launch_lpb3_decode_pure(b200ans_ctx* c, DecArgs a, siz
 bool use_pure_records(const b200ans_ctx* c, const DecArgs& a)
 {
     const int mode = env_int("B200ANS_PURE", -1); // 0 / 1 force, default by size
-    if (!c->dec_have_pure || mode == 0 || env_int("B200ANS_NO_L3", 0) || env_int("B200ANS_L3_DEC", 0))
+    if (!(c->dec_have_pure || c->dec_pure_possible) || mode == 0 || env_int("B200ANS_NO_L3", 0) || env_int("B200ANS_L3_DEC", 0))
         return false;
     if ((reinterpret_cast<uintptr_t>(a.out) & 31) != 0 || a.block_syms % 8u != 0u)
         return false;

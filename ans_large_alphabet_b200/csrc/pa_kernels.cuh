@@ -20,7 +20,7 @@
 //            arithmetically from the symbol (fold_unmap / msb_unmap), so no M-entry slot table exists at all
 //            (ans_fold.hpp:179-207 builds one; the contents are a pure function of nfreqs, the layout is ours).
 // The steps of a chain are serial and a warp issues in order, so the kernels are bound by latency x resident
-// models (ncu r01e: 6.3 cycles per issued instruction, 0.9 ms per round of tasks whatever the warp count); the
+// models (ncu, first version of these kernels: 6.3 cycles per issued instruction, 0.9 ms per round of tasks whatever the warp count); the
 // tables are this small -- about 1.3 KB (encoder) / 1.9 KB (decoder) per model for a 527-symbol alphabet -- so that
 // all 14 warps (112 models) an SM needs for 2^27 symbols in 8192-symbol blocks are resident at once.
 // Both need log2 M <= 16 (cum fits 16 bits; frequencies are at most 65535 by the 16-bit guard of adjust_freqs,

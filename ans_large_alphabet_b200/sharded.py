@@ -48,7 +48,28 @@ def reduce_histogram(bins, group=None):
     import torch.distributed as dist
 
     _all_reduce(bins, dist.ReduceOp.SUM, group)
+    if bins.is_cuda:  # one asynchronous copy into page-locked memory + one stream synchronisation
+        import torch
+
+        host = _pinned_like(bins)
+        host.copy_(bins, non_blocking=True)
+        torch.cuda.current_stream(bins.device).synchronize()
+        return host.numpy().view(np.uint64).copy()
     return bins.cpu().numpy().view(np.uint64)
+
+
+_PINNED = {}
+
+
+def _pinned_like(t):
+    """page-locked staging tensor of t's shape (cached: a step's histogram has the same shape every time)"""
+    import torch
+
+    key = (tuple(t.shape), t.dtype)
+    buf = _PINNED.get(key)
+    if buf is None:
+        buf = _PINNED[key] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+    return buf
 
 
 def reduce_bins_and_max(buf, opt_bins, group=None):
@@ -94,7 +115,10 @@ def global_histogram(codec, method, f, d_src, n, group=None, sync=None):
         # maximum in its own slot behind the bins (sum of one-hot slots = all-gather).  Only an alphabet beyond
         # OPT_BINS needs the second pass.
         rank = dist.get_rank(group) if world > 1 else 0
-        buf = torch.zeros(OPT_BINS + world, dtype=torch.int64, device=dev)
+        buf = getattr(codec, "_shard_bins", None)  # reused from step to step: one memset instead of an allocation
+        if buf is None or buf.numel() != OPT_BINS + world or buf.device != dev:
+            buf = codec._shard_bins = torch.empty(OPT_BINS + world, dtype=torch.int64, device=dev)
+        buf.zero_()
         sync()
         # the kernel's 32-bit maximum lands in the low half of this rank's (zeroed, little-endian) int64 slot
         codec.histogram_max_device(METHOD_INT, f, d_src.data_ptr(), n, buf.data_ptr(), OPT_BINS,

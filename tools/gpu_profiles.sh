@@ -4,6 +4,7 @@
 tag=${1:-r01e}
 out=gpurun_out/$tag; mkdir -p $out
 K="histogram_kernel|lpb3_encode_kernel|compact_kernel|lpb3_decode_kernel"
+timeout 1500 python -m pytest tests -m gpu -x -q > $out/pytest_gpu.log 2>&1; echo "pytest exit $?"; tail -3 $out/pytest_gpu.log
 timeout 600 python bench.py > $out/bench_c2.json 2> $out/bench_c2.err; echo "bench c2 exit $?"
 for wl in fold1 fold2 ans30 c4 c1 c5; do
   timeout 600 python bench.py --workload $wl --no-targets > $out/bench_$wl.json 2> $out/bench_$wl.err; echo "bench $wl exit $?"
