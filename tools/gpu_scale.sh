@@ -7,7 +7,7 @@ for wl in ${WLS:-c2 fold1 c4 c5}; do
   extra="--no-targets --no-cpu"; [ $wl = c2 ] && extra="--no-targets"
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $port bench.py --gpus $N --steps 10 --warmup 3 --workload $wl $extra > $out/bench_${wl}_n$N.json 2> $out/bench_${wl}_n$N.err; echo "$wl N=$N exit $?"
 done
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29650 bench.py --impl reference --gpus $N --steps 2 --warmup 1 > $out/bench_ref_n$N.json 2> $out/bench_ref_n$N.err; echo "ref N=$N exit $?"
+[ -z "$SKIP_REF" ] && timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29650 bench.py --impl reference --gpus $N --steps 2 --warmup 1 > $out/bench_ref_n$N.json 2> $out/bench_ref_n$N.err; echo "ref N=$N exit $?"
 for f in $out/bench_*_n$N.json; do python - "$f" <<'PY'
 import json,sys
 try:
