@@ -1885,7 +1885,14 @@ extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32
     CU(c, cudaSetDevice(c->device));
     if (c->block_syms != 0 && !env_int("B200ANS_NO_PIPELINE", 0)) {
         c->stats.ms_decode = c->stats.ms_model = 0.f;
-        return decompress_pipelined(c, method, f, dst, n, src, src_bytes);
+        const int rc = decompress_pipelined(c, method, f, dst, n, src, src_bytes);
+        if (rc != B200ANS_OK && c->copy_in) { // nothing of a failed call may still be reading or writing the caller's buffers
+            cudaStreamSynchronize(c->copy_in);
+            cudaStreamSynchronize(c->stream);
+            cudaStreamSynchronize(c->copy_out);
+            cudaGetLastError();
+        }
+        return rc;
     }
     CU(c, c->io_out.reserve(src_bytes + 64));
     CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
