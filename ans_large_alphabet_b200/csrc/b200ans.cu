@@ -2235,20 +2235,26 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
     return B200ANS_OK;
 }
 
-extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, size_t n,
-    const uint8_t* d_src, size_t src_bytes)
+namespace {
+
+// Decoder of a pseudo-adaptive container at d_src (device).  With h_src / h_dst set, the container still sits in host
+// memory and the symbols are wanted there: header and size tables are read from h_src, the payload travels in runs
+// of models on `copy_in` behind the front part (sizes + preludes), every run is decoded as soon as it has arrived and
+// its symbols leave on `copy_out` while the next run is decoded (the same three-stream pipeline as
+// decompress_pipelined).  Without them the container is already in HBM and nothing is copied.
+int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, size_t n, const uint8_t* d_src,
+    size_t src_bytes, const uint8_t* h_src, uint32_t* h_dst)
 {
-    if (!c)
-        return B200ANS_E_ARG;
-    if ((!d_dst && n) || !d_src || (reinterpret_cast<uintptr_t>(d_src) & 15))
-        return c->fail(B200ANS_E_ARG, "pa_decompress: bad argument (d_src must be 16-byte aligned)");
-    CU(c, cudaSetDevice(c->device));
     c->stats.ms_decode = c->stats.ms_model = 0.f;
     if (src_bytes < B200ANS_HEADER_BYTES)
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: shorter than a header");
     Header h;
-    CU(c, cudaMemcpyAsync(&h, d_src, sizeof h, cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+    if (h_src) {
+        std::memcpy(&h, h_src, sizeof h);
+    } else {
+        CU(c, cudaMemcpyAsync(&h, d_src, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+    }
     if (h.magic != B200ANS_MAGIC || h.version != 1 || !(h.flags & kFlagPseudoAdaptive))
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: not a pseudo-adaptive b200ans container");
     if (h.method != method || h.fidelity != f)
@@ -2268,6 +2274,47 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
     const size_t payload_at = pre_at + h.prelude_bytes;
     if (payload_at + h.payload_bytes > src_bytes || payload_at < pre_at)
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: container truncated");
+
+    // host buffers: runs of models with about equal payload, queued on copy_in behind the front part
+    constexpr int kMaxRuns = b200ans_ctx::kPipeChunks;
+    uint32_t run_end[kMaxRuns];
+    uint64_t run_bytes_end[kMaxRuns];
+    int runs = 0;
+    if (h_src) {
+        const int cap = std::max(1, std::min(kMaxRuns, env_int("B200ANS_PA_RUNS", kMaxRuns)));
+        const int want = int(std::max<uint64_t>(1, std::min<uint64_t>(uint64_t(cap), h.payload_bytes / (uint64_t(8) << 20))));
+        const uint8_t* tp = h_src + sizes_at + size_t(nm) * 4;
+        uint64_t total = 0;
+        const uint64_t per = (h.payload_bytes + uint64_t(want) - 1) / uint64_t(want);
+        for (uint32_t b = 0; b < nm; b++) {
+            uint32_t v;
+            std::memcpy(&v, tp + size_t(b) * 4, 4);
+            total += (uint64_t(v) + 15u) & ~uint64_t(15);
+            if (total > h.payload_bytes)
+                return c->fail(B200ANS_E_FORMAT, "pa_decompress: block size table does not add up");
+            // runs end on a multiple of 8 models (one warp's task) so that no task straddles two runs
+            if ((total >= per * uint64_t(runs + 1) && runs < want - 1 && (b + 1) % 8 == 0) || b == nm - 1) {
+                run_end[runs] = b + 1;
+                run_bytes_end[runs] = total;
+                runs++;
+            }
+        }
+        RET(ensure_side_streams(c));
+        CU(c, cudaEventRecord(c->ev[5], c->stream));
+        CU(c, cudaStreamWaitEvent(c->copy_in, c->ev[5], 0));
+        CU(c, cudaStreamWaitEvent(c->copy_out, c->ev[5], 0));
+        uint8_t* d_in = const_cast<uint8_t*>(d_src);
+        CU(c, cudaMemcpyAsync(d_in, h_src, payload_at, cudaMemcpyHostToDevice, c->copy_in));
+        CU(c, cudaMemsetAsync(d_in + src_bytes, 0, 64, c->copy_in));
+        CU(c, cudaEventRecord(c->ev_in[kMaxRuns], c->copy_in));
+        for (int r = 0; r < runs; r++) {
+            const uint64_t lo = r ? run_bytes_end[r - 1] : 0;
+            if (run_bytes_end[r] > lo)
+                CU(c, cudaMemcpyAsync(d_in + payload_at + lo, h_src + payload_at + lo, size_t(run_bytes_end[r] - lo), cudaMemcpyHostToDevice, c->copy_in));
+            CU(c, cudaEventRecord(c->ev_in[r], c->copy_in));
+        }
+        CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[kMaxRuns], 0));
+    }
 
     // device: size scans, preludes -> frequencies (pa_prelude_decode_kernel), one synchronisation for the verdicts
     CU(c, cudaEventRecord(c->ev[3], c->stream));
@@ -2324,6 +2371,43 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
             break;
     }
     const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && c->h_small()->max_log2 <= 16u && pl.warps >= 2u;
+    if (smem_tables && h_src && runs > 1) {
+        // one launch per run of models; the pointers of the argument block move to the run's first model
+        CU(c, cudaEventRecord(c->ev[0], c->stream));
+        auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
+        const size_t warp_bytes = size_t(8) * pa_dec_group_bytes(a.pa_syms, a.pa_bucket_log2);
+        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(size_t(pl.max_warps) * warp_bytes)));
+        for (int r = 0; r < runs; r++) {
+            const uint32_t b0 = r ? run_end[r - 1] : 0, b1 = run_end[r];
+            const uint64_t s0 = uint64_t(b0) * h.block_syms, s1 = std::min<uint64_t>(n, uint64_t(b1) * h.block_syms);
+            DecArgs ar = a;
+            ar.offsets = a.offsets + b0;
+            ar.block_bytes = a.block_bytes + b0;
+            ar.out = d_dst + s0;
+            ar.n = size_t(s1 - s0);
+            ar.n_blocks = b1 - b0;
+            ar.pa_log2 = d_lg + b0;
+            ar.pa_nfreqs = a.pa_nfreqs + size_t(b0) * nbins;
+            const PaLaunch pr = pa_launch_shape(c, 0, warp_bytes, (b1 - b0 + 7) / 8);
+            CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
+            k<<<pr.grid, pr.warps * 32, pr.smem, c->stream>>>(ar);
+            c->stats.launches++;
+            CU(c, cudaGetLastError());
+            CU(c, cudaEventRecord(c->ev_dec[r], c->stream));
+            CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_dec[r], 0));
+            CU(c, cudaMemcpyAsync(h_dst + s0, d_dst + s0, size_t(s1 - s0) * 4, cudaMemcpyDeviceToHost, c->copy_out));
+        }
+        CU(c, cudaEventRecord(c->ev[1], c->stream));
+        CU(c, cudaEventRecord(c->ev[6], c->copy_out));
+        CU(c, cudaStreamWaitEvent(c->stream, c->ev[6], 0)); // the call's work ends on `stream`
+        CU(c, cudaStreamSynchronize(c->stream));
+        c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
+        c->stats.n_blocks = nm;
+        return B200ANS_OK;
+    }
+    if (h_src)
+        for (int r = 0; r < runs; r++)
+            CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
     if (smem_tables) {
         CU(c, cudaEventRecord(c->ev[0], c->stream));
         auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
@@ -2358,10 +2442,25 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
         CU(c, cudaGetLastError());
     }
     CU(c, cudaEventRecord(c->ev[1], c->stream));
+    if (h_dst)
+        CU(c, cudaMemcpyAsync(h_dst, d_dst, n * 4, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
     c->stats.n_blocks = nm;
     return B200ANS_OK;
+}
+
+} // namespace
+
+extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, size_t n,
+    const uint8_t* d_src, size_t src_bytes)
+{
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!d_dst && n) || !d_src || (reinterpret_cast<uintptr_t>(d_src) & 15))
+        return c->fail(B200ANS_E_ARG, "pa_decompress: bad argument (d_src must be 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    return pa_decompress_core(c, method, f, d_dst, n, d_src, src_bytes, nullptr, nullptr);
 }
 
 extern "C" int b200ans_pa_compress(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms, uint8_t* dst, size_t cap,
@@ -2398,11 +2497,12 @@ extern "C" int b200ans_pa_decompress(b200ans_ctx* c, int method, uint32_t f, uin
     CU(c, cudaSetDevice(c->device));
     CU(c, c->io_out.reserve(src_bytes + 64));
     CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
-    CU(c, cudaMemcpyAsync(c->io_out.p, src, src_bytes, cudaMemcpyHostToDevice, c->stream));
-    CU(c, cudaMemsetAsync(c->io_out.as<uint8_t>() + src_bytes, 0, 64, c->stream));
-    RET(b200ans_pa_decompress_device(c, method, f, c->io_in.as<uint32_t>(), n, c->io_out.as<uint8_t>(), src_bytes));
-    if (n)
-        CU(c, cudaMemcpyAsync(dst, c->io_in.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
-    return B200ANS_OK;
+    const int rc = pa_decompress_core(c, method, f, c->io_in.as<uint32_t>(), n, c->io_out.as<uint8_t>(), src_bytes, src, dst);
+    if (rc != B200ANS_OK && c->copy_in) { // nothing of a failed call may still be reading or writing the caller's buffers
+        cudaStreamSynchronize(c->copy_in);
+        cudaStreamSynchronize(c->stream);
+        cudaStreamSynchronize(c->copy_out);
+        cudaGetLastError();
+    }
+    return rc;
 }

@@ -148,3 +148,25 @@ def test_host_fallback_of_the_normaliser_gives_the_same_bytes(codec, monkeypatch
     finally:
         other.close()
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("runs", [1, 3, 8])
+def test_host_buffer_decode_in_runs_of_models(codec, monkeypatch, runs):
+    """b200ans_pa_decompress with host buffers moves the payload in runs of models (copy in / decode / copy out
+    overlapped); any number of runs gives the same symbols, and a size table that does not add up is refused with
+    nothing left in flight"""
+    import ans_large_alphabet_b200 as P
+
+    monkeypatch.setenv("B200ANS_PA_RUNS", str(runs))
+    n = (1 << 24) + 777
+    data = _inputs.make("zipf20", n, seed=21)
+    blob = codec.pa_compress(M_FOLD, 1, 8192, data).copy()
+    assert blob.size > (24 << 20)  # enough payload for several runs of 8 MiB
+    assert np.array_equal(codec.pa_decompress(M_FOLD, 1, blob, n), data)
+    nm = (n + 8191) // 8192
+    bad = blob.copy()
+    sizes = bad[64 : 64 + 8 * nm].view(np.uint32)
+    sizes[nm + nm // 2] += 16  # one payload size off by a 16-byte unit
+    with pytest.raises(P.B200AnsError):
+        codec.pa_decompress(M_FOLD, 1, bad, n)
+    assert np.array_equal(codec.pa_decompress(M_FOLD, 1, blob, n), data)
