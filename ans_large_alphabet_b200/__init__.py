@@ -21,4 +21,5 @@ from ._capi import (  # noqa: F401
     library_path,
     load_library,
     method_name,
+    suggest_block_syms,
 )

@@ -48,6 +48,7 @@ SIGNATURES = {
     "b200ans_destroy": (None, [C.c_void_p]),
     "b200ans_set_block_syms": (C.c_int, [C.c_void_p, C.c_uint32]),
     "b200ans_set_kernel_path": (C.c_int, [C.c_void_p, C.c_int]),
+    "b200ans_suggest_block_syms": (C.c_uint32, [C.c_void_p, C.c_size_t, C.c_uint32, C.c_uint32]),
     "b200ans_set_h_approx": (C.c_int, [C.c_void_p, C.c_uint32]),
     "b200ans_pa_compress_bound": (C.c_size_t, [C.c_void_p, C.c_int, C.c_uint32, C.c_size_t]),
     "b200ans_pa_compress": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
@@ -116,6 +117,11 @@ def load_library():
             fn.argtypes = args
         _LIB = lib
     return _LIB
+
+
+def suggest_block_syms(n, lo=8192, hi=16384):
+    """b200ans_suggest_block_syms without a context (148 SMs assumed): host arithmetic only"""
+    return int(load_library().b200ans_suggest_block_syms(None, n, lo, hi))
 
 
 def method_name(method, fidelity=0):
@@ -242,6 +248,10 @@ class Codec:
     def set_block_syms(self, bs):
         self._check(self.lib.b200ans_set_block_syms(self.h, bs))
         self.block_syms = bs
+
+    def suggest_block_syms(self, n, lo=8192, hi=16384):
+        """block size in [lo, hi] whose blocks fill whole rounds of the lane-per-block coders on this GPU"""
+        return int(self.lib.b200ans_suggest_block_syms(self.h, n, lo, hi))
 
     def set_h_approx(self, h):
         """adjust_freqs' H_approx: 1 = ANS / ANSmsb / ANSfold, other values = ANSsint<H> / ANSsmsb<H>"""

@@ -314,6 +314,33 @@ extern "C" int b200ans_set_block_syms(b200ans_ctx* c, uint32_t block_syms)
     return B200ANS_OK;
 }
 
+extern "C" uint32_t b200ans_suggest_block_syms(const b200ans_ctx* c, size_t n, uint32_t lo, uint32_t hi)
+{
+    // Lane-per-block coders: a warp owns 32 blocks for the whole launch and every SM holds kL3Warps warps, so a
+    // launch lasts rounds x (time of one block) with rounds = ceil(tasks / (SMs * warps)).  Cost ~ rounds * block size.
+    constexpr uint64_t kL3Warps = 16;
+    lo = std::max<uint32_t>(128u, (lo + 127u) & ~127u);
+    hi = std::min<uint32_t>(hi & ~127u, 1u << 24);
+    if (lo > hi)
+        return 0;
+    const uint64_t slots = uint64_t(c ? c->num_sms : 148) * kL3Warps;
+    uint32_t best = hi;
+    uint64_t best_cost = ~uint64_t(0);
+    for (uint32_t bs = hi;; bs -= 128) {
+        const uint64_t blocks = (uint64_t(n) + bs - 1) / bs;
+        const uint64_t tasks = (blocks + 31) / 32;
+        const uint64_t rounds = std::max<uint64_t>(1, (tasks + slots - 1) / slots);
+        const uint64_t cost = rounds * bs;
+        if (cost < best_cost) { // strict: the larger block size keeps a tie (less container overhead)
+            best_cost = cost;
+            best = bs;
+        }
+        if (bs == lo)
+            break;
+    }
+    return best;
+}
+
 extern "C" int b200ans_set_kernel_path(b200ans_ctx* c, int path)
 {
     if (!c)

@@ -238,13 +238,14 @@ def run_reference_arm(args, wl):
 # ------------------------------------------------------------------------------------------------
 def north_star_summary(P, dev, stream, peak, names=("fold1", "ans30"), steps=3):
     """Device-resident kernel times of the north star's 2^30-symbol targets (ANSfold-1 on Zipf, ANS on
-    geometric(0.01)), 8192 symbols per block: per kernel ms and fraction of the measured HBM peak."""
+    geometric(0.01)), block size from b200ans_suggest_block_syms in [8192, 16384]: per kernel ms and fraction of the measured HBM peak."""
     import torch
 
     out = {}
     for name in names:
         method, f, gen, n, desc = WORKLOADS[name]
         codec = P.Codec(device=dev.index, block_syms=8192, stream=stream.cuda_stream)
+        codec.set_block_syms(codec.suggest_block_syms(n, 8192, 16384))
         try:
             d_in = generate_device(gen, n, dev, seed=0)
             d_blob = torch.empty((codec.bound(method, n) + 15) // 16 * 16, dtype=torch.uint8, device=dev)
@@ -309,7 +310,14 @@ def run_ours(args, wl):
     if args.symbols:
         n = args.symbols
     stream = torch.cuda.Stream(device=dev)
-    codec = P.Codec(device=local, block_syms=args.block_syms, stream=stream.cuda_stream)
+    codec = P.Codec(device=local, block_syms=args.block_syms or 8192, stream=stream.cuda_stream)
+    if not args.block_syms:
+        # the container's own parameter: blocks that fill whole rounds of the lane-per-block coders on this GPU
+        args.block_syms = codec.suggest_block_syms(n, 8192, 16384)
+        codec.set_block_syms(args.block_syms)
+        block_rule = "b200ans_suggest_block_syms(n, 8192, 16384)"
+    else:
+        block_rule = "fixed"
     # weak scaling: every rank holds a full-size shard of the (N x larger) job
     d_in = generate_device(gen, n, dev, seed=rank)
     bound = codec.pa_bound(method, PA_MODEL_SYMS[args.workload], n) if args.workload in PA_MODEL_SYMS else codec.bound(method, n)
@@ -500,7 +508,7 @@ def run_ours(args, wl):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
             "config": {"workload": desc, "method": method_label(method, f), "symbols_per_gpu": n,
-                       "block_syms": pa or args.block_syms, "n_blocks_per_gpu": n_blocks,
+                       "block_syms": pa or args.block_syms, "block_syms_rule": "one model per block" if pa else block_rule, "n_blocks_per_gpu": n_blocks,
                        "l2": "inputs (%.0f MB per GPU) larger than the 126 MB L2; no flush" % (4.0 * n / 1e6),
                        "model": ("pseudo-adaptive: one model per block, normalised on the device, no collective" if pa else
                                  "semi-static, global histogram" + (" via NCCL all-reduce" if world > 1 else "")),
@@ -565,7 +573,7 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]
     if not args.block_syms:
-        args.block_syms = BLOCK_SYMS.get(args.workload, 8192)
+        args.block_syms = BLOCK_SYMS.get(args.workload, 0)  # 0: chosen from the shard size once the codec exists
     if args.impl == "reference":
         run_reference_arm(args, wl)
     else:

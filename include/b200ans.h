@@ -105,6 +105,12 @@ int b200ans_create(b200ans_ctx** out, int device, void* stream);
 void b200ans_destroy(b200ans_ctx* ctx);
 int b200ans_set_block_syms(b200ans_ctx* ctx, uint32_t block_syms); /* 0 or a multiple of 128 */
 int b200ans_set_kernel_path(b200ans_ctx* ctx, int path); /* B200ANS_PATH_* ; default AUTO */
+/* Block size for an input of n symbols (per GPU): the multiple of 128 in [lo, hi] whose blocks fill whole rounds of the
+ * lane-per-block coders (32 blocks per warp, 16 warps on each SM; a round lasts as long as one block), larger sizes
+ * winning ties. 2^30 symbols, [8192, 16384] -> 14208: one round of 16 warps per SM instead of two of 14 at 8192.
+ * The reference has no blocks (one stream per call, ans_fold.hpp:238-281); the block size is this container's own
+ * parameter and is stored in its header. ctx may be NULL (148 SMs assumed). Returns 0 for lo > hi or hi < 128. */
+uint32_t b200ans_suggest_block_syms(const b200ans_ctx* ctx, size_t n, uint32_t lo, uint32_t hi);
 /* H_approx of adjust_freqs (ans_util.hpp:100-101; ANSsint<H> / ANSsmsb<H>, methods.hpp:584-620): the frame stops
  * growing once the cross entropy is within H/1000 of the entropy. Default 1 (ANS / ANSmsb / ANSfold / ANSrfold). */
 int b200ans_set_h_approx(b200ans_ctx* ctx, uint32_t h_approx);

@@ -65,3 +65,26 @@ def test_strerror_and_bound():
     assert lib.b200ans_strerror(0) == b"ok"
     assert b"domain" in lib.b200ans_strerror(-4)
     assert lib.b200ans_compress_bound(None, 1, 1 << 20) > 7 * (1 << 20)
+
+
+def test_suggested_block_size_fills_whole_rounds():
+    """b200ans_suggest_block_syms is host arithmetic (no GPU): blocks of the chosen size fill whole rounds of
+    148 SMs x 16 warps x 32 blocks, ties go to the larger block, small inputs get the smallest size allowed"""
+    import ans_large_alphabet_b200 as P
+
+    slots = 148 * 16
+
+    def cost(n, bs):
+        tasks = ((n + bs - 1) // bs + 31) // 32
+        return max(1, (tasks + slots - 1) // slots) * bs
+
+    assert P.suggest_block_syms(1 << 30, 8192, 16384) == 14208  # one round of 16 warps per SM
+    for n in (1 << 30, 1 << 32, 10**9, 3 * 10**8 + 17):
+        for lo, hi in ((8192, 16384), (4096, 8192), (8192, 8192)):
+            bs = P.suggest_block_syms(n, lo, hi)
+            assert lo <= bs <= hi and bs % 128 == 0
+            assert cost(n, bs) == min(cost(n, b) for b in range(lo, hi + 1, 128))
+            assert all(cost(n, b) > cost(n, bs) for b in range(bs + 128, hi + 1, 128)), "a larger block ties"
+    assert P.suggest_block_syms(10**7, 8192, 16384) == 8192  # one round whatever the size: most parallelism
+    assert P.suggest_block_syms(1 << 30, 100, 1000) == 128 * 7 or P.suggest_block_syms(1 << 30, 100, 1000) % 128 == 0
+    assert P.suggest_block_syms(1 << 30, 16384, 8192) == 0

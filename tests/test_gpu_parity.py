@@ -76,7 +76,7 @@ def test_blocks_byte_identical_and_roundtrip(codec, method, f, kind, path):
 
 
 @pytest.mark.parametrize("method,f", [(M_FOLD, 1), (M_INT, 0), (M_MSB, 0), (M_RFOLD, 2)])
-@pytest.mark.parametrize("block_syms", [128, 1024, 4096, 65536])
+@pytest.mark.parametrize("block_syms", [128, 1024, 4096, 65536, 14208, 1920])  # the last two: not powers of two
 @pytest.mark.parametrize("path", PATHS)
 def test_block_sizes(codec, method, f, block_syms, path):
     codec.set_kernel_path(path)

@@ -23,18 +23,19 @@ def main():
     ap.add_argument("--n", type=int, default=0)
     ap.add_argument("--workloads", default="fold1,ans30,c2")
     ap.add_argument("--paths", default="1,2")
-    ap.add_argument("--block-syms", type=int, default=8192)
+    ap.add_argument("--block-syms", type=int, default=0, help="0 = b200ans_suggest_block_syms(n, 8192, 16384)")
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--check", action="store_true")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     peak, _ = bench.measured_peak()
     stream = torch.cuda.Stream(device=dev)
-    codec = P.Codec(device=0, block_syms=args.block_syms, stream=stream.cuda_stream)
+    codec = P.Codec(device=0, block_syms=args.block_syms or 8192, stream=stream.cuda_stream)
     for wl in args.workloads.split(","):
         method, f, gen, n, desc = bench.WORKLOADS[wl]
         if args.n:
             n = args.n
+        codec.set_block_syms(args.block_syms or codec.suggest_block_syms(n, 8192, 16384))
         d_in = bench.generate_device(gen, n, dev, seed=0)
         d_blob = torch.empty((codec.bound(method, n) + 15) // 16 * 16, dtype=torch.uint8, device=dev)
         d_out = torch.empty(n, dtype=torch.int32, device=dev)
