@@ -803,6 +803,78 @@ static double now_ns(void)
 }
 
 /* table_efficiency.cpp:77-101 style: min over `runs`, single thread */
+/* ---- pseudo-adaptive driver with the dense-rank alphabet remap, one block (src/pseudo_adaptive.cpp:83-125) ----
+ * The driver marks the values present in the block, replaces every value by its 1-based rank among them (:86-99),
+ * turns the sorted list of present values into running sums held in uint32_t (:101-103), writes
+ * [u32 sigma][u32 last sum + 1][interpolative code of the sums, universe last sum + 1] (:105-112) and, unless the
+ * block holds one distinct value, appends T::encode of the ranks (:114-121).  Sums that leave 32 bits are outside
+ * the driver's working domain (the list handed to the interpolative coder would no longer be increasing): -2. */
+static int cmp_u32(const void* a, const void* b)
+{
+    const uint32_t x = *(const uint32_t*)a, y = *(const uint32_t*)b;
+    return x < y ? -1 : x > y;
+}
+
+long orc_pa_remap_block(int method, uint32_t f, const uint32_t* in, size_t n, uint8_t* dst, size_t cap,
+    uint32_t* remapped_out, size_t* alphabet_bytes)
+{
+    if (n == 0 || !in || !dst)
+        return -1;
+    uint32_t* present = (uint32_t*)malloc(n * sizeof(uint32_t));
+    uint32_t* ranks = remapped_out ? remapped_out : (uint32_t*)malloc(n * sizeof(uint32_t));
+    long result = -1;
+    memcpy(present, in, n * sizeof(uint32_t));
+    qsort(present, n, sizeof(uint32_t), cmp_u32);
+    size_t sigma = 1;
+    for (size_t i = 1; i < n; i++)
+        if (present[i] != present[sigma - 1])
+            present[sigma++] = present[i];
+    for (size_t k = 0; k < n; k++) { /* rank = number of present values <= in[k] */
+        size_t lo = 0, hi = sigma;
+        while (hi - lo > 1) {
+            const size_t mid = (lo + hi) / 2;
+            if (present[mid] <= in[k])
+                lo = mid;
+            else
+                hi = mid;
+        }
+        ranks[k] = (uint32_t)(lo + 1);
+    }
+    uint64_t run = 0;
+    for (size_t i = 0; i < sigma; i++) {
+        run += present[i];
+        if (run > 0xFFFFFFFEull) {
+            result = -2;
+            goto done;
+        }
+        present[i] = (uint32_t)run;
+    }
+    if (cap < 8 + 8 * sigma + 64) {
+        result = -3;
+        goto done;
+    }
+    {
+        const uint32_t head[2] = { (uint32_t)sigma, present[sigma - 1] + 1u };
+        memcpy(dst, head, 8);
+        const long ib = orc_interp_encode((uint32_t*)(dst + 8), present, sigma, (size_t)present[sigma - 1] + 1u);
+        size_t at = 8 + (size_t)ib;
+        if (alphabet_bytes)
+            *alphabet_bytes = at;
+        if (sigma != 1) {
+            const long eb = orc_compress(method, f, dst + at, cap - at, ranks, n);
+            if (eb < 0)
+                goto done;
+            at += (size_t)eb;
+        }
+        result = (long)at;
+    }
+done:
+    free(present);
+    if (!remapped_out)
+        free(ranks);
+    return result;
+}
+
 int orc_time(int method, uint32_t f, const uint32_t* in, size_t n, int runs, double* enc_ns, double* dec_ns,
     size_t* bytes)
 {

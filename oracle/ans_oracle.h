@@ -4,7 +4,7 @@
  * mpetri/ans-large-alphabet: ans_int, ans_fold<f>, ans_msb, ans_reorder_fold<f>, their
  * ans_util.hpp model utilities and the interp.hpp/vbyte.hpp prelude.
  *
- * Parity status: PINNED.  tests/test_oracle_vs_reference.py checks every function here
+ * Parity status: PINNED.  tests/test_oracle_golden.py checks every function here
  * against the unmodified reference headers compiled into oracle/_ref/libansref.so
  * (oracle/ref_shim.cpp), and tests/golden/ holds vectors generated from that library.
  */
@@ -50,6 +50,12 @@ long orc_model_rfold_info(orc_model* m, uint64_t* sigma, uint32_t* most_frequent
 long orc_encode_block(orc_model* m, const uint32_t* in, size_t n, uint8_t* dst);
 int orc_decode_block(orc_model* m, const uint8_t* src, size_t bytes, uint32_t* out, size_t n);
 void orc_model_free(orc_model* m);
+
+/* src/pseudo_adaptive.cpp:83-125, one block of the driver with the dense-rank alphabet remap: returns the bytes
+ * written ([u32 sigma][u32 universe][interp of the running sums of the present values] + T::encode of the ranks),
+ * *alphabet_bytes = the part before T::encode; -2 when the running sums leave 32 bits */
+long orc_pa_remap_block(int method, uint32_t f, const uint32_t* in, size_t n, uint8_t* dst, size_t cap,
+    uint32_t* remapped_out, size_t* alphabet_bytes);
 
 /* single-thread timing helper for bench.py's cpu_baseline ("kind": "port") */
 int orc_time(int method, uint32_t f, const uint32_t* in, size_t n, int runs, double* enc_ns,

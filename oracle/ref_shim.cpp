@@ -418,6 +418,56 @@ int ref_generate(int kind, uint32_t seed, uint32_t range, double q, uint32_t sub
 }
 
 // table_efficiency.cpp:77-101 style timing: min of `runs`, ns. Round trip is verified.
+// ---- one block of the pseudo-adaptive driver (src/pseudo_adaptive.cpp:83-125; the driver itself needs Boost) ------
+// The driver's steps on one block, with the reference's own interpolative coder and T::encode (= ans_X_compress,
+// methods.hpp:484-512) doing the coding: presence flags over [0, max], running count = 1-based rank, the list of
+// present values turned into uint32_t running sums, [sigma][last + 1][interp], then the coder on the ranks.
+long ref_pa_remap_block(int method, uint32_t f, const uint32_t* in, size_t n, uint8_t* dst, size_t cap,
+    uint32_t* remapped_out, size_t* alphabet_bytes)
+{
+    if (n == 0 || !in || !dst)
+        return -1;
+    const uint32_t top = *std::max_element(in, in + n);
+    std::vector<uint32_t> rank_of(size_t(top) + 1, 0);
+    for (size_t k = 0; k < n; k++)
+        rank_of[in[k]] = 1;
+    std::vector<uint32_t> alphabet;
+    for (size_t v = 0; v <= top; v++) {
+        if (rank_of[v] == 1)
+            alphabet.push_back(uint32_t(v));
+        if (v)
+            rank_of[v] += rank_of[v - 1];
+    }
+    std::vector<uint32_t> ranks(n);
+    for (size_t k = 0; k < n; k++)
+        ranks[k] = rank_of[in[k]];
+    uint64_t run = 0;
+    for (auto& a : alphabet) {
+        run += a;
+        if (run > 0xFFFFFFFEull)
+            return -2; // the driver's uint32_t sums would wrap: outside its working domain
+        a = uint32_t(run);
+    }
+    if (cap < 8 + 8 * alphabet.size() + 64)
+        return -3;
+    uint32_t* out32 = reinterpret_cast<uint32_t*>(dst);
+    *out32++ = uint32_t(alphabet.size());
+    *out32++ = alphabet.back() + 1;
+    const size_t ib = interpolative_internal::encode(out32, alphabet.data(), alphabet.size(), alphabet.back() + 1);
+    size_t at = 8 + ib;
+    if (alphabet_bytes)
+        *alphabet_bytes = at;
+    if (alphabet.size() != 1) {
+        const long eb = ref_compress(method, f, dst + at, cap - at, ranks.data(), n);
+        if (eb < 0)
+            return -1;
+        at += size_t(eb);
+    }
+    if (remapped_out)
+        std::copy(ranks.begin(), ranks.end(), remapped_out);
+    return long(at);
+}
+
 int ref_time(int method, uint32_t f, const uint32_t* in, size_t n, int runs, double* enc_ns, double* dec_ns,
     size_t* bytes)
 {

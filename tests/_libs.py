@@ -112,6 +112,22 @@ class _CpuCodec:
         assert rc == 0
         return out[:n].copy()
 
+    def pa_remap_block(self, method, f, data):
+        """one block of src/pseudo_adaptive.cpp:83-125 -> (bytes, alphabet bytes, ranks); None when the driver's
+        32-bit running sums of the block alphabet would wrap"""
+        fn = self._f("pa_remap_block")
+        fn.restype = C.c_long
+        fn.argtypes = [C.c_int, C.c_uint32, u32p, C.c_size_t, u8p, C.c_size_t, u32p, C.POINTER(C.c_size_t)]
+        data = np.ascontiguousarray(data, dtype=np.uint32)
+        out = np.zeros(data.size * 16 + (1 << 16) + (8 << 20) * (method == M_INT), dtype=np.uint8)
+        ranks = np.zeros(data.size, dtype=np.uint32)
+        ab = C.c_size_t()
+        nb = fn(method, f, ptr(data, u32p), data.size, ptr(out, u8p), out.size, ptr(ranks, u32p), C.byref(ab))
+        if nb == -2:
+            return None
+        assert nb >= 0, nb
+        return out[:nb].copy(), ab.value, ranks
+
     # ---- model utilities ----------------------------------------------------------------
     def adjust_freqs(self, freqs, largest_sym, require_u16, h_approx=1):
         freqs = np.ascontiguousarray(freqs, dtype=np.uint64)

@@ -10,7 +10,8 @@ Each vector holds a small seeded input and what the reference produced for it:
   stream                ans_X_compress whole stream                    (ans_fold.hpp:238-281 ...)
   block_payloads        the 4-state loop of ans_fold.hpp:250-278 driven per 1024-symbol block with the global model
 plus known answers of the fold / msb mappings (ans_fold.hpp:38-65, ans_msb.hpp:41-73) and the
-interpolative coder (interp.hpp:100-118).  The reference leaves the unused high bits of its last
+interpolative coder (interp.hpp:100-118), and blocks of the pseudo-adaptive driver with its dense-rank alphabet
+remap (src/pseudo_adaptive.cpp:83-125; `python tests/golden/make_golden.py pa_remap` writes only those).  The reference leaves the unused high bits of its last
 interp word uninitialised (bits.hpp:148); they are masked to zero here so the vectors are stable.
 """
 import os
@@ -51,8 +52,38 @@ def mask_tail(prelude):
     return prelude
 
 
+PA_REMAP_CASES = [
+    # method, f, input kind, block length, seed   (one block of src/pseudo_adaptive.cpp:83-125 each)
+    (M_INT, 0, "zipf20", 8192, 31), (M_MSB, 0, "zipf20", 8192, 32), (M_INT, 0, "geom", 4096, 33),
+    (M_MSB, 0, "zipf16", 1024, 34), (M_INT, 0, "u8", 777, 35), (M_MSB, 0, "zipf12s", 16384, 36),
+]
+
+
+def pa_remap_vectors(ref):
+    """the driver's dense-rank remap + block alphabet + T::encode, block by block"""
+    out = {}
+    for j, (method, f, kind, n, seed) in enumerate(PA_REMAP_CASES):
+        data = _inputs.make(kind, n, seed=seed)
+        blob, alpha_bytes, ranks = ref.pa_remap_block(method, f, data)
+        coder_prelude = ref.model_create(method, f, ranks).serialize().size
+        assert np.array_equal(ref.decompress(method, f, blob[alpha_bytes:], n), ranks)
+        out[f"data{j}"], out[f"blob{j}"], out[f"ranks{j}"] = data, blob, ranks
+        out[f"meta{j}"] = np.array([method, f, alpha_bytes, coder_prelude], dtype=np.int64)
+    single = np.full(1000, 12345, dtype=np.uint32)  # one distinct value: alphabet only (pseudo_adaptive.cpp:114)
+    blob, alpha_bytes, ranks = ref.pa_remap_block(M_INT, 0, single)
+    assert blob.size == alpha_bytes
+    j = len(PA_REMAP_CASES)
+    out[f"data{j}"], out[f"blob{j}"], out[f"ranks{j}"] = single, blob, ranks
+    out[f"meta{j}"] = np.array([M_INT, 0, alpha_bytes, 0], dtype=np.int64)
+    np.savez_compressed(os.path.join(HERE, "pa_remap.npz"), count=np.int32(j + 1), **out)
+    print(f"pa_remap: {j + 1} blocks")
+
+
 def main():
     ref = reference()
+    if len(sys.argv) > 1 and sys.argv[1] == "pa_remap":
+        pa_remap_vectors(ref)
+        return
     for name, method, f, kind, n, seed in CASES:
         data = _inputs.make(kind, n, seed=seed)
         model = ref.model_create(method, f, data)
@@ -127,6 +158,7 @@ def main():
         hs[f"n{j}"] = ref.adjust_freqs(h, largest, bool(u16))
     np.savez_compressed(os.path.join(HERE, "adjust_freqs.npz"), **hs)
     print("interp + adjust_freqs vectors written")
+    pa_remap_vectors(ref)
 
 
 if __name__ == "__main__":

@@ -15,7 +15,7 @@ from _libs import M_FOLD, M_INT, M_MSB, M_RFOLD, have_reference
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLD, "*.npz"))
-               if os.path.basename(p)[:-4] not in ("mappings", "interp", "adjust_freqs"))
+               if os.path.basename(p)[:-4] not in ("mappings", "interp", "adjust_freqs", "pa_remap"))
 
 
 def load(name):
@@ -28,7 +28,7 @@ def split_blocks(g):
 
 
 def test_golden_set_is_complete():
-    assert len(CASES) >= 14 and {"mappings", "interp", "adjust_freqs"} <= {os.path.basename(p)[:-4] for p in glob.glob(GOLD + "/*.npz")}
+    assert len(CASES) >= 14 and {"mappings", "interp", "adjust_freqs", "pa_remap"} <= {os.path.basename(p)[:-4] for p in glob.glob(GOLD + "/*.npz")}
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -163,3 +163,49 @@ def test_oracle_adjust_freqs_live(orc, ref):
         largest = int(np.nonzero(h)[0][-1])
         for u16 in (True, False):
             assert np.array_equal(orc.adjust_freqs(h, largest, u16), ref.adjust_freqs(h, largest, u16)), (trial, u16)
+
+
+def remap_blocks_equal(a, a_alpha, b, b_alpha, coder_prelude):
+    """[sigma][universe][interp] and the coder's prelude up to the reference's undefined padding bits, the rest exactly"""
+    if a.size != b.size or a_alpha != b_alpha:
+        return False
+    if not _container.prelude_equal(a[:a_alpha], b[:b_alpha]):
+        return False
+    if a.size == a_alpha:
+        return True
+    at = a_alpha + coder_prelude
+    return _container.prelude_equal(a[a_alpha:at], b[b_alpha:at]) and np.array_equal(a[at:], b[at:])
+
+
+def test_oracle_pa_remap_blocks_match_reference(orc):
+    """src/pseudo_adaptive.cpp:83-125 block by block: ranks, block alphabet and coder output of the oracle against
+    vectors written by the reference's own interpolative coder and ans_X_compress; the ranks decode and map back"""
+    g = load("pa_remap")
+    for j in range(int(g["count"])):
+        method, f, alpha_bytes, coder_prelude = (int(x) for x in g[f"meta{j}"])
+        data, want = g[f"data{j}"], g[f"blob{j}"]
+        blob, ab, ranks = orc.pa_remap_block(method, f, data)
+        assert np.array_equal(ranks, g[f"ranks{j}"]), j
+        assert remap_blocks_equal(blob, ab, want, alpha_bytes, coder_prelude), j
+        # and back: alphabet from the running sums, values from the ranks
+        sigma, universe = (int(x) for x in want[:8].view(np.uint32))
+        sums = orc.interp_decode(want[8:alpha_bytes].view(np.uint32), sigma, universe).astype(np.int64)
+        alphabet = np.diff(np.concatenate([[0], sums]))
+        assert universe == sums[-1] + 1 and np.array_equal(alphabet, np.unique(data))
+        got = orc.decompress(method, f, want[alpha_bytes:], data.size) if sigma != 1 else np.ones(data.size, np.uint32)
+        assert np.array_equal(alphabet[got.astype(np.int64) - 1], data), j
+
+
+@live
+@pytest.mark.parametrize("method,f", [(M_INT, 0), (M_MSB, 0), (M_FOLD, 1)])
+def test_oracle_pa_remap_live(orc, ref, method, f):
+    rng = np.random.default_rng(17)
+    for kind, n in (("zipf20", 8192), ("zipf16", 1280), ("geom", 65536), ("u8", 129), ("zipf12s", 4096)):
+        data = _inputs.make(kind, n, seed=int(rng.integers(1, 1000)))
+        if rng.random() < 0.5:
+            data[int(rng.integers(0, n))] = 0  # a block that holds the value 0 (pseudo_adaptive.cpp:92-93)
+        a, b = orc.pa_remap_block(method, f, data), ref.pa_remap_block(method, f, data)
+        pre = ref.model_create(method, f, b[2]).serialize().size
+        assert np.array_equal(a[2], b[2]) and remap_blocks_equal(a[0], a[1], b[0], b[1], pre), (kind, n)
+    wide = (rng.integers(1 << 20, 1 << 24, size=4096)).astype(np.uint32)  # running sums beyond 32 bits
+    assert orc.pa_remap_block(method, f, wide) is None and ref.pa_remap_block(method, f, wide) is None
