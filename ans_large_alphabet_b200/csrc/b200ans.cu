@@ -318,7 +318,8 @@ extern "C" uint32_t b200ans_suggest_block_syms(const b200ans_ctx* c, size_t n, u
 {
     // Lane-per-block coders: a warp owns 32 blocks for the whole launch and every SM holds kL3Warps warps, so a
     // launch lasts rounds x (time of one block) with rounds = ceil(tasks / (SMs * warps)).  Cost ~ rounds * block size.
-    constexpr uint64_t kL3Warps = 16;
+    const char* wide = std::getenv("B200ANS_L3_ENC_WIDE"); // the unmeasured 22-warp encoder shape (lpb3_kernels.cuh)
+    const uint64_t kL3Warps = wide && std::atoi(wide) ? 22 : 16;
     lo = std::max<uint32_t>(128u, (lo + 127u) & ~127u);
     hi = std::min<uint32_t>(hi & ~127u, 1u << 24);
     if (lo > hi)
@@ -1152,7 +1153,7 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
         if ((size_t(alphabet) << r) * 16 + 64 > c->max_smem || table_bytes + 2048 > c->max_smem)
             continue;
         const uint32_t fit = uint32_t(std::min<size_t>(CFG::MAXW, (c->max_smem - table_bytes - 1024) / L3Geom<CFG>::kWarpBytes));
-        if (fit >= std::min<uint32_t>(want_warps, 16u) || r == 0) {
+        if (fit >= std::min<uint32_t>(want_warps, uint32_t(CFG::MAXW)) || r == 0) {
             rep = r;
             max_warps = fit;
             break;
@@ -1202,6 +1203,8 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
 
 template <int METHOD> int launch_lpb3_encode_t(b200ans_ctx* c, const EncArgs& a)
 {
+    if (env_int("B200ANS_L3_ENC_WIDE", 0)) // up to 22 warps per SM; unmeasured (lpb3_kernels.cuh, L3CfgWide)
+        return launch_lpb3_encode_cfg<METHOD, L3CfgWide>(c, a);
     return launch_lpb3_encode_cfg<METHOD, L3Cfg>(c, a);
 }
 

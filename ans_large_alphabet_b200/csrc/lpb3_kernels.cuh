@@ -38,6 +38,12 @@ namespace b200ans {
 struct L3Cfg {
     static constexpr int TQ = 4, STAGES = 2, DQ = 2, MAXW = 16;
 };
+// The same encoder with room for 22 warps per CTA (92 registers per thread still fit: 65 536 / 704 = 93).  Selected by
+// B200ANS_L3_ENC_WIDE=1 only: written at the end of round 1 without GPU time left, so it is NOT measured and not the
+// default; the default kernels and their launch shape are unchanged.
+struct L3CfgWide {
+    static constexpr int TQ = 4, STAGES = 2, DQ = 2, MAXW = 22;
+};
 // output row: 12 carried bytes + 28 per quad + slack for the final partial word; an odd number of 16-byte chunks
 template <class CFG> struct L3Geom {
     static constexpr int kTileBytes = 32 * CFG::TQ * 16;
