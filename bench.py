@@ -245,7 +245,8 @@ def north_star_summary(P, dev, stream, peak, names=("fold1", "ans30"), steps=3):
     for name in names:
         method, f, gen, n, desc = WORKLOADS[name]
         codec = P.Codec(device=dev.index, block_syms=8192, stream=stream.cuda_stream)
-        codec.set_block_syms(codec.suggest_block_syms(n, 8192, 16384))
+        block_syms = codec.suggest_block_syms(n, 8192, 16384)
+        codec.set_block_syms(block_syms)
         try:
             d_in = generate_device(gen, n, dev, seed=0)
             d_blob = torch.empty((codec.bound(method, n) + 15) // 16 * 16, dtype=torch.uint8, device=dev)
@@ -274,7 +275,7 @@ def north_star_summary(P, dev, stream, peak, names=("fold1", "ans30"), steps=3):
             c = s1.payload_bytes / n
             alg = {"histogram": 4.0 * n, "encode": (4.0 + c) * n, "compact": 2.0 * c * n, "decode": (4.0 + c) * n}
             out[name] = {
-                "workload": desc, "roundtrip_ok": bool(torch.equal(d_in, d_out)), "bits_per_symbol": 8.0 * nb / n,
+                "workload": desc, "block_syms": block_syms, "roundtrip_ok": bool(torch.equal(d_in, d_out)), "bits_per_symbol": 8.0 * nb / n,
                 "encode_ms": enc_ms, "decode_ms": dec_ms, "encode_gbs": 4.0 * n / (enc_ms * 1e6), "decode_gbs": 4.0 * n / (dec_ms * 1e6),
                 "kernels": {k: {"ms": v, "achieved_gbs": alg[k] / (v * 1e6), "frac": alg[k] / (v * 1e6) / peak} for k, v in acc.items() if v > 0},
             }
