@@ -30,7 +30,7 @@ class Stats(C.Structure):
         ("ms_compact", C.c_float), ("ms_decode", C.c_float), ("ms_h2d", C.c_float), ("ms_d2h", C.c_float),
         ("launches", C.c_uint64), ("frame_size", C.c_uint64), ("n_symbols_model", C.c_uint32),
         ("n_blocks", C.c_uint32), ("prelude_bytes", C.c_uint64), ("payload_bytes", C.c_uint64),
-        ("total_bytes", C.c_uint64),
+        ("total_bytes", C.c_uint64), ("encode_kernel", C.c_char * 32), ("decode_kernel", C.c_char * 32),
     ]
 
 

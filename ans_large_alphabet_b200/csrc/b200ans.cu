@@ -220,6 +220,11 @@ double reciprocal_up(uint32_t f)
     return r;
 }
 
+void set_name(char (&dst)[32], const char* name)
+{
+    std::snprintf(dst, sizeof dst, "%s", name);
+}
+
 double now_ms()
 {
     using namespace std::chrono;
@@ -318,8 +323,7 @@ extern "C" uint32_t b200ans_suggest_block_syms(const b200ans_ctx* c, size_t n, u
 {
     // Lane-per-block coders: a warp owns 32 blocks for the whole launch and every SM holds kL3Warps warps, so a
     // launch lasts rounds x (time of one block) with rounds = ceil(tasks / (SMs * warps)).  Cost ~ rounds * block size.
-    const char* wide = std::getenv("B200ANS_L3_ENC_WIDE"); // the unmeasured 22-warp encoder shape (lpb3_kernels.cuh)
-    const uint64_t kL3Warps = wide && std::atoi(wide) ? 22 : 16;
+    const uint64_t kL3Warps = 16;
     lo = std::max<uint32_t>(128u, (lo + 127u) & ~127u);
     hi = std::min<uint32_t>(hi & ~127u, 1u << 24);
     if (lo > hi)
@@ -993,6 +997,7 @@ template <int METHOD> int launch_encode_t(b200ans_ctx* c, const EncArgs& a)
         const int grid = persistent_grid(c, k, kEncWarps * 32, rows, n_tasks, kEncWarps);
         k<<<grid, kEncWarps * 32, rows, c->stream>>>(a);
     }
+    set_name(c->stats.encode_kernel, "encode_kernel");
     c->stats.launches++;
     CU(c, cudaGetLastError());
     return B200ANS_OK;
@@ -1034,6 +1039,7 @@ int launch_lpb(b200ans_ctx* c, K k, size_t table_bytes, size_t warp_bytes, uint3
 
 template <int METHOD> int launch_lpb_encode_t(b200ans_ctx* c, const EncArgs& a)
 {
+    set_name(c->stats.encode_kernel, "lpb_encode_kernel");
     const bool smem_table = a.n_entries <= uint32_t(kLpbEncMaxSmemEntries);
     const size_t tb = smem_table ? size_t(a.n_entries) * sizeof(EncEntry) : 0;
     if (smem_table)
@@ -1047,7 +1053,9 @@ template <int METHOD, int TABLE> int launch_lpb_decode_tt(b200ans_ctx* c, const 
 {
     // L3 decoder (lpb3_kernels.cuh) needs 16-byte aligned output; QI = 2 stores whole 32-byte sectors
     const uintptr_t out_addr = reinterpret_cast<uintptr_t>(a.out);
+    set_name(c->stats.decode_kernel, "lpb_decode_kernel");
     if ((out_addr & 15) == 0 && a.block_syms % 8u == 0u && !env_int("B200ANS_NO_L3", 0)) {
+        set_name(c->stats.decode_kernel, "lpb3_decode_kernel");
         const size_t tb = align_up(table_bytes, 16);
         const int shape = env_int("B200ANS_L3_DEC", 0);
         if ((out_addr & 31) == 0 && shape == 0)
@@ -1078,6 +1086,7 @@ template <int METHOD> int launch_lpb3_decode_pure(b200ans_ctx* c, DecArgs a, siz
         c->dec_have_pure = true;
     }
     a.rank_rec = c->dec_bits_pure.as<RankRec>();
+    set_name(c->stats.decode_kernel, "lpb3_decode_kernel");
     const size_t tb = align_up(table_bytes, 16);
     return launch_lpb(c, lpb3_decode_kernel<METHOD, DEC_INT_SMEM_PURE, 2, 16>, tb + 256, L3DecGeom<2>::kWarpBytes, a.n_blocks, &a, 16);
 }
@@ -1196,6 +1205,7 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
         k1<<<grid, warps * 32, smem, c->stream>>>(a, g, tmap);
     else
         k<<<grid, warps * 32, smem, c->stream>>>(a, g, tmap);
+    set_name(c->stats.encode_kernel, "lpb3_encode_kernel");
     c->stats.launches++;
     CU(c, cudaGetLastError());
     return B200ANS_OK;
@@ -1203,8 +1213,6 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
 
 template <int METHOD> int launch_lpb3_encode_t(b200ans_ctx* c, const EncArgs& a)
 {
-    if (env_int("B200ANS_L3_ENC_WIDE", 0)) // up to 22 warps per SM; unmeasured (lpb3_kernels.cuh, L3CfgWide)
-        return launch_lpb3_encode_cfg<METHOD, L3CfgWide>(c, a);
     return launch_lpb3_encode_cfg<METHOD, L3Cfg>(c, a);
 }
 
@@ -1263,6 +1271,7 @@ template <int METHOD, int TABLE> int launch_decode_tt(b200ans_ctx* c, const DecA
     const uint32_t n_tasks = (a.n_blocks + 7) / 8;
     const int grid = persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps);
     k<<<grid, kDecWarps * 32, smem, c->stream>>>(a);
+    set_name(c->stats.decode_kernel, "decode_kernel");
     c->stats.launches++;
     CU(c, cudaGetLastError());
     return B200ANS_OK;
@@ -1276,6 +1285,7 @@ template <int TABLE> int launch_int_decode_t(b200ans_ctx* c, const DecArgs& a, s
     const uint32_t n_tasks = (a.n_blocks + 7) / 8;
     const int grid = persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps);
     k<<<grid, kDecWarps * 32, smem, c->stream>>>(a);
+    set_name(c->stats.decode_kernel, "int_decode_kernel");
     c->stats.launches++;
     CU(c, cudaGetLastError());
     return B200ANS_OK;
@@ -2207,9 +2217,11 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
         auto k = method == METHOD_MSB ? pa_smem_encode_kernel<METHOD_MSB> : pa_smem_encode_kernel<METHOD_FOLD>;
         CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
         k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
+        set_name(c->stats.encode_kernel, "pa_smem_encode_kernel");
         c->stats.launches++;
         CU(c, cudaGetLastError());
     } else {
+        set_name(c->stats.encode_kernel, "encode_kernel");
         const size_t rows = size_t(kEncWarps) * 8 * kEncRowBytes;
         if (method == METHOD_MSB) {
             auto k = encode_kernel<METHOD_MSB, false, true>;
@@ -2401,6 +2413,7 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
             break;
     }
     const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && c->h_small()->max_log2 <= 16u && pl.warps >= 2u;
+    set_name(c->stats.decode_kernel, smem_tables ? "pa_smem_decode_kernel" : "decode_kernel");
     if (smem_tables && h_src && runs > 1) {
         // one launch per run of models; the pointers of the argument block move to the run's first model
         CU(c, cudaEventRecord(c->ev[0], c->stream));

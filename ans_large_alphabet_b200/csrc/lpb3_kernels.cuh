@@ -38,12 +38,9 @@ namespace b200ans {
 struct L3Cfg {
     static constexpr int TQ = 4, STAGES = 2, DQ = 2, MAXW = 16;
 };
-// The same encoder with room for 22 warps per CTA (92 registers per thread still fit: 65 536 / 704 = 93).  Selected by
-// B200ANS_L3_ENC_WIDE=1 only: written at the end of round 1 without GPU time left, so it is NOT measured and not the
-// default; the default kernels and their launch shape are unchanged.
-struct L3CfgWide {
-    static constexpr int TQ = 4, STAGES = 2, DQ = 2, MAXW = 22;
-};
+// (A 22-warp shape of the same encoder -- 92 registers per thread still fit -- was measured in round 2: parity green,
+// but 2.11 ms against 1.705 ms for ANSfold-1 at 2^30 symbols, 2.31 against 2.01 for ANSfold-2, 2.04 against 1.98 for
+// ANS: more TMA gather streams per SM than the memory system likes.  Removed.)
 // output row: 12 carried bytes + 28 per quad + slack for the final partial word; an odd number of 16-byte chunks
 template <class CFG> struct L3Geom {
     static constexpr int kTileBytes = 32 * CFG::TQ * 16;

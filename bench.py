@@ -14,7 +14,13 @@ reported separately.
   --impl reference : the reference's own single-threaded CPU coder (oracle/_ref/libansref.so,
            the unmodified headers; falls back to the C port) on a bounded sample per step
 
-python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c1|c3|fold1|...] [--impl ours|reference]
+The default workload is BASELINE.json's config 5 as ONE FIXED JOB: semi-static ANSfold-1 over 2^32 symbols (the
+configuration the north star's >= 7x-on-8-GPUs target is stated on; it fits one B200), split into N contiguous shards
+of 2^32 / N symbols -> "scaling": "strong".  The same line carries `north_star_2p30`: the 2^30-symbol single-GPU
+targets (ANSfold-1, ANSfold-2, ANS) kernel by kernel, and `parity`: blocks of the step's container compared byte for
+byte with the reference coder (oracle/_ref) run on those blocks with the same global model, outside the timed region.
+
+python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c5|c2|c1|c3|c3r|fold1|...] [--impl ours|reference]
 """
 import argparse
 import json
@@ -40,7 +46,8 @@ WORKLOADS = {
     "c2": (M_INT, 0, ("geom", 0.01), 100_000_000, "C2 ANS (ans_int), 1e8-symbol geometric(p=0.01)"),
     "c3": (M_FOLD, 2, ("zipf", 1 << 24, 1.0, 0), 1_000_000_000, "C3 ANSfold-2, 1e9-symbol Zipf(1.0, 2^24)"),
     "c3r": (M_RFOLD, 2, ("zipf", 1 << 24, 1.0, 0), 1_000_000_000, "C3 ANSrfold-2, 1e9-symbol Zipf(1.0, 2^24)"),
-    "c5": (M_FOLD, 1, ("zipf", 1 << 20, 1.2, 1), 1 << 30, "C5-style ANSfold-1, 2^30-symbol Zipf(1.2, 2^20)-1 per GPU"),
+    "c5": (M_FOLD, 1, ("zipf", 1 << 20, 1.2, 1), 1 << 32, "C5 semi-static ANSfold-1, ONE 2^32-symbol BWT-MTF-style job (Zipf(1.2, 2^20)-1), split over the GPUs"),
+    "c5w": (M_FOLD, 1, ("zipf", 1 << 20, 1.2, 1), 1 << 30, "C5-style ANSfold-1, 2^30-symbol Zipf(1.2, 2^20)-1 per GPU (weak scaling)"),
     "fold1": (M_FOLD, 1, ("zipf", 1 << 20, 1.0, 0), 1 << 30, "ANSfold-1, 2^30-symbol Zipf(1.0, 2^20)"),
     "fold2": (M_FOLD, 2, ("zipf", 1 << 20, 1.0, 0), 1 << 30, "ANSfold-2, 2^30-symbol Zipf(1.0, 2^20)"),
     "msb": (M_MSB, 0, ("zipf", 1 << 20, 1.0, 0), 1 << 30, "ANSmsb, 2^30-symbol Zipf(1.0, 2^20)"),
@@ -49,7 +56,10 @@ WORKLOADS = {
 }
 # pseudo-adaptive workloads: symbols per model (every block has its own histogram / model / prelude; no collective)
 PA_MODEL_SYMS = {"c4": 8192}
-DEFAULT_WORKLOAD = "c2"  # the single-GPU configuration BASELINE.json's metric is quoted on (configs[1])
+# Fixed-size jobs: the symbol count is the JOB's, every rank takes 1/N of it ("scaling": "strong").  Everything else
+# keeps the symbol count per GPU ("weak").
+STRONG = {"c5"}
+DEFAULT_WORKLOAD = "c5"  # BASELINE.json configs[4]: the largest single-GPU configuration, the one the targets are stated on
 # Symbols per block (a container parameter).  8192 is the library default; the 1e8-symbol C2 input has only 12 207 such
 # blocks x 4 rANS chains = 48 828 independent chains for 148 SMs, so it runs with 4096 (twice the chains; the size
 # overhead against the reference's whole stream, reported in the line, stays below the 1 % budget).
@@ -220,7 +230,7 @@ def run_reference_arm(args, wl):
     line = {
         "impl": "reference", "metric": METRIC, "value": gbs, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": (enc + dec) / args.steps / 1e6, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "scaling": "strong" if args.workload in STRONG else "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": {"workload": desc, "method": method_label(method, f), "symbols_per_step": per_step,
                    "note": "bounded sample of the workload per step; CPU throughput does not depend on n"},
         "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": 1, "kind": kind,
@@ -236,9 +246,126 @@ def run_reference_arm(args, wl):
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
-def north_star_summary(P, dev, stream, peak, names=("fold1", "ans30"), steps=3):
-    """Device-resident kernel times of the north star's 2^30-symbol targets (ANSfold-1 on Zipf, ANS on
-    geometric(0.01)), block size from b200ans_suggest_block_syms in [8192, 16384]: per kernel ms and fraction of the measured HBM peak."""
+def blob_capacity(codec, method, n, pa=0):
+    """Destination capacity: the library's worst-case bound for small inputs; 3 bytes per symbol (ANS: 4) for the
+    2^30 / 2^32-symbol jobs, whose worst case (7 bytes per symbol) would not fit next to the data (the call fails with
+    B200ANS_E_CAPACITY if the data turned out less compressible, it never overruns)."""
+    bound = codec.pa_bound(method, pa, n) if pa else codec.bound(method, n)
+    if n >= 1 << 28:
+        bound = min(bound, (4 if method == M_INT else 3) * n + (64 << 20))
+    return (bound + 15) // 16 * 16
+
+
+def alg_bytes(n, c):
+    """algorithmic bytes per launch; c = payload bytes per symbol"""
+    return {"histogram": 4.0 * n, "encode": (4.0 + c) * n, "compact": 2.0 * c * n, "decode": (4.0 + c) * n}
+
+
+def block_parity(codec, method, f, d_in, n, d_blob, nbytes, group, world, k=64, seed=0):
+    """Outside the timed region: k random blocks (+ the first and the last) of this rank's container against the
+    REFERENCE coder (oracle/_ref, unmodified headers) run on those blocks with the same global model -- byte for byte
+    -- plus normalised frequencies and prelude.  The reference model is built from the global histogram (counted here
+    with torch.bincount, not with the library) by the reference's own adjust_freqs.  ANSrfold (no histogram
+    constructor in the shim): the reference DECODER, loaded from our prelude, must return the block's symbols."""
+    import torch
+    import torch.distributed as dist
+
+    import _container
+    from _libs import have_reference, reference
+
+    if not have_reference():
+        return {"checked": 0, "note": "oracle/_ref/libansref.so not present"}
+    ref = reference()
+    dev = d_in.device
+    front = d_blob[: min(nbytes, 64 + (64 << 20))].cpu().numpy()
+    hdr = codec_container_info(front)
+    bs, nb, pre = hdr["block_syms"], hdr["n_blocks"], hdr["prelude_bytes"]
+    table_at = 64 + (pre + 3) // 4 * 4
+    payload_at = (table_at + 4 * nb + 15) // 16 * 16
+    if front.size < payload_at:
+        front = d_blob[:payload_at].cpu().numpy()
+    sizes = front[table_at : table_at + 4 * nb].view(np.uint32).astype(np.int64)
+    offs = np.concatenate([[0], np.cumsum((sizes + 15) // 16 * 16)[:-1]])
+    prelude = front[64 : 64 + pre]
+    out = {"blocks": int(nb), "block_syms": int(bs)}
+    model = None
+    if method != M_RFOLD:
+        # the reference's counts: its own mapping (the host restatement is pinned against it), counted by torch
+        if method == M_INT:
+            mx = d_in.max().to(torch.int64).reshape(1)
+            if world > 1:
+                dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
+            nbins = int(mx.item()) + 1
+            sym = d_in
+        else:
+            nbins = 1280 if method == M_MSB else 1 << (f + 9)
+            sym = None
+        bins = torch.zeros(nbins, dtype=torch.int64, device=dev)
+        chunk = 1 << 27
+        for lo in range(0, n, chunk):
+            v = d_in[lo : lo + chunk].to(torch.int64)
+            if method != M_INT:
+                v = fold_symbols_torch(v, method, f)
+            bins += torch.bincount(v, minlength=nbins)[:nbins]
+        if world > 1:
+            dist.all_reduce(bins, op=dist.ReduceOp.SUM, group=group)
+        hbins = bins.cpu().numpy().astype(np.uint64)
+        largest = int(np.nonzero(hbins)[0][-1])
+        model = ref.model_from_hist(method, f, hbins[: largest + 1] if method == M_INT else hbins)
+        frame, nfreqs = model.info()
+        ours_frame, ours_nf = codec.model_nfreqs()
+        out["nfreqs_equal"] = bool(ours_frame == frame and np.array_equal(ours_nf, nfreqs))
+        out["prelude_equal"] = bool(_container.prelude_equal(prelude, model.serialize()))
+        out["frame_size"] = int(frame)
+    dec = ref.model_load(method, f, prelude) if method == M_RFOLD else None
+    rng = np.random.default_rng(seed)
+    pick = sorted(set([0, nb - 1] + [int(x) for x in rng.integers(0, nb, k)]))
+    bad = []
+    for b in pick:
+        lo, hi = b * bs, min(n, (b + 1) * bs)
+        syms = d_in[lo:hi].cpu().numpy().view(np.uint32)
+        pay = d_blob[payload_at + int(offs[b]) : payload_at + int(offs[b]) + int(sizes[b])].cpu().numpy()
+        if model is not None:
+            want = model.encode_block(syms)
+            same = want.size == pay.size and np.array_equal(want, pay)
+        else:
+            same = np.array_equal(dec.decode_block(pay, hi - lo), syms)
+        if not same:
+            bad.append(b)
+    out.update({"checked": len(pick), "mismatched": bad,
+                "how": ("payload bytes == reference encode_symbol/flush_state loop on the block (ans_fold.hpp:250-278), model from the global histogram"
+                        if model is not None else "reference decoder (model loaded from our prelude) returns the block's symbols"),
+                "ok": not bad and out.get("nfreqs_equal", True) and out.get("prelude_equal", True)})
+    return out
+
+
+def codec_container_info(front):
+    import ans_large_alphabet_b200 as P
+
+    return P.host_api().container_info(front)
+
+
+def fold_symbols_torch(v, method, f):
+    """ans_fold_mapping<f> (ans_fold.hpp:38-50) / ans_msb_mapping (ans_msb.hpp:41-50) on an int64 tensor"""
+    import torch
+
+    if method == M_MSB:
+        k = (v > 256).to(torch.int64) + (v > 65536).to(torch.int64) + (v > (1 << 24)).to(torch.int64)
+        return (v >> (8 * k)) + 256 * k
+    thres, step = 1 << (f + 7), 255 << (f - 1)
+    k = torch.zeros_like(v)
+    x = v.clone()
+    for _ in range(3):
+        big = x >= thres
+        x = torch.where(big, x >> 8, x)
+        k += big.to(torch.int64)
+    return x + k * step
+
+
+def north_star_summary(P, dev, stream, peak, names=("fold1", "fold2", "ans30"), steps=3):
+    """Device-resident kernel times of the north star's 2^30-symbol targets (ANSfold-1 / ANSfold-2 on Zipf, ANS on
+    geometric(0.01)), block size from b200ans_suggest_block_syms in [8192, 16384]: per kernel ms and fraction of the
+    measured HBM peak, plus the byte-parity of sampled blocks against the reference."""
     import torch
 
     out = {}
@@ -249,7 +376,7 @@ def north_star_summary(P, dev, stream, peak, names=("fold1", "ans30"), steps=3):
         codec.set_block_syms(block_syms)
         try:
             d_in = generate_device(gen, n, dev, seed=0)
-            d_blob = torch.empty((codec.bound(method, n) + 15) // 16 * 16, dtype=torch.uint8, device=dev)
+            d_blob = torch.empty(blob_capacity(codec, method, n), dtype=torch.uint8, device=dev)
             d_out = torch.empty(n, dtype=torch.int32, device=dev)
             torch.cuda.synchronize(dev)
             acc = {"histogram": 0.0, "encode": 0.0, "compact": 0.0, "decode": 0.0}
@@ -273,11 +400,18 @@ def north_star_summary(P, dev, stream, peak, names=("fold1", "ans30"), steps=3):
                     enc_ms += e0.elapsed_time(e1) / steps
                     dec_ms += e1.elapsed_time(e2) / steps
             c = s1.payload_bytes / n
-            alg = {"histogram": 4.0 * n, "encode": (4.0 + c) * n, "compact": 2.0 * c * n, "decode": (4.0 + c) * n}
+            alg = alg_bytes(n, c)
+            names_k = {"histogram": "histogram_kernel", "encode": s1.encode_kernel.decode(), "compact": "compact_kernel",
+                       "decode": s2.decode_kernel.decode()}
+            with torch.cuda.stream(stream):
+                par = block_parity(codec, method, f, d_in, n, d_blob, nb, None, 1, k=64)
             out[name] = {
                 "workload": desc, "block_syms": block_syms, "roundtrip_ok": bool(torch.equal(d_in, d_out)), "bits_per_symbol": 8.0 * nb / n,
                 "encode_ms": enc_ms, "decode_ms": dec_ms, "encode_gbs": 4.0 * n / (enc_ms * 1e6), "decode_gbs": 4.0 * n / (dec_ms * 1e6),
-                "kernels": {k: {"ms": v, "achieved_gbs": alg[k] / (v * 1e6), "frac": alg[k] / (v * 1e6) / peak} for k, v in acc.items() if v > 0},
+                "encode_pass_frac": (8.0 + c) * n / (enc_ms * 1e6) / peak, "decode_pass_frac": (4.0 + c) * n / (dec_ms * 1e6) / peak,
+                "kernels": {k: {"kernel": names_k[k], "ms": v, "achieved_gbs": alg[k] / (v * 1e6), "frac": alg[k] / (v * 1e6) / peak}
+                            for k, v in acc.items() if v > 0},
+                "parity": par,
             }
             del d_in, d_blob, d_out
         except Exception as e:  # never let the extra block take the headline line down
@@ -286,6 +420,34 @@ def north_star_summary(P, dev, stream, peak, names=("fold1", "ans30"), steps=3):
             codec.close()
         torch.cuda.empty_cache()
     return out
+
+
+def copy_only(stream, dev, h_in, d_in, h_blob, d_blob, h_out, d_out, nbh, reps):
+    """The same bytes as one e2e step and nothing else: 4n in + container out (encode side), container in + 4n out
+    (decode side), page-locked buffers, the two directions of each side on their own streams (PCIe is full duplex).
+    Returns ms per step -- the floor any host-buffer implementation on this box has."""
+    import torch
+
+    side = torch.cuda.Stream(device=dev)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    t0.record(stream)
+    for _ in range(reps):
+        side.wait_stream(stream)
+        with torch.cuda.stream(stream):
+            d_in.copy_(h_in, non_blocking=True)
+        with torch.cuda.stream(side):
+            h_blob[:nbh].copy_(d_blob[:nbh], non_blocking=True)
+        stream.wait_stream(side)
+        side.wait_stream(stream)
+        with torch.cuda.stream(stream):
+            d_blob[:nbh].copy_(h_blob[:nbh], non_blocking=True)
+        with torch.cuda.stream(side):
+            h_out.copy_(d_out, non_blocking=True)
+        stream.wait_stream(side)
+    t1.record(stream)
+    torch.cuda.synchronize(dev)
+    return t0.elapsed_time(t1) / reps
 
 
 def run_ours(args, wl):
@@ -310,6 +472,11 @@ def run_ours(args, wl):
 
     if args.symbols:
         n = args.symbols
+    strong = args.workload in STRONG and not args.symbols
+    n_job = n * world if not strong else n
+    if strong:
+        # one fixed job, contiguous shards of whole blocks' worth of symbols; 2^32 / N is exact for N = 1, 2, 4, 8
+        n = n_job // world
     stream = torch.cuda.Stream(device=dev)
     codec = P.Codec(device=local, block_syms=args.block_syms or 8192, stream=stream.cuda_stream)
     if not args.block_syms:
@@ -319,10 +486,9 @@ def run_ours(args, wl):
         block_rule = "b200ans_suggest_block_syms(n, 8192, 16384)"
     else:
         block_rule = "fixed"
-    # weak scaling: every rank holds a full-size shard of the (N x larger) job
+    pa = PA_MODEL_SYMS.get(args.workload, 0)
     d_in = generate_device(gen, n, dev, seed=rank)
-    bound = codec.pa_bound(method, PA_MODEL_SYMS[args.workload], n) if args.workload in PA_MODEL_SYMS else codec.bound(method, n)
-    d_blob = torch.empty((bound + 15) // 16 * 16, dtype=torch.uint8, device=dev)
+    d_blob = torch.empty(blob_capacity(codec, method, n, pa), dtype=torch.uint8, device=dev)
     d_out = torch.empty(n, dtype=torch.int32, device=dev)
     torch.cuda.synchronize(dev)
 
@@ -337,7 +503,6 @@ def run_ours(args, wl):
         torch.cuda.synchronize(dev)
 
     kern = {"histogram": 0.0, "encode": 0.0, "compact": 0.0, "decode": 0.0, "model_host": 0.0}
-    pa = PA_MODEL_SYMS.get(args.workload, 0)
 
     def enc_dev():
         if pa:  # per-block models: nothing is shared between ranks
@@ -365,7 +530,7 @@ def run_ours(args, wl):
             acc["compact"] += s.ms_compact
             acc["decode"] += s2.ms_decode
             acc["model_host"] += enc_model + s2.ms_model
-        return nb, s2
+        return nb, s, s2
 
     # ---- device-resident timing -------------------------------------------------------------
     for _ in range(args.warmup):
@@ -376,25 +541,37 @@ def run_ours(args, wl):
         time.sleep(0.25)
     launches0 = codec.stats().launches
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    # separate encode / decode split, measured with events on the codec's stream
     barrier()
     t_wall0 = time.time()
     with torch.cuda.stream(stream):
         ev0.record(stream)
     nb = 0
     for _ in range(args.steps):
-        nb, st = device_step(kern)
+        nb, st1, st2 = device_step(kern)
     with torch.cuda.stream(stream):
         ev1.record(stream)
     barrier()
     t_wall1 = time.time()
     ms_total = ev0.elapsed_time(ev1)
     launches = codec.stats().launches - launches0
+    # A timed region shorter than a few nvidia-smi periods: every rank keeps the same step running (untimed) for about
+    # 1.5 s so that the sampler sees the clocks under this load.  The count comes from the max-over-ranks step time, so
+    # all ranks agree on it (the sharded step holds a collective).
+    tmax = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX, group=group)
+    if float(tmax.item()) < 1500.0:
+        extra = int(min(400, math.ceil(1500.0 / max(float(tmax.item()) / args.steps, 0.05))))
+        for _ in range(extra):
+            device_step(None)
+        torch.cuda.synchronize(dev)
+        t_wall1 = time.time()
     clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
     ok = bool(torch.equal(d_in, d_out))
     st = codec.stats()
-    payload_bytes, total_bytes, n_blocks = st.payload_bytes, nb, st.n_blocks
-    frame, nsyms, prelude_bytes = st.frame_size, st.n_symbols_model, st.prelude_bytes
+    payload_bytes, total_bytes, n_blocks = st1.payload_bytes, nb, st1.n_blocks
+    frame, nsyms, prelude_bytes = st1.frame_size, st1.n_symbols_model, st1.prelude_bytes
+    enc_name, dec_name = st1.encode_kernel.decode(), st2.decode_kernel.decode()
 
     # encode-only / decode-only split (events around each pass)
     enc_ms = dec_ms = 0.0
@@ -413,6 +590,15 @@ def run_ours(args, wl):
         dec_ms += e1.elapsed_time(e2)
     enc_ms /= reps
     dec_ms /= reps
+
+    # ---- byte parity of this step's container against the reference (outside every timed region) ----
+    parity = None
+    if not pa and not args.no_parity:
+        with torch.cuda.stream(stream):
+            if world > 1:  # the staged path leaves the global model in the codec; re-encode so the check sees this step's bytes
+                nb = enc_dev()
+            parity = block_parity(codec, method, f, d_in, n, d_blob, nb, group, world, k=64, seed=rank)
+        torch.cuda.synchronize(dev)
 
     # ---- end to end: pinned host buffers through the host entry points ------------------------
     h_in = torch.empty(n, dtype=torch.int32).pin_memory()
@@ -442,9 +628,9 @@ def run_ours(args, wl):
     for _ in range(min(args.warmup, 2)):
         e2e_step()
     e2e_steps = max(1, min(args.steps, 5))
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     tw0 = time.perf_counter()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(stream):
         f0.record(stream)
     for _ in range(e2e_steps):
@@ -452,17 +638,27 @@ def run_ours(args, wl):
     with torch.cuda.stream(stream):
         f1.record(stream)
     barrier()
-    e2e_ms = max(f0.elapsed_time(f1), (time.perf_counter() - tw0) * 1e3 * 0.0)  # device clock
+    e2e_wall_ms = (time.perf_counter() - tw0) * 1e3  # host wall clock, barrier to barrier: what a caller waits for
+    e2e_dev_ms = f0.elapsed_time(f1)
+    e2e_ms = max(e2e_wall_ms, e2e_dev_ms)
     e2e_ok = bool(torch.equal(h_in, h_out))
+    d_out.zero_()
+    barrier()
+    copy_ms = copy_only(stream, dev, h_in, d_in, h_blob, d_blob, h_out, d_out, nbh, reps=min(3, e2e_steps))
 
     # ---- reduce over ranks: MAX time ----------------------------------------------------------
-    t = torch.tensor([ms_total, e2e_ms, enc_ms, dec_ms], dtype=torch.float64, device=dev)
-    okt = torch.tensor([int(ok and e2e_ok)], dtype=torch.int32, device=dev)
+    t = torch.tensor([ms_total, e2e_ms, enc_ms, dec_ms, copy_ms, e2e_dev_ms], dtype=torch.float64, device=dev)
+    par_ok = True if parity is None else bool(parity.get("ok", True))
+    okt = torch.tensor([int(ok and e2e_ok), int(par_ok)], dtype=torch.int32, device=dev)
+    kt = torch.tensor([kern[k] for k in ("histogram", "encode", "compact", "decode", "model_host")], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         dist.all_reduce(okt, op=dist.ReduceOp.MIN, group=group)
-    ms_total, e2e_ms, enc_ms, dec_ms = (float(x) for x in t.tolist())
-    all_ok = bool(okt.item())
+        dist.all_reduce(kt, op=dist.ReduceOp.MAX, group=group)
+    ms_total, e2e_ms, enc_ms, dec_ms, copy_ms, e2e_dev_ms = (float(x) for x in t.tolist())
+    all_ok, par_all_ok = bool(okt[0].item()), bool(okt[1].item())
+    for k, v in zip(("histogram", "encode", "compact", "decode", "model_host"), kt.tolist()):
+        kern[k] = float(v)
 
     if rank == 0:
         ms_step = ms_total / args.steps
@@ -471,21 +667,23 @@ def run_ours(args, wl):
         c = payload_bytes / n
         peak, peak_src = measured_peak()
         per = {k: v / args.steps for k, v in kern.items()}
-        alg = {"histogram": 4.0 * n, "encode": (4.0 + c) * n, "compact": 2.0 * c * n, "decode": (4.0 + c) * n}
+        alg = alg_bytes(n, c)
+        knames = {"histogram": "histogram_kernel", "encode": enc_name, "compact": "compact_kernel", "decode": dec_name}
         kernels = {}
         for k in ("histogram", "encode", "compact", "decode"):
             if per[k] > 0:
                 a = alg[k] / (per[k] * 1e6)
-                kernels[k] = {"ms": per[k], "algorithmic_bytes": alg[k], "achieved_gbs": a, "frac": a / peak}
-        dom = max(("encode", "decode", "histogram", "compact"), key=lambda k: per[k])
-        roofline = {"bound": "hbm", "kernel": dom + "_kernel", "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
+                kernels[k] = {"kernel": knames[k], "ms": per[k], "algorithmic_bytes": alg[k], "achieved_gbs": a, "frac": a / peak}
+        dom = max(kernels, key=lambda k: per[k])
+        roofline = {"bound": "hbm", "kernel": knames[dom], "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
                     "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_symbol": alg[dom] / n, "ms_per_launch": per[dom]}
+                    "algorithmic_bytes_per_symbol": alg[dom] / n, "ms_per_launch": per[dom],
+                    "note": "per launch on one GPU (max over ranks); algorithmic bytes = SURVEY 8(d) x the rank's symbols"}
         # DRAM bytes of that kernel from the committed `ncu --set full` capture of this workload (tools/ncu_traffic.py)
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
                 tr = json.load(fh).get(args.workload, {}).get(dom)
-            if tr and not args.symbols:
+            if tr and not args.symbols and world == 1:
                 roofline["traffic"] = tr["dram_bytes_per_launch"]
                 roofline["traffic_source"] = f"ncu dram__bytes_read.sum + dram__bytes_write.sum, {tr['kernel']}, profiles/ ({tr['source']})"
                 roofline["traffic_over_algorithmic"] = tr["dram_bytes_per_launch"] / alg[dom]
@@ -493,7 +691,6 @@ def run_ours(args, wl):
             pass
         # CPU baseline on a bounded sample of the same workload (rank 0, N = 1 only)
         cpu = None
-        bps_sample = None
         if world == 1 and not args.no_cpu:
             ns = min(n, args.cpu_sample)
             sample = d_in[:ns].cpu().numpy().view(np.uint32)
@@ -506,22 +703,28 @@ def run_ours(args, wl):
         d2h = nbh + 4 * n
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
-            "config": {"workload": desc, "method": method_label(method, f), "symbols_per_gpu": n,
+            "config": {"workload": desc, "method": method_label(method, f), "symbols_job": n_job, "symbols_per_gpu": n,
                        "block_syms": pa or args.block_syms, "block_syms_rule": "one model per block" if pa else block_rule, "n_blocks_per_gpu": n_blocks,
                        "l2": "inputs (%.0f MB per GPU) larger than the 126 MB L2; no flush" % (4.0 * n / 1e6),
                        "model": ("pseudo-adaptive: one model per block, normalised on the device, no collective" if pa else
                                  "semi-static, global histogram" + (" via NCCL all-reduce" if world > 1 else "")),
-                       "frame_size": frame, "model_symbols": nsyms},
+                       "frame_size": frame, "model_symbols": nsyms,
+                       "frame_note": ("jobs of 2^31 symbols and more: the reference's 32-bit accumulators in cross_entropy (util.hpp:288-289) "
+                                      "change adjust_freqs' stopping rule; the frame is the reference's for this histogram (SURVEY 3.8)"
+                                      if n_job >= 1 << 31 else None)},
             "encode_gbs": 4.0 * n * world / (enc_ms * 1e6), "decode_gbs": 4.0 * n * world / (dec_ms * 1e6),
             "encode_ms": enc_ms, "decode_ms": dec_ms,
             "bits_per_symbol": 8.0 * total_bytes / n, "payload_bytes_per_symbol": c, "prelude_bytes": prelude_bytes,
-            "roundtrip_ok": all_ok,
+            "roundtrip_ok": all_ok, "parity": dict(parity or {}, all_ranks_ok=par_all_ok),
             "roofline": roofline, "kernels": kernels, "host_model_ms_per_step": per["model_host"],
             "cpu_baseline": cpu,
             "e2e": {"value": gb_step / (e2e_ms / e2e_steps / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+                    "clock": "host wall clock, barrier to barrier, max over ranks", "device_ms_per_step": e2e_dev_ms / e2e_steps,
+                    "copy_only_ms": copy_ms, "copy_only_gbs": gb_step / (copy_ms / 1e3),
+                    "copy_only_note": "the same bytes per step with cudaMemcpyAsync only, both directions overlapped, all ranks at once",
                     "api": "b200ans_pa_compress + b200ans_pa_decompress (host buffers, pinned)" if pa
                     else "b200ans_compress + b200ans_decompress (host buffers, pinned)" if world == 1
                     else "pinned H2D + staged device API + D2H per rank"},
@@ -537,6 +740,8 @@ def run_ours(args, wl):
         dist.destroy_process_group()
     if not all_ok:
         raise SystemExit("bench.py: round trip FAILED")
+    if not par_all_ok:
+        raise SystemExit("bench.py: block parity against the reference FAILED")
 
 
 _REAL_STDOUT = None
@@ -570,6 +775,7 @@ def main():
     ap.add_argument("--no-targets", action="store_true", help="skip the 2^30-symbol north-star summary")
     ap.add_argument("--cpu-sample", type=int, default=100_000_000)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the byte comparison of sampled blocks with the reference")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]

@@ -85,6 +85,8 @@ typedef struct b200ans_stats {
     uint64_t prelude_bytes;
     uint64_t payload_bytes; /* sum of block payload bytes (unpadded)           */
     uint64_t total_bytes;   /* whole container                                 */
+    char encode_kernel[32]; /* block encoder / decoder the most recent call launched   */
+    char decode_kernel[32]; /* (as ncu names them: "lpb3_encode_kernel", ...)          */
 } b200ans_stats;
 
 /* What a container says about itself (the reference stores neither n nor the byte count, methods.hpp:541-546). */

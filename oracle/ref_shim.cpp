@@ -105,6 +105,37 @@ struct ref_model {
 
 template <class T> static void del(void* p) { delete static_cast<T*>(p); }
 
+// The same models from a HISTOGRAM instead of the input (2^30 / 2^32-symbol jobs, where a CPU counting pass would take
+// minutes and the counts already exist): the members create() fills after its counting loop -- ans_fold.hpp:79-92,
+// ans_msb.hpp:86-100, ans_int.hpp:50-66 -- are public, so they are filled here in the same order with the reference's
+// own adjust_freqs; encode_symbol / flush_state / serialize are then the reference's.  `bins` must hold the
+// reference's counts: 2^(f+9) bins (FOLD), 1280 (MSB), max value + 1 (INT).
+template <class Enc> static Enc* enc_from_hist(const uint64_t* bins, size_t nbins, bool u16, bool skip_absent)
+{
+    auto* model = new Enc();
+    std::vector<uint64_t> freqs(bins, bins + nbins);
+    uint32_t max_sym = 0;
+    for (size_t s = 0; s < nbins; s++)
+        if (freqs[s])
+            max_sym = uint32_t(s);
+    model->nfreqs = adjust_freqs(freqs, max_sym, u16);
+    model->frame_size = std::accumulate(std::begin(model->nfreqs), std::end(model->nfreqs), 0);
+    uint64_t cur_base = 0;
+    const uint64_t tmp = constants::K * constants::RADIX;
+    model->table.resize(max_sym + 1);
+    for (size_t sym = 0; sym < model->nfreqs.size(); sym++) {
+        if (skip_absent && model->nfreqs[sym] == 0)
+            continue;
+        model->table[sym].freq = model->nfreqs[sym];
+        model->table[sym].base = cur_base;
+        model->table[sym].sym_upper_bound = tmp * model->nfreqs[sym];
+        cur_base += model->nfreqs[sym];
+    }
+    model->lower_bound = constants::K * model->frame_size;
+    return model;
+}
+
+
 extern "C" {
 
 // ---- whole-stream reference coders (methods.hpp:484-567 call exactly these) ----------
@@ -236,6 +267,24 @@ ref_model* ref_model_create(int method, uint32_t f, const uint32_t* in, size_t n
     case M_RFOLD:
         switch (f) {
 #define C(F) case F: m->enc = new ans_reorder_fold_encode<F>(ans_reorder_fold_encode<F>::create(in, n)); return m;
+            C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
+#undef C
+        }
+        break;
+    }
+    delete m;
+    return nullptr;
+}
+
+ref_model* ref_model_from_hist(int method, uint32_t f, const uint64_t* bins, size_t nbins)
+{
+    auto* m = new ref_model { method, f, nullptr, nullptr };
+    switch (method) {
+    case M_INT: m->enc = enc_from_hist<ans_int_encode>(bins, nbins, false, true); return m;
+    case M_MSB: m->enc = enc_from_hist<ans_msb_encode>(bins, nbins, true, false); return m;
+    case M_FOLD:
+        switch (f) {
+#define C(F) case F: m->enc = enc_from_hist<ans_fold_encode<F>>(bins, nbins, true, false); return m;
             C(1) C(2) C(3) C(4) C(5) C(6) C(7) C(8)
 #undef C
         }

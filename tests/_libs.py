@@ -173,6 +173,17 @@ class _CpuCodec:
         assert h
         return _Model(self, h)
 
+    def model_from_hist(self, method, f, bins):
+        """reference shim only: the encoder model create() would build for an input with these counts (2^30 / 2^32-symbol
+        jobs: the counts exist, a CPU counting pass would take minutes); ANS / ANSmsb / ANSfold-f"""
+        fn = self._f("model_from_hist")
+        fn.restype = C.c_void_p
+        fn.argtypes = [C.c_int, C.c_uint32, u64p, C.c_size_t]
+        bins = np.ascontiguousarray(bins, dtype=np.uint64)
+        h = fn(method, f, ptr(bins, u64p), bins.size)
+        assert h
+        return _Model(self, h)
+
     def model_load(self, method, f, prelude):
         buf = np.zeros(len(prelude) + 16, dtype=np.uint8)
         buf[: len(prelude)] = prelude

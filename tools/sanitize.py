@@ -41,8 +41,6 @@ def main():
     cases.append(("nopure-ANS", P.PATH_AUTO, M_INT, 0, geom, {"B200ANS_PURE": "0"}))
     cases.append(("nointdec-ANS", P.PATH_GROUP, M_INT, 0, geom, {"B200ANS_NO_INTDEC": "1"}))
     cases.append(("nopipe-fold1", P.PATH_AUTO, M_FOLD, 1, zipf, {"B200ANS_NO_PIPELINE": "1"}))
-    cases.append(("wide-fold1", P.PATH_LPB, M_FOLD, 1, zipf, {"B200ANS_L3_ENC_WIDE": "1"}))
-    cases.append(("wide-ANS", P.PATH_LPB, M_INT, 0, geom, {"B200ANS_L3_ENC_WIDE": "1"}))
     for label, path, method, f, data, env in cases:
         if only and only not in label:
             continue
