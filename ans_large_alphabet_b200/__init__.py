@@ -17,6 +17,7 @@ from ._capi import (  # noqa: F401
     PATH_LPB,
     Stats,
     build_library,
+    comm_unique_id,
     host_api,
     library_path,
     load_library,

@@ -31,6 +31,7 @@ class Stats(C.Structure):
         ("launches", C.c_uint64), ("frame_size", C.c_uint64), ("n_symbols_model", C.c_uint32),
         ("n_blocks", C.c_uint32), ("prelude_bytes", C.c_uint64), ("payload_bytes", C.c_uint64),
         ("total_bytes", C.c_uint64), ("encode_kernel", C.c_char * 32), ("decode_kernel", C.c_char * 32),
+        ("ms_allreduce", C.c_float), ("model_flags", C.c_uint32),
     ]
 
 
@@ -77,6 +78,14 @@ SIGNATURES = {
     "b200ans_encode_blocks_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_block_stride": (C.c_int, [C.c_void_p, C.c_int, szp]),
     "b200ans_decode_blocks_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200ans_comm_unique_id": (C.c_int, [u8p]),
+    "b200ans_comm_init": (C.c_int, [C.c_void_p, u8p, C.c_int, C.c_int]),
+    "b200ans_comm_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "b200ans_comm_release": (C.c_int, [C.c_void_p]),
+    "b200ans_allreduce_hist": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200ans_compress_sharded_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
+    "b200ans_compress_sharded": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
+    "b200ans_scale_freqs": (C.c_int, [u32p, u64p, C.c_size_t, u32p, C.c_size_t, C.c_int64, C.c_uint64, C.POINTER(C.c_int)]),
     "b200ans_adjust_freqs": (C.c_int, [u64p, C.c_size_t, C.c_uint32, C.c_int, C.c_uint32, u32p]),
     "b200ans_serialize_interp": (C.c_int, [u32p, C.c_size_t, C.c_uint64, u8p, C.c_size_t, szp]),
     "b200ans_load_interp": (C.c_int, [u8p, u32p, C.c_size_t, szp, szp]),
@@ -119,6 +128,15 @@ def load_library():
     return _LIB
 
 
+def comm_unique_id():
+    """a fresh NCCL unique id (128 bytes, numpy uint8): rank 0 calls this and hands the bytes to every rank"""
+    uid = np.zeros(128, dtype=np.uint8)
+    rc = load_library().b200ans_comm_unique_id(uid.ctypes.data_as(u8p))
+    if rc:
+        raise B200AnsError(rc, "NCCL unavailable (libnccl.so.2)")
+    return uid
+
+
 def suggest_block_syms(n, lo=8192, hi=16384):
     """b200ans_suggest_block_syms without a context (148 SMs assumed): host arithmetic only"""
     return int(load_library().b200ans_suggest_block_syms(None, n, lo, hi))
@@ -146,6 +164,19 @@ class _HostApi:
         if rc:
             raise B200AnsError(rc, "adjust_freqs")
         return out
+
+    def scale_freqs(self, freqs, mapping, frame, freq_sum=None):
+        """scale_freqs (ans_util.hpp:77-95): (S, fits) for the counts `freqs`, symbols visited in `mapping` order"""
+        freqs = np.ascontiguousarray(freqs, dtype=np.uint64)
+        mapping = np.ascontiguousarray(mapping, dtype=np.uint32)
+        out = np.zeros(freqs.size, dtype=np.uint32)
+        fits = C.c_int()
+        total = int(freqs.sum()) if freq_sum is None else int(freq_sum)
+        rc = self.lib.b200ans_scale_freqs(_p(out, u32p), _p(freqs, u64p), freqs.size, _p(mapping, u32p), mapping.size, int(frame),
+                                          total, C.byref(fits))
+        if rc:
+            raise B200AnsError(rc, "scale_freqs")
+        return out, bool(fits.value)
 
     def serialize_interp(self, nfreqs, frame_size):
         nfreqs = np.ascontiguousarray(nfreqs, dtype=np.uint32)
@@ -335,6 +366,32 @@ class Codec:
 
     def decompress_device(self, method, f, d_dst, n, d_src, nbytes):
         self._check(self.lib.b200ans_decompress_device(self.h, method, f, d_dst, n, d_src, nbytes))
+
+    # ---- multi-GPU (one context per GPU; NCCL is opened by the library) ---------------------------
+    def comm_init(self, unique_id, rank, world):
+        """collective: ncclCommInitRank with the 128-byte id rank 0 got from comm_unique_id()"""
+        uid = np.ascontiguousarray(unique_id, dtype=np.uint8)
+        assert uid.size == 128
+        self._check(self.lib.b200ans_comm_init(self.h, _p(uid, u8p), rank, world))
+
+    def comm_attach(self, nccl_comm, rank, world):
+        self._check(self.lib.b200ans_comm_attach(self.h, nccl_comm, rank, world))
+
+    def comm_release(self):
+        self._check(self.lib.b200ans_comm_release(self.h))
+
+    def allreduce_hist(self, d_bins, nbins, d_max=None):
+        self._check(self.lib.b200ans_allreduce_hist(self.h, d_bins, nbins, d_max))
+
+    def compress_sharded_device(self, method, f, d_dst, cap, d_src, n):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_compress_sharded_device(self.h, method, f, d_dst, cap, d_src, n, C.byref(nb)))
+        return nb.value
+
+    def compress_sharded_ptr(self, method, f, dst_ptr, cap, src_ptr, n):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_compress_sharded(self.h, method, f, dst_ptr, cap, src_ptr, n, C.byref(nb)))
+        return nb.value
 
     def max_device(self, d_src, n, d_max):
         self._check(self.lib.b200ans_max_device(self.h, d_src, n, d_max))

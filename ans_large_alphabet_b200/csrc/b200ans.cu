@@ -3,12 +3,16 @@
 // decoder run on the GPU or the call fails.
 #include "../../include/b200ans.h"
 
+#include <dlfcn.h>
+
 #include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstdio>
 #include <cstring>
+#include <new>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -74,7 +78,60 @@ constexpr uint32_t kFlagPseudoAdaptive = 1u; // Header::flags bit 0: one model p
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// ---- NCCL, opened at run time (no link-time dependency: the library loads on machines without NCCL, and a process
+// that already holds libnccl.so.2 -- torch's copy, say -- shares it).  Only the handful of entry points the histogram
+// exchange needs; enum values are NCCL 2.x's (nccl.h: ncclSum = 0, ncclMax = 2, ncclUint32 = 3, ncclUint64 = 5).
+struct NcclUniqueId {
+    char internal[B200ANS_COMM_ID_BYTES];
+};
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(NcclUniqueId*) = nullptr;
+    int (*CommInitRank)(void**, int, NcclUniqueId, int) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool ok = false;
+};
+constexpr int kNcclSum = 0, kNcclMax = 2, kNcclUint32 = 3, kNcclUint64 = 5;
+
+const NcclApi& nccl_api()
+{
+    static const NcclApi api = []() {
+        NcclApi a;
+        const char* override_path = std::getenv("B200ANS_NCCL_LIB");
+        for (const char* name : { override_path, "libnccl.so.2", "libnccl.so" }) {
+            if (!name || !*name)
+                continue;
+            a.lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+            if (a.lib)
+                break;
+        }
+        if (!a.lib)
+            return a;
+        auto sym = [&](const char* n) { return dlsym(a.lib, n); };
+        a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(sym("ncclGetUniqueId"));
+        a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(sym("ncclCommInitRank"));
+        a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(sym("ncclCommDestroy"));
+        a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(sym("ncclAllReduce"));
+        a.GroupStart = reinterpret_cast<decltype(a.GroupStart)>(sym("ncclGroupStart"));
+        a.GroupEnd = reinterpret_cast<decltype(a.GroupEnd)>(sym("ncclGroupEnd"));
+        a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
+        a.ok = a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllReduce && a.GroupStart && a.GroupEnd && a.GetErrorString;
+        return a;
+    }();
+    return api;
+}
+
 } // namespace
+
+// No C++ exception crosses the C ABI (include/b200ans.h): every extern "C" function is a function-try-block.
+#define B200ANS_CATCH_INT                                                                                              \
+    catch (const std::bad_alloc&) { return B200ANS_E_NOMEM; }                                                          \
+    catch (const std::length_error&) { return B200ANS_E_NOMEM; }                                                       \
+    catch (...) { return B200ANS_E_INTERNAL; }
 
 struct b200ans_ctx {
     int device = 0;
@@ -150,10 +207,23 @@ struct b200ans_ctx {
     uint32_t dec_n_present = 0;
     uint32_t dec_dense = 0;
 
+    // multi-GPU: the communicator the histogram exchange runs on (b200ans_comm_init / _attach)
+    void* comm = nullptr;
+    cudaEvent_t ev_ar[2] {};
+    bool ar_timed = false;
+    bool own_comm = false;
+    int comm_rank = 0, comm_world = 1;
+
     int fail(int code, const std::string& what)
     {
         err = what;
         return code;
+    }
+    int nccl_fail(int e, const char* where)
+    {
+        const NcclApi& a = nccl_api();
+        err = std::string(where) + ": " + (a.ok ? a.GetErrorString(e) : "NCCL not loaded");
+        return B200ANS_E_NCCL;
     }
     int cuda_fail(cudaError_t e, const char* where)
     {
@@ -237,7 +307,7 @@ double now_ms()
 // context
 // ==========================================================================================
 extern "C" int b200ans_create(b200ans_ctx** out, int device, void* stream)
-{
+try {
     if (!out)
         return B200ANS_E_ARG;
     *out = nullptr;
@@ -268,6 +338,8 @@ extern "C" int b200ans_create(b200ans_ctx** out, int device, void* stream)
     }
     for (auto& e : c->ev)
         cudaEventCreate(&e);
+    for (auto& e : c->ev_ar)
+        cudaEventCreate(&e);
     if (cudaHostAlloc(reinterpret_cast<void**>(&c->pinned), b200ans_ctx::kPinnedBins + 64, cudaHostAllocDefault) != cudaSuccess)
         c->pinned = nullptr;
     if (!c->pinned || c->small.reserve(256) != cudaSuccess) {
@@ -277,6 +349,7 @@ extern "C" int b200ans_create(b200ans_ctx** out, int device, void* stream)
     *out = c;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" void b200ans_destroy(b200ans_ctx* c)
 {
@@ -288,6 +361,9 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
              &c->dec_slots, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys })
         b->release();
     for (auto& e : c->ev)
+        if (e)
+            cudaEventDestroy(e);
+    for (auto& e : c->ev_ar)
         if (e)
             cudaEventDestroy(e);
     for (auto& e : c->ev_in)
@@ -304,13 +380,15 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
         cudaFreeHost(c->pinned);
     if (c->pa_pinned)
         cudaFreeHost(c->pa_pinned);
+    if (c->comm && c->own_comm && nccl_api().ok)
+        nccl_api().CommDestroy(c->comm);
     if (c->own_stream)
         cudaStreamDestroy(c->stream);
     delete c;
 }
 
 extern "C" int b200ans_set_block_syms(b200ans_ctx* c, uint32_t block_syms)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (block_syms != 0 && (block_syms % 128 != 0 || block_syms > (1u << 24)))
@@ -318,6 +396,7 @@ extern "C" int b200ans_set_block_syms(b200ans_ctx* c, uint32_t block_syms)
     c->block_syms = block_syms;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" uint32_t b200ans_suggest_block_syms(const b200ans_ctx* c, size_t n, uint32_t lo, uint32_t hi)
 {
@@ -347,7 +426,7 @@ extern "C" uint32_t b200ans_suggest_block_syms(const b200ans_ctx* c, size_t n, u
 }
 
 extern "C" int b200ans_set_kernel_path(b200ans_ctx* c, int path)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (path != B200ANS_PATH_AUTO && path != B200ANS_PATH_GROUP && path != B200ANS_PATH_LPB)
@@ -355,9 +434,10 @@ extern "C" int b200ans_set_kernel_path(b200ans_ctx* c, int path)
     c->kernel_path = path;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_container_info(const uint8_t* src, size_t src_bytes, b200ans_container* out)
-{
+try {
     if (!src || !out)
         return B200ANS_E_ARG;
     if (src_bytes < B200ANS_HEADER_BYTES)
@@ -378,9 +458,10 @@ extern "C" int b200ans_container_info(const uint8_t* src, size_t src_bytes, b200
         : align_up(B200ANS_HEADER_BYTES + align_up(h.prelude_bytes, 4) + size_t(h.n_blocks) * 4, 16) + h.payload_bytes;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_set_h_approx(b200ans_ctx* c, uint32_t h_approx)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (h_approx == 0 || h_approx > 1000)
@@ -388,14 +469,16 @@ extern "C" int b200ans_set_h_approx(b200ans_ctx* c, uint32_t h_approx)
     c->h_approx = h_approx;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_get_stats(const b200ans_ctx* c, b200ans_stats* out)
-{
+try {
     if (!c || !out)
         return B200ANS_E_ARG;
     *out = c->stats;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" const char* b200ans_last_error(const b200ans_ctx* c) { return c ? c->err.c_str() : "null context"; }
 
@@ -409,6 +492,9 @@ extern "C" const char* b200ans_strerror(int code)
     case B200ANS_E_DOMAIN: return "input outside the coder's valid domain";
     case B200ANS_E_FORMAT: return "not a b200ans container";
     case B200ANS_E_STATE: return "call sequence error";
+    case B200ANS_E_NCCL: return "NCCL unavailable or a collective failed";
+    case B200ANS_E_NOMEM: return "host allocation failed";
+    case B200ANS_E_INTERNAL: return "internal error (exception stopped at the ABI boundary)";
     }
     return "unknown error";
 }
@@ -443,7 +529,7 @@ extern "C" size_t b200ans_compress_bound(const b200ans_ctx* c, int method, size_
 // ==========================================================================================
 extern "C" int b200ans_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_t largest_sym, int require_u16,
     uint32_t H_approx, uint32_t* out)
-{
+try {
     if (!freqs || !out || largest_sym >= nbins)
         return B200ANS_E_ARG;
     std::vector<uint64_t> F(freqs, freqs + nbins);
@@ -451,10 +537,29 @@ extern "C" int b200ans_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_
     std::copy(s.begin(), s.end(), out);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
+
+// scale_freqs (ans_util.hpp:77-95)
+extern "C" int b200ans_scale_freqs(uint32_t* S, const uint64_t* F, size_t nbins, const uint32_t* mapping, size_t sigma,
+    int64_t M, uint64_t freq_sum, int* fits)
+try {
+    if (!S || !F || !mapping || !fits || sigma > nbins)
+        return B200ANS_E_ARG;
+    for (size_t r = 0; r < sigma; r++)
+        if (mapping[r] >= nbins)
+            return B200ANS_E_ARG;
+    std::vector<uint32_t> s(S, S + nbins), map(mapping, mapping + sigma);
+    const std::vector<uint64_t> f(F, F + nbins);
+    const bool failed = scale_freqs(s, f, map, M, sigma, size_t(freq_sum));
+    std::copy(s.begin(), s.end(), S);
+    *fits = failed ? 0 : 1;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_serialize_interp(const uint32_t* nfreqs, size_t count, uint64_t frame_size, uint8_t* dst,
     size_t capacity, size_t* out_bytes)
-{
+try {
     if (!nfreqs || !dst || !out_bytes || count == 0)
         return B200ANS_E_ARG;
     if (capacity < 8 * count + 16)
@@ -465,9 +570,10 @@ extern "C" int b200ans_serialize_interp(const uint32_t* nfreqs, size_t count, ui
     *out_bytes = size_t(p - dst);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_load_interp(const uint8_t* src, uint32_t* dst, size_t capacity, size_t* out_count, size_t* consumed)
-{
+try {
     if (!src || !out_count)
         return B200ANS_E_ARG;
     const uint8_t* p = src;
@@ -481,17 +587,19 @@ extern "C" int b200ans_load_interp(const uint8_t* src, uint32_t* dst, size_t cap
     std::copy(v.begin(), v.end(), dst);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_interp_encode(uint32_t* dst, const uint32_t* in, size_t n, size_t universe, size_t* out_bytes)
-{
+try {
     if (!dst || (!in && n) || !out_bytes)
         return B200ANS_E_ARG;
     *out_bytes = interp_encode(dst, in, n, universe);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_interp_decode(const uint32_t* src, uint32_t* out, size_t n, size_t universe, size_t* words_read)
-{
+try {
     if (!src || (!out && n))
         return B200ANS_E_ARG;
     const size_t w = interp_decode(src, out, n, universe);
@@ -499,6 +607,7 @@ extern "C" int b200ans_interp_decode(const uint32_t* src, uint32_t* out, size_t 
         *words_read = w;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" uint32_t b200ans_fold_map(uint32_t f, uint32_t x, uint32_t* nbytes)
 {
@@ -620,7 +729,7 @@ __global__ void __launch_bounds__(512) max_kernel(const uint32_t* __restrict__ i
 } // namespace
 
 extern "C" int b200ans_max_device(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t* d_max)
-{
+try {
     if (!c || !d_src || !d_max || (reinterpret_cast<uintptr_t>(d_src) & 15))
         return c ? c->fail(B200ANS_E_ARG, "max: null or unaligned pointer") : B200ANS_E_ARG;
     CU(c, cudaSetDevice(c->device));
@@ -631,10 +740,11 @@ extern "C" int b200ans_max_device(b200ans_ctx* c, const uint32_t* d_src, size_t 
     CU(c, cudaGetLastError());
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_histogram_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n,
     uint64_t* d_bins, size_t nbins)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!d_src || !d_bins || !valid_method(method, f) || (reinterpret_cast<uintptr_t>(d_src) & 15))
@@ -642,13 +752,14 @@ extern "C" int b200ans_histogram_device(b200ans_ctx* c, int method, uint32_t f, 
     CU(c, cudaSetDevice(c->device));
     return histogram_dispatch(c, method, f, d_src, n, d_bins, nbins, c->d_max());
 }
+B200ANS_CATCH_INT
 
 // As b200ans_histogram_device, and the largest raw value of the input goes to *d_max (device, zeroed here).  Values
 // whose bin is beyond nbins are not counted, so a caller that guesses the alphabet (plain ANS: ans_int.hpp:42-49
 // takes the maximum first) counts optimistically in ONE pass and looks at the maximum afterwards.
 extern "C" int b200ans_histogram_max_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n,
     uint64_t* d_bins, size_t nbins, uint32_t* d_max)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!d_src || !d_bins || !d_max || !valid_method(method, f) || (reinterpret_cast<uintptr_t>(d_src) & 15))
@@ -657,6 +768,7 @@ extern "C" int b200ans_histogram_max_device(b200ans_ctx* c, int method, uint32_t
     CU(c, cudaMemsetAsync(d_max, 0, 4, c->stream));
     return histogram_dispatch(c, method, f, d_src, n, d_bins, nbins, d_max);
 }
+B200ANS_CATCH_INT
 
 // ==========================================================================================
 // models
@@ -665,7 +777,7 @@ extern "C" int b200ans_histogram_max_device(b200ans_ctx* c, int method, uint32_t
 // ans_reorder_fold.hpp:75-106: order values by (-count, value), the first 2^(f+7) become
 // 0..2^(f+7)-1 and everything else moves up by 2^(f+7); identity if fewer distinct values.
 extern "C" int b200ans_rfold_prepare(b200ans_ctx* c, uint32_t f, const uint64_t* raw_bins, size_t nvalues)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!raw_bins || nvalues == 0 || f < 1 || f > 8 || nvalues > (size_t(1) << 31))
@@ -677,6 +789,12 @@ extern "C" int b200ans_rfold_prepare(b200ans_ctx* c, uint32_t f, const uint64_t*
         if (raw_bins[v])
             seen.emplace_back(raw_bins[v], uint32_t(v));
     c->rfold_sigma = seen.size();
+    // Fewer than 2^(f+7) distinct values: the reference's encoder keeps the identity mapping (ans_reorder_fold.hpp:94-97)
+    // but its decoder subtracts 2^(f+7) from every value regardless (:301), so such an input only round-trips when all
+    // values are below the threshold (then nothing is folded and the subtraction cancels the table's own offset).
+    if (seen.size() < thres && !seen.empty() && seen.back().second >= thres)
+        return c->fail(B200ANS_E_DOMAIN,
+            "ANSrfold: fewer than 2^(f+7) distinct values and a value >= 2^(f+7): the reference's decoder returns wrong values for this input");
     std::vector<uint32_t> mapping(nvalues);
     c->most_frequent.clear();
     if (seen.size() < thres) {
@@ -703,11 +821,12 @@ extern "C" int b200ans_rfold_prepare(b200ans_ctx* c, uint32_t f, const uint64_t*
     c->have_mapping = true;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 // ans_X_encode::create after the counting loop (ans_fold.hpp:79-92) + serialize (ans_fold.hpp:96-99,
 // ans_reorder_fold.hpp:132-154) + the device encoder table.
 extern "C" int b200ans_model_build(b200ans_ctx* c, int method, uint32_t f, const uint64_t* bins, size_t nbins)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!bins || !valid_method(method, f) || nbins == 0)
@@ -775,12 +894,19 @@ extern "C" int b200ans_model_build(b200ans_ctx* c, int method, uint32_t f, const
     c->stats.frame_size = frame;
     c->stats.n_symbols_model = uint32_t(c->nfreqs.size());
     c->stats.prelude_bytes = c->prelude.size();
+    {
+        uint64_t total = 0;
+        for (uint64_t v : freqs)
+            total += v;
+        c->stats.model_flags = total >= (uint64_t(1) << 31) ? B200ANS_MODEL_INT_ACCUMULATOR_QUIRK : 0u;
+    }
     c->stats.ms_model = float(now_ms() - t0);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_model_prelude(b200ans_ctx* c, uint8_t* dst, size_t capacity, size_t* out_bytes)
-{
+try {
     if (!c || !out_bytes)
         return B200ANS_E_ARG;
     if (!c->have_enc)
@@ -793,9 +919,10 @@ extern "C" int b200ans_model_prelude(b200ans_ctx* c, uint8_t* dst, size_t capaci
     std::memcpy(dst, c->prelude.data(), c->prelude.size());
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_model_nfreqs(b200ans_ctx* c, uint32_t* dst, size_t capacity, size_t* out_count, uint64_t* frame_size)
-{
+try {
     if (!c || !out_count)
         return B200ANS_E_ARG;
     if (!c->have_enc)
@@ -810,12 +937,13 @@ extern "C" int b200ans_model_nfreqs(b200ans_ctx* c, uint32_t* dst, size_t capaci
     std::copy(c->nfreqs.begin(), c->nfreqs.end(), dst);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 // ans_X_decode::load (ans_fold.hpp:179-207, ans_int.hpp:116-164, ans_msb.hpp:179-204,
 // ans_reorder_fold.hpp:235-279): prelude -> nfreqs -> slot tables, uploaded to the device.
 extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const uint8_t* prelude, size_t prelude_bytes,
     size_t* consumed)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!prelude || !valid_method(method, f) || prelude_bytes < 3)
@@ -823,13 +951,14 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
     CU(c, cudaSetDevice(c->device));
     const double t0 = now_ms();
     c->have_dec = false;
-    // the interp reader may look one 32-bit word past the end: work on a padded copy
-    std::vector<uint8_t> buf(prelude_bytes + 16, 0);
-    std::memcpy(buf.data(), prelude, prelude_bytes);
-    const uint8_t* p = buf.data();
+    // untrusted bytes: every read is bounded by the caller's buffer (host/prelude.hpp ans_load_interp_checked)
+    const uint8_t* p = prelude;
+    const uint8_t* const end = prelude + prelude_bytes;
     const uint32_t thres = 1u << (f + 7);
     std::vector<uint32_t> most_frequent;
     if (method == METHOD_RFOLD) {
+        if (prelude_bytes < 4 + 3)
+            return c->fail(B200ANS_E_FORMAT, "model_load: truncated rfold prelude");
         uint32_t flag;
         std::memcpy(&flag, p, 4);
         p += 4;
@@ -839,29 +968,23 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
                 return c->fail(B200ANS_E_FORMAT, "model_load: truncated rfold prelude");
             std::memcpy(most_frequent.data(), p, size_t(4) * thres);
             p += size_t(4) * thres;
-        } else {
+        } else if (flag == 0) {
             for (uint32_t i = 0; i < thres; i++)
                 most_frequent[i] = i;
+        } else {
+            return c->fail(B200ANS_E_FORMAT, "model_load: bad rfold prelude flag");
         }
     }
-    {   // sanity-check the vbyte/log2 header before trusting it with allocations
-        const uint8_t* q = p;
-        const uint32_t max_sym = vbyte_decode_u32(q);
-        const uint32_t lg = *q;
-        if (lg > 28 || size_t(max_sym) + 1 > (size_t(1) << 28))
-            return c->fail(B200ANS_E_FORMAT, "model_load: implausible prelude header");
-        const size_t limit = method == METHOD_INT ? (size_t(1) << 28)
-                                                  : (method == METHOD_MSB ? size_t(kMsbMaxSigma) : (size_t(1) << (f + 9)));
-        if (size_t(max_sym) + 1 > limit)
-            return c->fail(B200ANS_E_FORMAT, "model_load: alphabet larger than the method allows");
-    }
+    // one limit on both sides: b200ans_compress refuses plain-ANS alphabets beyond 2^28 values, frames beyond 2^28 slots
+    const size_t limit = method == METHOD_INT ? (size_t(1) << 28)
+                                              : (method == METHOD_MSB ? size_t(kMsbMaxSigma) : (size_t(1) << (f + 9)));
     size_t used = 0;
-    const std::vector<uint32_t> nfreqs = ans_load_interp(p, &used);
-    const size_t total_used = size_t(p - buf.data()) + used;
-    if (total_used > prelude_bytes + 4)
-        return c->fail(B200ANS_E_FORMAT, "model_load: prelude runs past its buffer");
+    std::vector<uint32_t> nfreqs;
+    if (!ans_load_interp_checked(p, end, limit, 28u, nfreqs, &used))
+        return c->fail(B200ANS_E_FORMAT, "model_load: prelude cut off, or its header is implausible for this method");
+    const size_t total_used = size_t(p - prelude) + used;
     if (consumed)
-        *consumed = std::min(total_used, prelude_bytes);
+        *consumed = total_used;
     uint64_t frame = 0;
     for (uint32_t v : nfreqs)
         frame += v;
@@ -958,6 +1081,7 @@ extern "C" int b200ans_model_load(b200ans_ctx* c, int method, uint32_t f, const 
     c->stats.ms_model = float(now_ms() - t0);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 // ==========================================================================================
 // K2 / K3 launches
@@ -1179,7 +1303,8 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
     g.rep_log2 = uint32_t(rep);
     g.table_alloc = alloc;
     g.n_full_blocks = uint32_t(a.n / a.block_syms);
-    g.max_value = METHOD == METHOD_INT ? 0xFFFFFFFFu : max_value_below(METHOD, a.fidelity, a.n_entries);
+    // folded coders: the largest value the model covers, and never 2^30 or more (ans_fold.hpp:198-200)
+    g.max_value = METHOD == METHOD_INT ? 0xFFFFFFFFu : std::min(max_value_below(METHOD, a.fidelity, a.n_entries), (1u << 30) - 1u);
 
     CUtensorMap tmap;
     const cuuint64_t dims[2] = { a.block_syms, g.n_full_blocks };
@@ -1310,6 +1435,7 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     a.rank_ent = c->dec_ent.as<RankEntry>();
     a.n_present = c->dec_n_present;
     a.dense = c->dec_dense;
+    a.error_flag = c->d_err(); // the caller zeroes it before the first launch of a call and reads it after the last
     const size_t frame = size_t(1) << c->dec_log2_frame;
     if (use_lpb(c, n_blocks, false)) {
         const size_t lbudget = c->max_smem > size_t(16) * kLpbDecWarpBytes + 4096 ? c->max_smem - size_t(16) * kLpbDecWarpBytes - 4096 : 0;
@@ -1415,6 +1541,26 @@ int read_small(b200ans_ctx* c)
     return B200ANS_OK;
 }
 
+int write_empty_container(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap, size_t* out_bytes)
+{
+    if (c->block_syms == 0) { // the reference cannot represent an empty input either
+        *out_bytes = 0;
+        return B200ANS_OK;
+    }
+    if (cap < B200ANS_HEADER_BYTES)
+        return c->fail(B200ANS_E_CAPACITY, "destination too small");
+    Header h {};
+    h.magic = B200ANS_MAGIC;
+    h.version = 1;
+    h.method = uint8_t(method);
+    h.fidelity = uint8_t(f);
+    h.block_syms = c->block_syms;
+    CU(c, cudaMemcpyAsync(d_dst, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    *out_bytes = B200ANS_HEADER_BYTES;
+    return B200ANS_OK;
+}
+
 int check_error_flag(b200ans_ctx* c)
 {
     uint32_t flag = 0;
@@ -1431,16 +1577,17 @@ int check_error_flag(b200ans_ctx* c)
 // staged encode / decode
 // ==========================================================================================
 extern "C" int b200ans_block_stride(const b200ans_ctx* c, int method, size_t* stride)
-{
+try {
     if (!c || !stride || c->block_syms == 0)
         return B200ANS_E_ARG;
     *stride = block_stride(method, c->block_syms);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_encode_blocks_device(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint8_t* d_scratch,
     size_t stride, uint32_t* d_block_bytes)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!d_src || !d_scratch || !d_block_bytes || n == 0 || (reinterpret_cast<uintptr_t>(d_src) & 15)
@@ -1463,10 +1610,11 @@ extern "C" int b200ans_encode_blocks_device(b200ans_ctx* c, const uint32_t* d_sr
     c->stats.n_blocks = uint32_t(nb);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_decode_blocks_device(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_offsets,
     const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!d_payload || !d_offsets || !d_block_bytes || !d_dst || n == 0)
@@ -1478,26 +1626,41 @@ extern "C" int b200ans_decode_blocks_device(b200ans_ctx* c, const uint8_t* d_pay
     CU(c, cudaSetDevice(c->device));
     const uint32_t bs = c->block_syms ? c->block_syms : uint32_t(n);
     const uint64_t nb = (n + bs - 1) / bs;
+    CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
+    {   // untrusted sizes: at least the four states, whole words for plain ANS
+        const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>((nb + 255) / 256, uint64_t(c->num_sms) * 4)));
+        check_block_sizes_kernel<<<grid, 256, 0, c->stream>>>(d_block_bytes, uint32_t(nb), c->dec_method == METHOD_INT && c->block_syms ? 3u : 0u, c->d_err());
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+        RET(read_small(c));
+        if (c->h_small()->error_flag)
+            return c->fail(B200ANS_E_FORMAT, "decode: a block is shorter than its four states, or a plain-ANS block is not a whole number of words");
+    }
     CU(c, cudaEventRecord(c->ev[0], c->stream));
     RET(launch_decode(c, d_payload, d_offsets, d_block_bytes, n, bs, uint32_t(nb), d_dst));
     CU(c, cudaEventRecord(c->ev[1], c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+    RET(read_small(c));
     c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
     c->stats.n_blocks = uint32_t(nb);
+    if (c->h_small()->error_flag)
+        return c->fail(B200ANS_E_FORMAT, "decode: a block's payload was not consumed exactly (corrupt stream or wrong model)");
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 // current model + d_src -> container (or reference wire format when block_syms == 0) at d_dst
 extern "C" int b200ans_encode_device(b200ans_ctx* c, uint8_t* d_dst, size_t cap, const uint32_t* d_src, size_t n,
     size_t* out_bytes)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
-    if (!d_dst || !d_src || !out_bytes || n == 0 || (reinterpret_cast<uintptr_t>(d_src) & 15)
+    if (!d_dst || (!d_src && n) || !out_bytes || (reinterpret_cast<uintptr_t>(d_src) & 15)
         || (reinterpret_cast<uintptr_t>(d_dst) & 15))
         return c->fail(B200ANS_E_ARG, "encode: null / unaligned argument");
     if (!c->have_enc)
         return c->fail(B200ANS_E_STATE, "encode: build a model first");
+    if (n == 0) // an empty shard of a multi-GPU job: a container without blocks
+        return write_empty_container(c, c->enc_method, c->enc_f, d_dst, cap, out_bytes);
     if (c->block_syms == 0 && n >= (uint64_t(1) << 32))
         return c->fail(B200ANS_E_ARG, "single-block mode is limited to 2^32-1 symbols");
     CU(c, cudaSetDevice(c->device));
@@ -1583,39 +1746,58 @@ extern "C" int b200ans_encode_device(b200ans_ctx* c, uint8_t* d_dst, size_t cap,
     c->stats.total_bytes = *out_bytes;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 // ==========================================================================================
 // one-shot paths
 // ==========================================================================================
 namespace {
 
-int write_empty_container(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap, size_t* out_bytes)
+// in place on the context's stream: bins summed, *d_max maximised over the ranks (one NCCL group)
+int allreduce_hist(b200ans_ctx* c, uint64_t* d_bins, size_t nbins, uint32_t* d_max)
 {
-    if (c->block_syms == 0) { // the reference cannot represent an empty input either
-        *out_bytes = 0;
+    if (!c->comm) // (a world of one still goes through NCCL: the same code path as N > 1)
         return B200ANS_OK;
+    const NcclApi& n = nccl_api();
+    if (!n.ok)
+        return c->fail(B200ANS_E_NCCL, "libnccl.so.2 could not be loaded");
+    int e = n.GroupStart();
+    if (e)
+        return c->nccl_fail(e, "ncclGroupStart");
+    if (d_bins && nbins) {
+        e = n.AllReduce(d_bins, d_bins, nbins, kNcclUint64, kNcclSum, c->comm, c->stream);
+        if (e) {
+            n.GroupEnd();
+            return c->nccl_fail(e, "ncclAllReduce(histogram)");
+        }
     }
-    if (cap < B200ANS_HEADER_BYTES)
-        return c->fail(B200ANS_E_CAPACITY, "destination too small");
-    Header h {};
-    h.magic = B200ANS_MAGIC;
-    h.version = 1;
-    h.method = uint8_t(method);
-    h.fidelity = uint8_t(f);
-    h.block_syms = c->block_syms;
-    CU(c, cudaMemcpyAsync(d_dst, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
-    *out_bytes = B200ANS_HEADER_BYTES;
+    if (d_max) {
+        e = n.AllReduce(d_max, d_max, 1, kNcclUint32, kNcclMax, c->comm, c->stream);
+        if (e) {
+            n.GroupEnd();
+            return c->nccl_fail(e, "ncclAllReduce(max)");
+        }
+    }
+    e = n.GroupEnd();
+    if (e)
+        return c->nccl_fail(e, "ncclGroupEnd");
     return B200ANS_OK;
 }
 
-// device histogram -> host bins
+// device histogram [-> all-reduce over the communicator] -> host bins
 int histogram_to_host(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n, size_t nbins,
-    std::vector<uint64_t>& host_bins, uint32_t* max_value = nullptr)
+    std::vector<uint64_t>& host_bins, uint32_t* max_value, bool sharded)
 {
     CU(c, c->bins.reserve(nbins * 8));
     CU(c, cudaMemsetAsync(c->bins.p, 0, nbins * 8, c->stream));
-    RET(histogram_dispatch(c, method, f, d_src, n, c->bins.as<uint64_t>(), nbins, c->d_max()));
+    if (n)
+        RET(histogram_dispatch(c, method, f, d_src, n, c->bins.as<uint64_t>(), nbins, c->d_max()));
+    if (sharded) {
+        CU(c, cudaEventRecord(c->ev_ar[0], c->stream));
+        RET(allreduce_hist(c, c->bins.as<uint64_t>(), nbins, max_value ? c->d_max() : nullptr));
+        CU(c, cudaEventRecord(c->ev_ar[1], c->stream));
+        c->ar_timed = true;
+    }
     host_bins.resize(nbins);
     if (nbins * 8 <= b200ans_ctx::kPinnedBins) {
         // bins and the running maximum through pinned memory: both copies are asynchronous, one synchronisation
@@ -1624,30 +1806,33 @@ int histogram_to_host(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_
         std::memcpy(host_bins.data(), c->pinned, nbins * 8);
         if (max_value)
             *max_value = c->h_small()->max_value;
-        return B200ANS_OK;
+    } else {
+        CU(c, cudaMemcpyAsync(host_bins.data(), c->bins.p, nbins * 8, cudaMemcpyDeviceToHost, c->stream));
+        if (max_value)
+            CU(c, cudaMemcpyAsync(max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
     }
-    CU(c, cudaMemcpyAsync(host_bins.data(), c->bins.p, nbins * 8, cudaMemcpyDeviceToHost, c->stream));
-    if (max_value)
-        CU(c, cudaMemcpyAsync(max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+    if (sharded && c->ar_timed) {
+        c->stats.ms_allreduce += elapsed(c->ev_ar[0], c->ev_ar[1]);
+        c->ar_timed = false;
+    }
     return B200ANS_OK;
 }
 
-} // namespace
-
-// ans_X_compress with device-resident buffers: histogram (K1) -> host normalise -> encode (K2)
-extern "C" int b200ans_compress_device(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap,
-    const uint32_t* d_src, size_t n, size_t* out_bytes)
+// ans_X_compress with device-resident buffers: histogram (K1) [-> all-reduce] -> host normalise -> encode (K2)
+int compress_device_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap, const uint32_t* d_src, size_t n,
+    size_t* out_bytes, bool sharded)
 {
-    if (!c)
-        return B200ANS_E_ARG;
     if (!d_dst || !out_bytes || (!d_src && n) || !valid_method(method, f)
         || (reinterpret_cast<uintptr_t>(d_src) & 15) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
         return c->fail(B200ANS_E_ARG, "compress: bad argument (device buffers must be 16-byte aligned)");
     CU(c, cudaSetDevice(c->device));
-    c->stats.ms_histogram = c->stats.ms_encode = c->stats.ms_compact = c->stats.ms_model = 0.f;
-    if (n == 0)
+    sharded = sharded && c->comm;
+    c->stats.ms_histogram = c->stats.ms_encode = c->stats.ms_compact = c->stats.ms_model = c->stats.ms_allreduce = 0.f;
+    if (n == 0 && !sharded)
         return write_empty_container(c, method, f, d_dst, cap, out_bytes);
+    if (sharded && c->block_syms == 0)
+        return c->fail(B200ANS_E_ARG, "sharded compression writes blocked containers (block_syms > 0)");
 
     CU(c, cudaEventRecord(c->ev[3], c->stream));
     CU(c, cudaMemsetAsync(c->d_max(), 0, 4, c->stream));
@@ -1658,39 +1843,162 @@ extern "C" int b200ans_compress_device(b200ans_ctx* c, int method, uint32_t f, u
         // while it counts, so alphabets that fit four shared-memory replicas need one pass: count into kOptBins
         // bins (larger values are dropped by the kernel's bounds check) and look at the maximum afterwards.
         constexpr size_t kOptBins = kHistSmemWords / 4 - 1;
-        RET(histogram_to_host(c, METHOD_INT, f, d_src, n, kOptBins, bins, &max_value));
-        if (max_value >= (1u << 30))
-            return c->fail(B200ANS_E_DOMAIN, "plain ANS: alphabets beyond 2^30 are not supported");
+        RET(histogram_to_host(c, METHOD_INT, f, d_src, n, kOptBins, bins, &max_value, sharded));
+        // one limit on both sides: b200ans_model_load refuses alphabets beyond 2^28 values too
+        if (max_value >= (1u << 28))
+            return c->fail(B200ANS_E_DOMAIN, "plain ANS: values of 2^28 and more are not supported (one table entry per value up to the maximum)");
         if (max_value >= kOptBins)
-            RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins));
+            RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins, nullptr, sharded));
         else
             bins.resize(size_t(max_value) + 1);
     } else if (method == METHOD_RFOLD) {
-        RET(b200ans_max_device(c, d_src, n, c->d_max()));
+        if (n)
+            RET(b200ans_max_device(c, d_src, n, c->d_max()));
+        if (sharded)
+            RET(allreduce_hist(c, nullptr, 0, c->d_max()));
         CU(c, cudaMemcpyAsync(&max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
         CU(c, cudaStreamSynchronize(c->stream));
         if (uint64_t(max_value) + (1u << (f + 7)) >= (1u << 30))
             return c->fail(B200ANS_E_DOMAIN, "ANSrfold needs value + 2^(f+7) < 2^30");
-        RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins));
+        RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins, nullptr, sharded));
         RET(b200ans_rfold_prepare(c, f, bins.data(), bins.size()));
-        RET(histogram_to_host(c, METHOD_RFOLD, f, d_src, n, alphabet_bins(method, f, 0), bins));
+        RET(histogram_to_host(c, METHOD_RFOLD, f, d_src, n, alphabet_bins(method, f, 0), bins, nullptr, sharded));
     } else {
-        RET(histogram_to_host(c, method, f, d_src, n, alphabet_bins(method, f, 0), bins, &max_value));
+        RET(histogram_to_host(c, method, f, d_src, n, alphabet_bins(method, f, 0), bins, &max_value, sharded));
         if (max_value >= (1u << 30)) // the decoder keeps the byte count in bits 30-31 (ans_fold.hpp:198-200)
             return c->fail(B200ANS_E_DOMAIN, "folded coders need values < 2^30");
     }
     CU(c, cudaEventRecord(c->ev[4], c->stream));
     CU(c, cudaEventSynchronize(c->ev[4]));
-    const float ms_hist = elapsed(c->ev[3], c->ev[4]);
+    const float ms_hist = elapsed(c->ev[3], c->ev[4]) - c->stats.ms_allreduce;
+    {
+        bool any = false;
+        for (uint64_t v : bins)
+            any = any || v != 0;
+        if (!any) // every shard of the job is empty
+            return write_empty_container(c, method, f, d_dst, cap, out_bytes);
+    }
     RET(b200ans_model_build(c, method, f, bins.data(), bins.size()));
+    if (n == 0) { // this rank's shard is empty: it took part in the reduction, its container holds no blocks
+        c->stats.ms_histogram = ms_hist;
+        return write_empty_container(c, method, f, d_dst, cap, out_bytes);
+    }
     RET(b200ans_encode_device(c, d_dst, cap, d_src, n, out_bytes));
     c->stats.ms_histogram = ms_hist;
     return B200ANS_OK;
 }
 
+} // namespace
+
+extern "C" int b200ans_compress_device(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap,
+    const uint32_t* d_src, size_t n, size_t* out_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    return compress_device_impl(c, method, f, d_dst, cap, d_src, n, out_bytes, false);
+}
+B200ANS_CATCH_INT
+
+// ==========================================================================================
+// multi-GPU: communicator + sharded compression
+// ==========================================================================================
+extern "C" int b200ans_comm_unique_id(uint8_t id[B200ANS_COMM_ID_BYTES])
+try {
+    if (!id)
+        return B200ANS_E_ARG;
+    const NcclApi& n = nccl_api();
+    if (!n.ok)
+        return B200ANS_E_NCCL;
+    NcclUniqueId u;
+    if (n.GetUniqueId(&u) != 0)
+        return B200ANS_E_NCCL;
+    std::memcpy(id, u.internal, B200ANS_COMM_ID_BYTES);
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_comm_release(b200ans_ctx* c)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (c->comm && c->own_comm && nccl_api().ok) {
+        cudaSetDevice(c->device);
+        cudaStreamSynchronize(c->stream);
+        nccl_api().CommDestroy(c->comm);
+    }
+    c->comm = nullptr;
+    c->own_comm = false;
+    c->comm_rank = 0;
+    c->comm_world = 1;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_comm_init(b200ans_ctx* c, const uint8_t id[B200ANS_COMM_ID_BYTES], int rank, int world)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!id || world < 1 || rank < 0 || rank >= world)
+        return c->fail(B200ANS_E_ARG, "comm_init: bad rank / world");
+    const NcclApi& n = nccl_api();
+    if (!n.ok)
+        return c->fail(B200ANS_E_NCCL, "libnccl.so.2 could not be loaded");
+    b200ans_comm_release(c);
+    CU(c, cudaSetDevice(c->device));
+    NcclUniqueId u;
+    std::memcpy(u.internal, id, B200ANS_COMM_ID_BYTES);
+    void* comm = nullptr;
+    const int e = n.CommInitRank(&comm, world, u, rank);
+    if (e)
+        return c->nccl_fail(e, "ncclCommInitRank");
+    c->comm = comm;
+    c->own_comm = true;
+    c->comm_rank = rank;
+    c->comm_world = world;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_comm_attach(b200ans_ctx* c, void* nccl_comm, int rank, int world)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!nccl_comm || world < 1 || rank < 0 || rank >= world)
+        return c->fail(B200ANS_E_ARG, "comm_attach: bad communicator / rank / world");
+    if (!nccl_api().ok)
+        return c->fail(B200ANS_E_NCCL, "libnccl.so.2 could not be loaded");
+    b200ans_comm_release(c);
+    c->comm = nccl_comm;
+    c->own_comm = false;
+    c->comm_rank = rank;
+    c->comm_world = world;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_allreduce_hist(b200ans_ctx* c, uint64_t* d_bins, size_t nbins, uint32_t* d_max)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!d_bins && nbins) || (!d_bins && !d_max))
+        return c->fail(B200ANS_E_ARG, "allreduce_hist: nothing to reduce");
+    CU(c, cudaSetDevice(c->device));
+    return allreduce_hist(c, d_bins, nbins, d_max);
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_compress_sharded_device(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap,
+    const uint32_t* d_src, size_t n, size_t* out_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    return compress_device_impl(c, method, f, d_dst, cap, d_src, n, out_bytes, true);
+}
+B200ANS_CATCH_INT
+
 extern "C" int b200ans_decompress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, size_t n,
     const uint8_t* d_src, size_t src_bytes)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if ((!d_dst && n) || !d_src || !valid_method(method, f) || (reinterpret_cast<uintptr_t>(d_src) & 15))
@@ -1742,7 +2050,7 @@ extern "C" int b200ans_decompress_device(b200ans_ctx* c, int method, uint32_t f,
         return c->fail(B200ANS_E_FORMAT, "decompress: inconsistent block geometry");
     const size_t table_at = B200ANS_HEADER_BYTES + align_up(h.prelude_bytes, 4);
     const size_t payload_at = align_up(table_at + size_t(h.n_blocks) * 4, 16);
-    if (payload_at + h.payload_bytes > src_bytes)
+    if (payload_at > src_bytes || h.payload_bytes > src_bytes - payload_at || h.prelude_bytes < 3)
         return c->fail(B200ANS_E_FORMAT, "decompress: container truncated");
     std::vector<uint8_t> prelude(h.prelude_bytes);
     const size_t have = std::min<size_t>(h.prelude_bytes, head - B200ANS_HEADER_BYTES);
@@ -1769,13 +2077,14 @@ extern "C" int b200ans_decompress_device(b200ans_ctx* c, int method, uint32_t f,
     c->block_syms = saved;
     return rc;
 }
+B200ANS_CATCH_INT
 
 // ---- host buffers: what methods.hpp's encode()/decode() hand over ----------------------------
-extern "C" int b200ans_compress(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, size_t cap, const uint32_t* src,
-    size_t n, size_t* out_bytes)
+namespace {
+
+int compress_host_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, size_t cap, const uint32_t* src, size_t n,
+    size_t* out_bytes, bool sharded)
 {
-    if (!c)
-        return B200ANS_E_ARG;
     if (!dst || !out_bytes || (!src && n) || !valid_method(method, f))
         return c->fail(B200ANS_E_ARG, "compress: bad argument");
     CU(c, cudaSetDevice(c->device));
@@ -1787,7 +2096,7 @@ extern "C" int b200ans_compress(b200ans_ctx* c, int method, uint32_t f, uint8_t*
         CU(c, cudaMemcpyAsync(c->io_in.p, src, n * 4, cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaEventRecord(c->ev[6], c->stream));
     size_t bytes = 0;
-    RET(b200ans_compress_device(c, method, f, c->io_out.as<uint8_t>(), std::min(bound, c->io_out.cap), c->io_in.as<uint32_t>(), n, &bytes));
+    RET(compress_device_impl(c, method, f, c->io_out.as<uint8_t>(), std::min(bound, c->io_out.cap), c->io_in.as<uint32_t>(), n, &bytes, sharded));
     if (bytes > cap)
         return c->fail(B200ANS_E_CAPACITY, "compress: destination too small");
     CU(c, cudaEventRecord(c->ev[7], c->stream));
@@ -1800,6 +2109,26 @@ extern "C" int b200ans_compress(b200ans_ctx* c, int method, uint32_t f, uint8_t*
     *out_bytes = bytes;
     return B200ANS_OK;
 }
+
+} // namespace
+
+extern "C" int b200ans_compress(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, size_t cap, const uint32_t* src,
+    size_t n, size_t* out_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    return compress_host_impl(c, method, f, dst, cap, src, n, out_bytes, false);
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_compress_sharded(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, size_t cap,
+    const uint32_t* src, size_t n, size_t* out_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    return compress_host_impl(c, method, f, dst, cap, src, n, out_bytes, true);
+}
+B200ANS_CATCH_INT
 
 namespace {
 
@@ -1846,8 +2175,8 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
         for (uint32_t b = 0; b < nb; b++) {
             uint32_t v;
             std::memcpy(&v, tp + size_t(b) * 4, 4);
-            if (v < 32u)
-                return c->fail(B200ANS_E_FORMAT, "decompress: a block is shorter than its four states");
+            if (v < 32u || v > 0x7FFFFF00u || (method == METHOD_INT && (v & 3u)))
+                return c->fail(B200ANS_E_FORMAT, "decompress: a block is shorter than its four states (or, plain ANS, not a whole number of words)");
             total += (uint64_t(v) + 15u) & ~uint64_t(15);
             if (total > h.payload_bytes)
                 return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
@@ -1888,6 +2217,7 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
     scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, nb, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
     c->stats.launches++;
     CU(c, cudaGetLastError());
+    CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
     CU(c, cudaEventRecord(c->ev[0], c->stream));
     for (int r = 0; r < runs; r++) {
         const uint32_t b0 = r ? run_end[r - 1] : 0, b1 = run_end[r];
@@ -1905,11 +2235,13 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
     CU(c, cudaEventRecord(c->ev[6], c->copy_out));
     CU(c, cudaStreamWaitEvent(c->stream, c->ev[6], 0)); // the call's work ends on `stream`, as every other entry point's
     CU(c, cudaEventRecord(c->ev[7], c->stream));
-    CU(c, cudaStreamSynchronize(c->stream));
+    RET(read_small(c)); // the call's one synchronisation: error flag + everything above
     c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
     c->stats.ms_h2d = 0.f; // overlapped: the stages are not separable
     c->stats.ms_d2h = elapsed(c->ev[1], c->ev[7]);
     c->stats.n_blocks = nb;
+    if (c->h_small()->error_flag)
+        return c->fail(B200ANS_E_FORMAT, "decompress: a block's payload was not consumed exactly (corrupt stream)");
     return B200ANS_OK;
 }
 
@@ -1917,7 +2249,7 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
 
 extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src,
     size_t src_bytes)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if ((!dst && n) || !src || !valid_method(method, f))
@@ -1950,6 +2282,7 @@ extern "C" int b200ans_decompress(b200ans_ctx* c, int method, uint32_t f, uint32
     c->stats.ms_d2h = elapsed(c->ev[7], c->ev[3]);
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 // ==========================================================================================
 // pseudo-adaptive mode: one semi-static model per block of `model_syms` symbols
@@ -2031,7 +2364,7 @@ extern "C" size_t b200ans_pa_compress_bound(const b200ans_ctx* c, int method, ui
 
 extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms, uint8_t* d_dst,
     size_t cap, const uint32_t* d_src, size_t n, size_t* out_bytes)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!d_dst || !out_bytes || (!d_src && n) || (reinterpret_cast<uintptr_t>(d_src) & 15) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
@@ -2276,6 +2609,7 @@ extern "C" int b200ans_pa_compress_device(b200ans_ctx* c, int method, uint32_t f
             ms_host, undecided, elapsed(c->ev[6], c->ev[7]));
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 namespace {
 
@@ -2497,7 +2831,7 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
 
 extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, size_t n,
     const uint8_t* d_src, size_t src_bytes)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if ((!d_dst && n) || !d_src || (reinterpret_cast<uintptr_t>(d_src) & 15))
@@ -2505,10 +2839,11 @@ extern "C" int b200ans_pa_decompress_device(b200ans_ctx* c, int method, uint32_t
     CU(c, cudaSetDevice(c->device));
     return pa_decompress_core(c, method, f, d_dst, n, d_src, src_bytes, nullptr, nullptr);
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_pa_compress(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms, uint8_t* dst, size_t cap,
     const uint32_t* src, size_t n, size_t* out_bytes)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if (!dst || !out_bytes || (!src && n) || model_syms == 0)
@@ -2529,10 +2864,11 @@ extern "C" int b200ans_pa_compress(b200ans_ctx* c, int method, uint32_t f, uint3
     *out_bytes = bytes;
     return B200ANS_OK;
 }
+B200ANS_CATCH_INT
 
 extern "C" int b200ans_pa_decompress(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src,
     size_t src_bytes)
-{
+try {
     if (!c)
         return B200ANS_E_ARG;
     if ((!dst && n) || !src)
@@ -2549,3 +2885,4 @@ extern "C" int b200ans_pa_decompress(b200ans_ctx* c, int method, uint32_t f, uin
     }
     return rc;
 }
+B200ANS_CATCH_INT

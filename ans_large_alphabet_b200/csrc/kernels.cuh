@@ -107,6 +107,7 @@ struct DecArgs {
     uint32_t pa_nbins;
     uint32_t pa_syms;         // table entries per model: beyond the largest symbol of every model, multiple of 16
     uint32_t pa_bucket_log2;  // the bucket index has 2^pa_bucket_log2 entries per model
+    uint32_t* error_flag;     // set to 2 when a block's payload is not consumed exactly (corrupt container); may be null
 };
 
 enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3, DEC_INT_SMEM_PURE = 4 };
@@ -532,7 +533,9 @@ __global__ void __launch_bounds__(kEncWarps * 32) encode_kernel(const EncArgs a)
                 const uint32_t v = vcur[i];
                 uint32_t k;
                 uint32_t sym = map_value<METHOD>(v, f, k);
-                if (sym >= a.n_entries) { // value outside the model: flag, stay in bounds
+                // value outside the model, or (folded coders) beyond 2^30 - 1, where the decoder's packed word has no
+                // room for it (ans_fold.hpp:198-200): flag, stay in bounds
+                if (sym >= a.n_entries || (METHOD != METHOD_INT && v >= (1u << 30))) {
                     if (active)
                         *a.error_flag = 1u;
                     sym = 0;
@@ -683,6 +686,7 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
             x = v + lower;
         }
         int32_t cursor = int32_t(delta + size - 32u); // one past the next byte to consume
+        bool underrun = false;
 
         for (uint32_t s0 = 0; s0 < max_steps; s0 += kDecTile) {
             // stage [lo, lo + 288) around the cursor
@@ -718,7 +722,9 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
                 // forward inclusive scan: lane 0 of the group consumes first
                 uint32_t incl, total;
                 group_scan(active ? k : 0u, renorm, grp_base, scan_mine, incl, total);
-                const int32_t end = cursor - int32_t(incl - c); // my bytes are [end - c, end)
+                // (a corrupt payload can ask for more bytes than the block has: positions stop at 0, the row's front
+                // padding takes the window's under-read, the block is flagged below)
+                const int32_t end = max(cursor - int32_t(incl - c), 0); // my bytes are [end - c, end)
                 // 8-byte window [end-8, end) from three aligned words
                 const int32_t wa = end - 8;
                 const uint32_t* wp = reinterpret_cast<const uint32_t*>(stage + (wa & ~3));
@@ -734,9 +740,13 @@ __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
                     x = nx;
                     out[idx] = mapped + exc - rfold_bias;
                 }
-                cursor -= int32_t(total);
+                underrun |= cursor < int32_t(total);
+                cursor = max(cursor - int32_t(total), 0);
             }
         }
+        // a well-formed block is consumed down to its first byte, exactly
+        if (have_block && a.error_flag && (underrun || cursor != int32_t(delta)))
+            *a.error_flag = 2u;
     }
 }
 
@@ -797,6 +807,7 @@ __global__ void __launch_bounds__(kDecWarps * 32) int_decode_kernel(const DecArg
             x = (uint64_t(__ldg(sp)) | (uint64_t(__ldg(sp + 1)) << 32)) + lower;
         }
         int32_t wcur = int32_t((delta + size - 32u) >> 2); // one past the next word to consume
+        bool underrun = false;
 
         for (uint32_t s0 = 0; s0 < max_steps; s0 += kIntDecTile) {
             // stage the words [lo, wcur): at most 4 * kIntDecTile are consumed before the next refill
@@ -838,9 +849,12 @@ __global__ void __launch_bounds__(kDecWarps * 32) int_decode_kernel(const DecArg
                     x = nx;
                     out[idx] = sym;
                 }
-                wcur -= int32_t(__popc(flags));
+                underrun |= wcur < int32_t(__popc(flags));
+                wcur = max(wcur - int32_t(__popc(flags)), 0); // corrupt payload: stay inside the row
             }
         }
+        if (have_block && a.error_flag && (underrun || wcur != int32_t(delta >> 2)))
+            *a.error_flag = 2u;
     }
 }
 
@@ -905,6 +919,20 @@ __global__ void __launch_bounds__(1024) scan_block_sizes_kernel(const uint32_t* 
             offsets[b] = carry + incl - p;
         carry += __shfl_sync(0xffffffffu, incl, 31);
     }
+}
+
+// Untrusted size table: every block must hold its four 64-bit states (>= 32 bytes) and, where `align_mask` says so
+// (plain ANS: whole 32-bit words), be aligned; sets *flag = 3 otherwise.
+__global__ void __launch_bounds__(256) check_block_sizes_kernel(const uint32_t* __restrict__ bytes, uint32_t n_blocks, uint32_t align_mask,
+    uint32_t* __restrict__ flag)
+{
+    bool bad = false;
+    for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < n_blocks; b += gridDim.x * blockDim.x) {
+        const uint32_t v = __ldg(bytes + b);
+        bad |= v < 32u || (v & align_mask) != 0u || v > 0x7FFFFF00u;
+    }
+    if (__any_sync(0xffffffffu, bad) && lane_id() == 0)
+        *flag = 3u;
 }
 
 // one warp per block: scratch + b*stride  ->  payload + offsets[b]; also fills the container's size table.

@@ -712,6 +712,10 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
             }
         }
         cp_async_wait<0>();
+        // a well-formed block is consumed down to its first byte, exactly: the reader stands `fill / 8` bytes into the
+        // word above rp
+        if (have_block && a.error_flag && rd.rp + 4 + int32_t(rd.fill >> 3) != int32_t(delta))
+            *a.error_flag = 2u;
     }
 }
 

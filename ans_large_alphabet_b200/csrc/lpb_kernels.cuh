@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(kLpbMaxWarps * 32, 1) lpb_encode_kernel(const 
                 v = __ldg(a.mapping + v);
             }
             uint32_t sym = map_value<METHOD>(v, f, k);
-            if (sym >= a.n_entries) {
+            if (sym >= a.n_entries || (METHOD != METHOD_INT && v >= (1u << 30))) { // (ans_fold.hpp:198-200: values < 2^30)
                 bad |= uint32_t(active);
                 sym = 0;
             }

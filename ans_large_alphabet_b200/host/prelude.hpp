@@ -41,6 +41,23 @@ inline uint32_t vbyte_decode_u32(const uint8_t*& in)
     }
 }
 
+// The same for untrusted input: never reads at or beyond `end`, never shifts by 32 or more (a u32 has at most five
+// groups); `ok` is cleared when the number is cut off or too long.
+inline uint32_t vbyte_decode_u32(const uint8_t*& in, const uint8_t* end, bool& ok)
+{
+    uint32_t x = 0;
+    for (uint32_t shift = 0; shift < 35; shift += 7) {
+        if (in >= end)
+            break;
+        const uint8_t c = *in++;
+        x += uint32_t(c & 0x7F) << shift;
+        if (c < 0x80)
+            return x;
+    }
+    ok = false;
+    return 0;
+}
+
 namespace detail {
 
     // LSB-first packer of (value, width<=32) fields into little-endian 32-bit words at an
@@ -86,14 +103,18 @@ namespace detail {
 
     class word_unpacker {
     public:
-        explicit word_unpacker(const uint8_t* src) : in_(src) {}
+        // `end` (optional): one past the last readable byte; a word that would cross it reads as zero and sets overrun()
+        explicit word_unpacker(const uint8_t* src, const uint8_t* end = nullptr) : in_(src), end_(end) {}
         uint64_t get(unsigned width)
         {
             if (width == 0)
                 return 0;
             if (fill_ < width) {
-                uint32_t w;
-                std::memcpy(&w, in_, sizeof w);
+                uint32_t w = 0;
+                if (end_ && size_t(end_ - in_) < sizeof w)
+                    overrun_ = true;
+                else
+                    std::memcpy(&w, in_, sizeof w);
                 in_ += sizeof w;
                 words_++;
                 acc_ |= uint64_t(w) << fill_;
@@ -105,9 +126,12 @@ namespace detail {
             return v;
         }
         size_t words() const { return words_; }
+        bool overrun() const { return overrun_; }
 
     private:
         const uint8_t* in_;
+        const uint8_t* end_;
+        bool overrun_ = false;
         uint64_t acc_ = 0;
         unsigned fill_ = 0;
         size_t words_ = 0;
@@ -171,7 +195,7 @@ namespace detail {
 
     inline void interp_get(word_unpacker& r, uint32_t* v, size_t n, uint64_t low, uint64_t high)
     {
-        while (n != 0) {
+        while (n != 0 && !r.overrun()) {
             const size_t h = (n + 1) >> 1, left = h - 1, right = n - h;
             const uint64_t mid = low + left - 1 + get_centered(r, high - right - low - left + 1);
             v[h - 1] = uint32_t(mid - 1);
@@ -236,6 +260,39 @@ inline std::vector<uint32_t> ans_load_interp(const uint8_t* in_u8, size_t* consu
     if (consumed)
         *consumed = size_t(p - in_u8) + words * sizeof(uint32_t);
     return vec;
+}
+
+// ans_load_interp for untrusted bytes: nothing at or beyond `end` is read, the alphabet is limited to `max_symbols`
+// and log2 M to `max_log2`; returns false (vec unspecified) when the prelude is cut off or implausible.  Whether the
+// frequencies add up to the frame is the caller's check.
+inline bool ans_load_interp_checked(const uint8_t* in_u8, const uint8_t* end, size_t max_symbols, unsigned max_log2,
+    std::vector<uint32_t>& vec, size_t* consumed = nullptr)
+{
+    const uint8_t* p = in_u8;
+    bool ok = true;
+    const uint32_t max_sym = vbyte_decode_u32(p, end, ok);
+    if (!ok || p >= end || size_t(max_sym) + 1 > max_symbols)
+        return false;
+    const unsigned lg = *p++;
+    if (lg > max_log2)
+        return false;
+    const uint64_t frame_size = uint64_t(1) << lg;
+    vec.assign(size_t(max_sym) + 1, 0u);
+    detail::word_unpacker r(p, end);
+    detail::interp_get(r, vec.data(), vec.size(), 1, frame_size + vec.size() + 2);
+    if (r.overrun())
+        return false;
+    uint32_t below = vec[0];
+    for (size_t s = 1; s < vec.size(); s++) {
+        const uint32_t here = vec[s];
+        if (here <= below) // prefix sums of (nfreq + 1) climb strictly
+            return false;
+        vec[s] = here - below - 1;
+        below = here;
+    }
+    if (consumed)
+        *consumed = size_t(p - in_u8) + r.words() * sizeof(uint32_t);
+    return true;
 }
 
 } // namespace b200ans

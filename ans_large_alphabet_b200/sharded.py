@@ -140,8 +140,37 @@ def global_histogram(codec, method, f, d_src, n, group=None, sync=None):
     return hist(method, alphabet_bins(method, f))
 
 
+def init_comm(codec, group=None):
+    """Give `codec` its NCCL communicator over the ranks of `group`: rank 0 draws the unique id (b200ans_comm_unique_id),
+    torch.distributed only carries the 128 bytes to the others, b200ans_comm_init is the collective ncclCommInitRank.
+    After this b200ans_compress_sharded[_device] runs the histogram exchange inside the library, on the codec's
+    stream.  Works with any torch backend (the bytes travel as a CPU tensor under gloo, a CUDA tensor under nccl)."""
+    import torch
+    import torch.distributed as dist
+
+    from ._capi import comm_unique_id
+
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    uid = comm_unique_id() if rank == 0 else np.zeros(128, dtype=np.uint8)
+    t = torch.from_numpy(uid)
+    on_gpu = dist.get_backend(group) == "nccl"
+    if on_gpu:
+        t = t.cuda()
+    dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    codec.comm_init(t.cpu().numpy(), rank, world)
+    return rank, world
+
+
 def compress_shard(codec, method, f, d_src, n, d_dst, group=None, sync=None):
-    """Semi-static encode of this rank's shard with the GLOBAL model. Returns container bytes."""
+    """Semi-static encode of this rank's shard with the GLOBAL model (b200ans_compress_sharded_device: histogram ->
+    one NCCL all-reduce inside the library -> normalise -> encode). Returns container bytes.  The codec needs its
+    communicator (init_comm) when the group has more than one rank."""
+    return codec.compress_sharded_device(method, f, d_dst.data_ptr(), d_dst.numel() * d_dst.element_size(), d_src.data_ptr(), n)
+
+
+def compress_shard_staged(codec, method, f, d_src, n, d_dst, group=None, sync=None):
+    """The same through the staged entry points with torch.distributed doing the all-reduce (round 1's path; kept as the
+    cross-check of the library's own exchange)."""
     bins = global_histogram(codec, method, f, d_src, n, group, sync)
     codec.model_build(method, f, bins)
     return codec.encode_device(d_dst.data_ptr(), d_dst.numel() * d_dst.element_size(), d_src.data_ptr(), n)

@@ -487,6 +487,10 @@ def run_ours(args, wl):
     else:
         block_rule = "fixed"
     pa = PA_MODEL_SYMS.get(args.workload, 0)
+    if world > 1 and not pa:
+        # the library's own NCCL communicator (ncclCommInitRank inside b200ans_comm_init; torch.distributed only carries
+        # the unique id): the histogram all-reduce then runs inside b200ans_compress_sharded[_device], on the codec's stream
+        sharded.init_comm(codec, group)
     d_in = generate_device(gen, n, dev, seed=rank)
     d_blob = torch.empty(blob_capacity(codec, method, n, pa), dtype=torch.uint8, device=dev)
     d_out = torch.empty(n, dtype=torch.int32, device=dev)
@@ -502,14 +506,14 @@ def run_ours(args, wl):
             dist.barrier(group)
         torch.cuda.synchronize(dev)
 
-    kern = {"histogram": 0.0, "encode": 0.0, "compact": 0.0, "decode": 0.0, "model_host": 0.0}
+    kern = {"histogram": 0.0, "encode": 0.0, "compact": 0.0, "decode": 0.0, "model_host": 0.0, "allreduce": 0.0}
 
     def enc_dev():
         if pa:  # per-block models: nothing is shared between ranks
             return codec.pa_compress_device(method, f, pa, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
         if world == 1:
             return codec.compress_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
-        return sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
+        return codec.compress_sharded_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
 
     def dec_dev(nbytes):
         if pa:
@@ -530,6 +534,7 @@ def run_ours(args, wl):
             acc["compact"] += s.ms_compact
             acc["decode"] += s2.ms_decode
             acc["model_host"] += enc_model + s2.ms_model
+            acc["allreduce"] += s.ms_allreduce
         return nb, s, s2
 
     # ---- device-resident timing -------------------------------------------------------------
@@ -616,13 +621,10 @@ def run_ours(args, wl):
             nbh = codec.compress_ptr(method, f, h_blob.data_ptr(), h_blob.numel(), h_in.data_ptr(), n)
             codec.decompress_ptr(method, f, h_out.data_ptr(), n, h_blob.data_ptr(), nbh)
             return nbh
-        with torch.cuda.stream(stream):
-            d_in.copy_(h_in, non_blocking=True)
-            nbh = sharded.compress_shard(codec, method, f, d_in, n, d_blob, group, sync)
-            h_blob[:nbh].copy_(d_blob[:nbh], non_blocking=True)
-            stream.synchronize()
-            # decoding needs no collective: the same host-buffer call as at N = 1 (copy-in / decode / copy-out pipeline)
-            codec.decompress_ptr(method, f, h_out.data_ptr(), n, h_blob.data_ptr(), nbh)
+        # host buffers in, host buffers out: the collective host-buffer entry point, then (no collective) the same
+        # pipelined decode call as at N = 1
+        nbh = codec.compress_sharded_ptr(method, f, h_blob.data_ptr(), h_blob.numel(), h_in.data_ptr(), n)
+        codec.decompress_ptr(method, f, h_out.data_ptr(), n, h_blob.data_ptr(), nbh)
         return nbh
 
     for _ in range(min(args.warmup, 2)):
@@ -650,14 +652,15 @@ def run_ours(args, wl):
     t = torch.tensor([ms_total, e2e_ms, enc_ms, dec_ms, copy_ms, e2e_dev_ms], dtype=torch.float64, device=dev)
     par_ok = True if parity is None else bool(parity.get("ok", True))
     okt = torch.tensor([int(ok and e2e_ok), int(par_ok)], dtype=torch.int32, device=dev)
-    kt = torch.tensor([kern[k] for k in ("histogram", "encode", "compact", "decode", "model_host")], dtype=torch.float64, device=dev)
+    KEYS = ("histogram", "encode", "compact", "decode", "model_host", "allreduce")
+    kt = torch.tensor([kern[k] for k in KEYS], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         dist.all_reduce(okt, op=dist.ReduceOp.MIN, group=group)
         dist.all_reduce(kt, op=dist.ReduceOp.MAX, group=group)
     ms_total, e2e_ms, enc_ms, dec_ms, copy_ms, e2e_dev_ms = (float(x) for x in t.tolist())
     all_ok, par_all_ok = bool(okt[0].item()), bool(okt[1].item())
-    for k, v in zip(("histogram", "encode", "compact", "decode", "model_host"), kt.tolist()):
+    for k, v in zip(KEYS, kt.tolist()):
         kern[k] = float(v)
 
     if rank == 0:
@@ -709,7 +712,7 @@ def run_ours(args, wl):
                        "block_syms": pa or args.block_syms, "block_syms_rule": "one model per block" if pa else block_rule, "n_blocks_per_gpu": n_blocks,
                        "l2": "inputs (%.0f MB per GPU) larger than the 126 MB L2; no flush" % (4.0 * n / 1e6),
                        "model": ("pseudo-adaptive: one model per block, normalised on the device, no collective" if pa else
-                                 "semi-static, global histogram" + (" via NCCL all-reduce" if world > 1 else "")),
+                                 "semi-static, global histogram" + (" via one ncclAllReduce inside b200ans_compress_sharded" if world > 1 else "")),
                        "frame_size": frame, "model_symbols": nsyms,
                        "frame_note": ("jobs of 2^31 symbols and more: the reference's 32-bit accumulators in cross_entropy (util.hpp:288-289) "
                                       "change adjust_freqs' stopping rule; the frame is the reference's for this histogram (SURVEY 3.8)"
@@ -719,6 +722,7 @@ def run_ours(args, wl):
             "bits_per_symbol": 8.0 * total_bytes / n, "payload_bytes_per_symbol": c, "prelude_bytes": prelude_bytes,
             "roundtrip_ok": all_ok, "parity": dict(parity or {}, all_ranks_ok=par_all_ok),
             "roofline": roofline, "kernels": kernels, "host_model_ms_per_step": per["model_host"],
+            "allreduce_ms_per_step": per["allreduce"],
             "cpu_baseline": cpu,
             "e2e": {"value": gb_step / (e2e_ms / e2e_steps / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
@@ -727,7 +731,7 @@ def run_ours(args, wl):
                     "copy_only_note": "the same bytes per step with cudaMemcpyAsync only, both directions overlapped, all ranks at once",
                     "api": "b200ans_pa_compress + b200ans_pa_decompress (host buffers, pinned)" if pa
                     else "b200ans_compress + b200ans_decompress (host buffers, pinned)" if world == 1
-                    else "pinned H2D + staged device API + D2H per rank"},
+                    else "b200ans_compress_sharded + b200ans_decompress per rank (host buffers, pinned)"},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if world == 1 and not args.no_targets and not args.symbols:

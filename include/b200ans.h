@@ -52,6 +52,9 @@ extern "C" {
 #define B200ANS_E_DOMAIN (-4)   /* input outside the reference's valid domain */
 #define B200ANS_E_FORMAT (-5)   /* not a b200ans container / corrupt header */
 #define B200ANS_E_STATE (-6)    /* call sequence error (e.g. encode before a model exists) */
+#define B200ANS_E_NCCL (-7)     /* NCCL missing (libnccl.so.2 is loaded on first use) or a collective failed */
+#define B200ANS_E_NOMEM (-8)    /* host allocation failed */
+#define B200ANS_E_INTERNAL (-9) /* an unexpected C++ exception was stopped at the ABI boundary */
 
 #define B200ANS_METHOD_INT 0   /* "ANS"        plain large-alphabet ANS, ans_int.hpp          */
 #define B200ANS_METHOD_FOLD 1  /* "ANSfold-f"  ans_fold.hpp                                   */
@@ -87,7 +90,14 @@ typedef struct b200ans_stats {
     uint64_t total_bytes;   /* whole container                                 */
     char encode_kernel[32]; /* block encoder / decoder the most recent call launched   */
     char decode_kernel[32]; /* (as ncu names them: "lpb3_encode_kernel", ...)          */
+    float ms_allreduce;     /* histogram / maximum all-reduce (sharded calls)          */
+    uint32_t model_flags;   /* B200ANS_MODEL_* of the current encoder model            */
 } b200ans_stats;
+/* The model was normalised from 2^31 symbols or more: the reference's cross_entropy() sums the counts in an `int`
+ * (util.hpp:288-289), so adjust_freqs' stopping rule changes -- in [2^31, 2^32) the first frame that fits is taken
+ * (a tiny frame, more bits per symbol), from 2^32 on the frame grows until a frequency nears 16 bits (2^18 .. 2^19
+ * slots).  b200ans reproduces this bit for bit (the frame is part of the stream format); the flag tells the caller. */
+#define B200ANS_MODEL_INT_ACCUMULATOR_QUIRK 1u
 
 /* What a container says about itself (the reference stores neither n nor the byte count, methods.hpp:541-546). */
 typedef struct b200ans_container {
@@ -175,6 +185,33 @@ int b200ans_block_stride(const b200ans_ctx* ctx, int method, size_t* stride);
 int b200ans_decode_blocks_device(b200ans_ctx* ctx, const uint8_t* d_payload, const uint64_t* d_offsets,
     const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst);
 
+/* ---- multi-GPU: one context per GPU (one process per GPU, or one thread per GPU) ---------- */
+/* the input is split into per-GPU block ranges; the single semi-static model comes from ONE
+ * all-reduce (sum) of the histogram -- plus the maximum for the coders whose alphabet is the value range -- after
+ * which every rank runs the same deterministic normalisation on the same counts (identical model, no broadcast) and
+ * codes its own shard.  Decoding needs no communication: b200ans_decompress[_device] per shard.
+ * The reference has no counterpart (single process, ans_fold.hpp:68-92 counts one array); NCCL is opened with
+ * dlopen("libnccl.so.2") on first use, so a process that already holds NCCL (torch) shares that copy. */
+#define B200ANS_COMM_ID_BYTES 128
+/* rank 0: a fresh NCCL unique id (ncclGetUniqueId); hand the bytes to every rank by any means */
+int b200ans_comm_unique_id(uint8_t id[B200ANS_COMM_ID_BYTES]);
+/* collective over all ranks: ncclCommInitRank on the context's device; the context owns the communicator */
+int b200ans_comm_init(b200ans_ctx* ctx, const uint8_t id[B200ANS_COMM_ID_BYTES], int rank, int world);
+/* or borrow a communicator the caller already has (an ncclComm_t as void*); never destroyed by the library */
+int b200ans_comm_attach(b200ans_ctx* ctx, void* nccl_comm, int rank, int world);
+int b200ans_comm_release(b200ans_ctx* ctx);
+/* in place, on the context's stream: d_bins[nbins] (device u64) summed over the ranks and, when d_max is not NULL,
+ * *d_max (device u32) replaced by the maximum over the ranks -- one NCCL group. Without a communicator: no-op. */
+int b200ans_allreduce_hist(b200ans_ctx* ctx, uint64_t* d_bins, size_t nbins, uint32_t* d_max);
+/* b200ans_compress_device / b200ans_compress on this rank's shard with the GLOBAL model: histogram (K1) -> all-reduce
+ * -> normalise -> encode (K2).  Collective: every rank of the communicator must call it, a rank whose shard is empty
+ * (n == 0) included -- it takes part in the reduction and writes an empty container.  Each rank gets its own
+ * container (the same prelude in all of them). */
+int b200ans_compress_sharded_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint8_t* d_dst, size_t dst_capacity,
+    const uint32_t* d_src, size_t n, size_t* out_bytes);
+int b200ans_compress_sharded(b200ans_ctx* ctx, int method, uint32_t fidelity, uint8_t* dst, size_t dst_capacity,
+    const uint32_t* src, size_t n, size_t* out_bytes);
+
 /* ---- pseudo-adaptive mode (src/pseudo_adaptive.cpp:64-177) ------------------------------ */
 /* Every `model_syms` consecutive symbols (a multiple of 128 in [1024, 2^24]) are coded with their own semi-static
  * model -- own histogram, own adjust_freqs, own prelude -- as the reference's driver does by calling T::encode block by
@@ -197,6 +234,11 @@ int b200ans_pa_decompress_device(b200ans_ctx* ctx, int method, uint32_t fidelity
 /* out: largest_sym + 1 entries */
 int b200ans_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_t largest_sym, int require_u16,
     uint32_t H_approx, uint32_t* out);
+/* scale_freqs (ans_util.hpp:77-95): one fit of the counts F[nbins] to the frame M -- symbols in `mapping` order
+ * (sigma entries, rarest first), running ratio, (uint32_t)(0.5 + ratio * F), floor at 1.  S[nbins] receives the
+ * shares; *fits = 1 iff the frame came out exactly (the reference's return value). */
+int b200ans_scale_freqs(uint32_t* S, const uint64_t* F, size_t nbins, const uint32_t* mapping, size_t sigma, int64_t M,
+    uint64_t freq_sum, int* fits);
 int b200ans_serialize_interp(const uint32_t* nfreqs, size_t count, uint64_t frame_size, uint8_t* dst, size_t capacity,
     size_t* out_bytes);
 /* dst may be NULL to query the count; consumed may be NULL */

@@ -205,6 +205,17 @@ int ref_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_t largest_sym, 
     return (int)s.size();
 }
 
+// scale_freqs (ans_util.hpp:77-95) as is: S in/out (nbins entries), returns the reference's bool ("the fit failed")
+int ref_scale_freqs(uint32_t* S, const uint64_t* F, size_t nbins, const uint32_t* mapping, size_t sigma, int64_t M,
+    uint64_t freq_sum)
+{
+    std::vector<uint32_t> s(S, S + nbins), map(mapping, mapping + sigma);
+    std::vector<uint64_t> f(F, F + nbins);
+    const bool failed = scale_freqs(s, f, map, M, sigma, freq_sum);
+    std::copy(s.begin(), s.end(), S);
+    return failed ? 1 : 0;
+}
+
 // returns total prelude bytes (vbyte + log2 byte + interp words) written to out
 long ref_serialize_interp(const uint32_t* nfreqs, size_t count, uint64_t frame_size, uint8_t* out)
 {

@@ -136,6 +136,18 @@ class _CpuCodec:
                                 ptr(out, u32p))
         return out
 
+    def scale_freqs(self, freqs, mapping, frame, freq_sum=None):
+        """reference shim only: scale_freqs (ans_util.hpp:77-95) -> (S, fits)"""
+        fn = self.lib.ref_scale_freqs
+        fn.restype = C.c_int
+        fn.argtypes = [u32p, u64p, C.c_size_t, u32p, C.c_size_t, C.c_int64, C.c_uint64]
+        freqs = np.ascontiguousarray(freqs, dtype=np.uint64)
+        mapping = np.ascontiguousarray(mapping, dtype=np.uint32)
+        out = np.zeros(freqs.size, dtype=np.uint32)
+        failed = fn(ptr(out, u32p), ptr(freqs, u64p), freqs.size, ptr(mapping, u32p), mapping.size, int(frame),
+                    int(freqs.sum()) if freq_sum is None else int(freq_sum))
+        return out, not failed
+
     def serialize_interp(self, nfreqs, frame_size):
         nfreqs = np.ascontiguousarray(nfreqs, dtype=np.uint32)
         out = np.zeros(nfreqs.size * 8 + 64, dtype=np.uint8)

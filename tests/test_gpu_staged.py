@@ -1,0 +1,286 @@
+"""-m gpu: the staged entry points on their own (histogram / maximum against numpy counts), the known-answer runs of
+BASELINE.json's configs 1 and 2 on the reference's own generator, the multi-GPU entry point on one rank, the domain
+limits the advisor listed, and corrupt containers (an error code, never a fault)."""
+import numpy as np
+import pytest
+
+import _container
+import _inputs
+from _libs import M_FOLD, M_INT, M_MSB, M_RFOLD, have_reference, oracle, reference, ref_generate
+
+pytestmark = pytest.mark.gpu
+
+
+def cpu():
+    return reference() if have_reference() else oracle()
+
+
+def _host_symbols(host, method, f, data):
+    if method == M_INT:
+        return data
+    uniq, inv = np.unique(data, return_inverse=True)
+    sym = np.array([host.msb_map(int(v))[0] if method == M_MSB else host.fold_map(f, int(v))[0] for v in uniq], dtype=np.uint32)
+    return sym[inv]
+
+
+def fnv1a64(b):
+    h = 0xCBF29CE484222325
+    for x in np.asarray(b, dtype=np.uint8).tobytes():
+        h = ((h ^ x) * 0x100000001B3) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+# ---- K1 alone ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("method,f,kind,n", [
+    (M_FOLD, 1, "zipf20", 1_000_003), (M_FOLD, 2, "wide", 300_001), (M_FOLD, 5, "zipf20", 200_000), (M_FOLD, 8, "wide", 200_000),
+    (M_MSB, 0, "wide", 300_001), (M_INT, 0, "geom", 1_000_003),  # every bin in shared memory
+    (M_INT, 0, "zipf20", 2_000_001),  # 2^20 + 1 bins: privatised head + global atomics
+    (M_INT, 0, "u16", 500_000),       # 65 536 bins, flat: mostly global atomics
+])
+def test_histogram_device_equals_host_count(codec, host, method, f, kind, n):
+    import torch
+
+    data = _inputs.make(kind, n, seed=13)
+    sym = _host_symbols(host, method, f, data)
+    nbins = int(data.max()) + 1 if method == M_INT else (1280 if method == M_MSB else 1 << (f + 9))
+    want = np.bincount(sym, minlength=nbins).astype(np.uint64)
+    d_in = torch.from_numpy(data.view(np.int32)).cuda()
+    d_bins = torch.zeros(nbins, dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    codec.histogram_device(method, f, d_in.data_ptr(), n, d_bins.data_ptr(), nbins)
+    torch.cuda.synchronize()
+    got = d_bins.cpu().numpy().view(np.uint64)
+    assert np.array_equal(got, want)
+    # a second call ADDS (the caller zeroes): two shards into one set of bins
+    codec.histogram_device(method, f, d_in.data_ptr(), n // 2 // 4 * 4, d_bins.data_ptr(), nbins)
+    torch.cuda.synchronize()
+    want2 = want + np.bincount(sym[: n // 2 // 4 * 4], minlength=nbins).astype(np.uint64)
+    assert np.array_equal(d_bins.cpu().numpy().view(np.uint64), want2)
+
+
+@pytest.mark.parametrize("kind,n,nbins", [("geom", 700_001, 3071), ("zipf20", 700_001, 3071), ("geom", 5, 3071), ("u8", 100_000, 100)])
+def test_histogram_max_and_max_device(codec, kind, n, nbins):
+    """one pass: optimistic counts into nbins bins (larger values dropped) + the running maximum"""
+    import torch
+
+    data = _inputs.make(kind, n, seed=17)
+    d_in = torch.from_numpy(data.view(np.int32)).cuda()
+    d_bins = torch.zeros(nbins, dtype=torch.int64, device="cuda")
+    d_max = torch.full((2,), 12345, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    codec.histogram_max_device(M_INT, 0, d_in.data_ptr(), n, d_bins.data_ptr(), nbins, d_max.data_ptr())
+    torch.cuda.synchronize()
+    assert int(d_max[0].item()) == int(data.max()) and int(d_max[1].item()) == 12345
+    want = np.bincount(data[data < nbins], minlength=nbins).astype(np.uint64)
+    assert np.array_equal(d_bins.cpu().numpy().view(np.uint64), want)
+    d_max.zero_()
+    torch.cuda.synchronize()
+    codec.max_device(d_in.data_ptr(), n, d_max.data_ptr())
+    torch.cuda.synchronize()
+    assert int(d_max[0].item()) == int(data.max())
+
+
+# ---- known answers: BASELINE.json configs 1 and 2 on the reference's own generator -------------------------------
+@pytest.mark.parametrize("name,kind,n,rng,q,method,f,fnv", [
+    ("C1", "zipf", 10_000_000, 1 << 20, 1.0, M_FOLD, 1, 0x1BBEC9F971751D8A),
+    ("C2", "geom", 100_000_000, 0, 0.01, M_INT, 0, 0xCFC2A87688DC9104),
+])
+def test_config_known_answers(codec, ref, name, kind, n, rng, q, method, f, fnv):
+    """generate_inputs.cpp:70-117 (mt19937(0) + zipf_dist.hpp / std::geometric_distribution) through the product in
+    reference-wire-format mode: the stream equals ans_X_compress() of the unmodified reference byte for byte (modulo
+    its uninitialised prelude padding bits), the blocked container's sampled blocks equal the per-block oracle, and --
+    where this libstdc++ generates the survey's stream -- the FNV-1a64 of SURVEY.md section 6."""
+    data = ref_generate(kind, n, seed=0, rng=rng, q=q)
+    want = ref.compress(method, f, data)
+    codec.set_block_syms(0)
+    try:
+        got = codec.compress(method, f, data).copy()
+    finally:
+        codec.set_block_syms(8192)
+    assert got.size == want.size
+    pre = codec.model_prelude().size
+    assert _container.prelude_equal(got[:pre], want[:pre])
+    assert np.array_equal(got[pre:], want[pre:]), f"{name}: payload differs from the reference's whole stream"
+    # the known answer of the survey session (same toolchain family); the payload comparison above is the authority
+    first = {"zipf": [2912, 110351, 134483, 115219], "geom": [89, 185, 194, 186]}[kind]
+    if list(data[:4]) == first:
+        patched = got.copy()
+        patched[:pre] = want[:pre]  # the reference's own padding bits
+        assert fnv1a64(patched) == fnv1a64(want)
+        if fnv1a64(want) != fnv:  # the reference's padding bits are uninitialised memory: informational only
+            import warnings
+
+            warnings.warn(f"{name}: this build of the reference hashes to {fnv1a64(want):016x}, the survey recorded {fnv:016x}")
+    assert np.array_equal(codec.decompress(method, f, want, n), data), "cannot decode the reference's stream"
+    # blocked container of the same input: sampled blocks against the per-block oracle, full round trip
+    bs = 4096
+    codec.set_block_syms(bs)
+    try:
+        blob = codec.compress(method, f, data).copy()
+        c = _container.parse(blob)
+        model = ref.model_create(method, f, data)
+        assert _container.prelude_equal(c["prelude"], model.serialize())
+        for b in np.random.default_rng(1).integers(0, c["n_blocks"], 48):
+            assert np.array_equal(c["blocks"][b], model.encode_block(data[b * bs : (b + 1) * bs])), (name, int(b))
+        assert np.array_equal(codec.decompress(method, f, blob, n), data)
+        assert blob.size <= want.size * 1.01
+    finally:
+        codec.set_block_syms(8192)
+
+
+# ---- the multi-GPU entry point, one rank ----------------------------------------------------------------------------
+@pytest.mark.parametrize("method,f,kind", [(M_FOLD, 1, "zipf20"), (M_INT, 0, "geom"), (M_INT, 0, "zipf16"), (M_RFOLD, 1, "zipf20"), (M_MSB, 0, "wide")])
+def test_sharded_entry_single_rank(method, f, kind):
+    """b200ans_comm_init with a world of one (ncclCommInitRank really runs) + b200ans_compress_sharded[_device]:
+    the same bytes as b200ans_compress, stats carry the all-reduce, an empty shard writes an empty container."""
+    import torch
+
+    import ans_large_alphabet_b200 as P
+
+    codec = P.Codec(device=0, block_syms=8192)
+    try:
+        try:
+            codec.comm_init(P.comm_unique_id(), 0, 1)
+        except P.B200AnsError as e:
+            if e.code == -7:
+                pytest.skip("NCCL not available on this box")
+            raise
+        data = _inputs.make(kind, 300_007, seed=21)
+        want = codec.compress(method, f, data).copy()
+        d_in = torch.from_numpy(data.view(np.int32)).cuda()
+        d_blob = torch.empty((codec.bound(method, data.size) + 15) // 16 * 16, dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        nb = codec.compress_sharded_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), data.size)
+        assert np.array_equal(d_blob[:nb].cpu().numpy(), want)
+        out = np.empty(want.size + 64, dtype=np.uint8)
+        nb2 = codec.compress_sharded_ptr(method, f, out.ctypes.data, out.size, data.ctypes.data, data.size)
+        assert np.array_equal(out[:nb2], want)
+        # an empty shard: a 64-byte container, and nothing to decode
+        nb3 = codec.compress_sharded_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), 0)
+        assert nb3 == 64 and codec.decompress(method, f, d_blob[:64].cpu().numpy(), 0).size == 0
+        codec.comm_release()
+    finally:
+        codec.close()
+
+
+def test_staged_encode_of_an_empty_shard(codec):
+    """a rank of a staged multi-GPU job whose shard is empty: b200ans_encode_device writes an empty container"""
+    import torch
+
+    data = _inputs.make("zipf16", 50_000, seed=2)
+    codec.compress(M_FOLD, 1, data)  # leaves a model in the context
+    d_blob = torch.zeros(256, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    assert codec.encode_device(d_blob.data_ptr(), 256, 0, 0) == 64
+    assert codec.decompress(M_FOLD, 1, d_blob[:64].cpu().numpy(), 0).size == 0
+
+
+# ---- domain limits (round-1 advisor findings) ------------------------------------------------------------------------
+def test_rfold_identity_mapping_domain(codec):
+    """fewer than 2^(f+7) distinct values: fine while every value is below 2^(f+7), E_DOMAIN otherwise (the reference's
+    decoder would return value - 2^(f+7), ans_reorder_fold.hpp:92-96 vs :301)"""
+    import ans_large_alphabet_b200 as P
+
+    rng = np.random.default_rng(5)
+    small = rng.integers(0, 200, 20_000, dtype=np.uint32)  # all below 2^8
+    blob = codec.compress(M_RFOLD, 1, small).copy()
+    assert np.array_equal(codec.decompress(M_RFOLD, 1, blob, small.size), small)
+    bad = (rng.integers(0, 10, 20_000, dtype=np.uint32) + 1_000_000).astype(np.uint32)  # ten values, all >= 2^8
+    with pytest.raises(P.B200AnsError) as e:
+        codec.compress(M_RFOLD, 1, bad)
+    assert e.value.code == -4
+
+
+def test_plain_ans_value_limit_is_the_same_on_both_sides(codec):
+    """values of 2^28 and more: refused by compress (model_load would refuse the prelude); a sparse alphabet just
+    below the limit round-trips"""
+    import ans_large_alphabet_b200 as P
+
+    rng = np.random.default_rng(6)
+    base = rng.integers(0, 50, 10_000, dtype=np.uint32)
+    too_big = base.copy()
+    too_big[17] = 1 << 28
+    with pytest.raises(P.B200AnsError) as e:
+        codec.compress(M_INT, 0, too_big)
+    assert e.value.code == -4
+    sparse = base.copy()
+    sparse[17] = (1 << 22) + 5  # 4M-entry alphabet, 51 symbols present
+    blob = codec.compress(M_INT, 0, sparse).copy()
+    assert np.array_equal(codec.decompress(M_INT, 0, blob, sparse.size), sparse)
+
+
+@pytest.mark.parametrize("path", [1, 2])
+def test_staged_path_checks_the_value_range(codec, path):
+    """the staged entry points see no maximum: the encoders themselves refuse values >= 2^30 for the folded coders"""
+    import torch
+
+    import ans_large_alphabet_b200 as P
+
+    codec.set_kernel_path(path)
+    n = 40_000
+    data = _inputs.make("zipf16", n, seed=8)
+    data[n // 2] = (1 << 30) + 7
+    d_in = torch.from_numpy(data.view(np.int32)).cuda()
+    bins = torch.zeros(1024, dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    codec.histogram_device(M_FOLD, 1, d_in.data_ptr(), n, bins.data_ptr(), 1024)
+    torch.cuda.synchronize()
+    codec.model_build(M_FOLD, 1, bins.cpu().numpy().view(np.uint64))
+    d_blob = torch.empty((codec.bound(M_FOLD, n) + 15) // 16 * 16, dtype=torch.uint8, device="cuda")
+    with pytest.raises(P.B200AnsError) as e:
+        codec.encode_device(d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
+    assert e.value.code == -4
+
+
+# ---- corrupt containers: an error code, never a fault ------------------------------------------------------------------
+@pytest.mark.parametrize("method,f,kind", [(M_FOLD, 1, "zipf20"), (M_INT, 0, "geom"), (M_MSB, 0, "wide"), (M_RFOLD, 1, "zipf20")])
+@pytest.mark.parametrize("path", [1, 2])
+@pytest.mark.parametrize("device_entry", [False, True])
+def test_corrupt_containers_fail_cleanly(codec, method, f, kind, path, device_entry):
+    import struct
+
+    import torch
+
+    import ans_large_alphabet_b200 as P
+
+    codec.set_kernel_path(path)
+    n = 90_001
+    data = _inputs.make(kind, n, seed=9)
+    good = codec.compress(method, f, data).copy()
+    c = _container.parse(good)
+
+    def decode(blob):
+        blob = np.ascontiguousarray(blob)
+        if not device_entry:
+            return codec.decompress(method, f, blob, n)
+        d = torch.zeros((blob.size + 15) // 16 * 16 + 64, dtype=torch.uint8, device="cuda")
+        d[: blob.size] = torch.from_numpy(blob).cuda()
+        out = torch.empty(n, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        codec.decompress_device(method, f, out.data_ptr(), n, d.data_ptr(), blob.size)
+        return out.cpu().numpy().view(np.uint32)
+
+    table_at = 64 + (c["prelude"].size + 3) // 4 * 4
+    cases = {}
+    b = good.copy(); b[table_at : table_at + 4] = np.frombuffer(struct.pack("<I", 8), np.uint8); cases["block shorter than its states"] = b
+    b = good.copy(); b[table_at + 4 : table_at + 8] = np.frombuffer(struct.pack("<I", 0xFFFFFFF0), np.uint8); cases["huge block size"] = b
+    b = good.copy(); b[64] = 0xFF; b[65] = 0xFF; b[66] = 0xFF; b[67] = 0x7F; cases["prelude claims a huge alphabet"] = b
+    cases["truncated"] = good[: good.size // 2].copy()
+    cases["prelude only"] = good[: 64 + 2].copy()
+    b = good.copy(); b[24:28] = np.frombuffer(struct.pack("<I", 2), np.uint8); cases["prelude length 2"] = b
+    for name, blob in cases.items():
+        with pytest.raises(P.B200AnsError) as e:
+            decode(blob)
+        assert e.value.code in (-5, -1), (name, e.value.code)
+    # flipped payload bytes: either an error (the block is not consumed exactly) or different symbols -- never a fault
+    rng = np.random.default_rng(4)
+    for trial in range(6):
+        blob = good.copy()
+        at = c["payload_at"] + int(rng.integers(0, c["payload_bytes"]))
+        blob[at : at + 16] ^= rng.integers(1, 255, min(16, blob.size - at), dtype=np.uint8)
+        try:
+            decode(blob)
+        except P.B200AnsError as e:
+            assert e.value.code == -5
+    # the context is still healthy
+    assert np.array_equal(decode(good), data)
