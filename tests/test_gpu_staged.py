@@ -95,23 +95,20 @@ def test_config_known_answers(codec, ref, name, kind, n, rng, q, method, f, fnv)
     codec.set_block_syms(0)
     try:
         got = codec.compress(method, f, data).copy()
+        pre = codec.model_prelude().size
+        assert np.array_equal(codec.decompress(method, f, want, n), data), "cannot decode the reference's stream"
     finally:
         codec.set_block_syms(8192)
     assert got.size == want.size
-    pre = codec.model_prelude().size
     assert _container.prelude_equal(got[:pre], want[:pre])
     assert np.array_equal(got[pre:], want[pre:]), f"{name}: payload differs from the reference's whole stream"
-    # the known answer of the survey session (same toolchain family); the payload comparison above is the authority
+    # the known answer of the survey session: informational (the reference leaves its prelude padding bits uninitialised,
+    # bits.hpp:148, so the hash of its stream is not a function of the input alone); the comparison above is the authority
     first = {"zipf": [2912, 110351, 134483, 115219], "geom": [89, 185, 194, 186]}[kind]
-    if list(data[:4]) == first:
-        patched = got.copy()
-        patched[:pre] = want[:pre]  # the reference's own padding bits
-        assert fnv1a64(patched) == fnv1a64(want)
-        if fnv1a64(want) != fnv:  # the reference's padding bits are uninitialised memory: informational only
-            import warnings
+    if list(data[:4]) == first and fnv1a64(want) != fnv:
+        import warnings
 
-            warnings.warn(f"{name}: this build of the reference hashes to {fnv1a64(want):016x}, the survey recorded {fnv:016x}")
-    assert np.array_equal(codec.decompress(method, f, want, n), data), "cannot decode the reference's stream"
+        warnings.warn(f"{name}: this build of the reference hashes to {fnv1a64(want):016x}, the survey recorded {fnv:016x}")
     # blocked container of the same input: sampled blocks against the per-block oracle, full round trip
     bs = 4096
     codec.set_block_syms(bs)
@@ -281,6 +278,6 @@ def test_corrupt_containers_fail_cleanly(codec, method, f, kind, path, device_en
         try:
             decode(blob)
         except P.B200AnsError as e:
-            assert e.value.code == -5
+            assert e.code == -5
     # the context is still healthy
     assert np.array_equal(decode(good), data)

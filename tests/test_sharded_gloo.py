@@ -99,3 +99,78 @@ def test_two_rank_global_model_equals_reference(tmp_path):
     g = np.load(os.path.join(HERE, "golden", "int_geom.npz"))
     want = np.bincount(g["data"]).astype(np.uint64)
     assert np.array_equal(r0["int_geom_onepass"], want) and np.array_equal(r1["int_geom_onepass"], want)
+
+
+# ---- -m gpu: the library's own NCCL exchange, two ranks (needs two GPUs; the 1-GPU box skips it) -------------------
+def _gpu_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, HERE)
+    import torch
+    import torch.distributed as dist
+
+    import ans_large_alphabet_b200 as P
+    from ans_large_alphabet_b200 import sharded
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)  # only carries the NCCL unique id
+    codec = P.Codec(device=rank, block_syms=1024)
+    sharded.init_comm(codec, dist.group.WORLD)
+    res = {}
+    for name in ("fold1_zipf20", "msb_zipf20", "int_geom", "rfold2_zipf20"):
+        g = np.load(os.path.join(HERE, "golden", name + ".npz"))
+        method, f, data = int(g["method"]), int(g["fidelity"]), g["data"]
+        lo, hi = sharded.shard_range(data.size, 1024, rank, world)
+        if name == "msb_zipf20":  # rank 1's shard is empty: it takes part in the reduction, writes an empty container
+            lo, hi = (0, data.size) if rank == 0 else (data.size, data.size)
+        mine = np.ascontiguousarray(data[lo:hi])
+        d_in = torch.from_numpy(mine.view(np.int32)).cuda() if mine.size else torch.zeros(4, dtype=torch.int32, device="cuda")
+        d_blob = torch.empty((codec.bound(method, max(mine.size, 1)) + 15) // 16 * 16, dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        nb = codec.compress_sharded_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), mine.size)
+        blob = d_blob[:nb].cpu().numpy()
+        frame, nfreqs = codec.model_nfreqs()
+        res[name + "_nfreqs"] = nfreqs
+        res[name + "_prelude"] = codec.model_prelude()
+        res[name + "_blob"] = blob
+        res[name + "_range"] = np.array([lo, hi])
+        back = codec.decompress(method, f, blob, mine.size)
+        res[name + "_ok"] = np.array([int(np.array_equal(back, mine))])
+    np.savez(os.path.join(out_dir, f"gpu_rank{rank}.npz"), **res)
+    codec.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_gpu_sharded_compress_uses_the_global_model(tmp_path):
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+
+    import _container
+    from _libs import have_reference, oracle, reference
+
+    cpu = reference() if have_reference() else oracle()
+    port = _free_port()
+    mp.spawn(_gpu_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    r = [np.load(tmp_path / "gpu_rank0.npz"), np.load(tmp_path / "gpu_rank1.npz")]
+    for name in ("fold1_zipf20", "msb_zipf20", "int_geom", "rfold2_zipf20"):
+        g = np.load(os.path.join(HERE, "golden", name + ".npz"))
+        method, f, data = int(g["method"]), int(g["fidelity"]), g["data"]
+        assert np.array_equal(r[0][name + "_nfreqs"], g["nfreqs"]) and np.array_equal(r[1][name + "_nfreqs"], g["nfreqs"]), name
+        assert _container.prelude_equal(r[0][name + "_prelude"], g["prelude"]) and np.array_equal(r[0][name + "_prelude"], r[1][name + "_prelude"])
+        assert int(r[0][name + "_ok"][0]) == 1 and int(r[1][name + "_ok"][0]) == 1
+        model = cpu.model_create(method, f, data)
+        for k in (0, 1):
+            lo, hi = (int(x) for x in r[k][name + "_range"])
+            if hi == lo:
+                assert r[k][name + "_blob"].size == 64
+                continue
+            c = _container.parse(r[k][name + "_blob"])
+            for b, payload in enumerate(c["blocks"]):
+                want = model.encode_block(data[lo + b * 1024 : min(hi, lo + (b + 1) * 1024)])
+                assert np.array_equal(payload, want), (name, k, b)
