@@ -78,6 +78,7 @@ SIGNATURES = {
     "b200ans_encode_blocks_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_block_stride": (C.c_int, [C.c_void_p, C.c_int, szp]),
     "b200ans_decode_blocks_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200ans_decode_blocks_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_comm_unique_id": (C.c_int, [u8p]),
     "b200ans_comm_init": (C.c_int, [C.c_void_p, u8p, C.c_int, C.c_int]),
     "b200ans_comm_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
@@ -366,6 +367,10 @@ class Codec:
 
     def decompress_device(self, method, f, d_dst, n, d_src, nbytes):
         self._check(self.lib.b200ans_decompress_device(self.h, method, f, d_dst, n, d_src, nbytes))
+
+    def decode_blocks_noalloc(self, d_payload, payload_bytes, d_block_bytes, n, d_dst):
+        """container-layout blocks + the loaded model -> symbols, with no allocation (offsets in a static device array)"""
+        self._check(self.lib.b200ans_decode_blocks_noalloc(self.h, d_payload, payload_bytes, d_block_bytes, n, d_dst))
 
     # ---- multi-GPU (one context per GPU; NCCL is opened by the library) ---------------------------
     def comm_init(self, unique_id, rank, world):

@@ -1648,6 +1648,102 @@ try {
 }
 B200ANS_CATCH_INT
 
+// ==========================================================================================
+// decode without any allocation (no counterpart in the reference)
+// ==========================================================================================
+// b200ans_decompress_device keeps the per-block payload offsets in a grow-only cudaMalloc'ed buffer (ctx->offsets), which
+// callers that may not allocate (CUDA graph capture, tight serving loops) cannot use.  Here that scratch -- the offsets the
+// size scan writes and the decoder reads, plus the scan's totals -- is a file-scope device array of fixed size.
+// Every GPU that loads the library holds these 513 KiB until the process exits.  ALL calls on a device share the array
+// and it keeps the last call's contents: the scan rewrites every entry a call reads before the decoder starts (stream
+// order), nothing has to start at zero; calls that overlap on the GPU (two contexts / streams on one device) race.
+constexpr uint32_t kNoAllocMaxBlocks = B200ANS_NOALLOC_MAX_BLOCKS;
+constexpr uint32_t kNoAllocHead = 32; // u64 words in front of the offsets: [0..1] the scan's totals
+static __device__ __align__(256) uint64_t g_noalloc_scratch[kNoAllocHead + kNoAllocMaxBlocks];
+
+namespace {
+
+constexpr int kNoAllocMaxDevices = 64;
+uint64_t* g_noalloc_addr[kNoAllocMaxDevices]; // device address of g_noalloc_scratch, per device (0: not resolved yet)
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+int noalloc_scratch(b200ans_ctx* c, uint64_t** out)
+{
+    if (c->device < 0 || c->device >= kNoAllocMaxDevices)
+        return c->fail(B200ANS_E_ARG, "decode_blocks_noalloc: device index beyond the per-device address table");
+    uint64_t* p = __atomic_load_n(&g_noalloc_addr[c->device], __ATOMIC_ACQUIRE);
+    if (!p) {
+        CU(c, cudaSetDevice(c->device));
+        void* sym = nullptr;
+        CU(c, cudaGetSymbolAddress(&sym, g_noalloc_scratch));
+        if (!sym)
+            return c->fail(B200ANS_E_CUDA, "decode_blocks_noalloc: cudaGetSymbolAddress returned no address");
+        p = static_cast<uint64_t*>(sym);
+        __atomic_store_n(&g_noalloc_addr[c->device], p, __ATOMIC_RELEASE); // every thread resolves the same address
+    }
+    *out = p;
+    return B200ANS_OK;
+}
+
+} // namespace
+
+extern "C" int b200ans_decode_blocks_noalloc(b200ans_ctx* c, const uint8_t* d_payload, size_t payload_bytes,
+    const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_payload || !d_block_bytes || !d_dst || n == 0 || (reinterpret_cast<uintptr_t>(d_payload) & 15)
+        || (reinterpret_cast<uintptr_t>(d_block_bytes) & 3))
+        return c->fail(B200ANS_E_ARG, "decode_blocks_noalloc: null / unaligned argument (payload: 16 bytes, sizes: 4 bytes)");
+    if (!c->have_dec)
+        return c->fail(B200ANS_E_STATE, "decode_blocks_noalloc: load a model first (b200ans_model_load is the set-up step that may allocate)");
+    if (c->block_syms == 0)
+        return c->fail(B200ANS_E_ARG, "decode_blocks_noalloc: needs a blocked layout (block_syms > 0)");
+    const uint32_t bs = c->block_syms;
+    const uint64_t nb = (uint64_t(n) + bs - 1) / bs;
+    if (nb > kNoAllocMaxBlocks)
+        return c->fail(B200ANS_E_ARG, "decode_blocks_noalloc: more than B200ANS_NOALLOC_MAX_BLOCKS (65536) blocks; the static scratch holds no more -- use b200ans_decompress_device");
+    if (env_int("B200ANS_PURE", -1) == 1 && !c->dec_have_pure && c->dec_pure_possible)
+        return c->fail(B200ANS_E_STATE, "decode_blocks_noalloc: B200ANS_PURE=1 would build (and allocate) the whole-group rank records");
+    CU(c, cudaSetDevice(c->device));
+    uint64_t* scratch = nullptr;
+    RET(noalloc_scratch(c, &scratch));
+    uint64_t* d_totals = scratch;
+    uint64_t* d_offsets = scratch + kNoAllocHead;
+
+    CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
+    {   // untrusted sizes, as in b200ans_decode_blocks_device; then offsets[b] = sum of the padded sizes in front of b
+        const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>((nb + 255) / 256, uint64_t(c->num_sms) * 4)));
+        check_block_sizes_kernel<<<grid, 256, 0, c->stream>>>(d_block_bytes, uint32_t(nb), c->dec_method == METHOD_INT ? 3u : 0u, c->d_err());
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+        scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_block_bytes, uint32_t(nb), d_offsets, d_totals, nullptr);
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+        // the scan's padded total next to the error flag: one small read through the context's pinned block
+        CU(c, cudaMemcpyAsync(c->d_totals(), d_totals, 16, cudaMemcpyDeviceToDevice, c->stream));
+        RET(read_small(c));
+        if (c->h_small()->error_flag)
+            return c->fail(B200ANS_E_FORMAT, "decode: a block is shorter than its four states, or a plain-ANS block is not a whole number of words");
+        if (c->h_small()->totals[0] > payload_bytes)
+            return c->fail(B200ANS_E_FORMAT, "decode_blocks_noalloc: the block sizes add up to more than payload_bytes");
+    }
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    c->dec_words_aligned = true; // blocks start 16-byte aligned: the payload base is, the offsets are multiples of 16
+    const int rc = launch_decode(c, d_payload, d_offsets, d_block_bytes, n, bs, uint32_t(nb), d_dst);
+    c->dec_words_aligned = false;
+    RET(rc);
+    CU(c, cudaEventRecord(c->ev[1], c->stream));
+    RET(read_small(c));
+    c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
+    c->stats.n_blocks = uint32_t(nb);
+    if (c->h_small()->error_flag)
+        return c->fail(B200ANS_E_FORMAT, "decode: a block's payload was not consumed exactly (corrupt stream or wrong model)");
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
 // current model + d_src -> container (or reference wire format when block_syms == 0) at d_dst
 extern "C" int b200ans_encode_device(b200ans_ctx* c, uint8_t* d_dst, size_t cap, const uint32_t* d_src, size_t n,
     size_t* out_bytes)

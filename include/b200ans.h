@@ -185,6 +185,23 @@ int b200ans_block_stride(const b200ans_ctx* ctx, int method, size_t* stride);
 int b200ans_decode_blocks_device(b200ans_ctx* ctx, const uint8_t* d_payload, const uint64_t* d_offsets,
     const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst);
 
+/* ---- decoding without any allocation ---------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * b200ans_decode_blocks_device's work for blocks laid out as in the container's payload area -- block b starts at
+ * d_payload + sum over b' < b of roundup16(d_block_bytes[b']) -- with the current decoder model (b200ans_model_load is
+ * the set-up step, and the one that may allocate).  The per-block offsets, which b200ans_decompress_device keeps in a
+ * cudaMalloc'ed grow-only buffer, live in a file-scope device array of B200ANS_NOALLOC_MAX_BLOCKS entries (513 KiB, held
+ * by every GPU that loads the library until the process exits); this call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine.  More blocks than that (n / block_syms, rounded up): B200ANS_E_ARG.
+ * d_payload 16-byte aligned, payload_bytes = bytes readable behind it (the sizes must not add up to more);
+ * block size = the context's (b200ans_set_block_syms); symbols go to d_dst[0..n).
+ * ALL calls on one GPU share the array and it keeps the last call's contents (everything a call reads is rewritten by
+ * the same call first, in stream order): calls that overlap on the GPU -- two contexts or streams -- race. */
+#define B200ANS_NOALLOC_MAX_BLOCKS 65536u
+int b200ans_decode_blocks_noalloc(b200ans_ctx* ctx, const uint8_t* d_payload, size_t payload_bytes,
+    const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst);
+
 /* ---- multi-GPU: one context per GPU (one process per GPU, or one thread per GPU) ---------- */
 /* the input is split into per-GPU block ranges; the single semi-static model comes from ONE
  * all-reduce (sum) of the histogram -- plus the maximum for the coders whose alphabet is the value range -- after
