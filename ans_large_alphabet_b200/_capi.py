@@ -70,6 +70,7 @@ SIGNATURES = {
     "b200ans_histogram_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "b200ans_histogram_max_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_rfold_prepare": (C.c_int, [C.c_void_p, C.c_uint32, u64p, C.c_size_t]),
+    "b200ans_rfold_prepare_device": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_model_build": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u64p, C.c_size_t]),
     "b200ans_model_prelude": (C.c_int, [C.c_void_p, u8p, C.c_size_t, szp]),
     "b200ans_model_nfreqs": (C.c_int, [C.c_void_p, u32p, C.c_size_t, szp, u64p]),
@@ -410,6 +411,9 @@ class Codec:
     def rfold_prepare(self, f, raw_bins):
         raw_bins = np.ascontiguousarray(raw_bins, dtype=np.uint64)
         self._check(self.lib.b200ans_rfold_prepare(self.h, f, _p(raw_bins, u64p), raw_bins.size))
+
+    def rfold_prepare_device(self, f, d_raw_bins, nvalues, d_folded_bins):
+        self._check(self.lib.b200ans_rfold_prepare_device(self.h, f, d_raw_bins, nvalues, d_folded_bins))
 
     def model_build(self, method, f, bins):
         bins = np.ascontiguousarray(bins, dtype=np.uint64)

@@ -22,6 +22,7 @@
 #include "kernels.cuh"
 #include "lpb_kernels.cuh"
 #include "lpb3_kernels.cuh"
+#include "rfold_kernels.cuh"
 #include "pa_kernels.cuh"
 
 using namespace b200ans;
@@ -162,6 +163,11 @@ struct b200ans_ctx {
 
     // grow-only device buffers
     DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre, pa_keys;
+    // ANSrfold on the device (rfold_kernels.cuh): raw histogram, selection state, candidates, hash of the hot values
+    DevBuf rf_raw, rf_raw32, rf_state, rf_hist, rf_tiles, rf_cand_count, rf_cand_value, rf_most, rf_tags, rf_disp, enc_table_rf;
+    size_t rf_guess = 0;          // value range the next optimistic raw histogram is sized for
+    bool rf_hash_ok = false;      // the L3 encoder's perfect hash of most_frequent[] is on the device
+    uint32_t rf_mul = 0, rf_bshift = 0;
     uint32_t pa_undecided = 0;    // models of the last pa_compress the device normaliser handed to the host
     uint8_t* pa_pinned = nullptr; // pseudo-adaptive mode: counts / frequencies of all models (pinned, grows on demand)
     size_t pa_pinned_cap = 0;
@@ -358,7 +364,9 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys })
+             &c->dec_slots, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys,
+             &c->rf_raw, &c->rf_raw32, &c->rf_state, &c->rf_hist, &c->rf_tiles, &c->rf_cand_count, &c->rf_cand_value, &c->rf_most, &c->rf_tags, &c->rf_disp,
+             &c->enc_table_rf })
         b->release();
     for (auto& e : c->ev)
         if (e)
@@ -649,9 +657,10 @@ namespace {
 
 template <int METHOD>
 int launch_histogram(b200ans_ctx* c, uint32_t f, const uint32_t* d_src, size_t n, uint64_t* d_bins, size_t nbins,
-    uint32_t* d_max)
+    uint32_t* d_max, unsigned int* d_bins32 = nullptr)
 {
     HistArgs a {};
+    a.bins32 = d_bins32;
     a.in = d_src;
     a.n = n;
     a.fidelity = f;
@@ -671,7 +680,9 @@ int launch_histogram(b200ans_ctx* c, uint32_t f, const uint32_t* d_src, size_t n
         a.stride += 1;
     const size_t smem_bytes = size_t(a.replicas) * a.stride * sizeof(uint32_t);
     const bool all_smem = a.smem_bins == a.nbins;
-    auto k = all_smem ? histogram_kernel<METHOD, true> : histogram_kernel<METHOD, false>;
+    auto k = all_smem ? histogram_kernel<METHOD, true> : (d_bins32 && METHOD == METHOD_INT) ? histogram_kernel<METHOD, false, METHOD == METHOD_INT> : histogram_kernel<METHOD, false>;
+    if (all_smem && d_bins32)
+        return c->fail(B200ANS_E_INTERNAL, "histogram: 32-bit bins are for alphabets beyond the shared-memory head");
     CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kHistSmemWords * 4 + 1024)));
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kHistThreads, smem_bytes) != cudaSuccess || per_sm < 1) {
@@ -774,6 +785,69 @@ B200ANS_CATCH_INT
 // models
 // ==========================================================================================
 
+
+namespace {
+
+// Perfect hash of the K = 2^(f+7) most frequent values for the L3 encoder (lpb3_kernels.cuh L3Rfold): "hash and
+// displace" -- bucket b = (v * mul) >> bshift carries a displacement d_b, slot(v) = (v * mul + d_b) & (K - 1), every
+// hot value gets a slot of its own (K slots for K values: minimal).  Buckets are placed largest first.
+bool rfold_build_hash(const std::vector<uint32_t>& hot, uint32_t mul, uint32_t bshift, std::vector<uint32_t>& tags,
+    std::vector<uint16_t>& disp, std::vector<uint32_t>& slot_of_rank)
+{
+    const uint32_t K = uint32_t(hot.size());
+    const uint32_t B = 1u << (32u - bshift);
+    std::vector<std::vector<uint32_t>> buckets(B);
+    for (uint32_t r = 0; r < K; r++)
+        buckets[(hot[r] * mul) >> bshift].push_back(r);
+    std::vector<uint32_t> order(B);
+    for (uint32_t b = 0; b < B; b++)
+        order[b] = b;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return buckets[x].size() > buckets[y].size(); });
+    tags.assign(K, 0xFFFFFFFFu);
+    disp.assign(B, 0);
+    slot_of_rank.assign(K, 0);
+    std::vector<uint8_t> used(K, 0);
+    for (uint32_t b : order) {
+        const auto& keys = buckets[b];
+        if (keys.empty())
+            break;
+        bool placed = false;
+        for (uint32_t d = 0; d < K && !placed; d++) {
+            bool ok = true;
+            size_t i = 0;
+            for (; i < keys.size(); i++) {
+                const uint32_t s = (hot[keys[i]] * mul + d) & (K - 1);
+                if (used[s]) {
+                    ok = false;
+                    break;
+                }
+                used[s] = 2; // tentatively
+            }
+            if (ok) {
+                for (uint32_t r : keys) {
+                    const uint32_t s = (hot[r] * mul + d) & (K - 1);
+                    used[s] = 1;
+                    tags[s] = hot[r];
+                    slot_of_rank[r] = s;
+                }
+                disp[b] = uint16_t(d);
+                placed = true;
+            } else {
+                for (size_t j = 0; j < i; j++) {
+                    const uint32_t s = (hot[keys[j]] * mul + d) & (K - 1);
+                    if (used[s] == 2)
+                        used[s] = 0;
+                }
+            }
+        }
+        if (!placed)
+            return false;
+    }
+    return true;
+}
+
+} // namespace
+
 // ans_reorder_fold.hpp:75-106: order values by (-count, value), the first 2^(f+7) become
 // 0..2^(f+7)-1 and everything else moves up by 2^(f+7); identity if fewer distinct values.
 extern "C" int b200ans_rfold_prepare(b200ans_ctx* c, uint32_t f, const uint64_t* raw_bins, size_t nvalues)
@@ -816,6 +890,95 @@ try {
     CU(c, c->mapping.reserve(nvalues * sizeof(uint32_t)));
     CU(c, cudaMemcpyAsync(c->mapping.p, mapping.data(), nvalues * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
+    c->n_values = uint32_t(nvalues);
+    c->map_f = f;
+    c->have_mapping = true;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+
+namespace {
+
+// rfold_kernels.cuh steps 1-5 on the context's stream: from the raw device histogram to most_frequent[] (rf_most),
+// mapping[] and the folded histogram; nothing is read back here.  `count_bits`: no count needs more bits.
+int rfold_select_launch(b200ans_ctx* c, uint32_t f, const uint64_t* d_raw, uint32_t nvalues, uint32_t count_bits, uint64_t* d_folded)
+{
+    const uint32_t K = 1u << (f + 7);
+    const uint32_t n_tiles = (nvalues + kRfTile - 1) / kRfTile;
+    const size_t nfolded = alphabet_bins(METHOD_RFOLD, f, 0);
+    CU(c, c->rf_state.reserve(sizeof(RfState)));
+    CU(c, c->rf_hist.reserve(kRfDigits * 4));
+    CU(c, c->rf_tiles.reserve(size_t(n_tiles) * 4));
+    CU(c, c->rf_cand_count.reserve(size_t(K) * 8));
+    CU(c, c->rf_cand_value.reserve(size_t(K) * 4));
+    CU(c, c->rf_most.reserve(size_t(K) * 4));
+    CU(c, c->mapping.reserve(size_t(nvalues) * 4));
+    CU(c, cudaMemsetAsync(c->rf_state.p, 0, sizeof(RfState), c->stream));
+    CU(c, cudaMemsetAsync(c->rf_hist.p, 0, kRfDigits * 4, c->stream));
+    CU(c, cudaMemsetAsync(d_folded, 0, nfolded * 8, c->stream));
+    RfState* st = c->rf_state.as<RfState>();
+    const auto* raw = reinterpret_cast<const unsigned long long*>(d_raw);
+    const int grid = int(std::max<uint32_t>(1, std::min<uint32_t>((nvalues + kRfThreads - 1) / kRfThreads, uint32_t(c->num_sms) * 8)));
+    const int tile_grid = int(std::max<uint32_t>(1, std::min<uint32_t>(n_tiles, uint32_t(c->num_sms) * 8)));
+    const uint32_t passes = std::max<uint32_t>(1, (std::min<uint32_t>(count_bits, 64) + kRfDigitBits - 1) / kRfDigitBits);
+    for (uint32_t p = 0; p < passes; p++) {
+        const uint32_t shift = (passes - 1 - p) * kRfDigitBits;
+        rf_digit_hist_kernel<<<grid, kRfThreads, 0, c->stream>>>(raw, nvalues, shift, p == 0, st, c->rf_hist.as<unsigned int>(), st);
+        rf_digit_pick_kernel<<<1, kRfDigits / 4, 0, c->stream>>>(c->rf_hist.as<unsigned int>(), shift, p == 0, K, st);
+        c->stats.launches += 2;
+    }
+    rf_tie_count_kernel<<<tile_grid, kRfThreads, 0, c->stream>>>(raw, nvalues, st, c->rf_tiles.as<unsigned int>());
+    rf_tie_scan_kernel<<<1, 1024, 0, c->stream>>>(c->rf_tiles.as<unsigned int>(), n_tiles);
+    rf_collect_kernel<<<tile_grid, kRfThreads, 0, c->stream>>>(raw, nvalues, st, c->rf_tiles.as<unsigned int>(), K,
+        c->rf_cand_count.as<unsigned long long>(), c->rf_cand_value.as<uint32_t>());
+    rf_rank_kernel<<<(K + kRfThreads - 1) / kRfThreads, kRfThreads, 0, c->stream>>>(st, K, c->rf_cand_count.as<unsigned long long>(),
+        c->rf_cand_value.as<uint32_t>(), c->rf_most.as<uint32_t>());
+    rf_mapping_fill_kernel<<<grid, kRfThreads, 0, c->stream>>>(st, K, nvalues, c->mapping.as<uint32_t>());
+    rf_mapping_hot_kernel<<<(K + kRfThreads - 1) / kRfThreads, kRfThreads, 0, c->stream>>>(st, K, c->rf_most.as<uint32_t>(), c->mapping.as<uint32_t>());
+    if (nfolded * 8 <= 48 * 1024)
+        rf_fold_bins_kernel<true><<<grid, kRfThreads, nfolded * 8, c->stream>>>(raw, nvalues, c->mapping.as<uint32_t>(), f, uint32_t(nfolded),
+            reinterpret_cast<unsigned long long*>(d_folded));
+    else
+        rf_fold_bins_kernel<false><<<grid, kRfThreads, 0, c->stream>>>(raw, nvalues, c->mapping.as<uint32_t>(), f, uint32_t(nfolded),
+            reinterpret_cast<unsigned long long*>(d_folded));
+    c->stats.launches += 7;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
+} // namespace
+
+// Device counterpart of b200ans_rfold_prepare (K4 of SURVEY.md section 8a; ans_reorder_fold.hpp:75-115): from the raw
+// histogram of the value range ON THE DEVICE to the value reordering (mapping[] stays on the device, most_frequent[]
+// comes back for the prelude) and the folded histogram over the reordered values, which is written to d_folded_bins
+// (2^(f+9) x u64, device) -- no second pass over the input.  One stream synchronisation, at the end.
+extern "C" int b200ans_rfold_prepare_device(b200ans_ctx* c, uint32_t f, const uint64_t* d_raw_bins, size_t nvalues, uint64_t* d_folded_bins)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_raw_bins || !d_folded_bins || nvalues == 0 || f < 1 || f > 8 || nvalues > (size_t(1) << 30))
+        return c->fail(B200ANS_E_ARG, "rfold_prepare_device: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    c->have_mapping = false;
+    const uint32_t K = 1u << (f + 7);
+    RET(rfold_select_launch(c, f, d_raw_bins, uint32_t(nvalues), 64, d_folded_bins));
+    RfState st;
+    std::vector<uint32_t> most(K);
+    CU(c, cudaMemcpyAsync(&st, c->rf_state.p, sizeof st, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaMemcpyAsync(most.data(), c->rf_most.p, size_t(K) * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->rfold_sigma = st.sigma;
+    c->most_frequent.clear();
+    if (st.reorder) {
+        c->most_frequent = std::move(most);
+    } else {
+        // identity mapping (ans_reorder_fold.hpp:94-97); the reference's decoder still subtracts 2^(f+7) (:301), so the
+        // input only round-trips when every value is below the threshold (b200ans_rfold_prepare has the details)
+        if (st.sigma != 0 && st.max_seen >= K)
+            return c->fail(B200ANS_E_DOMAIN,
+                "ANSrfold: fewer than 2^(f+7) distinct values and a value >= 2^(f+7): the reference's decoder returns wrong values for this input");
+    }
     c->n_values = uint32_t(nvalues);
     c->map_f = f;
     c->have_mapping = true;
@@ -888,6 +1051,37 @@ try {
     CU(c, c->enc_table.reserve(table.size() * sizeof(EncEntry)));
     // pageable source: cudaMemcpyAsync returns once the buffer is staged, so `table` may go out of scope
     CU(c, cudaMemcpyAsync(c->enc_table.p, table.data(), table.size() * sizeof(EncEntry), cudaMemcpyHostToDevice, c->stream));
+    // ANSrfold, L3 encoder: hash of the hot values + a copy of the table whose first K entries sit at the hash slots
+    c->rf_hash_ok = false;
+    if (method == METHOD_RFOLD && !c->most_frequent.empty() && f <= 3 && table.size() >= c->most_frequent.size()) {
+        const uint32_t K = uint32_t(c->most_frequent.size());
+        const uint32_t bshift = 32u - (f + 6u); // K / 2 buckets
+        std::vector<uint32_t> tags, slot_of_rank;
+        std::vector<uint16_t> disp;
+        uint32_t mul = 0x9E3779B1u;
+        bool ok = false;
+        for (int attempt = 0; attempt < 16 && !ok; attempt++, mul = mul * 0x01000193u + 0x7F4A7C15u) {
+            mul |= 1u;
+            ok = rfold_build_hash(c->most_frequent, mul, bshift, tags, disp, slot_of_rank);
+            if (ok)
+                break;
+        }
+        if (ok) {
+            std::vector<EncEntry> table_rf(table);
+            for (uint32_t r = 0; r < K; r++)
+                table_rf[slot_of_rank[r]] = table[r];
+            CU(c, c->enc_table_rf.reserve(table_rf.size() * sizeof(EncEntry)));
+            CU(c, c->rf_tags.reserve(tags.size() * 4));
+            CU(c, c->rf_disp.reserve(disp.size() * 2));
+            CU(c, cudaMemcpyAsync(c->enc_table_rf.p, table_rf.data(), table_rf.size() * sizeof(EncEntry), cudaMemcpyHostToDevice, c->stream));
+            CU(c, cudaMemcpyAsync(c->rf_tags.p, tags.data(), tags.size() * 4, cudaMemcpyHostToDevice, c->stream));
+            CU(c, cudaMemcpyAsync(c->rf_disp.p, disp.data(), disp.size() * 2, cudaMemcpyHostToDevice, c->stream));
+            CU(c, cudaStreamSynchronize(c->stream)); // the sources are locals
+            c->rf_mul = mul;
+            c->rf_bshift = bshift;
+            c->rf_hash_ok = true;
+        }
+    }
     c->enc_method = method;
     c->enc_f = f;
     c->have_enc = true;
@@ -1271,7 +1465,11 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
     tensor_map_encode_fn encode = tensor_map_encoder();
     if (!encode)
         return 1;
+    if (METHOD == METHOD_RFOLD && !c->rf_hash_ok)
+        return 1;
     const uint32_t alphabet = METHOD == METHOD_INT ? a.n_entries + 1u : uint32_t(alphabet_bins(METHOD, a.fidelity, 0));
+    // RFOLD: tags + displacements of the hot values' hash sit between the table and the tiles
+    const size_t aux_bytes = METHOD == METHOD_RFOLD ? align_up((size_t(4) << (a.fidelity + 7)) + (size_t(2) << (a.fidelity + 6)), 1024) : 0;
     const uint32_t alloc = METHOD == METHOD_INT ? a.n_entries + 1u : a.n_entries;
     const uint32_t n_tasks = (a.n_blocks + 31) / 32;
     const uint32_t sms = uint32_t(c->num_sms);
@@ -1283,9 +1481,9 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
     for (int r = rep_hi; r >= 0; r--) {
         const size_t table_bytes = align_up((size_t(alloc) << r) * 16, 1024);
         // every address the mapping can produce must stay inside the CTA's shared-memory window
-        if ((size_t(alphabet) << r) * 16 + 64 > c->max_smem || table_bytes + 2048 > c->max_smem)
+        if ((size_t(alphabet) << r) * 16 + 64 > c->max_smem || table_bytes + aux_bytes + 2048 > c->max_smem)
             continue;
-        const uint32_t fit = uint32_t(std::min<size_t>(CFG::MAXW, (c->max_smem - table_bytes - 1024) / L3Geom<CFG>::kWarpBytes));
+        const uint32_t fit = uint32_t(std::min<size_t>(CFG::MAXW, (c->max_smem - table_bytes - aux_bytes - 1024) / L3Geom<CFG>::kWarpBytes));
         if (fit >= std::min<uint32_t>(want_warps, uint32_t(CFG::MAXW)) || r == 0) {
             rep = r;
             max_warps = fit;
@@ -1305,6 +1503,14 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
     g.n_full_blocks = uint32_t(a.n / a.block_syms);
     // folded coders: the largest value the model covers, and never 2^30 or more (ans_fold.hpp:198-200)
     g.max_value = METHOD == METHOD_INT ? 0xFFFFFFFFu : std::min(max_value_below(METHOD, a.fidelity, a.n_entries), (1u << 30) - 1u);
+    EncArgs a2 = a;
+    if (METHOD == METHOD_RFOLD) {
+        g.rf_tags = c->rf_tags.as<uint32_t>();
+        g.rf_disp = c->rf_disp.as<uint16_t>();
+        g.rf_mul = c->rf_mul;
+        g.rf_bshift = c->rf_bshift;
+        a2.table = c->enc_table_rf.as<EncEntry>();
+    }
 
     CUtensorMap tmap;
     const cuuint64_t dims[2] = { a.block_syms, g.n_full_blocks };
@@ -1327,9 +1533,9 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
     const bool f1 = METHOD == METHOD_FOLD && a.fidelity == 1;
     CU(c, cudaFuncSetAttribute(f1 ? k1 : k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     if (f1)
-        k1<<<grid, warps * 32, smem, c->stream>>>(a, g, tmap);
+        k1<<<grid, warps * 32, smem, c->stream>>>(a2, g, tmap);
     else
-        k<<<grid, warps * 32, smem, c->stream>>>(a, g, tmap);
+        k<<<grid, warps * 32, smem, c->stream>>>(a2, g, tmap);
     set_name(c->stats.encode_kernel, "lpb3_encode_kernel");
     c->stats.launches++;
     CU(c, cudaGetLastError());
@@ -1368,6 +1574,7 @@ int launch_encode(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t bloc
         case METHOD_INT: rc3 = launch_lpb3_encode_t<METHOD_INT>(c, a); break;
         case METHOD_FOLD: rc3 = launch_lpb3_encode_t<METHOD_FOLD>(c, a); break;
         case METHOD_MSB: rc3 = launch_lpb3_encode_t<METHOD_MSB>(c, a); break;
+        case METHOD_RFOLD: rc3 = launch_lpb3_encode_t<METHOD_RFOLD>(c, a); break;
         default: break;
         }
         if (rc3 <= 0)
@@ -1948,17 +2155,64 @@ int compress_device_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst,
         else
             bins.resize(size_t(max_value) + 1);
     } else if (method == METHOD_RFOLD) {
-        if (n)
-            RET(b200ans_max_device(c, d_src, n, c->d_max()));
-        if (sharded)
-            RET(allreduce_hist(c, nullptr, 0, c->d_max()));
-        CU(c, cudaMemcpyAsync(&max_value, c->d_max(), 4, cudaMemcpyDeviceToHost, c->stream));
-        CU(c, cudaStreamSynchronize(c->stream));
-        if (uint64_t(max_value) + (1u << (f + 7)) >= (1u << 30))
+        // K4 on the device: ONE optimistic pass counts the raw values into `guess` bins while it keeps the running
+        // maximum (a second pass only when a value lies beyond the guess); selection of the 2^(f+7) most frequent
+        // values, mapping[] and the folded histogram follow on the device from the raw bins (rfold_kernels.cuh).
+        const uint32_t K = 1u << (f + 7);
+        size_t guess = std::max<size_t>(c->rf_guess, std::min<size_t>(size_t(1) << 24, std::max<size_t>(65536, size_t(next_power_of_two(uint64_t(n) * 4)))));
+        for (int attempt = 0;; attempt++) {
+            CU(c, c->rf_raw.reserve(guess * 8));
+            CU(c, cudaMemsetAsync(c->d_max(), 0, 4, c->stream));
+            if (n && uint64_t(n) < (uint64_t(1) << 32) && guess > kHistSmemWords) {
+                // 32-bit counters for the pass (they stay in L2), widened afterwards
+                CU(c, c->rf_raw32.reserve(guess * 4));
+                CU(c, cudaMemsetAsync(c->rf_raw32.p, 0, guess * 4, c->stream));
+                RET(launch_histogram<METHOD_INT>(c, f, d_src, n, nullptr, guess, c->d_max(), c->rf_raw32.as<unsigned int>()));
+                widen_bins_kernel<<<c->num_sms * 8, 256, 0, c->stream>>>(c->rf_raw32.as<unsigned int>(), c->rf_raw.as<unsigned long long>(), uint32_t(guess));
+                c->stats.launches++;
+            } else {
+                CU(c, cudaMemsetAsync(c->rf_raw.p, 0, guess * 8, c->stream));
+                if (n)
+                    RET(histogram_dispatch(c, METHOD_INT, f, d_src, n, c->rf_raw.as<uint64_t>(), guess, c->d_max()));
+            }
+            if (sharded) {
+                CU(c, cudaEventRecord(c->ev_ar[0], c->stream));
+                RET(allreduce_hist(c, c->rf_raw.as<uint64_t>(), guess, c->d_max()));
+                CU(c, cudaEventRecord(c->ev_ar[1], c->stream));
+            }
+            RET(read_small(c));
+            if (sharded)
+                c->stats.ms_allreduce += elapsed(c->ev_ar[0], c->ev_ar[1]);
+            max_value = c->h_small()->max_value;
+            if (max_value < guess || attempt == 1)
+                break;
+            guess = align_up(size_t(max_value) + 1, 4096);
+        }
+        c->rf_guess = guess;
+        if (uint64_t(max_value) + K >= (1u << 30))
             return c->fail(B200ANS_E_DOMAIN, "ANSrfold needs value + 2^(f+7) < 2^30");
-        RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins, nullptr, sharded));
-        RET(b200ans_rfold_prepare(c, f, bins.data(), bins.size()));
-        RET(histogram_to_host(c, METHOD_RFOLD, f, d_src, n, alphabet_bins(method, f, 0), bins, nullptr, sharded));
+        const size_t nfolded = alphabet_bins(method, f, 0);
+        CU(c, c->bins.reserve(nfolded * 8));
+        const uint32_t count_bits = sharded ? 64u : uint32_t(64 - __builtin_clzll(uint64_t(n) | 1));
+        c->have_mapping = false;
+        RET(rfold_select_launch(c, f, c->rf_raw.as<uint64_t>(), max_value + 1, count_bits, c->bins.as<uint64_t>()));
+        RfState st;
+        c->most_frequent.resize(K);
+        bins.resize(nfolded);
+        CU(c, cudaMemcpyAsync(&st, c->rf_state.p, sizeof st, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaMemcpyAsync(c->most_frequent.data(), c->rf_most.p, size_t(K) * 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaMemcpyAsync(bins.data(), c->bins.p, nfolded * 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        c->rfold_sigma = st.sigma;
+        if (!st.reorder) {
+            c->most_frequent.clear();
+            if (st.sigma != 0 && max_value >= K)
+                return c->fail(B200ANS_E_DOMAIN,
+                    "ANSrfold: fewer than 2^(f+7) distinct values and a value >= 2^(f+7): the reference's decoder returns wrong values for this input");
+        }
+        c->n_values = max_value + 1;
+        c->map_f = f;
+        c->have_mapping = true;
     } else {
         RET(histogram_to_host(c, method, f, d_src, n, alphabet_bins(method, f, 0), bins, &max_value, sharded));
         if (max_value >= (1u << 30)) // the decoder keeps the byte count in bits 30-31 (ans_fold.hpp:198-200)

@@ -327,6 +327,7 @@ struct HistArgs {
     uint32_t replicas;  // power of two
     uint32_t stride;    // words between replicas (odd multiple: +1 bank per replica)
     uint32_t* max_value;
+    unsigned int* bins32; // BINS32: 32-bit global bins (raw alphabets of inputs below 2^32 symbols: half the L2 footprint)
 };
 
 __device__ __forceinline__ void red_shared_inc(uint32_t addr)
@@ -337,7 +338,10 @@ __device__ __forceinline__ void red_shared_inc(uint32_t addr)
 // ALL_SMEM: every bin has a shared-memory counter (all folded alphabets up to fidelity 4, small raw alphabets).
 // Then counting is branch-free: bin address straight from the bit position of the value (as in lpb3_kernels.cuh
 // l3_entry_addr), one `red.shared` on a 32-bit shared address.
-template <int METHOD, bool ALL_SMEM>
+// BINS32 (raw alphabets beyond the shared-memory head, ANSrfold's pre-pass): the counters that take the global atomics
+// are 32 bits wide -- 64 MB instead of 128 MB for config 3's 2^24 values, so they stay in the 126 MB L2 while the
+// input streams past them (loads marked evict-first); with 64-bit bins every cold count is a DRAM read-modify-write.
+template <int METHOD, bool ALL_SMEM, bool BINS32 = false>
 __global__ void __launch_bounds__(kHistThreads) histogram_kernel(const HistArgs a)
 {
     extern __shared__ uint32_t s_bins[];
@@ -375,8 +379,12 @@ __global__ void __launch_bounds__(kHistThreads) histogram_kernel(const HistArgs 
             const uint32_t bin = map_value<METHOD>(mv, f, k);
             if (bin < smem_bins)
                 atomicAdd(mine + bin, 1u);
-            else if (bin < nbins)
-                atomicAdd(a.bins + bin, 1ull);
+            else if (bin < nbins) {
+                if (BINS32)
+                    atomicAdd(a.bins32 + bin, 1u);
+                else
+                    atomicAdd(a.bins + bin, 1ull);
+            }
         }
         local_max = max(local_max, v);
     };
@@ -387,8 +395,8 @@ __global__ void __launch_bounds__(kHistThreads) histogram_kernel(const HistArgs 
     const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
     uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     for (; i + stride < n4; i += 2 * stride) {
-        const uint4 q0 = __ldg(in4 + i);
-        const uint4 q1 = __ldg(in4 + i + stride);
+        const uint4 q0 = BINS32 ? __ldcs(in4 + i) : __ldg(in4 + i);
+        const uint4 q1 = BINS32 ? __ldcs(in4 + i + stride) : __ldg(in4 + i + stride);
         count(q0.x), count(q0.y), count(q0.z), count(q0.w);
         count(q1.x), count(q1.y), count(q1.z), count(q1.w);
     }
@@ -411,9 +419,20 @@ __global__ void __launch_bounds__(kHistThreads) histogram_kernel(const HistArgs 
         uint32_t c = 0;
         for (uint32_t r = 0; r < a.replicas; r++)
             c += s_bins[r * a.stride + b];
-        if (c)
-            atomicAdd(a.bins + b, (unsigned long long)c);
+        if (c) {
+            if (BINS32)
+                atomicAdd(a.bins32 + b, c);
+            else
+                atomicAdd(a.bins + b, (unsigned long long)c);
+        }
     }
+}
+
+// 32-bit counters -> 64-bit bins (added: the caller zeroes)
+__global__ void __launch_bounds__(256) widen_bins_kernel(const unsigned int* __restrict__ in, unsigned long long* __restrict__ out, uint32_t n)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        out[i] = in[i];
 }
 
 // ------------------------------------------------------------------------------------------

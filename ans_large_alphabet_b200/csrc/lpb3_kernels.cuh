@@ -54,7 +54,19 @@ struct Enc3Args {
     uint32_t rep_log2;      // log2 of the number of table replicas (0..3)
     uint32_t table_alloc;   // entries per replica: covers every symbol the mapping can produce
     uint32_t n_full_blocks; // rows of the tensor map (blocks that hold block_syms symbols)
-    uint32_t max_value;     // FOLD / MSB: largest input value whose symbol is < n_entries
+    uint32_t max_value;     // FOLD / MSB: largest input value whose symbol is < n_entries (RFOLD: largest reordered value)
+    // RFOLD: perfect hash of the K = 2^(f+7) most frequent values (built by the host, b200ans.cu rfold_build_hash):
+    // slot(v) = (v * mul + disp[(v * mul) >> bshift]) & (K - 1); v is one of them iff tags[slot] == v, and the table
+    // entry of its id then sits AT the slot (the first K table entries are permuted accordingly)
+    const uint32_t* rf_tags; // K values (0xFFFFFFFF = empty)
+    const uint16_t* rf_disp; // 2^(32 - bshift) displacements
+    uint32_t rf_mul;
+    uint32_t rf_bshift;
+};
+
+// RFOLD: where the hash lives in shared memory
+struct L3Rfold {
+    uint32_t s_tags, s_disp, mul, bshift, kmask, K;
 };
 
 // ---- mbarrier / TMA (PTX ISA 8.x, sm_90+) ---------------------------------------------------
@@ -161,10 +173,25 @@ struct L3Packer {
 };
 
 // value -> shared-memory address of its table entry (replica chosen by `lane_tb`) and 8 * (raw low bytes)
+// RFOLD (ans_reorder_fold.hpp:156-168: encode_symbol folds mapping[v]): `v` comes back as the reordered value the raw
+// bytes are taken from -- 0 for one of the K most frequent values (no raw bytes, entry at its hash slot), v + K otherwise.
 template <int METHOD, int FID>
-__device__ __forceinline__ uint32_t l3_entry_addr(uint32_t v, uint32_t lane_tb, uint32_t ent_stride, uint32_t k8_stride, uint32_t f,
-    uint32_t n_entries, uint32_t& k8)
+__device__ __forceinline__ uint32_t l3_entry_addr(uint32_t& v, uint32_t lane_tb, uint32_t ent_stride, uint32_t k8_stride, uint32_t f,
+    uint32_t n_entries, uint32_t& k8, const L3Rfold& rf)
 {
+    if (METHOD == METHOD_RFOLD) {
+        const uint32_t h = v * rf.mul;
+        uint32_t d, t;
+        asm volatile("ld.shared.u16 %0, [%1];" : "=r"(d) : "r"(rf.s_disp + ((h >> rf.bshift) << 1)));
+        const uint32_t s = (h + d) & rf.kmask;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t) : "r"(rf.s_tags + (s << 2)));
+        const bool hot = t == v;
+        v = hot ? 0u : v + rf.K;
+        const uint32_t fl = bfind_u32(v | (1u << (f - 1u))) - (f - 1u);
+        k8 = fl & 0x18u;
+        const uint32_t idx = hot ? s : (v >> k8);
+        return mad_lo(idx, ent_stride, mad_lo(k8, k8_stride, lane_tb));
+    }
     if (METHOD == METHOD_INT) {
         k8 = 0;
         return mad_lo(min(v, n_entries), ent_stride, lane_tb); // entry n_entries is the "no such symbol" sentinel
@@ -199,7 +226,23 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
     const uint32_t s_base = smem_u32(smem_raw);
     const uint32_t s_table = s_base;
     const uint32_t table_bytes = (g.table_alloc << g.rep_log2) * 16u;
-    const uint32_t s_tiles = s_base + ((table_bytes + 1023u) & ~1023u);
+    // RFOLD: [tags: K x u32][displacements: u16] between the table and the tiles
+    L3Rfold rf {};
+    uint32_t aux_bytes = 0;
+    if (METHOD == METHOD_RFOLD) {
+        rf.K = 1u << (a.fidelity + 7u);
+        rf.kmask = rf.K - 1u;
+        rf.mul = g.rf_mul;
+        rf.bshift = g.rf_bshift;
+        rf.s_tags = s_base + ((table_bytes + 1023u) & ~1023u);
+        rf.s_disp = rf.s_tags + rf.K * 4u;
+        aux_bytes = (rf.K * 4u + ((1u << (32u - g.rf_bshift)) << 1) + 1023u) & ~1023u;
+        for (uint32_t i = threadIdx.x; i < rf.K; i += blockDim.x)
+            sts32(rf.s_tags + i * 4u, __ldg(g.rf_tags + i));
+        for (uint32_t i = threadIdx.x; i < (1u << (32u - g.rf_bshift)); i += blockDim.x)
+            asm volatile("st.shared.u16 [%0], %1;" ::"r"(rf.s_disp + i * 2u), "h"(__ldg(g.rf_disp + i)) : "memory");
+    }
+    const uint32_t s_tiles = s_base + ((table_bytes + 1023u) & ~1023u) + aux_bytes;
     const uint32_t s_rows = s_tiles + warps_per_cta * uint32_t(STAGES * kTileBytes);
     const uint32_t s_bars = s_rows + warps_per_cta * 32u * kOutRow;
 
@@ -307,11 +350,11 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
             uint32_t k8[4], nfr[4], base[4], fr16[4];
             double rcp[4];
             bool rn[4];
-            if (METHOD != METHOD_INT)
+            if (METHOD != METHOD_INT && METHOD != METHOD_RFOLD)
                 vmax = max(vmax, max(max(v[0], v[1]), max(v[2], v[3])));
 #pragma unroll
             for (int c = 0; c < 4; c++) {
-                const uint32_t addr = l3_entry_addr<METHOD, FID>(v[c], lane_tb, ent_stride, k8_stride, f, a.n_entries, k8[c]);
+                const uint32_t addr = l3_entry_addr<METHOD, FID>(v[c], lane_tb, ent_stride, k8_stride, f, a.n_entries, k8[c], rf);
                 const uint4 e = lds128(addr);
                 nfr[c] = e.x;
                 base[c] = e.y;
@@ -320,6 +363,8 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                     badf = fmaf(__uint_as_float(e.w), 0.f, badf); // NaN (no such symbol) sticks
                 fr16[c] = nfr[c] * 0xFFFFFFF0u;               // freq * 16
             }
+            if (METHOD == METHOD_RFOLD) // the reordered values (0 for the K most frequent ones)
+                vmax = max(vmax, max(max(v[0], v[1]), max(v[2], v[3])));
 #pragma unroll
             for (int c = 0; c < 4; c++) // state >= freq * K * 2^32 (ans_fold.hpp:105)
                 rn[c] = active && (xhi[c] >= fr16[c]);
@@ -399,10 +444,10 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
             if (__any_sync(0xffffffffu, tail != 0u)) { // tail symbols on state 0 (ans_fold.hpp:257-261)
                 for (uint32_t s = 0; s < 3u; s++) {
                     const bool active = s < tail;
-                    const uint32_t v = active ? __ldg(a.in + first + (nb - 1u - s)) : 0u;
+                    uint32_t v = active ? __ldg(a.in + first + (nb - 1u - s)) : 0u;
                     // run the symbol as a "quad" whose other three members are inactive: rotate it into slot 0
                     uint32_t k8;
-                    const uint32_t addr = l3_entry_addr<METHOD, FID>(v, lane_tb, ent_stride, k8_stride, f, a.n_entries, k8);
+                    const uint32_t addr = l3_entry_addr<METHOD, FID>(v, lane_tb, ent_stride, k8_stride, f, a.n_entries, k8, rf);
                     const uint4 e = lds128(addr);
                     if (active) {
                         badf = fmaf(__uint_as_float(e.w), 0.f, badf);
@@ -549,9 +594,13 @@ struct L3Reader {
     }
 };
 
+// (Measured in round 2 and dropped: refilling the rings in 64-byte chunks by groups of four lanes, so that one LDGSTS
+// touches 8 lines instead of 32 and brings whole sectors -- byte-exact, 1.955 -> 1.947 ms for ANSfold-1 at 2^30 symbols,
+// 2.32 -> 2.47 ms on the rank/select tables: the copies are not what the LSU pipe spends its wavefronts on.)
 template <int METHOD, int TABLE, int QI, int MAXW>
 __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs a)
 {
+    constexpr uint32_t ALIGN = 16u; // payload view and refill granularity
     constexpr int RING = L3DecGeom<QI>::kRing;
     constexpr int DIST = L3DecGeom<QI>::kDist;
     constexpr bool kInt = (METHOD == METHOD_INT);
@@ -587,9 +636,9 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
         const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
         const bool uniform = __all_sync(0xffffffffu, have_block && quads == max_quads);
 
-        // 16-byte aligned view of the payload; positions count bytes from pay16
+        // ALIGN-byte aligned view of the payload; positions count bytes from pay16
         const uint8_t* pay = a.payload + (have_block ? a.offsets[blk] : 0);
-        const uint32_t delta = uint32_t(reinterpret_cast<uintptr_t>(pay) & 15u);
+        const uint32_t delta = uint32_t(reinterpret_cast<uintptr_t>(pay) & (ALIGN - 1u));
         const uint8_t* pay16 = pay - delta;
         const uint32_t size = have_block ? a.block_bytes[blk] : 32u;
         const int32_t p0 = int32_t(delta + size - 32u); // one past the last payload byte below the four states
@@ -621,9 +670,9 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
         }
 
         // ring: chunks [fetched_lo, ...) are resident (or in flight); refill down to `DIST` bytes below the cursor
-        int32_t fetched_lo = (rd.rp + 4 + 15) & ~15;
+        int32_t fetched_lo = (rd.rp + 4 + int32_t(ALIGN) - 1) & ~int32_t(ALIGN - 1u);
         auto refill = [&]() {
-            const int32_t want = max(rd.rp + 4 - DIST, 0) & ~15;
+            const int32_t want = max(rd.rp + 4 - DIST, 0) & ~int32_t(ALIGN - 1u);
             while (__any_sync(0xffffffffu, have_block && fetched_lo > want)) {
                 if (have_block && fetched_lo > want) {
                     fetched_lo -= 16;

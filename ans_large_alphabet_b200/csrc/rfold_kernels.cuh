@@ -1,0 +1,336 @@
+// b200ans device code (sm_100a): the ANSrfold model on the device ("K4" of SURVEY.md section 8a).
+//
+// ans_reorder_fold_encode::create (ans_reorder_fold.hpp:75-106) sorts (-count, value) over the whole value range,
+// gives the first K = 2^(f+7) values the ids 0..K-1 and moves everything else up by K; the folded histogram is then
+// counted over mapping[in[i]] (:110-115).  Here, from the raw device histogram `raw[v]`:
+//
+//   1. rf_digit_hist / rf_digit_pick : radix select (12 bits per pass, most significant digit first) of the K-th
+//      largest count T; n_gt = values with count > T, need_eq = K - n_gt; sigma = distinct values.
+//   2. rf_tie_count / rf_tie_scan / rf_collect : the candidates are every value with count > T and the need_eq
+//      SMALLEST values with count == T (the reference's tie-break: pairs compare by value after the count) -- an
+//      ordered selection: per-tile counts of ties, their exclusive scan, then every tile emits its share.
+//   3. rf_rank : id of a candidate = number of candidates that sort before it (K^2 compares, K <= 32768).
+//   4. rf_mapping_fill / rf_mapping_hot : mapping[v] = v + K, mapping[most_frequent[r]] = r (identity when
+//      sigma < K, ans_reorder_fold.hpp:94-97).
+//   5. rf_fold_bins : the folded histogram follows from the raw one -- freqs[fold(mapping[v])] += raw[v] -- a pass
+//      over the value range (16 M bins for C3) instead of a second pass over the input (1e9 symbols).
+//
+// Nothing comes back to the host before step 5; the host then reads the folded bins, most_frequent[] and sigma in
+// one synchronisation and builds the model (normalisation and prelude stay on the host, as the north star says).
+#pragma once
+
+#include "kernels.cuh"
+
+namespace b200ans {
+
+// device-side state of one selection (all counters zeroed by the host before step 1)
+struct RfState {
+    unsigned long long prefix;   // bits of T fixed so far (above the current digit)
+    unsigned long long k_left;   // how many of the values matching the prefix are still wanted
+    unsigned long long sigma;    // distinct values
+    unsigned long long n_gt;     // values with count > T  (after the last pick)
+    unsigned long long need_eq;  // values with count == T to take, smallest first
+    unsigned int n_emitted;      // candidates with count > T written so far (rf_collect)
+    unsigned int reorder;        // 1: sigma >= K, the mapping reorders; 0: identity mapping
+    unsigned int max_seen;       // largest value with a non-zero count
+    unsigned int pad;
+};
+
+constexpr int kRfThreads = 256;
+constexpr uint32_t kRfTile = 4096; // values per tile of the ordered selection
+
+constexpr uint32_t kRfDigitBits = 12;
+constexpr uint32_t kRfDigits = 1u << kRfDigitBits;
+
+// digit histogram of the counts whose bits above `shift + kRfDigitBits` equal the prefix (privatised per CTA: most
+// counts of a skewed input share their upper digits); the first pass also counts sigma and the largest value seen
+__global__ void __launch_bounds__(kRfThreads) rf_digit_hist_kernel(const unsigned long long* __restrict__ raw, uint32_t nvalues,
+    uint32_t shift, bool first, const RfState* __restrict__ st, unsigned int* __restrict__ hist /* kRfDigits, zeroed */,
+    RfState* __restrict__ st_out)
+{
+    __shared__ unsigned int s_hist[kRfDigits];
+    for (uint32_t i = threadIdx.x; i < kRfDigits; i += blockDim.x)
+        s_hist[i] = 0u;
+    __syncthreads();
+    const unsigned long long prefix = first ? 0ull : st->prefix;
+    const uint32_t hi_shift = shift + kRfDigitBits;
+    unsigned int nz = 0, top = 0;
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nvalues; v += gridDim.x * blockDim.x) {
+        const unsigned long long c = raw[v];
+        nz += c != 0ull;
+        if (c != 0ull)
+            top = v; // v only grows
+        if (hi_shift >= 64u || (c >> hi_shift) == (prefix >> hi_shift))
+            atomicAdd(s_hist + uint32_t((c >> shift) & (kRfDigits - 1u)), 1u);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < kRfDigits; i += blockDim.x)
+        if (s_hist[i])
+            atomicAdd(hist + i, s_hist[i]);
+    if (first) {
+        for (int o = 16; o > 0; o >>= 1) {
+            nz += __shfl_xor_sync(0xffffffffu, nz, o);
+            top = max(top, __shfl_xor_sync(0xffffffffu, top, o));
+        }
+        if ((threadIdx.x & 31) == 0 && nz) {
+            atomicAdd(&st_out->sigma, (unsigned long long)nz);
+            atomicMax(&st_out->max_seen, top);
+        }
+    }
+}
+
+// one CTA of kRfDigits / 4 threads: find the digit at which the counts, walked from the top, cover k_left values; fix it
+__global__ void __launch_bounds__(kRfDigits / 4) rf_digit_pick_kernel(unsigned int* __restrict__ hist, uint32_t shift, bool first, uint32_t K,
+    RfState* __restrict__ st)
+{
+    constexpr uint32_t kT = kRfDigits / 4;
+    __shared__ unsigned long long s_warp[kT / 32];
+    __shared__ unsigned long long s_above;
+    __shared__ unsigned int s_digit, s_found;
+    const uint32_t t = threadIdx.x;
+    if (t == 0)
+        s_found = 0u;
+    const unsigned long long k_left = first ? (unsigned long long)K : st->k_left;
+    // thread 0 owns the four highest digits, thread kT - 1 the four lowest: a prefix sum over t = "values above"
+    const uint32_t base = 4u * (kT - 1u - t);
+    const uint4 h = *reinterpret_cast<const uint4*>(hist + base);
+    const unsigned long long own = (unsigned long long)h.x + h.y + h.z + h.w;
+    unsigned long long incl = own;
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long up = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((t & 31u) >= uint32_t(o))
+            incl += up;
+    }
+    if ((t & 31u) == 31u)
+        s_warp[t >> 5] = incl;
+    __syncthreads();
+    unsigned long long above = 0;
+    for (uint32_t w = 0; w < (t >> 5); w++)
+        above += s_warp[w];
+    above += incl - own;
+    if (above < k_left && k_left <= above + own) { // exactly one thread, when k_left values exist at all
+        const unsigned int hh[4] = { h.w, h.z, h.y, h.x };
+        unsigned int d = base + 3u;
+        for (int j = 0; j < 4; j++, d--) {
+            if (above + hh[j] >= k_left)
+                break;
+            above += hh[j];
+        }
+        s_digit = d;
+        s_above = above;
+        s_found = 1u;
+    }
+    __syncthreads();
+    if (t == 0) {
+        // (not found: fewer than k_left values in all -- sigma < K, nothing of this is used)
+        const unsigned int d = s_found ? s_digit : 0u;
+        const unsigned long long ab = s_found ? s_above : 0ull;
+        st->prefix = (first ? 0ull : st->prefix) | ((unsigned long long)d << shift);
+        st->k_left = k_left - ab;
+        if (shift == 0u) {
+            // T = prefix; k_left - ab values with count == T are still wanted
+            st->need_eq = k_left - ab;
+            st->n_gt = (unsigned long long)K - (k_left - ab);
+            st->reorder = (st->sigma >= (unsigned long long)K) ? 1u : 0u;
+        }
+    }
+    __syncthreads();
+    *reinterpret_cast<uint4*>(hist + base) = make_uint4(0u, 0u, 0u, 0u); // ready for the next pass
+}
+
+// per tile of kRfTile values: how many have count == T
+__global__ void __launch_bounds__(kRfThreads) rf_tie_count_kernel(const unsigned long long* __restrict__ raw, uint32_t nvalues,
+    const RfState* __restrict__ st, unsigned int* __restrict__ tile_ties)
+{
+    __shared__ unsigned int s_cnt;
+    const unsigned long long T = st->prefix;
+    for (uint32_t tile = blockIdx.x; tile * uint64_t(kRfTile) < nvalues; tile += gridDim.x) {
+        if (threadIdx.x == 0)
+            s_cnt = 0;
+        __syncthreads();
+        unsigned int c = 0;
+        for (uint32_t j = threadIdx.x; j < kRfTile; j += kRfThreads) {
+            const uint64_t v = uint64_t(tile) * kRfTile + j;
+            if (v < nvalues && raw[v] == T)
+                c++;
+        }
+        for (int o = 16; o > 0; o >>= 1)
+            c += __shfl_xor_sync(0xffffffffu, c, o);
+        if ((threadIdx.x & 31) == 0 && c)
+            atomicAdd(&s_cnt, c);
+        __syncthreads();
+        if (threadIdx.x == 0)
+            tile_ties[tile] = s_cnt;
+        __syncthreads();
+    }
+}
+
+// one CTA: exclusive scan of the per-tile tie counts, in place (64-bit running sum, clamped to 2^32 - 1: only
+// ranks below need_eq <= 32768 matter)
+__global__ void __launch_bounds__(1024) rf_tie_scan_kernel(unsigned int* __restrict__ tile_ties, uint32_t n_tiles)
+{
+    __shared__ unsigned long long s_warp[32];
+    __shared__ unsigned long long s_carry;
+    if (threadIdx.x == 0)
+        s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_tiles; base += 1024u) {
+        const uint32_t i = base + threadIdx.x;
+        const unsigned long long mine = i < n_tiles ? tile_ties[i] : 0u;
+        unsigned long long incl = mine;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long up = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((threadIdx.x & 31) >= o)
+                incl += up;
+        }
+        if ((threadIdx.x & 31) == 31)
+            s_warp[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        unsigned long long before = s_carry;
+        for (uint32_t w = 0; w < (threadIdx.x >> 5); w++)
+            before += s_warp[w];
+        const unsigned long long excl = before + incl - mine;
+        if (i < n_tiles)
+            tile_ties[i] = excl > 0xFFFFFFFFull ? 0xFFFFFFFFu : (unsigned int)excl;
+        __syncthreads();
+        if (threadIdx.x == 1023)
+            s_carry = before + incl;
+        __syncthreads();
+    }
+}
+
+// candidates: {count > T} (any order) and the first need_eq of {count == T} in value order
+__global__ void __launch_bounds__(kRfThreads) rf_collect_kernel(const unsigned long long* __restrict__ raw, uint32_t nvalues,
+    RfState* __restrict__ st, const unsigned int* __restrict__ tile_ties, uint32_t K, unsigned long long* __restrict__ cand_count,
+    uint32_t* __restrict__ cand_value)
+{
+    __shared__ unsigned int s_warp[kRfThreads / 32];
+    if (!st->reorder)
+        return;
+    const unsigned long long T = st->prefix;
+    const unsigned long long need_eq = st->need_eq;
+    const uint32_t n_gt = uint32_t(st->n_gt);
+    constexpr uint32_t kPer = kRfTile / kRfThreads; // consecutive values per thread: value order inside the tile
+    for (uint32_t tile = blockIdx.x; tile * uint64_t(kRfTile) < nvalues; tile += gridDim.x) {
+        const uint64_t v0 = uint64_t(tile) * kRfTile + threadIdx.x * kPer;
+        unsigned long long cnt[kPer];
+        unsigned int ties = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < kPer; j++) {
+            cnt[j] = v0 + j < nvalues ? raw[v0 + j] : 0ull;
+            ties += (v0 + j < nvalues && cnt[j] == T);
+        }
+        // exclusive scan of `ties` over the CTA's threads (thread order = value order)
+        unsigned int incl = ties;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int up = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((threadIdx.x & 31) >= o)
+                incl += up;
+        }
+        if ((threadIdx.x & 31) == 31)
+            s_warp[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        unsigned long long rank = tile_ties[tile];
+        for (uint32_t w = 0; w < (threadIdx.x >> 5); w++)
+            rank += s_warp[w];
+        rank += incl - ties;
+#pragma unroll
+        for (uint32_t j = 0; j < kPer; j++) {
+            if (v0 + j >= nvalues)
+                continue;
+            if (cnt[j] > T) {
+                const unsigned int at = atomicAdd(&st->n_emitted, 1u);
+                if (at < K) {
+                    cand_count[at] = cnt[j];
+                    cand_value[at] = uint32_t(v0 + j);
+                }
+            } else if (cnt[j] == T) {
+                if (rank < need_eq) {
+                    cand_count[n_gt + uint32_t(rank)] = T;
+                    cand_value[n_gt + uint32_t(rank)] = uint32_t(v0 + j);
+                }
+                rank++;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// id of candidate i = number of candidates hotter than it ((-count, value) order, ans_reorder_fold.hpp:86)
+__global__ void __launch_bounds__(kRfThreads) rf_rank_kernel(const RfState* __restrict__ st, uint32_t K,
+    const unsigned long long* __restrict__ cand_count, const uint32_t* __restrict__ cand_value, uint32_t* __restrict__ most_frequent)
+{
+    __shared__ unsigned long long s_c[kRfThreads];
+    __shared__ uint32_t s_v[kRfThreads];
+    if (!st->reorder)
+        return;
+    const uint32_t i = blockIdx.x * kRfThreads + threadIdx.x;
+    const unsigned long long ci = i < K ? cand_count[i] : 0ull;
+    const uint32_t vi = i < K ? cand_value[i] : 0u;
+    uint32_t rank = 0;
+    for (uint32_t base = 0; base < K; base += kRfThreads) {
+        const uint32_t j = base + threadIdx.x;
+        s_c[threadIdx.x] = j < K ? cand_count[j] : 0ull;
+        s_v[threadIdx.x] = j < K ? cand_value[j] : 0xFFFFFFFFu;
+        __syncthreads();
+        const uint32_t lim = min(uint32_t(kRfThreads), K - base);
+        for (uint32_t t = 0; t < lim; t++)
+            rank += (s_c[t] > ci) || (s_c[t] == ci && s_v[t] < vi);
+        __syncthreads();
+    }
+    if (i < K)
+        most_frequent[rank] = vi;
+}
+
+// mapping[v] = v + K (or v when the model keeps the identity mapping)
+__global__ void __launch_bounds__(kRfThreads) rf_mapping_fill_kernel(const RfState* __restrict__ st, uint32_t K, uint32_t nvalues,
+    uint32_t* __restrict__ mapping)
+{
+    const uint32_t bias = st->reorder ? K : 0u;
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nvalues; v += gridDim.x * blockDim.x)
+        mapping[v] = v + bias;
+}
+__global__ void __launch_bounds__(kRfThreads) rf_mapping_hot_kernel(const RfState* __restrict__ st, uint32_t K,
+    const uint32_t* __restrict__ most_frequent, uint32_t* __restrict__ mapping)
+{
+    if (!st->reorder)
+        return;
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < K)
+        mapping[most_frequent[r]] = r;
+}
+
+// folded histogram from the raw one: bins[fold(mapping[v])] += raw[v]  (ans_reorder_fold.hpp:110-115)
+// SMEM: the folded alphabet (2^(f+9) 64-bit counters) fits the CTA's shared memory.
+template <bool SMEM>
+__global__ void __launch_bounds__(kRfThreads) rf_fold_bins_kernel(const unsigned long long* __restrict__ raw, uint32_t nvalues,
+    const uint32_t* __restrict__ mapping, uint32_t f, uint32_t nbins, unsigned long long* __restrict__ bins)
+{
+    extern __shared__ unsigned long long s_fold[];
+    if (SMEM) {
+        for (uint32_t i = threadIdx.x; i < nbins; i += blockDim.x)
+            s_fold[i] = 0ull;
+        __syncthreads();
+    }
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nvalues; v += gridDim.x * blockDim.x) {
+        const unsigned long long c = raw[v];
+        if (c == 0ull)
+            continue;
+        uint32_t k;
+        const uint32_t bin = fold_map(mapping[v], f, k);
+        if (bin < nbins) {
+            if (SMEM)
+                atomicAdd(s_fold + bin, c);
+            else
+                atomicAdd(bins + bin, c);
+        }
+    }
+    if (SMEM) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < nbins; i += blockDim.x)
+            if (s_fold[i])
+                atomicAdd(bins + i, s_fold[i]);
+    }
+}
+
+} // namespace b200ans

@@ -164,6 +164,14 @@ int b200ans_histogram_max_device(b200ans_ctx* ctx, int method, uint32_t fidelity
  * frequent values, ties to the smaller value (ans_reorder_fold.hpp:79-106), and upload the
  * value -> reordered-value table. */
 int b200ans_rfold_prepare(b200ans_ctx* ctx, uint32_t fidelity, const uint64_t* raw_bins, size_t nvalues);
+/* the same on the device (ans_reorder_fold.hpp:75-115, the whole of create() before adjust_freqs): d_raw_bins is the
+ * full-alphabet histogram in device memory (u64[nvalues], e.g. from b200ans_histogram_max_device with method INT,
+ * all-reduced by the caller when the job is sharded); selects the 2^(f+7) most frequent values (radix select on the
+ * counts, ties to the smaller value), fills the value -> reordered-value table, and writes the FOLDED histogram over
+ * the reordered values to d_folded_bins (device u64[2^(f+9)]) -- derived from the raw bins, no second pass over the
+ * input.  most_frequent[] comes back for the prelude; one stream synchronisation. */
+int b200ans_rfold_prepare_device(b200ans_ctx* ctx, uint32_t fidelity, const uint64_t* d_raw_bins, size_t nvalues,
+    uint64_t* d_folded_bins);
 /* host histogram -> normalised model (adjust_freqs) + prelude + device encoder tables. */
 int b200ans_model_build(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint64_t* bins, size_t nbins);
 /* prelude of the current model; returns its size through out_bytes */

@@ -26,6 +26,8 @@ def main():
     ap.add_argument("--block-syms", type=int, default=0, help="0 = b200ans_suggest_block_syms(n, 8192, 16384)")
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--bins-scale", type=int, default=1, help="folded coders: multiply the histogram by this before the "
+                    "model is built (4 on 2^30 symbols gives the frame adjust_freqs picks for a 2^32-symbol job)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     peak, _ = bench.measured_peak()
@@ -46,7 +48,15 @@ def main():
             nb = 0
             for it in range(3 + args.reps):
                 with torch.cuda.stream(stream):
-                    nb = codec.compress_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
+                    if args.bins_scale > 1:
+                        nbins = 1 << (f + 9) if method == bench.M_FOLD else 1024
+                        d_bins = torch.zeros(nbins, dtype=torch.int64, device=dev)
+                        codec.histogram_device(method, f, d_in.data_ptr(), n, d_bins.data_ptr(), nbins)
+                        stream.synchronize()
+                        codec.model_build(method, f, (d_bins.cpu().numpy().astype("uint64") * args.bins_scale))
+                        nb = codec.encode_device(d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
+                    else:
+                        nb = codec.compress_device(method, f, d_blob.data_ptr(), d_blob.numel(), d_in.data_ptr(), n)
                     s = codec.stats()
                     codec.decompress_device(method, f, d_out.data_ptr(), n, d_blob.data_ptr(), nb)
                     s2 = codec.stats()
