@@ -31,7 +31,7 @@ class Stats(C.Structure):
         ("launches", C.c_uint64), ("frame_size", C.c_uint64), ("n_symbols_model", C.c_uint32),
         ("n_blocks", C.c_uint32), ("prelude_bytes", C.c_uint64), ("payload_bytes", C.c_uint64),
         ("total_bytes", C.c_uint64), ("encode_kernel", C.c_char * 32), ("decode_kernel", C.c_char * 32),
-        ("ms_allreduce", C.c_float), ("model_flags", C.c_uint32),
+        ("ms_allreduce", C.c_float), ("model_flags", C.c_uint32), ("model_cache_hits", C.c_uint64),
     ]
 
 
@@ -70,6 +70,9 @@ SIGNATURES = {
     "b200ans_histogram_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "b200ans_histogram_max_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_rfold_prepare": (C.c_int, [C.c_void_p, C.c_uint32, u64p, C.c_size_t]),
+    "b200ans_model_create": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u32p, C.c_size_t]),
+    "b200ans_model_create_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t]),
+    "b200ans_model_most_frequent": (C.c_int, [C.c_void_p, u32p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_uint64)]),
     "b200ans_rfold_prepare_device": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_model_build": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u64p, C.c_size_t]),
     "b200ans_model_prelude": (C.c_int, [C.c_void_p, u8p, C.c_size_t, szp]),
@@ -414,6 +417,21 @@ class Codec:
 
     def rfold_prepare_device(self, f, d_raw_bins, nvalues, d_folded_bins):
         self._check(self.lib.b200ans_rfold_prepare_device(self.h, f, d_raw_bins, nvalues, d_folded_bins))
+
+    def model_create(self, method, f, data):
+        data = np.ascontiguousarray(data, dtype=np.uint32)
+        self._check(self.lib.b200ans_model_create(self.h, method, f, _p(data, u32p), data.size))
+
+    def model_create_device(self, method, f, d_src, n):
+        self._check(self.lib.b200ans_model_create_device(self.h, method, f, d_src, n))
+
+    def model_most_frequent(self):
+        cnt, sigma = C.c_size_t(), C.c_uint64()
+        self._check(self.lib.b200ans_model_most_frequent(self.h, None, 0, C.byref(cnt), C.byref(sigma)))
+        out = np.zeros(cnt.value, dtype=np.uint32)
+        if cnt.value:
+            self._check(self.lib.b200ans_model_most_frequent(self.h, _p(out, u32p), out.size, C.byref(cnt), C.byref(sigma)))
+        return out, sigma.value
 
     def model_build(self, method, f, bins):
         bins = np.ascontiguousarray(bins, dtype=np.uint64)

@@ -212,6 +212,7 @@ struct b200ans_ctx {
     uint32_t dec_n_syms = 0;
     uint32_t dec_n_present = 0;
     uint32_t dec_dense = 0;
+    std::vector<uint8_t> dec_prelude; // the prelude the decoder tables on the device were built from (model cache key)
 
     // multi-GPU: the communicator the histogram exchange runs on (b200ans_comm_init / _attach)
     void* comm = nullptr;
@@ -1144,7 +1145,20 @@ try {
         return c->fail(B200ANS_E_ARG, "model_load: bad argument");
     CU(c, cudaSetDevice(c->device));
     const double t0 = now_ms();
+    // The decoder tables on the device are a pure function of (method, fidelity, prelude bytes): a prelude that starts
+    // with the bytes of the model already loaded -- the shards of one job, a container decoded again -- costs a memcmp.
+    if (c->have_dec && c->dec_method == method && c->dec_f == f && !c->dec_prelude.empty() && prelude_bytes >= c->dec_prelude.size()
+        && std::memcmp(prelude, c->dec_prelude.data(), c->dec_prelude.size()) == 0 && !std::getenv("B200ANS_NO_MODEL_CACHE")) {
+        if (consumed)
+            *consumed = c->dec_prelude.size();
+        c->stats.frame_size = uint64_t(1) << c->dec_log2_frame;
+        c->stats.n_symbols_model = c->dec_n_syms;
+        c->stats.model_cache_hits++;
+        c->stats.ms_model = float(now_ms() - t0);
+        return B200ANS_OK;
+    }
     c->have_dec = false;
+    c->dec_prelude.clear();
     // untrusted bytes: every read is bounded by the caller's buffer (host/prelude.hpp ans_load_interp_checked)
     const uint8_t* p = prelude;
     const uint8_t* const end = prelude + prelude_bytes;
@@ -1269,6 +1283,7 @@ try {
     c->dec_f = f;
     c->dec_log2_frame = lg;
     c->dec_n_syms = uint32_t(nfreqs.size());
+    c->dec_prelude.assign(prelude, prelude + total_used);
     c->have_dec = true;
     c->stats.frame_size = frame;
     c->stats.n_symbols_model = uint32_t(nfreqs.size());
@@ -2122,21 +2137,12 @@ int histogram_to_host(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_
     return B200ANS_OK;
 }
 
-// ans_X_compress with device-resident buffers: histogram (K1) [-> all-reduce] -> host normalise -> encode (K2)
-int compress_device_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap, const uint32_t* d_src, size_t n,
-    size_t* out_bytes, bool sharded)
+// ans_X_encode::create (ans_fold.hpp:68-92, ans_int.hpp:38-68, ans_msb.hpp:77-101, ans_reorder_fold.hpp:70-130) with the
+// input on the device: histogram (K1) [-> all-reduce] -> host normalise -> encoder tables.  *empty: nothing to model
+// (every shard of the job is empty).
+int model_from_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n, bool sharded, bool* empty)
 {
-    if (!d_dst || !out_bytes || (!d_src && n) || !valid_method(method, f)
-        || (reinterpret_cast<uintptr_t>(d_src) & 15) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
-        return c->fail(B200ANS_E_ARG, "compress: bad argument (device buffers must be 16-byte aligned)");
-    CU(c, cudaSetDevice(c->device));
-    sharded = sharded && c->comm;
-    c->stats.ms_histogram = c->stats.ms_encode = c->stats.ms_compact = c->stats.ms_model = c->stats.ms_allreduce = 0.f;
-    if (n == 0 && !sharded)
-        return write_empty_container(c, method, f, d_dst, cap, out_bytes);
-    if (sharded && c->block_syms == 0)
-        return c->fail(B200ANS_E_ARG, "sharded compression writes blocked containers (block_syms > 0)");
-
+    *empty = false;
     CU(c, cudaEventRecord(c->ev[3], c->stream));
     CU(c, cudaMemsetAsync(c->d_max(), 0, 4, c->stream));
     uint32_t max_value = 0;
@@ -2225,10 +2231,35 @@ int compress_device_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst,
         bool any = false;
         for (uint64_t v : bins)
             any = any || v != 0;
-        if (!any) // every shard of the job is empty
-            return write_empty_container(c, method, f, d_dst, cap, out_bytes);
+        if (!any) { // every shard of the job is empty
+            *empty = true;
+            return B200ANS_OK;
+        }
     }
     RET(b200ans_model_build(c, method, f, bins.data(), bins.size()));
+    c->stats.ms_histogram = ms_hist;
+    return B200ANS_OK;
+}
+
+// ans_X_compress with device-resident buffers: histogram (K1) [-> all-reduce] -> host normalise -> encode (K2)
+int compress_device_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* d_dst, size_t cap, const uint32_t* d_src, size_t n,
+    size_t* out_bytes, bool sharded)
+{
+    if (!d_dst || !out_bytes || (!d_src && n) || !valid_method(method, f)
+        || (reinterpret_cast<uintptr_t>(d_src) & 15) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
+        return c->fail(B200ANS_E_ARG, "compress: bad argument (device buffers must be 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    sharded = sharded && c->comm;
+    c->stats.ms_histogram = c->stats.ms_encode = c->stats.ms_compact = c->stats.ms_model = c->stats.ms_allreduce = 0.f;
+    if (n == 0 && !sharded)
+        return write_empty_container(c, method, f, d_dst, cap, out_bytes);
+    if (sharded && c->block_syms == 0)
+        return c->fail(B200ANS_E_ARG, "sharded compression writes blocked containers (block_syms > 0)");
+    bool empty = false;
+    RET(model_from_device(c, method, f, d_src, n, sharded, &empty));
+    if (empty)
+        return write_empty_container(c, method, f, d_dst, cap, out_bytes);
+    const float ms_hist = c->stats.ms_histogram;
     if (n == 0) { // this rank's shard is empty: it took part in the reduction, its container holds no blocks
         c->stats.ms_histogram = ms_hist;
         return write_empty_container(c, method, f, d_dst, cap, out_bytes);
@@ -2246,6 +2277,57 @@ try {
     if (!c)
         return B200ANS_E_ARG;
     return compress_device_impl(c, method, f, d_dst, cap, d_src, n, out_bytes, false);
+}
+B200ANS_CATCH_INT
+
+// ans_X_encode::create(in_u32, n) (ans_fold.hpp:68-92, ans_int.hpp:38-68, ans_msb.hpp:77-101, ans_reorder_fold.hpp:70-130)
+// as a call of its own: device histogram (ANSrfold: + selection of the most frequent values) -> host normalisation ->
+// prelude + device encoder tables.  The model becomes the context's current encoder model (b200ans_model_prelude /
+// _nfreqs / _most_frequent read it, b200ans_encode_device codes with it).
+extern "C" int b200ans_model_create_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_src, size_t n)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_src || n == 0 || !valid_method(method, f) || (reinterpret_cast<uintptr_t>(d_src) & 15))
+        return c->fail(B200ANS_E_ARG, "model_create: bad argument (d_src must be 16-byte aligned, n > 0)");
+    CU(c, cudaSetDevice(c->device));
+    c->stats.ms_histogram = c->stats.ms_model = c->stats.ms_allreduce = 0.f;
+    bool empty = false;
+    return model_from_device(c, method, f, d_src, n, false, &empty);
+}
+B200ANS_CATCH_INT
+
+// the same for a host buffer: the symbols are copied to the device (they stay in the context's input buffer)
+extern "C" int b200ans_model_create(b200ans_ctx* c, int method, uint32_t f, const uint32_t* src, size_t n)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!src || n == 0 || !valid_method(method, f))
+        return c->fail(B200ANS_E_ARG, "model_create: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
+    CU(c, cudaMemcpyAsync(c->io_in.p, src, n * 4, cudaMemcpyHostToDevice, c->stream));
+    return b200ans_model_create_device(c, method, f, c->io_in.as<uint32_t>(), n);
+}
+B200ANS_CATCH_INT
+
+// ANSrfold: most_frequent[] and sigma of the current encoder model (ans_reorder_fold.hpp:180-184); count 0 when the
+// model keeps the identity mapping
+extern "C" int b200ans_model_most_frequent(b200ans_ctx* c, uint32_t* dst, size_t capacity, size_t* out_count, uint64_t* sigma)
+try {
+    if (!c || !out_count)
+        return B200ANS_E_ARG;
+    if (!c->have_enc || c->enc_method != METHOD_RFOLD)
+        return c->fail(B200ANS_E_STATE, "no ANSrfold encoder model");
+    *out_count = c->most_frequent.size();
+    if (sigma)
+        *sigma = c->rfold_sigma;
+    if (!dst)
+        return B200ANS_OK;
+    if (capacity < c->most_frequent.size())
+        return c->fail(B200ANS_E_CAPACITY, "most_frequent buffer too small");
+    std::copy(c->most_frequent.begin(), c->most_frequent.end(), dst);
+    return B200ANS_OK;
 }
 B200ANS_CATCH_INT
 

@@ -301,7 +301,10 @@ __global__ void __launch_bounds__(kRfThreads) rf_mapping_hot_kernel(const RfStat
 }
 
 // folded histogram from the raw one: bins[fold(mapping[v])] += raw[v]  (ans_reorder_fold.hpp:110-115)
+// A thread walks kRfRun consecutive values: all but the K hot ones map to v + K, whose folded bin changes once every
+// 256 (65 536, ...) values, so the thread sums a run in a register and touches a counter when the bin changes.
 // SMEM: the folded alphabet (2^(f+9) 64-bit counters) fits the CTA's shared memory.
+constexpr uint32_t kRfRun = 16;
 template <bool SMEM>
 __global__ void __launch_bounds__(kRfThreads) rf_fold_bins_kernel(const unsigned long long* __restrict__ raw, uint32_t nvalues,
     const uint32_t* __restrict__ mapping, uint32_t f, uint32_t nbins, unsigned long long* __restrict__ bins)
@@ -312,18 +315,36 @@ __global__ void __launch_bounds__(kRfThreads) rf_fold_bins_kernel(const unsigned
             s_fold[i] = 0ull;
         __syncthreads();
     }
-    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nvalues; v += gridDim.x * blockDim.x) {
-        const unsigned long long c = raw[v];
-        if (c == 0ull)
-            continue;
-        uint32_t k;
-        const uint32_t bin = fold_map(mapping[v], f, k);
-        if (bin < nbins) {
+    auto flush = [&](uint32_t bin, unsigned long long sum) {
+        if (sum != 0ull && bin < nbins) {
             if (SMEM)
-                atomicAdd(s_fold + bin, c);
+                atomicAdd(s_fold + bin, sum);
             else
-                atomicAdd(bins + bin, c);
+                atomicAdd(bins + bin, sum);
         }
+    };
+    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x * kRfRun;
+    for (uint64_t v0 = (uint64_t(blockIdx.x) * blockDim.x + threadIdx.x) * kRfRun; v0 < nvalues; v0 += stride) {
+        uint32_t cur = 0xFFFFFFFFu;
+        unsigned long long sum = 0ull;
+#pragma unroll 4
+        for (uint32_t j = 0; j < kRfRun; j++) {
+            const uint64_t v = v0 + j;
+            if (v >= nvalues)
+                break;
+            const unsigned long long c = raw[v];
+            if (c == 0ull)
+                continue;
+            uint32_t k;
+            const uint32_t bin = fold_map(mapping[v], f, k);
+            if (bin != cur) {
+                flush(cur, sum);
+                cur = bin;
+                sum = 0ull;
+            }
+            sum += c;
+        }
+        flush(cur, sum);
     }
     if (SMEM) {
         __syncthreads();

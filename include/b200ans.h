@@ -92,6 +92,8 @@ typedef struct b200ans_stats {
     char decode_kernel[32]; /* (as ncu names them: "lpb3_encode_kernel", ...)          */
     float ms_allreduce;     /* histogram / maximum all-reduce (sharded calls)          */
     uint32_t model_flags;   /* B200ANS_MODEL_* of the current encoder model            */
+    uint64_t model_cache_hits; /* b200ans_model_load calls (decompress included) answered by the decoder model already
+                                * on the device: same method, fidelity and prelude bytes (since creation)           */
 } b200ans_stats;
 /* The model was normalised from 2^31 symbols or more: the reference's cross_entropy() sums the counts in an `int`
  * (util.hpp:288-289), so adjust_freqs' stopping rule changes -- in [2^31, 2^32) the first frame that fits is taken
@@ -174,6 +176,15 @@ int b200ans_rfold_prepare_device(b200ans_ctx* ctx, uint32_t fidelity, const uint
     uint64_t* d_folded_bins);
 /* host histogram -> normalised model (adjust_freqs) + prelude + device encoder tables. */
 int b200ans_model_build(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint64_t* bins, size_t nbins);
+/* ans_X_encode::create(in_u32, n) as one call (ans_fold.hpp:68-92, ans_int.hpp:38-68, ans_msb.hpp:77-101,
+ * ans_reorder_fold.hpp:70-130): device histogram (+ ANSrfold's selection of the most frequent values) -> normalised
+ * model + prelude + device encoder tables; becomes the context's current encoder model.  Host buffer (copied to the
+ * device) or device buffer (16-byte aligned). */
+int b200ans_model_create(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint32_t* src, size_t n);
+int b200ans_model_create_device(b200ans_ctx* ctx, int method, uint32_t fidelity, const uint32_t* d_src, size_t n);
+/* ANSrfold: most_frequent[] (2^(f+7) values, or none for the identity mapping) and sigma of the current encoder model
+ * (ans_reorder_fold.hpp:180-184) */
+int b200ans_model_most_frequent(b200ans_ctx* ctx, uint32_t* dst, size_t capacity, size_t* out_count, uint64_t* sigma);
 /* prelude of the current model; returns its size through out_bytes */
 int b200ans_model_prelude(b200ans_ctx* ctx, uint8_t* dst, size_t capacity, size_t* out_bytes);
 /* normalised frequencies of the current model (count = max_sym + 1) */

@@ -19,6 +19,10 @@
 //   ans_serialize_interp     ans_util.hpp:46-63             b200::ans_serialize_interp
 //   ans_load_interp          ans_util.hpp:25-42             b200::ans_load_interp
 //   next_power_of_two / is_power_of_two  ans_util.hpp:65,74 b200::next_power_of_two / is_power_of_two
+//   scale_freqs              ans_util.hpp:77-95             b200::scale_freqs
+//   ans_fold_encode<f> / ans_fold_decode<f>   ans_fold.hpp:67-125,177-235     b200::ans_fold_encode<f> / _decode<f>
+//   ans_int_encode / _decode, ans_msb_encode / _decode, ans_reorder_fold_encode<f> / _decode<f>     likewise
+//     (create / serialize / load and the public fields; the per-symbol steps are GPU block coders here, see below)
 //
 // Same static signatures as the reference structs -- `static std::string name()`,
 // `static size_t encode(const uint32_t* in, size_t n, uint8_t* out, size_t out_cap, uint8_t* buf = NULL)`,
@@ -38,6 +42,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <string>
 #include <vector>
 
@@ -173,6 +178,20 @@ inline std::vector<uint32_t> adjust_freqs(
     return out;
 }
 
+// one fit of the counts F to the frame M, symbols in `mapping` order; true when the fit FAILED (the reference's return
+// value, ans_util.hpp:77-95: `return M != 0` with the frame left over)
+inline bool scale_freqs(std::vector<uint32_t>& S, const std::vector<uint64_t>& F, std::vector<uint32_t>& mapping, int64_t M,
+    size_t sigma, size_t freq_sum)
+{
+    int fits = 0;
+    if (S.size() < F.size())
+        S.resize(F.size());
+    const int rc = b200ans_scale_freqs(S.data(), F.data(), F.size(), mapping.data(), sigma, M, freq_sum, &fits);
+    if (rc != B200ANS_OK)
+        quit("scale_freqs", rc, nullptr);
+    return fits == 0;
+}
+
 // writes vbyte(max_sym), log2(frame), interpolative code; advances out_u8; returns the interp bytes (ans_util.hpp:46-63)
 inline size_t ans_serialize_interp(std::vector<uint32_t>& vec, size_t frame_size, uint8_t*& out_u8)
 {
@@ -202,6 +221,145 @@ inline std::vector<uint32_t> ans_load_interp(const uint8_t* in_u8)
         quit("ans_load_interp", rc, nullptr);
     return out;
 }
+
+// ---- the model structs (ans_fold.hpp:67-125,177-235; ans_int.hpp:38-110,112-195; ans_msb.hpp:75-128,177-233;
+//      ans_reorder_fold.hpp:70-186,233-310) ------------------------------------------------------------------------
+// Same shape as the reference's: `T::create(in_u32, n)` builds the model from the input (histogram on the GPU,
+// adjust_freqs on the host), `serialize(out_u8)` writes the prelude, advances the pointer and returns what the
+// reference's returns; `T::load(in_u8, in_bytes)` reads a prelude back.  Public fields as in the reference: nfreqs,
+// table (encoder: {freq, base, sym_upper_bound}), frame_size, lower_bound, frame_mask, frame_log2, and for ANSrfold
+// most_frequent and sigma.  What is NOT here, on purpose: the per-symbol steps encode_symbol / decode_sym /
+// flush_state / init_state -- they would be a CPU coder, and this library has none.  Their place is taken by
+// `encode(dst, capacity, in_u32, n)`, which runs the block coders on the GPU (a b200ans container; the prelude inside
+// it is the one serialize() writes), and by b200::ans_X_decompress for the way back.
+// create() / load() make the model the current encoder / decoder model of the thread's context.
+struct enc_entry { // ans_fold.hpp:30-34 (freq widened to 32 bits so that plain ANS fits too, ans_int.hpp:32-36)
+    uint32_t freq;
+    uint32_t base;
+    uint64_t sym_upper_bound;
+};
+
+template <int METHOD, uint32_t fidelity> struct encode_model {
+    static encode_model create(const uint32_t* in_u32, size_t n)
+    {
+        b200ans_ctx* ctx = context();
+        int rc = b200ans_model_create(ctx, METHOD, fidelity, in_u32, n);
+        if (rc != B200ANS_OK)
+            quit("create", rc, ctx);
+        encode_model m;
+        size_t count = 0;
+        rc = b200ans_model_nfreqs(ctx, nullptr, 0, &count, &m.frame_size);
+        if (rc == B200ANS_OK) {
+            m.nfreqs.resize(count);
+            rc = b200ans_model_nfreqs(ctx, m.nfreqs.data(), m.nfreqs.size(), &count, &m.frame_size);
+        }
+        if (rc != B200ANS_OK)
+            quit("create", rc, ctx);
+        m.lower_bound = 16 * m.frame_size; // constants::K * frame_size (ans_fold.hpp:91)
+        m.table.resize(m.nfreqs.size());
+        uint64_t base = 0;
+        for (size_t s = 0; s < m.nfreqs.size(); s++) {
+            m.table[s] = enc_entry { m.nfreqs[s], uint32_t(base), (uint64_t(16) << 32) * m.nfreqs[s] };
+            base += m.nfreqs[s];
+        }
+        if (METHOD == B200ANS_METHOD_RFOLD) {
+            size_t k = 0;
+            rc = b200ans_model_most_frequent(ctx, nullptr, 0, &k, &m.sigma);
+            m.most_frequent.resize(k);
+            if (rc == B200ANS_OK && k)
+                rc = b200ans_model_most_frequent(ctx, m.most_frequent.data(), k, &k, &m.sigma);
+            if (rc != B200ANS_OK)
+                quit("create", rc, ctx);
+        }
+        size_t pb = 0;
+        b200ans_model_prelude(ctx, nullptr, 0, &pb);
+        m.prelude.resize(pb);
+        rc = b200ans_model_prelude(ctx, m.prelude.data(), m.prelude.size(), &pb);
+        if (rc != B200ANS_OK)
+            quit("create", rc, ctx);
+        return m;
+    }
+
+    // writes the prelude, advances out_u8; returns what the reference's serialize() returns: the interpolative part's
+    // bytes (ans_util.hpp:46-63 -- not the vbyte + log2 M header), plus, for ANSrfold, the flag word and the
+    // most_frequent list (ans_reorder_fold.hpp:132-154)
+    size_t serialize(uint8_t*& out_u8)
+    {
+        std::memcpy(out_u8, prelude.data(), prelude.size());
+        out_u8 += prelude.size();
+        size_t header = 2; // vbyte(max_sym) + the log2 M byte
+        for (uint32_t m = uint32_t(nfreqs.size() - 1); m >= 128; m >>= 7)
+            header++;
+        return prelude.size() - header;
+    }
+
+    uint64_t initial_state() const { return lower_bound; }
+
+    // the block coders on the GPU; the model is a pure function of the input, so this is the one-shot call (it
+    // rebuilds the same model on the device).  Writes a b200ans container, returns its size.
+    size_t encode(uint8_t* dst, size_t dstCapacity, const uint32_t* in_u32, size_t n) const
+    {
+        return compress(METHOD, fidelity, dst, dstCapacity, in_u32, n);
+    }
+
+    std::vector<uint32_t> nfreqs;
+    std::vector<enc_entry> table;
+    std::vector<uint32_t> most_frequent; // ANSrfold
+    uint64_t frame_size = 0;
+    uint64_t lower_bound = 0;
+    uint64_t sigma = 0;                  // ANSrfold
+    std::vector<uint8_t> prelude;        // (not in the reference: the bytes serialize() writes)
+};
+
+template <int METHOD, uint32_t fidelity> struct decode_model {
+    // the reference's load(in_u8) trusts the stream; here the number of readable bytes is part of the call
+    static decode_model load(const uint8_t* in_u8, size_t in_bytes, size_t* consumed = nullptr)
+    {
+        b200ans_ctx* ctx = context();
+        size_t used = 0;
+        const int rc = b200ans_model_load(ctx, METHOD, fidelity, in_u8, in_bytes, &used); // bounded, validated
+        if (rc != B200ANS_OK)
+            quit("load", rc, ctx);
+        decode_model m;
+        const uint8_t* p = in_u8;
+        if (METHOD == B200ANS_METHOD_RFOLD) { // flag [+ most_frequent] (ans_reorder_fold.hpp:238-252)
+            uint32_t flag;
+            std::memcpy(&flag, p, 4);
+            p += 4;
+            if (flag) {
+                m.most_frequent.resize(size_t(1) << (fidelity + 7));
+                std::memcpy(m.most_frequent.data(), p, 4 * m.most_frequent.size());
+                p += 4 * m.most_frequent.size();
+            }
+        }
+        m.nfreqs = ans_load_interp(p);
+        for (uint32_t v : m.nfreqs)
+            m.frame_size += v;
+        m.frame_mask = m.frame_size - 1;
+        while ((uint64_t(1) << m.frame_log2) < m.frame_size)
+            m.frame_log2++;
+        m.lower_bound = 16 * m.frame_size;
+        if (consumed)
+            *consumed = used;
+        return m;
+    }
+
+    std::vector<uint32_t> nfreqs;
+    std::vector<uint32_t> most_frequent; // ANSrfold
+    uint64_t frame_size = 0;
+    uint64_t frame_mask = 0;
+    uint64_t frame_log2 = 0;
+    uint64_t lower_bound = 0;
+};
+
+template <uint32_t fidelity> using ans_fold_encode = encode_model<B200ANS_METHOD_FOLD, fidelity>;
+template <uint32_t fidelity> using ans_fold_decode = decode_model<B200ANS_METHOD_FOLD, fidelity>;
+template <uint32_t fidelity> using ans_reorder_fold_encode = encode_model<B200ANS_METHOD_RFOLD, fidelity>;
+template <uint32_t fidelity> using ans_reorder_fold_decode = decode_model<B200ANS_METHOD_RFOLD, fidelity>;
+using ans_int_encode = encode_model<B200ANS_METHOD_INT, 0>;
+using ans_int_decode = decode_model<B200ANS_METHOD_INT, 0>;
+using ans_msb_encode = encode_model<B200ANS_METHOD_MSB, 0>;
+using ans_msb_decode = decode_model<B200ANS_METHOD_MSB, 0>;
 
 } // namespace b200
 

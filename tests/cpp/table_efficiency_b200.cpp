@@ -98,6 +98,69 @@ int main(int argc, char** argv)
     std::printf("model API: sigma=%zu frame=%llu prelude=%zu bytes (interp %zu)  %s\n", nfreqs.size(), (unsigned long long)frame,
         size_t(p - prelude.data()), interp_bytes, model_ok ? "OK" : "MISMATCH");
     ok = ok && model_ok;
+
+    // scale_freqs (ans_util.hpp:77-95): one fit of the same counts to the frame adjust_freqs chose reproduces its answer
+    {
+        std::vector<std::pair<uint64_t, uint32_t>> order;
+        uint64_t total = 0;
+        for (uint32_t s = 0; s <= largest; s++)
+            if (freqs[s]) {
+                order.emplace_back(freqs[s], s);
+                total += freqs[s];
+            }
+        std::sort(order.begin(), order.end());
+        std::vector<uint32_t> mapping;
+        for (auto& pr : order)
+            mapping.push_back(pr.second);
+        std::vector<uint32_t> S(largest + 1, 0);
+        std::vector<uint64_t> F(freqs.begin(), freqs.begin() + largest + 1);
+        const bool failed = b200::scale_freqs(S, F, mapping, int64_t(frame), mapping.size(), total);
+        const bool sf_ok = !failed && S == nfreqs;
+        std::printf("scale_freqs: %s\n", sf_ok ? "OK" : "MISMATCH");
+        ok = ok && sf_ok;
+    }
+
+    // the model structs (ans_fold.hpp:67-125,177-235 and siblings): create -> serialize -> load, fields as in the reference
+    {
+        auto enc = b200::ans_fold_encode<1>::create(inputs[1].data(), inputs[1].size());
+        std::vector<uint8_t> pre(enc.nfreqs.size() * 8 + 128);
+        uint8_t* q = pre.data();
+        const size_t ret = enc.serialize(q);
+        size_t used = 0;
+        auto dec = b200::ans_fold_decode<1>::load(pre.data(), size_t(q - pre.data()), &used);
+        uint64_t sum = 0;
+        for (uint32_t v : enc.nfreqs)
+            sum += v;
+        bool m_ok = dec.nfreqs == enc.nfreqs && sum == enc.frame_size && enc.lower_bound == 16 * enc.frame_size
+            && enc.initial_state() == enc.lower_bound && dec.frame_mask == enc.frame_size - 1 && (uint64_t(1) << dec.frame_log2) == dec.frame_size
+            && used == size_t(q - pre.data()) && ret > 0 && ret < used && enc.table.size() == enc.nfreqs.size()
+            && enc.table.back().base + enc.table.back().freq == enc.frame_size;
+        // the struct's model is the one the one-shot coder uses: same prelude inside the container
+        std::vector<uint8_t> blob(inputs[1].size() * 8 + 4096);
+        const size_t nb = enc.encode(blob.data(), blob.size(), inputs[1].data(), inputs[1].size());
+        b200ans_container info;
+        m_ok = m_ok && b200ans_container_info(blob.data(), nb, &info) == B200ANS_OK && info.prelude_bytes == used
+            && std::memcmp(blob.data() + B200ANS_HEADER_BYTES, pre.data(), used) == 0;
+        std::vector<uint32_t> out(inputs[1].size());
+        b200::ans_fold_decompress<1>(out.data(), out.size(), blob.data(), nb);
+        m_ok = m_ok && out == inputs[1];
+        std::printf("model structs ANSfold-1: sigma'=%zu frame=%llu prelude=%zu  %s\n", enc.nfreqs.size(),
+            (unsigned long long)enc.frame_size, used, m_ok ? "OK" : "MISMATCH");
+        ok = ok && m_ok;
+
+        auto renc = b200::ans_reorder_fold_encode<1>::create(inputs[1].data(), inputs[1].size());
+        std::vector<uint8_t> rpre(renc.nfreqs.size() * 8 + 128 + 4 * renc.most_frequent.size());
+        uint8_t* rq = rpre.data();
+        renc.serialize(rq);
+        auto rdec = b200::ans_reorder_fold_decode<1>::load(rpre.data(), size_t(rq - rpre.data()));
+        const bool r_ok = rdec.nfreqs == renc.nfreqs && rdec.most_frequent == renc.most_frequent && renc.most_frequent.size() == 256
+            && renc.sigma >= 256;
+        auto ienc = b200::ans_int_encode::create(inputs[0].data(), inputs[0].size());
+        auto menc = b200::ans_msb_encode::create(inputs[1].data(), inputs[1].size());
+        const bool i_ok = b200::is_power_of_two(ienc.frame_size) && b200::is_power_of_two(menc.frame_size) && menc.nfreqs.size() <= 1280;
+        std::printf("model structs ANSrfold-1 / ANS / ANSmsb: %s\n", (r_ok && i_ok) ? "OK" : "MISMATCH");
+        ok = ok && r_ok && i_ok;
+    }
     std::printf(ok ? "ALL OK\n" : "FAILED\n");
     return ok ? 0 : 1;
 }

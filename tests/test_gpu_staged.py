@@ -281,3 +281,25 @@ def test_corrupt_containers_fail_cleanly(codec, method, f, kind, path, device_en
             assert e.code == -5
     # the context is still healthy
     assert np.array_equal(decode(good), data)
+
+
+# ---- decoder model cache -----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("method,f,kind", [(M_FOLD, 1, "zipf20"), (M_INT, 0, "geom"), (M_RFOLD, 2, "zipf20")])
+def test_decoder_model_cache(codec, method, f, kind):
+    """b200ans_model_load keeps the prelude its device tables were built from: the same model again (the shards of a
+    job, a container decoded twice) is a hit, another model or method is a miss, and results never change"""
+    a = _inputs.make(kind, 150_001, seed=21)
+    b = _inputs.make(kind, 150_001, seed=22)
+    blob_a = codec.compress(method, f, a).copy()
+    blob_b = codec.compress(method, f, b).copy()
+    assert np.array_equal(codec.decompress(method, f, blob_a, a.size), a)
+    h0 = codec.stats().model_cache_hits
+    assert np.array_equal(codec.decompress(method, f, blob_a, a.size), a)
+    assert codec.stats().model_cache_hits == h0 + 1
+    assert np.array_equal(codec.decompress(method, f, blob_b, b.size), b)  # other model: rebuilt
+    assert codec.stats().model_cache_hits == h0 + 1
+    assert np.array_equal(codec.decompress(method, f, blob_a, a.size), a)  # and back: rebuilt again
+    assert codec.stats().model_cache_hits == h0 + 1
+    # two shards coded with ONE model (staged path): the second decode is a hit
+    codec.model_load(method, f, _container.parse(blob_a)["prelude"])
+    assert codec.stats().model_cache_hits == h0 + 2
