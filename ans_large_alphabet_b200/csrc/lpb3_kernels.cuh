@@ -597,6 +597,11 @@ struct L3Reader {
 // (Measured in round 2 and dropped: refilling the rings in 64-byte chunks by groups of four lanes, so that one LDGSTS
 // touches 8 lines instead of 32 and brings whole sectors -- byte-exact, 1.955 -> 1.947 ms for ANSfold-1 at 2^30 symbols,
 // 2.32 -> 2.47 ms on the rank/select tables: the copies are not what the LSU pipe spends its wavefronts on.)
+// (Also measured in round 2 and dropped: the decoded symbols leaving through TMA -- a swizzled 1 KiB tile per warp in
+// shared memory, two conflict-free STS.128 per lane and iteration, one cp.async.bulk.tensor store of 32 blocks x 8
+// symbols -- instead of a 32-byte STG per lane (14 LSU wavefronts per warp and iteration).  Byte-exact, and the LSU
+// wavefronts do go down, but the kernel does not get faster: ANSfold-1 1.956 -> 1.999 ms, ANS 2.18 -> 2.95 ms, the
+// 2^18-slot model 2.274 -> 2.240 ms at 2^30 symbols.)
 template <int METHOD, int TABLE, int QI, int MAXW>
 __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs a)
 {
