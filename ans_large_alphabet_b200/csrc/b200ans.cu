@@ -164,9 +164,11 @@ struct b200ans_ctx {
     // grow-only device buffers
     DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre, pa_keys;
     // ANSrfold on the device (rfold_kernels.cuh): raw histogram, selection state, candidates, hash of the hot values
+    DevBuf rf_sbuckets, rf_stags, rf_fast, rf_cand, rf_ctags, rf_cdisp, rf_cslot, rf_ccount, rf_sketch; // the fast route (rfold_kernels.cuh)
     DevBuf rf_raw, rf_raw32, rf_state, rf_hist, rf_tiles, rf_cand_count, rf_cand_value, rf_most, rf_tags, rf_disp, enc_table_rf;
     size_t rf_guess = 0;          // value range the next optimistic raw histogram is sized for
     bool rf_hash_ok = false;      // the L3 encoder's perfect hash of most_frequent[] is on the device
+    bool rf_fast_used = false;    // the current ANSrfold mapping came from the fast route (rfold_fast_model)
     uint32_t rf_mul = 0, rf_bshift = 0;
     uint32_t pa_undecided = 0;    // models of the last pa_compress the device normaliser handed to the host
     uint8_t* pa_pinned = nullptr; // pseudo-adaptive mode: counts / frequencies of all models (pinned, grows on demand)
@@ -366,6 +368,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
              &c->dec_slots, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys,
+             &c->rf_sbuckets, &c->rf_stags, &c->rf_fast, &c->rf_cand, &c->rf_ctags, &c->rf_cdisp, &c->rf_cslot, &c->rf_ccount, &c->rf_sketch,
              &c->rf_raw, &c->rf_raw32, &c->rf_state, &c->rf_hist, &c->rf_tiles, &c->rf_cand_count, &c->rf_cand_value, &c->rf_most, &c->rf_tags, &c->rf_disp,
              &c->enc_table_rf })
         b->release();
@@ -792,13 +795,13 @@ namespace {
 // Perfect hash of the K = 2^(f+7) most frequent values for the L3 encoder (lpb3_kernels.cuh L3Rfold): "hash and
 // displace" -- bucket b = (v * mul) >> bshift carries a displacement d_b, slot(v) = (v * mul + d_b) & (K - 1), every
 // hot value gets a slot of its own (K slots for K values: minimal).  Buckets are placed largest first.
-bool rfold_build_hash(const std::vector<uint32_t>& hot, uint32_t mul, uint32_t bshift, std::vector<uint32_t>& tags,
+bool rfold_build_hash(const std::vector<uint32_t>& hot, uint32_t slots, uint32_t mul, uint32_t bshift, std::vector<uint32_t>& tags,
     std::vector<uint16_t>& disp, std::vector<uint32_t>& slot_of_rank)
 {
-    const uint32_t K = uint32_t(hot.size());
+    const uint32_t K = slots; // a power of two, at least hot.size()
     const uint32_t B = 1u << (32u - bshift);
     std::vector<std::vector<uint32_t>> buckets(B);
-    for (uint32_t r = 0; r < K; r++)
+    for (uint32_t r = 0; r < hot.size(); r++)
         buckets[(hot[r] * mul) >> bshift].push_back(r);
     std::vector<uint32_t> order(B);
     for (uint32_t b = 0; b < B; b++)
@@ -806,7 +809,7 @@ bool rfold_build_hash(const std::vector<uint32_t>& hot, uint32_t mul, uint32_t b
     std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return buckets[x].size() > buckets[y].size(); });
     tags.assign(K, 0xFFFFFFFFu);
     disp.assign(B, 0);
-    slot_of_rank.assign(K, 0);
+    slot_of_rank.assign(hot.size(), 0);
     std::vector<uint8_t> used(K, 0);
     for (uint32_t b : order) {
         const auto& keys = buckets[b];
@@ -894,6 +897,7 @@ try {
     c->n_values = uint32_t(nvalues);
     c->map_f = f;
     c->have_mapping = true;
+    c->rf_fast_used = false;
     return B200ANS_OK;
 }
 B200ANS_CATCH_INT
@@ -983,6 +987,7 @@ try {
     c->n_values = uint32_t(nvalues);
     c->map_f = f;
     c->have_mapping = true;
+    c->rf_fast_used = false;
     return B200ANS_OK;
 }
 B200ANS_CATCH_INT
@@ -1063,7 +1068,7 @@ try {
         bool ok = false;
         for (int attempt = 0; attempt < 16 && !ok; attempt++, mul = mul * 0x01000193u + 0x7F4A7C15u) {
             mul |= 1u;
-            ok = rfold_build_hash(c->most_frequent, mul, bshift, tags, disp, slot_of_rank);
+            ok = rfold_build_hash(c->most_frequent, K, mul, bshift, tags, disp, slot_of_rank);
             if (ok)
                 break;
         }
@@ -1093,7 +1098,8 @@ try {
         uint64_t total = 0;
         for (uint64_t v : freqs)
             total += v;
-        c->stats.model_flags = total >= (uint64_t(1) << 31) ? B200ANS_MODEL_INT_ACCUMULATOR_QUIRK : 0u;
+        c->stats.model_flags = (total >= (uint64_t(1) << 31) ? B200ANS_MODEL_INT_ACCUMULATOR_QUIRK : 0u)
+            | (method == METHOD_RFOLD && c->rf_fast_used ? B200ANS_MODEL_RFOLD_FAST : 0u);
     }
     c->stats.ms_model = float(now_ms() - t0);
     return B200ANS_OK;
@@ -2137,6 +2143,116 @@ int histogram_to_host(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_
     return B200ANS_OK;
 }
 
+// ANSrfold, the fast route (rfold_kernels.cuh, second half): sample -> candidates -> ONE pass that counts the candidates
+// exactly and bounds everything else -> exact selection, or *done = false and the caller takes the raw histogram.
+int rfold_fast_model(b200ans_ctx* c, uint32_t f, const uint32_t* d_src, size_t n, std::vector<uint64_t>& bins, uint32_t* max_value, bool* done)
+{
+    *done = false;
+    const uint32_t K = 1u << (f + 7);
+    const size_t nfolded = alphabet_bins(METHOD_RFOLD, f, 0);
+    const size_t nb = size_t(1) << kRfSampleBucketsLog2;
+    CU(c, c->rf_sbuckets.reserve(nb * 8));
+    CU(c, c->rf_stags.reserve(nb * 4));
+    CU(c, c->rf_state.reserve(sizeof(RfState)));
+    CU(c, c->rf_hist.reserve(kRfDigits * 4));
+    CU(c, c->rf_fast.reserve(sizeof(RfFast)));
+    CU(c, c->rf_cand.reserve(kRfCand * 4));
+    CU(c, c->rf_ctags.reserve(kRfCandSlots * 4));
+    CU(c, c->rf_cdisp.reserve(size_t(2) << kRfCandBucketsLog2));
+    CU(c, c->rf_ccount.reserve(kRfCandSlots * 8));
+    CU(c, c->rf_sketch.reserve(size_t(8) << kRfSketchLog2));
+    CU(c, c->rf_most.reserve(size_t(K) * 4));
+    CU(c, c->bins.reserve(nfolded * 8));
+    CU(c, cudaMemsetAsync(c->rf_sbuckets.p, 0, nb * 8, c->stream));
+    CU(c, cudaMemsetAsync(c->rf_stags.p, 0xFF, nb * 4, c->stream));
+    CU(c, cudaMemsetAsync(c->rf_state.p, 0, sizeof(RfState), c->stream));
+    CU(c, cudaMemsetAsync(c->rf_hist.p, 0, kRfDigits * 4, c->stream));
+    CU(c, cudaMemsetAsync(c->rf_fast.p, 0, sizeof(RfFast), c->stream));
+    CU(c, cudaMemsetAsync(c->rf_cand.p, 0xFF, kRfCand * 4, c->stream));
+    CU(c, cudaMemsetAsync(c->rf_ccount.p, 0, kRfCandSlots * 8, c->stream));
+    CU(c, cudaMemsetAsync(c->rf_sketch.p, 0, size_t(8) << kRfSketchLog2, c->stream));
+    CU(c, cudaMemsetAsync(c->bins.p, 0, nfolded * 8, c->stream));
+    CU(c, cudaMemsetAsync(c->d_max(), 0, 4, c->stream));
+    RfState* st = c->rf_state.as<RfState>();
+    RfFast* fs = c->rf_fast.as<RfFast>();
+    auto* buckets = c->rf_sbuckets.as<unsigned long long>();
+    // 1. sample, 2. the fullest buckets
+    const uint32_t n_sample_vec = uint32_t(std::min<uint64_t>(uint64_t(n) >> 2, uint64_t(1) << 17)); // 2^19 symbols
+    const int sgrid = int(std::max<uint32_t>(1, std::min<uint32_t>((n_sample_vec + 255) / 256, uint32_t(c->num_sms) * 8)));
+    rf_sample_kernel<<<sgrid, 256, 0, c->stream>>>(d_src, n, n_sample_vec, buckets, c->rf_stags.as<uint32_t>());
+    const int bgrid = int(std::min<uint32_t>(uint32_t(nb / kRfThreads), uint32_t(c->num_sms) * 8));
+    for (uint32_t p = 0; p < 2; p++) { // sample counts stay below 2^24
+        const uint32_t shift = (1 - p) * kRfDigitBits;
+        rf_digit_hist_kernel<<<bgrid, kRfThreads, 0, c->stream>>>(buckets, uint32_t(nb), shift, p == 0, st, c->rf_hist.as<unsigned int>(), st);
+        rf_digit_pick_kernel<<<1, kRfDigits / 4, 0, c->stream>>>(c->rf_hist.as<unsigned int>(), shift, p == 0, kRfCand, st);
+    }
+    rf_cand_collect_kernel<<<bgrid, 256, 0, c->stream>>>(buckets, c->rf_stags.as<uint32_t>(), st, false, fs, c->rf_cand.as<uint32_t>());
+    rf_cand_collect_kernel<<<bgrid, 256, 0, c->stream>>>(buckets, c->rf_stags.as<uint32_t>(), st, true, fs, c->rf_cand.as<uint32_t>());
+    c->stats.launches += 7;
+    std::vector<uint32_t> cand(kRfCand);
+    CU(c, cudaMemcpyAsync(cand.data(), c->rf_cand.p, kRfCand * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    std::sort(cand.begin(), cand.end());
+    cand.erase(std::unique(cand.begin(), cand.end()), cand.end());
+    while (!cand.empty() && cand.back() == 0xFFFFFFFFu)
+        cand.pop_back();
+    if (cand.size() < K)
+        return B200ANS_OK; // too few distinct values in the sample: the raw histogram decides
+    // perfect hash of the candidates
+    std::vector<uint32_t> tags, slot_of;
+    std::vector<uint16_t> disp;
+    uint32_t mul = 0x9E3779B1u;
+    bool ok = false;
+    for (int attempt = 0; attempt < 16 && !ok; attempt++, mul = mul * 0x01000193u + 0x7F4A7C15u) {
+        mul |= 1u;
+        ok = rfold_build_hash(cand, kRfCandSlots, mul, 32u - kRfCandBucketsLog2, tags, disp, slot_of);
+        if (ok)
+            break;
+    }
+    if (!ok)
+        return B200ANS_OK;
+    CU(c, cudaMemcpyAsync(c->rf_ctags.p, tags.data(), kRfCandSlots * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaMemcpyAsync(c->rf_cdisp.p, disp.data(), disp.size() * 2, cudaMemcpyHostToDevice, c->stream));
+    std::vector<uint16_t> cslot(slot_of.begin(), slot_of.end()); // candidate -> slot, for the ranking
+    CU(c, c->rf_cslot.reserve(kRfCand * 2));
+    CU(c, cudaMemcpyAsync(c->rf_cslot.p, cslot.data(), cslot.size() * 2, cudaMemcpyHostToDevice, c->stream));
+    // 3. the pass, 4. ids and the proof
+    const size_t smem = (size_t(2) * kRfCandSlots + (size_t(1) << kRfSketchLog2) + nfolded) * 4 + (size_t(2) << kRfCandBucketsLog2);
+    CU(c, cudaFuncSetAttribute(rf_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    rf_count_kernel<<<c->num_sms, kRfCountThreads, smem, c->stream>>>(d_src, n, f, c->rf_ctags.as<uint32_t>(), c->rf_cdisp.as<uint16_t>(), mul,
+        uint32_t(nfolded), c->rf_ccount.as<unsigned long long>(), c->rf_sketch.as<unsigned long long>(), c->bins.as<unsigned long long>(), c->d_max());
+    rf_cand_rank_kernel<<<(uint32_t(cand.size()) * 32 + kRfThreads - 1) / kRfThreads, kRfThreads, 0, c->stream>>>(c->rf_ctags.as<uint32_t>(),
+        c->rf_ccount.as<unsigned long long>(), c->rf_cslot.as<uint16_t>(), uint32_t(cand.size()), K, f, uint32_t(nfolded), c->rf_most.as<uint32_t>(),
+        c->bins.as<unsigned long long>(), fs);
+    rf_verify_kernel<<<1, 1024, 0, c->stream>>>(c->rf_sketch.as<unsigned long long>(), K, fs);
+    c->stats.launches += 3;
+    CU(c, cudaGetLastError());
+    RfFast h_fs;
+    std::vector<uint32_t> most(K);
+    bins.resize(nfolded);
+    CU(c, cudaMemcpyAsync(&h_fs, fs, sizeof h_fs, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaMemcpyAsync(most.data(), c->rf_most.p, size_t(K) * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaMemcpyAsync(bins.data(), c->bins.p, nfolded * 8, cudaMemcpyDeviceToHost, c->stream));
+    RET(read_small(c));
+    *max_value = c->h_small()->max_value;
+    if (!h_fs.ok)
+        return B200ANS_OK; // a value outside the candidates could reach the K-th count (flat input, ties): not proven
+    if (uint64_t(*max_value) + K >= (1u << 30))
+        return c->fail(B200ANS_E_DOMAIN, "ANSrfold needs value + 2^(f+7) < 2^30");
+    c->most_frequent = std::move(most);
+    c->rfold_sigma = h_fs.n_valid; // (a lower bound: the fast route does not count the distinct values)
+    c->n_values = *max_value + 1;
+    CU(c, c->mapping.reserve(size_t(c->n_values) * 4));
+    const int grid = int(std::max<uint32_t>(1, std::min<uint32_t>((c->n_values + kRfThreads - 1) / kRfThreads, uint32_t(c->num_sms) * 8)));
+    rf_mapping_fill_kernel<<<grid, kRfThreads, 0, c->stream>>>(nullptr, K, c->n_values, c->mapping.as<uint32_t>());
+    rf_mapping_hot_kernel<<<(K + kRfThreads - 1) / kRfThreads, kRfThreads, 0, c->stream>>>(nullptr, K, c->rf_most.as<uint32_t>(), c->mapping.as<uint32_t>());
+    c->stats.launches += 2;
+    c->map_f = f;
+    c->have_mapping = true;
+    *done = true;
+    return B200ANS_OK;
+}
+
 // ans_X_encode::create (ans_fold.hpp:68-92, ans_int.hpp:38-68, ans_msb.hpp:77-101, ans_reorder_fold.hpp:70-130) with the
 // input on the device: histogram (K1) [-> all-reduce] -> host normalise -> encoder tables.  *empty: nothing to model
 // (every shard of the job is empty).
@@ -2165,6 +2281,17 @@ int model_from_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_
         // maximum (a second pass only when a value lies beyond the guess); selection of the 2^(f+7) most frequent
         // values, mapping[] and the folded histogram follow on the device from the raw bins (rfold_kernels.cuh).
         const uint32_t K = 1u << (f + 7);
+        bool rf_done = false;
+        {   // the fast route for large inputs whose folded alphabet fits shared memory (it proves its own exactness or
+            // declines); B200ANS_RF_FAST = 0 / 1 switches it off / forces it for any size
+            const int mode = env_int("B200ANS_RF_FAST", -1);
+            bool done = false;
+            if (!sharded && f <= 3 && n >= 4 && mode != 0 && (mode == 1 || n >= (size_t(1) << 24)))
+                RET(rfold_fast_model(c, f, d_src, n, bins, &max_value, &done));
+            c->rf_fast_used = done;
+            rf_done = done;
+        }
+        if (!rf_done) {
         size_t guess = std::max<size_t>(c->rf_guess, std::min<size_t>(size_t(1) << 24, std::max<size_t>(65536, size_t(next_power_of_two(uint64_t(n) * 4)))));
         for (int attempt = 0;; attempt++) {
             CU(c, c->rf_raw.reserve(guess * 8));
@@ -2219,6 +2346,7 @@ int model_from_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_
         c->n_values = max_value + 1;
         c->map_f = f;
         c->have_mapping = true;
+        }
     } else {
         RET(histogram_to_host(c, method, f, d_src, n, alphabet_bins(method, f, 0), bins, &max_value, sharded));
         if (max_value >= (1u << 30)) // the decoder keeps the byte count in bits 30-31 (ans_fold.hpp:198-200)

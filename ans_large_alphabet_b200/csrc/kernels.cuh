@@ -23,8 +23,8 @@ namespace b200ans {
 
 // Encoder entry, one per (mapped) symbol.  Replaces enc_entry_fold/_int/_msb/_reorder_fold
 // {freq, base, sym_upper_bound} (ans_fold.hpp:30-34 ...): the upper bound is recomputed as
-// freq << 36, and `rcp` is a reciprocal rounded towards zero far enough that
-// trunc(double(state) * rcp) is floor(state / freq) or one less (fixed up exactly).
+// freq << 36, and `rcp` is the smallest double >= 1 / freq (b200ans.cu reciprocal_up): ans_push52 (lpb_kernels.cuh)
+// gets floor(state / freq) exactly from one DFMA.RZ with it; ans_push below multiplies towards zero and fixes up.
 struct __align__(16) EncEntry {
     uint32_t freq;
     uint32_t base;

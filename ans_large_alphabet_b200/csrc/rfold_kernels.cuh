@@ -286,14 +286,14 @@ __global__ void __launch_bounds__(kRfThreads) rf_rank_kernel(const RfState* __re
 __global__ void __launch_bounds__(kRfThreads) rf_mapping_fill_kernel(const RfState* __restrict__ st, uint32_t K, uint32_t nvalues,
     uint32_t* __restrict__ mapping)
 {
-    const uint32_t bias = st->reorder ? K : 0u;
+    const uint32_t bias = (!st || st->reorder) ? K : 0u; // (no state: the caller knows that the model reorders)
     for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < nvalues; v += gridDim.x * blockDim.x)
         mapping[v] = v + bias;
 }
 __global__ void __launch_bounds__(kRfThreads) rf_mapping_hot_kernel(const RfState* __restrict__ st, uint32_t K,
     const uint32_t* __restrict__ most_frequent, uint32_t* __restrict__ mapping)
 {
-    if (!st->reorder)
+    if (st && !st->reorder)
         return;
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r < K)
@@ -351,6 +351,217 @@ __global__ void __launch_bounds__(kRfThreads) rf_fold_bins_kernel(const unsigned
         for (uint32_t i = threadIdx.x; i < nbins; i += blockDim.x)
             if (s_fold[i])
                 atomicAdd(bins + i, s_fold[i]);
+    }
+}
+
+
+// ==========================================================================================
+// The fast route: exact selection WITHOUT counting every value
+// ==========================================================================================
+// The raw histogram costs one global atomic per cold symbol (440 M of them for config 3: 3.3 ms at the L2's atomic
+// rate, and 48 ms when the hot values do not sit in the privatised head).  But the model needs exact counts only for
+// values that can be among the K most frequent, and of everything else only the folded histogram of v + K.  So:
+//   1. rf_sample_kernel      : 2^19 symbols at a stride -> their exact counts in an open-addressing table keyed by value
+//   2. (radix select above)  : the kRfCand most frequent values of the sample = the candidates; the host builds their
+//                              perfect hash
+//   3. rf_count_kernel       : ONE pass over the input, everything in shared memory: a candidate -> its exact counter;
+//                              any other value -> a hashed counter of the sketch (an upper bound for every value that
+//                              falls into it) and the folded bin of v + K
+//   4. rf_cand_rank_kernel   : the candidates ranked by (-count, value): ids, most_frequent[], their folded bins
+//      rf_verify_kernel      : T = the K-th largest candidate count.  If every sketch counter is below T, no value
+//                              outside the candidates can reach T -- the selection is the reference's, exactly;
+//                              otherwise (or with fewer than K candidates) the caller falls back to the raw histogram.
+constexpr uint32_t kRfCand = 4096;          // candidates at most
+constexpr uint32_t kRfCandSlots = 8192;     // slots of their perfect hash (load <= 1/2: the host finds it at once)
+constexpr uint32_t kRfCandBucketsLog2 = 11; // displacement buckets of that hash
+constexpr uint32_t kRfSampleBucketsLog2 = 20; // slots of the sample's table (2^19 symbols at most: load <= 1/2)
+constexpr uint32_t kRfSketchLog2 = 15;      // sketch counters per CTA (128 KiB: with the candidates and the folded bins it fills the SM)
+constexpr uint32_t kRfSampleMul = 0x9E3779B1u, kRfSketchMul = 0x85EBCA6Bu;
+constexpr int kRfCountThreads = 1024;
+
+struct RfFast {
+    unsigned long long t_count;   // T: count of the candidate with id K - 1
+    unsigned int n_valid;         // candidates with a non-zero exact count
+    unsigned int max_sketch_hi;   // (unused)
+    unsigned long long max_sketch; // largest sketch counter
+    unsigned int ok;              // 1: the selection is exact
+    unsigned int n_cand;          // candidates collected
+};
+
+__global__ void __launch_bounds__(256) rf_sample_kernel(const uint32_t* __restrict__ in, uint64_t n, uint32_t n_sample_vec,
+    unsigned long long* __restrict__ buckets /* counts, zeroed */, uint32_t* __restrict__ tags /* keys, 0xFFFFFFFF = empty */)
+{
+    const uint64_t n4 = n >> 2;
+    const uint4* in4 = reinterpret_cast<const uint4*>(in);
+    constexpr uint32_t kMask = (1u << kRfSampleBucketsLog2) - 1u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_sample_vec; i += gridDim.x * blockDim.x) {
+        const uint64_t at = (uint64_t(i) * n4) / n_sample_vec;
+        const uint4 q = __ldg(in4 + at);
+        const uint32_t v[4] = { q.x, q.y, q.z, q.w };
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (v[j] == 0xFFFFFFFFu)
+                continue; // (outside every coder's domain; the pass over the input reports it)
+            uint32_t b = (v[j] * kRfSampleMul) >> (32u - kRfSampleBucketsLog2);
+            for (;;) { // linear probing; the table is at most half full
+                const uint32_t old = atomicCAS(tags + b, 0xFFFFFFFFu, v[j]);
+                if (old == 0xFFFFFFFFu || old == v[j])
+                    break;
+                b = (b + 1u) & kMask;
+            }
+            atomicAdd(buckets + b, 1ull);
+        }
+    }
+}
+
+// candidates = the values whose sample count is > T, then those with count == T (T > 0) while there is room
+__global__ void __launch_bounds__(256) rf_cand_collect_kernel(const unsigned long long* __restrict__ buckets, const uint32_t* __restrict__ tags,
+    const RfState* __restrict__ st, bool ties, RfFast* __restrict__ fs, uint32_t* __restrict__ cand)
+{
+    const unsigned long long T = st->prefix;
+    for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < (1u << kRfSampleBucketsLog2); b += gridDim.x * blockDim.x) {
+        const unsigned long long c = buckets[b];
+        if (ties ? (c == T && T != 0ull) : (c > T)) {
+            const unsigned int at = atomicAdd(&fs->n_cand, 1u);
+            if (at < kRfCand)
+                cand[at] = tags[b];
+        }
+    }
+}
+
+// the one pass over the input (see above).  cand_tags / cand_disp: perfect hash of the candidates (host-built).
+__global__ void __launch_bounds__(kRfCountThreads, 1) rf_count_kernel(const uint32_t* __restrict__ in, uint64_t n, uint32_t f,
+    const uint32_t* __restrict__ cand_tags, const uint16_t* __restrict__ cand_disp, uint32_t mul, uint32_t nfolded,
+    unsigned long long* __restrict__ cand_count, unsigned long long* __restrict__ sketch, unsigned long long* __restrict__ bins,
+    uint32_t* __restrict__ max_value)
+{
+    extern __shared__ uint32_t s_rf[];
+    uint32_t* s_tags = s_rf;                                   // kRfCandSlots
+    uint32_t* s_cnt = s_tags + kRfCandSlots;                   // kRfCandSlots
+    uint32_t* s_sketch = s_cnt + kRfCandSlots;                 // 2^kRfSketchLog2
+    uint32_t* s_fold = s_sketch + (1u << kRfSketchLog2);       // nfolded
+    uint16_t* s_disp = reinterpret_cast<uint16_t*>(s_fold + nfolded); // 2^kRfCandBucketsLog2
+    for (uint32_t i = threadIdx.x; i < kRfCandSlots; i += blockDim.x) {
+        s_tags[i] = __ldg(cand_tags + i);
+        s_cnt[i] = 0u;
+    }
+    for (uint32_t i = threadIdx.x; i < (1u << kRfSketchLog2); i += blockDim.x)
+        s_sketch[i] = 0u;
+    for (uint32_t i = threadIdx.x; i < nfolded; i += blockDim.x)
+        s_fold[i] = 0u;
+    for (uint32_t i = threadIdx.x; i < (1u << kRfCandBucketsLog2); i += blockDim.x)
+        s_disp[i] = __ldg(cand_disp + i);
+    __syncthreads();
+    const uint32_t a_tags = uint32_t(__cvta_generic_to_shared(s_tags)), a_cnt = uint32_t(__cvta_generic_to_shared(s_cnt));
+    const uint32_t a_sketch = uint32_t(__cvta_generic_to_shared(s_sketch)), a_fold = uint32_t(__cvta_generic_to_shared(s_fold));
+    const uint32_t K = 1u << (f + 7u);
+    uint32_t local_max = 0;
+    auto count = [&](uint32_t v) {
+        const uint32_t h = v * mul;
+        const uint32_t d = s_disp[h >> (32u - kRfCandBucketsLog2)];
+        const uint32_t s = (h + d) & (kRfCandSlots - 1u);
+        local_max = max(local_max, v);
+        if (s_tags[s] == v) {
+            red_shared_inc(a_cnt + (s << 2));
+        } else {
+            red_shared_inc(a_sketch + (((v * kRfSketchMul) >> (32u - kRfSketchLog2)) << 2));
+            uint32_t k;
+            const uint32_t bin = fold_map(v + K, f, k);
+            if (bin < nfolded)
+                red_shared_inc(a_fold + (bin << 2));
+        }
+        (void)a_tags;
+    };
+    const uint64_t n4 = n >> 2;
+    const uint4* in4 = reinterpret_cast<const uint4*>(in);
+    // a CTA's counters are 32 bits wide: it takes at most 2^32 - 1 symbols (the host sizes the grid accordingly)
+    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+    uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    for (; i + stride < n4; i += 2 * stride) {
+        const uint4 q0 = __ldcs(in4 + i);
+        const uint4 q1 = __ldcs(in4 + i + stride);
+        count(q0.x), count(q0.y), count(q0.z), count(q0.w);
+        count(q1.x), count(q1.y), count(q1.z), count(q1.w);
+    }
+    if (i < n4) {
+        const uint4 q0 = __ldcs(in4 + i);
+        count(q0.x), count(q0.y), count(q0.z), count(q0.w);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < 3) {
+        const uint64_t t = (n4 << 2) + threadIdx.x;
+        if (t < n)
+            count(in[t]);
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        local_max = max(local_max, __shfl_xor_sync(0xffffffffu, local_max, o));
+    if ((threadIdx.x & 31) == 0 && local_max != 0)
+        atomicMax(max_value, local_max);
+    __syncthreads();
+    for (uint32_t j = threadIdx.x; j < kRfCandSlots; j += blockDim.x)
+        if (s_cnt[j])
+            atomicAdd(cand_count + j, (unsigned long long)s_cnt[j]);
+    for (uint32_t j = threadIdx.x; j < (1u << kRfSketchLog2); j += blockDim.x)
+        if (s_sketch[j])
+            atomicAdd(sketch + j, (unsigned long long)s_sketch[j]);
+    for (uint32_t j = threadIdx.x; j < nfolded; j += blockDim.x)
+        if (s_fold[j])
+            atomicAdd(bins + j, (unsigned long long)s_fold[j]);
+}
+
+// candidates (candidate i sits in slot cand_slot[i]: value tags[slot], exact count cand_count[slot]) ranked by
+// (-count, value), one warp per candidate: the first K get the ids
+__global__ void __launch_bounds__(kRfThreads) rf_cand_rank_kernel(const uint32_t* __restrict__ tags, const unsigned long long* __restrict__ cand_count,
+    const uint16_t* __restrict__ cand_slot, uint32_t n_cand, uint32_t K, uint32_t f, uint32_t nfolded, uint32_t* __restrict__ most_frequent,
+    unsigned long long* __restrict__ bins, RfFast* __restrict__ fs)
+{
+    const uint32_t i = (blockIdx.x * kRfThreads + threadIdx.x) >> 5;
+    if (i >= n_cand)
+        return;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t si = cand_slot[i];
+    const uint32_t vi = tags[si];
+    const unsigned long long ci = cand_count[si];
+    uint32_t rank = 0;
+    for (uint32_t j = lane; j < n_cand; j += 32u) {
+        const uint32_t sj = cand_slot[j];
+        const unsigned long long cj = cand_count[sj];
+        rank += (cj > ci) || (cj == ci && tags[sj] < vi);
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        rank += __shfl_xor_sync(0xffffffffu, rank, o);
+    if (lane != 0 || ci == 0ull)
+        return; // (candidates that never occur rank behind every one that does: they take no id)
+    atomicAdd(&fs->n_valid, 1u);
+    if (rank < K) {
+        most_frequent[rank] = vi;
+        atomicAdd(bins + rank, ci); // fold(id) = id below the threshold
+        if (rank == K - 1u)
+            fs->t_count = ci;
+    } else {
+        uint32_t k;
+        const uint32_t bin = fold_map(vi + K, f, k);
+        if (bin < nfolded)
+            atomicAdd(bins + bin, ci);
+    }
+}
+
+__global__ void __launch_bounds__(1024) rf_verify_kernel(const unsigned long long* __restrict__ sketch, uint32_t K, RfFast* __restrict__ fs)
+{
+    __shared__ unsigned long long s_max[32];
+    unsigned long long m = 0;
+    for (uint32_t j = threadIdx.x; j < (1u << kRfSketchLog2); j += blockDim.x)
+        m = max(m, sketch[j]);
+    for (int o = 16; o > 0; o >>= 1)
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0)
+        s_max[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 32; w++)
+            m = max(m, s_max[w]);
+        fs->max_sketch = m;
+        // strictly below T: a value outside the candidates with count == T could win a tie on the value
+        fs->ok = (fs->n_valid >= K && fs->t_count != 0ull && m < fs->t_count) ? 1u : 0u;
     }
 }
 

@@ -100,6 +100,10 @@ typedef struct b200ans_stats {
  * (a tiny frame, more bits per symbol), from 2^32 on the frame grows until a frequency nears 16 bits (2^18 .. 2^19
  * slots).  b200ans reproduces this bit for bit (the frame is part of the stream format); the flag tells the caller. */
 #define B200ANS_MODEL_INT_ACCUMULATOR_QUIRK 1u
+/* ANSrfold: the value reordering came from the fast route -- a sample proposes candidates, ONE pass counts them exactly
+ * and bounds every other value, and the route only answers when that bound proves the selection exact (otherwise the
+ * raw histogram of the whole value range decides, as in ans_reorder_fold.hpp:75-106).  Same model either way. */
+#define B200ANS_MODEL_RFOLD_FAST 2u
 
 /* What a container says about itself (the reference stores neither n nor the byte count, methods.hpp:541-546). */
 typedef struct b200ans_container {

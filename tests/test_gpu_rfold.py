@@ -22,12 +22,12 @@ def scattered_zipf(n, log2_alphabet, seed):
     return ((r * np.uint64(0x9E3779B1)) & np.uint64((1 << log2_alphabet) - 1)).astype(np.uint32)
 
 
-def ties_at_the_boundary(f, seed):
+def ties_at_the_boundary(f, seed, tie_mult=3):
     """far more values share the K-th largest count than fit: the K selected ones must be the smallest values"""
     K = 1 << (f + 7)
     rng = np.random.default_rng(seed)
     hot = rng.permutation(5 * K)[: K // 2].astype(np.uint32) + 7      # K/2 values, 9 times each
-    tie = (rng.permutation(40 * K)[: 3 * K].astype(np.uint32) + 5 * K + 7)  # 3K values, 4 times each: K/2 of them get in
+    tie = (rng.permutation(40 * K)[: tie_mult * K].astype(np.uint32) + 5 * K + 7)  # 3K values, 4 times each: K/2 of them get in
     cold = np.arange(50 * K, 50 * K + 4 * K, dtype=np.uint32)           # once each
     data = np.concatenate([np.repeat(hot, 9), np.repeat(tie, 4), cold])
     rng.shuffle(data)
@@ -140,3 +140,36 @@ def test_identity_mapping_and_its_domain(codec):
     with pytest.raises(P.B200AnsError) as e:
         codec.compress(M_RFOLD, 1, data)
     assert e.value.code == -4
+
+
+@pytest.mark.parametrize("f,kind,n,expect_fast", [
+    (2, "scattered", 3_000_017, True), (1, "scattered", 1_500_001, True), (2, "zipf20", 2_000_003, True), (3, "scattered", 6_000_011, True),
+    (2, "ties", 0, True),        # every value is a candidate (3840 distinct): exact counts, ties by value
+    (2, "ties30", 0, False),     # 15 360 values share the K-th count: the bound cannot prove the selection
+    (2, "flat", 400_000, False),  # uniform values: no candidate stands out
+])
+def test_fast_route_is_exact_or_declines(codec, monkeypatch, f, kind, n, expect_fast):
+    """B200ANS_MODEL_RFOLD_FAST: candidates from a sample, one pass with exact candidate counts and a hashed upper bound
+    for everything else; the route answers only when the bound proves the selection -- the container must equal the one
+    the raw histogram gives, byte for byte, either way"""
+    if kind == "scattered":
+        data = scattered_zipf(n, 22, seed=9)
+    elif kind == "ties":
+        data = ties_at_the_boundary(f, 7)
+    elif kind == "ties30":
+        data = ties_at_the_boundary(f, 7, tie_mult=30)
+    elif kind == "flat":
+        data = np.random.default_rng(4).integers(0, 1 << 16, n, dtype=np.uint32)
+    else:
+        data = _inputs.make(kind, n, seed=9)
+    codec.set_block_syms(8192)
+    monkeypatch.setenv("B200ANS_RF_FAST", "0")
+    want = codec.compress(M_RFOLD, f, data).copy()
+    assert codec.stats().model_flags & 2 == 0
+    monkeypatch.setenv("B200ANS_RF_FAST", "1")
+    got = codec.compress(M_RFOLD, f, data).copy()
+    assert bool(codec.stats().model_flags & 2) == expect_fast
+    assert np.array_equal(got, want)
+    assert np.array_equal(codec.decompress(M_RFOLD, f, got, data.size), data)
+    ref_pre = cpu().model_create(M_RFOLD, f, data).serialize()
+    assert _container.prelude_equal(_container.parse(got)["prelude"], ref_pre)
