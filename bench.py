@@ -481,9 +481,11 @@ def run_ours(args, wl):
     codec = P.Codec(device=local, block_syms=args.block_syms or 8192, stream=stream.cuda_stream)
     if not args.block_syms:
         # the container's own parameter: blocks that fill whole rounds of the lane-per-block coders on this GPU
-        args.block_syms = codec.suggest_block_syms(n, 8192, 16384)
+        # (from 6144 up: a 2^29-symbol shard -- the 2^32-symbol job on eight GPUs -- is exactly one round of 7168-symbol
+        # blocks, where 8192 would leave a seventh of the warps without work)
+        args.block_syms = codec.suggest_block_syms(n, 6144, 16384)
         codec.set_block_syms(args.block_syms)
-        block_rule = "b200ans_suggest_block_syms(n, 8192, 16384)"
+        block_rule = "b200ans_suggest_block_syms(n, 6144, 16384)"
     else:
         block_rule = "fixed"
     pa = PA_MODEL_SYMS.get(args.workload, 0)
