@@ -73,6 +73,11 @@ SIGNATURES = {
     "b200ans_model_create": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u32p, C.c_size_t]),
     "b200ans_model_create_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t]),
     "b200ans_model_most_frequent": (C.c_int, [C.c_void_p, u32p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_uint64)]),
+    "b200ans_byte_compress": (C.c_int, [C.c_void_p, u8p, C.c_size_t, u8p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "b200ans_byte_decompress": (C.c_int, [C.c_void_p, u8p, C.c_size_t, u8p, C.c_size_t]),
+    "b200ans_byte_compress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "b200ans_byte_decompress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "b200ans_byte_adjust_freqs": (C.c_int, [u64p, C.POINTER(C.c_uint16)]),
     "b200ans_rfold_prepare_device": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_model_build": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u64p, C.c_size_t]),
     "b200ans_model_prelude": (C.c_int, [C.c_void_p, u8p, C.c_size_t, szp]),
@@ -168,6 +173,15 @@ class _HostApi:
         rc = self.lib.b200ans_adjust_freqs(_p(freqs, u64p), freqs.size, largest_sym, int(require_u16), h_approx, _p(out, u32p))
         if rc:
             raise B200AnsError(rc, "adjust_freqs")
+        return out
+
+    def byte_adjust_freqs(self, freqs):
+        freqs = np.ascontiguousarray(freqs, dtype=np.uint64)
+        assert freqs.size == 256
+        out = np.zeros(256, dtype=np.uint16)
+        rc = self.lib.b200ans_byte_adjust_freqs(_p(freqs, u64p), out.ctypes.data_as(C.POINTER(C.c_uint16)))
+        if rc:
+            raise B200AnsError(rc, "byte_adjust_freqs")
         return out
 
     def scale_freqs(self, freqs, mapping, frame, freq_sum=None):
@@ -417,6 +431,19 @@ class Codec:
 
     def rfold_prepare_device(self, f, d_raw_bins, nvalues, d_folded_bins):
         self._check(self.lib.b200ans_rfold_prepare_device(self.h, f, d_raw_bins, nvalues, d_folded_bins))
+
+    def byte_compress(self, data):
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        out = np.zeros(self.bound(4, data.size), dtype=np.uint8)
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_byte_compress(self.h, _p(out, u8p), out.size, _p(data, u8p), data.size, C.byref(nb)))
+        return out[: nb.value]
+
+    def byte_decompress(self, blob, n):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        out = np.zeros(n, dtype=np.uint8)
+        self._check(self.lib.b200ans_byte_decompress(self.h, _p(out, u8p), n, _p(blob, u8p), blob.size))
+        return out
 
     def model_create(self, method, f, data):
         data = np.ascontiguousarray(data, dtype=np.uint32)

@@ -162,7 +162,7 @@ struct b200ans_ctx {
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, pa_nfreqs, pa_pre, pa_keys;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, io_bytes, pa_nfreqs, pa_pre, pa_keys;
     // ANSrfold on the device (rfold_kernels.cuh): raw histogram, selection state, candidates, hash of the hot values
     DevBuf rf_sbuckets, rf_stags, rf_fast, rf_cand, rf_ctags, rf_cdisp, rf_cslot, rf_ccount, rf_sketch; // the fast route (rfold_kernels.cuh)
     DevBuf rf_raw, rf_raw32, rf_state, rf_hist, rf_tiles, rf_cand_count, rf_cand_value, rf_most, rf_tags, rf_disp, enc_table_rf;
@@ -260,7 +260,7 @@ namespace {
 
 bool valid_method(int method, uint32_t f)
 {
-    if (method == METHOD_INT || method == METHOD_MSB)
+    if (method == METHOD_INT || method == METHOD_MSB || method == METHOD_BYTE)
         return true;
     if (method == METHOD_FOLD || method == METHOD_RFOLD)
         return f >= 1 && f <= 8;
@@ -271,6 +271,7 @@ size_t alphabet_bins(int method, uint32_t f, uint32_t max_value)
 {
     switch (method) {
     case METHOD_INT: return size_t(max_value) + 1;
+    case METHOD_BYTE: return kByteSigma;
     case METHOD_MSB: return kMsbMaxSigma;
     default: return size_t(1) << (f + 9);
     }
@@ -279,7 +280,7 @@ size_t alphabet_bins(int method, uint32_t f, uint32_t max_value)
 // worst-case payload bytes of one block (+32 so whole-sector stores never leave the slot); slots are 32-byte aligned
 size_t block_stride(int method, size_t block_syms)
 {
-    const size_t per_sym = (method == METHOD_INT) ? 4 : 7;
+    const size_t per_sym = (coder_of(method) == METHOD_INT) ? 4 : 7;
     return align_up(per_sym * block_syms + 32, 32) + 32;
 }
 
@@ -367,7 +368,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys,
+             &c->dec_slots, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->io_bytes, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys,
              &c->rf_sbuckets, &c->rf_stags, &c->rf_fast, &c->rf_cand, &c->rf_ctags, &c->rf_cdisp, &c->rf_cslot, &c->rf_ccount, &c->rf_sketch,
              &c->rf_raw, &c->rf_raw32, &c->rf_state, &c->rf_hist, &c->rf_tiles, &c->rf_cand_count, &c->rf_cand_value, &c->rf_most, &c->rf_tags, &c->rf_disp,
              &c->enc_table_rf })
@@ -456,7 +457,7 @@ try {
         return B200ANS_E_FORMAT;
     Header h;
     std::memcpy(&h, src, sizeof h);
-    if (h.magic != B200ANS_MAGIC || h.version != 1 || h.method > METHOD_RFOLD)
+    if (h.magic != B200ANS_MAGIC || h.version != 1 || h.method > METHOD_BYTE)
         return B200ANS_E_FORMAT;
     out->method = h.method;
     out->fidelity = h.fidelity;
@@ -518,6 +519,7 @@ extern "C" const char* b200ans_method_name(int method, uint32_t fidelity, char* 
         return "";
     switch (method) {
     case METHOD_INT: snprintf(buf, buflen, "ANS"); break;
+    case METHOD_BYTE: snprintf(buf, buflen, "ANSbyte"); break;
     case METHOD_MSB: snprintf(buf, buflen, "ANSmsb"); break;
     case METHOD_FOLD: snprintf(buf, buflen, "ANSfold-%u", fidelity); break;
     case METHOD_RFOLD: snprintf(buf, buflen, "ANSrfold-%u", fidelity); break;
@@ -529,7 +531,7 @@ extern "C" const char* b200ans_method_name(int method, uint32_t fidelity, char* 
 extern "C" size_t b200ans_compress_bound(const b200ans_ctx* c, int method, size_t n)
 {
     const uint32_t bs = c ? c->block_syms : B200ANS_DEFAULT_BLOCK_SYMS;
-    const size_t per_sym = (method == METHOD_INT) ? 4 : 7;
+    const size_t per_sym = (coder_of(method) == METHOD_INT) ? 4 : 7;
     const size_t n_blocks = bs ? (n + bs - 1) / bs : 1;
     // header + prelude (worst case ~ 5 bytes per distinct symbol, bounded by n and 2^30) + table + payloads
     const size_t prelude = 4096 + 8 * std::min<size_t>(n, size_t(1) << 26) + (size_t(4) << 12);
@@ -708,7 +710,8 @@ int histogram_dispatch(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d
     if (nbins == 0 || nbins > (size_t(1) << 31))
         return c->fail(B200ANS_E_ARG, "histogram: bad bin count");
     switch (method) {
-    case METHOD_INT: return launch_histogram<METHOD_INT>(c, f, d_src, n, d_bins, nbins, d_max);
+    case METHOD_INT:
+    case METHOD_BYTE: return launch_histogram<METHOD_INT>(c, f, d_src, n, d_bins, nbins, d_max);
     case METHOD_FOLD: return launch_histogram<METHOD_FOLD>(c, f, d_src, n, d_bins, nbins, d_max);
     case METHOD_MSB: return launch_histogram<METHOD_MSB>(c, f, d_src, n, d_bins, nbins, d_max);
     case METHOD_RFOLD:
@@ -1018,7 +1021,15 @@ try {
     if (method == METHOD_INT && sigma < 2)
         return c->fail(B200ANS_E_DOMAIN,
             "plain ANS needs at least two distinct symbols (the reference's adjust_freqs never terminates otherwise)");
-    c->nfreqs = adjust_freqs(freqs, max_sym, method != METHOD_INT, c->h_approx);
+    if (method == METHOD_BYTE) { // ans_byte.hpp:99-120: all 256 entries, its own normaliser
+        if (nbins > kByteSigma)
+            return c->fail(B200ANS_E_ARG, "model_build(BYTE): at most 256 bins");
+        freqs.resize(kByteSigma, 0);
+        const std::array<uint16_t, 256> nf = byte_adjust_freqs(freqs.data());
+        c->nfreqs.assign(nf.begin(), nf.end());
+    } else {
+        c->nfreqs = adjust_freqs(freqs, max_sym, method != METHOD_INT, c->h_approx);
+    }
     uint64_t frame = 0;
     for (uint32_t v : c->nfreqs)
         frame += v;
@@ -1039,7 +1050,15 @@ try {
             p += 4 * c->most_frequent.size();
         }
     }
-    ans_serialize_interp(c->nfreqs, size_t(frame), p);
+    if (method == METHOD_BYTE) { // ans_byte.hpp:122-137: interp code of the running sums of (nfreq + 1), no header
+        uint32_t inc[kByteSigma];
+        inc[0] = c->nfreqs[0];
+        for (uint32_t sym = 1; sym < kByteSigma; sym++)
+            inc[sym] = inc[sym - 1] + c->nfreqs[sym] + 1;
+        p += interp_encode(p, inc, kByteSigma, kByteMaxFrame + kByteSigma);
+    } else {
+        ans_serialize_interp(c->nfreqs, size_t(frame), p);
+    }
     c->prelude.resize(size_t(p - c->prelude.data()));
 
     // encoder table: {freq, base = exclusive prefix sum, smallest double >= 1/freq}
@@ -1194,7 +1213,22 @@ try {
                                               : (method == METHOD_MSB ? size_t(kMsbMaxSigma) : (size_t(1) << (f + 9)));
     size_t used = 0;
     std::vector<uint32_t> nfreqs;
-    if (!ans_load_interp_checked(p, end, limit, 28u, nfreqs, &used))
+    if (method == METHOD_BYTE) { // ans_byte_decode::load (ans_byte.hpp:178-190), bounded
+        nfreqs.assign(kByteSigma, 0u);
+        detail::word_unpacker r(p, end);
+        detail::interp_get(r, nfreqs.data(), kByteSigma, 1, uint64_t(kByteMaxFrame + kByteSigma) + 1);
+        if (r.overrun())
+            return c->fail(B200ANS_E_FORMAT, "model_load: prelude cut off");
+        uint32_t below = nfreqs[0];
+        for (uint32_t sym = 1; sym < kByteSigma; sym++) {
+            const uint32_t here = nfreqs[sym];
+            if (here <= below)
+                return c->fail(B200ANS_E_FORMAT, "model_load: byte model's running sums do not climb");
+            nfreqs[sym] = here - below - 1;
+            below = here;
+        }
+        used = r.words() * sizeof(uint32_t);
+    } else if (!ans_load_interp_checked(p, end, limit, 28u, nfreqs, &used))
         return c->fail(B200ANS_E_FORMAT, "model_load: prelude cut off, or its header is implausible for this method");
     const size_t total_used = size_t(p - prelude) + used;
     if (consumed)
@@ -1202,7 +1236,7 @@ try {
     uint64_t frame = 0;
     for (uint32_t v : nfreqs)
         frame += v;
-    if (!is_power_of_two(frame) || frame > (uint64_t(1) << 28))
+    if (!is_power_of_two(frame) || frame > (uint64_t(1) << 28) || (method == METHOD_BYTE && frame > kByteMaxFrame))
         return c->fail(B200ANS_E_FORMAT, "model_load: frequencies do not sum to a power of two");
     const uint32_t lg = uint32_t(63 - __builtin_clzll(frame));
 
@@ -1247,7 +1281,7 @@ try {
         return B200ANS_OK;
     };
     c->dec_fold_rank = false;
-    if (method == METHOD_INT) {
+    if (coder_of(method) == METHOD_INT) {
         RET(upload_rank([](uint32_t s) { return s; }));
         c->dec_dense = c->dec_n_present == nfreqs.size() ? 1u : 0u;
     } else {
@@ -1591,7 +1625,7 @@ int launch_encode(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t bloc
     CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
     if (use_lpb(c, n_blocks, true)) {
         int rc3 = 1;
-        switch (c->enc_method) {
+        switch (coder_of(c->enc_method)) {
         case METHOD_INT: rc3 = launch_lpb3_encode_t<METHOD_INT>(c, a); break;
         case METHOD_FOLD: rc3 = launch_lpb3_encode_t<METHOD_FOLD>(c, a); break;
         case METHOD_MSB: rc3 = launch_lpb3_encode_t<METHOD_MSB>(c, a); break;
@@ -1600,14 +1634,14 @@ int launch_encode(b200ans_ctx* c, const uint32_t* d_src, size_t n, uint32_t bloc
         }
         if (rc3 <= 0)
             return rc3;
-        switch (c->enc_method) {
+        switch (coder_of(c->enc_method)) {
         case METHOD_INT: return launch_lpb_encode_t<METHOD_INT>(c, a);
         case METHOD_FOLD: return launch_lpb_encode_t<METHOD_FOLD>(c, a);
         case METHOD_MSB: return launch_lpb_encode_t<METHOD_MSB>(c, a);
         case METHOD_RFOLD: return launch_lpb_encode_t<METHOD_RFOLD>(c, a);
         }
     }
-    switch (c->enc_method) {
+    switch (coder_of(c->enc_method)) {
     case METHOD_INT: return launch_encode_t<METHOD_INT>(c, a);
     case METHOD_FOLD: return launch_encode_t<METHOD_FOLD>(c, a);
     case METHOD_MSB: return launch_encode_t<METHOD_MSB>(c, a);
@@ -1667,7 +1701,7 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     const size_t frame = size_t(1) << c->dec_log2_frame;
     if (use_lpb(c, n_blocks, false)) {
         const size_t lbudget = c->max_smem > size_t(16) * kLpbDecWarpBytes + 4096 ? c->max_smem - size_t(16) * kLpbDecWarpBytes - 4096 : 0;
-        if (c->dec_method == METHOD_INT) {
+        if (coder_of(c->dec_method) == METHOD_INT) {
             const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_dense);
             if (tb <= std::min<size_t>(lbudget, size_t(100) << 10))
                 return use_pure_records(c, a) ? launch_lpb3_decode_pure<METHOD_INT>(c, a, tb) : launch_lpb_decode_tt<METHOD_INT, DEC_INT_SMEM>(c, a, tb);
@@ -1681,19 +1715,19 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
             if (rb <= room && !env_int("B200ANS_RANK_GLOBAL", 0)) {
                 if (c->dec_method == METHOD_FOLD && use_pure_records(c, a))
                     return launch_lpb3_decode_pure<METHOD_FOLD>(c, a, rb);
-                switch (c->dec_method) {
+                switch (coder_of(c->dec_method)) {
                 case METHOD_FOLD: return launch_lpb_decode_tt<METHOD_FOLD, DEC_INT_SMEM>(c, a, rb);
                 case METHOD_MSB: return launch_lpb_decode_tt<METHOD_MSB, DEC_INT_SMEM>(c, a, rb);
                 case METHOD_RFOLD: return launch_lpb_decode_tt<METHOD_RFOLD, DEC_INT_SMEM>(c, a, rb);
                 }
             }
-            switch (c->dec_method) {
+            switch (coder_of(c->dec_method)) {
             case METHOD_FOLD: return launch_lpb_decode_tt<METHOD_FOLD, DEC_INT_GLOBAL>(c, a, 0);
             case METHOD_MSB: return launch_lpb_decode_tt<METHOD_MSB, DEC_INT_GLOBAL>(c, a, 0);
             case METHOD_RFOLD: return launch_lpb_decode_tt<METHOD_RFOLD, DEC_INT_GLOBAL>(c, a, 0);
             }
         }
-        switch (c->dec_method) {
+        switch (coder_of(c->dec_method)) {
         case METHOD_FOLD:
             return smem ? launch_lpb_decode_tt<METHOD_FOLD, DEC_FOLD_SMEM>(c, a, tb)
                         : launch_lpb_decode_tt<METHOD_FOLD, DEC_FOLD_GLOBAL>(c, a, 0);
@@ -1708,7 +1742,7 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     }
     const size_t rows = size_t(kDecWarps) * 8 * kDecRowBytes;
     const size_t budget = c->max_smem > rows + 1024 ? c->max_smem - rows - 1024 : 0;
-    if (c->dec_method == METHOD_INT) {
+    if (coder_of(c->dec_method) == METHOD_INT) {
         const size_t tb = DecTables<METHOD_INT, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, c->dec_dense);
         const bool words = c->dec_words_aligned && (reinterpret_cast<uintptr_t>(d_payload) & 3) == 0 && !env_int("B200ANS_NO_INTDEC", 0);
         if (tb <= std::min<size_t>(budget, size_t(100) << 10))
@@ -1720,19 +1754,19 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
     if (c->dec_fold_rank) {
         const size_t rb = DecTables<METHOD_FOLD, DEC_INT_SMEM>::smem_bytes(uint32_t(frame), c->dec_n_present, 0);
         if (rb <= budget && !env_int("B200ANS_RANK_GLOBAL", 0)) {
-            switch (c->dec_method) {
+            switch (coder_of(c->dec_method)) {
             case METHOD_FOLD: return launch_decode_tt<METHOD_FOLD, DEC_INT_SMEM>(c, a, rb);
             case METHOD_MSB: return launch_decode_tt<METHOD_MSB, DEC_INT_SMEM>(c, a, rb);
             case METHOD_RFOLD: return launch_decode_tt<METHOD_RFOLD, DEC_INT_SMEM>(c, a, rb);
             }
         }
-        switch (c->dec_method) {
+        switch (coder_of(c->dec_method)) {
         case METHOD_FOLD: return launch_decode_tt<METHOD_FOLD, DEC_INT_GLOBAL>(c, a, 0);
         case METHOD_MSB: return launch_decode_tt<METHOD_MSB, DEC_INT_GLOBAL>(c, a, 0);
         case METHOD_RFOLD: return launch_decode_tt<METHOD_RFOLD, DEC_INT_GLOBAL>(c, a, 0);
         }
     }
-    switch (c->dec_method) {
+    switch (coder_of(c->dec_method)) {
     case METHOD_FOLD:
         return smem ? launch_decode_tt<METHOD_FOLD, DEC_FOLD_SMEM>(c, a, tb)
                     : launch_decode_tt<METHOD_FOLD, DEC_FOLD_GLOBAL>(c, a, 0);
@@ -1857,7 +1891,7 @@ try {
     CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
     {   // untrusted sizes: at least the four states, whole words for plain ANS
         const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>((nb + 255) / 256, uint64_t(c->num_sms) * 4)));
-        check_block_sizes_kernel<<<grid, 256, 0, c->stream>>>(d_block_bytes, uint32_t(nb), c->dec_method == METHOD_INT && c->block_syms ? 3u : 0u, c->d_err());
+        check_block_sizes_kernel<<<grid, 256, 0, c->stream>>>(d_block_bytes, uint32_t(nb), coder_of(c->dec_method) == METHOD_INT && c->block_syms ? 3u : 0u, c->d_err());
         c->stats.launches++;
         CU(c, cudaGetLastError());
         RET(read_small(c));
@@ -1943,7 +1977,7 @@ try {
     CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
     {   // untrusted sizes, as in b200ans_decode_blocks_device; then offsets[b] = sum of the padded sizes in front of b
         const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>((nb + 255) / 256, uint64_t(c->num_sms) * 4)));
-        check_block_sizes_kernel<<<grid, 256, 0, c->stream>>>(d_block_bytes, uint32_t(nb), c->dec_method == METHOD_INT ? 3u : 0u, c->d_err());
+        check_block_sizes_kernel<<<grid, 256, 0, c->stream>>>(d_block_bytes, uint32_t(nb), coder_of(c->dec_method) == METHOD_INT ? 3u : 0u, c->d_err());
         c->stats.launches++;
         CU(c, cudaGetLastError());
         scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_block_bytes, uint32_t(nb), d_offsets, d_totals, nullptr);
@@ -2276,6 +2310,10 @@ int model_from_device(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_
             RET(histogram_to_host(c, METHOD_INT, f, d_src, n, size_t(max_value) + 1, bins, nullptr, sharded));
         else
             bins.resize(size_t(max_value) + 1);
+    } else if (method == METHOD_BYTE) {
+        RET(histogram_to_host(c, METHOD_BYTE, f, d_src, n, kByteSigma, bins, &max_value, sharded));
+        if (max_value >= kByteSigma)
+            return c->fail(B200ANS_E_DOMAIN, "ANSbyte codes bytes: values must be below 256");
     } else if (method == METHOD_RFOLD) {
         // K4 on the device: ONE optimistic pass counts the raw values into `guess` bins while it keeps the running
         // maximum (a second pass only when a value lies beyond the guess); selection of the 2^(f+7) most frequent
@@ -2455,6 +2493,142 @@ try {
     if (capacity < c->most_frequent.size())
         return c->fail(B200ANS_E_CAPACITY, "most_frequent buffer too small");
     std::copy(c->most_frequent.begin(), c->most_frequent.end(), dst);
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+// ==========================================================================================
+// ans_byte (ans_byte.hpp): the byte coder of the vbyte+ANS baselines (methods.hpp:432-482)
+// ==========================================================================================
+// Same 4-state coder as plain ANS over 256 symbols, with its own normaliser (frame <= 4096) and prelude.  METHOD_BYTE
+// runs through every uint32 entry point (values below 256); these take and return BYTES: the symbols are widened to
+// uint32 on the device in front of the block coders and narrowed behind them.
+namespace {
+
+__global__ void __launch_bounds__(256) widen_bytes_kernel(const uint8_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t n)
+{
+    const uint64_t n4 = n >> 2; // (in is 4-byte aligned: our own buffer)
+    const uint32_t* in4 = reinterpret_cast<const uint32_t*>(in);
+    uint4* out4 = reinterpret_cast<uint4*>(out);
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += uint64_t(gridDim.x) * blockDim.x) {
+        const uint32_t w = __ldg(in4 + i);
+        out4[i] = make_uint4(w & 0xFFu, (w >> 8) & 0xFFu, (w >> 16) & 0xFFu, w >> 24);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3u))
+        out[(n4 << 2) + threadIdx.x] = in[(n4 << 2) + threadIdx.x];
+}
+
+__global__ void __launch_bounds__(256) narrow_bytes_kernel(const uint32_t* __restrict__ in, uint8_t* __restrict__ out, uint64_t n)
+{
+    const uint64_t n4 = n >> 2;
+    const uint4* in4 = reinterpret_cast<const uint4*>(in);
+    uint32_t* out4 = reinterpret_cast<uint32_t*>(out);
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += uint64_t(gridDim.x) * blockDim.x) {
+        const uint4 q = __ldg(in4 + i);
+        out4[i] = (q.x & 0xFFu) | ((q.y & 0xFFu) << 8) | ((q.z & 0xFFu) << 16) | (q.w << 24);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3u))
+        out[(n4 << 2) + threadIdx.x] = uint8_t(in[(n4 << 2) + threadIdx.x]);
+}
+
+int byte_grid(const b200ans_ctx* c, size_t n) { return int(std::max<size_t>(1, std::min<size_t>(((n >> 2) + 255) / 256, size_t(c->num_sms) * 8))); }
+
+} // namespace
+
+// ans_byte_compress (ans_byte.hpp:236-277) with device buffers: d_src holds n bytes (4-byte aligned), d_dst the container
+extern "C" int b200ans_byte_compress_device(b200ans_ctx* c, uint8_t* d_dst, size_t cap, const uint8_t* d_src, size_t n, size_t* out_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_dst || !out_bytes || (!d_src && n) || (reinterpret_cast<uintptr_t>(d_src) & 3) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
+        return c->fail(B200ANS_E_ARG, "byte_compress: bad argument (source 4-byte, destination 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
+    if (n) {
+        widen_bytes_kernel<<<byte_grid(c, n), 256, 0, c->stream>>>(d_src, c->io_in.as<uint32_t>(), n);
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    }
+    return compress_device_impl(c, METHOD_BYTE, 0, d_dst, cap, c->io_in.as<uint32_t>(), n, out_bytes, false);
+}
+B200ANS_CATCH_INT
+
+// ans_byte_decompress (ans_byte.hpp:279-305): n bytes to d_dst (4-byte aligned)
+extern "C" int b200ans_byte_decompress_device(b200ans_ctx* c, uint8_t* d_dst, size_t n, const uint8_t* d_src, size_t src_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!d_dst && n) || !d_src || (reinterpret_cast<uintptr_t>(d_dst) & 3))
+        return c->fail(B200ANS_E_ARG, "byte_decompress: bad argument (destination 4-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->io_in.reserve(std::max<size_t>(align_up(n * 4, 32), 32)));
+    RET(b200ans_decompress_device(c, METHOD_BYTE, 0, c->io_in.as<uint32_t>(), n, d_src, src_bytes));
+    if (n) {
+        narrow_bytes_kernel<<<byte_grid(c, n), 256, 0, c->stream>>>(c->io_in.as<uint32_t>(), d_dst, n);
+        c->stats.launches++;
+        CU(c, cudaGetLastError());
+    }
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+// host buffers
+extern "C" int b200ans_byte_compress(b200ans_ctx* c, uint8_t* dst, size_t cap, const uint8_t* src, size_t n, size_t* out_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!dst || !out_bytes || (!src && n))
+        return c->fail(B200ANS_E_ARG, "byte_compress: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    const size_t bound = std::min(b200ans_compress_bound(c, METHOD_BYTE, n), std::max<size_t>(cap + 64, 4096));
+    CU(c, c->io_bytes.reserve(std::max<size_t>(align_up(n, 16), 16)));
+    CU(c, c->io_out.reserve(bound));
+    if (n)
+        CU(c, cudaMemcpyAsync(c->io_bytes.p, src, n, cudaMemcpyHostToDevice, c->stream));
+    size_t bytes = 0;
+    RET(b200ans_byte_compress_device(c, c->io_out.as<uint8_t>(), std::min(bound, c->io_out.cap), c->io_bytes.as<uint8_t>(), n, &bytes));
+    if (bytes > cap)
+        return c->fail(B200ANS_E_CAPACITY, "byte_compress: destination too small");
+    if (bytes)
+        CU(c, cudaMemcpyAsync(dst, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    *out_bytes = bytes;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_byte_decompress(b200ans_ctx* c, uint8_t* dst, size_t n, const uint8_t* src, size_t src_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!dst && n) || !src)
+        return c->fail(B200ANS_E_ARG, "byte_decompress: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    if (n == 0 && c->block_syms == 0)
+        return B200ANS_OK;
+    CU(c, c->io_out.reserve(std::max<size_t>(align_up(src_bytes, 16), 64)));
+    CU(c, c->io_bytes.reserve(std::max<size_t>(align_up(n, 16), 16)));
+    CU(c, cudaMemcpyAsync(c->io_out.p, src, src_bytes, cudaMemcpyHostToDevice, c->stream));
+    RET(b200ans_byte_decompress_device(c, c->io_bytes.as<uint8_t>(), n, c->io_out.as<uint8_t>(), src_bytes));
+    if (n)
+        CU(c, cudaMemcpyAsync(dst, c->io_bytes.p, n, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+// the byte normaliser on its own (ans_byte.hpp:41-97); host only
+extern "C" int b200ans_byte_adjust_freqs(const uint64_t* freqs, uint16_t* out)
+try {
+    if (!freqs || !out)
+        return B200ANS_E_ARG;
+    uint64_t total = 0;
+    for (int i = 0; i < 256; i++)
+        total += freqs[i];
+    if (total == 0)
+        return B200ANS_E_DOMAIN;
+    const std::array<uint16_t, 256> nf = byte_adjust_freqs(freqs);
+    std::copy(nf.begin(), nf.end(), out);
     return B200ANS_OK;
 }
 B200ANS_CATCH_INT
@@ -2735,7 +2909,7 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
         for (uint32_t b = 0; b < nb; b++) {
             uint32_t v;
             std::memcpy(&v, tp + size_t(b) * 4, 4);
-            if (v < 32u || v > 0x7FFFFF00u || (method == METHOD_INT && (v & 3u)))
+            if (v < 32u || v > 0x7FFFFF00u || (coder_of(method) == METHOD_INT && (v & 3u)))
                 return c->fail(B200ANS_E_FORMAT, "decompress: a block is shorter than its four states (or, plain ANS, not a whole number of words)");
             total += (uint64_t(v) + 15u) & ~uint64_t(15);
             if (total > h.payload_bytes)

@@ -20,7 +20,13 @@
 
 namespace b200ans {
 
-enum method_t : int { METHOD_INT = 0, METHOD_FOLD = 1, METHOD_MSB = 2, METHOD_RFOLD = 3 };
+enum method_t : int { METHOD_INT = 0, METHOD_FOLD = 1, METHOD_MSB = 2, METHOD_RFOLD = 3, METHOD_BYTE = 4 };
+// METHOD_BYTE (ans_byte.hpp): 256 symbols, its own normaliser and prelude; the coder is plain ANS's (no raw bytes)
+B200ANS_HD int coder_of(int method) { return method == METHOD_BYTE ? METHOD_INT : method; }
+
+constexpr uint32_t kByteSigma = 256;        // ans_byte.hpp:25  constants::MAX_SIGMA
+constexpr uint32_t kByteMaxFrame = 4096;    // ans_byte.hpp:26  constants::MAX_FRAME_SIZE
+constexpr uint32_t kByteFrameFactor = 64;   // ans_byte.hpp:27  constants::FRAME_FACTOR
 
 constexpr uint32_t kAnsK = 16;         // ans_byte.hpp:30  constants::K
 constexpr uint32_t kRadixLog2 = 32;    // ans_byte.hpp:28  constants::RADIX_LOG2

@@ -24,6 +24,7 @@
 #include <cstdint>
 #include <limits>
 #include <utility>
+#include <array>
 #include <vector>
 
 namespace b200ans {
@@ -237,6 +238,62 @@ inline std::vector<uint32_t> adjust_freqs(
         }
         frame <<= kBatch;
     }
+}
+
+
+// ans_byte.hpp:41-97: normalise byte counts to a frame of min(4096, 64 x distinct symbols) rounded up to a power of two.
+// Scale down with a fudge factor that shrinks by 0.01 per try until the truncated shares fit, then hand the slack out
+// from the top symbol down in proportion, whatever is left to the largest share.  Same double operations in the same
+// order as the reference (no expression here can be contracted into an FMA).
+inline std::array<uint16_t, 256> byte_adjust_freqs(const uint64_t* freqs /* 256 */)
+{
+    std::array<uint16_t, 256> adj {};
+    size_t uniq = 0, initial_sum = 0;
+    for (size_t i = 0; i < 256; i++) {
+        initial_sum += freqs[i];
+        uniq += freqs[i] != 0;
+    }
+    size_t target = uniq * 64;
+    if (target > 4096)
+        target = 4096;
+    if (!is_power_of_two(target))
+        target = size_t(next_power_of_two(target));
+    const double c = double(target) / double(initial_sum);
+    size_t cur = ~size_t(0);
+    double fudge = 1.0;
+    while (cur > target) {
+        fudge -= 0.01;
+        cur = 0;
+        for (size_t sym = 0; sym < 256; sym++) {
+            adj[sym] = uint16_t(fudge * double(freqs[sym]) * c);
+            if (adj[sym] == 0 && freqs[sym] != 0)
+                adj[sym] = 1;
+            cur += adj[sym];
+        }
+    }
+    int64_t excess = int64_t(target) - int64_t(cur);
+    for (size_t sym = 0; sym < 256; sym++) {
+        const uint16_t ncnt = adj[255 - sym];
+        if (ncnt == 0)
+            continue;
+        const double ratio = double(excess) / double(cur);
+        size_t adder = size_t(ratio * double(ncnt));
+        if (adder > size_t(excess))
+            adder = size_t(excess);
+        excess -= int64_t(adder);
+        cur -= ncnt;
+        adj[255 - sym] = uint16_t(adj[255 - sym] + adder);
+    }
+    if (excess != 0) {
+        size_t max_freq = 0, max_sym = 0;
+        for (size_t sym = 0; sym < 256; sym++)
+            if (adj[sym] > max_freq) {
+                max_freq = adj[sym];
+                max_sym = sym;
+            }
+        adj[max_sym] = uint16_t(adj[max_sym] + excess);
+    }
+    return adj;
 }
 
 } // namespace b200ans

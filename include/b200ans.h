@@ -60,6 +60,7 @@ extern "C" {
 #define B200ANS_METHOD_FOLD 1  /* "ANSfold-f"  ans_fold.hpp                                   */
 #define B200ANS_METHOD_MSB 2   /* "ANSmsb"     ans_msb.hpp                                    */
 #define B200ANS_METHOD_RFOLD 3 /* "ANSrfold-f" ans_reorder_fold.hpp                           */
+#define B200ANS_METHOD_BYTE 4  /* "ANSbyte"    ans_byte.hpp (bytes: values below 256)            */
 
 /* kernel families (both produce identical bytes; AUTO picks by block count) */
 #define B200ANS_PATH_AUTO 0
@@ -269,6 +270,19 @@ int b200ans_pa_compress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, 
                                size_t dst_capacity, const uint32_t* d_src, size_t n, size_t* out_bytes);
 int b200ans_pa_decompress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* d_dst, size_t n,
                                  const uint8_t* d_src, size_t src_bytes);
+
+/* ---- ans_byte (ans_byte.hpp): the byte coder behind the vbyteANS / streamvbyteANS baselines (methods.hpp:432-482) ----
+ * B200ANS_METHOD_BYTE: 256 symbols, frame <= 4096, the reference's byte normaliser (ans_byte.hpp:41-97) and prelude
+ * (:122-137), the same 4-state coder as plain ANS (:236-305).  The method also runs through every uint32 entry point
+ * above (values below 256); these take and return bytes.  Block payloads and, with block_syms = 0, the whole stream
+ * are byte-identical to ans_byte_compress. */
+int b200ans_byte_compress(b200ans_ctx* ctx, uint8_t* dst, size_t dst_capacity, const uint8_t* src, size_t n, size_t* out_bytes);
+int b200ans_byte_decompress(b200ans_ctx* ctx, uint8_t* dst, size_t n, const uint8_t* src, size_t src_bytes);
+/* device buffers: bytes 4-byte aligned, the container 16-byte aligned */
+int b200ans_byte_compress_device(b200ans_ctx* ctx, uint8_t* d_dst, size_t dst_capacity, const uint8_t* d_src, size_t n, size_t* out_bytes);
+int b200ans_byte_decompress_device(b200ans_ctx* ctx, uint8_t* d_dst, size_t n, const uint8_t* d_src, size_t src_bytes);
+/* adjust_freqs of ans_byte.hpp:41-97 (host only): freqs[256] -> out[256], summing to min(4096, 64 x distinct) rounded up to 2^k */
+int b200ans_byte_adjust_freqs(const uint64_t* freqs, uint16_t* out);
 
 /* ---- host-only model API (ans_util.hpp / interp.hpp); usable without a GPU ------------- */
 /* out: largest_sym + 1 entries */

@@ -15,6 +15,7 @@
 //   ans_fold_compress<f> / _decompress  ans_fold.hpp:238,283            b200::ans_fold_compress<f> / ...
 //   ans_msb_compress / _decompress      ans_msb.hpp:235,294             b200::ans_msb_compress / ...
 //   ans_reorder_fold_compress<f> / ...  ans_reorder_fold.hpp:312,357    b200::ans_reorder_fold_compress<f> / ...
+//   ans_byte_compress / _decompress     ans_byte.hpp:236,279            b200::ans_byte_compress / _decompress
 //   adjust_freqs             ans_util.hpp:100-157           b200::adjust_freqs
 //   ans_serialize_interp     ans_util.hpp:46-63             b200::ans_serialize_interp
 //   ans_load_interp          ans_util.hpp:25-42             b200::ans_load_interp
@@ -154,6 +155,24 @@ template <uint32_t H_approx> size_t ans_smsb_compress(uint8_t* dst, size_t dstCa
 inline void ans_smsb_decompress(uint32_t* dst, size_t to_decode, const uint8_t* cSrc, size_t cSrcSize)
 {
     decompress(B200ANS_METHOD_MSB, 0, dst, to_decode, cSrc, cSrcSize);
+}
+
+// ans_byte_compress / _decompress (ans_byte.hpp:236,279): the byte coder of the vbyte+ANS baselines
+inline size_t ans_byte_compress(void* dst, size_t dstCapacity, const void* src, size_t srcSize)
+{
+    b200ans_ctx* ctx = context();
+    size_t bytes = 0;
+    const int rc = b200ans_byte_compress(ctx, static_cast<uint8_t*>(dst), dstCapacity, static_cast<const uint8_t*>(src), srcSize, &bytes);
+    if (rc != B200ANS_OK)
+        quit("ans_byte_compress", rc, ctx);
+    return bytes;
+}
+inline void ans_byte_decompress(void* dst, size_t to_decode, const void* cSrc, size_t cSrcSize)
+{
+    b200ans_ctx* ctx = context();
+    const int rc = b200ans_byte_decompress(ctx, static_cast<uint8_t*>(dst), to_decode, static_cast<const uint8_t*>(cSrc), cSrcSize);
+    if (rc != B200ANS_OK)
+        quit("ans_byte_decompress", rc, ctx);
 }
 
 // ---- the ans_util.hpp model API (host only; no GPU needed) -------------------------------------------------------

@@ -443,6 +443,59 @@ long orc_load_interp(const uint8_t* in, uint32_t* out)
     return (long)count;
 }
 
+/* ans_byte.hpp:41-97 -- the byte coder's own normaliser: frame = min(4096, 64 x distinct symbols) rounded up to a power
+ * of two; truncated shares with a fudge factor that shrinks by 0.01 per try until they fit; the slack goes out from the
+ * top symbol down in proportion, the rest to the largest share. */
+void orc_byte_adjust_freqs(const uint64_t* freqs, uint16_t* adj)
+{
+    size_t uniq = 0, initial_sum = 0;
+    for (size_t i = 0; i < 256; i++) {
+        initial_sum += freqs[i];
+        uniq += freqs[i] != 0;
+        adj[i] = 0;
+    }
+    size_t target = uniq * 64; /* :52-58 */
+    if (target > 4096)
+        target = 4096;
+    if (!is_pow2(target))
+        target = (size_t)next_pow2(target);
+    double c = (double)target / (double)initial_sum;
+    size_t cur = (size_t)-1;
+    double fudge = 1.0;
+    while (cur > target) { /* :63-72 */
+        fudge -= 0.01;
+        cur = 0;
+        for (size_t sym = 0; sym < 256; sym++) {
+            adj[sym] = (uint16_t)(fudge * (double)freqs[sym] * c);
+            if (adj[sym] == 0 && freqs[sym] != 0)
+                adj[sym] = 1;
+            cur += adj[sym];
+        }
+    }
+    int64_t excess = (int64_t)target - (int64_t)cur; /* :73-86 */
+    for (size_t sym = 0; sym < 256; sym++) {
+        uint16_t ncnt = adj[255 - sym];
+        if (ncnt == 0)
+            continue;
+        double ratio = (double)excess / (double)cur;
+        size_t adder = (size_t)(ratio * (double)ncnt);
+        if (adder > (size_t)excess)
+            adder = (size_t)excess;
+        excess -= (int64_t)adder;
+        cur -= ncnt;
+        adj[255 - sym] = (uint16_t)(adj[255 - sym] + adder);
+    }
+    if (excess != 0) { /* :87-97 */
+        size_t max_freq = 0, max_sym = 0;
+        for (size_t sym = 0; sym < 256; sym++)
+            if (adj[sym] > max_freq) {
+                max_freq = adj[sym];
+                max_sym = sym;
+            }
+        adj[max_sym] = (uint16_t)(adj[max_sym] + excess);
+    }
+}
+
 /* ---------------------------------------------------------------------------- models */
 
 struct orc_model {
@@ -469,6 +522,7 @@ static size_t nbins_of(int method, uint32_t f, uint32_t max_value)
 {
     switch (method) {
     case ORC_INT: return (size_t)max_value + 1; /* ans_int.hpp:46 */
+    case ORC_BYTE: return 256;                   /* ans_byte.hpp:25 */
     case ORC_MSB: return MSB_MAX_SIGMA;          /* ans_msb.hpp:79 */
     default: return (size_t)1 << (f + 9);        /* ans_fold.hpp:70 */
     }
@@ -477,7 +531,8 @@ static size_t nbins_of(int method, uint32_t f, uint32_t max_value)
 static inline uint32_t map_symbol(const orc_model* m, uint32_t x, uint32_t* k)
 {
     switch (m->method) {
-    case ORC_INT: *k = 0; return x;
+    case ORC_INT:
+    case ORC_BYTE: *k = 0; return x;
     case ORC_MSB: return orc_msb_mapping(x, k);
     case ORC_FOLD: return orc_fold_mapping(m->f, x, k);
     default: return orc_fold_mapping(m->f, m->mapping[x], k); /* ans_reorder_fold.hpp:158-159 */
@@ -570,6 +625,17 @@ orc_model* orc_model_create(int method, uint32_t f, const uint32_t* in, size_t n
         if (s > max_sym)
             max_sym = s;
     }
+    if (method == ORC_BYTE) { /* ans_byte.hpp:99-120: all 256 entries, the byte normaliser */
+        uint16_t nf[256];
+        orc_byte_adjust_freqs(freqs, nf);
+        m->nsyms = 256;
+        m->nfreqs = (uint32_t*)calloc(256, sizeof(uint32_t));
+        for (size_t s = 0; s < 256; s++)
+            m->nfreqs[s] = nf[s];
+        free(freqs);
+        finish_encoder(m);
+        return m;
+    }
     m->nsyms = (size_t)max_sym + 1;
     m->nfreqs = (uint32_t*)calloc(m->nsyms, sizeof(uint32_t));
     orc_adjust_freqs(freqs, nbins, max_sym, method != ORC_INT, 1, m->nfreqs);
@@ -608,6 +674,14 @@ long orc_model_serialize(orc_model* m, uint8_t* out)
             memcpy(p, m->most_frequent, m->n_mf * 4);
             p += m->n_mf * 4;
         }
+    }
+    if (m->method == ORC_BYTE) { /* ans_byte.hpp:122-137: running sums of (nfreq + 1), universe 4096 + 256, no header */
+        uint32_t inc[256];
+        inc[0] = m->nfreqs[0];
+        for (size_t s = 1; s < 256; s++)
+            inc[s] = inc[s - 1] + m->nfreqs[s] + 1;
+        long ib = orc_interp_encode((uint32_t*)p, inc, 256, 4096 + 256);
+        return (p - out) + ib;
     }
     p += orc_serialize_interp(m->nfreqs, m->nsyms, m->M, p);
     return p - out;
@@ -680,9 +754,21 @@ orc_model* orc_model_load(int method, uint32_t f, const uint8_t* prelude)
                 m->most_frequent[i] = (uint32_t)i;
         }
     }
-    m->nsyms = (size_t)orc_load_interp(p, NULL);
-    m->nfreqs = (uint32_t*)malloc(m->nsyms * sizeof(uint32_t));
-    orc_load_interp(p, m->nfreqs);
+    if (method == ORC_BYTE) { /* ans_byte.hpp:178-190 */
+        m->nsyms = 256;
+        m->nfreqs = (uint32_t*)malloc(256 * sizeof(uint32_t));
+        orc_interp_decode((const uint32_t*)p, m->nfreqs, 256, 4096 + 256);
+        uint32_t prev = m->nfreqs[0];
+        for (size_t s = 1; s < 256; s++) {
+            uint32_t cur = m->nfreqs[s];
+            m->nfreqs[s] = cur - prev - 1;
+            prev = cur;
+        }
+    } else {
+        m->nsyms = (size_t)orc_load_interp(p, NULL);
+        m->nfreqs = (uint32_t*)malloc(m->nsyms * sizeof(uint32_t));
+        orc_load_interp(p, m->nfreqs);
+    }
     finish_encoder(m);
     m->d_freq = (uint32_t*)malloc(m->M * sizeof(uint32_t));
     m->d_off = (uint32_t*)malloc(m->M * sizeof(uint32_t));
@@ -700,7 +786,7 @@ orc_model* orc_model_load(int method, uint32_t f, const uint8_t* prelude)
             } else
                 orc_fold_undo(f, (uint32_t)s, &val, &k);
         }
-        if (method != ORC_INT)
+        if (method != ORC_INT && method != ORC_BYTE)
             val += k << 30;
         for (uint32_t j = 0; j < m->nfreqs[s]; j++) {
             size_t slot = m->base[s] + j;
@@ -724,7 +810,7 @@ static inline uint32_t decode_sym(const orc_model* m, uint64_t* state, const uin
         memcpy(&w, *in, 4);
         *state = (*state << ANS_RADIX_LOG2) | w;
     }
-    if (m->method == ORC_INT)
+    if (m->method == ORC_INT || m->method == ORC_BYTE)
         return val;
     static const uint32_t mask[4] = { 0x0, 0xFF, 0xFFFF, 0xFFFFFF };
     uint32_t k = val >> 30, w;

@@ -17,7 +17,7 @@
 extern "C" {
 #endif
 
-enum { ORC_INT = 0, ORC_FOLD = 1, ORC_MSB = 2, ORC_RFOLD = 3 };
+enum { ORC_INT = 0, ORC_FOLD = 1, ORC_MSB = 2, ORC_RFOLD = 3, ORC_BYTE = 4 }; /* ORC_BYTE: ans_byte.hpp, symbols < 256 handed over as uint32_t */
 
 typedef struct orc_model orc_model;
 
@@ -34,6 +34,8 @@ int orc_adjust_freqs(const uint64_t* freqs, size_t nbins, uint32_t largest_sym, 
 long orc_serialize_interp(const uint32_t* nfreqs, size_t count, uint64_t frame_size, uint8_t* out);
 long orc_load_interp(const uint8_t* in, uint32_t* out);
 /* interp.hpp:100-118 */
+/* ans_byte.hpp:41-97: freqs[256] -> out[256] */
+void orc_byte_adjust_freqs(const uint64_t* freqs, uint16_t* out);
 long orc_interp_encode(uint32_t* dst, const uint32_t* in, size_t n, size_t u);
 long orc_interp_decode(const uint32_t* src, uint32_t* out, size_t n, size_t u);
 

@@ -31,7 +31,15 @@
 #include "ans_smsb.hpp"
 #include "zipf_dist.hpp"
 
-enum { M_INT = 0, M_FOLD = 1, M_MSB = 2, M_RFOLD = 3 };
+enum { M_INT = 0, M_FOLD = 1, M_MSB = 2, M_RFOLD = 3, M_BYTE = 4 }; // M_BYTE: ans_byte.hpp, the symbols are bytes handed over as uint32_t
+
+static std::vector<uint8_t> to_bytes(const uint32_t* in, size_t n)
+{
+    std::vector<uint8_t> b(n);
+    for (size_t i = 0; i < n; i++)
+        b[i] = uint8_t(in[i]);
+    return b;
+}
 
 #define FOLD_DISPATCH(f, EXPR)                                                                 \
     switch (f) {                                                                               \
@@ -146,6 +154,10 @@ long ref_compress(int method, uint32_t f, uint8_t* dst, size_t cap, const uint32
     case M_MSB: return (long)ans_msb_compress(dst, cap, src, n);
     case M_FOLD: FOLD_DISPATCH(f, return (long)ans_fold_compress<F>(dst, cap, src, n));
     case M_RFOLD: FOLD_DISPATCH(f, return (long)ans_reorder_fold_compress<F>(dst, cap, src, n));
+    case M_BYTE: {
+        const std::vector<uint8_t> b = to_bytes(src, n);
+        return (long)ans_byte_compress(dst, cap, b.data(), n);
+    }
     }
     return -1;
 }
@@ -190,6 +202,12 @@ int ref_decompress(int method, uint32_t f, uint32_t* dst, size_t n, const uint8_
     case M_MSB: ans_msb_decompress(dst, n, src, bytes); return 0;
     case M_FOLD: FOLD_DISPATCH(f, ans_fold_decompress<F>(dst, n, src, bytes); return 0);
     case M_RFOLD: FOLD_DISPATCH(f, ans_reorder_fold_decompress<F>(dst, n, src, bytes); return 0);
+    case M_BYTE: {
+        std::vector<uint8_t> b(n);
+        ans_byte_decompress(b.data(), n, src, bytes);
+        std::copy(b.begin(), b.end(), dst);
+        return 0;
+    }
     }
     return -1;
 }
@@ -268,6 +286,11 @@ ref_model* ref_model_create(int method, uint32_t f, const uint32_t* in, size_t n
     switch (method) {
     case M_INT: m->enc = new ans_int_encode(ans_int_encode::create(in, n)); return m;
     case M_MSB: m->enc = new ans_msb_encode(ans_msb_encode::create(in, n)); return m;
+    case M_BYTE: {
+        const std::vector<uint8_t> b = to_bytes(in, n);
+        m->enc = new ans_byte_encode(ans_byte_encode::create(b.data(), n));
+        return m;
+    }
     case M_FOLD:
         switch (f) {
 #define C(F) case F: m->enc = new ans_fold_encode<F>(ans_fold_encode<F>::create(in, n)); return m;
@@ -309,6 +332,7 @@ ref_model* ref_model_from_hist(int method, uint32_t f, const uint64_t* bins, siz
     switch ((m)->method) {                                                                     \
     case M_INT: { auto& e = *static_cast<ans_int_encode*>((m)->enc); EXPR; } break;            \
     case M_MSB: { auto& e = *static_cast<ans_msb_encode*>((m)->enc); EXPR; } break;            \
+    case M_BYTE: { auto& e = *static_cast<ans_byte_encode*>((m)->enc); EXPR; } break;          \
     case M_FOLD: FOLD_DISPATCH((m)->f, auto& e = *static_cast<ans_fold_encode<F>*>((m)->enc); EXPR); break; \
     case M_RFOLD: FOLD_DISPATCH((m)->f, auto& e = *static_cast<ans_reorder_fold_encode<F>*>((m)->enc); EXPR); break; \
     }
@@ -351,6 +375,7 @@ ref_model* ref_model_load(int method, uint32_t f, const uint8_t* prelude)
     switch (method) {
     case M_INT: m->dec = new ans_int_decode(ans_int_decode::load(prelude)); return m;
     case M_MSB: m->dec = new ans_msb_decode(ans_msb_decode::load(prelude)); return m;
+    case M_BYTE: m->dec = new ans_byte_decode(ans_byte_decode::load(prelude)); return m;
     case M_FOLD:
         switch (f) {
 #define C(F) case F: m->dec = new ans_fold_decode<F>(ans_fold_decode<F>::load(prelude)); return m;
@@ -391,6 +416,12 @@ int ref_decode_block(ref_model* m, const uint8_t* src, size_t bytes, uint32_t* o
             [](ans_msb_decode& mm, uint64_t& s, const uint8_t*& in) { return mm.decode_sym(s, in); });
         return 0;
     }
+    case M_BYTE: {
+        auto& d = *static_cast<ans_byte_decode*>(m->dec);
+        decode_range(d, src, bytes, out, n,
+            [](ans_byte_decode& mm, uint64_t& s, const uint8_t*& in) { return uint32_t(mm.decode_sym(s, in)); });
+        return 0;
+    }
     case M_FOLD:
         FOLD_DISPATCH(m->f, auto& d = *static_cast<ans_fold_decode<F>*>(m->dec);
                       decode_range(d, src, bytes, out, n,
@@ -415,6 +446,7 @@ void ref_model_free(ref_model* m)
         switch (m->method) {
         case M_INT: del<ans_int_encode>(m->enc); break;
         case M_MSB: del<ans_msb_encode>(m->enc); break;
+        case M_BYTE: del<ans_byte_encode>(m->enc); break;
         case M_FOLD:
             switch (m->f) {
 #define C(F) case F: del<ans_fold_encode<F>>(m->enc); break;
@@ -435,6 +467,7 @@ void ref_model_free(ref_model* m)
         switch (m->method) {
         case M_INT: del<ans_int_decode>(m->dec); break;
         case M_MSB: del<ans_msb_decode>(m->dec); break;
+        case M_BYTE: del<ans_byte_decode>(m->dec); break;
         case M_FOLD:
             switch (m->f) {
 #define C(F) case F: del<ans_fold_decode<F>>(m->dec); break;

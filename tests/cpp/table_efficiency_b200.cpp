@@ -161,6 +161,18 @@ int main(int argc, char** argv)
         std::printf("model structs ANSrfold-1 / ANS / ANSmsb: %s\n", (r_ok && i_ok) ? "OK" : "MISMATCH");
         ok = ok && r_ok && i_ok;
     }
+    // ans_byte (ans_byte.hpp:236,279): the byte coder of the vbyteANS / streamvbyteANS baselines
+    {
+        std::vector<uint8_t> bytes(inputs[0].size());
+        for (size_t i = 0; i < bytes.size(); i++)
+            bytes[i] = uint8_t(std::min<uint32_t>(inputs[0][i], 255));
+        std::vector<uint8_t> blob(bytes.size() * 4 + 4096), back(bytes.size());
+        const size_t nb = b200::ans_byte_compress(blob.data(), blob.size(), bytes.data(), bytes.size());
+        b200::ans_byte_decompress(back.data(), back.size(), blob.data(), nb);
+        const bool b_ok = back == bytes && nb < bytes.size();
+        std::printf("ans_byte: %zu -> %zu bytes  %s\n", bytes.size(), nb, b_ok ? "OK" : "MISMATCH");
+        ok = ok && b_ok;
+    }
     std::printf(ok ? "ALL OK\n" : "FAILED\n");
     return ok ? 0 : 1;
 }

@@ -11,7 +11,8 @@ Each vector holds a small seeded input and what the reference produced for it:
   block_payloads        the 4-state loop of ans_fold.hpp:250-278 driven per 1024-symbol block with the global model
 plus known answers of the fold / msb mappings (ans_fold.hpp:38-65, ans_msb.hpp:41-73) and the
 interpolative coder (interp.hpp:100-118), and blocks of the pseudo-adaptive driver with its dense-rank alphabet
-remap (src/pseudo_adaptive.cpp:83-125; `python tests/golden/make_golden.py pa_remap` writes only those).  The reference leaves the unused high bits of its last
+remap (src/pseudo_adaptive.cpp:83-125; `python tests/golden/make_golden.py pa_remap` writes only those), and ans_byte
+(ans_byte.hpp; `... make_golden.py ans_byte`).  The reference leaves the unused high bits of its last
 interp word uninitialised (bits.hpp:148); they are masked to zero here so the vectors are stable.
 """
 import os
@@ -79,10 +80,38 @@ def pa_remap_vectors(ref):
     print(f"pa_remap: {j + 1} blocks")
 
 
+def ans_byte_vectors(ref):
+    """ans_byte (ans_byte.hpp): byte inputs, the byte normaliser's frequencies, prelude, whole stream, 1024-symbol blocks"""
+    M_BYTE = 4
+    rng = np.random.default_rng(77)
+    cases = [
+        ("uniform", rng.integers(0, 256, 20011)), ("geom", np.minimum(rng.geometric(0.04, 20011) - 1, 255)),
+        ("vbyte", np.where(rng.random(9001) < 0.9, 128 + rng.geometric(0.1, 9001) % 128, rng.integers(0, 128, 9001))),
+        ("few", rng.integers(3, 8, 5003)), ("one", np.full(777, 77)), ("tiny", rng.integers(0, 256, 5)),
+    ]
+    out = {}
+    for j, (name, data) in enumerate(cases):
+        data = data.astype(np.uint32)
+        model = ref.model_create(M_BYTE, 0, data)
+        frame, nfreqs = model.info()
+        stream = ref.compress(M_BYTE, 0, data)
+        assert np.array_equal(ref.decompress(M_BYTE, 0, stream, data.size), data)
+        payloads = [model.encode_block(data[b : b + BLOCK]) for b in range(0, data.size, BLOCK)]
+        out[f"data{j}"], out[f"nfreqs{j}"], out[f"frame{j}"] = data.astype(np.uint8), nfreqs.astype(np.uint16), np.uint64(frame)
+        out[f"prelude{j}"], out[f"stream{j}"] = model.serialize(), stream
+        out[f"block_sizes{j}"] = np.array([p.size for p in payloads], dtype=np.uint32)
+        out[f"block_payloads{j}"] = np.concatenate(payloads)
+        print(f"ans_byte {name}: n={data.size} frame={frame} stream={stream.size}B")
+    np.savez_compressed(os.path.join(HERE, "ans_byte.npz"), count=np.int32(len(cases)), **out)
+
+
 def main():
     ref = reference()
     if len(sys.argv) > 1 and sys.argv[1] == "pa_remap":
         pa_remap_vectors(ref)
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "ans_byte":
+        ans_byte_vectors(ref)
         return
     for name, method, f, kind, n, seed in CASES:
         data = _inputs.make(kind, n, seed=seed)
@@ -159,6 +188,7 @@ def main():
     np.savez_compressed(os.path.join(HERE, "adjust_freqs.npz"), **hs)
     print("interp + adjust_freqs vectors written")
     pa_remap_vectors(ref)
+    ans_byte_vectors(ref)
 
 
 if __name__ == "__main__":

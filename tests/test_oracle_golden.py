@@ -15,7 +15,7 @@ from _libs import M_FOLD, M_INT, M_MSB, M_RFOLD, have_reference
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLD, "*.npz"))
-               if os.path.basename(p)[:-4] not in ("mappings", "interp", "adjust_freqs", "pa_remap"))
+               if os.path.basename(p)[:-4] not in ("mappings", "interp", "adjust_freqs", "pa_remap", "ans_byte"))
 
 
 def load(name):
@@ -209,3 +209,28 @@ def test_oracle_pa_remap_live(orc, ref, method, f):
         assert np.array_equal(a[2], b[2]) and remap_blocks_equal(a[0], a[1], b[0], b[1], pre), (kind, n)
     wide = (rng.integers(1 << 20, 1 << 24, size=4096)).astype(np.uint32)  # running sums beyond 32 bits
     assert orc.pa_remap_block(method, f, wide) is None and ref.pa_remap_block(method, f, wide) is None
+
+
+def test_oracle_and_host_ans_byte_match_reference(orc, host):
+    """ans_byte (ans_byte.hpp): the C restatement (ORC_BYTE) and the product's host normaliser against the reference's
+    frequencies, prelude, whole stream and 1024-symbol blocks (tests/golden/ans_byte.npz)"""
+    g = load("ans_byte")
+    for j in range(int(g["count"])):
+        data = g[f"data{j}"].astype(np.uint32)
+        m = orc.model_create(4, 0, data)
+        frame, nfreqs = m.info()
+        assert frame == int(g[f"frame{j}"]) and np.array_equal(nfreqs, g[f"nfreqs{j}"].astype(np.uint32))
+        got = host.byte_adjust_freqs(np.bincount(data, minlength=256))
+        assert np.array_equal(got, g[f"nfreqs{j}"]), "b200ans_byte_adjust_freqs differs from the reference"
+        pre = g[f"prelude{j}"]
+        assert _container.prelude_equal(m.serialize(), pre)
+        stream = orc.compress(4, 0, data)
+        assert stream.size == g[f"stream{j}"].size and np.array_equal(stream[pre.size :], g[f"stream{j}"][pre.size :])
+        assert np.array_equal(orc.decompress(4, 0, g[f"stream{j}"], data.size), data)
+        offs = np.concatenate([[0], np.cumsum(g[f"block_sizes{j}"].astype(np.int64))])
+        dec = orc.model_load(4, 0, pre)
+        for b in range(len(offs) - 1):
+            blk = data[b * 1024 : (b + 1) * 1024]
+            want = g[f"block_payloads{j}"][offs[b] : offs[b + 1]]
+            assert np.array_equal(m.encode_block(blk), want), f"case {j} block {b}"
+            assert np.array_equal(dec.decode_block(want, blk.size), blk)
