@@ -162,7 +162,7 @@ struct b200ans_ctx {
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, io_bytes, pa_nfreqs, pa_pre, pa_keys;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_syms, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, io_bytes, pa_nfreqs, pa_pre, pa_keys;
     // ANSrfold on the device (rfold_kernels.cuh): raw histogram, selection state, candidates, hash of the hot values
     DevBuf rf_sbuckets, rf_stags, rf_fast, rf_cand, rf_ctags, rf_cdisp, rf_cslot, rf_ccount, rf_sketch; // the fast route (rfold_kernels.cuh)
     DevBuf rf_raw, rf_raw32, rf_state, rf_hist, rf_tiles, rf_cand_count, rf_cand_value, rf_most, rf_tags, rf_disp, enc_table_rf;
@@ -368,7 +368,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->io_bytes, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys,
+             &c->dec_slots, &c->dec_syms, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->io_bytes, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys,
              &c->rf_sbuckets, &c->rf_stags, &c->rf_fast, &c->rf_cand, &c->rf_ctags, &c->rf_cdisp, &c->rf_cslot, &c->rf_ccount, &c->rf_sketch,
              &c->rf_raw, &c->rf_raw32, &c->rf_state, &c->rf_hist, &c->rf_tiles, &c->rf_cand_count, &c->rf_cand_value, &c->rf_most, &c->rf_tags, &c->rf_disp,
              &c->enc_table_rf })
@@ -1306,17 +1306,22 @@ try {
             c->dec_dense = 0;
             c->dec_fold_rank = true;
         } else {
-            std::vector<DecEntry> slots(frame);
+            // the M-entry slot table is filled on the device (kernels.cuh dec_slots_fill_kernel) from one record per
+            // present symbol
+            std::vector<SlotSym> syms;
             uint64_t base = 0;
             for (size_t s = 0; s < nfreqs.size(); s++) {
-                const uint32_t fr = nfreqs[s];
-                const uint32_t mapped = packed(uint32_t(s));
-                for (uint32_t j = 0; j < fr; j++)
-                    slots[base + j] = DecEntry { uint16_t(fr), uint16_t(j), mapped };
-                base += fr;
+                if (nfreqs[s])
+                    syms.push_back(SlotSym { uint32_t(base), nfreqs[s], packed(uint32_t(s)) });
+                base += nfreqs[s];
             }
-            CU(c, c->dec_slots.reserve(slots.size() * sizeof(DecEntry)));
-            CU(c, cudaMemcpyAsync(c->dec_slots.p, slots.data(), slots.size() * sizeof(DecEntry), cudaMemcpyHostToDevice, c->stream));
+            CU(c, c->dec_slots.reserve(size_t(frame) * sizeof(DecEntry)));
+            CU(c, c->dec_syms.reserve(syms.size() * sizeof(SlotSym)));
+            CU(c, cudaMemcpyAsync(c->dec_syms.p, syms.data(), syms.size() * sizeof(SlotSym), cudaMemcpyHostToDevice, c->stream));
+            dec_slots_fill_kernel<<<int(std::max<uint64_t>(1, (frame + 255) / 256)), 256, 0, c->stream>>>(c->dec_syms.as<SlotSym>(), uint32_t(syms.size()),
+                uint32_t(frame), c->dec_slots.as<DecEntry>());
+            c->stats.launches++;
+            CU(c, cudaGetLastError());
         }
     }
     c->dec_method = method;

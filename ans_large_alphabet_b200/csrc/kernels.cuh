@@ -242,6 +242,30 @@ template <int METHOD, int TABLE> struct DecTables {
     }
 };
 
+// K3a, the decoder's table fill (ans_fold.hpp:192-204, ans_msb.hpp:189-201, ans_reorder_fold.hpp:262-276): the host sends
+// one {first slot, freq, packed word} per present symbol, a thread per frame slot finds its symbol by binary search.
+struct SlotSym {
+    uint32_t base;   // first slot of the symbol
+    uint32_t freq;
+    uint32_t packed; // unfolded base value | raw bytes << 30 (rfold: most_frequent[s] + 2^(f+7) for the reordered values)
+};
+__global__ void __launch_bounds__(256) dec_slots_fill_kernel(const SlotSym* __restrict__ syms, uint32_t n_present, uint32_t frame,
+    DecEntry* __restrict__ slots)
+{
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < frame; slot += gridDim.x * blockDim.x) {
+        uint32_t lo = 0, hi = n_present; // syms[lo].base <= slot < syms[hi].base (syms[n_present].base = frame)
+        while (hi - lo > 1u) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(&syms[mid].base) <= slot)
+                lo = mid;
+            else
+                hi = mid;
+        }
+        const uint32_t base = __ldg(&syms[lo].base), freq = __ldg(&syms[lo].freq);
+        slots[slot] = DecEntry { uint16_t(freq), uint16_t(slot - base), __ldg(&syms[lo].packed) };
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // Small helpers
 // ------------------------------------------------------------------------------------------
