@@ -162,7 +162,8 @@ struct b200ans_ctx {
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_syms, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, io_bytes, pa_nfreqs, pa_pre, pa_keys;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_syms, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, io_bytes, pa_nfreqs, pa_pre, pa_keys, pa_log2tab;
+    bool pa_log2_ready = false;
     // ANSrfold on the device (rfold_kernels.cuh): raw histogram, selection state, candidates, hash of the hot values
     DevBuf rf_sbuckets, rf_stags, rf_fast, rf_cand, rf_ctags, rf_cdisp, rf_cslot, rf_ccount, rf_sketch; // the fast route (rfold_kernels.cuh)
     DevBuf rf_raw, rf_raw32, rf_state, rf_hist, rf_tiles, rf_cand_count, rf_cand_value, rf_most, rf_tags, rf_disp, enc_table_rf;
@@ -368,7 +369,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_syms, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->io_bytes, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys,
+             &c->dec_slots, &c->dec_syms, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->io_bytes, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys, &c->pa_log2tab,
              &c->rf_sbuckets, &c->rf_stags, &c->rf_fast, &c->rf_cand, &c->rf_ctags, &c->rf_cdisp, &c->rf_cslot, &c->rf_ccount, &c->rf_sketch,
              &c->rf_raw, &c->rf_raw32, &c->rf_state, &c->rf_hist, &c->rf_tiles, &c->rf_cand_count, &c->rf_cand_value, &c->rf_most, &c->rf_tags, &c->rf_disp,
              &c->enc_table_rf })
@@ -3164,7 +3165,14 @@ try {
         while (n_keys < nbins)
             n_keys <<= 1;
         const size_t smem = size_t(n_keys) * 8;
-        const int grid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 16));
+        // as many CTAs (one model at a time each) as the SMs hold: 64 threads + the keys in shared memory
+        const int grid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * uint32_t(std::max<size_t>(1, std::min<size_t>(32, (c->max_smem_sm - 4096) / (smem + 2048))))));
+        if (!c->pa_log2_ready) { // once per context (kernels.cuh pa_log2_table_kernel)
+            CU(c, c->pa_log2tab.reserve(size_t(kPaLog2Tab) * 8));
+            pa_log2_table_kernel<<<kPaLog2Tab / 256, 256, 0, c->stream>>>(c->pa_log2tab.as<double>());
+            c->stats.launches++;
+            c->pa_log2_ready = true;
+        }
         // B200ANS_PA_MARGIN (testing): a huge margin sends every model to the host's adjust_freqs
         const char* mv = std::getenv("B200ANS_PA_MARGIN");
         const double margin = mv && *mv ? std::atof(mv) : kPaMargin;
@@ -3176,7 +3184,7 @@ try {
             c->pa_nfreqs.as<uint32_t>());
         const uint32_t fit_threads = nm * 8u;
         pa_fit_kernel<<<(fit_threads + kPaFitThreads - 1) / kPaFitThreads, kPaFitThreads, 0, c->stream>>>(d_keys, n_keys, d_meta, nbins, nm,
-            margin, c->pa_nfreqs.as<uint32_t>(), d_lg, d_status, c->d_max_log2());
+            margin, c->pa_nfreqs.as<uint32_t>(), d_lg, d_status, c->d_max_log2(), c->pa_log2tab.as<double>());
         c->stats.launches += 2;
         CU(c, cudaGetLastError());
     }

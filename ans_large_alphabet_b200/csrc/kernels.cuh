@@ -1199,9 +1199,19 @@ struct PaMeta {
 };
 
 // STORE: write the shares to `shares` (the winning fit); otherwise accumulate the cross entropy
+// log2 of the integers below 2^16 (the shares of every fit that can win), computed once per context by the same device
+// log2 the fits would call: a load instead of ~40 FP64 instructions per symbol and frame, same values
+constexpr uint32_t kPaLog2Tab = 65536;
+__global__ void __launch_bounds__(256) pa_log2_table_kernel(double* __restrict__ tab)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < kPaLog2Tab)
+        tab[i] = log2(double(i));
+}
+
 template <bool STORE>
 __device__ __forceinline__ void pa_fit(const uint64_t* __restrict__ keys, uint32_t first, uint32_t n_keys, uint32_t lgM, uint64_t rest,
-    double inv_total, uint32_t* __restrict__ shares, bool& failed, uint32_t& top, double& xh)
+    double inv_total, uint32_t* __restrict__ shares, bool& failed, uint32_t& top, double& xh, const double* __restrict__ log2_tab = nullptr)
 {
     int64_t M = int64_t(1) << lgM;
     const double lgm = double(lgM);
@@ -1218,7 +1228,7 @@ __device__ __forceinline__ void pa_fit(const uint64_t* __restrict__ keys, uint32
         if (STORE)
             shares[sym] = share;
         else
-            acc = fma(double(cnt) * inv_total, log2(double(share)) - lgm, acc);
+            acc = fma(double(cnt) * inv_total, (share < kPaLog2Tab ? __ldg(log2_tab + share) : log2(double(share))) - lgm, acc);
         mx = max(mx, share);
         M -= int64_t(share);
         rest -= cnt;
@@ -1339,7 +1349,7 @@ __global__ void __launch_bounds__(kPaNormThreads) pa_sort_kernel(const uint32_t*
 // status: 0 = decided here, 1 = unusable (the reference would return an empty model), 2 = undecided (host decides)
 __global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* __restrict__ gkeys, uint32_t n_keys, const PaMeta* __restrict__ meta,
     uint32_t nbins, uint32_t n_models, double margin, uint32_t* __restrict__ nfreqs, uint8_t* __restrict__ log2_frame,
-    uint8_t* __restrict__ status, uint32_t* __restrict__ max_log2)
+    uint8_t* __restrict__ status, uint32_t* __restrict__ max_log2, const double* __restrict__ log2_tab)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t j = t & 7u;
@@ -1355,7 +1365,7 @@ __global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* _
         uint32_t top = 0;
         double xh = 0.0;
         if (st < 0)
-            pa_fit<false>(keys, mt.first, n_keys, mt.frame0_lg + 8u * round + j, mt.total, mt.inv_total, nullptr, failed, top, xh);
+            pa_fit<false>(keys, mt.first, n_keys, mt.frame0_lg + 8u * round + j, mt.total, mt.inv_total, nullptr, failed, top, xh, log2_tab);
         const uint32_t code = failed ? 0xFFFFFFFFu : top;
 #pragma unroll
         for (int jj = 0; jj < 8; jj++) { // every lane of the group walks the eight results in the reference's order
