@@ -73,6 +73,10 @@ SIGNATURES = {
     "b200ans_model_create": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u32p, C.c_size_t]),
     "b200ans_model_create_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t]),
     "b200ans_model_most_frequent": (C.c_int, [C.c_void_p, u32p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_uint64)]),
+    "b200ans_pa_remap_compress": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, u8p, C.c_size_t, u32p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "b200ans_pa_remap_decompress": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, u32p, C.c_size_t, u8p, C.c_size_t]),
+    "b200ans_pa_remap_compress_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "b200ans_pa_remap_decompress_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "b200ans_byte_compress": (C.c_int, [C.c_void_p, u8p, C.c_size_t, u8p, C.c_size_t, C.POINTER(C.c_size_t)]),
     "b200ans_byte_decompress": (C.c_int, [C.c_void_p, u8p, C.c_size_t, u8p, C.c_size_t]),
     "b200ans_byte_compress_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
@@ -431,6 +435,27 @@ class Codec:
 
     def rfold_prepare_device(self, f, d_raw_bins, nvalues, d_folded_bins):
         self._check(self.lib.b200ans_rfold_prepare_device(self.h, f, d_raw_bins, nvalues, d_folded_bins))
+
+    def pa_remap_compress(self, method, f, model_syms, data):
+        data = np.ascontiguousarray(data, dtype=np.uint32)
+        out = np.zeros(self.pa_bound(method, model_syms, data.size) + data.size * 4 + (data.size // model_syms + 2) * 48 + 256, dtype=np.uint8)
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_pa_remap_compress(self.h, method, f, model_syms, _p(out, u8p), out.size, _p(data, u32p), data.size, C.byref(nb)))
+        return out[: nb.value]
+
+    def pa_remap_decompress(self, method, f, blob, n):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        out = np.zeros(n, dtype=np.uint32)
+        self._check(self.lib.b200ans_pa_remap_decompress(self.h, method, f, _p(out, u32p), n, _p(blob, u8p), blob.size))
+        return out
+
+    def pa_remap_compress_device(self, method, f, model_syms, d_dst, cap, d_src, n):
+        nb = C.c_size_t()
+        self._check(self.lib.b200ans_pa_remap_compress_device(self.h, method, f, model_syms, d_dst, cap, d_src, n, C.byref(nb)))
+        return nb.value
+
+    def pa_remap_decompress_device(self, method, f, d_dst, n, d_src, nbytes):
+        self._check(self.lib.b200ans_pa_remap_decompress_device(self.h, method, f, d_dst, n, d_src, nbytes))
 
     def byte_compress(self, data):
         data = np.ascontiguousarray(data, dtype=np.uint8)

@@ -22,6 +22,7 @@
 #include "kernels.cuh"
 #include "lpb_kernels.cuh"
 #include "lpb3_kernels.cuh"
+#include "remap_kernels.cuh"
 #include "rfold_kernels.cuh"
 #include "pa_kernels.cuh"
 
@@ -76,6 +77,7 @@ struct Header {
 };
 static_assert(sizeof(Header) == B200ANS_HEADER_BYTES, "container header is 64 bytes");
 constexpr uint32_t kFlagPseudoAdaptive = 1u; // Header::flags bit 0: one model per block (pseudo-adaptive container)
+constexpr uint32_t kFlagRemap = 2u;          // Header::flags bit 1: per-block dense-rank alphabets in front of a pseudo-adaptive container of the ranks
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -162,7 +164,7 @@ struct b200ans_ctx {
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
 
     // grow-only device buffers
-    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_syms, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, io_bytes, pa_nfreqs, pa_pre, pa_keys, pa_log2tab;
+    DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_syms, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, io_bytes, pa_nfreqs, pa_pre, pa_keys, pa_log2tab, rm_ranks, rm_vals, rm_sigma, rm_alpha, rm_bytes, rm_offsets, rm_err;
     bool pa_log2_ready = false;
     // ANSrfold on the device (rfold_kernels.cuh): raw histogram, selection state, candidates, hash of the hot values
     DevBuf rf_sbuckets, rf_stags, rf_fast, rf_cand, rf_ctags, rf_cdisp, rf_cslot, rf_ccount, rf_sketch; // the fast route (rfold_kernels.cuh)
@@ -369,7 +371,7 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (DevBuf* b : { &c->bins, &c->small, &c->scratch, &c->block_bytes, &c->offsets, &c->enc_table, &c->mapping,
-             &c->dec_slots, &c->dec_syms, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->io_bytes, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys, &c->pa_log2tab,
+             &c->dec_slots, &c->dec_syms, &c->dec_bits, &c->dec_bits_pure, &c->dec_cnt, &c->dec_ent, &c->io_in, &c->io_out, &c->io_bytes, &c->pa_nfreqs, &c->pa_pre, &c->pa_keys, &c->pa_log2tab, &c->rm_ranks, &c->rm_vals, &c->rm_sigma, &c->rm_alpha, &c->rm_bytes, &c->rm_offsets, &c->rm_err,
              &c->rf_sbuckets, &c->rf_stags, &c->rf_fast, &c->rf_cand, &c->rf_ctags, &c->rf_cdisp, &c->rf_cslot, &c->rf_ccount, &c->rf_sketch,
              &c->rf_raw, &c->rf_raw32, &c->rf_state, &c->rf_hist, &c->rf_tiles, &c->rf_cand_count, &c->rf_cand_value, &c->rf_most, &c->rf_tags, &c->rf_disp,
              &c->enc_table_rf })
@@ -3633,3 +3635,203 @@ try {
     return rc;
 }
 B200ANS_CATCH_INT
+
+// ==========================================================================================
+// pseudo-adaptive mode with the driver's dense-rank alphabet remap (src/pseudo_adaptive.cpp:83-125; remap_kernels.cuh)
+// ==========================================================================================
+// Container: [header, flags = pseudo-adaptive | remap; reserved[0..7] = bytes of the alphabet section; payload_bytes =
+// bytes of the inner container][u32 alphabet bytes of block b][pad to 16][alphabets, each 16-byte aligned:
+// [sigma][universe][interp of the running sums], byte for byte what the driver writes in front of block b]
+// [the pseudo-adaptive container of the RANKS (b200ans_pa_compress_device): prelude(b) + payload(b) = T::encode(ranks of b)]
+extern "C" int b200ans_pa_remap_compress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms, uint8_t* d_dst, size_t cap,
+    const uint32_t* d_src, size_t n, size_t* out_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!d_dst || !out_bytes || (!d_src && n) || (reinterpret_cast<uintptr_t>(d_src) & 15) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
+        return c->fail(B200ANS_E_ARG, "pa_remap_compress: bad argument (device buffers must be 16-byte aligned)");
+    if (method != METHOD_MSB)
+        return c->fail(B200ANS_E_ARG, "pa_remap_compress: the remapped blocks are coded with ANSmsb (per-block plain ANS is not offered)");
+    RET(pa_check(c, method, f, model_syms));
+    CU(c, cudaSetDevice(c->device));
+    const uint64_t nm64 = (n + model_syms - 1) / model_syms;
+    if (nm64 > (uint64_t(1) << 24))
+        return c->fail(B200ANS_E_ARG, "pa_remap_compress: more than 2^24 blocks");
+    const uint32_t nm = uint32_t(nm64);
+    Header h {};
+    h.magic = B200ANS_MAGIC;
+    h.version = 1;
+    h.method = uint8_t(method);
+    h.fidelity = uint8_t(f);
+    h.n_symbols = n;
+    h.block_syms = model_syms;
+    h.n_blocks = nm;
+    h.flags = kFlagPseudoAdaptive | kFlagRemap;
+    const size_t table_at = B200ANS_HEADER_BYTES;
+    const size_t alpha_at = align_up(table_at + size_t(nm) * 4, 16);
+    if (cap < alpha_at)
+        return c->fail(B200ANS_E_CAPACITY, "pa_remap_compress: destination too small");
+    if (n == 0) {
+        CU(c, cudaMemcpyAsync(d_dst, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        *out_bytes = B200ANS_HEADER_BYTES;
+        return B200ANS_OK;
+    }
+    // the value range decides the shared-memory bitmap
+    CU(c, cudaMemsetAsync(c->small.p, 0, 64, c->stream));
+    RET(b200ans_max_device(c, d_src, n, c->d_max()));
+    RET(read_small(c));
+    const uint32_t max_value = c->h_small()->max_value;
+    if (max_value > kRemapMaxValue || remap_smem_bytes(max_value) > c->max_smem)
+        return c->fail(B200ANS_E_DOMAIN, "pa_remap_compress: the block alphabets are ranked in shared memory: values up to 2^20 + 2^17");
+    const uint64_t alpha_stride = align_up(size_t(8) + size_t(4) * std::min<size_t>(model_syms, size_t(max_value) + 1) + 16, 16);
+    CU(c, c->rm_ranks.reserve(align_up(n * 4, 16)));
+    CU(c, c->rm_vals.reserve(size_t(nm) * model_syms * 4));
+    CU(c, c->rm_sigma.reserve(size_t(nm) * 4));
+    CU(c, c->rm_alpha.reserve(size_t(nm) * alpha_stride));
+    CU(c, c->rm_bytes.reserve(size_t(nm) * 4));
+    CU(c, c->rm_offsets.reserve(size_t(nm) * 8));
+    CU(c, c->rm_err.reserve(16));
+    CU(c, cudaMemsetAsync(c->rm_err.p, 0, 16, c->stream));
+    const size_t smem = remap_smem_bytes(max_value);
+    CU(c, cudaFuncSetAttribute(remap_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    const int per_sm = int(std::max<size_t>(1, std::min<size_t>(2, c->max_smem_sm / (smem + 4096))));
+    remap_block_kernel<<<int(std::min<uint32_t>(nm, uint32_t(c->num_sms * per_sm))), kRemapThreads, smem, c->stream>>>(d_src, n, model_syms, nm,
+        max_value, c->rm_ranks.as<uint32_t>(), c->rm_vals.as<uint32_t>(), c->rm_sigma.as<uint32_t>());
+    remap_alpha_kernel<<<(nm + kRemapEncThreads / 32 - 1) / (kRemapEncThreads / 32), kRemapEncThreads, 0, c->stream>>>(c->rm_vals.as<uint32_t>(),
+        c->rm_sigma.as<uint32_t>(), model_syms, nm, c->rm_alpha.as<uint8_t>(), alpha_stride, c->rm_bytes.as<uint32_t>(), c->rm_err.as<uint32_t>());
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(c->rm_bytes.as<uint32_t>(), nm, c->rm_offsets.as<uint64_t>(), c->d_totals(), nullptr);
+    const int cgrid = int(std::max<uint32_t>(1, std::min<uint32_t>((nm + 7) / 8, uint32_t(c->num_sms) * 8)));
+    compact_kernel<<<cgrid, 256, 0, c->stream>>>(c->rm_alpha.as<uint8_t>(), alpha_stride, c->rm_bytes.as<uint32_t>(), c->rm_offsets.as<uint64_t>(), nm,
+        d_dst + alpha_at, reinterpret_cast<uint32_t*>(d_dst + table_at), uint64_t(cap - alpha_at));
+    c->stats.launches += 4;
+    CU(c, cudaGetLastError());
+    uint32_t err = 0;
+    CU(c, cudaMemcpyAsync(&err, c->rm_err.p, 4, cudaMemcpyDeviceToHost, c->stream));
+    RET(read_small(c));
+    if (err)
+        return c->fail(B200ANS_E_DOMAIN, "pa_remap_compress: the running sums of a block's alphabet exceed 32 bits (outside the reference driver's working domain)");
+    const uint64_t alpha_total = c->h_small()->totals[0];
+    const size_t inner_at = alpha_at + alpha_total;
+    if (cap < inner_at + B200ANS_HEADER_BYTES)
+        return c->fail(B200ANS_E_CAPACITY, "pa_remap_compress: destination too small");
+    size_t inner_bytes = 0;
+    RET(b200ans_pa_compress_device(c, method, f, model_syms, d_dst + inner_at, cap - inner_at, c->rm_ranks.as<uint32_t>(), n, &inner_bytes));
+    h.payload_bytes = inner_bytes;
+    std::memcpy(h.reserved, &alpha_total, 8);
+    CU(c, cudaMemcpyAsync(d_dst, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    *out_bytes = inner_at + inner_bytes;
+    c->stats.total_bytes = *out_bytes;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_pa_remap_decompress_device(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, size_t n, const uint8_t* d_src,
+    size_t src_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!d_dst && n) || !d_src || (reinterpret_cast<uintptr_t>(d_src) & 15))
+        return c->fail(B200ANS_E_ARG, "pa_remap_decompress: bad argument (d_src must be 16-byte aligned)");
+    CU(c, cudaSetDevice(c->device));
+    if (src_bytes < B200ANS_HEADER_BYTES)
+        return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: shorter than a header");
+    Header h;
+    CU(c, cudaMemcpyAsync(&h, d_src, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (h.magic != B200ANS_MAGIC || h.version != 1 || h.flags != (kFlagPseudoAdaptive | kFlagRemap))
+        return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: not a remapped pseudo-adaptive container");
+    if (h.method != method || method != METHOD_MSB)
+        return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: container was written by another method");
+    if (h.n_symbols != n)
+        return c->fail(B200ANS_E_ARG, "pa_remap_decompress: symbol count does not match the container");
+    if (n == 0)
+        return B200ANS_OK;
+    const uint32_t model_syms = h.block_syms;
+    if (pa_check(c, method, f, model_syms) != B200ANS_OK || h.n_blocks != (n + model_syms - 1) / model_syms)
+        return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: inconsistent block geometry");
+    const uint32_t nm = h.n_blocks;
+    uint64_t alpha_total = 0;
+    std::memcpy(&alpha_total, h.reserved, 8);
+    const size_t table_at = B200ANS_HEADER_BYTES;
+    const size_t alpha_at = align_up(table_at + size_t(nm) * 4, 16);
+    if (alpha_at > src_bytes || alpha_total > src_bytes - alpha_at || (alpha_total & 15) || h.payload_bytes > src_bytes - alpha_at - alpha_total
+        || h.payload_bytes < B200ANS_HEADER_BYTES)
+        return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: container truncated");
+    const size_t inner_at = alpha_at + alpha_total;
+    CU(c, c->rm_ranks.reserve(align_up(n * 4, 32)));
+    CU(c, c->rm_vals.reserve(size_t(nm) * model_syms * 4));
+    CU(c, c->rm_sigma.reserve(size_t(nm) * 4));
+    CU(c, c->rm_offsets.reserve(size_t(nm) * 8));
+    CU(c, c->rm_err.reserve(16));
+    CU(c, cudaMemsetAsync(c->rm_err.p, 0, 16, c->stream));
+    CU(c, cudaMemsetAsync(c->small.p, 0, 64, c->stream));
+    const uint32_t* d_sizes = reinterpret_cast<const uint32_t*>(d_src + table_at);
+    scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, nm, c->rm_offsets.as<uint64_t>(), c->d_totals(), nullptr);
+    remap_alpha_decode_kernel<<<(nm + kRemapAlphaThreads - 1) / kRemapAlphaThreads, kRemapAlphaThreads, 0, c->stream>>>(d_src + alpha_at,
+        c->rm_offsets.as<uint64_t>(), d_sizes, alpha_total, model_syms, nm, c->rm_vals.as<uint32_t>(), c->rm_sigma.as<uint32_t>(), c->rm_err.as<uint32_t>());
+    c->stats.launches += 2;
+    CU(c, cudaGetLastError());
+    RET(read_small(c));
+    if (c->h_small()->totals[0] != alpha_total)
+        return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: alphabet size table does not add up");
+    RET(b200ans_pa_decompress_device(c, method, f, c->rm_ranks.as<uint32_t>(), n, d_src + inner_at, h.payload_bytes));
+    const int grid = int(std::max<size_t>(1, std::min<size_t>((n + 255) / 256, size_t(c->num_sms) * 16)));
+    unremap_kernel<<<grid, 256, 0, c->stream>>>(c->rm_ranks.as<uint32_t>(), n, model_syms, c->rm_vals.as<uint32_t>(), c->rm_sigma.as<uint32_t>(), d_dst,
+        c->rm_err.as<uint32_t>());
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    uint32_t err = 0;
+    CU(c, cudaMemcpyAsync(&err, c->rm_err.p, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (err)
+        return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: a block alphabet or a rank is corrupt");
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+// host buffers
+extern "C" int b200ans_pa_remap_compress(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms, uint8_t* dst, size_t cap, const uint32_t* src,
+    size_t n, size_t* out_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!dst || !out_bytes || (!src && n))
+        return c->fail(B200ANS_E_ARG, "pa_remap_compress: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    // the alphabets can take as much as the block itself (4 bytes per distinct value) on top of the coded ranks
+    const size_t bound = b200ans_pa_compress_bound(c, method, model_syms, n) + n * 4 + (n / std::max<uint32_t>(model_syms, 1u) + 2) * 48 + 256;
+    CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
+    CU(c, c->io_out.reserve(bound));
+    if (n)
+        CU(c, cudaMemcpyAsync(c->io_in.p, src, n * 4, cudaMemcpyHostToDevice, c->stream));
+    size_t bytes = 0;
+    RET(b200ans_pa_remap_compress_device(c, method, f, model_syms, c->io_out.as<uint8_t>(), c->io_out.cap, c->io_in.as<uint32_t>(), n, &bytes));
+    if (bytes > cap)
+        return c->fail(B200ANS_E_CAPACITY, "pa_remap_compress: destination too small");
+    CU(c, cudaMemcpyAsync(dst, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    *out_bytes = bytes;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_pa_remap_decompress(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, size_t n, const uint8_t* src, size_t src_bytes)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if ((!dst && n) || !src)
+        return c->fail(B200ANS_E_ARG, "pa_remap_decompress: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, c->io_out.reserve(std::max<size_t>(align_up(src_bytes, 16), 64)));
+    CU(c, c->io_in.reserve(std::max<size_t>(align_up(n * 4, 32), 32)));
+    CU(c, cudaMemcpyAsync(c->io_out.p, src, src_bytes, cudaMemcpyHostToDevice, c->stream));
+    RET(b200ans_pa_remap_decompress_device(c, method, f, c->io_in.as<uint32_t>(), n, c->io_out.as<uint8_t>(), src_bytes));
+    if (n)
+        CU(c, cudaMemcpyAsync(dst, c->io_in.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+

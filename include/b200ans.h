@@ -271,6 +271,22 @@ int b200ans_pa_compress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, 
 int b200ans_pa_decompress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* d_dst, size_t n,
                                  const uint8_t* d_src, size_t src_bytes);
 
+/* ---- pseudo-adaptive mode with the driver's dense-rank alphabet remap (src/pseudo_adaptive.cpp:83-125) ----
+ * Per block of model_syms symbols: the values that occur become the ranks 1..sigma, the block is coded as those ranks
+ * with ANSmsb (its own model, as b200ans_pa_compress), and the block alphabet goes in front as the driver writes it:
+ * [u32 sigma][u32 universe][interpolative code of the running sums of the sorted values].  Alphabet bytes and
+ * prelude + payload of every block are byte-identical to the driver's output for that block (a block with one distinct
+ * value still gets a coded body here; the driver writes the alphabet only).  Values up to 2^20 + 2^17 (the block's value
+ * range is ranked in shared memory); an alphabet whose running sums pass 32 bits is B200ANS_E_DOMAIN, as it is outside
+ * the driver's own working domain.  method: B200ANS_METHOD_MSB (per-block plain ANS is not offered). */
+int b200ans_pa_remap_compress(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t model_syms, uint8_t* dst, size_t dst_capacity,
+    const uint32_t* src, size_t n, size_t* out_bytes);
+int b200ans_pa_remap_decompress(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* dst, size_t n, const uint8_t* src, size_t src_bytes);
+int b200ans_pa_remap_compress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t model_syms, uint8_t* d_dst, size_t dst_capacity,
+    const uint32_t* d_src, size_t n, size_t* out_bytes);
+int b200ans_pa_remap_decompress_device(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* d_dst, size_t n, const uint8_t* d_src,
+    size_t src_bytes);
+
 /* ---- ans_byte (ans_byte.hpp): the byte coder behind the vbyteANS / streamvbyteANS baselines (methods.hpp:432-482) ----
  * B200ANS_METHOD_BYTE: 256 symbols, frame <= 4096, the reference's byte normaliser (ans_byte.hpp:41-97) and prelude
  * (:122-137), the same 4-state coder as plain ANS (:236-305).  The method also runs through every uint32 entry point
