@@ -162,6 +162,7 @@ struct b200ans_ctx {
     static constexpr int kPipeChunks = 8;
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
+    cudaEvent_t ev_side[2] {}; // fork / join of work that runs beside the main stream inside one call (remap: alphabets beside ranks)
 
     // grow-only device buffers
     DevBuf bins, small, scratch, block_bytes, offsets, enc_table, mapping, dec_slots, dec_syms, dec_bits, dec_bits_pure, dec_cnt, dec_ent, io_in, io_out, io_bytes, pa_nfreqs, pa_pre, pa_keys, pa_log2tab, rm_ranks, rm_vals, rm_sigma, rm_alpha, rm_bytes, rm_offsets, rm_err;
@@ -386,6 +387,9 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
         if (e)
             cudaEventDestroy(e);
     for (auto& e : c->ev_dec)
+        if (e)
+            cudaEventDestroy(e);
+    for (auto& e : c->ev_side)
         if (e)
             cudaEventDestroy(e);
     if (c->copy_in)
@@ -1605,6 +1609,89 @@ template <int METHOD, class CFG> int launch_lpb3_encode_cfg(b200ans_ctx* c, cons
     return B200ANS_OK;
 }
 
+// Pseudo-adaptive mode through the L3 encoder (lpb3_kernels.cuh, PA = true): every lane keeps its block's model in shared
+// memory.  Returns B200ANS_OK after a launch, 1 when the models do not fit one wave of warps (the caller then takes the
+// four-lanes-per-block coder of pa_kernels.cuh).  B200ANS_NO_PA3=1 (testing) declines always.
+struct Pa3Cfg {
+    static constexpr int TQ = 4, STAGES = 2, DQ = 2, MAXW = 8;
+};
+template <int METHOD> int launch_pa3_encode(b200ans_ctx* c, const EncArgs& a, uint32_t max_lg)
+{
+    using CFG = Pa3Cfg;
+    constexpr int TQ = CFG::TQ;
+    if (a.block_syms % 128u != 0u || a.n / a.block_syms == 0 || max_lg > 15u || env_int("B200ANS_NO_PA3", 0) || env_int("B200ANS_NO_L3", 0))
+        return 1;
+    tensor_map_encode_fn encode = tensor_map_encoder();
+    if (!encode)
+        return 1;
+    Enc3Args g {};
+    g.pa_rcp_n = std::min<uint32_t>(4097u, (1u << max_lg) + 1u);
+    g.pa_tab_stride = uint32_t(align_up((size_t(a.pa_syms) + 2) * 2, 8));
+    if (((g.pa_tab_stride >> 3) & 1u) == 0u)
+        g.pa_tab_stride += 8; // an odd number of 8-byte bank pairs between the lanes' tables
+    const uint32_t n_tasks = (a.n_blocks + 31) / 32;
+    const uint32_t sms = uint32_t(c->num_sms);
+    const size_t fixed = size_t(g.pa_rcp_n) * 8 + 2048; // reciprocals + alignment slack of the tiles
+    const size_t per_warp = size_t(32) * g.pa_tab_stride + L3Geom<CFG>::kWarpBytes;
+    if (c->max_smem < fixed + per_warp)
+        return 1;
+    const uint32_t max_warps = uint32_t(std::min<size_t>(CFG::MAXW, (c->max_smem - fixed) / per_warp));
+    const uint32_t want_warps = (n_tasks + sms - 1) / sms;
+    if (max_warps < std::min<uint32_t>(want_warps, 4u)) // more than one wave of tasks, or fewer than four warps per SM
+        return 1;
+    const uint32_t waves = (n_tasks + sms * max_warps - 1) / (sms * max_warps);
+    const uint32_t warps = std::max<uint32_t>(1, std::min<uint32_t>(max_warps, (n_tasks + sms * waves - 1) / (sms * waves)));
+    const uint32_t grid = std::min<uint32_t>(sms, (n_tasks + warps - 1) / warps);
+    g.n_full_blocks = uint32_t(a.n / a.block_syms);
+    g.max_value = std::min(max_value_below(METHOD, a.fidelity, a.pa_syms), (1u << 30) - 1u);
+
+    CUtensorMap tmap;
+    const cuuint64_t dims[2] = { a.block_syms, g.n_full_blocks };
+    const cuuint64_t strides[1] = { cuuint64_t(a.block_syms) * 4 };
+    const cuuint32_t box[2] = { 4 * TQ, 32 };
+    const cuuint32_t estr[2] = { 1, 1 };
+    const CUresult rc = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint32_t*>(a.in), dims, strides, box, estr,
+        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS)
+        return 1;
+    const size_t smem = align_up(size_t(g.pa_rcp_n) * 8 + size_t(warps) * 32 * g.pa_tab_stride, 1024) + 1024 + size_t(warps) * L3Geom<CFG>::kWarpBytes;
+    auto k = lpb3_encode_kernel<METHOD, 0, CFG, true>;
+    auto k1 = lpb3_encode_kernel<METHOD, 1, CFG, true>;
+    const bool f1 = METHOD == METHOD_FOLD && a.fidelity == 1;
+    CU(c, cudaFuncSetAttribute(f1 ? k1 : k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    if (f1)
+        k1<<<grid, warps * 32, smem, c->stream>>>(a, g, tmap);
+    else
+        k<<<grid, warps * 32, smem, c->stream>>>(a, g, tmap);
+    set_name(c->stats.encode_kernel, "lpb3_encode_kernel<PA>");
+    c->stats.launches++;
+    CU(c, cudaGetLastError());
+    return B200ANS_OK;
+}
+
+// ... and through the L3 decoder (TABLE = DEC_PA_LANE): the finest bucket index (2^9 .. 2^6 entries per model) that
+// still lets four warps per SM -- or one wave of tasks -- be resident.  Returns 1 when even the coarsest does not.
+template <int METHOD> int launch_pa3_decode(b200ans_ctx* c, DecArgs a, uint32_t max_lg)
+{
+    constexpr int MAXW = 8;
+    if (max_lg > 15u || (reinterpret_cast<uintptr_t>(a.out) & 15) != 0 || a.block_syms % 8u != 0u || env_int("B200ANS_NO_PA3", 0)
+        || env_int("B200ANS_NO_L3", 0))
+        return 1;
+    const uint32_t n_tasks = (a.n_blocks + 31) / 32;
+    const uint32_t want_warps = std::min<uint32_t>(4u, (n_tasks + uint32_t(c->num_sms) - 1) / uint32_t(c->num_sms));
+    const size_t room = c->max_smem - 1024 - 128;
+    for (uint32_t blog = uint32_t(std::max(6, std::min(9, env_int("B200ANS_PA3_BLOG", 9)))); blog >= 6u; blog--) {
+        const uint32_t stride = pa3_dec_tab_stride(a.pa_syms, blog);
+        const size_t warp_bytes = size_t(32) * stride + L3DecGeom<1>::kWarpBytes;
+        if (room / warp_bytes < want_warps)
+            continue;
+        a.pa_bucket_log2 = blog;
+        a.pa_tab_stride = stride;
+        return launch_lpb(c, lpb3_decode_kernel<METHOD, DEC_PA_LANE, 1, MAXW>, 0, warp_bytes, a.n_blocks, &a, MAXW);
+    }
+    return 1;
+}
+
 template <int METHOD> int launch_lpb3_encode_t(b200ans_ctx* c, const EncArgs& a)
 {
     return launch_lpb3_encode_cfg<METHOD, L3Cfg>(c, a);
@@ -1799,6 +1886,8 @@ int ensure_side_streams(b200ans_ctx* c)
     for (auto& e : c->ev_in)
         CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto& e : c->ev_dec)
+        CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : c->ev_side)
         CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     return B200ANS_OK;
 }
@@ -3182,8 +3271,19 @@ try {
         CU(c, c->pa_keys.reserve(keys_bytes + size_t(nm) * sizeof(PaMeta)));
         uint64_t* d_keys = c->pa_keys.as<uint64_t>();
         PaMeta* d_meta = reinterpret_cast<PaMeta*>(c->pa_keys.as<uint8_t>() + keys_bytes);
-        pa_sort_kernel<<<grid, kPaNormThreads, smem, c->stream>>>(c->bins.as<uint32_t>(), nbins, nm, c->h_approx, d_keys, d_meta,
-            c->pa_nfreqs.as<uint32_t>());
+        // counting sort (one warp per model) whenever the symbols with large counts fit its side list; B200ANS_PA_BITONIC=1
+        // (testing) keeps the bitonic sort of the first version
+        if (uint64_t(model_syms) <= uint64_t(kPaSortSmall) * kPaSortBig && !env_int("B200ANS_PA_BITONIC", 0)) {
+            const size_t csmem = pa_sort_smem_bytes();
+            CU(c, cudaFuncSetAttribute(pa_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(csmem)));
+            const uint32_t per_sm = uint32_t(std::max<size_t>(1, (c->max_smem_sm - 4096) / (csmem + 1024)));
+            const uint32_t cgrid = std::min<uint32_t>((nm + kPaSortWarps - 1) / kPaSortWarps, uint32_t(c->num_sms) * per_sm);
+            pa_sort_kernel<<<cgrid, kPaSortWarps * 32, csmem, c->stream>>>(c->bins.as<uint32_t>(), nbins, n_keys, nm, c->h_approx, d_keys, d_meta,
+                c->pa_nfreqs.as<uint32_t>(), c->pa_log2tab.as<double>());
+        } else {
+            pa_sort_bitonic_kernel<<<grid, kPaNormThreads, smem, c->stream>>>(c->bins.as<uint32_t>(), nbins, nm, c->h_approx, d_keys, d_meta,
+                c->pa_nfreqs.as<uint32_t>());
+        }
         const uint32_t fit_threads = nm * 8u;
         pa_fit_kernel<<<(fit_threads + kPaFitThreads - 1) / kPaFitThreads, kPaFitThreads, 0, c->stream>>>(d_keys, n_keys, d_meta, nbins, nm,
             margin, c->pa_nfreqs.as<uint32_t>(), d_lg, d_status, c->d_max_log2(), c->pa_log2tab.as<double>());
@@ -3237,9 +3337,8 @@ try {
     const float ms_host = float(now_ms() - t0);
 
     // Preludes on the device (the counts are no longer needed: their buffer is the coder's scratch), then their sizes
-    // are scanned.  The prelude coder is one thread per model (a serial bit stream each: 3.5 warps per SM for 16 384
-    // models) and needs only the frequencies, as the encoder does: it runs NEXT TO the encoder on a side stream, and
-    // its total comes back while the encoder runs.
+    // are scanned.  The prelude coder (one warp per model) needs only the frequencies, as the encoder does: it runs
+    // NEXT TO the encoder on a side stream, and its total comes back while the encoder runs.
     RET(ensure_side_streams(c));
     CU(c, cudaEventRecord(c->ev[6], c->stream));
     CU(c, cudaStreamWaitEvent(c->copy_in, c->ev[6], 0));
@@ -3248,8 +3347,14 @@ try {
     uint8_t* d_pre = c->pa_pre.as<uint8_t>();
     uint64_t* d_pre_off = reinterpret_cast<uint64_t*>(d_pre + size_t(nm) * pre_stride);
     uint32_t* d_pre_bytes = reinterpret_cast<uint32_t*>(d_pre_off + nm);
-    pa_prelude_encode_kernel<<<(nm + kPaPreThreads - 1) / kPaPreThreads, kPaPreThreads, 0, c->copy_in>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm,
-        d_lg, c->bins.as<uint32_t>(), d_pre, pre_stride, d_pre_bytes);
+    {
+        const size_t smem = pa_prelude_enc_smem(nbins);
+        CU(c, cudaFuncSetAttribute(pa_prelude_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        const uint32_t per_sm = uint32_t(std::max<size_t>(1, std::min<size_t>(8, (c->max_smem_sm - 4096) / (smem + 1024))));
+        const uint32_t grid = std::min<uint32_t>((nm + kPaPreEncWarps - 1) / kPaPreEncWarps, uint32_t(c->num_sms) * per_sm);
+        pa_prelude_encode_kernel<<<grid, kPaPreEncWarps * 32, smem, c->copy_in>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, d_lg, d_pre, pre_stride,
+            d_pre_bytes);
+    }
     scan_block_sizes_kernel<<<1, 1024, 0, c->copy_in>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
     c->stats.launches += 2;
     CU(c, cudaGetLastError());
@@ -3295,7 +3400,14 @@ try {
         CU(c, cudaGetLastError());
     }
     CU(c, cudaEventRecord(c->ev[0], c->stream));
-    if (smem_tables) {
+    // first choice: a lane per block (the L3 encoder with per-lane models), when one wave of warps holds all the models
+    int rc3 = 1;
+    if (smem_tables)
+        rc3 = method == METHOD_MSB ? launch_pa3_encode<METHOD_MSB>(c, a, max_lg) : launch_pa3_encode<METHOD_FOLD>(c, a, max_lg);
+    if (rc3 < 0)
+        return rc3;
+    if (rc3 == B200ANS_OK) {
+    } else if (smem_tables) {
         auto k = method == METHOD_MSB ? pa_smem_encode_kernel<METHOD_MSB> : pa_smem_encode_kernel<METHOD_FOLD>;
         CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
         k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
@@ -3455,8 +3567,10 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
     scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
     scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_pay_bytes, nm, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
     pa_prelude_decode_kernel<<<(nm + kPaPreThreads - 1) / kPaPreThreads, kPaPreThreads, 0, c->stream>>>(d_src + pre_at, d_pre_off, d_pre_bytes,
-        uint64_t(h.prelude_bytes), nbins, nm, c->bins.as<uint32_t>(), c->pa_nfreqs.as<uint32_t>(), d_lg, c->d_err(), c->d_max_log2(), c->d_max_symbol());
-    c->stats.launches += 3;
+        uint64_t(h.prelude_bytes), nbins, nm, c->bins.as<uint32_t>(), c->pa_nfreqs.as<uint32_t>(), d_lg);
+    pa_prelude_finish_kernel<<<(nm + kPaPreFinishWarps - 1) / kPaPreFinishWarps, kPaPreFinishWarps * 32, 0, c->stream>>>(c->bins.as<uint32_t>(), nbins, nm,
+        c->pa_nfreqs.as<uint32_t>(), d_lg, c->d_err(), c->d_max_log2(), c->d_max_symbol());
+    c->stats.launches += 4;
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(c->ev[4], c->stream));
     RET(read_small(c));
@@ -3495,8 +3609,18 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
         if (pl.max_warps >= want_warps || blog_env)
             break;
     }
-    const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && c->h_small()->max_log2 <= 16u && pl.warps >= 2u;
+    // (frames of 2^16 slots go to the slot tables: cum[] is 16 bits wide and the searches compare it)
+    const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && c->h_small()->max_log2 <= 15u && pl.warps >= 2u;
     set_name(c->stats.decode_kernel, smem_tables ? "pa_smem_decode_kernel" : "decode_kernel");
+    const uint32_t max_lg = c->h_small()->max_log2;
+    auto pa3 = [&](const DecArgs& ar) { // first choice: a lane per block (the L3 decoder with per-lane models)
+        if (!smem_tables)
+            return 1;
+        const int rc = method == METHOD_MSB ? launch_pa3_decode<METHOD_MSB>(c, ar, max_lg) : launch_pa3_decode<METHOD_FOLD>(c, ar, max_lg);
+        if (rc == B200ANS_OK)
+            set_name(c->stats.decode_kernel, "lpb3_decode_kernel<PA>");
+        return rc;
+    };
     if (smem_tables && h_src && runs > 1) {
         // one launch per run of models; the pointers of the argument block move to the run's first model
         CU(c, cudaEventRecord(c->ev[0], c->stream));
@@ -3516,8 +3640,13 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
             ar.pa_nfreqs = a.pa_nfreqs + size_t(b0) * nbins;
             const PaLaunch pr = pa_launch_shape(c, 0, warp_bytes, (b1 - b0 + 7) / 8);
             CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
-            k<<<pr.grid, pr.warps * 32, pr.smem, c->stream>>>(ar);
-            c->stats.launches++;
+            const int rc3 = pa3(ar);
+            if (rc3 < 0)
+                return rc3;
+            if (rc3 != B200ANS_OK) {
+                k<<<pr.grid, pr.warps * 32, pr.smem, c->stream>>>(ar);
+                c->stats.launches++;
+            }
             CU(c, cudaGetLastError());
             CU(c, cudaEventRecord(c->ev_dec[r], c->stream));
             CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_dec[r], 0));
@@ -3536,10 +3665,15 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
             CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
     if (smem_tables) {
         CU(c, cudaEventRecord(c->ev[0], c->stream));
-        auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
-        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
-        k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
-        c->stats.launches++;
+        const int rc3 = pa3(a);
+        if (rc3 < 0)
+            return rc3;
+        if (rc3 != B200ANS_OK) {
+            auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
+            CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
+            k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
+            c->stats.launches++;
+        }
         CU(c, cudaGetLastError());
     } else {
         const uint64_t slot_stride = uint64_t(1) << c->h_small()->max_log2;
@@ -3769,14 +3903,29 @@ try {
     CU(c, cudaMemsetAsync(c->small.p, 0, 64, c->stream));
     const uint32_t* d_sizes = reinterpret_cast<const uint32_t*>(d_src + table_at);
     scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, nm, c->rm_offsets.as<uint64_t>(), c->d_totals(), nullptr);
-    remap_alpha_decode_kernel<<<(nm + kRemapAlphaThreads - 1) / kRemapAlphaThreads, kRemapAlphaThreads, 0, c->stream>>>(d_src + alpha_at,
-        c->rm_offsets.as<uint64_t>(), d_sizes, alpha_total, model_syms, nm, c->rm_vals.as<uint32_t>(), c->rm_sigma.as<uint32_t>(), c->rm_err.as<uint32_t>());
-    c->stats.launches += 2;
+    c->stats.launches++;
     CU(c, cudaGetLastError());
     RET(read_small(c));
     if (c->h_small()->totals[0] != alpha_total)
         return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: alphabet size table does not add up");
-    RET(b200ans_pa_decompress_device(c, method, f, c->rm_ranks.as<uint32_t>(), n, d_src + inner_at, h.payload_bytes));
+    // The alphabets (a serial bit stream per block, one thread each: 3.5 warps per SM for 16 384 blocks) are decoded on a
+    // side stream NEXT TO the ranks: both are chains of dependent steps that leave most issue slots free.
+    RET(ensure_side_streams(c));
+    CU(c, cudaEventRecord(c->ev_side[0], c->stream));
+    CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_side[0], 0));
+    remap_alpha_decode_kernel<<<(nm + kRemapAlphaThreads - 1) / kRemapAlphaThreads, kRemapAlphaThreads, 0, c->copy_out>>>(d_src + alpha_at,
+        c->rm_offsets.as<uint64_t>(), d_sizes, alpha_total, model_syms, nm, c->rm_vals.as<uint32_t>(), c->rm_sigma.as<uint32_t>());
+    remap_alpha_finish_kernel<<<(nm + kRemapEncThreads / 32 - 1) / (kRemapEncThreads / 32), kRemapEncThreads, 0, c->copy_out>>>(c->rm_vals.as<uint32_t>(),
+        c->rm_sigma.as<uint32_t>(), model_syms, nm, c->rm_err.as<uint32_t>());
+    c->stats.launches += 2;
+    CU(c, cudaGetLastError());
+    CU(c, cudaEventRecord(c->ev_side[1], c->copy_out));
+    const int inner = b200ans_pa_decompress_device(c, method, f, c->rm_ranks.as<uint32_t>(), n, d_src + inner_at, h.payload_bytes);
+    CU(c, cudaStreamWaitEvent(c->stream, c->ev_side[1], 0)); // (also on failure: nothing of this call may still be running when it returns)
+    if (inner != B200ANS_OK) {
+        cudaStreamSynchronize(c->copy_out);
+        return inner;
+    }
     const int grid = int(std::max<size_t>(1, std::min<size_t>((n + 255) / 256, size_t(c->num_sms) * 16)));
     unremap_kernel<<<grid, 256, 0, c->stream>>>(c->rm_ranks.as<uint32_t>(), n, model_syms, c->rm_vals.as<uint32_t>(), c->rm_sigma.as<uint32_t>(), d_dst,
         c->rm_err.as<uint32_t>());

@@ -62,6 +62,9 @@ struct Enc3Args {
     const uint16_t* rf_disp; // 2^(32 - bshift) displacements
     uint32_t rf_mul;
     uint32_t rf_bshift;
+    // PA (pseudo-adaptive mode: every block has its own model, EncArgs::pa_*): per-lane prefix-sum tables
+    uint32_t pa_rcp_n;      // reciprocals kept per CTA: frequencies below this never divide
+    uint32_t pa_tab_stride; // bytes between the lanes' tables (a multiple of 8)
 };
 
 // RFOLD: where the hash lives in shared memory
@@ -211,7 +214,14 @@ __device__ __forceinline__ uint32_t l3_entry_addr(uint32_t& v, uint32_t lane_tb,
     return mad_lo(xs, ent_stride, mad_lo(k8, k8_stride, lane_tb));
 }
 
-template <int METHOD, int FID, class CFG>
+//
+// PA = pseudo-adaptive mode (src/pseudo_adaptive.cpp:64-177: one model per block): the lane's block has its OWN model, so
+// instead of the CTA's replicated table every lane keeps the prefix sums of its model's frequencies (u16 per symbol,
+// built by the warp at the start of the task from EncArgs::pa_nfreqs) in its own stretch of shared memory; base and
+// frequency are two 16-bit loads, the reciprocal comes from a per-CTA table indexed by the frequency.  Everything else
+// -- TMA tiles, packer, state update, drains -- is the same code.  (The first pseudo-adaptive coders, pa_kernels.cuh,
+// give each block four lanes, one per state: 150 instructions per 4-symbol step and a shuffle-scan on the chain.)
+template <int METHOD, int FID, class CFG, bool PA = false>
 __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const EncArgs a, const Enc3Args g, const __grid_constant__ CUtensorMap tmap)
 {
     constexpr int TQ = CFG::TQ, STAGES = CFG::STAGES, DQ = CFG::DQ;
@@ -225,7 +235,7 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
     const uint32_t warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0); // warp-uniform for the compiler too
     const uint32_t s_base = smem_u32(smem_raw);
     const uint32_t s_table = s_base;
-    const uint32_t table_bytes = (g.table_alloc << g.rep_log2) * 16u;
+    const uint32_t table_bytes = PA ? g.pa_rcp_n * 8u + warps_per_cta * 32u * g.pa_tab_stride : (g.table_alloc << g.rep_log2) * 16u;
     // RFOLD: [tags: K x u32][displacements: u16] between the table and the tiles
     L3Rfold rf {};
     uint32_t aux_bytes = 0;
@@ -247,7 +257,12 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
     const uint32_t s_bars = s_rows + warps_per_cta * 32u * kOutRow;
 
     // ---- replicated table: entry e of replica r at ((e << rep_log2) + r) * 16 ---------------
-    {
+    if (PA) { // reciprocals by frequency; the lanes' tables follow per task
+        for (uint32_t i = threadIdx.x; i < g.pa_rcp_n; i += blockDim.x) {
+            const double r = i ? pa_reciprocal_up(i) : 0.0;
+            asm volatile("st.shared.f64 [%0], %1;" ::"r"(s_table + i * 8u), "d"(r) : "memory");
+        }
+    } else {
         const uint32_t total = g.table_alloc << g.rep_log2;
         const uint4* src = reinterpret_cast<const uint4*>(a.table);
         for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) {
@@ -271,12 +286,16 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
     }
     __syncthreads();
 
-    const uint32_t log2_frame = a.log2_frame;
-    const uint32_t frame = 1u << log2_frame;
+    uint32_t log2_frame = a.log2_frame; // (PA: the lane's own, set per task)
+    uint32_t frame = 1u << log2_frame;
     const uint32_t f = a.fidelity;
-    const uint32_t lower_hi = (log2_frame + 4u >= 32u) ? (1u << (log2_frame + 4u - 32u)) : 0u; // L = 16 M (ans_fold.hpp:91)
-    const uint32_t lower_lo = (log2_frame + 4u >= 32u) ? 0u : (1u << (log2_frame + 4u));
-    const uint32_t neg_bias = 0u - (0x43300000u << log2_frame); // cancels the double's exponent bits in q_hi * M
+    uint32_t lower_hi = (log2_frame + 4u >= 32u) ? (1u << (log2_frame + 4u - 32u)) : 0u; // L = 16 M (ans_fold.hpp:91)
+    uint32_t lower_lo = (log2_frame + 4u >= 32u) ? 0u : (1u << (log2_frame + 4u));
+    uint32_t neg_bias = 0u - (0x43300000u << log2_frame); // cancels the double's exponent bits in q_hi * M
+    const uint32_t pa_tabs = s_table + g.pa_rcp_n * 8u + warp * 32u * g.pa_tab_stride; // PA: the warp's 32 tables
+    const uint16_t* my_cum = reinterpret_cast<const uint16_t*>(smem_raw + g.pa_rcp_n * 8u + (warp * 32u + lane) * g.pa_tab_stride);
+    const double* pa_rcp = reinterpret_cast<const double*>(smem_raw);
+    bool pa_bad = false;
     const uint32_t ent_stride = 16u << g.rep_log2;
     const uint32_t step = (METHOD == METHOD_MSB) ? 256u : (255u << (f - 1u));
     const uint32_t k8_stride = (METHOD == METHOD_INT) ? 0u : (step * ent_stride) >> 3;
@@ -312,6 +331,78 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
         uint32_t flushed = 0;
         float badf = 0.f;
         uint32_t vmax = 0u;
+
+        if (PA) {
+            // the 32 models of the task: cum[s] = slots before symbol s for s in [0, syms], cum[syms + 1] = cum[syms]
+            // (a symbol beyond the model reads frequency 0 there), 128 symbols per step of the warp
+            const uint32_t syms = a.pa_syms; // multiple of 16
+            __syncwarp();
+            for (uint32_t j = 0; j < 32u; j++) {
+                const uint32_t m = min(blk0 + j, a.n_blocks - 1u);
+                const uint4* nf = reinterpret_cast<const uint4*>(a.pa_nfreqs + uint64_t(m) * a.pa_nbins);
+                const uint32_t tab = pa_tabs + j * g.pa_tab_stride;
+                uint32_t carry = 0;
+                for (uint32_t base = 0; base < syms; base += 128u) {
+                    const uint32_t s = base + 4u * lane;
+                    const uint4 q = s < syms ? __ldg(nf + (s >> 2)) : make_uint4(0u, 0u, 0u, 0u);
+                    const uint32_t mine = q.x + q.y + q.z + q.w;
+                    uint32_t incl = mine;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= uint32_t(o))
+                            incl += up;
+                    }
+                    const uint32_t c0 = carry + incl - mine, c1 = c0 + q.x, c2 = c1 + q.y, c3 = c2 + q.z;
+                    if (s < syms)
+                        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(tab + 2u * s), "r"((c0 & 0xFFFFu) | (c1 << 16)), "r"((c2 & 0xFFFFu) | (c3 << 16)) : "memory");
+                    carry += __shfl_sync(0xffffffffu, incl, 31);
+                }
+                if (lane == 0)
+                    sts32(tab + 2u * syms, (carry & 0xFFFFu) | (carry << 16));
+            }
+            __syncwarp();
+            log2_frame = a.pa_log2[min(blk, a.n_blocks - 1u)];
+            frame = 1u << log2_frame;
+            lower_hi = 0u; // log2 M <= 15 here
+            lower_lo = 1u << (log2_frame + 4u);
+            neg_bias = 0u - (0x43300000u << log2_frame);
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                xlo[c] = lower_lo;
+                xhi[c] = lower_hi;
+            }
+        }
+        // table entry of one value: {-freq, base, reciprocal}, 8 * (raw low bytes); v comes back as l3_entry_addr leaves it
+        auto entry = [&](uint32_t& v, bool active, uint32_t& k8, uint32_t& nfr, uint32_t& base, double& rcp) {
+            if (PA) {
+                uint32_t fl;
+                if (METHOD == METHOD_MSB)
+                    fl = bfind_u32((max(v, 1u) - 1u) | 1u);
+                else if (FID == 1)
+                    fl = bfind_u32(v | 1u);
+                else
+                    fl = bfind_u32(v | (1u << (f - 1u))) - (f - 1u);
+                k8 = fl & 0x18u;
+                const uint32_t pa_step = (METHOD == METHOD_MSB) ? 256u : (255u << (f - 1u));
+                const uint32_t sym = min(mad_lo(k8 >> 3, pa_step, v >> k8), a.pa_syms); // entry pa_syms: frequency 0
+                // (plain loads, not asm volatile: the compiler is free to overlap the four lookups of a quad)
+                const uint32_t c0 = my_cum[sym], c1 = my_cum[sym + 1u];
+                const uint32_t fr = (c1 - c0) & 0xFFFFu;
+                base = c0;
+                nfr = 0u - fr;
+                rcp = fr < g.pa_rcp_n ? pa_rcp[fr] : pa_reciprocal_up(fr);
+                pa_bad |= active && fr == 0u;
+            } else {
+                const uint32_t addr = l3_entry_addr<METHOD, FID>(v, lane_tb, ent_stride, k8_stride, f, a.n_entries, k8, rf);
+                const uint4 e = lds128(addr);
+                nfr = e.x;
+                base = e.y;
+                rcp = __hiloint2double(int(e.w), int(e.z));
+                if (active)
+                    badf = fmaf(__uint_as_float(e.w), 0.f, badf); // NaN (no such symbol) sticks
+            }
+        };
 
         // Whole 32-byte sectors go to global memory (a 16-byte store is a partial-sector write, which the
         // memory system handles at less than half the speed); what is left (< 32 bytes) moves to the row's front.
@@ -354,14 +445,8 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                 vmax = max(vmax, max(max(v[0], v[1]), max(v[2], v[3])));
 #pragma unroll
             for (int c = 0; c < 4; c++) {
-                const uint32_t addr = l3_entry_addr<METHOD, FID>(v[c], lane_tb, ent_stride, k8_stride, f, a.n_entries, k8[c], rf);
-                const uint4 e = lds128(addr);
-                nfr[c] = e.x;
-                base[c] = e.y;
-                rcp[c] = __hiloint2double(int(e.w), int(e.z));
-                if (active)
-                    badf = fmaf(__uint_as_float(e.w), 0.f, badf); // NaN (no such symbol) sticks
-                fr16[c] = nfr[c] * 0xFFFFFFF0u;               // freq * 16
+                entry(v[c], active, k8[c], nfr[c], base[c], rcp[c]);
+                fr16[c] = nfr[c] * 0xFFFFFFF0u; // freq * 16
             }
             if (METHOD == METHOD_RFOLD) // the reordered values (0 for the K most frequent ones)
                 vmax = max(vmax, max(max(v[0], v[1]), max(v[2], v[3])));
@@ -447,12 +532,12 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                     uint32_t v = active ? __ldg(a.in + first + (nb - 1u - s)) : 0u;
                     // run the symbol as a "quad" whose other three members are inactive: rotate it into slot 0
                     uint32_t k8;
-                    const uint32_t addr = l3_entry_addr<METHOD, FID>(v, lane_tb, ent_stride, k8_stride, f, a.n_entries, k8, rf);
-                    const uint4 e = lds128(addr);
-                    if (active) {
-                        badf = fmaf(__uint_as_float(e.w), 0.f, badf);
+                    uint4 e;
+                    double e_rcp;
+                    entry(v, active, k8, e.x, e.y, e_rcp);
+                    e.z = uint32_t(__double2loint(e_rcp)), e.w = uint32_t(__double2hiint(e_rcp));
+                    if (active)
                         vmax = max(vmax, v);
-                    }
                     const uint32_t fr16 = e.x * 0xFFFFFFF0u;
                     const bool rn = active && (xhi[0] >= fr16);
                     if (METHOD != METHOD_INT) {
@@ -517,7 +602,7 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
             if (have_block)
                 a.block_bytes[blk] = total;
         }
-        bool bad = badf != badf;
+        bool bad = badf != badf || (PA && pa_bad);
         if (METHOD != METHOD_INT)
             bad = bad || vmax > g.max_value;
         if (bad && have_block)
@@ -602,9 +687,24 @@ struct L3Reader {
 // symbols -- instead of a 32-byte STG per lane (14 LSU wavefronts per warp and iteration).  Byte-exact, and the LSU
 // wavefronts do go down, but the kernel does not get faster: ANSfold-1 1.956 -> 1.999 ms, ANS 2.18 -> 2.95 ms, the
 // 2^18-slot model 2.274 -> 2.240 ms at 2^30 symbols.)
+//
+// TABLE == DEC_PA_LANE = pseudo-adaptive mode (one model per block): every lane keeps ITS model in its own stretch of
+// shared memory -- cum[s] = slots before symbol s (u16) and a bucket index (the symbol that holds every 2^bshift-th
+// slot), built by the warp at the start of the task from DecArgs::pa_nfreqs -- and finds slot -> symbol by a binary
+// search between two bucket entries with a trip count fixed per task (the widest bucket of its 32 models); the
+// unfolded value and raw byte count follow arithmetically from the symbol.  Reader, state update and stores are the
+// same code.  (pa_kernels.cuh gives each block four lanes, one per state, with a shuffle-scan on the chain.)
+__host__ __device__ inline uint32_t pa3_cum_bytes(uint32_t syms) { return ((syms + 2u) * 2u + 7u) & ~7u; }
+__host__ __device__ inline uint32_t pa3_dec_tab_stride(uint32_t syms, uint32_t bucket_log2)
+{
+    uint32_t b = (pa3_cum_bytes(syms) + ((1u << bucket_log2) + 1u) * 2u + 7u) & ~7u;
+    return ((b >> 3) & 1u) ? b : b + 8u; // an odd number of 8-byte bank pairs between the lanes' tables
+}
+
 template <int METHOD, int TABLE, int QI, int MAXW>
 __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs a)
 {
+    constexpr bool PA = (TABLE == DEC_PA_LANE);
     constexpr uint32_t ALIGN = 16u; // payload view and refill granularity
     constexpr int RING = L3DecGeom<QI>::kRing;
     constexpr int DIST = L3DecGeom<QI>::kDist;
@@ -612,18 +712,23 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t frame = 1u << a.log2_frame;
     DecTables<METHOD, TABLE> tables;
-    const size_t table_bytes = tables.load(a, smem_raw);
+    const size_t table_bytes = PA ? size_t(blockDim.x) * a.pa_tab_stride : tables.load(a, smem_raw);
     uint8_t* s_rings = smem_raw + table_bytes;
     s_rings += (uint32_t(RING) - (smem_u32(s_rings) & uint32_t(RING - 1))) & uint32_t(RING - 1); // the host adds RING bytes of slack
 
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t warps_per_cta = blockDim.x >> 5;
-    const uint32_t log2_frame = a.log2_frame;
-    const uint32_t frame_mask = frame - 1u;
-    const uint32_t lower_shift = log2_frame + 4u; // L = 16 M (ans_fold.hpp:91); at most 32
-    const uint32_t lower_lo = lower_shift >= 32u ? 0u : (1u << lower_shift);
+    uint32_t log2_frame = a.log2_frame; // (PA: the lane's own, set per task)
+    uint32_t frame_mask = frame - 1u;
+    uint32_t lower_shift = log2_frame + 4u; // L = 16 M (ans_fold.hpp:91); at most 32
+    uint32_t lower_lo = lower_shift >= 32u ? 0u : (1u << lower_shift);
     const uint32_t lower_hi = lower_shift >= 32u ? 1u : 0u;
+    // PA: the warp's 32 tables, mine, my bucket index
+    const uint32_t pa_tabs = smem_u32(smem_raw) + warp * 32u * a.pa_tab_stride;
+    const uint16_t* my_cum = reinterpret_cast<const uint16_t*>(smem_raw + size_t(warp * 32u + lane) * a.pa_tab_stride);
+    const uint16_t* my_bkt = my_cum + (pa3_cum_bytes(a.pa_syms) >> 1);
+    uint32_t pa_bshift = 0, pa_trips = 0;
     const uint32_t rfold_bias = (METHOD == METHOD_RFOLD) ? (1u << (a.fidelity + 7)) : 0u; // ans_reorder_fold.hpp:301
     const uint32_t B = a.block_syms;
 
@@ -640,6 +745,72 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
         const uint32_t quads = nb >> 2;
         const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
         const bool uniform = __all_sync(0xffffffffu, have_block && quads == max_quads);
+
+        if (PA) {
+            // the 32 models of the task: cum[s] for s in [0, syms + 1], bucket[b] = symbol that holds slot b << bshift
+            // (bucket[n_buckets] = syms - 1: where the search in the last bucket ends), 128 symbols per step of the warp
+            const uint32_t syms = a.pa_syms; // multiple of 16
+            const uint32_t blog = a.pa_bucket_log2;
+            uint32_t widest = 0;
+            __syncwarp();
+            for (uint32_t j = 0; j < 32u; j++) {
+                const uint32_t m = min(task * 32u + j, a.n_blocks - 1u);
+                const uint32_t lg = a.pa_log2[m];
+                const uint32_t bs = lg > blog ? lg - blog : 0u;
+                const uint32_t n_buckets = 1u << (lg - bs);
+                const uint4* nf = reinterpret_cast<const uint4*>(a.pa_nfreqs + uint64_t(m) * a.pa_nbins);
+                const uint32_t tab = pa_tabs + j * a.pa_tab_stride;
+                const uint32_t bkt = tab + pa3_cum_bytes(syms);
+                const uint32_t bround = (1u << bs) - 1u;
+                uint32_t carry = 0;
+                for (uint32_t base = 0; base < syms; base += 128u) {
+                    const uint32_t s = base + 4u * lane;
+                    const uint4 q = s < syms ? __ldg(nf + (s >> 2)) : make_uint4(0u, 0u, 0u, 0u);
+                    const uint32_t mine = q.x + q.y + q.z + q.w;
+                    uint32_t incl = mine;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= uint32_t(o))
+                            incl += up;
+                    }
+                    const uint32_t fr[4] = { q.x, q.y, q.z, q.w };
+                    uint32_t c[5];
+                    c[0] = carry + incl - mine;
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        c[i + 1] = c[i] + fr[i];
+                        if (fr[i]) {
+                            const uint32_t b1 = (c[i + 1] - 1u) >> bs;
+                            for (uint32_t b = (c[i] + bround) >> bs; b <= b1; b++)
+                                asm volatile("st.shared.u16 [%0], %1;" ::"r"(bkt + 2u * b), "h"(uint16_t(s + uint32_t(i))) : "memory");
+                        }
+                    }
+                    if (s < syms)
+                        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(tab + 2u * s), "r"((c[0] & 0xFFFFu) | (c[1] << 16)), "r"((c[2] & 0xFFFFu) | (c[3] << 16)) : "memory");
+                    carry += __shfl_sync(0xffffffffu, incl, 31);
+                }
+                if (lane == 0) {
+                    sts32(tab + 2u * syms, (carry & 0xFFFFu) | (carry << 16));
+                    asm volatile("st.shared.u16 [%0], %1;" ::"r"(bkt + 2u * n_buckets), "h"(uint16_t(syms - 1u)) : "memory");
+                }
+                __syncwarp();
+                for (uint32_t b = lane; b < n_buckets; b += 32u) {
+                    uint32_t s0, s1;
+                    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(s0) : "r"(bkt + 2u * b));
+                    asm volatile("ld.shared.u16 %0, [%1+2];" : "=r"(s1) : "r"(bkt + 2u * b));
+                    widest = max(widest, s1 - s0);
+                }
+            }
+            widest = __reduce_max_sync(0xffffffffu, widest);
+            pa_trips = 32u - uint32_t(__clz(widest)); // ceil(log2(widest + 1)) halvings settle every search
+            log2_frame = a.pa_log2[min(blk, a.n_blocks - 1u)];
+            pa_bshift = log2_frame > blog ? log2_frame - blog : 0u;
+            frame_mask = (1u << log2_frame) - 1u;
+            lower_shift = log2_frame + 4u; // < 32: log2 M <= 16 here
+            lower_lo = 1u << lower_shift;
+            __syncwarp();
+        }
 
         // ALIGN-byte aligned view of the payload; positions count bytes from pay16
         const uint8_t* pay = a.payload + (have_block ? a.offsets[blk] : 0);
@@ -691,10 +862,8 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
         // one symbol per chain: slot lookup + state update (ans_fold.hpp:216-220); returns the renormalisation flag
         uint32_t nlo[4], nhi[4], raw[4], kk[4];
         bool rn[4];
-        auto advance = [&](int g, bool active) {
+        auto update = [&](int g, bool active, uint32_t freq, uint32_t offset, uint32_t k) {
             const int c = 3 - g; // index 4t+g is decoded by state 3-g (ans_fold.hpp:300-305)
-            uint32_t freq, offset, k;
-            tables.lookup_raw(xlo[c] & frame_mask, freq, offset, raw[g], k);
             kk[g] = active ? k : 0u;
             const uint32_t q_lo = __funnelshift_r(xlo[c], xhi[c], log2_frame);
             const uint32_t q_hi = xhi[c] >> log2_frame;
@@ -703,6 +872,62 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
             nhi[g] = uint32_t(p >> 32) + freq * q_hi;
             // state < L = 2^(log2 M + 4)
             rn[g] = active && (lower_shift >= 32u ? nhi[g] == 0u : (nhi[g] == 0u && nlo[g] < lower_lo));
+        };
+        auto advance = [&](int g, bool active) {
+            uint32_t freq, offset, k;
+            if (PA) {
+                // largest symbol in [bucket[b], bucket[b + 1]] with cum[symbol] <= slot
+                const uint32_t slot = xlo[3 - g] & frame_mask;
+                uint32_t slo = my_bkt[slot >> pa_bshift], shi = my_bkt[(slot >> pa_bshift) + 1u];
+                for (uint32_t t = 0; t < pa_trips; t++) {
+                    const uint32_t mid = (slo + shi + 1u) >> 1;
+                    const bool le = uint32_t(my_cum[mid]) <= slot;
+                    slo = le ? mid : slo;
+                    shi = le ? shi : mid - 1u;
+                }
+                const uint32_t c0 = my_cum[slo];
+                freq = (uint32_t(my_cum[slo + 1u]) - c0) & 0xFFFFu;
+                offset = slot - c0;
+                raw[g] = pa_unmap<METHOD>(slo, a.fidelity, k);
+                raw[g] |= k << 30;
+            } else {
+                tables.lookup_raw(xlo[3 - g] & frame_mask, freq, offset, raw[g], k);
+            }
+            update(g, active, freq, offset, k);
+        };
+        // PA: the four searches of a quad in ONE loop (plain loads: their latencies overlap)
+        auto advance4 = [&](bool active) {
+            if (!PA) {
+#pragma unroll
+                for (int g = 0; g < 4; g++)
+                    advance(g, active);
+                return;
+            }
+            uint32_t slot[4], slo[4], shi[4];
+#pragma unroll
+            for (int g = 0; g < 4; g++) {
+                slot[g] = xlo[3 - g] & frame_mask;
+                slo[g] = my_bkt[slot[g] >> pa_bshift];
+                shi[g] = my_bkt[(slot[g] >> pa_bshift) + 1u];
+            }
+            for (uint32_t t = 0; t < pa_trips; t++) {
+#pragma unroll
+                for (int g = 0; g < 4; g++) {
+                    const uint32_t mid = (slo[g] + shi[g] + 1u) >> 1;
+                    const bool le = uint32_t(my_cum[mid]) <= slot[g];
+                    slo[g] = le ? mid : slo[g];
+                    shi[g] = le ? shi[g] : mid - 1u;
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < 4; g++) {
+                const uint32_t c0 = my_cum[slo[g]];
+                const uint32_t freq = (uint32_t(my_cum[slo[g] + 1u]) - c0) & 0xFFFFu;
+                uint32_t k;
+                raw[g] = pa_unmap<METHOD>(slo[g], a.fidelity, k);
+                raw[g] |= k << 30;
+                update(g, active, freq, slot[g] - c0, k);
+            }
         };
         auto finish = [&](int g, bool active) -> uint32_t {
             const int c = 3 - g;
@@ -727,9 +952,7 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
 #pragma unroll
                 for (int j = 0; j < QI; j++) {
                     const bool active = FULL || (q0 + uint32_t(j)) < quads;
-#pragma unroll
-                    for (int g = 0; g < 4; g++)
-                        advance(g, active);
+                    advance4(active);
 #pragma unroll
                     for (int g = 0; g < 4; g++)
                         val[4 * j + g] = finish(g, active);

@@ -101,16 +101,7 @@ __device__ __forceinline__ void pa_build_cum(const uint32_t* __restrict__ nf_mod
     }
 }
 
-template <int METHOD> __device__ __forceinline__ uint32_t pa_unmap(uint32_t s, uint32_t f, uint32_t& k)
-{
-    if (METHOD == METHOD_MSB)
-        return msb_unmap(s, k);
-    // fold_unmap (ans_fold.hpp:150-175) without the divide: k <= 3 because values stay below 2^30
-    const uint32_t thres = 1u << (f + 7);
-    const uint32_t step = 255u << (f - 1);
-    k = uint32_t(s >= thres) + uint32_t(s >= thres + step) + uint32_t(s >= thres + 2u * step);
-    return (s - step * k) << (8u * k);
-}
+// (pa_unmap: kernels.cuh)
 
 // ------------------------------------------------------------------------------------------
 // encoder: encode_kernel<METHOD, false, true> with the block's table in shared memory

@@ -348,65 +348,66 @@ __global__ void __launch_bounds__(kRemapEncThreads) remap_alpha_kernel(uint32_t*
         out32[z] = 0u;
 }
 
-// [sigma][universe][interp] of block b at src + offsets[b] (alpha_bytes[b] of them)  ->  the block's sorted distinct values
+// [sigma][universe][interp] of block b at src + offsets[b] (alpha_bytes[b] of them)  ->  the running sums the code carries, in
+// alphabet[b][0 .. sigma), sigma[b] (0: not a valid alphabet).  One thread per block, the lockstep serial decoder of
+// kernels.cuh (pa_interp_decode) on 64-bit bounds; remap_alpha_finish_kernel turns the sums back into values.
+// (The first version -- a loop trip per node or per pop, the stack in local memory -- took 4.9 ms for 16 384 alphabets
+// of ~5000 values, most of a remap decode.)
+constexpr int kRemapDepth = 22; // pending right halves: log2(sigma) + 1, sigma <= 2^21
 __global__ void __launch_bounds__(kRemapAlphaThreads) remap_alpha_decode_kernel(const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets,
     const uint32_t* __restrict__ alpha_bytes, uint64_t region_bytes, uint32_t model_syms, uint32_t n_models, uint32_t* __restrict__ alphabet,
-    uint32_t* __restrict__ sigma, uint32_t* __restrict__ error)
+    uint32_t* __restrict__ sigma)
 {
+    __shared__ uint32_t s_stack[kRemapDepth * 6 * kRemapAlphaThreads];
     const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n_models)
         return;
-    RemapReader r;
-    const bool inside = offsets[b] + alpha_bytes[b] <= region_bytes && (alpha_bytes[b] & 3u) == 0u; // the size table is untrusted
-    r.in = reinterpret_cast<const uint32_t*>(src + (inside ? offsets[b] : 0)); // (src and the offsets are 16-byte aligned)
-    r.limit = inside ? alpha_bytes[b] >> 2 : 0u;
-    r.start();
-    uint32_t* v = alphabet + uint64_t(b) * model_syms;
-    uint32_t cnt_all = r.get(32u);
-    const uint32_t universe = r.get(32u);
-    bool bad = !inside || cnt_all == 0u || cnt_all > model_syms || universe == 0u;
+    const bool inside = offsets[b] + alpha_bytes[b] <= region_bytes && (alpha_bytes[b] & 3u) == 0u && alpha_bytes[b] >= 8u; // the size table is untrusted
+    const uint32_t* head = reinterpret_cast<const uint32_t*>(src + (inside ? offsets[b] : 0)); // (src and the offsets are 16-byte aligned)
+    uint32_t cnt_all = inside ? __ldg(head) : 0u;
+    const uint32_t universe = inside ? __ldg(head + 1) : 0u;
+    bool bad = !inside || cnt_all == 0u || cnt_all > model_syms || cnt_all > (1u << (kRemapDepth - 1)) || universe == 0u;
     if (bad)
         cnt_all = 0u;
-    uint32_t st_off[kRemapStack], st_n[kRemapStack];
-    uint64_t st_low[kRemapStack], st_high[kRemapStack];
-    int sp = 0;
-    uint32_t off = 0, cnt = cnt_all;
-    uint64_t low = 1u, high = uint64_t(universe) + 1u;
-    for (;;) {
-        if (cnt == 0) {
-            if (sp == 0)
-                break;
-            sp--;
-            off = st_off[sp], cnt = st_n[sp], low = st_low[sp], high = st_high[sp];
-            continue;
-        }
-        const uint32_t h = (cnt + 1u) >> 1, left = h - 1u, right = cnt - h;
-        if (high < uint64_t(right) + low + left) { // not a sequence this coder wrote
-            bad = true;
-            break;
-        }
-        const uint64_t u = high - right - low - left + 1u;
-        const uint64_t mid = low + left - 1u + remap_get_centered(r, u);
-        v[off + h - 1u] = uint32_t(mid - 1u);
-        st_off[sp] = off + h, st_n[sp] = right, st_low[sp] = mid + 1u, st_high[sp] = high;
-        sp++;
-        cnt = left;
-        high = mid - 1u;
-    }
-    if (r.pos > r.limit + 1u)
+    PaWordReader r;
+    r.start(src, (inside ? offsets[b] : 0) + 8u, region_bytes ? region_bytes - 1u : 0u);
+    if (!pa_interp_decode<uint64_t>(r, cnt_all, uint64_t(1), uint64_t(universe) + 1u, ~uint64_t(0), alphabet + uint64_t(b) * model_syms,
+            s_stack + threadIdx.x, kRemapAlphaThreads))
         bad = true;
-    // running sums back to the values; they must climb
-    uint32_t below = 0;
-    for (uint32_t j = 0; j < cnt_all && !bad; j++) {
-        const uint32_t here = v[j];
-        if (j && here < below)
-            bad = true;
-        v[j] = here - below;
-        below = here;
-    }
+    if (!bad && r.bits_used() > (uint64_t(alpha_bytes[b]) - 8u) * 8u)
+        bad = true;
     sigma[b] = bad ? 0u : cnt_all;
-    if (bad)
+}
+
+// running sums back to the values, in place; they must climb.  One warp per block.
+__global__ void __launch_bounds__(kRemapEncThreads) remap_alpha_finish_kernel(uint32_t* __restrict__ alphabet, uint32_t* __restrict__ sigma, uint32_t model_syms,
+    uint32_t n_models, uint32_t* __restrict__ error)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t b = blockIdx.x * (kRemapEncThreads / 32) + (threadIdx.x >> 5);
+    if (b >= n_models)
+        return;
+    uint32_t* v = alphabet + uint64_t(b) * model_syms;
+    const uint32_t cnt_all = sigma[b];
+    bool bad = cnt_all == 0u;
+    uint32_t below = 0;
+    for (uint32_t base = 0; base < cnt_all; base += 32u) {
+        const uint32_t j = base + lane;
+        const uint32_t here = j < cnt_all ? v[j] : 0xFFFFFFFFu;
+        uint32_t prev = __shfl_up_sync(0xffffffffu, here, 1);
+        if (lane == 0)
+            prev = below;
+        if (j < cnt_all) {
+            if (j && here < prev)
+                bad = true;
+            v[j] = here - prev;
+        }
+        below = __shfl_sync(0xffffffffu, here, 31);
+    }
+    if (__any_sync(0xffffffffu, bad) && lane == 0) {
+        sigma[b] = 0u;
         *error = 4u;
+    }
 }
 
 // value = alphabet[block][rank - 1]

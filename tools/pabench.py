@@ -58,7 +58,8 @@ def main():
             row = dict(model_syms=S, n=n, models=(n + S - 1) // S, bits_per_symbol=8.0 * nb / n, semi_static_bits_per_symbol=8.0 * semi / n,
                        enc_wall_ms=(t1 - t0) * 1e3, dec_wall_ms=(t2 - t1) * 1e3, hist_ms=s.ms_histogram, enc_host_model_ms=s.ms_model,
                        enc_kernel_ms=s.ms_encode, compact_ms=s.ms_compact, dec_host_model_ms=s2.ms_model, dec_kernel_ms=s2.ms_decode,
-                       enc_gbs=4.0 * n / (t1 - t0) / 1e9, dec_gbs=4.0 * n / (t2 - t1) / 1e9)
+                       enc_gbs=4.0 * n / (t1 - t0) / 1e9, dec_gbs=4.0 * n / (t2 - t1) / 1e9,
+                       enc_kernel=s.encode_kernel.decode(), dec_kernel=s2.decode_kernel.decode())
             if it and (best is None or row["enc_wall_ms"] + row["dec_wall_ms"] < best["enc_wall_ms"] + best["dec_wall_ms"]):
                 best = row
         best["ok"] = bool(torch.equal(d_in, d_out))
