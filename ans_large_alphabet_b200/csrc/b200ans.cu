@@ -162,6 +162,7 @@ struct b200ans_ctx {
     static constexpr int kPipeChunks = 8;
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
+    bool pa3_off = false; // pa_compress: the retry without the lane-per-block encoder is running
     cudaEvent_t ev_side[2] {}; // fork / join of work that runs beside the main stream inside one call (remap: alphabets beside ranks)
 
     // grow-only device buffers
@@ -1619,13 +1620,15 @@ template <int METHOD> int launch_pa3_encode(b200ans_ctx* c, const EncArgs& a, ui
 {
     using CFG = Pa3Cfg;
     constexpr int TQ = CFG::TQ;
-    if (a.block_syms % 128u != 0u || a.n / a.block_syms == 0 || max_lg > 15u || env_int("B200ANS_NO_PA3", 0) || env_int("B200ANS_NO_L3", 0))
+    if (a.block_syms % 128u != 0u || a.n / a.block_syms == 0 || max_lg > 15u || c->pa3_off || env_int("B200ANS_NO_PA3", 0)
+        || env_int("B200ANS_NO_L3", 0))
         return 1;
     tensor_map_encode_fn encode = tensor_map_encoder();
     if (!encode)
         return 1;
     Enc3Args g {};
-    g.pa_rcp_n = std::min<uint32_t>(4097u, (1u << max_lg) + 1u);
+    // 32 KiB of reciprocals cover the frequencies up to 4096 (B200ANS_PA3_RCPN, testing: a shorter table)
+    g.pa_rcp_n = std::min<uint32_t>(uint32_t(std::max(2, env_int("B200ANS_PA3_RCPN", 4097))), (1u << max_lg) + 1u);
     g.pa_tab_stride = uint32_t(align_up((size_t(a.pa_syms) + 2) * 2, 8));
     if (((g.pa_tab_stride >> 3) & 1u) == 0u)
         g.pa_tab_stride += 8; // an odd number of 8-byte bank pairs between the lanes' tables
@@ -1667,29 +1670,6 @@ template <int METHOD> int launch_pa3_encode(b200ans_ctx* c, const EncArgs& a, ui
     c->stats.launches++;
     CU(c, cudaGetLastError());
     return B200ANS_OK;
-}
-
-// ... and through the L3 decoder (TABLE = DEC_PA_LANE): the finest bucket index (2^9 .. 2^6 entries per model) that
-// still lets four warps per SM -- or one wave of tasks -- be resident.  Returns 1 when even the coarsest does not.
-template <int METHOD> int launch_pa3_decode(b200ans_ctx* c, DecArgs a, uint32_t max_lg)
-{
-    constexpr int MAXW = 8;
-    if (max_lg > 15u || (reinterpret_cast<uintptr_t>(a.out) & 15) != 0 || a.block_syms % 8u != 0u || env_int("B200ANS_NO_PA3", 0)
-        || env_int("B200ANS_NO_L3", 0))
-        return 1;
-    const uint32_t n_tasks = (a.n_blocks + 31) / 32;
-    const uint32_t want_warps = std::min<uint32_t>(4u, (n_tasks + uint32_t(c->num_sms) - 1) / uint32_t(c->num_sms));
-    const size_t room = c->max_smem - 1024 - 128;
-    for (uint32_t blog = uint32_t(std::max(6, std::min(9, env_int("B200ANS_PA3_BLOG", 9)))); blog >= 6u; blog--) {
-        const uint32_t stride = pa3_dec_tab_stride(a.pa_syms, blog);
-        const size_t warp_bytes = size_t(32) * stride + L3DecGeom<1>::kWarpBytes;
-        if (room / warp_bytes < want_warps)
-            continue;
-        a.pa_bucket_log2 = blog;
-        a.pa_tab_stride = stride;
-        return launch_lpb(c, lpb3_decode_kernel<METHOD, DEC_PA_LANE, 1, MAXW>, 0, warp_bytes, a.n_blocks, &a, MAXW);
-    }
-    return 1;
 }
 
 template <int METHOD> int launch_lpb3_encode_t(b200ans_ctx* c, const EncArgs& a)
@@ -3284,9 +3264,11 @@ try {
             pa_sort_bitonic_kernel<<<grid, kPaNormThreads, smem, c->stream>>>(c->bins.as<uint32_t>(), nbins, nm, c->h_approx, d_keys, d_meta,
                 c->pa_nfreqs.as<uint32_t>());
         }
-        const uint32_t fit_threads = nm * 8u;
-        pa_fit_kernel<<<(fit_threads + kPaFitThreads - 1) / kPaFitThreads, kPaFitThreads, 0, c->stream>>>(d_keys, n_keys, d_meta, nbins, nm,
-            margin, c->pa_nfreqs.as<uint32_t>(), d_lg, d_status, c->d_max_log2(), c->pa_log2tab.as<double>());
+        const uint32_t fit_threads = nm * uint32_t(kPaFitGroup);
+        pa_fit_kernel<<<(fit_threads + kPaFitThreads - 1) / kPaFitThreads, kPaFitThreads, 0, c->stream>>>(d_keys, n_keys, d_meta, nm, margin, d_lg,
+            d_status, c->d_max_log2(), c->pa_log2tab.as<double>());
+        pa_fit_store_kernel<<<(nm + 31) / 32, 32, 0, c->stream>>>(d_keys, n_keys, d_meta, nbins, nm, d_lg, d_status, c->pa_nfreqs.as<uint32_t>());
+        c->stats.launches++;
         c->stats.launches += 2;
         CU(c, cudaGetLastError());
     }
@@ -3392,20 +3374,21 @@ try {
     const uint32_t n_tasks = (nm + 7) / 8;
     PaLaunch pl = pa_launch_shape(c, size_t(kPaRcpN) * 8, size_t(8) * pa_enc_group_bytes(a.pa_syms), n_tasks);
     const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && max_lg <= 16u && pl.warps >= 2u;
-    if (!smem_tables) {
+    CU(c, cudaEventRecord(c->ev[0], c->stream));
+    // first choice: a lane per block (the L3 encoder with per-lane models, lpb3_kernels.cuh)
+    int rc3 = 1;
+    if (c->kernel_path != B200ANS_PATH_GROUP)
+        rc3 = method == METHOD_MSB ? launch_pa3_encode<METHOD_MSB>(c, a, max_lg) : launch_pa3_encode<METHOD_FOLD>(c, a, max_lg);
+    if (rc3 < 0)
+        return rc3;
+    if (rc3 != B200ANS_OK && !smem_tables) {
         CU(c, c->enc_table.reserve(size_t(nm) * nbins * sizeof(EncEntry)));
         a.table = c->enc_table.as<EncEntry>();
         pa_enc_tables_kernel<<<mgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, c->enc_table.as<EncEntry>());
         c->stats.launches++;
         CU(c, cudaGetLastError());
+        CU(c, cudaEventRecord(c->ev[0], c->stream));
     }
-    CU(c, cudaEventRecord(c->ev[0], c->stream));
-    // first choice: a lane per block (the L3 encoder with per-lane models), when one wave of warps holds all the models
-    int rc3 = 1;
-    if (smem_tables)
-        rc3 = method == METHOD_MSB ? launch_pa3_encode<METHOD_MSB>(c, a, max_lg) : launch_pa3_encode<METHOD_FOLD>(c, a, max_lg);
-    if (rc3 < 0)
-        return rc3;
     if (rc3 == B200ANS_OK) {
     } else if (smem_tables) {
         auto k = method == METHOD_MSB ? pa_smem_encode_kernel<METHOD_MSB> : pa_smem_encode_kernel<METHOD_FOLD>;
@@ -3452,6 +3435,16 @@ try {
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(c->ev[2], c->stream));
     RET(read_small(c));
+    if ((c->h_small()->error_flag & 2u) && !c->pa3_off) {
+        // a model the lane-per-block encoder does not take (two different frequencies beyond its reciprocal table): the
+        // whole input again through the four-lanes-per-block encoder
+        struct Once {
+            bool& flag;
+            explicit Once(bool& f) : flag(f) { flag = true; }
+            ~Once() { flag = false; }
+        } once(c->pa3_off);
+        return b200ans_pa_compress_device(c, method, f, model_syms, d_dst, cap, d_src, n, out_bytes);
+    }
     if (c->h_small()->error_flag)
         return c->fail(B200ANS_E_DOMAIN, "pa_compress: a symbol had no frequency in its block's model");
     const size_t total = payload_at + c->h_small()->totals[0];
@@ -3612,15 +3605,6 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
     // (frames of 2^16 slots go to the slot tables: cum[] is 16 bits wide and the searches compare it)
     const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && c->h_small()->max_log2 <= 15u && pl.warps >= 2u;
     set_name(c->stats.decode_kernel, smem_tables ? "pa_smem_decode_kernel" : "decode_kernel");
-    const uint32_t max_lg = c->h_small()->max_log2;
-    auto pa3 = [&](const DecArgs& ar) { // first choice: a lane per block (the L3 decoder with per-lane models)
-        if (!smem_tables)
-            return 1;
-        const int rc = method == METHOD_MSB ? launch_pa3_decode<METHOD_MSB>(c, ar, max_lg) : launch_pa3_decode<METHOD_FOLD>(c, ar, max_lg);
-        if (rc == B200ANS_OK)
-            set_name(c->stats.decode_kernel, "lpb3_decode_kernel<PA>");
-        return rc;
-    };
     if (smem_tables && h_src && runs > 1) {
         // one launch per run of models; the pointers of the argument block move to the run's first model
         CU(c, cudaEventRecord(c->ev[0], c->stream));
@@ -3640,13 +3624,8 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
             ar.pa_nfreqs = a.pa_nfreqs + size_t(b0) * nbins;
             const PaLaunch pr = pa_launch_shape(c, 0, warp_bytes, (b1 - b0 + 7) / 8);
             CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
-            const int rc3 = pa3(ar);
-            if (rc3 < 0)
-                return rc3;
-            if (rc3 != B200ANS_OK) {
-                k<<<pr.grid, pr.warps * 32, pr.smem, c->stream>>>(ar);
-                c->stats.launches++;
-            }
+            k<<<pr.grid, pr.warps * 32, pr.smem, c->stream>>>(ar);
+            c->stats.launches++;
             CU(c, cudaGetLastError());
             CU(c, cudaEventRecord(c->ev_dec[r], c->stream));
             CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_dec[r], 0));
@@ -3665,15 +3644,10 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
             CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
     if (smem_tables) {
         CU(c, cudaEventRecord(c->ev[0], c->stream));
-        const int rc3 = pa3(a);
-        if (rc3 < 0)
-            return rc3;
-        if (rc3 != B200ANS_OK) {
-            auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
-            CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
-            k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
-            c->stats.launches++;
-        }
+        auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
+        CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
+        k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
+        c->stats.launches++;
         CU(c, cudaGetLastError());
     } else {
         const uint64_t slot_stride = uint64_t(1) << c->h_small()->max_log2;

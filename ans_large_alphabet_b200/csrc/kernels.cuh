@@ -107,11 +107,10 @@ struct DecArgs {
     uint32_t pa_nbins;
     uint32_t pa_syms;         // table entries per model: beyond the largest symbol of every model, multiple of 16
     uint32_t pa_bucket_log2;  // the bucket index has 2^pa_bucket_log2 entries per model
-    uint32_t pa_tab_stride;   // DEC_PA_LANE (lpb3_kernels.cuh): bytes between the lanes' tables
     uint32_t* error_flag;     // set to 2 when a block's payload is not consumed exactly (corrupt container); may be null
 };
 
-enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3, DEC_INT_SMEM_PURE = 4, DEC_PA_LANE = 5 };
+enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3, DEC_INT_SMEM_PURE = 4 };
 
 // DEC_INT_SMEM_PURE: the same index, but a 32-slot group that lies inside ONE symbol (no symbol starts at its slots
 // 1..31) carries that symbol's answer in its own record -- x = base | rank<11:0> << 20, y = 1 << 31 | rank<22:12> << 20 |
@@ -1230,23 +1229,66 @@ __device__ __forceinline__ void pa_fit(const uint64_t* __restrict__ keys, uint32
     const double lgm = double(lgM);
     double acc = 0.0;
     uint32_t mx = 0;
-    for (uint32_t r = first; r < n_keys; r++) {
-        const uint64_t key = __ldg(keys + r);
-        const uint32_t sym = uint32_t(key) & 0xFFFFu;
-        const uint64_t cnt = key >> 16;
-        const double ratio = double(M) / double(rest);
-        uint32_t share = uint32_t(fma(ratio, double(cnt), 0.5));
-        if (share == 0)
-            share = 1;
-        if (STORE)
-            shares[sym] = share;
-        else
-            acc = fma(double(cnt) * inv_total, (share < kPaLog2Tab ? __ldg(log2_tab + share) : log2(double(share))) - lgm, acc);
-        mx = max(mx, share);
-        M -= int64_t(share);
-        rest -= cnt;
-        if (M < 0)
-            break;
+    // the keys come in batches of four, one batch ahead of the chain M -> ratio -> share -> M: a global load per step on
+    // that chain was most of its latency (ncu r02x: 1.0k cycles per step with 14 warps per SM)
+    constexpr uint32_t kAhead = 4;
+    uint64_t nxt[kAhead];
+#pragma unroll
+    for (uint32_t i = 0; i < kAhead; i++)
+        nxt[i] = first + i < n_keys ? __ldg(keys + first + i) : 0u;
+    // ... and the log2 of a share (a gather from a 512 KiB table) is consumed one batch later: a warp issues in order, so
+    // the cross-entropy term waiting for its load would hold up the next step of the chain
+    double w_prev[kAhead], l_prev[kAhead];
+#pragma unroll
+    for (uint32_t i = 0; i < kAhead; i++)
+        w_prev[i] = 0.0, l_prev[i] = 0.0;
+    bool done = false;
+    for (uint32_t r = first; r < n_keys && !done; r += kAhead) {
+        uint64_t cur[kAhead];
+#pragma unroll
+        for (uint32_t i = 0; i < kAhead; i++) {
+            cur[i] = nxt[i];
+            nxt[i] = r + kAhead + i < n_keys ? __ldg(keys + r + kAhead + i) : 0u;
+        }
+#pragma unroll
+        for (uint32_t i = 0; i < kAhead; i++) {
+            if (done || r + i >= n_keys)
+                break;
+            const uint64_t key = cur[i];
+            const uint32_t sym = uint32_t(key) & 0xFFFFu;
+            const uint64_t cnt = key >> 16;
+            const double ratio = double(M) / double(rest);
+            uint32_t share = uint32_t(fma(ratio, double(cnt), 0.5));
+            if (share == 0)
+                share = 1;
+            if (STORE) {
+                shares[sym] = share;
+            } else {
+                acc = fma(w_prev[i], l_prev[i] - lgm, acc); // the term of four steps ago (0 x anything at the start)
+                w_prev[i] = double(cnt) * inv_total;
+                l_prev[i] = share < kPaLog2Tab ? __ldg(log2_tab + share) : log2(double(share));
+            }
+            mx = max(mx, share);
+            M -= int64_t(share);
+            rest -= cnt;
+            done = M < 0;
+        }
+    }
+    if (!STORE) {
+        // the pending terms, oldest first.  The batch may have ended anywhere: position i of the last (partial) batch holds
+        // a newer term than position i + 1 .. of the batch before, so the order is by age, not by index
+        const uint32_t steps = n_keys > first ? n_keys - first : 0u;
+        const uint32_t start = steps % kAhead; // oldest pending position (when the loop ran to the end)
+#pragma unroll
+        for (uint32_t i = 0; i < kAhead; i++) {
+            const uint32_t at = (start + i) % kAhead;
+            double w = 0.0, l = 0.0;
+#pragma unroll
+            for (uint32_t z = 0; z < kAhead; z++)
+                if (z == at)
+                    w = w_prev[z], l = l_prev[z];
+            acc = fma(w, l - lgm, acc);
+        }
     }
     failed = M != 0;
     top = mx;
@@ -1481,30 +1523,35 @@ __global__ void __launch_bounds__(kPaSortWarps * 32) pa_sort_kernel(const uint32
 }
 
 // status: 0 = decided here, 1 = unusable (the reference would return an empty model), 2 = undecided (host decides)
+// Four lanes per model fit four frames at a time (round 2: eight at a time left five of eight chains unused on typical
+// blocks, whose frame is M0 .. 8 M0); the shares of the winning frame are written by pa_fit_store_kernel, one THREAD per
+// model (inside this kernel that pass ran with one lane in eight active).
+constexpr int kPaFitGroup = 4;
 __global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* __restrict__ gkeys, uint32_t n_keys, const PaMeta* __restrict__ meta,
-    uint32_t nbins, uint32_t n_models, double margin, uint32_t* __restrict__ nfreqs, uint8_t* __restrict__ log2_frame,
-    uint8_t* __restrict__ status, uint32_t* __restrict__ max_log2, const double* __restrict__ log2_tab)
+    uint32_t n_models, double margin, uint8_t* __restrict__ log2_frame, uint8_t* __restrict__ status, uint32_t* __restrict__ max_log2,
+    const double* __restrict__ log2_tab)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t j = t & 7u;
-    const bool live = (t >> 3) < n_models;
-    const uint32_t model = live ? (t >> 3) : n_models - 1u; // spare lanes shadow the last model: shuffles stay full-warp
+    const uint32_t j = t & uint32_t(kPaFitGroup - 1);
+    const bool live = (t / kPaFitGroup) < n_models;
+    const uint32_t model = live ? (t / kPaFitGroup) : n_models - 1u; // spare lanes shadow the last model: shuffles stay full-warp
     const PaMeta mt = meta[model];
     const uint64_t* keys = gkeys + uint64_t(model) * n_keys;
     int st = mt.sigma == 0 ? 1 : -1, choice = -1, last_good = -1;
-    for (int round = 0; round < 4; round++) {
+    for (int round = 0; round < 32 / kPaFitGroup; round++) {
         if (!__any_sync(0xffffffffu, st < 0))
             break;
         bool failed = true;
         uint32_t top = 0;
         double xh = 0.0;
         if (st < 0)
-            pa_fit<false>(keys, mt.first, n_keys, mt.frame0_lg + 8u * round + j, mt.total, mt.inv_total, nullptr, failed, top, xh, log2_tab);
+            pa_fit<false>(keys, mt.first, n_keys, mt.frame0_lg + uint32_t(kPaFitGroup * round) + j, mt.total, mt.inv_total, nullptr, failed, top, xh,
+                log2_tab);
         const uint32_t code = failed ? 0xFFFFFFFFu : top;
 #pragma unroll
-        for (int jj = 0; jj < 8; jj++) { // every lane of the group walks the eight results in the reference's order
-            const uint32_t cj = __shfl_sync(0xffffffffu, code, jj, 8);
-            const double xj = __shfl_sync(0xffffffffu, xh, jj, 8);
+        for (int jj = 0; jj < kPaFitGroup; jj++) { // every lane of the group walks the results in the reference's order
+            const uint32_t cj = __shfl_sync(0xffffffffu, code, jj, kPaFitGroup);
+            const double xj = __shfl_sync(0xffffffffu, xh, jj, kPaFitGroup);
             if (st >= 0 || cj == 0xFFFFFFFFu)
                 continue;
             if (cj >= 65535u) { // the 16-bit guard: back to the last good fit (possibly none)
@@ -1516,28 +1563,34 @@ __global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* _
             if (fabs(d) <= margin) {
                 st = 2;
             } else if (d < 0.0) {
-                choice = 8 * round + jj;
+                choice = kPaFitGroup * round + jj;
                 st = 0;
             } else {
-                last_good = 8 * round + jj;
+                last_good = kPaFitGroup * round + jj;
             }
         }
     }
     if (st < 0)
         st = 2; // no decision in 32 doublings: let the host look at it
     if (live && j == 0u) {
-        uint32_t lg = 0;
-        if (st == 0) {
-            lg = mt.frame0_lg + uint32_t(choice);
-            bool failed;
-            uint32_t top;
-            double xh;
-            pa_fit<true>(keys, mt.first, n_keys, lg, mt.total, mt.inv_total, nfreqs + uint64_t(model) * nbins, failed, top, xh);
-        }
+        const uint32_t lg = st == 0 ? mt.frame0_lg + uint32_t(choice) : 0u;
         status[model] = uint8_t(st);
         log2_frame[model] = uint8_t(lg);
         atomicMax(max_log2, lg); // the coder picks its table layout by the largest frame
     }
+}
+
+__global__ void __launch_bounds__(kPaFitThreads) pa_fit_store_kernel(const uint64_t* __restrict__ gkeys, uint32_t n_keys, const PaMeta* __restrict__ meta,
+    uint32_t nbins, uint32_t n_models, const uint8_t* __restrict__ log2_frame, const uint8_t* __restrict__ status, uint32_t* __restrict__ nfreqs)
+{
+    const uint32_t model = blockIdx.x * blockDim.x + threadIdx.x;
+    if (model >= n_models || status[model] != 0)
+        return;
+    const PaMeta mt = meta[model];
+    bool failed;
+    uint32_t top;
+    double xh;
+    pa_fit<true>(gkeys + uint64_t(model) * n_keys, mt.first, n_keys, log2_frame[model], mt.total, mt.inv_total, nfreqs + uint64_t(model) * nbins, failed, top, xh);
 }
 
 

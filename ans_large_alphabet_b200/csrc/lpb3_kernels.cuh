@@ -296,6 +296,8 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
     const uint16_t* my_cum = reinterpret_cast<const uint16_t*>(smem_raw + g.pa_rcp_n * 8u + (warp * 32u + lane) * g.pa_tab_stride);
     const double* pa_rcp = reinterpret_cast<const double*>(smem_raw);
     bool pa_bad = false;
+    uint32_t dom_freq = 0; // PA: the largest frequency of the lane's model, and its reciprocal
+    double dom_rcp = 0.0;
     const uint32_t ent_stride = 16u << g.rep_log2;
     const uint32_t step = (METHOD == METHOD_MSB) ? 256u : (255u << (f - 1u));
     const uint32_t k8_stride = (METHOD == METHOD_INT) ? 0u : (step * ent_stride) >> 3;
@@ -341,11 +343,14 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                 const uint32_t m = min(blk0 + j, a.n_blocks - 1u);
                 const uint4* nf = reinterpret_cast<const uint4*>(a.pa_nfreqs + uint64_t(m) * a.pa_nbins);
                 const uint32_t tab = pa_tabs + j * g.pa_tab_stride;
-                uint32_t carry = 0;
+                uint32_t carry = 0, top = 0, low_big = 0xFFFFFFFFu; // largest frequency; smallest one beyond the reciprocal table
                 for (uint32_t base = 0; base < syms; base += 128u) {
                     const uint32_t s = base + 4u * lane;
                     const uint4 q = s < syms ? __ldg(nf + (s >> 2)) : make_uint4(0u, 0u, 0u, 0u);
                     const uint32_t mine = q.x + q.y + q.z + q.w;
+                    top = max(top, max(max(q.x, q.y), max(q.z, q.w)));
+                    low_big = min(low_big, min(min(q.x >= g.pa_rcp_n ? q.x : 0xFFFFFFFFu, q.y >= g.pa_rcp_n ? q.y : 0xFFFFFFFFu),
+                                           min(q.z >= g.pa_rcp_n ? q.z : 0xFFFFFFFFu, q.w >= g.pa_rcp_n ? q.w : 0xFFFFFFFFu)));
                     uint32_t incl = mine;
 #pragma unroll
                     for (int o = 1; o < 32; o <<= 1) {
@@ -360,7 +365,14 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                 }
                 if (lane == 0)
                     sts32(tab + 2u * syms, (carry & 0xFFFFu) | (carry << 16));
+                top = __reduce_max_sync(0xffffffffu, top);
+                low_big = __reduce_min_sync(0xffffffffu, low_big);
+                if (lane == j)
+                    dom_freq = top;
+                if (low_big != 0xFFFFFFFFu && low_big != top && lane == 0)
+                    atomicOr(a.error_flag, 2u); // not for this kernel
             }
+            dom_rcp = pa_reciprocal_up(max(dom_freq, 1u));
             __syncwarp();
             log2_frame = a.pa_log2[min(blk, a.n_blocks - 1u)];
             frame = 1u << log2_frame;
@@ -391,7 +403,12 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
                 const uint32_t fr = (c1 - c0) & 0xFFFFu;
                 base = c0;
                 nfr = 0u - fr;
-                rcp = fr < g.pa_rcp_n ? pa_rcp[fr] : pa_reciprocal_up(fr);
+                // reciprocal: by table; beyond it (frequencies above 4096: at most a few symbols of a model, nearly always
+                // one) the lane's largest frequency has its own in a register.  Straight-line code: a divide in this
+                // place, inlined or called, doubled the kernel's time (r02x / r02z2) -- a model with TWO different
+                // frequencies beyond the table sets bit 1 of the error flag instead and the host codes the input again
+                // with pa_kernels.cuh.
+                rcp = fr >= g.pa_rcp_n ? dom_rcp : pa_rcp[min(fr, g.pa_rcp_n - 1u)];
                 pa_bad |= active && fr == 0u;
             } else {
                 const uint32_t addr = l3_entry_addr<METHOD, FID>(v, lane_tb, ent_stride, k8_stride, f, a.n_entries, k8, rf);
@@ -687,24 +704,14 @@ struct L3Reader {
 // symbols -- instead of a 32-byte STG per lane (14 LSU wavefronts per warp and iteration).  Byte-exact, and the LSU
 // wavefronts do go down, but the kernel does not get faster: ANSfold-1 1.956 -> 1.999 ms, ANS 2.18 -> 2.95 ms, the
 // 2^18-slot model 2.274 -> 2.240 ms at 2^30 symbols.)
-//
-// TABLE == DEC_PA_LANE = pseudo-adaptive mode (one model per block): every lane keeps ITS model in its own stretch of
-// shared memory -- cum[s] = slots before symbol s (u16) and a bucket index (the symbol that holds every 2^bshift-th
-// slot), built by the warp at the start of the task from DecArgs::pa_nfreqs -- and finds slot -> symbol by a binary
-// search between two bucket entries with a trip count fixed per task (the widest bucket of its 32 models); the
-// unfolded value and raw byte count follow arithmetically from the symbol.  Reader, state update and stores are the
-// same code.  (pa_kernels.cuh gives each block four lanes, one per state, with a shuffle-scan on the chain.)
-__host__ __device__ inline uint32_t pa3_cum_bytes(uint32_t syms) { return ((syms + 2u) * 2u + 7u) & ~7u; }
-__host__ __device__ inline uint32_t pa3_dec_tab_stride(uint32_t syms, uint32_t bucket_log2)
-{
-    uint32_t b = (pa3_cum_bytes(syms) + ((1u << bucket_log2) + 1u) * 2u + 7u) & ~7u;
-    return ((b >> 3) & 1u) ? b : b + 8u; // an odd number of 8-byte bank pairs between the lanes' tables
-}
-
+// (Measured in round 2 and dropped: a pseudo-adaptive flavour of this decoder -- one model per block, kept by its lane in
+// shared memory as 16-bit prefix sums + a bucket index, slot -> symbol by a binary search with a trip count fixed per
+// task, as the PA flavour of the encoder above keeps its tables.  Byte-exact, but 118 instructions per symbol against 39
+// here, the search being most of them: 1.40 ms for 2^27 symbols in 16 384 blocks against 1.14 ms for the four-lanes-per-
+// block decoder of pa_kernels.cuh; a finer bucket index no longer leaves room for four warps per SM.)
 template <int METHOD, int TABLE, int QI, int MAXW>
 __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs a)
 {
-    constexpr bool PA = (TABLE == DEC_PA_LANE);
     constexpr uint32_t ALIGN = 16u; // payload view and refill granularity
     constexpr int RING = L3DecGeom<QI>::kRing;
     constexpr int DIST = L3DecGeom<QI>::kDist;
@@ -712,23 +719,18 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const uint32_t frame = 1u << a.log2_frame;
     DecTables<METHOD, TABLE> tables;
-    const size_t table_bytes = PA ? size_t(blockDim.x) * a.pa_tab_stride : tables.load(a, smem_raw);
+    const size_t table_bytes = tables.load(a, smem_raw);
     uint8_t* s_rings = smem_raw + table_bytes;
     s_rings += (uint32_t(RING) - (smem_u32(s_rings) & uint32_t(RING - 1))) & uint32_t(RING - 1); // the host adds RING bytes of slack
 
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t warps_per_cta = blockDim.x >> 5;
-    uint32_t log2_frame = a.log2_frame; // (PA: the lane's own, set per task)
-    uint32_t frame_mask = frame - 1u;
-    uint32_t lower_shift = log2_frame + 4u; // L = 16 M (ans_fold.hpp:91); at most 32
-    uint32_t lower_lo = lower_shift >= 32u ? 0u : (1u << lower_shift);
+    const uint32_t log2_frame = a.log2_frame;
+    const uint32_t frame_mask = frame - 1u;
+    const uint32_t lower_shift = log2_frame + 4u; // L = 16 M (ans_fold.hpp:91); at most 32
+    const uint32_t lower_lo = lower_shift >= 32u ? 0u : (1u << lower_shift);
     const uint32_t lower_hi = lower_shift >= 32u ? 1u : 0u;
-    // PA: the warp's 32 tables, mine, my bucket index
-    const uint32_t pa_tabs = smem_u32(smem_raw) + warp * 32u * a.pa_tab_stride;
-    const uint16_t* my_cum = reinterpret_cast<const uint16_t*>(smem_raw + size_t(warp * 32u + lane) * a.pa_tab_stride);
-    const uint16_t* my_bkt = my_cum + (pa3_cum_bytes(a.pa_syms) >> 1);
-    uint32_t pa_bshift = 0, pa_trips = 0;
     const uint32_t rfold_bias = (METHOD == METHOD_RFOLD) ? (1u << (a.fidelity + 7)) : 0u; // ans_reorder_fold.hpp:301
     const uint32_t B = a.block_syms;
 
@@ -745,72 +747,6 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
         const uint32_t quads = nb >> 2;
         const uint32_t max_quads = __reduce_max_sync(0xffffffffu, quads);
         const bool uniform = __all_sync(0xffffffffu, have_block && quads == max_quads);
-
-        if (PA) {
-            // the 32 models of the task: cum[s] for s in [0, syms + 1], bucket[b] = symbol that holds slot b << bshift
-            // (bucket[n_buckets] = syms - 1: where the search in the last bucket ends), 128 symbols per step of the warp
-            const uint32_t syms = a.pa_syms; // multiple of 16
-            const uint32_t blog = a.pa_bucket_log2;
-            uint32_t widest = 0;
-            __syncwarp();
-            for (uint32_t j = 0; j < 32u; j++) {
-                const uint32_t m = min(task * 32u + j, a.n_blocks - 1u);
-                const uint32_t lg = a.pa_log2[m];
-                const uint32_t bs = lg > blog ? lg - blog : 0u;
-                const uint32_t n_buckets = 1u << (lg - bs);
-                const uint4* nf = reinterpret_cast<const uint4*>(a.pa_nfreqs + uint64_t(m) * a.pa_nbins);
-                const uint32_t tab = pa_tabs + j * a.pa_tab_stride;
-                const uint32_t bkt = tab + pa3_cum_bytes(syms);
-                const uint32_t bround = (1u << bs) - 1u;
-                uint32_t carry = 0;
-                for (uint32_t base = 0; base < syms; base += 128u) {
-                    const uint32_t s = base + 4u * lane;
-                    const uint4 q = s < syms ? __ldg(nf + (s >> 2)) : make_uint4(0u, 0u, 0u, 0u);
-                    const uint32_t mine = q.x + q.y + q.z + q.w;
-                    uint32_t incl = mine;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
-                        if (lane >= uint32_t(o))
-                            incl += up;
-                    }
-                    const uint32_t fr[4] = { q.x, q.y, q.z, q.w };
-                    uint32_t c[5];
-                    c[0] = carry + incl - mine;
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        c[i + 1] = c[i] + fr[i];
-                        if (fr[i]) {
-                            const uint32_t b1 = (c[i + 1] - 1u) >> bs;
-                            for (uint32_t b = (c[i] + bround) >> bs; b <= b1; b++)
-                                asm volatile("st.shared.u16 [%0], %1;" ::"r"(bkt + 2u * b), "h"(uint16_t(s + uint32_t(i))) : "memory");
-                        }
-                    }
-                    if (s < syms)
-                        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(tab + 2u * s), "r"((c[0] & 0xFFFFu) | (c[1] << 16)), "r"((c[2] & 0xFFFFu) | (c[3] << 16)) : "memory");
-                    carry += __shfl_sync(0xffffffffu, incl, 31);
-                }
-                if (lane == 0) {
-                    sts32(tab + 2u * syms, (carry & 0xFFFFu) | (carry << 16));
-                    asm volatile("st.shared.u16 [%0], %1;" ::"r"(bkt + 2u * n_buckets), "h"(uint16_t(syms - 1u)) : "memory");
-                }
-                __syncwarp();
-                for (uint32_t b = lane; b < n_buckets; b += 32u) {
-                    uint32_t s0, s1;
-                    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(s0) : "r"(bkt + 2u * b));
-                    asm volatile("ld.shared.u16 %0, [%1+2];" : "=r"(s1) : "r"(bkt + 2u * b));
-                    widest = max(widest, s1 - s0);
-                }
-            }
-            widest = __reduce_max_sync(0xffffffffu, widest);
-            pa_trips = 32u - uint32_t(__clz(widest)); // ceil(log2(widest + 1)) halvings settle every search
-            log2_frame = a.pa_log2[min(blk, a.n_blocks - 1u)];
-            pa_bshift = log2_frame > blog ? log2_frame - blog : 0u;
-            frame_mask = (1u << log2_frame) - 1u;
-            lower_shift = log2_frame + 4u; // < 32: log2 M <= 16 here
-            lower_lo = 1u << lower_shift;
-            __syncwarp();
-        }
 
         // ALIGN-byte aligned view of the payload; positions count bytes from pay16
         const uint8_t* pay = a.payload + (have_block ? a.offsets[blk] : 0);
@@ -862,8 +798,10 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
         // one symbol per chain: slot lookup + state update (ans_fold.hpp:216-220); returns the renormalisation flag
         uint32_t nlo[4], nhi[4], raw[4], kk[4];
         bool rn[4];
-        auto update = [&](int g, bool active, uint32_t freq, uint32_t offset, uint32_t k) {
+        auto advance = [&](int g, bool active) {
             const int c = 3 - g; // index 4t+g is decoded by state 3-g (ans_fold.hpp:300-305)
+            uint32_t freq, offset, k;
+            tables.lookup_raw(xlo[c] & frame_mask, freq, offset, raw[g], k);
             kk[g] = active ? k : 0u;
             const uint32_t q_lo = __funnelshift_r(xlo[c], xhi[c], log2_frame);
             const uint32_t q_hi = xhi[c] >> log2_frame;
@@ -872,62 +810,6 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
             nhi[g] = uint32_t(p >> 32) + freq * q_hi;
             // state < L = 2^(log2 M + 4)
             rn[g] = active && (lower_shift >= 32u ? nhi[g] == 0u : (nhi[g] == 0u && nlo[g] < lower_lo));
-        };
-        auto advance = [&](int g, bool active) {
-            uint32_t freq, offset, k;
-            if (PA) {
-                // largest symbol in [bucket[b], bucket[b + 1]] with cum[symbol] <= slot
-                const uint32_t slot = xlo[3 - g] & frame_mask;
-                uint32_t slo = my_bkt[slot >> pa_bshift], shi = my_bkt[(slot >> pa_bshift) + 1u];
-                for (uint32_t t = 0; t < pa_trips; t++) {
-                    const uint32_t mid = (slo + shi + 1u) >> 1;
-                    const bool le = uint32_t(my_cum[mid]) <= slot;
-                    slo = le ? mid : slo;
-                    shi = le ? shi : mid - 1u;
-                }
-                const uint32_t c0 = my_cum[slo];
-                freq = (uint32_t(my_cum[slo + 1u]) - c0) & 0xFFFFu;
-                offset = slot - c0;
-                raw[g] = pa_unmap<METHOD>(slo, a.fidelity, k);
-                raw[g] |= k << 30;
-            } else {
-                tables.lookup_raw(xlo[3 - g] & frame_mask, freq, offset, raw[g], k);
-            }
-            update(g, active, freq, offset, k);
-        };
-        // PA: the four searches of a quad in ONE loop (plain loads: their latencies overlap)
-        auto advance4 = [&](bool active) {
-            if (!PA) {
-#pragma unroll
-                for (int g = 0; g < 4; g++)
-                    advance(g, active);
-                return;
-            }
-            uint32_t slot[4], slo[4], shi[4];
-#pragma unroll
-            for (int g = 0; g < 4; g++) {
-                slot[g] = xlo[3 - g] & frame_mask;
-                slo[g] = my_bkt[slot[g] >> pa_bshift];
-                shi[g] = my_bkt[(slot[g] >> pa_bshift) + 1u];
-            }
-            for (uint32_t t = 0; t < pa_trips; t++) {
-#pragma unroll
-                for (int g = 0; g < 4; g++) {
-                    const uint32_t mid = (slo[g] + shi[g] + 1u) >> 1;
-                    const bool le = uint32_t(my_cum[mid]) <= slot[g];
-                    slo[g] = le ? mid : slo[g];
-                    shi[g] = le ? shi[g] : mid - 1u;
-                }
-            }
-#pragma unroll
-            for (int g = 0; g < 4; g++) {
-                const uint32_t c0 = my_cum[slo[g]];
-                const uint32_t freq = (uint32_t(my_cum[slo[g] + 1u]) - c0) & 0xFFFFu;
-                uint32_t k;
-                raw[g] = pa_unmap<METHOD>(slo[g], a.fidelity, k);
-                raw[g] |= k << 30;
-                update(g, active, freq, slot[g] - c0, k);
-            }
         };
         auto finish = [&](int g, bool active) -> uint32_t {
             const int c = 3 - g;
@@ -952,7 +834,9 @@ __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs
 #pragma unroll
                 for (int j = 0; j < QI; j++) {
                     const bool active = FULL || (q0 + uint32_t(j)) < quads;
-                    advance4(active);
+#pragma unroll
+                    for (int g = 0; g < 4; g++)
+                        advance(g, active);
 #pragma unroll
                     for (int g = 0; g < 4; g++)
                         val[4 * j + g] = finish(g, active);

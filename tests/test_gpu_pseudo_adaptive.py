@@ -170,3 +170,31 @@ def test_host_buffer_decode_in_runs_of_models(codec, monkeypatch, runs):
     with pytest.raises(P.B200AnsError):
         codec.pa_decompress(M_FOLD, 1, bad, n)
     assert np.array_equal(codec.pa_decompress(M_FOLD, 1, blob, n), data)
+
+
+@pytest.mark.parametrize("heavy,lane_per_block", [((0.5,), True), ((0.3, 0.3), False)])
+def test_lane_per_block_encoder_frequencies_beyond_its_reciprocal_table(codec, monkeypatch, heavy, lane_per_block):
+    """The lane-per-block encoder (lpb3_kernels.cuh, PA) takes reciprocals from a table indexed by the frequency. One
+    frequency beyond the table per model is served from a register; a model with two sends the whole input through the
+    four-lanes-per-block encoder again. Same bytes either way (a short table stands in for frequencies above 4096)."""
+    rng = np.random.default_rng(11)
+    n = 8192 * 5 + 100
+    data = rng.integers(2, 300, size=n, dtype=np.uint32)
+    u = rng.random(n)
+    lo = 0.0
+    for v, p in enumerate(heavy):
+        data[(u >= lo) & (u < lo + p)] = v
+        lo += p
+    monkeypatch.setenv("B200ANS_NO_PA3", "1")
+    want = codec.pa_compress(M_FOLD, 1, 8192, data).copy()
+    assert codec.stats().encode_kernel.decode() != "lpb3_encode_kernel<PA>"
+    monkeypatch.delenv("B200ANS_NO_PA3")
+    monkeypatch.setenv("B200ANS_PA3_RCPN", "257")
+    got = codec.pa_compress(M_FOLD, 1, 8192, data).copy()
+    assert (codec.stats().encode_kernel.decode() == "lpb3_encode_kernel<PA>") == lane_per_block
+    assert np.array_equal(got, want)
+    assert np.array_equal(codec.pa_decompress(M_FOLD, 1, got, n), data)
+    monkeypatch.delenv("B200ANS_PA3_RCPN")
+    got = codec.pa_compress(M_FOLD, 1, 8192, data).copy()
+    assert codec.stats().encode_kernel.decode() == "lpb3_encode_kernel<PA>"
+    assert np.array_equal(got, want)
