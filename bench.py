@@ -422,10 +422,12 @@ def north_star_summary(P, dev, stream, peak, names=("fold1", "fold2", "ans30"), 
     return out
 
 
-def copy_only(stream, dev, h_in, d_in, h_blob, d_blob, h_out, d_out, nbh, reps):
+def copy_only(stream, dev, h_in, d_in, h_blob, d_blob, h_out, d_out, nbh, reps, serial_encode=False):
     """The same bytes as one e2e step and nothing else: 4n in + container out (encode side), container in + 4n out
     (decode side), page-locked buffers, the two directions of each side on their own streams (PCIe is full duplex).
-    Returns ms per step -- the floor any host-buffer implementation on this box has."""
+    Returns ms per step -- the floor any host-buffer implementation on this box has. `serial_encode`: the encode side's
+    two copies one after the other, as the data dependence of a semi-static coder forces them (no byte of the container
+    exists before the whole input has been counted)."""
     import torch
 
     side = torch.cuda.Stream(device=dev)
@@ -436,6 +438,8 @@ def copy_only(stream, dev, h_in, d_in, h_blob, d_blob, h_out, d_out, nbh, reps):
         side.wait_stream(stream)
         with torch.cuda.stream(stream):
             d_in.copy_(h_in, non_blocking=True)
+        if serial_encode:
+            side.wait_stream(stream)
         with torch.cuda.stream(side):
             h_blob[:nbh].copy_(d_blob[:nbh], non_blocking=True)
         stream.wait_stream(side)
@@ -649,9 +653,10 @@ def run_ours(args, wl):
     d_out.zero_()
     barrier()
     copy_ms = copy_only(stream, dev, h_in, d_in, h_blob, d_blob, h_out, d_out, nbh, reps=min(3, e2e_steps))
+    copy_serial_ms = copy_only(stream, dev, h_in, d_in, h_blob, d_blob, h_out, d_out, nbh, reps=min(3, e2e_steps), serial_encode=True)
 
     # ---- reduce over ranks: MAX time ----------------------------------------------------------
-    t = torch.tensor([ms_total, e2e_ms, enc_ms, dec_ms, copy_ms, e2e_dev_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, e2e_ms, enc_ms, dec_ms, copy_ms, e2e_dev_ms, copy_serial_ms], dtype=torch.float64, device=dev)
     par_ok = True if parity is None else bool(parity.get("ok", True))
     okt = torch.tensor([int(ok and e2e_ok), int(par_ok)], dtype=torch.int32, device=dev)
     KEYS = ("histogram", "encode", "compact", "decode", "model_host", "allreduce")
@@ -660,7 +665,7 @@ def run_ours(args, wl):
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         dist.all_reduce(okt, op=dist.ReduceOp.MIN, group=group)
         dist.all_reduce(kt, op=dist.ReduceOp.MAX, group=group)
-    ms_total, e2e_ms, enc_ms, dec_ms, copy_ms, e2e_dev_ms = (float(x) for x in t.tolist())
+    ms_total, e2e_ms, enc_ms, dec_ms, copy_ms, e2e_dev_ms, copy_serial_ms = (float(x) for x in t.tolist())
     all_ok, par_all_ok = bool(okt[0].item()), bool(okt[1].item())
     for k, v in zip(KEYS, kt.tolist()):
         kern[k] = float(v)
@@ -730,6 +735,9 @@ def run_ours(args, wl):
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
                     "clock": "host wall clock, barrier to barrier, max over ranks", "device_ms_per_step": e2e_dev_ms / e2e_steps,
                     "copy_only_ms": copy_ms, "copy_only_gbs": gb_step / (copy_ms / 1e3),
+                    "copy_floor_ms": copy_serial_ms, "copy_floor_gbs": gb_step / (copy_serial_ms / 1e3),
+                    "copy_floor_note": "as copy_only, but the encode side's copy-out after its copy-in: a semi-static coder cannot write a byte "
+                                       "before it has counted the whole input, so this is the floor of b200ans_compress + b200ans_decompress",
                     "copy_only_note": "the same bytes per step with cudaMemcpyAsync only, both directions overlapped, all ranks at once",
                     "api": "b200ans_pa_compress + b200ans_pa_decompress (host buffers, pinned)" if pa
                     else "b200ans_compress + b200ans_decompress (host buffers, pinned)" if world == 1
