@@ -32,6 +32,7 @@ class Stats(C.Structure):
         ("n_blocks", C.c_uint32), ("prelude_bytes", C.c_uint64), ("payload_bytes", C.c_uint64),
         ("total_bytes", C.c_uint64), ("encode_kernel", C.c_char * 32), ("decode_kernel", C.c_char * 32),
         ("ms_allreduce", C.c_float), ("model_flags", C.c_uint32), ("model_cache_hits", C.c_uint64),
+        ("peer_exchanges", C.c_uint64),
     ]
 
 
@@ -95,6 +96,9 @@ SIGNATURES = {
     "b200ans_comm_unique_id": (C.c_int, [u8p]),
     "b200ans_comm_init": (C.c_int, [C.c_void_p, u8p, C.c_int, C.c_int]),
     "b200ans_comm_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "b200ans_comm_ipc_export": (C.c_int, [C.c_void_p, u8p]),
+    "b200ans_comm_ipc_attach": (C.c_int, [C.c_void_p, C.c_int, C.c_int, u8p]),
+    "b200ans_comm_ipc_release": (C.c_int, [C.c_void_p]),
     "b200ans_comm_release": (C.c_int, [C.c_void_p]),
     "b200ans_allreduce_hist": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200ans_compress_sharded_device": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, szp]),
@@ -403,6 +407,21 @@ class Codec:
 
     def comm_attach(self, nccl_comm, rank, world):
         self._check(self.lib.b200ans_comm_attach(self.h, nccl_comm, rank, world))
+
+    def comm_ipc_export(self):
+        """this rank's exchange buffer for the histogram exchange over NVLink peer memory, as 64 opaque bytes"""
+        h = np.zeros(64, dtype=np.uint8)
+        self._check(self.lib.b200ans_comm_ipc_export(self.h, _p(h, u8p)))
+        return h
+
+    def comm_ipc_attach(self, rank, world, handles):
+        """map the other ranks' exchange buffers (`handles`: world x 64 bytes in rank order)"""
+        hs = np.ascontiguousarray(handles, dtype=np.uint8).reshape(-1)
+        assert hs.size == 64 * world
+        self._check(self.lib.b200ans_comm_ipc_attach(self.h, rank, world, _p(hs, u8p)))
+
+    def comm_ipc_release(self):
+        self._check(self.lib.b200ans_comm_ipc_release(self.h))
 
     def comm_release(self):
         self._check(self.lib.b200ans_comm_release(self.h))

@@ -163,6 +163,13 @@ struct b200ans_ctx {
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
     bool pa3_off = false; // pa_compress: the retry without the lane-per-block encoder is running
+    // histogram exchange over NVLink peer memory (b200ans_comm_ipc_export / _attach): my exchange buffer, everybody's
+    // (ipc_peer[ipc_rank] is mine), how many exchanges have run
+    static constexpr int kIpcMaxWorld = 16;
+    void* ipc_buf = nullptr;
+    void* ipc_peer[kIpcMaxWorld] {};
+    int ipc_rank = 0, ipc_world = 0;
+    uint32_t ipc_epoch = 0;
     cudaEvent_t ev_side[2] {}; // fork / join of work that runs beside the main stream inside one call (remap: alphabets beside ranks)
 
     // grow-only device buffers
@@ -403,6 +410,13 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
         cudaFreeHost(c->pa_pinned);
     if (c->comm && c->own_comm && nccl_api().ok)
         nccl_api().CommDestroy(c->comm);
+    if (c->ipc_buf) {
+        for (int p = 0; p < c->ipc_world; p++)
+            if (p != c->ipc_rank && c->ipc_peer[p])
+                cudaIpcCloseMemHandle(c->ipc_peer[p]);
+        cudaFree(c->ipc_buf);
+        c->ipc_buf = nullptr;
+    }
     if (c->own_stream)
         cudaStreamDestroy(c->stream);
     delete c;
@@ -2184,6 +2198,80 @@ try {
 B200ANS_CATCH_INT
 
 // ==========================================================================================
+// histogram exchange over NVLink peer memory
+// ==========================================================================================
+// The semi-static model needs ONE exchange per input: the sum of every rank's bins (8 KiB for ANSfold-1).  At eight
+// GPUs an ncclAllReduce of that size costs 0.08-0.18 ms of a 3.1 ms step (profiles/r02m, r02s) -- launch, protocol
+// set-up and a ring or tree of hops for a payload that fits one packet per peer.  When the ranks are processes on one
+// NVSwitch node each of them exports an exchange buffer by CUDA IPC and maps everybody else's; the exchange is then ONE
+// kernel of one CTA: store my bins into my slot of every peer's buffer (remote stores over NVLink), fence, raise my
+// flag on every peer to this exchange's number (st.release.sys), wait until every peer's flag in MY buffer has reached
+// it (ld.acquire.sys, bounded spin), add the slots up.  Slots are double-buffered by the parity of the exchange number:
+// a rank cannot finish exchange e + 1 before every peer has entered it, i.e. has left exchange e, so nobody writes
+// into a slot that is still being read.  Payloads beyond a slot (ANSrfold's raw bins, 128 MiB) stay with NCCL.
+constexpr uint32_t kIpcFlagWords = 32;       // 64-bit words in front of the slots: one u32 flag per peer (+ padding)
+constexpr uint32_t kIpcSlotWords = 8192 + 8; // bins + the running maximum
+constexpr size_t kIpcBufBytes = (size_t(kIpcFlagWords) + size_t(2) * b200ans_ctx::kIpcMaxWorld * kIpcSlotWords) * 8;
+constexpr uint32_t kIpcSpinLimit = 1u << 24; // x >= 0.2 us: a peer that has not arrived after seconds is gone
+
+struct IpcArgs {
+    uint64_t* peer[b200ans_ctx::kIpcMaxWorld];
+    int rank, world;
+    uint32_t epoch;
+    uint64_t* bins;
+    uint32_t nbins;
+    uint32_t* d_max;
+};
+
+__global__ void __launch_bounds__(1024) ipc_allreduce_kernel(const IpcArgs a)
+{
+    const uint32_t par = a.epoch & 1u;
+    const uint32_t words = a.nbins + 1u; // the maximum rides behind the bins
+    const uint32_t mine_max = a.d_max ? *a.d_max : 0u;
+    for (int p = 0; p < a.world; p++) {
+        uint64_t* slot = a.peer[p] + kIpcFlagWords + size_t(par * b200ans_ctx::kIpcMaxWorld + uint32_t(a.rank)) * kIpcSlotWords;
+        for (uint32_t i = threadIdx.x; i < words; i += blockDim.x)
+            slot[i] = i < a.nbins ? a.bins[i] : uint64_t(mine_max);
+    }
+    __threadfence_system();
+    __syncthreads();
+    __shared__ uint32_t s_late;
+    if (threadIdx.x == 0)
+        s_late = 0u;
+    __syncthreads();
+    if (threadIdx.x < uint32_t(a.world)) {
+        uint32_t* theirs = reinterpret_cast<uint32_t*>(a.peer[threadIdx.x]) + a.rank; // my flag in that peer's buffer
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(a.epoch) : "memory");
+        const uint32_t* here = reinterpret_cast<const uint32_t*>(a.peer[a.rank]) + threadIdx.x;
+        uint32_t seen, spins = 0;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(here) : "memory");
+            if (int32_t(seen - a.epoch) >= 0)
+                break;
+            if (++spins > kIpcSpinLimit) {
+                atomicExch(&s_late, 1u);
+                break;
+            }
+            __nanosleep(200);
+        }
+    }
+    __syncthreads();
+    const uint64_t* base = a.peer[a.rank] + kIpcFlagWords + size_t(par * b200ans_ctx::kIpcMaxWorld) * kIpcSlotWords;
+    for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) {
+        uint64_t sum = 0, top = 0;
+        for (int p = 0; p < a.world; p++) {
+            const uint64_t v = __ldcg(base + size_t(p) * kIpcSlotWords + i); // (L2: the peers wrote it there)
+            sum += v;
+            top = max(top, v);
+        }
+        if (i < a.nbins)
+            a.bins[i] = (s_late && i == 0u) ? ~uint64_t(0) : sum; // a count nobody can have: the host reports the peer that never came
+        else if (a.d_max)
+            *a.d_max = uint32_t(top);
+    }
+}
+
+// ==========================================================================================
 // one-shot paths
 // ==========================================================================================
 namespace {
@@ -2191,6 +2279,22 @@ namespace {
 // in place on the context's stream: bins summed, *d_max maximised over the ranks (one NCCL group)
 int allreduce_hist(b200ans_ctx* c, uint64_t* d_bins, size_t nbins, uint32_t* d_max)
 {
+    if (c->ipc_world > 1 && nbins + 1 <= kIpcSlotWords && d_bins && nbins && !env_int("B200ANS_NO_IPC", 0)) {
+        IpcArgs a {};
+        for (int p = 0; p < c->ipc_world; p++)
+            a.peer[p] = static_cast<uint64_t*>(c->ipc_peer[p]);
+        a.rank = c->ipc_rank;
+        a.world = c->ipc_world;
+        a.epoch = ++c->ipc_epoch;
+        a.bins = d_bins;
+        a.nbins = uint32_t(nbins);
+        a.d_max = d_max;
+        ipc_allreduce_kernel<<<1, 1024, 0, c->stream>>>(a);
+        c->stats.launches++;
+        c->stats.peer_exchanges++;
+        CU(c, cudaGetLastError());
+        return B200ANS_OK;
+    }
     if (!c->comm) // (a world of one still goes through NCCL: the same code path as N > 1)
         return B200ANS_OK;
     const NcclApi& n = nccl_api();
@@ -2241,6 +2345,8 @@ int histogram_to_host(b200ans_ctx* c, int method, uint32_t f, const uint32_t* d_
         std::memcpy(host_bins.data(), c->pinned, nbins * 8);
         if (max_value)
             *max_value = c->h_small()->max_value;
+        if (sharded && nbins && host_bins[0] == ~uint64_t(0))
+            return c->fail(B200ANS_E_NCCL, "histogram exchange over peer memory: a rank did not arrive");
     } else {
         CU(c, cudaMemcpyAsync(host_bins.data(), c->bins.p, nbins * 8, cudaMemcpyDeviceToHost, c->stream));
         if (max_value)
@@ -2783,6 +2889,90 @@ try {
     c->own_comm = false;
     c->comm_rank = rank;
     c->comm_world = world;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+namespace {
+void ipc_release(b200ans_ctx* c)
+{
+    if (!c->ipc_buf)
+        return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (int p = 0; p < c->ipc_world; p++)
+        if (p != c->ipc_rank && c->ipc_peer[p])
+            cudaIpcCloseMemHandle(c->ipc_peer[p]);
+    cudaFree(c->ipc_buf);
+    c->ipc_buf = nullptr;
+    for (auto& p : c->ipc_peer)
+        p = nullptr;
+    c->ipc_world = 0;
+    c->ipc_rank = 0;
+    c->ipc_epoch = 0;
+}
+} // namespace
+
+extern "C" int b200ans_comm_ipc_export(b200ans_ctx* c, uint8_t handle[B200ANS_IPC_HANDLE_BYTES])
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!handle)
+        return c->fail(B200ANS_E_ARG, "comm_ipc_export: no room for the handle");
+    static_assert(sizeof(cudaIpcMemHandle_t) == B200ANS_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+    CU(c, cudaSetDevice(c->device));
+    ipc_release(c);
+    CU(c, cudaMalloc(&c->ipc_buf, kIpcBufBytes));
+    CU(c, cudaMemset(c->ipc_buf, 0, kIpcBufBytes));
+    CU(c, cudaDeviceSynchronize());
+    cudaIpcMemHandle_t h;
+    CU(c, cudaIpcGetMemHandle(&h, c->ipc_buf));
+    std::memcpy(handle, &h, sizeof h);
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_comm_ipc_attach(b200ans_ctx* c, int rank, int world, const uint8_t* handles)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    if (!handles || world < 1 || world > b200ans_ctx::kIpcMaxWorld || rank < 0 || rank >= world)
+        return c->fail(B200ANS_E_ARG, "comm_ipc_attach: bad rank / world (at most 16 ranks) / handles");
+    if (!c->ipc_buf)
+        return c->fail(B200ANS_E_ARG, "comm_ipc_attach: b200ans_comm_ipc_export comes first");
+    CU(c, cudaSetDevice(c->device));
+    for (int p = 0; p < world; p++) {
+        if (p == rank) {
+            c->ipc_peer[p] = c->ipc_buf;
+            continue;
+        }
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + size_t(p) * B200ANS_IPC_HANDLE_BYTES, sizeof h);
+        void* ptr = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            for (int q = 0; q < p; q++)
+                if (q != rank && c->ipc_peer[q]) {
+                    cudaIpcCloseMemHandle(c->ipc_peer[q]);
+                    c->ipc_peer[q] = nullptr;
+                }
+            return c->fail(B200ANS_E_NCCL, "comm_ipc_attach: cudaIpcOpenMemHandle failed (ranks must be processes on one NVLink node)");
+        }
+        c->ipc_peer[p] = ptr;
+    }
+    c->ipc_rank = rank;
+    c->ipc_world = world;
+    c->ipc_epoch = 0;
+    return B200ANS_OK;
+}
+B200ANS_CATCH_INT
+
+extern "C" int b200ans_comm_ipc_release(b200ans_ctx* c)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    ipc_release(c);
     return B200ANS_OK;
 }
 B200ANS_CATCH_INT

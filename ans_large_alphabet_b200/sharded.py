@@ -10,6 +10,8 @@ model without a broadcast.
 torch / torch.distributed are plumbing here (device buffers, the NCCL communicator); all coding
 work goes through the C-ABI of include/b200ans.h.
 """
+import os
+
 import numpy as np
 
 from ._capi import METHOD_FOLD, METHOD_INT, METHOD_MSB, METHOD_RFOLD
@@ -158,7 +160,35 @@ def init_comm(codec, group=None):
         t = t.cuda()
     dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
     codec.comm_init(t.cpu().numpy(), rank, world)
+    if world > 1 and os.environ.get("B200ANS_NO_IPC", "0") in ("", "0"):
+        init_ipc(codec, group)
     return rank, world
+
+
+def init_ipc(codec, group=None):
+    """The histogram exchange over NVLink peer memory (b200ans_comm_ipc_export / _attach): every rank exports its
+    exchange buffer, torch.distributed carries the 64-byte handles, every rank maps the others'.  For ranks that are
+    processes on one node; returns False (and leaves the NCCL path in place) where the buffers cannot be mapped."""
+    import torch
+    import torch.distributed as dist
+
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    mine = torch.from_numpy(codec.comm_ipc_export())
+    if dist.get_backend(group) == "nccl":
+        mine = mine.cuda()
+    every = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine, group=group)  # (also the barrier between everybody's export and anybody's attach)
+    ok = 1
+    try:
+        codec.comm_ipc_attach(rank, world, torch.stack(every).cpu().numpy())
+    except Exception:  # noqa: BLE001 -- not one node, or no peer access: every rank must then stay with NCCL
+        ok = 0
+    flag = torch.tensor([ok], dtype=torch.int32, device=mine.device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    if int(flag.item()) == 0:
+        codec.comm_ipc_release()
+        return False
+    return True
 
 
 def compress_shard(codec, method, f, d_src, n, d_dst, group=None, sync=None):

@@ -95,6 +95,8 @@ typedef struct b200ans_stats {
     uint32_t model_flags;   /* B200ANS_MODEL_* of the current encoder model            */
     uint64_t model_cache_hits; /* b200ans_model_load calls (decompress included) answered by the decoder model already
                                 * on the device: same method, fidelity and prelude bytes (since creation)           */
+    uint64_t peer_exchanges;   /* histogram exchanges that ran over NVLink peer memory (b200ans_comm_ipc_*; since
+                                * creation) -- the others went through ncclAllReduce                                 */
 } b200ans_stats;
 /* The model was normalised from 2^31 symbols or more: the reference's cross_entropy() sums the counts in an `int`
  * (util.hpp:288-289), so adjust_freqs' stopping rule changes -- in [2^31, 2^32) the first frame that fits is taken
@@ -241,8 +243,22 @@ int b200ans_comm_init(b200ans_ctx* ctx, const uint8_t id[B200ANS_COMM_ID_BYTES],
 /* or borrow a communicator the caller already has (an ncclComm_t as void*); never destroyed by the library */
 int b200ans_comm_attach(b200ans_ctx* ctx, void* nccl_comm, int rank, int world);
 int b200ans_comm_release(b200ans_ctx* ctx);
+/* Ranks that are processes on ONE NVLink / NVSwitch node can run the exchange over peer memory instead (CUDA IPC):
+ * every rank exports its exchange buffer (_export: 64 opaque bytes), hands the bytes to every other rank by any means,
+ * and maps the others' (_attach: `handles` = world x 64 bytes in rank order; every rank must have exported before any
+ * rank attaches).  b200ans_allreduce_hist and b200ans_compress_sharded[_device] then exchange payloads of up to 8192
+ * bins in ONE kernel -- remote stores into every peer's buffer, a release / acquire flag per peer, a local sum -- and
+ * keep NCCL for anything larger (ANSrfold's raw bins), so a communicator is still needed for those.  A rank that does
+ * not arrive within seconds makes the call fail with B200ANS_E_NCCL (the staged b200ans_allreduce_hist leaves ~0 in
+ * d_bins[0]).  _release: collective in effect -- no rank may still be exchanging; b200ans_destroy calls it.
+ * No counterpart in the reference. */
+#define B200ANS_IPC_HANDLE_BYTES 64
+int b200ans_comm_ipc_export(b200ans_ctx* ctx, uint8_t handle[B200ANS_IPC_HANDLE_BYTES]);
+int b200ans_comm_ipc_attach(b200ans_ctx* ctx, int rank, int world, const uint8_t* handles);
+int b200ans_comm_ipc_release(b200ans_ctx* ctx);
 /* in place, on the context's stream: d_bins[nbins] (device u64) summed over the ranks and, when d_max is not NULL,
- * *d_max (device u32) replaced by the maximum over the ranks -- one NCCL group. Without a communicator: no-op. */
+ * *d_max (device u32) replaced by the maximum over the ranks -- one kernel over peer memory after b200ans_comm_ipc_attach,
+ * else one NCCL group. Without either: no-op. */
 int b200ans_allreduce_hist(b200ans_ctx* ctx, uint64_t* d_bins, size_t nbins, uint32_t* d_max);
 /* b200ans_compress_device / b200ans_compress on this rank's shard with the GLOBAL model: histogram (K1) -> all-reduce
  * -> normalise -> encode (K2).  Collective: every rank of the communicator must call it, a rank whose shard is empty

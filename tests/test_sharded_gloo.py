@@ -102,7 +102,8 @@ def test_two_rank_global_model_equals_reference(tmp_path):
 
 
 # ---- -m gpu: the library's own NCCL exchange, two ranks (needs two GPUs; the 1-GPU box skips it) -------------------
-def _gpu_worker(rank, world, port, out_dir):
+def _gpu_worker(rank, world, port, out_dir, exchange):
+    os.environ["B200ANS_NO_IPC"] = "0" if exchange == "peer_memory" else "1"
     sys.path.insert(0, ROOT)
     sys.path.insert(0, HERE)
     import torch
@@ -137,14 +138,18 @@ def _gpu_worker(rank, world, port, out_dir):
         res[name + "_range"] = np.array([lo, hi])
         back = codec.decompress(method, f, blob, mine.size)
         res[name + "_ok"] = np.array([int(np.array_equal(back, mine))])
+    # fold-1, msb and plain ANS exchange 8 KiB .. 24 KiB: over peer memory when it is set up; ANSrfold's raw bins: NCCL
+    res["peer_exchanges"] = np.array([codec.stats().peer_exchanges])
     np.savez(os.path.join(out_dir, f"gpu_rank{rank}.npz"), **res)
+    dist.barrier()  # nobody unmaps an exchange buffer a peer may still be writing into
     codec.close()
     dist.barrier()
     dist.destroy_process_group()
 
 
 @pytest.mark.gpu
-def test_two_gpu_sharded_compress_uses_the_global_model(tmp_path):
+@pytest.mark.parametrize("exchange", ["peer_memory", "nccl"])  # b200ans_comm_ipc_* (one kernel over NVLink) / ncclAllReduce
+def test_two_gpu_sharded_compress_uses_the_global_model(tmp_path, exchange):
     import torch
 
     if torch.cuda.device_count() < 2:
@@ -156,8 +161,11 @@ def test_two_gpu_sharded_compress_uses_the_global_model(tmp_path):
 
     cpu = reference() if have_reference() else oracle()
     port = _free_port()
-    mp.spawn(_gpu_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_gpu_worker, args=(2, port, str(tmp_path), exchange), nprocs=2, join=True)
     r = [np.load(tmp_path / "gpu_rank0.npz"), np.load(tmp_path / "gpu_rank1.npz")]
+    for k in (0, 1):
+        n_peer = int(r[k]["peer_exchanges"][0])
+        assert (n_peer >= 3) if exchange == "peer_memory" else (n_peer == 0), n_peer
     for name in ("fold1_zipf20", "msb_zipf20", "int_geom", "rfold2_zipf20"):
         g = np.load(os.path.join(HERE, "golden", name + ".npz"))
         method, f, data = int(g["method"]), int(g["fidelity"]), g["data"]
