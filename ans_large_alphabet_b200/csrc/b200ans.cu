@@ -1965,11 +1965,13 @@ try {
 }
 B200ANS_CATCH_INT
 
-extern "C" int b200ans_decode_blocks_device(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_offsets,
-    const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst)
-try {
-    if (!c)
-        return B200ANS_E_ARG;
+namespace {
+// `expected_total` (or ~0): what the size scan in front of this call (its sum is in the context's control block) must
+// have added up to.  The size checks run on the device and the decoders return at once when one fails: ONE
+// synchronisation, behind the decode (round 2; there were three -- 40-50 us of a 1.1 ms config-2 step).
+int decode_blocks_impl(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_offsets, const uint32_t* d_block_bytes, size_t n,
+    uint32_t* d_dst, uint64_t expected_total)
+{
     if (!d_payload || !d_offsets || !d_block_bytes || !d_dst || n == 0)
         return c->fail(B200ANS_E_ARG, "decode_blocks: null argument");
     if (!c->have_dec)
@@ -1982,12 +1984,11 @@ try {
     CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
     {   // untrusted sizes: at least the four states, whole words for plain ANS
         const int grid = int(std::max<uint64_t>(1, std::min<uint64_t>((nb + 255) / 256, uint64_t(c->num_sms) * 4)));
-        check_block_sizes_kernel<<<grid, 256, 0, c->stream>>>(d_block_bytes, uint32_t(nb), coder_of(c->dec_method) == METHOD_INT && c->block_syms ? 3u : 0u, c->d_err());
+        const bool totals = expected_total != ~uint64_t(0);
+        check_block_sizes_kernel<<<grid, 256, 0, c->stream>>>(d_block_bytes, uint32_t(nb), coder_of(c->dec_method) == METHOD_INT && c->block_syms ? 3u : 0u, c->d_err(),
+            totals ? c->d_totals() : nullptr, expected_total);
         c->stats.launches++;
         CU(c, cudaGetLastError());
-        RET(read_small(c));
-        if (c->h_small()->error_flag)
-            return c->fail(B200ANS_E_FORMAT, "decode: a block is shorter than its four states, or a plain-ANS block is not a whole number of words");
     }
     CU(c, cudaEventRecord(c->ev[0], c->stream));
     RET(launch_decode(c, d_payload, d_offsets, d_block_bytes, n, bs, uint32_t(nb), d_dst));
@@ -1995,9 +1996,23 @@ try {
     RET(read_small(c));
     c->stats.ms_decode = elapsed(c->ev[0], c->ev[1]);
     c->stats.n_blocks = uint32_t(nb);
-    if (c->h_small()->error_flag)
+    const uint32_t flag = c->h_small()->error_flag;
+    if (flag == 4u)
+        return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
+    if (flag == 3u)
+        return c->fail(B200ANS_E_FORMAT, "decode: a block is shorter than its four states, or a plain-ANS block is not a whole number of words");
+    if (flag)
         return c->fail(B200ANS_E_FORMAT, "decode: a block's payload was not consumed exactly (corrupt stream or wrong model)");
     return B200ANS_OK;
+}
+} // namespace
+
+extern "C" int b200ans_decode_blocks_device(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_offsets,
+    const uint32_t* d_block_bytes, size_t n, uint32_t* d_dst)
+try {
+    if (!c)
+        return B200ANS_E_ARG;
+    return decode_blocks_impl(c, d_payload, d_offsets, d_block_bytes, n, d_dst, ~uint64_t(0));
 }
 B200ANS_CATCH_INT
 
@@ -3067,13 +3082,11 @@ try {
     scan_block_sizes_kernel<<<1, 1024, 0, c->stream>>>(d_sizes, h.n_blocks, c->offsets.as<uint64_t>(), c->d_totals(), nullptr);
     c->stats.launches++;
     CU(c, cudaGetLastError());
-    RET(read_small(c));
-    if (c->h_small()->totals[0] != h.payload_bytes)
-        return c->fail(B200ANS_E_FORMAT, "decompress: block size table does not add up");
     const uint32_t saved = c->block_syms;
     c->block_syms = h.block_syms;
     c->dec_words_aligned = true; // container blocks start 16-byte aligned (offsets come from our own scan)
-    const int rc = b200ans_decode_blocks_device(c, d_src + payload_at, c->offsets.as<uint64_t>(), d_sizes, n, d_dst);
+    // (the scan's total is compared with the header on the device, in front of the decoder)
+    const int rc = decode_blocks_impl(c, d_src + payload_at, c->offsets.as<uint64_t>(), d_sizes, n, d_dst, h.payload_bytes);
     c->dec_words_aligned = false;
     c->block_syms = saved;
     return rc;

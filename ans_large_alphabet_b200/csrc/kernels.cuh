@@ -678,6 +678,8 @@ constexpr int kDecRowBytes = kDecPad + kDecStageChunks * 16; // 304 = 19 * 16
 template <int METHOD, int TABLE, bool PA = false>
 __global__ void __launch_bounds__(kDecWarps * 32) decode_kernel(const DecArgs a)
 {
+    if (a.error_flag && *a.error_flag >= 3u) // the size checks in front of this launch failed (check_block_sizes_kernel)
+        return;
     static_assert(!PA || TABLE == DEC_FOLD_GLOBAL, "per-block models: folded slot tables in global memory");
     extern __shared__ __align__(16) uint8_t smem_raw[];
     DecTables<METHOD, TABLE> tables;
@@ -809,6 +811,8 @@ constexpr int kIntDecTile = 16; // steps per staged window: 16 steps x 4 lanes x
 template <int TABLE>
 __global__ void __launch_bounds__(kDecWarps * 32) int_decode_kernel(const DecArgs a)
 {
+    if (a.error_flag && *a.error_flag >= 3u) // the size checks in front of this launch failed (check_block_sizes_kernel)
+        return;
     static_assert(kDecPad + (kIntDecTile + 1) * 16 <= kDecRowBytes, "staged window does not fit the row");
     extern __shared__ __align__(16) uint8_t smem_raw[];
     DecTables<METHOD_INT, TABLE> tables;
@@ -966,16 +970,20 @@ __global__ void __launch_bounds__(1024) scan_block_sizes_kernel(const uint32_t* 
 
 // Untrusted size table: every block must hold its four 64-bit states (>= 32 bytes) and, where `align_mask` says so
 // (plain ANS: whole 32-bit words), be aligned; sets *flag = 3 otherwise.
+// `totals` / `expected` (optional): the size scan's sum must be what the container's header says (flag 4).  The block
+// decoders return at once when the flag is set, so neither verdict needs a host round trip in front of the decode.
 __global__ void __launch_bounds__(256) check_block_sizes_kernel(const uint32_t* __restrict__ bytes, uint32_t n_blocks, uint32_t align_mask,
-    uint32_t* __restrict__ flag)
+    uint32_t* __restrict__ flag, const uint64_t* __restrict__ totals = nullptr, uint64_t expected = 0)
 {
+    if (totals && blockIdx.x == 0 && threadIdx.x == 0 && totals[0] != expected)
+        atomicMax(flag, 4u);
     bool bad = false;
     for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < n_blocks; b += gridDim.x * blockDim.x) {
         const uint32_t v = __ldg(bytes + b);
         bad |= v < 32u || (v & align_mask) != 0u || v > 0x7FFFFF00u;
     }
     if (__any_sync(0xffffffffu, bad) && lane_id() == 0)
-        *flag = 3u;
+        atomicMax(flag, 3u);
 }
 
 // one warp per block: scratch + b*stride  ->  payload + offsets[b]; also fills the container's size table.

@@ -712,6 +712,8 @@ struct L3Reader {
 template <int METHOD, int TABLE, int QI, int MAXW>
 __global__ void __launch_bounds__(MAXW * 32, 1) lpb3_decode_kernel(const DecArgs a)
 {
+    if (a.error_flag && *a.error_flag >= 3u) // the size checks in front of this launch failed (check_block_sizes_kernel)
+        return;
     constexpr uint32_t ALIGN = 16u; // payload view and refill granularity
     constexpr int RING = L3DecGeom<QI>::kRing;
     constexpr int DIST = L3DecGeom<QI>::kDist;

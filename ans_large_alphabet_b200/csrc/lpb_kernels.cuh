@@ -319,6 +319,8 @@ constexpr int kLpbDecWarpBytes = 32 * (kLpbRing + kLpbDecOutRow);
 template <int METHOD, int TABLE>
 __global__ void __launch_bounds__(kLpbMaxWarps * 32, 1) lpb_decode_kernel(const DecArgs a)
 {
+    if (a.error_flag && *a.error_flag >= 3u) // the size checks in front of this launch failed (check_block_sizes_kernel)
+        return;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     constexpr bool kInt = (METHOD == METHOD_INT);
     const uint32_t frame = 1u << a.log2_frame;

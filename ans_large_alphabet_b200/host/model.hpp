@@ -229,9 +229,9 @@ inline std::vector<uint32_t> adjust_freqs(
                 continue;
             std::vector<uint32_t>& cur = cand[j];
             const uint32_t top = *std::max_element(cur.begin(), cur.end());
-            const double XH = detail::cross_entropy_shared_log(freqs, cur);
-            if (require_u16 && top >= std::numeric_limits<uint16_t>::max())
+            if (require_u16 && top >= std::numeric_limits<uint16_t>::max()) // (the reference computes XH first; it has no effect here)
                 return last_good;
+            const double XH = detail::cross_entropy_shared_log(freqs, cur);
             if (XH < limit)
                 return std::move(cur);
             last_good = cur;
