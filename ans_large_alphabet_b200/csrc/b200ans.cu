@@ -1660,7 +1660,7 @@ template <int METHOD> int launch_pa3_encode(b200ans_ctx* c, const EncArgs& a, ui
     const uint32_t warps = std::max<uint32_t>(1, std::min<uint32_t>(max_warps, (n_tasks + sms * waves - 1) / (sms * waves)));
     const uint32_t grid = std::min<uint32_t>(sms, (n_tasks + warps - 1) / warps);
     g.n_full_blocks = uint32_t(a.n / a.block_syms);
-    g.max_value = std::min(max_value_below(METHOD, a.fidelity, a.pa_syms), (1u << 30) - 1u);
+    g.max_value = METHOD == METHOD_INT ? 0xFFFFFFFFu : std::min(max_value_below(METHOD, a.fidelity, a.pa_syms), (1u << 30) - 1u);
 
     CUtensorMap tmap;
     const cuuint64_t dims[2] = { a.block_syms, g.n_full_blocks };
@@ -3313,12 +3313,22 @@ B200ANS_CATCH_INT
 // (pa_prelude_decode_kernel, pa_dec_tables_kernel, decode_kernel<.., PA>).  The host only lays the container out.
 namespace {
 
+constexpr uint32_t kPaIntMaxModelSyms = 16256; // bins 0 .. model_syms in 16 384 (prelude decoder depth, 16-bit symbols in the sort keys)
+// bins per model: the folded alphabet, or 0 .. model_syms for plain ANS (rounded up to a multiple of 16)
+uint32_t pa_bins(int method, uint32_t f, uint32_t model_syms)
+{
+    return method == METHOD_INT ? uint32_t(align_up(size_t(model_syms) + 1, 16)) : uint32_t(alphabet_bins(method, f, 0));
+}
+
 int pa_check(b200ans_ctx* c, int method, uint32_t f, uint32_t model_syms)
 {
-    if (!(method == METHOD_MSB || (method == METHOD_FOLD && f >= 1 && f <= 2)))
-        return c->fail(B200ANS_E_ARG, "pseudo-adaptive mode: ANSfold-1, ANSfold-2 and ANSmsb (alphabets up to 2048 bins)");
+    if (!(method == METHOD_MSB || method == METHOD_INT || (method == METHOD_FOLD && f >= 1 && f <= 2)))
+        return c->fail(B200ANS_E_ARG, "pseudo-adaptive mode: ANSfold-1, ANSfold-2, ANSmsb, and plain ANS over dense ranks");
     if (model_syms < 1024 || model_syms % 128 != 0 || model_syms > (1u << 24))
         return c->fail(B200ANS_E_ARG, "pseudo-adaptive mode: symbols per model must be a multiple of 128 in [1024, 2^24]");
+    // plain ANS: the alphabet of a block is 0 .. model_syms (ranks behind the driver's remap, pseudo_adaptive.cpp:83-99)
+    if (method == METHOD_INT && model_syms > kPaIntMaxModelSyms)
+        return c->fail(B200ANS_E_ARG, "pseudo-adaptive plain ANS: at most 16256 symbols per model");
     return B200ANS_OK;
 }
 
@@ -3372,7 +3382,7 @@ extern "C" size_t b200ans_pa_compress_bound(const b200ans_ctx* c, int method, ui
         return 0;
     const size_t models = (n + model_syms - 1) / model_syms;
     // per model: prelude (<= 8 bytes per bin + header), sizes, padding; per symbol at most 7 bytes + states
-    const size_t per_model = size_t(2048) * 8 + 128 + 8 + 32 + 64;
+    const size_t per_model = (method == METHOD_INT ? size_t(model_syms) + 16 : size_t(2048)) * 8 + 128 + 8 + 32 + 64;
     return B200ANS_HEADER_BYTES + models * per_model + n * (method == METHOD_INT ? 4 : 7) + 64;
 }
 
@@ -3407,7 +3417,7 @@ try {
         *out_bytes = B200ANS_HEADER_BYTES;
         return B200ANS_OK;
     }
-    const uint32_t nbins = uint32_t(alphabet_bins(method, f, 0));
+    const uint32_t nbins = pa_bins(method, f, model_syms);
     const size_t bins_bytes = size_t(nm) * nbins * 4;
     const size_t sizes_at = B200ANS_HEADER_BYTES;
     const size_t pre_at = align_up(sizes_at + size_t(nm) * 8, 16);
@@ -3421,10 +3431,9 @@ try {
     CU(c, cudaMemsetAsync(c->small.p, 0, 64, c->stream));
     {
         const size_t smem = size_t(4) * (nbins | 1u) * 4;
-        if (method == METHOD_MSB)
-            pa_histogram_kernel<METHOD_MSB><<<mgrid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
-        else
-            pa_histogram_kernel<METHOD_FOLD><<<mgrid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
+        auto hk = method == METHOD_MSB ? pa_histogram_kernel<METHOD_MSB> : method == METHOD_INT ? pa_histogram_kernel<METHOD_INT> : pa_histogram_kernel<METHOD_FOLD>;
+        CU(c, cudaFuncSetAttribute(hk, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        hk<<<mgrid, kPaThreads, smem, c->stream>>>(d_src, n, model_syms, nm, f, nbins, c->bins.as<uint32_t>(), c->d_max());
         c->stats.launches++;
         CU(c, cudaGetLastError());
     }
@@ -3469,7 +3478,7 @@ try {
         }
         const uint32_t fit_threads = nm * uint32_t(kPaFitGroup);
         pa_fit_kernel<<<(fit_threads + kPaFitThreads - 1) / kPaFitThreads, kPaFitThreads, 0, c->stream>>>(d_keys, n_keys, d_meta, nm, margin, d_lg,
-            d_status, c->d_max_log2(), c->pa_log2tab.as<double>());
+            d_status, c->d_max_log2(), c->pa_log2tab.as<double>(), method != METHOD_INT);
         pa_fit_store_kernel<<<(nm + 31) / 32, 32, 0, c->stream>>>(d_keys, n_keys, d_meta, nbins, nm, d_lg, d_status, c->pa_nfreqs.as<uint32_t>());
         c->stats.launches++;
         c->stats.launches += 2;
@@ -3481,6 +3490,8 @@ try {
     RET(read_small(c));
     c->stats.ms_histogram = elapsed(c->ev[3], c->ev[4]);
     const float ms_normalise = elapsed(c->ev[4], c->ev[5]);
+    if (method == METHOD_INT && c->h_small()->max_value > model_syms)
+        return c->fail(B200ANS_E_DOMAIN, "pseudo-adaptive plain ANS codes dense ranks: values up to the symbols per model");
     if (c->h_small()->max_value >= (1u << 30))
         return c->fail(B200ANS_E_DOMAIN, "folded coders need values < 2^30");
 
@@ -3504,7 +3515,13 @@ try {
             if (cnt[b])
                 max_sym = b;
         freqs.resize(size_t(max_sym) + 1);
-        const std::vector<uint32_t> nf = adjust_freqs(freqs, max_sym, true, c->h_approx);
+        // plain ANS has no 16-bit guard (ans_int.hpp:50) -- and without it adjust_freqs never returns for a block of ONE
+        // distinct symbol (entropy 0: no frame beats the limit).  The driver never codes such a block (pseudo_adaptive.cpp:114);
+        // here it gets the model the guarded normaliser gives it.
+        uint32_t distinct = 0;
+        for (uint32_t b = 0; b <= max_sym; b++)
+            distinct += cnt[b] != 0;
+        const std::vector<uint32_t> nf = adjust_freqs(freqs, max_sym, method != METHOD_INT || distinct < 2, c->h_approx);
         uint64_t frame = 0;
         for (uint32_t v : nf)
             frame += v;
@@ -3519,6 +3536,8 @@ try {
         CU(c, cudaStreamSynchronize(c->stream));
     }
     c->pa_undecided = undecided;
+    if (method == METHOD_INT && max_lg > 15u)
+        return c->fail(B200ANS_E_DOMAIN, "pseudo-adaptive plain ANS: a block's frame exceeds 2^15 slots (16-bit tables)");
     const float ms_host = float(now_ms() - t0);
 
     // Preludes on the device (the counts are no longer needed: their buffer is the coder's scratch), then their sizes
@@ -3533,12 +3552,14 @@ try {
     uint64_t* d_pre_off = reinterpret_cast<uint64_t*>(d_pre + size_t(nm) * pre_stride);
     uint32_t* d_pre_bytes = reinterpret_cast<uint32_t*>(d_pre_off + nm);
     {
-        const size_t smem = pa_prelude_enc_smem(nbins);
+        uint32_t pw = kPaPreEncWarps; // warps per CTA: as many as fit (plain ANS: 16 384 bins per model)
+        while (pw > 1 && pa_prelude_enc_smem(nbins, pw) + 2048 > c->max_smem)
+            pw >>= 1;
+        const size_t smem = pa_prelude_enc_smem(nbins, pw);
         CU(c, cudaFuncSetAttribute(pa_prelude_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         const uint32_t per_sm = uint32_t(std::max<size_t>(1, std::min<size_t>(8, (c->max_smem_sm - 4096) / (smem + 1024))));
-        const uint32_t grid = std::min<uint32_t>((nm + kPaPreEncWarps - 1) / kPaPreEncWarps, uint32_t(c->num_sms) * per_sm);
-        pa_prelude_encode_kernel<<<grid, kPaPreEncWarps * 32, smem, c->copy_in>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, d_lg, d_pre, pre_stride,
-            d_pre_bytes);
+        const uint32_t grid = std::min<uint32_t>((nm + pw - 1) / pw, uint32_t(c->num_sms) * per_sm);
+        pa_prelude_encode_kernel<<<grid, pw * 32, smem, c->copy_in>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, d_lg, d_pre, pre_stride, d_pre_bytes);
     }
     scan_block_sizes_kernel<<<1, 1024, 0, c->copy_in>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
     c->stats.launches += 2;
@@ -3571,7 +3592,9 @@ try {
     a.pa_nbins = nbins;
     {
         uint32_t kk;
-        const uint32_t top_sym = method == METHOD_MSB ? msb_map(c->h_small()->max_value, kk) : fold_map(c->h_small()->max_value, f, kk);
+        const uint32_t top_sym = method == METHOD_INT ? c->h_small()->max_value
+            : method == METHOD_MSB                    ? msb_map(c->h_small()->max_value, kk)
+                                                      : fold_map(c->h_small()->max_value, f, kk);
         a.pa_syms = std::min<uint32_t>(nbins, (top_sym + 1u + 15u) & ~15u);
     }
     const uint32_t n_tasks = (nm + 7) / 8;
@@ -3581,20 +3604,24 @@ try {
     // first choice: a lane per block (the L3 encoder with per-lane models, lpb3_kernels.cuh)
     int rc3 = 1;
     if (c->kernel_path != B200ANS_PATH_GROUP)
-        rc3 = method == METHOD_MSB ? launch_pa3_encode<METHOD_MSB>(c, a, max_lg) : launch_pa3_encode<METHOD_FOLD>(c, a, max_lg);
+        rc3 = method == METHOD_MSB ? launch_pa3_encode<METHOD_MSB>(c, a, max_lg)
+            : method == METHOD_INT ? launch_pa3_encode<METHOD_INT>(c, a, max_lg)
+                                   : launch_pa3_encode<METHOD_FOLD>(c, a, max_lg);
     if (rc3 < 0)
         return rc3;
     if (rc3 != B200ANS_OK && !smem_tables) {
         CU(c, c->enc_table.reserve(size_t(nm) * nbins * sizeof(EncEntry)));
         a.table = c->enc_table.as<EncEntry>();
-        pa_enc_tables_kernel<<<mgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, c->enc_table.as<EncEntry>());
+        pa_enc_tables_kernel<<<mgrid, kPaThreads, (size_t(nbins) + 8) * 4, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, c->enc_table.as<EncEntry>());
         c->stats.launches++;
         CU(c, cudaGetLastError());
         CU(c, cudaEventRecord(c->ev[0], c->stream));
     }
     if (rc3 == B200ANS_OK) {
     } else if (smem_tables) {
-        auto k = method == METHOD_MSB ? pa_smem_encode_kernel<METHOD_MSB> : pa_smem_encode_kernel<METHOD_FOLD>;
+        auto k = method == METHOD_MSB ? pa_smem_encode_kernel<METHOD_MSB>
+            : method == METHOD_INT    ? pa_smem_encode_kernel<METHOD_INT>
+                                      : pa_smem_encode_kernel<METHOD_FOLD>;
         CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
         k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
         set_name(c->stats.encode_kernel, "pa_smem_encode_kernel");
@@ -3605,6 +3632,9 @@ try {
         const size_t rows = size_t(kEncWarps) * 8 * kEncRowBytes;
         if (method == METHOD_MSB) {
             auto k = encode_kernel<METHOD_MSB, false, true>;
+            k<<<persistent_grid(c, k, kEncWarps * 32, rows, n_tasks, kEncWarps), kEncWarps * 32, rows, c->stream>>>(a);
+        } else if (method == METHOD_INT) {
+            auto k = encode_kernel<METHOD_INT, false, true>;
             k<<<persistent_grid(c, k, kEncWarps * 32, rows, n_tasks, kEncWarps), kEncWarps * 32, rows, c->stream>>>(a);
         } else {
             auto k = encode_kernel<METHOD_FOLD, false, true>;
@@ -3700,7 +3730,7 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
     const uint32_t nm = h.n_blocks;
     if (nm != (n + h.block_syms - 1) / h.block_syms)
         return c->fail(B200ANS_E_FORMAT, "pa_decompress: inconsistent block geometry");
-    const uint32_t nbins = uint32_t(alphabet_bins(method, f, 0));
+    const uint32_t nbins = pa_bins(method, f, h.block_syms);
     const size_t bins_bytes = size_t(nm) * nbins * 4;
     const size_t sizes_at = B200ANS_HEADER_BYTES;
     const size_t pre_at = align_up(sizes_at + size_t(nm) * 8, 16);
@@ -3811,7 +3841,7 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
     if (smem_tables && h_src && runs > 1) {
         // one launch per run of models; the pointers of the argument block move to the run's first model
         CU(c, cudaEventRecord(c->ev[0], c->stream));
-        auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
+        auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : method == METHOD_INT ? pa_smem_decode_kernel<METHOD_INT> : pa_smem_decode_kernel<METHOD_FOLD>;
         const size_t warp_bytes = size_t(8) * pa_dec_group_bytes(a.pa_syms, a.pa_bucket_log2);
         CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(size_t(pl.max_warps) * warp_bytes)));
         for (int r = 0; r < runs; r++) {
@@ -3847,7 +3877,7 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
             CU(c, cudaStreamWaitEvent(c->stream, c->ev_in[r], 0));
     if (smem_tables) {
         CU(c, cudaEventRecord(c->ev[0], c->stream));
-        auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : pa_smem_decode_kernel<METHOD_FOLD>;
+        auto k = method == METHOD_MSB ? pa_smem_decode_kernel<METHOD_MSB> : method == METHOD_INT ? pa_smem_decode_kernel<METHOD_INT> : pa_smem_decode_kernel<METHOD_FOLD>;
         CU(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(pl.smem)));
         k<<<pl.grid, pl.warps * 32, pl.smem, c->stream>>>(a);
         c->stats.launches++;
@@ -3858,10 +3888,8 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
             return c->fail(B200ANS_E_ARG, "pa_decompress: slot tables of all models exceed 48 GiB; decode in pieces");
         CU(c, c->dec_slots.reserve(slot_stride * nm * sizeof(DecEntry)));
         const int tgrid = int(std::min<uint32_t>(nm, uint32_t(c->num_sms) * 8));
-        if (method == METHOD_MSB)
-            pa_dec_tables_kernel<METHOD_MSB><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
-        else
-            pa_dec_tables_kernel<METHOD_FOLD><<<tgrid, kPaThreads, 0, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
+        auto tk = method == METHOD_MSB ? pa_dec_tables_kernel<METHOD_MSB> : method == METHOD_INT ? pa_dec_tables_kernel<METHOD_INT> : pa_dec_tables_kernel<METHOD_FOLD>;
+        tk<<<tgrid, kPaThreads, (size_t(nbins) + 8) * 4, c->stream>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, f, d_lg, c->dec_slots.as<DecEntry>(), slot_stride);
         c->stats.launches++;
         CU(c, cudaGetLastError());
         a.slots = c->dec_slots.as<DecEntry>();
@@ -3870,6 +3898,9 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
         const size_t smem = size_t(kDecWarps) * 8 * kDecRowBytes;
         if (method == METHOD_MSB) {
             auto k = decode_kernel<METHOD_MSB, DEC_FOLD_GLOBAL, true>;
+            k<<<persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps), kDecWarps * 32, smem, c->stream>>>(a);
+        } else if (method == METHOD_INT) {
+            auto k = decode_kernel<METHOD_INT, DEC_FOLD_GLOBAL, true>;
             k<<<persistent_grid(c, k, kDecWarps * 32, smem, n_tasks, kDecWarps), kDecWarps * 32, smem, c->stream>>>(a);
         } else {
             auto k = decode_kernel<METHOD_FOLD, DEC_FOLD_GLOBAL, true>;
@@ -3961,8 +3992,8 @@ try {
         return B200ANS_E_ARG;
     if (!d_dst || !out_bytes || (!d_src && n) || (reinterpret_cast<uintptr_t>(d_src) & 15) || (reinterpret_cast<uintptr_t>(d_dst) & 15))
         return c->fail(B200ANS_E_ARG, "pa_remap_compress: bad argument (device buffers must be 16-byte aligned)");
-    if (method != METHOD_MSB)
-        return c->fail(B200ANS_E_ARG, "pa_remap_compress: the remapped blocks are coded with ANSmsb (per-block plain ANS is not offered)");
+    if (method != METHOD_MSB && method != METHOD_INT)
+        return c->fail(B200ANS_E_ARG, "pa_remap_compress: the remapped blocks are coded with ANSmsb or plain ANS (run<ANSmsb> / run<ANSint>, pseudo_adaptive.cpp:235-236)");
     RET(pa_check(c, method, f, model_syms));
     CU(c, cudaSetDevice(c->device));
     const uint64_t nm64 = (n + model_syms - 1) / model_syms;
@@ -4053,7 +4084,7 @@ try {
     CU(c, cudaStreamSynchronize(c->stream));
     if (h.magic != B200ANS_MAGIC || h.version != 1 || h.flags != (kFlagPseudoAdaptive | kFlagRemap))
         return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: not a remapped pseudo-adaptive container");
-    if (h.method != method || method != METHOD_MSB)
+    if (h.method != method || (method != METHOD_MSB && method != METHOD_INT))
         return c->fail(B200ANS_E_FORMAT, "pa_remap_decompress: container was written by another method");
     if (h.n_symbols != n)
         return c->fail(B200ANS_E_ARG, "pa_remap_decompress: symbol count does not match the container");

@@ -1022,8 +1022,12 @@ __global__ void __launch_bounds__(256) compact_kernel(const uint8_t* __restrict_
 // ------------------------------------------------------------------------------------------
 
 // shared-memory byte offset of a value's bin (folded / msb alphabets), as in histogram_kernel<.., true>
-template <int METHOD> __device__ __forceinline__ uint32_t pa_bin_offset(uint32_t v, uint32_t f)
+// (plain ANS -- dense ranks behind the driver's remap: the bin is the value, clamped to the last bin; the host
+// rejects the input by its maximum then)
+template <int METHOD> __device__ __forceinline__ uint32_t pa_bin_offset(uint32_t v, uint32_t f, uint32_t last_bin = 0)
 {
+    if (METHOD == METHOD_INT)
+        return min(v, last_bin) << 2;
     const uint32_t step = METHOD == METHOD_MSB ? 256u : (255u << (f - 1u));
     uint32_t fl;
     if (METHOD == METHOD_MSB)
@@ -1055,15 +1059,15 @@ __global__ void __launch_bounds__(kPaThreads) pa_histogram_kernel(const uint32_t
         const uint4* in4 = reinterpret_cast<const uint4*>(in + first); // model_syms is a multiple of 128: aligned
         for (uint32_t i = threadIdx.x; i < (len >> 2); i += blockDim.x) {
             const uint4 q = __ldg(in4 + i);
-            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.x, fidelity));
-            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.y, fidelity));
-            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.z, fidelity));
-            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.w, fidelity));
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.x, fidelity, nbins - 1u));
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.y, fidelity, nbins - 1u));
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.z, fidelity, nbins - 1u));
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(q.w, fidelity, nbins - 1u));
             local_max = max(local_max, max(max(q.x, q.y), max(q.z, q.w)));
         }
         if (threadIdx.x < (len & 3u)) {
             const uint32_t v = in[first + (len & ~3u) + threadIdx.x];
-            red_shared_inc(mine_s + pa_bin_offset<METHOD>(v, fidelity));
+            red_shared_inc(mine_s + pa_bin_offset<METHOD>(v, fidelity, nbins - 1u));
             local_max = max(local_max, v);
         }
         __syncthreads();
@@ -1077,38 +1081,45 @@ __global__ void __launch_bounds__(kPaThreads) pa_histogram_kernel(const uint32_t
         atomicMax(max_value, local_max);
 }
 
-// exclusive prefix sum of a model's nfreqs into shared memory (nbins <= 2048); returns nothing, s_base[nbins] = M
+// exclusive prefix sum of a model's nfreqs into shared memory: s_base[0 .. nbins], s_base[nbins] = M
+// (2048 bins per pass of the CTA: each thread owns 8 consecutive bins; s_warp: kPaThreads / 32 + 1 words)
 __device__ __forceinline__ void pa_prefix(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t* s_base, uint32_t* s_warp)
 {
-    // each thread owns 8 consecutive bins (256 threads x 8 = 2048)
-    const uint32_t b0 = threadIdx.x * 8u;
-    uint32_t v[8], sum = 0;
+    uint32_t before = 0; // bins of the passes already done
+    for (uint32_t pass0 = 0; pass0 < nbins; pass0 += kPaThreads * 8u) {
+        const uint32_t b0 = pass0 + threadIdx.x * 8u;
+        uint32_t v[8], sum = 0;
 #pragma unroll
-    for (int j = 0; j < 8; j++) {
-        v[j] = b0 + j < nbins ? __ldg(nfreqs + b0 + j) : 0u;
-        sum += v[j];
-    }
-    uint32_t incl = sum;
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane_id() >= uint32_t(o))
-            incl += t;
-    }
-    if (lane_id() == 31)
-        s_warp[threadIdx.x >> 5] = incl;
-    __syncthreads();
-    uint32_t carry = 0;
-    for (uint32_t w = 0; w < (threadIdx.x >> 5); w++)
-        carry += s_warp[w];
-    uint32_t run = carry + incl - sum;
+        for (int j = 0; j < 8; j++) {
+            v[j] = b0 + j < nbins ? __ldg(nfreqs + b0 + j) : 0u;
+            sum += v[j];
+        }
+        uint32_t incl = sum;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane_id() >= uint32_t(o))
+                incl += t;
+        }
+        __syncthreads(); // (s_warp of the pass before has been read)
+        if (lane_id() == 31)
+            s_warp[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        uint32_t carry = before, all = 0;
+        for (uint32_t w = 0; w < kPaThreads / 32; w++) {
+            carry += w < (threadIdx.x >> 5) ? s_warp[w] : 0u;
+            all += s_warp[w];
+        }
+        uint32_t run = carry + incl - sum;
 #pragma unroll
-    for (int j = 0; j < 8; j++) {
-        if (b0 + j <= nbins)
-            s_base[b0 + j] = run;
-        run += v[j];
+        for (int j = 0; j < 8; j++) {
+            if (b0 + j <= nbins)
+                s_base[b0 + j] = run;
+            run += v[j];
+        }
+        before += all;
     }
-    if (threadIdx.x == blockDim.x - 1 && b0 + 8 <= nbins)
-        s_base[nbins] = run;
+    if (threadIdx.x == 0)
+        s_base[nbins] = before;
     __syncthreads();
 }
 
@@ -1125,7 +1136,7 @@ __device__ __forceinline__ double pa_reciprocal_up(uint32_t f)
 __global__ void __launch_bounds__(kPaThreads) pa_enc_tables_kernel(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t n_models,
     EncEntry* __restrict__ tables)
 {
-    __shared__ uint32_t s_base[2048 + 8];
+    extern __shared__ uint32_t s_base[]; // nbins + 8 words
     __shared__ uint32_t s_warp[kPaThreads / 32];
     for (uint32_t m = blockIdx.x; m < n_models; m += gridDim.x) {
         const uint32_t* nf = nfreqs + uint64_t(m) * nbins;
@@ -1148,7 +1159,7 @@ template <int METHOD>
 __global__ void __launch_bounds__(kPaThreads) pa_dec_tables_kernel(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t n_models,
     uint32_t fidelity, const uint8_t* __restrict__ log2_frame, DecEntry* __restrict__ slots, uint64_t slot_stride)
 {
-    __shared__ uint32_t s_base[2048 + 8];
+    extern __shared__ uint32_t s_base[]; // nbins + 8 words
     __shared__ uint32_t s_warp[kPaThreads / 32];
     for (uint32_t m = blockIdx.x; m < n_models; m += gridDim.x) {
         const uint32_t* nf = nfreqs + uint64_t(m) * nbins;
@@ -1167,7 +1178,9 @@ __global__ void __launch_bounds__(kPaThreads) pa_dec_tables_kernel(const uint32_
             }
             const uint32_t fr = s_base[lo + 1] - s_base[lo];
             uint32_t k = 0, value;
-            if (METHOD == METHOD_MSB)
+            if (METHOD == METHOD_INT)
+                value = lo;
+            else if (METHOD == METHOD_MSB)
                 value = msb_unmap(lo, k);
             else
                 value = fold_unmap(lo, fidelity, k);
@@ -1181,6 +1194,10 @@ __global__ void __launch_bounds__(kPaThreads) pa_dec_tables_kernel(const uint32_
 // symbol -> unfolded base value and raw byte count, arithmetically (pseudo-adaptive decoders: no slot table exists)
 template <int METHOD> __device__ __forceinline__ uint32_t pa_unmap(uint32_t s, uint32_t f, uint32_t& k)
 {
+    if (METHOD == METHOD_INT) {
+        k = 0;
+        return s;
+    }
     if (METHOD == METHOD_MSB)
         return msb_unmap(s, k);
     // fold_unmap (ans_fold.hpp:150-175) without the divide: k <= 3 because values stay below 2^30
@@ -1537,7 +1554,7 @@ __global__ void __launch_bounds__(kPaSortWarps * 32) pa_sort_kernel(const uint32
 constexpr int kPaFitGroup = 4;
 __global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* __restrict__ gkeys, uint32_t n_keys, const PaMeta* __restrict__ meta,
     uint32_t n_models, double margin, uint8_t* __restrict__ log2_frame, uint8_t* __restrict__ status, uint32_t* __restrict__ max_log2,
-    const double* __restrict__ log2_tab)
+    const double* __restrict__ log2_tab, bool require_u16)
 {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t j = t & uint32_t(kPaFitGroup - 1);
@@ -1563,6 +1580,10 @@ __global__ void __launch_bounds__(kPaFitThreads) pa_fit_kernel(const uint64_t* _
             if (st >= 0 || cj == 0xFFFFFFFFu)
                 continue;
             if (cj >= 65535u) { // the 16-bit guard: back to the last good fit (possibly none)
+                if (!require_u16) { // plain ANS has no guard (ans_int.hpp:50) and these coders no wider tables: the host decides
+                    st = 2;
+                    continue;
+                }
                 choice = last_good;
                 st = last_good < 0 ? 1 : 0;
                 continue;
@@ -1727,7 +1748,7 @@ __device__ __forceinline__ void pa_centered_code(uint32_t val, uint32_t u, uint3
     }
 }
 
-__host__ __device__ inline size_t pa_prelude_enc_smem(uint32_t nbins) { return size_t(kPaPreEncWarps) * (size_t(nbins) + 72u) * 4u; }
+__host__ __device__ inline size_t pa_prelude_enc_smem(uint32_t nbins, uint32_t warps = kPaPreEncWarps) { return size_t(warps) * (size_t(nbins) + 72u) * 4u; }
 
 // nfreqs[model][nbins], log2_frame[model]  ->  prelude bytes at pre + model * pre_stride, pre_bytes[model].
 // One WARP per model (round 2; the first version was one thread per model, 0.45 ms for 16 384 models next to the
@@ -1742,7 +1763,8 @@ __global__ void __launch_bounds__(kPaPreEncWarps * 32) pa_prelude_encode_kernel(
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     uint32_t* v = pa_pre_smem + size_t(warp) * (nbins + 72u); // the prefix sums the code is built on
     uint32_t* buf = v + nbins;                                 // 72 words of bit stream under construction
-    for (uint32_t m = blockIdx.x * kPaPreEncWarps + warp; m < n_models; m += gridDim.x * kPaPreEncWarps) {
+    const uint32_t cta_warps = blockDim.x >> 5; // (large alphabets leave room for fewer than kPaPreEncWarps)
+    for (uint32_t m = blockIdx.x * cta_warps + warp; m < n_models; m += gridDim.x * cta_warps) {
         const uint32_t* nf = nfreqs + uint64_t(m) * nbins;
         __syncwarp();
         uint32_t carry = 0, max_sym = 0;
@@ -1989,7 +2011,7 @@ __device__ __forceinline__ bool pa_interp_decode(PaWordReader& r, uint32_t n, W 
     return ok;
 }
 
-constexpr int kPaPreDepth = 14; // pending right halves: at most log2(n) + 1, n <= 8192 symbols per model
+constexpr int kPaPreDepth = 15; // pending right halves: at most log2(n) + 1, n <= 16384 symbols per model
 
 // prelude bytes of model m at src + offsets[m] (pre_bytes[m] of them)  ->  climb[model][0 .. n) (the prefix sums the code
 // carries), log2_frame[model] (0xFF: not a valid prelude), nfreqs[model][0] = n.  pa_prelude_finish_kernel follows.

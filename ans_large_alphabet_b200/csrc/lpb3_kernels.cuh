@@ -388,15 +388,17 @@ __global__ void __launch_bounds__(CFG::MAXW * 32, 1) lpb3_encode_kernel(const En
         // table entry of one value: {-freq, base, reciprocal}, 8 * (raw low bytes); v comes back as l3_entry_addr leaves it
         auto entry = [&](uint32_t& v, bool active, uint32_t& k8, uint32_t& nfr, uint32_t& base, double& rcp) {
             if (PA) {
-                uint32_t fl;
-                if (METHOD == METHOD_MSB)
+                uint32_t fl = 0;
+                if (METHOD == METHOD_INT)
+                    fl = 0; // plain ANS (dense ranks): the symbol is the value
+                else if (METHOD == METHOD_MSB)
                     fl = bfind_u32((max(v, 1u) - 1u) | 1u);
                 else if (FID == 1)
                     fl = bfind_u32(v | 1u);
                 else
                     fl = bfind_u32(v | (1u << (f - 1u))) - (f - 1u);
                 k8 = fl & 0x18u;
-                const uint32_t pa_step = (METHOD == METHOD_MSB) ? 256u : (255u << (f - 1u));
+                const uint32_t pa_step = (METHOD == METHOD_MSB) ? 256u : (METHOD == METHOD_INT) ? 0u : (255u << (f - 1u));
                 const uint32_t sym = min(mad_lo(k8 >> 3, pa_step, v >> k8), a.pa_syms); // entry pa_syms: frequency 0
                 // (plain loads, not asm volatile: the compiler is free to overlap the four lookups of a quad)
                 const uint32_t c0 = my_cum[sym], c1 = my_cum[sym + 1u];

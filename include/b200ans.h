@@ -272,7 +272,9 @@ int b200ans_compress_sharded(b200ans_ctx* ctx, int method, uint32_t fidelity, ui
 /* ---- pseudo-adaptive mode (src/pseudo_adaptive.cpp:64-177) ------------------------------ */
 /* Every `model_syms` consecutive symbols (a multiple of 128 in [1024, 2^24]) are coded with their own semi-static
  * model -- own histogram, own adjust_freqs, own prelude -- as the reference's driver does by calling T::encode block by
- * block; nothing is shared between blocks, so shards need no collective. Methods: ANSfold-1, ANSfold-2, ANSmsb.
+ * block; nothing is shared between blocks, so shards need no collective. Methods: ANSfold-1, ANSfold-2, ANSmsb, and
+ * plain ANS (B200ANS_METHOD_INT) for inputs whose values do not exceed model_syms <= 16256 -- the dense ranks the
+ * driver's remap produces (below); a block's alphabet is then 0 .. model_syms and its frame at most 2^15 slots.
  * Container: header (flags bit 0), u32 prelude bytes and u32 payload bytes per block, the preludes, the payloads;
  * prelude(b) followed by payload(b) is byte for byte what ans_X_compress() writes for block b (ans_fold.hpp:238-281).
  * The reference driver's dense-rank alphabet remap (pseudo_adaptive.cpp:83-105) is not applied: values are coded as
@@ -289,12 +291,15 @@ int b200ans_pa_decompress_device(b200ans_ctx* ctx, int method, uint32_t fidelity
 
 /* ---- pseudo-adaptive mode with the driver's dense-rank alphabet remap (src/pseudo_adaptive.cpp:83-125) ----
  * Per block of model_syms symbols: the values that occur become the ranks 1..sigma, the block is coded as those ranks
- * with ANSmsb (its own model, as b200ans_pa_compress), and the block alphabet goes in front as the driver writes it:
+ * with ANSmsb or plain ANS (its own model, as b200ans_pa_compress), and the block alphabet goes in front as the driver writes it:
  * [u32 sigma][u32 universe][interpolative code of the running sums of the sorted values].  Alphabet bytes and
  * prelude + payload of every block are byte-identical to the driver's output for that block (a block with one distinct
  * value still gets a coded body here; the driver writes the alphabet only).  Values up to 2^20 + 2^17 (the block's value
  * range is ranked in shared memory); an alphabet whose running sums pass 32 bits is B200ANS_E_DOMAIN, as it is outside
- * the driver's own working domain.  method: B200ANS_METHOD_MSB (per-block plain ANS is not offered). */
+ * the driver's own working domain.  method: B200ANS_METHOD_MSB or B200ANS_METHOD_INT (run<ANSmsb> / run<ANSint>,
+ * pseudo_adaptive.cpp:235-236; plain ANS: model_syms <= 16256, and a block with one distinct value -- which the driver
+ * never codes and for which ans_int.hpp's unguarded adjust_freqs would not terminate -- gets the guarded normaliser's
+ * model). */
 int b200ans_pa_remap_compress(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t model_syms, uint8_t* dst, size_t dst_capacity,
     const uint32_t* src, size_t n, size_t* out_bytes);
 int b200ans_pa_remap_decompress(b200ans_ctx* ctx, int method, uint32_t fidelity, uint32_t* dst, size_t n, const uint8_t* src, size_t src_bytes);

@@ -6,7 +6,7 @@ import pytest
 
 import _container
 import _inputs
-from _libs import M_MSB, have_reference, oracle, reference
+from _libs import M_INT, M_MSB, have_reference, oracle, reference
 
 pytestmark = pytest.mark.gpu
 
@@ -41,16 +41,19 @@ def split(blob, n, model_syms):
     return alphas, pres, pays
 
 
+@pytest.mark.parametrize("method", [M_MSB, M_INT])  # run<ANSmsb> / run<ANSint> (pseudo_adaptive.cpp:235-236)
 @pytest.mark.parametrize("kind,n,model_syms", [
     ("zipf20", 70_001, 8192), ("zipf16", 40_000, 1024), ("geom", 50_003, 4096), ("zipf12s", 100_000, 16384), ("u8", 9_000, 1024),
 ])
-def test_blocks_equal_the_reference_driver(codec, kind, n, model_syms):
+def test_blocks_equal_the_reference_driver(codec, kind, n, model_syms, method):
+    if method == M_INT and model_syms > 16256:
+        pytest.skip("per-block plain ANS: at most 16256 symbols per block")
     data = _inputs.make(kind, n, seed=41)
-    blob = codec.pa_remap_compress(M_MSB, 0, model_syms, data).copy()
+    blob = codec.pa_remap_compress(method, 0, model_syms, data).copy()
     alphas, pres, pays = split(blob, n, model_syms)
     for b in range(len(alphas)):
         block = data[b * model_syms : (b + 1) * model_syms]
-        want = cpu().pa_remap_block(M_MSB, 0, block)
+        want = cpu().pa_remap_block(method, 0, block)
         assert want is not None
         ref_blob, alpha_bytes, ranks = want
         # (equal but for the uninitialised padding bits of the reference's last interp word, bits.hpp:148)
@@ -59,7 +62,7 @@ def test_blocks_equal_the_reference_driver(codec, kind, n, model_syms):
             continue  # the driver writes the alphabet only (pseudo_adaptive.cpp:114)
         body = ref_blob[alpha_bytes:]
         assert _container.prelude_equal(pres[b], body[: pres[b].size]) and np.array_equal(pays[b], body[pres[b].size :]), f"block {b}: coded ranks differ"
-    assert np.array_equal(codec.pa_remap_decompress(M_MSB, 0, blob, n), data)
+    assert np.array_equal(codec.pa_remap_decompress(method, 0, blob, n), data)
 
 
 def test_large_round_trip_single_value_blocks_and_domain(codec):
@@ -81,8 +84,18 @@ def test_large_round_trip_single_value_blocks_and_domain(codec):
     with pytest.raises(P.B200AnsError) as e:  # value range beyond the shared-memory bitmap
         codec.pa_remap_compress(M_MSB, 0, 8192, np.array([1, 2, 3, 1 << 22] * 1000, dtype=np.uint32))
     assert e.value.code == -4
-    with pytest.raises(P.B200AnsError):  # per-block plain ANS is not offered
-        codec.pa_remap_compress(0, 0, 8192, data[:10000])
+    with pytest.raises(P.B200AnsError):  # the driver has no run<ANSfold>: ANSmsb and plain ANS only
+        codec.pa_remap_compress(1, 1, 8192, data[:10000])
+    # per-block plain ANS (run<ANSint>) at size: round trip, sampled blocks against the driver
+    blob_i = codec.pa_remap_compress(M_INT, 0, 8192, data).copy()
+    assert np.array_equal(codec.pa_remap_decompress(M_INT, 0, blob_i, n), data)
+    alphas_i, pres_i, pays_i = split(blob_i, n, 8192)
+    for b in (0, 7, 200, len(alphas_i) - 1):
+        block = data[b * 8192 : (b + 1) * 8192]
+        ref_blob, alpha_bytes, _ = cpu().pa_remap_block(M_INT, 0, block)
+        body = ref_blob[alpha_bytes:]
+        assert _container.prelude_equal(pres_i[b], body[: pres_i[b].size]) and np.array_equal(pays_i[b], body[pres_i[b].size :]), b
+    print(f"plain ANS of the ranks: {8.0 * blob_i.size / n:.3f} bits/symbol")
     bad = blob.copy()
     bad[64 + 4 * len(alphas) + 40] ^= 0x5A  # inside an alphabet
     try:

@@ -198,3 +198,25 @@ def test_lane_per_block_encoder_frequencies_beyond_its_reciprocal_table(codec, m
     got = codec.pa_compress(M_FOLD, 1, 8192, data).copy()
     assert codec.stats().encode_kernel.decode() == "lpb3_encode_kernel<PA>"
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("model_syms,n", [(1024, 30_000), (8192, 70_001)])
+def test_plain_ans_blocks_over_dense_ranks_equal_reference(codec, model_syms, n):
+    """Pseudo-adaptive plain ANS (run<ANSint> of the driver codes the dense ranks of its remap, pseudo_adaptive.cpp:235):
+    every block equals ans_int_compress(block); values beyond model_syms are outside the domain."""
+    import ans_large_alphabet_b200 as P
+
+    rng = np.random.default_rng(5)
+    data = np.minimum(rng.zipf(1.3, size=n), model_syms).astype(np.uint32)  # ranks 1 .. model_syms, skewed
+    blob = codec.pa_compress(M_INT, 0, model_syms, data).copy()
+    ref = cpu()
+    for m, (pre, pay) in enumerate(split(blob, n, model_syms)):
+        chunk = data[m * model_syms : (m + 1) * model_syms]
+        want = ref.compress(M_INT, 0, chunk)
+        assert pre.size + pay.size == want.size, m
+        assert _container.prelude_equal(pre, want[: pre.size]) and np.array_equal(pay, want[pre.size :]), m
+    assert np.array_equal(codec.pa_decompress(M_INT, 0, blob, n), data)
+    data[17] = model_syms + 1
+    with pytest.raises(P.B200AnsError) as e:
+        codec.pa_compress(M_INT, 0, model_syms, data)
+    assert e.value.code == -4

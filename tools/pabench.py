@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--model-syms", default="8192,16384,65536")
     ap.add_argument("--workload", default="fold1")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--remap-method", default="msb", choices=["msb", "int"], help="coder of the remapped blocks: ANSmsb or plain ANS")
     ap.add_argument("--remap", action="store_true", help="the driver's dense-rank remap in front of ANSmsb (b200ans_pa_remap_*), with the "
                     "reference driver's own BPI on a sample of blocks beside ours")
     args = ap.parse_args()
@@ -68,7 +69,7 @@ def main():
     if args.remap:
         import numpy as np
         from _libs import have_reference, reference
-        M_MSB = 2
+        M_MSB = 2 if args.remap_method == "msb" else 0  # (the method of the remapped blocks)
         for S in [int(x) for x in args.model_syms.split(",")]:
             cap = codec.pa_bound(M_MSB, S, n) + n * 4 + (n // S + 2) * 48 + 256
             d_blob = torch.empty((cap + 15) // 16 * 16, dtype=torch.uint8, device=dev)
@@ -83,7 +84,7 @@ def main():
                     codec.pa_remap_decompress_device(M_MSB, 0, d_out.data_ptr(), n, d_blob.data_ptr(), nb)
                     stream.synchronize()
                     t2 = time.perf_counter()
-                row = dict(mode="remap + ANSmsb", model_syms=S, n=n, blocks=(n + S - 1) // S, enc_wall_ms=(t1 - t0) * 1e3, dec_wall_ms=(t2 - t1) * 1e3,
+                row = dict(mode="remap + " + ("ANSmsb" if args.remap_method == "msb" else "ANS"), model_syms=S, n=n, blocks=(n + S - 1) // S, enc_wall_ms=(t1 - t0) * 1e3, dec_wall_ms=(t2 - t1) * 1e3,
                            bits_per_symbol_with_alphabets=8.0 * nb / n, enc_gbs=4.0 * n / (t1 - t0) / 1e9, dec_gbs=4.0 * n / (t2 - t1) / 1e9)
                 if it and (best is None or row["enc_wall_ms"] + row["dec_wall_ms"] < best["enc_wall_ms"] + best["dec_wall_ms"]):
                     best = row
