@@ -1816,6 +1816,16 @@ int launch_decode(b200ans_ctx* c, const uint8_t* d_payload, const uint64_t* d_of
             case METHOD_RFOLD: return launch_lpb_decode_tt<METHOD_RFOLD, DEC_INT_GLOBAL>(c, a, 0);
             }
         }
+        // two copies of the slot table (kernels.cuh DEC_FOLD_SMEM2) when they leave room for 16 warps of rings and the
+        // L3 decoder takes the input; B200ANS_DEC_TWICE=0 keeps one
+        const bool l3 = (reinterpret_cast<uintptr_t>(a.out) & 31) == 0 && a.block_syms % 8u == 0u && !env_int("B200ANS_NO_L3", 0) && !env_int("B200ANS_L3_DEC", 0);
+        if (smem && l3 && env_int("B200ANS_DEC_TWICE", 1) && 2 * tb + 256 + 1024 + size_t(16) * L3DecGeom<2>::kWarpBytes <= c->max_smem) {
+            switch (coder_of(c->dec_method)) {
+            case METHOD_FOLD: return launch_lpb_decode_tt<METHOD_FOLD, DEC_FOLD_SMEM2>(c, a, 2 * tb);
+            case METHOD_MSB: return launch_lpb_decode_tt<METHOD_MSB, DEC_FOLD_SMEM2>(c, a, 2 * tb);
+            case METHOD_RFOLD: return launch_lpb_decode_tt<METHOD_RFOLD, DEC_FOLD_SMEM2>(c, a, 2 * tb);
+            }
+        }
         switch (coder_of(c->dec_method)) {
         case METHOD_FOLD:
             return smem ? launch_lpb_decode_tt<METHOD_FOLD, DEC_FOLD_SMEM>(c, a, tb)

@@ -110,7 +110,13 @@ struct DecArgs {
     uint32_t* error_flag;     // set to 2 when a block's payload is not consumed exactly (corrupt container); may be null
 };
 
-enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3, DEC_INT_SMEM_PURE = 4 };
+enum dec_table_kind : int { DEC_FOLD_SMEM = 0, DEC_FOLD_GLOBAL = 1, DEC_INT_SMEM = 2, DEC_INT_GLOBAL = 3, DEC_INT_SMEM_PURE = 4, DEC_FOLD_SMEM2 = 5 };
+
+// DEC_FOLD_SMEM2: the M-entry slot table TWICE in shared memory, copy r in the odd / even 8-byte units (entry `slot` of
+// copy r at unit 2 * slot + r), lanes with an even lane id reading copy 0 and the others copy 1.  A random 8-byte lookup by
+// a half-warp then spreads 8 lanes over 8 bank pairs twice instead of 16 lanes over 16 -- an expected maximum of 2.4
+// lanes per pair instead of 3.1, 4.8 shared-memory wavefronts per lookup instead of 6.2 -- with the same instructions (the
+// copy is chosen by the lane's base pointer, the index scales by 16 bytes instead of 8).
 
 // DEC_INT_SMEM_PURE: the same index, but a 32-slot group that lies inside ONE symbol (no symbol starts at its slots
 // 1..31) carries that symbol's answer in its own record -- x = base | rank<11:0> << 20, y = 1 << 31 | rank<22:12> << 20 |
@@ -127,7 +133,8 @@ template <int METHOD, int TABLE> struct DecTables {
     static constexpr bool kPure = (TABLE == DEC_INT_SMEM_PURE);
     static constexpr bool kInt = (TABLE == DEC_INT_SMEM || TABLE == DEC_INT_GLOBAL || kPure); // rank/select lookup
     static constexpr bool kPacked = kInt && METHOD != METHOD_INT;                             // sym[] = value | k << 30
-    static constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM || kPure);
+    static constexpr bool kTwice = (TABLE == DEC_FOLD_SMEM2);
+    static constexpr bool kSmem = (TABLE == DEC_FOLD_SMEM || TABLE == DEC_INT_SMEM || kPure || kTwice);
     const DecEntry* slots;
     const RankRec* rec;
     const uint32_t* sym;
@@ -143,7 +150,7 @@ template <int METHOD, int TABLE> struct DecTables {
             return ((words * 8 + 15) & ~size_t(15)) + ((size_t(n_present) * 8 + 15) & ~size_t(15))
                 + (dense ? 0 : ((size_t(n_present) * 4 + 15) & ~size_t(15)));
         }
-        return (size_t(frame) * sizeof(DecEntry) + 15) & ~size_t(15);
+        return (size_t(frame) * sizeof(DecEntry) * (kTwice ? 2 : 1) + 15) & ~size_t(15);
     }
 
     // cooperative copy into shared memory (all threads of the CTA); returns the bytes used
@@ -180,9 +187,17 @@ template <int METHOD, int TABLE> struct DecTables {
         } else {
             const uint2* src = reinterpret_cast<const uint2*>(a.slots);
             uint2* dst = reinterpret_cast<uint2*>(smem);
-            for (size_t i = threadIdx.x; i < frame; i += blockDim.x)
-                dst[i] = __ldg(src + i);
-            slots = reinterpret_cast<const DecEntry*>(smem);
+            if (kTwice) {
+                for (size_t i = threadIdx.x; i < frame; i += blockDim.x) {
+                    const uint2 e = __ldg(src + i);
+                    *reinterpret_cast<uint4*>(dst + 2 * i) = make_uint4(e.x, e.y, e.x, e.y);
+                }
+                slots = reinterpret_cast<const DecEntry*>(smem) + (threadIdx.x & 1u);
+            } else {
+                for (size_t i = threadIdx.x; i < frame; i += blockDim.x)
+                    dst[i] = __ldg(src + i);
+                slots = reinterpret_cast<const DecEntry*>(smem);
+            }
         }
         __syncthreads();
         return smem_bytes(frame, a.n_present, a.dense);
@@ -196,7 +211,9 @@ template <int METHOD, int TABLE> struct DecTables {
             if (kPacked)
                 raw |= k << 30;
         } else {
-            const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(slots + slot) : __ldg(reinterpret_cast<const uint2*>(slots + slot));
+            const uint2 e = kTwice ? *reinterpret_cast<const uint2*>(slots + 2u * slot)
+                : kSmem            ? *reinterpret_cast<const uint2*>(slots + slot)
+                                   : __ldg(reinterpret_cast<const uint2*>(slots + slot));
             freq = e.x & 0xFFFFu;
             offset = e.x >> 16;
             raw = e.y;
@@ -233,7 +250,9 @@ template <int METHOD, int TABLE> struct DecTables {
                 mapped &= 0x3FFFFFFFu;
             }
         } else {
-            const uint2 e = kSmem ? *reinterpret_cast<const uint2*>(slots + slot) : __ldg(reinterpret_cast<const uint2*>(slots + slot));
+            const uint2 e = kTwice ? *reinterpret_cast<const uint2*>(slots + 2u * slot)
+                : kSmem            ? *reinterpret_cast<const uint2*>(slots + slot)
+                                   : __ldg(reinterpret_cast<const uint2*>(slots + slot));
             freq = e.x & 0xFFFFu;
             offset = e.x >> 16;
             mapped = e.y & 0x3FFFFFFFu;
