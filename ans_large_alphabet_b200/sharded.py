@@ -173,16 +173,21 @@ def init_ipc(codec, group=None):
     import torch.distributed as dist
 
     rank, world = dist.get_rank(group), dist.get_world_size(group)
-    mine = torch.from_numpy(codec.comm_ipc_export())
+    ok = 1
+    try:
+        handle = codec.comm_ipc_export()
+    except Exception:  # noqa: BLE001 -- no IPC here: this rank still takes part in the collectives below, then everybody stays with NCCL
+        handle, ok = np.zeros(64, dtype=np.uint8), 0
+    mine = torch.from_numpy(handle)
     if dist.get_backend(group) == "nccl":
         mine = mine.cuda()
     every = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(every, mine, group=group)  # (also the barrier between everybody's export and anybody's attach)
-    ok = 1
-    try:
-        codec.comm_ipc_attach(rank, world, torch.stack(every).cpu().numpy())
-    except Exception:  # noqa: BLE001 -- not one node, or no peer access: every rank must then stay with NCCL
-        ok = 0
+    if ok:
+        try:
+            codec.comm_ipc_attach(rank, world, torch.stack(every).cpu().numpy())
+        except Exception:  # noqa: BLE001 -- not one node, or no peer access
+            ok = 0
     flag = torch.tensor([ok], dtype=torch.int32, device=mine.device)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
     if int(flag.item()) == 0:
