@@ -1643,107 +1643,16 @@ __global__ void __launch_bounds__(kPaFitThreads) pa_fit_store_kernel(const uint6
 
 
 // ------------------------------------------------------------------------------------------
-// Preludes on the device (pseudo-adaptive mode): one thread per model writes / reads the reference-format prelude
+// Preludes on the device (pseudo-adaptive mode): the reference-format prelude of every model,
 //   vbyte(max_sym) . u8(log2 M) . binary interpolative code of the prefix sums of (nfreq + 1)
 // (ans_util.hpp:25-63, interp.hpp:28-118, bits.hpp:146-218; same bits as host/prelude.hpp).  The recursion of the
-// interpolative code is data-independent in shape, so it runs on an explicit stack of at most 12 frames.
+// interpolative code is data-independent in shape: the encoder walks it by position (a warp per model, 32 nodes at a
+// time), the decoder on an explicit stack (a thread per model: where a node starts depends on every node before it).
 // ------------------------------------------------------------------------------------------
-struct PaBitWriter {
-    uint8_t* out;
-    uint64_t acc = 0;
-    uint32_t fill = 0;
-    __device__ __forceinline__ void spill()
-    {
-        const uint32_t w = uint32_t(acc);
-        out[0] = uint8_t(w), out[1] = uint8_t(w >> 8), out[2] = uint8_t(w >> 16), out[3] = uint8_t(w >> 24);
-        out += 4;
-        acc >>= 32;
-        fill -= 32;
-    }
-    __device__ __forceinline__ void put(uint32_t value, uint32_t width)
-    {
-        if (width == 0)
-            return;
-        acc |= uint64_t(value & (0xFFFFFFFFu >> (32u - width))) << fill;
-        fill += width;
-        if (fill >= 32)
-            spill();
-    }
-    __device__ __forceinline__ void finish()
-    {
-        if (fill != 0) {
-            fill = 32;
-            spill();
-        }
-    }
-};
-
-struct PaBitReader {
-    const uint8_t* in;
-    uint32_t pos = 0;   // byte position of the next word
-    uint32_t limit = 0; // bytes that exist (reads beyond return zero)
-    uint64_t acc = 0;
-    uint32_t fill = 0;
-    __device__ __forceinline__ uint32_t byte(uint32_t i) const { return i < limit ? in[i] : 0u; }
-    __device__ __forceinline__ uint32_t get(uint32_t width)
-    {
-        if (width == 0)
-            return 0;
-        if (fill < width) {
-            const uint32_t w = byte(pos) | (byte(pos + 1) << 8) | (byte(pos + 2) << 16) | (byte(pos + 3) << 24);
-            pos += 4;
-            acc |= uint64_t(w) << fill;
-            fill += 32;
-        }
-        const uint32_t v = uint32_t(acc) & (0xFFFFFFFFu >> (32u - width));
-        acc >>= width;
-        fill -= width;
-        return v;
-    }
-};
-
-// centred minimal binary code for val in [1, u], u < 2^31 (host/prelude.hpp put_centered / get_centered)
-__device__ __forceinline__ void pa_put_centered(PaBitWriter& w, uint32_t val, uint32_t u)
-{
-    if (u == 1)
-        return;
-    const uint32_t b = 32u - __clz(u - 1u);
-    const uint32_t span = 1u << b;
-    const uint32_t longs = 2u * u - span;
-    val += u - (longs >> 1);
-    if (val > u)
-        val -= u;
-    const uint32_t shorts = span - u;
-    if (val <= shorts) {
-        w.put(val - 1u, b - 1u);
-    } else {
-        val += shorts;
-        w.put((val - 1u) >> 1, b - 1u);
-        w.put((val - 1u) & 1u, 1u);
-    }
-}
-
-__device__ __forceinline__ uint32_t pa_get_centered(PaBitReader& r, uint32_t u)
-{
-    if (u == 1)
-        return 1;
-    const uint32_t b = 32u - __clz(u - 1u);
-    const uint32_t span = 1u << b;
-    const uint32_t longs = 2u * u - span;
-    const uint32_t shorts = span - u;
-    uint32_t val = r.get(b - 1u) + 1u;
-    if (val > shorts)
-        val = 2u * val + r.get(1u) - shorts - 1u;
-    val += longs >> 1;
-    if (val > u)
-        val -= u;
-    return val;
-}
-
 constexpr int kPaPreThreads = 64;
 constexpr int kPaPreEncWarps = 8; // models per CTA of the prelude encoder
 
-// codeword of the centred minimal binary code as one LSB-first bit string (what pa_put_centered writes), u < 2^31
+// codeword of the centred minimal binary code as one LSB-first bit string (host/prelude.hpp put_centered), u < 2^31
 __device__ __forceinline__ void pa_centered_code(uint32_t val, uint32_t u, uint32_t& code, uint32_t& nbits)
 {
     code = 0;

@@ -134,76 +134,7 @@ __global__ void __launch_bounds__(kRemapThreads) remap_block_kernel(const uint32
     }
 }
 
-// centred minimal binary code with 64-bit arithmetic: u up to 2^32 (host/prelude.hpp put_centered / get_centered)
-__device__ __forceinline__ void remap_put_centered(PaBitWriter& w, uint64_t val, uint64_t u)
-{
-    if (u == 1)
-        return;
-    const uint32_t b = 64u - uint32_t(__clzll((long long)(u - 1u)));
-    const uint64_t span = uint64_t(1) << b;
-    const uint64_t longs = 2u * u - span;
-    val += u - (longs >> 1);
-    if (val > u)
-        val -= u;
-    const uint64_t shorts = span - u;
-    if (val <= shorts) {
-        w.put(uint32_t(val - 1u), b - 1u);
-    } else {
-        val += shorts;
-        w.put(uint32_t((val - 1u) >> 1), b - 1u);
-        w.put(uint32_t((val - 1u) & 1u), 1u);
-    }
-}
-// LSB-first bit reader over aligned 32-bit words (the alphabets start 16-byte aligned); reads beyond `limit` words give zero
-struct RemapReader {
-    const uint32_t* in;
-    uint32_t pos = 0;   // words taken so far
-    uint32_t limit = 0; // words that exist
-    uint32_t ahead0 = 0, ahead1 = 0; // the next two words, loaded before they are needed (a thread decodes alone: nothing else hides the latency)
-    uint64_t acc = 0;
-    uint32_t fill = 0;
-    __device__ __forceinline__ void start()
-    {
-        ahead0 = 0 < limit ? __ldg(in) : 0u;
-        ahead1 = 1 < limit ? __ldg(in + 1) : 0u;
-    }
-    __device__ __forceinline__ uint32_t get(uint32_t width)
-    {
-        if (width == 0)
-            return 0;
-        if (fill < width) {
-            const uint32_t w = ahead0;
-            ahead0 = ahead1;
-            ahead1 = pos + 2u < limit ? __ldg(in + pos + 2u) : 0u;
-            pos++;
-            acc |= uint64_t(w) << fill;
-            fill += 32;
-        }
-        const uint32_t v = uint32_t(acc) & (0xFFFFFFFFu >> (32u - width));
-        acc >>= width;
-        fill -= width;
-        return v;
-    }
-};
-__device__ __forceinline__ uint64_t remap_get_centered(RemapReader& r, uint64_t u)
-{
-    if (u == 1)
-        return 1;
-    const uint32_t b = 64u - uint32_t(__clzll((long long)(u - 1u)));
-    const uint64_t span = uint64_t(1) << b;
-    const uint64_t longs = 2u * u - span;
-    const uint64_t shorts = span - u;
-    uint64_t val = uint64_t(r.get(b - 1u)) + 1u;
-    if (val > shorts)
-        val = 2u * val + r.get(1u) - shorts - 1u;
-    val += longs >> 1;
-    if (val > u)
-        val -= u;
-    return val;
-}
-
 constexpr int kRemapAlphaThreads = 32;
-constexpr int kRemapStack = 34; // the recursion halves the list: depth <= log2(2^24) + a few
 constexpr int kRemapEncThreads = 256; // 8 warps = 8 blocks per CTA
 
 // codeword of the centred minimal binary code as one LSB-first bit string (host/prelude.hpp put_centered)
