@@ -3553,6 +3553,15 @@ try {
     // Preludes on the device (the counts are no longer needed: their buffer is the coder's scratch), then their sizes
     // are scanned.  The prelude coder (one warp per model) needs only the frequencies, as the encoder does: it runs
     // NEXT TO the encoder on a side stream, and its total comes back while the encoder runs.
+    // table entries per model: beyond the largest symbol of the input, a multiple of 16
+    uint32_t pa_syms;
+    {
+        uint32_t kk;
+        const uint32_t top_sym = method == METHOD_INT ? c->h_small()->max_value
+            : method == METHOD_MSB                    ? msb_map(c->h_small()->max_value, kk)
+                                                      : fold_map(c->h_small()->max_value, f, kk);
+        pa_syms = std::min<uint32_t>(nbins, (top_sym + 1u + 15u) & ~15u);
+    }
     RET(ensure_side_streams(c));
     CU(c, cudaEventRecord(c->ev[6], c->stream));
     CU(c, cudaStreamWaitEvent(c->copy_in, c->ev[6], 0));
@@ -3562,14 +3571,15 @@ try {
     uint64_t* d_pre_off = reinterpret_cast<uint64_t*>(d_pre + size_t(nm) * pre_stride);
     uint32_t* d_pre_bytes = reinterpret_cast<uint32_t*>(d_pre_off + nm);
     {
-        uint32_t pw = kPaPreEncWarps; // warps per CTA: as many as fit (plain ANS: 16 384 bins per model)
-        while (pw > 1 && pa_prelude_enc_smem(nbins, pw) + 2048 > c->max_smem)
+        // (the arrays in shared memory stop behind the largest symbol of the input: half of ANSfold-1's 1024 bins on C4)
+        uint32_t pw = kPaPreEncWarps; // warps per CTA: as many as fit (plain ANS: up to 16 384 bins per model)
+        while (pw > 1 && pa_prelude_enc_smem(pa_syms, pw) + 2048 > c->max_smem)
             pw >>= 1;
-        const size_t smem = pa_prelude_enc_smem(nbins, pw);
+        const size_t smem = pa_prelude_enc_smem(pa_syms, pw);
         CU(c, cudaFuncSetAttribute(pa_prelude_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
         const uint32_t per_sm = uint32_t(std::max<size_t>(1, std::min<size_t>(8, (c->max_smem_sm - 4096) / (smem + 1024))));
         const uint32_t grid = std::min<uint32_t>((nm + pw - 1) / pw, uint32_t(c->num_sms) * per_sm);
-        pa_prelude_encode_kernel<<<grid, pw * 32, smem, c->copy_in>>>(c->pa_nfreqs.as<uint32_t>(), nbins, nm, d_lg, d_pre, pre_stride, d_pre_bytes);
+        pa_prelude_encode_kernel<<<grid, pw * 32, smem, c->copy_in>>>(c->pa_nfreqs.as<uint32_t>(), nbins, pa_syms, nm, d_lg, d_pre, pre_stride, d_pre_bytes);
     }
     scan_block_sizes_kernel<<<1, 1024, 0, c->copy_in>>>(d_pre_bytes, nm, d_pre_off, c->d_totals_b(), nullptr);
     c->stats.launches += 2;
@@ -3600,13 +3610,7 @@ try {
     a.pa_table_stride = nbins;
     a.pa_nfreqs = c->pa_nfreqs.as<uint32_t>();
     a.pa_nbins = nbins;
-    {
-        uint32_t kk;
-        const uint32_t top_sym = method == METHOD_INT ? c->h_small()->max_value
-            : method == METHOD_MSB                    ? msb_map(c->h_small()->max_value, kk)
-                                                      : fold_map(c->h_small()->max_value, f, kk);
-        a.pa_syms = std::min<uint32_t>(nbins, (top_sym + 1u + 15u) & ~15u);
-    }
+    a.pa_syms = pa_syms;
     const uint32_t n_tasks = (nm + 7) / 8;
     PaLaunch pl = pa_launch_shape(c, size_t(kPaRcpN) * 8, size_t(8) * pa_enc_group_bytes(a.pa_syms), n_tasks);
     const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && max_lg <= 16u && pl.warps >= 2u;

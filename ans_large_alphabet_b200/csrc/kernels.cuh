@@ -1684,29 +1684,30 @@ __host__ __device__ inline size_t pa_prelude_enc_smem(uint32_t nbins, uint32_t w
 // (pre-order) and the segment it splits follow from p and n alone, and its bounds are the entries next to that segment.
 // So the lanes code 32 consecutive nodes at a time, a warp scan of the code lengths gives the bit positions, and the
 // words are assembled in shared memory (the same scheme as remap_alpha_kernel, remap_kernels.cuh).
-__global__ void __launch_bounds__(kPaPreEncWarps * 32) pa_prelude_encode_kernel(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t n_models,
-    const uint8_t* __restrict__ log2_frame, uint8_t* __restrict__ pre, uint32_t pre_stride, uint32_t* __restrict__ pre_bytes)
+// `scan_bins` <= nbins: no model has a symbol at or beyond it (the rows are nbins wide, the shared-memory arrays scan_bins).
+__global__ void __launch_bounds__(kPaPreEncWarps * 32) pa_prelude_encode_kernel(const uint32_t* __restrict__ nfreqs, uint32_t nbins, uint32_t scan_bins,
+    uint32_t n_models, const uint8_t* __restrict__ log2_frame, uint8_t* __restrict__ pre, uint32_t pre_stride, uint32_t* __restrict__ pre_bytes)
 {
     extern __shared__ __align__(16) uint32_t pa_pre_smem[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    uint32_t* v = pa_pre_smem + size_t(warp) * (nbins + 72u); // the prefix sums the code is built on
-    uint32_t* buf = v + nbins;                                 // 72 words of bit stream under construction
+    uint32_t* v = pa_pre_smem + size_t(warp) * (scan_bins + 72u); // the prefix sums the code is built on
+    uint32_t* buf = v + scan_bins;                                 // 72 words of bit stream under construction
     const uint32_t cta_warps = blockDim.x >> 5; // (large alphabets leave room for fewer than kPaPreEncWarps)
     for (uint32_t m = blockIdx.x * cta_warps + warp; m < n_models; m += gridDim.x * cta_warps) {
         const uint32_t* nf = nfreqs + uint64_t(m) * nbins;
         __syncwarp();
         uint32_t carry = 0, max_sym = 0;
-        for (uint32_t base = 0; base < nbins; base += 32u) {
+        for (uint32_t base = 0; base < scan_bins; base += 32u) {
             const uint32_t s = base + lane;
-            const uint32_t f = s < nbins ? __ldg(nf + s) : 0u;
-            uint32_t x = s < nbins ? f + (s ? 1u : 0u) : 0u;
+            const uint32_t f = s < scan_bins ? __ldg(nf + s) : 0u;
+            uint32_t x = s < scan_bins ? f + (s ? 1u : 0u) : 0u;
             for (int o = 1; o < 32; o <<= 1) {
                 const uint32_t up = __shfl_up_sync(0xffffffffu, x, o);
                 if (lane >= uint32_t(o))
                     x += up;
             }
             x += carry;
-            if (s < nbins)
+            if (s < scan_bins)
                 v[s] = x;
             carry = __shfl_sync(0xffffffffu, x, 31);
             const uint32_t present = __ballot_sync(0xffffffffu, f != 0u);
