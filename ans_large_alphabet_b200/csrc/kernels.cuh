@@ -1471,7 +1471,7 @@ __global__ void __launch_bounds__(kPaSortWarps * 32) pa_sort_kernel(const uint32
         const uint32_t* row = counts + uint64_t(model) * nbins;
         uint32_t* out = nfreqs + uint64_t(model) * nbins;
         // pass 1: how many symbols occur, how many have each small count, the large ones aside
-        uint32_t sigma = 0, n_big = 0, max_small = 0;
+        uint32_t sigma = 0, n_big = 0, max_small = 0, used_bins = 0; // used_bins: behind the last chunk that holds a count
         uint64_t total = 0;
         for (uint32_t base = 0; base < nbins; base += 32u) {
             const uint32_t b = base + lane;
@@ -1479,7 +1479,9 @@ __global__ void __launch_bounds__(kPaSortWarps * 32) pa_sort_kernel(const uint32
             if (b < nbins)
                 out[b] = 0; // the winning fit only writes the symbols that occur
             const bool small = cnt != 0u && cnt < kPaSortSmall, big = cnt >= kPaSortSmall;
-            sigma += uint32_t(__popc(__ballot_sync(0xffffffffu, cnt != 0u)));
+            const uint32_t present = __ballot_sync(0xffffffffu, cnt != 0u);
+            sigma += uint32_t(__popc(present));
+            used_bins = present ? base + 32u : used_bins;
             total += cnt;
             if (small) {
                 atomicAdd(hist + cnt, 1u);
@@ -1519,7 +1521,7 @@ __global__ void __launch_bounds__(kPaSortWarps * 32) pa_sort_kernel(const uint32
         const uint32_t first = n_keys - sigma;
         uint64_t* gk = gkeys + uint64_t(model) * n_keys + first;
         double acc = 0.0;
-        for (uint32_t base = 0; base < nbins; base += 32u) {
+        for (uint32_t base = 0; base < used_bins; base += 32u) {
             const uint32_t b = base + lane;
             const uint32_t cnt = b < nbins ? __ldg(row + b) : 0u;
             const bool small = cnt != 0u && cnt < kPaSortSmall;
