@@ -3850,7 +3850,9 @@ int pa_decompress_core(b200ans_ctx* c, int method, uint32_t f, uint32_t* d_dst, 
             break;
     }
     // (frames of 2^16 slots go to the slot tables: cum[] is 16 bits wide and the searches compare it)
-    const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && c->h_small()->max_log2 <= 15u && pl.warps >= 2u;
+    // ... and only when at most two rounds of tasks result: with a handful of resident warps per SM (plain ANS over 6000
+    // ranks: two) the latency-bound shared-memory decoder loses to the slot tables in global memory (12.4 against 7.0 ms)
+    const bool smem_tables = c->kernel_path != B200ANS_PATH_GROUP && c->h_small()->max_log2 <= 15u && pl.warps >= 2u && 2u * pl.max_warps >= want_warps;
     set_name(c->stats.decode_kernel, smem_tables ? "pa_smem_decode_kernel" : "decode_kernel");
     if (smem_tables && h_src && runs > 1) {
         // one launch per run of models; the pointers of the argument block move to the run's first model

@@ -2,7 +2,6 @@
 # r02a: exploratory. Host facts, the 22-warp encoder shape (parity + timing), C3 / C3r / 2^32-symbol C5 on one GPU.
 tag=${1:-r02a}; out=gpurun_out/$tag; mkdir -p $out
 { nproc; free -g; lscpu | head -20; nvidia-smi; ulimit -l; } > $out/host.txt 2>&1
-WLS="fold1 fold2 ans30" bash tools/gpu_wide.sh $tag > $out/wide.txt 2>&1; tail -12 $out/wide.txt
 for wl in c3 c3r; do
   timeout 900 python tools/kbench.py --workloads $wl --paths 0 --reps 2 > $out/kbench_$wl.txt 2>&1; echo "$wl exit $?"; tail -1 $out/kbench_$wl.txt | cut -c1-400
 done

@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--model-syms", default="8192,16384,65536")
     ap.add_argument("--workload", default="fold1")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--path", type=int, default=0, help="b200ans_set_kernel_path: 0 auto, 1 group kernels / global tables")
     ap.add_argument("--remap-method", default="msb", choices=["msb", "int"], help="coder of the remapped blocks: ANSmsb or plain ANS")
     ap.add_argument("--remap", action="store_true", help="the driver's dense-rank remap in front of ANSmsb (b200ans_pa_remap_*), with the "
                     "reference driver's own BPI on a sample of blocks beside ours")
@@ -30,6 +31,7 @@ def main():
     dev = torch.device("cuda", 0)
     stream = torch.cuda.Stream(device=dev)
     codec = P.Codec(device=0, block_syms=8192, stream=stream.cuda_stream)
+    codec.set_kernel_path(args.path)
     method, f, gen, _, desc = bench.WORKLOADS[args.workload]
     n = args.n
     d_in = bench.generate_device(gen, n, dev, seed=0)
