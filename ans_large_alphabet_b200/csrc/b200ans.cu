@@ -2966,6 +2966,12 @@ try {
     if (!c->ipc_buf)
         return c->fail(B200ANS_E_ARG, "comm_ipc_attach: b200ans_comm_ipc_export comes first");
     CU(c, cudaSetDevice(c->device));
+    for (int p = 0; p < c->ipc_world; p++) // attached before: those mappings go first
+        if (p != c->ipc_rank && c->ipc_peer[p]) {
+            cudaIpcCloseMemHandle(c->ipc_peer[p]);
+            c->ipc_peer[p] = nullptr;
+        }
+    c->ipc_world = 0;
     for (int p = 0; p < world; p++) {
         if (p == rank) {
             c->ipc_peer[p] = c->ipc_buf;
