@@ -6,6 +6,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
@@ -14,6 +15,7 @@
 #include <new>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../host/fold.hpp"
@@ -163,6 +165,14 @@ struct b200ans_ctx {
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t ev_in[kPipeChunks + 1] {}, ev_dec[kPipeChunks] {};
     bool pa3_off = false; // pa_compress: the retry without the lane-per-block encoder is running
+    // pageable host buffers (what std::vector hands the C++ adaptors): large copies go through page-locked staging
+    // buffers filled / drained by a few host threads (staged_h2d / staged_d2h)
+    static constexpr int kStageThreads = 8;   // at most (B200ANS_STAGE_THREADS picks fewer)
+    static constexpr size_t kStageChunk = size_t(8) << 20;
+    uint8_t* stage_buf[kStageThreads][2] {};
+    cudaStream_t stage_st[kStageThreads] {};
+    cudaEvent_t stage_ev[kStageThreads][2] {}, stage_done[kStageThreads] {}, stage_fork = nullptr;
+    bool stage_ready = false;
     // histogram exchange over NVLink peer memory (b200ans_comm_ipc_export / _attach): my exchange buffer, everybody's
     // (ipc_peer[ipc_rank] is mine), how many exchanges have run
     static constexpr int kIpcMaxWorld = 16;
@@ -410,6 +420,20 @@ extern "C" void b200ans_destroy(b200ans_ctx* c)
         cudaFreeHost(c->pa_pinned);
     if (c->comm && c->own_comm && nccl_api().ok)
         nccl_api().CommDestroy(c->comm);
+    for (int w = 0; w < b200ans_ctx::kStageThreads; w++) {
+        for (int b = 0; b < 2; b++) {
+            if (c->stage_buf[w][b])
+                cudaFreeHost(c->stage_buf[w][b]);
+            if (c->stage_ev[w][b])
+                cudaEventDestroy(c->stage_ev[w][b]);
+        }
+        if (c->stage_done[w])
+            cudaEventDestroy(c->stage_done[w]);
+        if (c->stage_st[w])
+            cudaStreamDestroy(c->stage_st[w]);
+    }
+    if (c->stage_fork)
+        cudaEventDestroy(c->stage_fork);
     if (c->ipc_buf) {
         for (int p = 0; p < c->ipc_world; p++)
             if (p != c->ipc_rank && c->ipc_peer[p])
@@ -3112,6 +3136,136 @@ B200ANS_CATCH_INT
 // ---- host buffers: what methods.hpp's encode()/decode() hand over ----------------------------
 namespace {
 
+// ---- pageable host buffers -----------------------------------------------------------------------------------------
+// cudaMemcpyAsync on pageable memory is staged by the driver at about 11 GB/s (profiles/r02aq: 11.2 GB/s end to end
+// against 46.5 GB/s with page-locked buffers) -- and that is the memory the reference's callers hold (std::vector,
+// methods.hpp:535-546).  Copies of 64 MiB and more on unregistered memory therefore go through the library's own
+// page-locked staging buffers: kStageThreads host threads each move every kStageThreads-th 16 MiB chunk, double-buffered,
+// on a stream of their own, so that the host-side memcpy of one chunk overlaps the PCIe transfer of the others.
+// B200ANS_NO_STAGING=1 keeps the plain copies.
+bool host_pageable(const void* p)
+{
+    cudaPointerAttributes a {};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return true;
+    }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+bool use_staging(const void* host, size_t bytes)
+{
+    return bytes >= (size_t(64) << 20) && !env_int("B200ANS_NO_STAGING", 0) && host_pageable(host);
+}
+
+int ensure_stager(b200ans_ctx* c)
+{
+    if (c->stage_ready)
+        return B200ANS_OK;
+    for (int w = 0; w < b200ans_ctx::kStageThreads; w++) {
+        CU(c, cudaStreamCreateWithFlags(&c->stage_st[w], cudaStreamNonBlocking));
+        CU(c, cudaEventCreateWithFlags(&c->stage_done[w], cudaEventDisableTiming));
+        for (int b = 0; b < 2; b++) {
+            CU(c, cudaHostAlloc(reinterpret_cast<void**>(&c->stage_buf[w][b]), b200ans_ctx::kStageChunk, cudaHostAllocDefault));
+            CU(c, cudaEventCreateWithFlags(&c->stage_ev[w][b], cudaEventDisableTiming));
+        }
+    }
+    CU(c, cudaEventCreateWithFlags(&c->stage_fork, cudaEventDisableTiming));
+    c->stage_ready = true;
+    return B200ANS_OK;
+}
+
+// host (pageable) -> device, ordered behind everything queued on `stream` so far; `stream` waits for the copies
+int staged_h2d(b200ans_ctx* c, void* d_dst, const void* h_src, size_t bytes, cudaStream_t stream)
+{
+    RET(ensure_stager(c));
+    const int T = std::max(1, std::min(int(b200ans_ctx::kStageThreads), env_int("B200ANS_STAGE_THREADS", b200ans_ctx::kStageThreads)));
+    constexpr size_t CH = b200ans_ctx::kStageChunk;
+    const size_t n_chunks = (bytes + CH - 1) / CH;
+    CU(c, cudaEventRecord(c->stage_fork, stream));
+    std::atomic<int> bad { 0 };
+    std::thread workers[b200ans_ctx::kStageThreads];
+    for (int w = 0; w < T; w++)
+        workers[w] = std::thread([=, &bad]() {
+            if (cudaSetDevice(c->device) != cudaSuccess || cudaStreamWaitEvent(c->stage_st[w], c->stage_fork, 0) != cudaSuccess) {
+                bad = 1;
+                return;
+            }
+            size_t round = 0;
+            for (size_t k = size_t(w); k < n_chunks; k += T, round++) {
+                const int b = int(round & 1);
+                const size_t at = k * CH, len = std::min(CH, bytes - at);
+                if (round >= 2 && cudaEventSynchronize(c->stage_ev[w][b]) != cudaSuccess) // the copy that last read this buffer
+                    bad = 1;
+                std::memcpy(c->stage_buf[w][b], static_cast<const uint8_t*>(h_src) + at, len);
+                if (cudaMemcpyAsync(static_cast<uint8_t*>(d_dst) + at, c->stage_buf[w][b], len, cudaMemcpyHostToDevice, c->stage_st[w]) != cudaSuccess
+                    || cudaEventRecord(c->stage_ev[w][b], c->stage_st[w]) != cudaSuccess)
+                    bad = 1;
+            }
+            if (cudaEventRecord(c->stage_done[w], c->stage_st[w]) != cudaSuccess)
+                bad = 1;
+        });
+    for (int w = 0; w < T; w++)
+        workers[w].join();
+    if (bad) {
+        cudaGetLastError();
+        return c->fail(B200ANS_E_CUDA, "staged host-to-device copy failed");
+    }
+    for (int w = 0; w < T; w++)
+        CU(c, cudaStreamWaitEvent(stream, c->stage_done[w], 0));
+    return B200ANS_OK;
+}
+
+// device -> host (pageable), ordered behind everything queued on `stream` so far; when `ready` is given, the chunk that
+// ends at byte offset `end` also waits for ready(end) (an event recorded on some stream, or null).  Returns with the
+// bytes in place.
+template <class Ready> int staged_d2h(b200ans_ctx* c, void* h_dst, const void* d_src, size_t bytes, cudaStream_t stream, Ready ready)
+{
+    RET(ensure_stager(c));
+    const int T = std::max(1, std::min(int(b200ans_ctx::kStageThreads), env_int("B200ANS_STAGE_THREADS", b200ans_ctx::kStageThreads)));
+    constexpr size_t CH = b200ans_ctx::kStageChunk;
+    const size_t n_chunks = (bytes + CH - 1) / CH;
+    CU(c, cudaEventRecord(c->stage_fork, stream));
+    std::atomic<int> bad { 0 };
+    std::thread workers[b200ans_ctx::kStageThreads];
+    for (int w = 0; w < T; w++)
+        workers[w] = std::thread([=, &bad]() {
+            if (cudaSetDevice(c->device) != cudaSuccess || cudaStreamWaitEvent(c->stage_st[w], c->stage_fork, 0) != cudaSuccess) {
+                bad = 1;
+                return;
+            }
+            size_t round = 0, prev_at = 0, prev_len = 0;
+            int prev_b = -1;
+            auto drain = [&]() { // the chunk before this one: wait for its copy, hand it to the caller's buffer
+                if (prev_b < 0)
+                    return;
+                if (cudaEventSynchronize(c->stage_ev[w][prev_b]) != cudaSuccess)
+                    bad = 1;
+                std::memcpy(static_cast<uint8_t*>(h_dst) + prev_at, c->stage_buf[w][prev_b], prev_len);
+            };
+            for (size_t k = size_t(w); k < n_chunks; k += T, round++) {
+                const int b = int(round & 1);
+                const size_t at = k * CH, len = std::min(CH, bytes - at);
+                cudaEvent_t dep = ready(at + len);
+                if (dep && cudaStreamWaitEvent(c->stage_st[w], dep, 0) != cudaSuccess)
+                    bad = 1;
+                if (cudaMemcpyAsync(c->stage_buf[w][b], static_cast<const uint8_t*>(d_src) + at, len, cudaMemcpyDeviceToHost, c->stage_st[w]) != cudaSuccess
+                    || cudaEventRecord(c->stage_ev[w][b], c->stage_st[w]) != cudaSuccess)
+                    bad = 1;
+                drain(); // (buffer 1 - b is free again after this)
+                prev_b = b, prev_at = at, prev_len = len;
+            }
+            drain();
+        });
+    for (int w = 0; w < T; w++)
+        workers[w].join();
+    if (bad) {
+        cudaGetLastError();
+        return c->fail(B200ANS_E_CUDA, "staged device-to-host copy failed");
+    }
+    return B200ANS_OK;
+}
+
 int compress_host_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, size_t cap, const uint32_t* src, size_t n,
     size_t* out_bytes, bool sharded)
 {
@@ -3122,7 +3276,9 @@ int compress_host_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, siz
     CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
     CU(c, c->io_out.reserve(bound));
     CU(c, cudaEventRecord(c->ev[5], c->stream));
-    if (n)
+    if (n && use_staging(src, n * 4))
+        RET(staged_h2d(c, c->io_in.p, src, n * 4, c->stream));
+    else if (n)
         CU(c, cudaMemcpyAsync(c->io_in.p, src, n * 4, cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaEventRecord(c->ev[6], c->stream));
     size_t bytes = 0;
@@ -3130,7 +3286,9 @@ int compress_host_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, siz
     if (bytes > cap)
         return c->fail(B200ANS_E_CAPACITY, "compress: destination too small");
     CU(c, cudaEventRecord(c->ev[7], c->stream));
-    if (bytes)
+    if (bytes && use_staging(dst, bytes))
+        RET(staged_d2h(c, dst, c->io_out.p, bytes, c->stream, [](size_t) { return cudaEvent_t(nullptr); }));
+    else if (bytes)
         CU(c, cudaMemcpyAsync(dst, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaEventRecord(c->ev[3], c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
@@ -3249,6 +3407,8 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
     CU(c, cudaGetLastError());
     CU(c, cudaMemsetAsync(c->d_err(), 0, 4, c->stream));
     CU(c, cudaEventRecord(c->ev[0], c->stream));
+    const bool staged_out = use_staging(dst, n * 4); // pageable destination: the symbols leave through the staging threads
+    uint64_t run_out_end[b200ans_ctx::kPipeChunks] {};
     for (int r = 0; r < runs; r++) {
         const uint32_t b0 = r ? run_end[r - 1] : 0, b1 = run_end[r];
         const uint64_t s0 = uint64_t(b0) * h.block_syms, s1 = std::min<uint64_t>(n, uint64_t(b1) * h.block_syms);
@@ -3258,9 +3418,19 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
         c->dec_words_aligned = false;
         RET(rc);
         CU(c, cudaEventRecord(c->ev_dec[r], c->stream));
-        CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_dec[r], 0));
-        CU(c, cudaMemcpyAsync(dst + s0, d_dst + s0, size_t(s1 - s0) * 4, cudaMemcpyDeviceToHost, c->copy_out));
+        run_out_end[r] = s1 * 4;
+        if (!staged_out) {
+            CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_dec[r], 0));
+            CU(c, cudaMemcpyAsync(dst + s0, d_dst + s0, size_t(s1 - s0) * 4, cudaMemcpyDeviceToHost, c->copy_out));
+        }
     }
+    if (staged_out) // a chunk of the output leaves once the run that decodes its last byte is done
+        RET(staged_d2h(c, dst, d_dst, n * 4, c->copy_out, [&](size_t end) {
+            int r = 0;
+            while (r < runs - 1 && run_out_end[r] < end)
+                r++;
+            return c->ev_dec[r];
+        }));
     CU(c, cudaEventRecord(c->ev[1], c->stream));
     CU(c, cudaEventRecord(c->ev[6], c->copy_out));
     CU(c, cudaStreamWaitEvent(c->stream, c->ev[6], 0)); // the call's work ends on `stream`, as every other entry point's
