@@ -83,7 +83,9 @@ namespace detail {
     // cross_entropy(P, Q) for normalised frequencies Q: log2(double(Q[i]) / m) is the same call with the same
     // argument for every symbol that got the same share, so it is evaluated once per distinct small Q[i]
     // (same bits, fewer libm calls: the tail of a large alphabet shares a handful of values).
-    inline double cross_entropy_shared_log(const std::vector<uint64_t>& P, const std::vector<uint32_t>& Q)
+    // `prob` (optional): P[i] / n for every i, computed once by the caller -- the same doubles this function would
+    // compute (adjust_freqs evaluates up to a dozen candidate frames against the same counts)
+    inline double cross_entropy_shared_log(const std::vector<uint64_t>& P, const std::vector<uint32_t>& Q, const std::vector<double>* prob = nullptr)
     {
         constexpr uint32_t kMemo = 4096;
         static thread_local double memo[kMemo];
@@ -93,13 +95,13 @@ namespace detail {
             std::fill(stamp, stamp + kMemo, 0u);
             epoch = 1;
         }
-        const double n = int_accumulated_sum(P);
+        const double n = prob ? 0.0 : int_accumulated_sum(P);
         const double m = int_accumulated_sum(Q);
         double acc = 0.0;
         for (size_t i = 0; i < P.size(); i++) {
             if (P[i] == 0 || Q[i] == 0)
                 continue;
-            const double p = double(P[i]) / n;
+            const double p = prob ? (*prob)[i] : double(P[i]) / n;
             const uint32_t share = Q[i];
             double lg;
             if (share < kMemo) {
@@ -221,6 +223,7 @@ inline std::vector<uint32_t> adjust_freqs(
     for (auto& v : cand)
         v.assign(size_t(largest_sym) + 1, 0);
     std::vector<uint32_t> last_good(size_t(largest_sym) + 1, 0);
+    std::vector<double> prob;
     for (;;) {
         bool failed[kBatch];
         detail::scale_freqs_batch<kBatch>(cand, failed, freqs, order, int64_t(frame), sigma, freq_sum);
@@ -231,7 +234,13 @@ inline std::vector<uint32_t> adjust_freqs(
             const uint32_t top = *std::max_element(cur.begin(), cur.end());
             if (require_u16 && top >= std::numeric_limits<uint16_t>::max()) // (the reference computes XH first; it has no effect here)
                 return last_good;
-            const double XH = detail::cross_entropy_shared_log(freqs, cur);
+            if (prob.empty()) { // P[i] / n, once for all candidate frames
+                const double n = detail::int_accumulated_sum(freqs);
+                prob.resize(freqs.size());
+                for (size_t i = 0; i < freqs.size(); i++)
+                    prob[i] = double(freqs[i]) / n;
+            }
+            const double XH = detail::cross_entropy_shared_log(freqs, cur, &prob);
             if (XH < limit)
                 return std::move(cur);
             last_good = cur;
