@@ -3185,7 +3185,9 @@ int staged_h2d(b200ans_ctx* c, void* d_dst, const void* h_src, size_t bytes, cud
     CU(c, cudaEventRecord(c->stage_fork, stream));
     std::atomic<int> bad { 0 };
     std::thread workers[b200ans_ctx::kStageThreads];
-    for (int w = 0; w < T; w++)
+    int started = 0;
+    try {
+    for (int w = 0; w < T; w++, started++)
         workers[w] = std::thread([=, &bad]() {
             if (cudaSetDevice(c->device) != cudaSuccess || cudaStreamWaitEvent(c->stage_st[w], c->stage_fork, 0) != cudaSuccess) {
                 bad = 1;
@@ -3205,7 +3207,10 @@ int staged_h2d(b200ans_ctx* c, void* d_dst, const void* h_src, size_t bytes, cud
             if (cudaEventRecord(c->stage_done[w], c->stage_st[w]) != cudaSuccess)
                 bad = 1;
         });
-    for (int w = 0; w < T; w++)
+    } catch (...) { // no thread to be had: the chunks of the missing workers stay uncopied, the call fails
+        bad = 1;
+    }
+    for (int w = 0; w < started; w++)
         workers[w].join();
     if (bad) {
         cudaGetLastError();
@@ -3228,7 +3233,9 @@ template <class Ready> int staged_d2h(b200ans_ctx* c, void* h_dst, const void* d
     CU(c, cudaEventRecord(c->stage_fork, stream));
     std::atomic<int> bad { 0 };
     std::thread workers[b200ans_ctx::kStageThreads];
-    for (int w = 0; w < T; w++)
+    int started = 0;
+    try {
+    for (int w = 0; w < T; w++, started++)
         workers[w] = std::thread([=, &bad]() {
             if (cudaSetDevice(c->device) != cudaSuccess || cudaStreamWaitEvent(c->stage_st[w], c->stage_fork, 0) != cudaSuccess) {
                 bad = 1;
@@ -3257,7 +3264,10 @@ template <class Ready> int staged_d2h(b200ans_ctx* c, void* h_dst, const void* d
             }
             drain();
         });
-    for (int w = 0; w < T; w++)
+    } catch (...) { // no thread to be had: the chunks of the missing workers stay uncopied, the call fails
+        bad = 1;
+    }
+    for (int w = 0; w < started; w++)
         workers[w].join();
     if (bad) {
         cudaGetLastError();
@@ -3276,9 +3286,8 @@ int compress_host_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, siz
     CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
     CU(c, c->io_out.reserve(bound));
     CU(c, cudaEventRecord(c->ev[5], c->stream));
-    if (n && use_staging(src, n * 4))
-        RET(staged_h2d(c, c->io_in.p, src, n * 4, c->stream));
-    else if (n)
+    // (a staged copy that fails -- no thread, no page-locked memory -- is redone as a plain one)
+    if (n && !(use_staging(src, n * 4) && staged_h2d(c, c->io_in.p, src, n * 4, c->stream) == B200ANS_OK))
         CU(c, cudaMemcpyAsync(c->io_in.p, src, n * 4, cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaEventRecord(c->ev[6], c->stream));
     size_t bytes = 0;
@@ -3286,9 +3295,7 @@ int compress_host_impl(b200ans_ctx* c, int method, uint32_t f, uint8_t* dst, siz
     if (bytes > cap)
         return c->fail(B200ANS_E_CAPACITY, "compress: destination too small");
     CU(c, cudaEventRecord(c->ev[7], c->stream));
-    if (bytes && use_staging(dst, bytes))
-        RET(staged_d2h(c, dst, c->io_out.p, bytes, c->stream, [](size_t) { return cudaEvent_t(nullptr); }));
-    else if (bytes)
+    if (bytes && !(use_staging(dst, bytes) && staged_d2h(c, dst, c->io_out.p, bytes, c->stream, [](size_t) { return cudaEvent_t(nullptr); }) == B200ANS_OK))
         CU(c, cudaMemcpyAsync(dst, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaEventRecord(c->ev[3], c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
@@ -3424,13 +3431,16 @@ int decompress_pipelined(b200ans_ctx* c, int method, uint32_t f, uint32_t* dst, 
             CU(c, cudaMemcpyAsync(dst + s0, d_dst + s0, size_t(s1 - s0) * 4, cudaMemcpyDeviceToHost, c->copy_out));
         }
     }
-    if (staged_out) // a chunk of the output leaves once the run that decodes its last byte is done
-        RET(staged_d2h(c, dst, d_dst, n * 4, c->copy_out, [&](size_t end) {
-            int r = 0;
-            while (r < runs - 1 && run_out_end[r] < end)
-                r++;
-            return c->ev_dec[r];
-        }));
+    if (staged_out // a chunk of the output leaves once the run that decodes its last byte is done
+        && staged_d2h(c, dst, d_dst, n * 4, c->copy_out, [&](size_t end) {
+               int r = 0;
+               while (r < runs - 1 && run_out_end[r] < end)
+                   r++;
+               return c->ev_dec[r];
+           }) != B200ANS_OK) {
+        CU(c, cudaStreamWaitEvent(c->copy_out, c->ev_dec[runs - 1], 0)); // (redone as one plain copy behind the last run)
+        CU(c, cudaMemcpyAsync(dst, d_dst, n * 4, cudaMemcpyDeviceToHost, c->copy_out));
+    }
     CU(c, cudaEventRecord(c->ev[1], c->stream));
     CU(c, cudaEventRecord(c->ev[6], c->copy_out));
     CU(c, cudaStreamWaitEvent(c->stream, c->ev[6], 0)); // the call's work ends on `stream`, as every other entry point's
