@@ -3139,7 +3139,7 @@ namespace {
 // ---- pageable host buffers -----------------------------------------------------------------------------------------
 // cudaMemcpyAsync on pageable memory is staged by the driver at about 11 GB/s (profiles/r02aq: 11.2 GB/s end to end
 // against 46.5 GB/s with page-locked buffers) -- and that is the memory the reference's callers hold (std::vector,
-// methods.hpp:535-546).  Copies of 64 MiB and more on unregistered memory therefore go through the library's own
+// methods.hpp:535-546).  Copies of 256 MiB and more on unregistered memory therefore go through the library's own
 // page-locked staging buffers: kStageThreads host threads each move every kStageThreads-th 16 MiB chunk, double-buffered,
 // on a stream of their own, so that the host-side memcpy of one chunk overlaps the PCIe transfer of the others.
 // B200ANS_NO_STAGING=1 keeps the plain copies.
@@ -3155,7 +3155,9 @@ bool host_pageable(const void* p)
 
 bool use_staging(const void* host, size_t bytes)
 {
-    return bytes >= (size_t(64) << 20) && !env_int("B200ANS_NO_STAGING", 0) && host_pageable(host);
+    // (from 256 MiB: setting the staging buffers up once costs about what a plain copy of that size does)
+    const size_t min_bytes = size_t(std::max(1, env_int("B200ANS_STAGE_MIN_MB", 256))) << 20; // (testing: a lower threshold)
+    return bytes >= min_bytes && !env_int("B200ANS_NO_STAGING", 0) && host_pageable(host);
 }
 
 int ensure_stager(b200ans_ctx* c)
@@ -4145,14 +4147,16 @@ try {
     const size_t bound = std::min(b200ans_pa_compress_bound(c, method, model_syms, n), std::max<size_t>(cap + 64, 4096));
     CU(c, c->io_in.reserve(std::max<size_t>(n * 4, 16)));
     CU(c, c->io_out.reserve(bound));
-    if (n)
+    // (pageable buffers: large copies through the staging threads, as in compress_host_impl)
+    if (n && !(use_staging(src, n * 4) && staged_h2d(c, c->io_in.p, src, n * 4, c->stream) == B200ANS_OK))
         CU(c, cudaMemcpyAsync(c->io_in.p, src, n * 4, cudaMemcpyHostToDevice, c->stream));
     size_t bytes = 0;
     RET(b200ans_pa_compress_device(c, method, f, model_syms, c->io_out.as<uint8_t>(), std::min(bound, c->io_out.cap),
         c->io_in.as<uint32_t>(), n, &bytes));
     if (bytes > cap)
         return c->fail(B200ANS_E_CAPACITY, "pa_compress: destination too small");
-    CU(c, cudaMemcpyAsync(dst, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    if (!(use_staging(dst, bytes) && staged_d2h(c, dst, c->io_out.p, bytes, c->stream, [](size_t) { return cudaEvent_t(nullptr); }) == B200ANS_OK))
+        CU(c, cudaMemcpyAsync(dst, c->io_out.p, bytes, cudaMemcpyDeviceToHost, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
     *out_bytes = bytes;
     return B200ANS_OK;
